@@ -243,7 +243,7 @@ static inline void roughplastic_sample(const Bsdf &b, V3 wi, float s1, V2 s2, BS
     bs.pdf = roughplastic_pdf(b, wi, bs.wo, active);
     active = active && bs.pdf > 0.f;
     V3 result = roughplastic_eval(b, wi, bs.wo, active);
-    w = mask3(V3(result.x / bs.pdf, result.y / bs.pdf, result.z / bs.pdf), active);
+    w = mask3(result / bs.pdf, active);   // Spectrum / Float -> result * rcp(pdf)
 }
 static inline void roughplastic_eval_pdf(const Bsdf &b, V3 wi, V3 wo, V3 &f, float &pdf) {
     float ci = wi.z, co = wo.z;

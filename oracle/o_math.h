@@ -54,7 +54,8 @@ static inline V3 operator+(V3 a, V3 b) { return { a.x + b.x, a.y + b.y, a.z + b.
 static inline V3 operator-(V3 a, V3 b) { return { a.x - b.x, a.y - b.y, a.z - b.z }; }
 static inline V3 operator*(V3 a, V3 b) { return { a.x * b.x, a.y * b.y, a.z * b.z }; }
 static inline V3 operator*(V3 a, float s) { return { a.x * s, a.y * s, a.z * s }; }
-static inline V3 operator/(V3 a, float s) { return { a.x / s, a.y / s, a.z / s }; }
+// drjit/array_router.h:218-232: (array of depth 2) / (Float) is lowered to a * rcp(b)
+static inline V3 operator/(V3 a, float s) { float r = rcp(s); return { a.x * r, a.y * r, a.z * r }; }
 static inline V3 operator-(V3 a) { return { -a.x, -a.y, -a.z }; }
 static inline V3 fmadd(V3 a, float b, V3 c) { return { fmadd(a.x, b, c.x), fmadd(a.y, b, c.y), fmadd(a.z, b, c.z) }; }
 static inline V3 fmadd(V3 a, V3 b, V3 c) { return { fmadd(a.x, b.x, c.x), fmadd(a.y, b.y, c.y), fmadd(a.z, b.z, c.z) }; }
