@@ -1,0 +1,124 @@
+/* amvpt.h -- C ABI of the B200-native AMVPT render path (libamvpt_b200.so).
+ *
+ * The reference (xacond00/mitsuba3-amvpt, Mitsuba 3.6.4 + the `mvpath` integrator) has no C-level operator
+ * interface: plugins export only `plugin_name()` / `plugin_descr()` (include/mitsuba/core/class.h:225-230) and
+ * everything else is C++ ABI templated on <Float, Spectrum>.  The entry points below are what an FFI for this path
+ * binds; each one names the reference interface it replaces.  INTEGRATION.md shows the C++ plugin shim a maintainer
+ * would add (an `Integrator` subclass whose render() forwards to amvpt_render()) and the ctypes binding used by the
+ * tests.  Conventions: plain pointers and sizes, caller-owned output buffers, int return codes (0 = ok, negative =
+ * error; amvpt_last_error() returns the thread-local message, mirroring the reference's Throw(...) strings), one
+ * render at a time per scene handle.  All matrices are row-major.  No CPU fallback exists: every compute entry point
+ * fails with AMVPT_ERR_CUDA when no sm_100a device is usable.
+ */
+#ifndef AMVPT_H
+#define AMVPT_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define AMVPT_OK 0
+#define AMVPT_ERR_INVALID (-1)   /* bad argument / scene description error (reference: Throw -> std::runtime_error) */
+#define AMVPT_ERR_CUDA (-2)      /* CUDA runtime failure or no device */
+#define AMVPT_ERR_IO (-3)        /* file not found / parse error */
+
+typedef struct amvpt_scene amvpt_scene;
+
+/* BSDF plugin parameters (src/bsdfs/{diffuse,conductor,dielectric,roughconductor,roughdielectric,roughplastic}.cpp
+ * constructors; `twosided` = wrapped in src/bsdfs/twosided.cpp).  type: 0 diffuse, 1 conductor, 2 dielectric,
+ * 3 roughconductor, 4 roughdielectric, 5 roughplastic.  distr: 0 beckmann, 1 ggx. */
+typedef struct amvpt_bsdf_desc {
+    int32_t type, twosided, distr, nonlinear;
+    float reflectance[3], eta[3], k[3], specular_reflectance[3], specular_transmittance[3];
+    float int_ior, ext_ior, alpha_u, alpha_v;
+} amvpt_bsdf_desc;
+
+/* `grid` multi-sensor over a perspective / thinlens sub-camera (src/sensors/grid.cpp:84-236,
+ * src/sensors/perspective.cpp:139-181, src/sensors/thinlens.cpp:152-187).  res_x / res_y = quilt size.
+ * fov_axis: 0 x, 1 y, 2 diagonal, 3 smaller, 4 larger (src/render/sensor.cpp:177-231). */
+typedef struct amvpt_grid_sensor_desc {
+    int32_t thinlens, fov_axis; uint32_t grid_x, grid_y, res_x, res_y; int32_t reverse_x, reverse_y;
+    int32_t use_cone, cam_center;
+    double to_world[16], fov;
+    float near_clip, far_clip, focus_distance, aperture_radius, cone_deg, cam_dist;
+    float cam_dir[3], cam_off[3];
+} amvpt_grid_sensor_desc;
+
+/* `mvpath` integrator parameters (src/integrators/mvpath.h:120-129; MonteCarloIntegrator
+ * src/render/integrator.cpp:503-520) + independent sampler seed / sample_count (src/samplers/independent.cpp). */
+typedef struct amvpt_integrator_desc {
+    int64_t max_depth; uint32_t rr_depth; int32_t hide_emitters; uint32_t spp_pass_lim;
+    uint32_t sampler_seed, sample_count;
+} amvpt_integrator_desc;
+
+/* Integrator::render(scene, sensor, seed, spp, develop, evaluate) arguments (include/mitsuba/render/integrator.h:77-96)
+ * plus the build-defined extensions (view sharding, scheduler choice, adaptive allocation). */
+typedef struct amvpt_render_desc {
+    uint32_t seed, spp;
+    int32_t scheduler;             /* 0 warp batches, 1 persistent + path regeneration (default), 2 wavefront */
+    int32_t collect_stats;         /* count rays / BVH nodes / triangle tests (slower) */
+    uint32_t rank, world;          /* this process renders the view tiles v with v mod world == rank */
+    int32_t adaptive; float adaptive_threshold; uint32_t adaptive_min_spp;
+    void *stream;                  /* cudaStream_t or NULL */
+    void (*allreduce)(float *dev, uint32_t n, void *user); void *allreduce_user;   /* stats all-reduce hook (NCCL) */
+} amvpt_render_desc;
+
+typedef struct amvpt_render_stats {
+    double seconds;                /* device time of the pass loop (CUDA events) */
+    uint64_t paths, closest_rays, shadow_rays, bvh_nodes, tri_tests, path_vertices;
+    uint32_t passes, launches, spp_done, pad;
+} amvpt_render_stats;
+
+const char *amvpt_last_error(void);
+int amvpt_device_count(void);
+
+/* ---- scene construction: Scene / Shape / BSDF / Emitter / Sensor plugin constructors --------------------------- */
+int amvpt_scene_create(amvpt_scene **out);
+void amvpt_scene_destroy(amvpt_scene *s);
+/* xml::load_file (src/core/xml.cpp) for the subset of SURVEY.md sec.8b; defines = "key=value" strings (-D) */
+int amvpt_scene_from_xml(const char *path, const char *const *defines, int n_defines, amvpt_scene **out);
+int amvpt_scene_from_xml_string(const char *xml, const char *base_dir, const char *const *defines, int n_defines, amvpt_scene **out);
+int amvpt_scene_add_bsdf(amvpt_scene *s, const amvpt_bsdf_desc *d);                     /* returns BSDF index */
+/* Mesh (src/render/mesh.cpp) with optional vertex normals and optional area emitter radiance (src/emitters/area.cpp) */
+int amvpt_scene_add_mesh(amvpt_scene *s, const float *positions, uint32_t n_vertices, const uint32_t *faces, uint32_t n_faces,
+                         const float *normals, int bsdf, const float *radiance, int flip_normals);   /* returns mesh index */
+int amvpt_scene_set_sensor_grid(amvpt_scene *s, const amvpt_grid_sensor_desc *d);
+/* `batch` multi-sensor (src/sensors/batch.cpp:94-180): n explicit perspective sub-cameras, film = n*res_x by res_y */
+int amvpt_scene_set_sensor_batch(amvpt_scene *s, uint32_t n, uint32_t res_x, uint32_t res_y, const float *sample_to_camera,
+                                 const float *to_world, float near_clip, float far_clip, int reverse_x);
+int amvpt_scene_set_integrator(amvpt_scene *s, const amvpt_integrator_desc *d);
+/* builds the BVH and uploads everything to `device` (Scene::Scene accel_init, src/render/scene.cpp:70-73) */
+int amvpt_scene_commit(amvpt_scene *s, int device);
+int amvpt_scene_info(amvpt_scene *s, uint32_t *film_w, uint32_t *film_h, uint32_t *n_views, uint32_t *n_prims,
+                     uint32_t *n_bvh_nodes, uint32_t *sample_count);
+int amvpt_scene_get_sensor(amvpt_scene *s, uint32_t index, float *sample_to_camera16, float *to_world16);
+int amvpt_scene_get_bsdf_tables(amvpt_scene *s, int bsdf, float *ext_transmittance64, float *scalars3);
+
+/* ---- the hot path ----------------------------------------------------------------------------------------------- */
+/* MVPathIntegrator::render (src/integrators/mvpath.cpp:7-278): accumulates into the scene's film (RGBW, float32) */
+int amvpt_render(amvpt_scene *s, const amvpt_render_desc *d, amvpt_render_stats *stats_out);
+int amvpt_cancel(amvpt_scene *s);                                        /* Integrator::cancel (integrator.h:303-306) */
+int amvpt_film_clear(amvpt_scene *s);                                    /* Film::prepare / clear (hdrfilm.cpp:245-273) */
+int amvpt_film_raw(amvpt_scene *s, float *rgbw_host);                    /* film storage, H*W*4 floats to host */
+int amvpt_film_develop(amvpt_scene *s, float *rgb_host);                 /* HDRFilm::develop (hdrfilm.cpp:321-408), H*W*3 to host */
+int amvpt_film_develop_device(amvpt_scene *s, float *rgb_dev, void *stream);
+int amvpt_film_device_ptr(amvpt_scene *s, void **rgbw_dev, void **moments_dev);   /* for the NCCL film gather */
+int amvpt_film_add_host(amvpt_scene *s, const float *rgbw_host);         /* ImageBlock::put_block (imageblock.cpp:135-172) */
+
+/* ---- parity taps (used by tests/; same meaning as the oracle's orc_* entry points) ------------------------------ */
+int amvpt_trace_lanes(amvpt_scene *s, uint32_t seed_value, uint32_t spp_per_pass, uint32_t lane_begin, uint32_t n, int trace,
+                      float *sample_pos, float *ray_o, float *ray_d, float *ray_maxt, uint32_t *view, float *radiance,
+                      uint32_t *pixel, uint32_t max_hits, uint32_t *hit_prim, float *hit_t, uint64_t *stats2);
+int amvpt_intersect(amvpt_scene *s, const float *o, const float *d, const float *maxt, uint32_t n, int any_hit,
+                    uint32_t *prim, float *tuv, uint64_t *stats2);
+int amvpt_bsdf_eval_pdf_sample(amvpt_scene *s, int bsdf, const float *wi, const float *wo, const float *s1, const float *s2, uint32_t n,
+                               float *f, float *pdf, float *bs_wo, float *bs_pdf, float *bs_eta, uint32_t *bs_type, float *weight);
+int amvpt_math1(int device, int op, const float *in, uint32_t n, float *out);
+int amvpt_sampler_stream(int device, uint32_t seed_value, uint32_t lane, uint32_t n, float *out);
+/* host-side checks of the BVH the kernels traverse: every triangle inside its leaf box, every child box inside its parent */
+int amvpt_bvh_validate(amvpt_scene *s, uint32_t *max_depth, uint32_t *n_leaves);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,138 @@
+// bvh.cpp -- host-side builder of the device BVH (replaces the reference's three acceleration back ends:
+// ShapeKDTree include/mitsuba/render/kdtree.h, Embree src/render/scene_embree.inl, OptiX src/render/scene_optix.inl).
+// Binned-SAH top-down build over padded triangle boxes, flattened into 64-byte two-child nodes and 48-byte
+// pre-gathered triangles in leaf order (layout: dtypes.h / DESIGN.md).  The tree only prunes: the hit that the
+// traversal reports is decided by Mesh::moeller_trumbore and the global-index tie rule, so it equals the brute-force
+// result as long as every box conservatively contains its triangles -- hence the padding below.
+#include "host.h"
+#include <algorithm>
+#include <cfloat>
+#include <cmath>
+
+namespace amvpt {
+
+namespace {
+struct Box {
+    float lo[3] = { FLT_MAX, FLT_MAX, FLT_MAX }, hi[3] = { -FLT_MAX, -FLT_MAX, -FLT_MAX };
+    void grow(const Box &b) { for (int a = 0; a < 3; ++a) { lo[a] = std::min(lo[a], b.lo[a]); hi[a] = std::max(hi[a], b.hi[a]); } }
+    void grow(const float *p) { for (int a = 0; a < 3; ++a) { lo[a] = std::min(lo[a], p[a]); hi[a] = std::max(hi[a], p[a]); } }
+    float half_area() const { float dx = hi[0] - lo[0], dy = hi[1] - lo[1], dz = hi[2] - lo[2]; return dx * dy + dy * dz + dz * dx; }
+};
+struct Prim { Box b; float c[3]; uint32_t prim; };
+struct TNode { Box b; int32_t left = -1, right = -1; uint32_t first = 0, count = 0; };
+
+const int kBins = 16, kMaxLeaf = 4, kSahDepth = 40;
+
+struct Builder {
+    std::vector<Prim> &prims; std::vector<TNode> nodes;
+    explicit Builder(std::vector<Prim> &p) : prims(p) { nodes.reserve(2 * p.size() + 2); }
+    int32_t build(uint32_t begin, uint32_t end, int depth) {
+        TNode n; Box cb;
+        for (uint32_t i = begin; i < end; ++i) { n.b.grow(prims[i].b); cb.grow(prims[i].c); }
+        n.first = begin; n.count = end - begin;
+        int32_t self = (int32_t) nodes.size(); nodes.push_back(n);
+        if (end - begin <= (uint32_t) kMaxLeaf) return self;
+        int axis = 0; float ext = cb.hi[0] - cb.lo[0];
+        for (int a = 1; a < 3; ++a) if (cb.hi[a] - cb.lo[a] > ext) { ext = cb.hi[a] - cb.lo[a]; axis = a; }
+        uint32_t mid = (begin + end) / 2; bool split = false;
+        if (ext > 0.f && depth < kSahDepth) {
+            struct Bin { Box b; uint32_t n = 0; } bins[kBins];
+            float k = kBins * (1.f - 1e-6f) / ext, lo = cb.lo[axis];
+            auto binof = [&](const Prim &p) { int b = (int) ((p.c[axis] - lo) * k); return std::min(std::max(b, 0), kBins - 1); };
+            for (uint32_t i = begin; i < end; ++i) { Bin &b = bins[binof(prims[i])]; b.n++; b.b.grow(prims[i].b); }
+            float la[kBins], ra[kBins]; uint32_t ln[kBins], rn[kBins];
+            { Box acc; uint32_t c = 0; for (int i = 0; i < kBins; ++i) { c += bins[i].n; if (bins[i].n) acc.grow(bins[i].b); la[i] = c ? acc.half_area() : 0.f; ln[i] = c; } }
+            { Box acc; uint32_t c = 0; for (int i = kBins - 1; i >= 0; --i) { c += bins[i].n; if (bins[i].n) acc.grow(bins[i].b); ra[i] = c ? acc.half_area() : 0.f; rn[i] = c; } }
+            int best = -1; float best_cost = FLT_MAX;
+            for (int i = 0; i < kBins - 1; ++i) {
+                if (!ln[i] || !rn[i + 1]) continue;
+                float c = la[i] * (float) ln[i] + ra[i + 1] * (float) rn[i + 1];
+                if (c < best_cost) { best_cost = c; best = i; }
+            }
+            if (best >= 0) {
+                uint32_t m = (uint32_t) (std::partition(prims.begin() + begin, prims.begin() + end, [&](const Prim &p) { return binof(p) <= best; }) - prims.begin());
+                if (m != begin && m != end) { mid = m; split = true; }
+            }
+        }
+        if (!split) {   // object median along the widest axis: guarantees termination and bounded depth
+            std::nth_element(prims.begin() + begin, prims.begin() + mid, prims.begin() + end,
+                             [axis](const Prim &a, const Prim &b) { return a.c[axis] < b.c[axis] || (a.c[axis] == b.c[axis] && a.prim < b.prim); });
+        }
+        int32_t l = build(begin, mid, depth + 1), r = build(mid, end, depth + 1);
+        nodes[self].left = l; nodes[self].right = r;
+        return self;
+    }
+    int depth_of(int32_t n) const { return nodes[n].left < 0 ? 1 : 1 + std::max(depth_of(nodes[n].left), depth_of(nodes[n].right)); }
+};
+} // namespace
+
+void build_bvh(const Scene &s, float scene_scale, BvhOut &out) {
+    uint32_t np = s.nprims();
+    std::vector<Prim> prims(np);
+    std::vector<uint32_t> prim_mesh(np);
+    // Padding: Moeller-Trumbore decides with a positional error of a few 2^-24 * (|origin| + |vertex| + t); boxes get
+    // an absolute margin tied to the scene scale plus a relative one, far above that error and far below feature size.
+    const float pad_abs = 2e-6f * scene_scale + 1e-30f;
+    uint32_t g = 0;
+    for (size_t mi = 0; mi < s.meshes.size(); ++mi) {
+        const HMesh &m = s.meshes[mi];
+        for (uint32_t f = 0; f < m.nfaces(); ++f, ++g) {
+            Prim &p = prims[g]; p.prim = g; prim_mesh[g] = (uint32_t) mi;
+            Box b; for (int k = 0; k < 3; ++k) b.grow(&m.pos[3 * m.faces[3 * f + k]]);
+            for (int a = 0; a < 3; ++a) {
+                p.c[a] = 0.5f * (b.lo[a] + b.hi[a]);
+                float pad = pad_abs + 1e-5f * std::max(std::fabs(b.lo[a]), std::fabs(b.hi[a])) + 1e-5f * (b.hi[a] - b.lo[a]);
+                b.lo[a] -= pad; b.hi[a] += pad;
+            }
+            p.b = b;
+        }
+    }
+    Builder bl(prims);
+    if (np) bl.build(0, np, 0);
+    if (np && bl.depth_of(0) > AM_STACK_SIZE - 2) AM_THROW("BVH depth %d exceeds the traversal stack", bl.depth_of(0));
+
+    // triangles in leaf order
+    out.tris.resize(3 * (size_t) np); out.prim_to_tri.resize(np);
+    bool any_nrm = false; for (auto &m : s.meshes) any_nrm |= !m.nrm.empty();
+    out.tri_nrm.assign(any_nrm ? 3 * (size_t) np : 0, make_float4(0.f, 0.f, 0.f, 0.f));
+    for (uint32_t i = 0; i < np; ++i) {
+        uint32_t prim = prims[i].prim, mi = prim_mesh[prim]; const HMesh &m = s.meshes[mi]; uint32_t f = prim - m.prim_offset;
+        out.prim_to_tri[prim] = i;
+        for (int k = 0; k < 3; ++k) {
+            const float *p = &m.pos[3 * m.faces[3 * f + k]];
+            uint32_t w = k == 0 ? prim : (k == 1 ? mi : 0u); float wf; memcpy(&wf, &w, 4);
+            out.tris[3 * (size_t) i + k] = make_float4(p[0], p[1], p[2], wf);
+            if (!m.nrm.empty()) { const float *n = &m.nrm[3 * m.faces[3 * f + k]]; out.tri_nrm[3 * (size_t) i + k] = make_float4(n[0], n[1], n[2], 0.f); }
+        }
+    }
+    // flatten: inner nodes numbered in depth-first order, each holding its two children's boxes
+    auto child_ref = [&](const std::vector<int32_t> &inner_id, int32_t c) -> int32_t {
+        const TNode &n = bl.nodes[c];
+        if (n.left < 0) return (int32_t) ~((n.first << 3) | n.count);
+        return inner_id[c];
+    };
+    std::vector<int32_t> inner_id(bl.nodes.size(), -1); int32_t n_inner = 0;
+    for (size_t i = 0; i < bl.nodes.size(); ++i) if (bl.nodes[i].left >= 0) inner_id[i] = n_inner++;
+    auto put = [&](int32_t id, const Box &a, int32_t ca, const Box &b, int32_t cb) {
+        float fa, fb; memcpy(&fa, &ca, 4); memcpy(&fb, &cb, 4);
+        out.nodes[4 * (size_t) id + 0] = make_float4(a.lo[0], a.hi[0], a.lo[1], a.hi[1]);
+        out.nodes[4 * (size_t) id + 1] = make_float4(b.lo[0], b.hi[0], b.lo[1], b.hi[1]);
+        out.nodes[4 * (size_t) id + 2] = make_float4(a.lo[2], a.hi[2], b.lo[2], b.hi[2]);
+        out.nodes[4 * (size_t) id + 3] = make_float4(fa, fb, 0.f, 0.f);
+    };
+    Box empty; for (int a = 0; a < 3; ++a) { empty.lo[a] = 0.f; empty.hi[a] = 0.f; }
+    const int32_t empty_leaf = (int32_t) ~0u;     // leaf with count 0
+    if (n_inner == 0) {
+        // zero or one leaf: synthesise a root so that node 0 is always an inner node
+        out.nodes.resize(4);
+        if (np) put(0, bl.nodes[0].b, child_ref(inner_id, 0), empty, empty_leaf); else put(0, empty, empty_leaf, empty, empty_leaf);
+        return;
+    }
+    out.nodes.resize(4 * (size_t) n_inner);
+    for (size_t i = 0; i < bl.nodes.size(); ++i) {
+        const TNode &n = bl.nodes[i]; if (n.left < 0) continue;
+        put(inner_id[i], bl.nodes[n.left].b, child_ref(inner_id, n.left), bl.nodes[n.right].b, child_ref(inner_id, n.right));
+    }
+}
+
+} // namespace amvpt

@@ -1,0 +1,259 @@
+// capi.cpp -- extern "C" boundary of libamvpt_b200.so (declared in include/amvpt.h).
+#include "../../include/amvpt.h"
+#include "host.h"
+#include <cstring>
+#include <functional>
+
+using namespace amvpt;
+
+struct amvpt_scene { Scene *s; };
+static thread_local std::string g_err;
+
+static int guard(const std::function<int()> &fn) {
+    try { return fn(); }
+    catch (const Error &e) {
+        g_err = e.what();
+        return g_err.rfind("CUDA error", 0) == 0 ? AMVPT_ERR_CUDA : (g_err.rfind("io:", 0) == 0 ? AMVPT_ERR_IO : AMVPT_ERR_INVALID);
+    }
+    catch (const std::exception &e) { g_err = e.what(); return AMVPT_ERR_INVALID; }
+}
+#define NEED(x) do { if (!(x)) AM_THROW("%s: null or invalid argument (%s)", __func__, #x); } while (0)
+
+// scratch device buffer that frees itself
+struct DBuf {
+    void *p = nullptr;
+    explicit DBuf(size_t bytes) { AM_CUDA(cudaMalloc(&p, bytes ? bytes : 16)); }
+    ~DBuf() { cudaFree(p); }
+    template <class T> T *as() { return (T *) p; }
+    void up(const void *h, size_t bytes) { if (bytes) AM_CUDA(cudaMemcpy(p, h, bytes, cudaMemcpyHostToDevice)); }
+    void down(void *h, size_t bytes) { if (bytes) AM_CUDA(cudaMemcpy(h, p, bytes, cudaMemcpyDeviceToHost)); }
+};
+static void need_device(int dev) {
+    int n = 0; cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n <= 0) AM_THROW("CUDA error: no CUDA device available (%s); this library has no CPU fallback", cudaGetErrorString(e));
+    if (dev < 0 || dev >= n) AM_THROW("CUDA error: device %d out of range (%d devices)", dev, n);
+    AM_CUDA(cudaSetDevice(dev));
+}
+static Scene &committed(amvpt_scene *h) {
+    if (!h || !h->s) AM_THROW("null scene handle");
+    if (!h->s->committed) AM_THROW("scene not committed (call amvpt_scene_commit first)");
+    AM_CUDA(cudaSetDevice(h->s->device));
+    return *h->s;
+}
+static std::vector<std::pair<std::string, std::string>> parse_defines(const char *const *defines, int n) {
+    std::vector<std::pair<std::string, std::string>> out;
+    for (int i = 0; i < n; ++i) {
+        std::string d = defines[i]; size_t eq = d.find('=');
+        if (eq == std::string::npos) AM_THROW("define '%s' is not of the form key=value", d.c_str());
+        out.emplace_back(d.substr(0, eq), d.substr(eq + 1));
+    }
+    return out;
+}
+
+extern "C" {
+
+const char *amvpt_last_error(void) { return g_err.c_str(); }
+int amvpt_device_count(void) { int n = 0; return cudaGetDeviceCount(&n) == cudaSuccess ? n : 0; }
+
+int amvpt_scene_create(amvpt_scene **out) {
+    return guard([&] { NEED(out); *out = new amvpt_scene{ new Scene() }; return AMVPT_OK; });
+}
+void amvpt_scene_destroy(amvpt_scene *s) { if (s) { delete s->s; delete s; } }
+int amvpt_scene_from_xml(const char *path, const char *const *defines, int n_defines, amvpt_scene **out) {
+    return guard([&] { NEED(path); NEED(out); *out = new amvpt_scene{ load_xml_file(path, parse_defines(defines, n_defines)) }; return AMVPT_OK; });
+}
+int amvpt_scene_from_xml_string(const char *xml, const char *base_dir, const char *const *defines, int n_defines, amvpt_scene **out) {
+    return guard([&] { NEED(xml); NEED(out);
+        *out = new amvpt_scene{ load_xml_string(xml, base_dir ? base_dir : ".", parse_defines(defines, n_defines)) }; return AMVPT_OK; });
+}
+int amvpt_scene_add_bsdf(amvpt_scene *h, const amvpt_bsdf_desc *d) {
+    return guard([&] { NEED(h); NEED(d);
+        if (d->type < 0 || d->type > 5) AM_THROW("unknown BSDF type %d", d->type);
+        DBsdf b{}; b.type = d->type; b.twosided = d->twosided; b.distr = d->distr; b.nonlinear = d->nonlinear;
+        for (int i = 0; i < 3; ++i) { b.reflectance[i] = d->reflectance[i]; b.eta[i] = d->eta[i]; b.k[i] = d->k[i];
+            b.spec_refl[i] = d->specular_reflectance[i]; b.spec_trans[i] = d->specular_transmittance[i]; }
+        b.ior_eta = d->int_ior / d->ext_ior; b.alpha_u = d->alpha_u; b.alpha_v = d->alpha_v;
+        return h->s->add_bsdf(b); });
+}
+int amvpt_scene_add_mesh(amvpt_scene *h, const float *pos, uint32_t nv, const uint32_t *faces, uint32_t nf, const float *normals,
+                         int bsdf, const float *radiance, int flip_normals) {
+    return guard([&] { NEED(h); NEED(pos || !nv); NEED(faces || !nf);
+        HMesh m; m.pos.assign(pos, pos + 3 * (size_t) nv); m.faces.assign(faces, faces + 3 * (size_t) nf);
+        if (normals) m.nrm.assign(normals, normals + 3 * (size_t) nv);
+        m.bsdf = bsdf; m.flip_normals = flip_normals;
+        return h->s->add_mesh(std::move(m), radiance); });
+}
+int amvpt_scene_set_sensor_grid(amvpt_scene *h, const amvpt_grid_sensor_desc *d) {
+    return guard([&] { NEED(h); NEED(d);
+        GridSensorParams g; g.thinlens = d->thinlens; g.fov_axis = d->fov_axis; g.grid_x = d->grid_x; g.grid_y = d->grid_y;
+        g.res_x = d->res_x; g.res_y = d->res_y; g.reverse_x = d->reverse_x; g.reverse_y = d->reverse_y; g.use_cone = d->use_cone; g.cam_center = d->cam_center;
+        for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) g.to_world.m[i][j] = d->to_world[4 * i + j];
+        g.fov = d->fov; g.near_clip = d->near_clip; g.far_clip = d->far_clip; g.focus_distance = d->focus_distance;
+        g.aperture_radius = d->aperture_radius; g.cone_deg = d->cone_deg; g.cam_dist = d->cam_dist;
+        for (int i = 0; i < 3; ++i) { g.cam_dir[i] = d->cam_dir[i]; g.cam_off[i] = d->cam_off[i]; }
+        h->s->set_sensor_grid(g); return AMVPT_OK; });
+}
+int amvpt_scene_set_sensor_batch(amvpt_scene *h, uint32_t n, uint32_t res_x, uint32_t res_y, const float *s2c, const float *to_world,
+                                 float near_clip, float far_clip, int reverse_x) {
+    return guard([&] { NEED(h); NEED(s2c); NEED(to_world);
+        h->s->set_sensor_explicit(n, res_x, res_y, s2c, to_world, near_clip, far_clip, reverse_x != 0); return AMVPT_OK; });
+}
+int amvpt_scene_set_integrator(amvpt_scene *h, const amvpt_integrator_desc *d) {
+    return guard([&] { NEED(h); NEED(d);
+        IntegratorParams &ip = h->s->integrator;
+        if (d->max_depth < 0 && d->max_depth != -1) AM_THROW("\"max_depth\" must be set to -1 (infinite) or a value >= 0");   // integrator.cpp:510-512
+        ip.max_depth = d->max_depth; ip.rr_depth = d->rr_depth; ip.hide_emitters = d->hide_emitters != 0; ip.spp_pass_lim = d->spp_pass_lim;
+        if (ip.rr_depth == 0) AM_THROW("\"rr_depth\" must be set to a value greater than zero!");                              // integrator.cpp:517-518
+        h->s->sampler_seed = d->sampler_seed; if (d->sample_count) h->s->sample_count = d->sample_count;
+        if (h->s->committed) { h->s->d.max_depth = ip.max_depth < 0 ? 0xffffffffu : (uint32_t) ip.max_depth; h->s->d.rr_depth = ip.rr_depth; }
+        return AMVPT_OK; });
+}
+int amvpt_scene_commit(amvpt_scene *h, int device) {
+    return guard([&] { NEED(h); need_device(device); h->s->commit(device); return AMVPT_OK; });
+}
+int amvpt_scene_info(amvpt_scene *h, uint32_t *film_w, uint32_t *film_h, uint32_t *n_views, uint32_t *n_prims, uint32_t *n_nodes, uint32_t *sample_count) {
+    return guard([&] { NEED(h); Scene &s = *h->s;
+        if (film_w) *film_w = s.film_w; if (film_h) *film_h = s.film_h; if (n_views) *n_views = (uint32_t) s.sensors.size();
+        if (n_prims) *n_prims = s.nprims(); if (n_nodes) *n_nodes = s.n_nodes; if (sample_count) *sample_count = s.sample_count;
+        return AMVPT_OK; });
+}
+int amvpt_scene_get_sensor(amvpt_scene *h, uint32_t index, float *s2c, float *to_world) {
+    return guard([&] { NEED(h); NEED(index < h->s->sensors.size()); const DSensor &c = h->s->sensors[index];
+        if (s2c) memcpy(s2c, c.s2c, 64);
+        if (to_world) { memcpy(to_world, c.to_world, 48); to_world[12] = to_world[13] = to_world[14] = 0.f; to_world[15] = 1.f; }
+        return AMVPT_OK; });
+}
+int amvpt_scene_get_bsdf_tables(amvpt_scene *h, int bsdf, float *ext_t, float *scalars) {
+    return guard([&] { NEED(h); NEED(bsdf >= 0 && bsdf < (int) h->s->bsdfs.size()); const DBsdf &b = h->s->bsdfs[bsdf];
+        if (ext_t) memcpy(ext_t, b.ext_transmittance, sizeof(b.ext_transmittance));
+        if (scalars) { scalars[0] = b.inv_eta_2; scalars[1] = b.spec_sampling_weight; scalars[2] = b.internal_reflectance; }
+        return AMVPT_OK; });
+}
+
+// ---- hot path
+int amvpt_render(amvpt_scene *h, const amvpt_render_desc *d, amvpt_render_stats *out) {
+    return guard([&] { NEED(d); Scene &s = committed(h);
+        RenderOptions o; o.seed = d->seed; o.spp = d->spp; o.scheduler = d->scheduler; o.stats = d->collect_stats != 0;
+        o.shard.rank = d->rank; o.shard.world = d->world ? d->world : 1; o.stream = (cudaStream_t) d->stream;
+        o.adaptive = d->adaptive != 0; o.adaptive_threshold = d->adaptive_threshold; o.adaptive_min_spp = d->adaptive_min_spp ? d->adaptive_min_spp : 16;
+        o.allreduce = d->allreduce; o.allreduce_user = d->allreduce_user;
+        render(s, o);
+        if (out) { const RenderStats &r = s.last; out->seconds = r.seconds; out->paths = r.paths; out->closest_rays = r.closest_rays; out->shadow_rays = r.shadow_rays;
+            out->bvh_nodes = r.nodes; out->tri_tests = r.tris; out->path_vertices = r.vertices; out->passes = r.passes; out->launches = r.launches; out->spp_done = r.spp_done; out->pad = 0; }
+        return AMVPT_OK; });
+}
+int amvpt_cancel(amvpt_scene *h) { return guard([&] { NEED(h); h->s->stop = true; return AMVPT_OK; }); }
+int amvpt_film_clear(amvpt_scene *h) { return guard([&] { Scene &s = committed(h); s.film_clear(nullptr); AM_CUDA(cudaDeviceSynchronize()); return AMVPT_OK; }); }
+int amvpt_film_raw(amvpt_scene *h, float *rgbw) {
+    return guard([&] { NEED(rgbw); Scene &s = committed(h);
+        AM_CUDA(cudaMemcpy(rgbw, s.film, sizeof(float4) * (size_t) s.film_w * s.film_h, cudaMemcpyDeviceToHost)); return AMVPT_OK; });
+}
+int amvpt_film_develop_device(amvpt_scene *h, float *rgb_dev, void *stream) {
+    return guard([&] { NEED(rgb_dev); Scene &s = committed(h);
+        launch_develop(s.film, rgb_dev, (size_t) s.film_w * s.film_h, (cudaStream_t) stream); AM_CUDA(cudaGetLastError()); return AMVPT_OK; });
+}
+int amvpt_film_develop(amvpt_scene *h, float *rgb) {
+    return guard([&] { NEED(rgb); Scene &s = committed(h); size_t npix = (size_t) s.film_w * s.film_h;
+        if (!s.rgb) s.rgb = (float *) s.dalloc(npix * 3 * sizeof(float));
+        launch_develop(s.film, s.rgb, npix, nullptr); AM_CUDA(cudaGetLastError());
+        AM_CUDA(cudaMemcpy(rgb, s.rgb, npix * 3 * sizeof(float), cudaMemcpyDeviceToHost)); return AMVPT_OK; });
+}
+int amvpt_film_device_ptr(amvpt_scene *h, void **rgbw, void **moments) {
+    return guard([&] { Scene &s = committed(h); if (rgbw) *rgbw = s.film; if (moments) *moments = s.moments; return AMVPT_OK; });
+}
+int amvpt_film_add_host(amvpt_scene *h, const float *rgbw) {
+    return guard([&] { NEED(rgbw); Scene &s = committed(h); size_t n = (size_t) s.film_w * s.film_h * 4;
+        std::vector<float> cur(n); AM_CUDA(cudaMemcpy(cur.data(), s.film, n * 4, cudaMemcpyDeviceToHost));
+        for (size_t i = 0; i < n; ++i) cur[i] += rgbw[i];
+        AM_CUDA(cudaMemcpy(s.film, cur.data(), n * 4, cudaMemcpyHostToDevice)); return AMVPT_OK; });
+}
+
+// ---- parity taps
+int amvpt_trace_lanes(amvpt_scene *h, uint32_t seed_value, uint32_t spp_per_pass, uint32_t lane_begin, uint32_t n, int trace,
+                      float *sample_pos, float *ray_o, float *ray_d, float *ray_maxt, uint32_t *view, float *radiance,
+                      uint32_t *pixel, uint32_t max_hits, uint32_t *hit_prim, float *hit_t, uint64_t *stats2) {
+    return guard([&] { Scene &s = committed(h); NEED(spp_per_pass > 0);
+        size_t N = n;
+        DBuf b_sp(N * 8), b_o(N * 12), b_d(N * 12), b_mt(N * 4), b_v(N * 4), b_r(N * 16), b_px(N * 4), b_hp(N * max_hits * 4), b_ht(N * max_hits * 4), b_c(8 * CTR_COUNT);
+        AM_CUDA(cudaMemset(b_c.p, 0, 8 * CTR_COUNT));
+        LaneTaps t; t.sample_pos = b_sp.as<float>(); t.ray_o = b_o.as<float>(); t.ray_d = b_d.as<float>(); t.ray_maxt = b_mt.as<float>();
+        t.view = b_v.as<uint32_t>(); t.radiance = b_r.as<float>(); t.pixel = b_px.as<uint32_t>(); t.max_hits = max_hits;
+        t.hit_prim = b_hp.as<uint32_t>(); t.hit_t = b_ht.as<float>();
+        launch_trace_lanes(s.d, seed_value, spp_per_pass, lane_begin, n, trace, t, b_c.as<unsigned long long>(), nullptr);
+        AM_CUDA(cudaGetLastError()); AM_CUDA(cudaDeviceSynchronize());
+        if (sample_pos) b_sp.down(sample_pos, N * 8);
+        if (ray_o) b_o.down(ray_o, N * 12);
+        if (ray_d) b_d.down(ray_d, N * 12);
+        if (ray_maxt) b_mt.down(ray_maxt, N * 4);
+        if (view) b_v.down(view, N * 4);
+        if (radiance) b_r.down(radiance, N * 16);
+        if (pixel) b_px.down(pixel, N * 4);
+        if (hit_prim && max_hits) b_hp.down(hit_prim, N * max_hits * 4);
+        if (hit_t && max_hits) b_ht.down(hit_t, N * max_hits * 4);
+        if (stats2) { unsigned long long c[CTR_COUNT]; b_c.down(c, sizeof(c)); stats2[0] = c[CTR_NODES]; stats2[1] = c[CTR_TRIS]; }
+        return AMVPT_OK; });
+}
+int amvpt_intersect(amvpt_scene *h, const float *o, const float *d, const float *maxt, uint32_t n, int any_hit, uint32_t *prim, float *tuv, uint64_t *stats2) {
+    return guard([&] { Scene &s = committed(h); NEED(o && d && maxt && prim); size_t N = n;
+        DBuf b_o(N * 12), b_d(N * 12), b_m(N * 4), b_p(N * 4), b_t(N * 12), b_c(8 * CTR_COUNT);
+        b_o.up(o, N * 12); b_d.up(d, N * 12); b_m.up(maxt, N * 4); AM_CUDA(cudaMemset(b_c.p, 0, 8 * CTR_COUNT));
+        launch_intersect(s.d, b_o.as<float>(), b_d.as<float>(), b_m.as<float>(), n, any_hit, b_p.as<uint32_t>(), b_t.as<float>(), b_c.as<unsigned long long>(), nullptr);
+        AM_CUDA(cudaGetLastError()); AM_CUDA(cudaDeviceSynchronize());
+        b_p.down(prim, N * 4); if (tuv) b_t.down(tuv, N * 12);
+        if (stats2) { unsigned long long c[CTR_COUNT]; b_c.down(c, sizeof(c)); stats2[0] = c[CTR_NODES]; stats2[1] = c[CTR_TRIS]; }
+        return AMVPT_OK; });
+}
+int amvpt_bsdf_eval_pdf_sample(amvpt_scene *h, int bsdf, const float *wi, const float *wo, const float *s1, const float *s2, uint32_t n,
+                               float *f, float *pdf, float *bs_wo, float *bs_pdf, float *bs_eta, uint32_t *bs_type, float *weight) {
+    return guard([&] { Scene &s = committed(h); NEED(bsdf >= 0 && bsdf < (int) s.bsdfs.size()); NEED(wi && wo && s1 && s2); size_t N = n;
+        DBuf b_wi(N * 12), b_wo(N * 12), b_s1(N * 4), b_s2(N * 8), b_out(N * 64);
+        b_wi.up(wi, N * 12); b_wo.up(wo, N * 12); b_s1.up(s1, N * 4); b_s2.up(s2, N * 8);
+        launch_bsdf_tap(s.d, bsdf, b_wi.as<float>(), b_wo.as<float>(), b_s1.as<float>(), b_s2.as<float>(), n, b_out.as<float>(), nullptr);
+        AM_CUDA(cudaGetLastError()); AM_CUDA(cudaDeviceSynchronize());
+        std::vector<float> q(N * 16); b_out.down(q.data(), N * 64);
+        for (size_t i = 0; i < N; ++i) { const float *r = &q[16 * i];
+            if (f) { f[3 * i] = r[0]; f[3 * i + 1] = r[1]; f[3 * i + 2] = r[2]; } if (pdf) pdf[i] = r[3];
+            if (bs_wo) { bs_wo[3 * i] = r[4]; bs_wo[3 * i + 1] = r[5]; bs_wo[3 * i + 2] = r[6]; } if (bs_pdf) bs_pdf[i] = r[7]; if (bs_eta) bs_eta[i] = r[8];
+            if (bs_type) memcpy(&bs_type[i], &r[9], 4); if (weight) { weight[3 * i] = r[10]; weight[3 * i + 1] = r[11]; weight[3 * i + 2] = r[12]; } }
+        return AMVPT_OK; });
+}
+int amvpt_math1(int device, int op, const float *in, uint32_t n, float *out) {
+    return guard([&] { NEED(in && out); need_device(device); size_t N = n; DBuf a(N * 4), b(N * 4); a.up(in, N * 4);
+        launch_math_tap(op, a.as<float>(), n, b.as<float>(), nullptr); AM_CUDA(cudaGetLastError()); AM_CUDA(cudaDeviceSynchronize()); b.down(out, N * 4); return AMVPT_OK; });
+}
+int amvpt_sampler_stream(int device, uint32_t seed_value, uint32_t lane, uint32_t n, float *out) {
+    return guard([&] { NEED(out); need_device(device); DBuf b((size_t) n * 4);
+        launch_sampler_tap(seed_value, lane, n, b.as<float>(), nullptr); AM_CUDA(cudaGetLastError()); AM_CUDA(cudaDeviceSynchronize()); b.down(out, (size_t) n * 4); return AMVPT_OK; });
+}
+// Host-side structural check of the tree that was uploaded (no GPU work): containment of triangles and child boxes.
+int amvpt_bvh_validate(amvpt_scene *h, uint32_t *max_depth, uint32_t *n_leaves) {
+    return guard([&] { NEED(h); Scene &s = *h->s; if (s.h_nodes.empty()) AM_THROW("scene not committed");
+        struct B { float lo[3], hi[3]; };
+        uint32_t leaves = 0, maxd = 0; std::vector<uint8_t> seen(s.h_tris.size() / 3, 0);
+        std::function<void(int32_t, const B *, uint32_t)> rec = [&](int32_t ref, const B *box, uint32_t depth) {
+            maxd = std::max(maxd, depth);
+            if (ref < 0) {
+                uint32_t code = ~(uint32_t) ref, first = code >> 3, count = code & 7u; leaves++;
+                for (uint32_t i = first; i < first + count; ++i) {
+                    if (seen[i]++) AM_THROW("bvh: triangle %u referenced twice", i);
+                    for (int k = 0; k < 3; ++k) { const float4 &v = s.h_tris[3 * (size_t) i + k]; float p[3] = { v.x, v.y, v.z };
+                        for (int a = 0; a < 3; ++a) if (box && (p[a] < box->lo[a] || p[a] > box->hi[a])) AM_THROW("bvh: triangle %u outside its leaf box", i); }
+                }
+                return;
+            }
+            const float4 *n = &s.h_nodes[4 * (size_t) ref];
+            B a = { { n[0].x, n[0].z, n[2].x }, { n[0].y, n[0].w, n[2].y } }, b = { { n[1].x, n[1].z, n[2].z }, { n[1].y, n[1].w, n[2].w } };
+            int32_t ca, cb; memcpy(&ca, &n[3].x, 4); memcpy(&cb, &n[3].y, 4);
+            bool a_empty = ca == -1, b_empty = cb == -1;
+            if (box) for (int k = 0; k < 3; ++k) {
+                if (!a_empty && (a.lo[k] < box->lo[k] || a.hi[k] > box->hi[k])) AM_THROW("bvh: child box outside parent at node %d", ref);
+                if (!b_empty && (b.lo[k] < box->lo[k] || b.hi[k] > box->hi[k])) AM_THROW("bvh: child box outside parent at node %d", ref);
+            }
+            rec(ca, &a, depth + 1); rec(cb, &b, depth + 1);
+        };
+        rec(0, nullptr, 0);
+        for (size_t i = 0; i < seen.size(); ++i) if (!seen[i]) AM_THROW("bvh: triangle %zu not referenced", i);
+        if (max_depth) *max_depth = maxd; if (n_leaves) *n_leaves = leaves; return AMVPT_OK; });
+}
+
+} // extern "C"

@@ -1,0 +1,283 @@
+// dscene.cuh -- device-resident scene of the AMVPT path: sub-sensor table, BVH, triangles, emitters,
+// and the per-ray / per-vertex device functions (camera ray, closest hit, any hit, surface
+// interaction, emitter sampling).  Data layout is described in DESIGN.md "Data layout in HBM".
+#pragma once
+#include "dtypes.h"
+
+namespace amvpt {
+
+struct Ray { V3 o, d; float maxt; };
+struct Hit { float t, u, v; uint32_t tri; };     // tri = position in DScene::tris, 0xffffffff = miss
+#define AM_NO_HIT 0xffffffffu
+
+AM_D float4 ldg4(const float4 *p) { return __ldg(p); }
+
+// ---------------------------------------------------------------- sensors
+// Transform4f * Point3f with perspective divide (include/mitsuba/core/transform.h:134-144)
+AM_D V3 xf_point_proj(const float *m, V3 p) {
+    float r[4];
+    #pragma unroll
+    for (int i = 0; i < 4; ++i) r[i] = m[4 * i + 3];
+    #pragma unroll
+    for (int i = 0; i < 4; ++i) r[i] = fmadd(m[4 * i + 0], p.x, r[i]);
+    #pragma unroll
+    for (int i = 0; i < 4; ++i) r[i] = fmadd(m[4 * i + 1], p.y, r[i]);
+    #pragma unroll
+    for (int i = 0; i < 4; ++i) r[i] = fmadd(m[4 * i + 2], p.z, r[i]);
+    float iw = rcp(r[3]);
+    return v3(r[0] * iw, r[1] * iw, r[2] * iw);
+}
+AM_D V3 xf_point_affine(const float *m, V3 p) {   // transform.h:121-129
+    return v3(fmadd(m[2], p.z, fmadd(m[1], p.y, fmadd(m[0], p.x, m[3]))),
+              fmadd(m[6], p.z, fmadd(m[5], p.y, fmadd(m[4], p.x, m[7]))),
+              fmadd(m[10], p.z, fmadd(m[9], p.y, fmadd(m[8], p.x, m[11]))));
+}
+AM_D V3 xf_vector(const float *m, V3 v) {         // transform.h:150-160
+    return v3(fmadd(m[2], v.z, fmadd(m[1], v.y, m[0] * v.x)),
+              fmadd(m[6], v.z, fmadd(m[5], v.y, m[4] * v.x)),
+              fmadd(m[10], v.z, fmadd(m[9], v.y, m[8] * v.x)));
+}
+// GridSensor::sample_ray (src/sensors/grid.cpp:238-267) [BatchSensor::sample_ray src/sensors/batch.cpp:132-160 is
+// the grid_y = 1, reverse_y = 0 case] -> PerspectiveCamera::sample_ray / ThinLensCamera::sample_ray.
+AM_D Ray sensor_sample_ray(const DScene &s, V2 pos, V2 aperture, uint32_t *view_out) {
+    float fx = pos.x * (float) s.grid_x, fy = pos.y * (float) s.grid_y;
+    uint32_t ux = (uint32_t) fx, uy = (uint32_t) fy, ix = ux, iy = uy;
+    if (s.reverse_x) ix = (s.grid_x - 1) - ix;
+    if (s.reverse_y) iy = (s.grid_y - 1) - iy;
+    uint32_t index = ix + s.grid_x * iy;
+    index = min(index, s.n_sensors - 1u);
+    V2 p2 = v2(fx - (float) ux, fy - (float) uy);
+    *view_out = index;
+    const float4 *c4 = reinterpret_cast<const float4 *>(s.sensors + index);
+    float m[32];
+    #pragma unroll
+    for (int i = 0; i < 8; ++i) { float4 q = ldg4(c4 + i); m[4 * i] = q.x; m[4 * i + 1] = q.y; m[4 * i + 2] = q.z; m[4 * i + 3] = q.w; }
+    const float *s2c = m, *tw = m + 16;
+    float near_clip = m[28], far_clip = m[29], aperture_radius = m[30], focus_distance = m[31];
+    V3 near_p = xf_point_proj(s2c, v3(p2.x + 0.f, p2.y + 0.f, 0.f));
+    Ray ray; V3 d;
+    if (!s.thinlens) {
+        d = normalize(near_p);
+        ray.o = v3(tw[3], tw[7], tw[11]);
+    } else {
+        V2 tmp = square_to_uniform_disk_concentric(aperture);
+        V3 ap = v3(aperture_radius * tmp.x, aperture_radius * tmp.y, 0.f);
+        V3 focus_p = near_p * fdiv(focus_distance, near_p.z);
+        d = normalize(focus_p - ap);
+        ray.o = xf_point_affine(tw, ap);
+    }
+    ray.d = xf_vector(tw, d);
+    float inv_z = rcp(d.z), near_t = near_clip * inv_z, far_t = far_clip * inv_z;
+    ray.o = ray.o + ray.d * near_t; ray.maxt = far_t - near_t;
+    return ray;
+}
+
+// ---------------------------------------------------------------- ray / triangle, BVH traversal
+// Mesh::moeller_trumbore (include/mitsuba/render/mesh.h:467-488)
+AM_D bool moeller_trumbore(const Ray &ray, V3 p0, V3 p1, V3 p2, float *t_o, float *u_o, float *v_o) {
+    V3 e1 = p1 - p0, e2 = p2 - p0;
+    V3 pvec = cross(ray.d, e2);
+    float inv_det = rcp(dot(e1, pvec));
+    V3 tvec = ray.o - p0;
+    float u = dot(tvec, pvec) * inv_det;
+    bool active = u >= 0.f && u <= 1.f;
+    V3 qvec = cross(tvec, e1);
+    float v = dot(ray.d, qvec) * inv_det;
+    active = active && v >= 0.f && u + v <= 1.f;
+    float t = dot(e2, qvec) * inv_det;
+    active = active && t >= 0.f && t <= ray.maxt;
+    *t_o = t; *u_o = u; *v_o = v;
+    return active;
+}
+
+#define AM_SLAB_EPS 1e-6f
+// Slab test of one child box.  Conservative: (lo - o) is correctly rounded, so t0/t1 carry a relative
+// error of a few ulp; the interval is widened by AM_SLAB_EPS and the builder pads every box (bvh.cpp).
+// fminf/fmaxf drop the NaN of 0 * inf (origin on a slab plane of an axis-parallel ray).
+AM_D bool slab(float lox, float hix, float loy, float hiy, float loz, float hiz, V3 o, V3 id, float tbest, float *tnear) {
+    float t0x = (lox - o.x) * id.x, t1x = (hix - o.x) * id.x;
+    float t0y = (loy - o.y) * id.y, t1y = (hiy - o.y) * id.y;
+    float t0z = (loz - o.z) * id.z, t1z = (hiz - o.z) * id.z;
+    float tmin = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), 0.f));
+    float tmax = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fminf(fmaxf(t0z, t1z), tbest));
+    *tnear = tmin;
+    return tmin * (1.f - AM_SLAB_EPS) <= tmax * (1.f + AM_SLAB_EPS);
+}
+
+// Closest hit (ANY = false) with the tie rule of ShapeKDTree::ray_intersect_naive
+// (include/mitsuba/render/kdtree.h:2445-2468): among equal t the primitive with the larger global index
+// wins.  ANY = true: Scene::ray_test semantics, first accepted triangle ends the traversal.
+template <bool ANY> AM_D Hit intersect(const DScene &s, const Ray &ray, uint32_t *n_nodes = nullptr, uint32_t *n_tris = nullptr) {
+    Hit h; h.t = AM_INF; h.u = 0.f; h.v = 0.f; h.tri = AM_NO_HIT;
+    uint32_t best_prim = 0;
+    float best = ray.maxt;
+    V3 id = v3(rcp(ray.d.x), rcp(ray.d.y), rcp(ray.d.z));
+    int32_t stack[AM_STACK_SIZE]; int sp = 0;
+    int32_t node = 0;
+    const int32_t SENTINEL = 0x7fffffff;
+    stack[sp++] = SENTINEL;
+    while (node != SENTINEL) {
+        if (node >= 0) {
+            const float4 *np = s.nodes + 4 * (size_t) node;
+            float4 n0 = ldg4(np), n1 = ldg4(np + 1), n2 = ldg4(np + 2), n3 = ldg4(np + 3);
+            if (n_nodes) (*n_nodes)++;
+            float ta, tb;
+            bool ha = slab(n0.x, n0.y, n0.z, n0.w, n2.x, n2.y, ray.o, id, best, &ta);
+            bool hb = slab(n1.x, n1.y, n1.z, n1.w, n2.z, n2.w, ray.o, id, best, &tb);
+            int32_t ca = __float_as_int(n3.x), cb = __float_as_int(n3.y);
+            if (ha && hb) {
+                bool swap = tb < ta;
+                int32_t nearc = swap ? cb : ca, farc = swap ? ca : cb;
+                stack[sp++] = farc; node = nearc;
+            } else if (ha) node = ca;
+            else if (hb) node = cb;
+            else node = stack[--sp];
+        } else {
+            uint32_t code = ~(uint32_t) node, first = code >> 3, count = code & 7u;
+            for (uint32_t i = 0; i < count; ++i) {
+                const float4 *tp = s.tris + 3 * (size_t) (first + i);
+                float4 a = ldg4(tp), b = ldg4(tp + 1), c = ldg4(tp + 2);
+                if (n_tris) (*n_tris)++;
+                float t, u, v;
+                if (moeller_trumbore(ray, v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), v3(c.x, c.y, c.z), &t, &u, &v)) {
+                    uint32_t prim = __float_as_uint(a.w);
+                    if (ANY) { h.t = t; h.u = u; h.v = v; h.tri = first + i; return h; }
+                    if (h.tri == AM_NO_HIT || t < h.t || (t == h.t && prim > best_prim)) {
+                        h.t = t; h.u = u; h.v = v; h.tri = first + i; best_prim = prim; best = t;
+                    }
+                }
+            }
+            node = stack[--sp];
+        }
+    }
+    return h;
+}
+
+// ---------------------------------------------------------------- surface interaction
+struct SI {
+    bool valid; float t; V3 p, n, sh_n, sh_s, sh_t, wi; uint32_t mesh, prim;
+    AM_D V3 to_local(V3 v) const { return v3(dot(v, sh_s), dot(v, sh_t), dot(v, sh_n)); }          // frame.h:34-36
+    AM_D V3 to_world(V3 v) const { return fmadd(sh_n, v.z, fmadd(sh_t, v.y, sh_s * v.x)); }        // frame.h:39-41
+};
+// Interaction::offset_p / spawn_ray / spawn_ray_to (include/mitsuba/render/interaction.h:140-170)
+AM_D V3 offset_p(V3 p, V3 n, V3 d) {
+    float mag = (1.f + max_(max_(fabs_(p.x), fabs_(p.y)), fabs_(p.z))) * AM_RAY_EPSILON;
+    mag = mulsign(mag, dot(n, d));
+    return fmadd(n, mag, p);
+}
+AM_D Ray spawn_ray(V3 p, V3 n, V3 d) { Ray r; r.o = offset_p(p, n, d); r.d = d; r.maxt = AM_LARGEST; return r; }
+AM_D Ray spawn_ray_to(V3 p, V3 n, V3 t) {
+    Ray r; r.o = offset_p(p, n, t - p);
+    V3 d = t - r.o; float dist = norm(d); r.d = d / dist;
+    r.maxt = dist * (1.f - AM_SHADOW_EPSILON);
+    return r;
+}
+// Mesh::compute_surface_interaction (src/render/mesh.cpp:1392-1565, meshes without texture coordinates) +
+// SurfaceInteraction::finalize_surface_interaction / initialize_sh_frame (interaction.h:278-289, 497-517)
+AM_D SI make_si(const DScene &s, const Ray &ray, const Hit &h, const DMesh **mesh_out) {
+    SI si; si.valid = h.tri != AM_NO_HIT; si.t = h.t; si.wi = -ray.d; si.mesh = 0; si.prim = AM_NO_HIT;
+    *mesh_out = nullptr;
+    if (!si.valid) return si;
+    const float4 *tp = s.tris + 3 * (size_t) h.tri;
+    float4 a = ldg4(tp), b = ldg4(tp + 1), c = ldg4(tp + 2);
+    V3 p0 = v3(a.x, a.y, a.z), p1 = v3(b.x, b.y, b.z), p2 = v3(c.x, c.y, c.z);
+    si.prim = __float_as_uint(a.w); si.mesh = __float_as_uint(b.w);
+    const DMesh *m = s.meshes + si.mesh; *mesh_out = m;
+    float b1 = h.u, b2 = h.v, b0 = 1.f - b1 - b2;
+    si.p = fmadd(p0, b0, fmadd(p1, b1, p2 * b2));
+    si.n = normalize(cross(p1 - p0, p2 - p0));
+    V3 dp_du, dp_dv; coordinate_system(si.n, &dp_du, &dp_dv);
+    if (m->has_normals) {
+        const float4 *np = s.tri_nrm + 3 * (size_t) h.tri;
+        float4 na = ldg4(np), nb = ldg4(np + 1), nc = ldg4(np + 2);
+        V3 n = fmadd(v3(nc.x, nc.y, nc.z), b2, fmadd(v3(nb.x, nb.y, nb.z), b1, v3(na.x, na.y, na.z) * b0));
+        si.sh_n = n * rsqrt(squared_norm(n));
+    } else si.sh_n = si.n;
+    if (m->flip_normals) { si.n = -si.n; si.sh_n = -si.sh_n; }
+    si.sh_s = normalize(fmadd(si.sh_n, -dot(si.sh_n, dp_du), dp_du));
+    if (dp_du.x == 0.f && dp_du.y == 0.f && dp_du.z == 0.f) { V3 t2; coordinate_system(si.sh_n, &si.sh_s, &t2); }
+    si.sh_t = cross(si.sh_n, si.sh_s);
+    si.wi = si.to_local(-ray.d);
+    return si;
+}
+
+// ---------------------------------------------------------------- emitters
+// DiscreteDistribution::sample (include/mitsuba/core/distr_1d.h:116-134) on dr::binary_search
+// (ext/drjit/include/drjit/util.h:134-185): fixed iteration count log2i(n-1)+1
+AM_D uint32_t distr_sample(const float *cdf, uint32_t n, float sum, float sample) {
+    sample *= sum;
+    uint32_t start = 0, end = n - 1, iterations = 0;
+    if (start < end) iterations = 32u - (uint32_t) __clz(end - start);
+    for (uint32_t i = 0; i < iterations; ++i) {
+        uint32_t middle = (start + end) >> 1;
+        float value = __ldg(cdf + middle);
+        bool cond = ((value < sample) || value == 0.f) && value != sum;
+        if (cond) start = min(middle + 1, end); else end = middle;
+    }
+    return start;
+}
+struct DirectionSample { V3 p, n, d; float pdf, dist; };
+// Scene::sample_emitter_direction (src/render/scene.cpp:295-346) + sample_emitter (:223-246) +
+// AreaLight::sample_direction (src/emitters/area.cpp:116-167) + Shape::sample_direction
+// (src/render/shape.cpp:360-377) + Mesh::sample_position (src/render/mesh.cpp:764-818) + visibility test.
+AM_D DirectionSample sample_emitter_direction(const DScene &s, const SI &ref, V2 sample, V3 *spec_out,
+                                              uint32_t *n_nodes, uint32_t *n_tris) {
+    DirectionSample ds; ds.p = v3(0.f); ds.n = v3(0.f); ds.d = v3(0.f); ds.pdf = 0.f; ds.dist = 0.f;
+    *spec_out = v3(0.f);
+    uint32_t ne = s.n_emitters; if (ne == 0) return ds;
+    uint32_t index = 0; float emitter_weight = 1.f;
+    if (ne >= 2) {
+        float ecf = (float) ne, scaled = sample.x * ecf;
+        index = min((uint32_t) scaled, ne - 1u);
+        emitter_weight = ecf; sample.x = scaled - (float) index;
+    }
+    const DEmitter *em = s.emitters + index; const DMesh *m = s.meshes + em->mesh;
+    const float *cdf = s.area_cdf + m->cdf_offset, *pmfp = s.area_pmf + m->cdf_offset;
+    uint32_t face = distr_sample(cdf, m->nfaces, m->sum, sample.y);
+    float pmf = __ldg(pmfp + face) * m->normalization, cdf0 = face > 0 ? __ldg(cdf + face - 1) * m->normalization : 0.f;
+    sample.y = fdiv(sample.y - cdf0, pmf);
+    uint32_t tri = __ldg(s.prim_to_tri + m->prim_offset + face);
+    const float4 *tp = s.tris + 3 * (size_t) tri;
+    float4 a = ldg4(tp), b = ldg4(tp + 1), c = ldg4(tp + 2);
+    V3 p0 = v3(a.x, a.y, a.z), e0 = v3(b.x, b.y, b.z) - p0, e1 = v3(c.x, c.y, c.z) - p0;
+    V2 bc = square_to_uniform_triangle(sample);
+    ds.p = fmadd(e0, bc.x, fmadd(e1, bc.y, p0));
+    ds.pdf = m->normalization;
+    if (m->has_normals) {
+        const float4 *np = s.tri_nrm + 3 * (size_t) tri;
+        float4 na = ldg4(np), nb = ldg4(np + 1), nc = ldg4(np + 2);
+        ds.n = fmadd(v3(na.x, na.y, na.z), 1.f - bc.x - bc.y, fmadd(v3(nb.x, nb.y, nb.z), bc.x, v3(nc.x, nc.y, nc.z) * bc.y));
+    } else ds.n = cross(e0, e1);
+    ds.n = normalize(ds.n);
+    if (m->flip_normals) ds.n = -ds.n;
+    ds.d = ds.p - ref.p;
+    float dist_squared = squared_norm(ds.d);
+    ds.dist = fsqrt(dist_squared);
+    ds.d = ds.d / ds.dist;
+    float dp = fabs_(dot(ds.d, ds.n)), x = fdiv(dist_squared, dp);
+    ds.pdf *= finite_(x) ? x : 0.f;
+    bool active = dot(ds.d, ds.n) < 0.f && ds.pdf != 0.f;
+    V3 spec = ld3(em->radiance) / ds.pdf;
+    spec = select3(active, spec);
+    ds.pdf *= rcp((float) ne);
+    spec = spec * emitter_weight;
+    if (ds.pdf != 0.f) {
+        Ray sr = spawn_ray_to(ref.p, ref.n, ds.p);
+        if (intersect<true>(s, sr, n_nodes, n_tris).tri != AM_NO_HIT) { spec = v3(0.f); ds.pdf = 0.f; }
+    }
+    *spec_out = spec;
+    return ds;
+}
+// Scene::pdf_emitter_direction (scene.cpp:351-360) + AreaLight::pdf_direction (area.cpp:169-195) +
+// Shape::pdf_direction (shape.cpp:379-390) + Mesh::pdf_position (mesh.cpp:846-849)
+AM_D float pdf_emitter_direction(const DScene &s, const DMesh *em_mesh, V3 d, V3 n, float dist) {
+    float dp = dot(d, n);
+    float pdf = em_mesh->normalization, adp = fabs_(dp);
+    pdf *= (adp != 0.f) ? fdiv(dist * dist, adp) : 0.f;
+    float value = dp < 0.f ? pdf : 0.f;
+    return value * (s.n_emitters == 0 ? 0.f : rcp((float) s.n_emitters));
+}
+// src/integrators/mvpath.h:306-311
+AM_D float mis_weight(float a, float b) { a *= a; b *= b; float w = fdiv(a, a + b); return finite_(w) ? w : 0.f; }
+
+} // namespace amvpt

@@ -1,0 +1,47 @@
+// dtypes.h -- plain-old-data records shared by the host library and the device code (HBM layout).
+#pragma once
+#include <cuda_runtime.h>
+#include "dbsdf.cuh"
+
+#define AM_STACK_SIZE 64   /* per-thread traversal stack entries; the builder bounds the tree depth accordingly */
+
+namespace amvpt {
+
+// 128 B per sub-camera.  PerspectiveCamera / ThinLensCamera members that sample_ray reads
+// (src/sensors/perspective.cpp:205-241, src/sensors/thinlens.cpp:220-257).
+struct DSensor {
+    float s2c[16];        // sample_to_camera.matrix, row-major
+    float to_world[12];   // first three rows of to_world.matrix
+    float near_clip, far_clip, aperture_radius, focus_distance;
+};
+struct DMesh {
+    int32_t bsdf, emitter, flip_normals, has_normals;
+    uint32_t prim_offset, nfaces;
+    float normalization, sum;      // 1 / area and unnormalised area (DiscreteDistribution, distr_1d.h:233-264)
+    uint32_t cdf_offset, pad[3];   // into DScene::area_cdf / area_pmf
+};
+struct DEmitter { int32_t mesh; float radiance[3]; };
+
+struct DScene {
+    // BVH2, 64 B per node = 4 x float4 (Aila-Laine layout):
+    //   n0 = (c0.lo.x, c0.hi.x, c0.lo.y, c0.hi.y)  n1 = (c1.lo.x, c1.hi.x, c1.lo.y, c1.hi.y)
+    //   n2 = (c0.lo.z, c0.hi.z, c1.lo.z, c1.hi.z)  n3 = (bits c0, bits c1, -, -)
+    // child >= 0: inner node index; child < 0: leaf, ~child = (first_tri << 3) | count (count <= 7)
+    const float4 *nodes;
+    // triangles in BVH leaf order, 48 B each = 3 x float4: (p0, bits prim), (p1, bits mesh), (p2, 0)
+    const float4 *tris;
+    const float4 *tri_nrm;      // vertex normals in the same order (3 x float4), or nullptr
+    const uint32_t *prim_to_tri; // global primitive index -> position in `tris`
+    const DMesh *meshes;
+    const DBsdf *bsdfs;
+    const DEmitter *emitters;
+    const DSensor *sensors;
+    const float *area_cdf, *area_pmf;
+    uint32_t n_tris, n_nodes, n_emitters, n_sensors;
+    uint32_t grid_x, grid_y;
+    int32_t reverse_x, reverse_y, thinlens, pad0;
+    uint32_t film_w, film_h;
+    uint32_t max_depth, rr_depth;
+};
+
+} // namespace amvpt

@@ -1,0 +1,124 @@
+// host.h -- host-side scene of the AMVPT path: the objects the reference's plugins would hold (meshes, BSDF
+// parameters, the grid / batch multi-sensor, HDR film, independent sampler, mvpath integrator parameters), their
+// device mirrors, and the render entry point that stands in for MVPathIntegrator::render().
+#pragma once
+#include "kernels.cuh"
+#include "htransform.h"
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+namespace amvpt {
+
+struct Error : std::runtime_error { using std::runtime_error::runtime_error; };
+#define AM_THROW(...) throw ::amvpt::Error(::amvpt::strfmt(__VA_ARGS__))
+std::string strfmt(const char *fmt, ...);
+void cuda_check(cudaError_t e, const char *what);
+#define AM_CUDA(x) ::amvpt::cuda_check((x), #x)
+
+// Mesh (src/render/mesh.cpp): positions / normals / faces + area distribution (mesh.cpp:444-486)
+struct HMesh {
+    std::string id;
+    std::vector<float> pos, nrm;          // 3 floats per vertex; nrm empty = no vertex normals
+    std::vector<uint32_t> faces;          // 3 indices per face
+    int bsdf = 0, emitter = -1, flip_normals = 0;
+    uint32_t prim_offset = 0;
+    std::vector<float> pmf, cdf; float sum = 0.f, normalization = 0.f;
+    uint32_t nfaces() const { return (uint32_t) (faces.size() / 3); }
+    void build_area_distr();
+};
+
+// src/integrators/mvpath.h:120-129 + MonteCarloIntegrator (src/render/integrator.cpp:503-520)
+struct IntegratorParams {
+    int64_t max_depth = -1; uint32_t rr_depth = 5; bool hide_emitters = false;
+    uint32_t spp_pass_lim = 16; bool sa_reuse = false, sa_mis = true, fast_mis = false, force_eval = true, debug = false;
+    uint32_t reuse_count = 1, adaptive = 0, block_size = 0; float timeout = -1.f;
+    bool is_mvpath = true;
+};
+// GridSensor parameters (src/sensors/grid.cpp:84-180) over a perspective / thinlens sub-camera
+struct GridSensorParams {
+    bool thinlens = false; int fov_axis = 0;   // 0 x, 1 y, 2 diagonal, 3 smaller, 4 larger
+    uint32_t grid_x = 1, grid_y = 1, res_x = 0, res_y = 0; bool reverse_x = false, reverse_y = true;
+    bool use_cone = false, cam_center = false;
+    M4d to_world = m4d_identity();
+    double fov = 45.0; bool has_focal_length = false; std::string focal_length = "50mm";
+    float near_clip = 1e-2f, far_clip = 1e4f, focus_distance = 1e4f, aperture_radius = 0.f, cone_deg = 0.f, cam_dist = 0.1f;
+    float cam_dir[3] = { 1.f, 0.f, 0.f }, cam_off[3] = { 0.f, 0.f, 0.f };
+};
+enum SchedulerMode { SCHED_WARP_BATCH = 0, SCHED_REGENERATE = 1, SCHED_WAVEFRONT = 2 };
+
+struct RenderStats {
+    double seconds = 0.0;            // device time of the pass loop (CUDA events)
+    unsigned long long paths = 0, closest_rays = 0, shadow_rays = 0, nodes = 0, tris = 0, vertices = 0;
+    uint32_t passes = 0, launches = 0, spp_done = 0;
+};
+struct Shard { uint32_t rank = 0, world = 1; };   // view tiles owned: {v : v mod world == rank}
+
+struct Scene {
+    // ---- host description
+    std::vector<HMesh> meshes; std::vector<DBsdf> bsdfs; std::vector<DEmitter> emitters; std::vector<DSensor> sensors;
+    std::vector<std::string> bsdf_ids;
+    uint32_t grid_x = 1, grid_y = 1, res_x = 0, res_y = 0; bool reverse_x = false, reverse_y = true, thinlens = false;
+    bool multi_sensor = false;
+    uint32_t film_w = 0, film_h = 0;
+    uint32_t sample_count = 4, sampler_seed = 0;
+    IntegratorParams integrator;
+    // ---- device mirror
+    int device = -1, sm_count = 148;
+    bool committed = false;
+    DScene d{};
+    std::vector<void *> allocs;
+    float4 *film = nullptr; float2 *moments = nullptr; float *rgb = nullptr;
+    unsigned long long *counters = nullptr; TileDesc *tiles_dev = nullptr; float *view_stats_dev = nullptr;
+    uint32_t tiles_cap = 0;
+    uint32_t n_nodes = 0, n_tris = 0;
+    volatile bool stop = false;
+    RenderStats last;
+    // oracle-visible copies for the parity tests of the BVH (same tree the kernels traverse)
+    std::vector<float4> h_nodes, h_tris;
+
+    ~Scene();
+    int add_bsdf(const DBsdf &b, const std::string &id = "");
+    int add_mesh(HMesh &&m, const float *radiance);
+    void set_sensor_grid(const GridSensorParams &g);
+    void set_sensor_explicit(uint32_t n, uint32_t res_x, uint32_t res_y, const float *s2c, const float *to_world,
+                             float near_clip, float far_clip, bool reverse_x);
+    void commit(int device);
+    void film_clear(cudaStream_t st);
+    void *dalloc(size_t bytes);
+    template <class T> T *upload(const std::vector<T> &v) {
+        T *p = (T *) dalloc(std::max<size_t>(v.size(), 1) * sizeof(T));
+        if (!v.empty()) AM_CUDA(cudaMemcpy(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
+        return p;
+    }
+    uint32_t nprims() const { uint32_t n = 0; for (auto &m : meshes) n += m.nfaces(); return n; }
+    std::vector<TileDesc> view_tiles(const Shard &sh) const;
+};
+
+// roughplastic.cpp:207-252 parameters_changed(): fills the derived members of a DBsdf record
+void bsdf_prepare(DBsdf &b);
+
+// bvh.cpp
+struct BvhOut { std::vector<float4> nodes, tris, tri_nrm; std::vector<uint32_t> prim_to_tri; };
+void build_bvh(const Scene &s, float scene_scale, BvhOut &out);
+
+// render.cpp -- MVPathIntegrator::render() (src/integrators/mvpath.cpp:7-278), wavefront branch
+struct RenderOptions {
+    uint32_t seed = 0, spp = 0; int scheduler = SCHED_REGENERATE; bool stats = false;
+    Shard shard; cudaStream_t stream = nullptr;
+    // adaptive allocator (build-defined): 0 = fixed spp; otherwise spp is the mean budget per pixel
+    bool adaptive = false; float adaptive_threshold = 0.f; uint32_t adaptive_min_spp = 16;
+    // optional collective hook: sums `n` floats across ranks in place (NCCL all-reduce in the multi-GPU driver)
+    void (*allreduce)(float *dev, uint32_t n, void *user) = nullptr; void *allreduce_user = nullptr;
+};
+void render(Scene &s, const RenderOptions &opt);
+
+// xml.cpp
+Scene *load_xml_file(const std::string &path, const std::vector<std::pair<std::string, std::string>> &defines);
+Scene *load_xml_string(const std::string &xml, const std::string &base_dir, const std::vector<std::pair<std::string, std::string>> &defines);
+// meshio.cpp
+void load_obj(const std::string &path, const M4d &to_world, bool face_normals, bool flip_tex, HMesh &out);
+void load_ply(const std::string &path, const M4d &to_world, bool face_normals, HMesh &out);
+void make_cube(const M4d &to_world, HMesh &out);
+
+} // namespace amvpt

@@ -1,0 +1,368 @@
+// kernels.cu -- sm_100a kernels of the AMVPT render loop.
+//   render_pass_kernel   : camera ray generation (MVPT::render lane map + render_sample + GridSensor /
+//                          PerspectiveCamera / ThinLensCamera::sample_ray), the path loop of
+//                          MVPT::sample_single (BVH closest hit, emitter hit MIS, next-event estimation with
+//                          a shadow ray, BSDF eval/pdf/sample, Russian roulette) and the ImageBlock::put splat,
+//                          as a persistent kernel whose warps refill finished lanes from a ticket counter.
+//   develop_kernel       : HDRFilm::develop (RGB / W)
+//   view_stats_kernel    : per-view error statistics for the adaptive allocator
+//   tap kernels          : parity taps (lanes, rays, BSDFs, leaf math) used by tests through the C ABI
+// Compiled with -fmad=false (see dmath.cuh).  Reference citations are relative to the upstream tree.
+#include "kernels.cuh"
+#include "dscene.cuh"
+
+namespace amvpt {
+
+// ------------------------------------------------------------------------------------------------
+struct PathState {
+    Ray ray; V3 throughput, result, prev_p; float eta, prev_bsdf_pdf; uint32_t depth;
+    bool prev_delta, valid_ray, active;
+    Pcg32 rng;
+};
+struct TapCtx { uint32_t max_hits, n_iter; uint32_t *hit_prim; float *hit_t; };
+struct StatCtx { uint32_t closest, shadow, nodes, tris, vertices; };
+
+AM_D void path_init(PathState &ps, const Ray &ray) {
+    ps.ray = ray; ps.throughput = v3(1.f); ps.result = v3(0.f); ps.prev_p = v3(0.f); ps.eta = 1.f; ps.prev_bsdf_pdf = 1.f;
+    ps.depth = 0; ps.prev_delta = true; ps.valid_ray = false;   // no environment emitter on this path (mvpath_single.h:98)
+    ps.active = true;
+}
+
+// One iteration of the while-loop of MVPT::sample_single (src/integrators/mvpath_single.h:130-275), wavefront
+// (JIT) semantics: every lane active at the top of the iteration draws 2 + 1 + 2 + 1 random numbers.
+template <bool TAP, bool STATS> AM_D void path_bounce(const DScene &s, PathState &ps, TapCtx *tap, StatCtx *st) {
+    uint32_t *cn = STATS ? &st->nodes : nullptr, *ct = STATS ? &st->tris : nullptr;
+    Hit h = intersect<false>(s, ps.ray, cn, ct);
+    if (STATS) { st->closest++; st->vertices++; }
+    const DMesh *mesh;
+    SI si = make_si(s, ps.ray, h, &mesh);
+    if (TAP) {
+        if (tap->n_iter < tap->max_hits) { tap->hit_prim[tap->n_iter] = si.prim; tap->hit_t[tap->n_iter] = h.t; }
+        tap->n_iter++;
+    }
+    // direct emission (:148-163); DirectionSample(scene, si, prev_si) records.h:141-149
+    if (si.valid && mesh->emitter >= 0) {
+        V3 rel = si.p - ps.prev_p; float dist = norm(rel); V3 d = rel / dist;
+        float em_pdf = 0.f;
+        if (!ps.prev_delta) em_pdf = pdf_emitter_direction(s, mesh, d, si.sh_n, dist);
+        float mis_bsdf = mis_weight(ps.prev_bsdf_pdf, em_pdf);
+        V3 le = select3(si.wi.z > 0.f && ps.prev_bsdf_pdf > 0.f, ld3(s.emitters[mesh->emitter].radiance));   // area.cpp:82-86
+        ps.result = fmadd(ps.throughput, le * mis_bsdf, ps.result);
+    }
+    bool active_next = (ps.depth + 1 < s.max_depth) && si.valid;
+    if (!active_next) {
+        // the lane finishes this iteration (its six draws and the BSDF call are unobservable) and leaves the loop
+        ps.valid_ray = ps.valid_ray || si.valid;     // :252
+        ps.active = false;
+        return;
+    }
+    const DBsdf &bsdf = s.bsdfs[mesh->bsdf];
+    // emitter sampling (:179-201)
+    bool active_em = (bsdf.flags & L_SMOOTH) != 0;
+    V2 es; es.x = ps.rng.next_f32(); es.y = ps.rng.next_f32();
+    DirectionSample ds; V3 em_weight = v3(0.f), wo = v3(0.f); ds.pdf = 0.f;
+    if (active_em) {
+        ds = sample_emitter_direction(s, si, es, &em_weight, cn, ct);
+        if (STATS) st->shadow++;
+        active_em = ds.pdf != 0.f;
+        wo = si.to_local(ds.d);
+    }
+    float s1 = ps.rng.next_f32(); V2 s2; s2.x = ps.rng.next_f32(); s2.y = ps.rng.next_f32();
+    BsdfResult br = bsdf_eval_pdf_sample(bsdf, si.wi, wo, s1, s2);
+    if (active_em) {
+        float mis_em = mis_weight(ds.pdf, br.pdf);
+        ps.result = fmadd(ps.throughput, br.f * em_weight * mis_em, ps.result);
+    }
+    ps.ray = spawn_ray(si.p, si.n, si.to_world(br.bs.wo));
+    ps.throughput = ps.throughput * br.weight;
+    ps.eta *= br.bs.eta;
+    ps.valid_ray = true;
+    ps.prev_p = si.p; ps.prev_bsdf_pdf = br.bs.pdf; ps.prev_delta = (br.bs.type & L_DELTA) != 0;
+    ps.depth += 1;
+    // Russian roulette (:264-274)
+    float tmax = hmax(ps.throughput);
+    float rr_prob = min_(tmax * sqr(ps.eta), .95f);
+    bool rr_active = ps.depth >= s.rr_depth, rr_continue = ps.rng.next_f32() < rr_prob;
+    if (rr_active) ps.throughput = ps.throughput * rcp(rr_prob);
+    ps.active = (!rr_active || rr_continue) && (tmax != 0.f);
+}
+
+// Lane -> (pixel, sampler, camera ray): MVPT::render lane map (src/integrators/mvpath.cpp:174-190) and
+// MVPT::render_sample (src/integrators/mvpath_single.h:50-75).
+struct LaneSetup { float spx, spy; uint32_t view, pixel; bool in_film; };
+AM_D void lane_setup(const DScene &s, uint32_t seed_value, uint32_t lane, uint32_t px, uint32_t py, PathState &ps, LaneSetup &ls) {
+    ps.rng = sampler_seed(seed_value, lane);
+    float sx = rcp((float) s.film_w), sy = rcp((float) s.film_h);
+    float jx = ps.rng.next_f32(), jy = ps.rng.next_f32();
+    ls.spx = (float) (int32_t) px + jx; ls.spy = (float) (int32_t) py + jy;
+    V2 adjusted = v2(fmadd(ls.spx, sx, -0.f * sx), fmadd(ls.spy, sy, -0.f * sy));
+    V2 aperture = v2(.5f, .5f);
+    if (s.thinlens) { aperture.x = ps.rng.next_f32(); aperture.y = ps.rng.next_f32(); }
+    Ray ray = sensor_sample_ray(s, adjusted, aperture, &ls.view);
+    path_init(ps, ray);
+    // ImageBlock::put, box filter (src/render/imageblock.cpp:210-233): pixel = floor(sample_pos)
+    uint32_t ux = (uint32_t) (int32_t) floorf(ls.spx), uy = (uint32_t) (int32_t) floorf(ls.spy);
+    ls.in_film = ux < s.film_w && uy < s.film_h;
+    ls.pixel = uy * s.film_w + ux;
+}
+
+// Map a launch-local lane ticket to (global lane, pixel) through the tile list.
+AM_D bool ticket_to_lane(const RenderParams &p, const DScene &s, unsigned long long ticket, uint32_t *lane, uint32_t *px, uint32_t *py) {
+    if (ticket >= p.n_lanes) return false;
+    uint32_t lo = 0, hi = p.n_tiles - 1;
+    while (lo < hi) {                       // last tile whose lane_begin <= ticket
+        uint32_t mid = (lo + hi + 1) >> 1;
+        if (p.tiles[mid].lane_begin <= ticket) lo = mid; else hi = mid - 1;
+    }
+    const TileDesc &t = p.tiles[lo];
+    unsigned long long r = ticket - t.lane_begin;
+    uint32_t k = (uint32_t) (r % t.spp), pl = (uint32_t) (r / t.spp);
+    uint32_t ty = pl / t.w, tx = pl - ty * t.w;
+    *px = t.x0 + tx; *py = t.y0 + ty;
+    *lane = (*py * s.film_w + *px) * p.spp_per_pass + k;
+    return true;
+}
+
+// Film splat with warp-aggregated atomics: lanes of the (converged) group `mask` that target the same pixel are
+// summed in lane order with shuffles and the lowest lane issues one 16-byte vector reduction (RED.128) per pixel.
+AM_D void splat_aggregated(unsigned mask, bool do_put, uint32_t pixel, float4 val, float4 *film, float2 *moments) {
+    unsigned lane = threadIdx.x & 31u;
+    uint32_t key = do_put ? pixel : 0xffffffffu;
+    unsigned peers = __match_any_sync(mask, key);
+    int iters = __reduce_max_sync(mask, do_put ? __popc(peers) : 0);
+    unsigned rem = peers;
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f); float m2 = 0.f;
+    float lum = 0.2126f * val.x + 0.7152f * val.y + 0.0722f * val.z, lum2 = lum * lum;
+    for (int i = 0; i < iters; ++i) {
+        int src = rem ? (__ffs(rem) - 1) : (int) lane;
+        float vx = __shfl_sync(mask, val.x, src), vy = __shfl_sync(mask, val.y, src),
+              vz = __shfl_sync(mask, val.z, src), vw = __shfl_sync(mask, val.w, src);
+        float vm = moments ? __shfl_sync(mask, lum2, src) : 0.f;
+        if (rem) { acc.x += vx; acc.y += vy; acc.z += vz; acc.w += vw; m2 += vm; }
+        rem &= rem - 1;
+    }
+    if (do_put && lane == (unsigned) (__ffs(peers) - 1)) {
+        atomicAdd(film + pixel, acc);
+        if (moments) atomicAdd(moments + pixel, make_float2(0.2126f * acc.x + 0.7152f * acc.y + 0.0722f * acc.z, m2));
+    }
+}
+
+AM_D void flush_stats(const StatCtx &st, unsigned long long *c) {
+    // warp-reduce, one atomic per counter per warp
+    uint32_t v[5] = { st.closest, st.shadow, st.nodes, st.tris, st.vertices };
+    #pragma unroll
+    for (int i = 0; i < 5; ++i) {
+        uint32_t x = __reduce_add_sync(0xffffffffu, v[i]);
+        if ((threadIdx.x & 31u) == 0 && x) atomicAdd(c + CTR_CLOSEST + i, (unsigned long long) x);
+    }
+}
+
+// MODE 0: a warp takes 32 consecutive tickets and traces them to completion before taking the next 32.
+// MODE 1: path regeneration -- whenever at least REGEN_MIN lanes of the warp are idle they splat and take fresh
+//         tickets together, so the warp stays full while paths have different lengths.
+#define AM_REGEN_MIN 8
+template <int MODE, bool STATS> __global__ void __launch_bounds__(128)
+render_pass_kernel(const DScene s, const RenderParams p) {
+    const unsigned lane_id = threadIdx.x & 31u;
+    PathState ps; LaneSetup ls; ps.active = false;
+    bool has_result = false, exhausted = false;
+    StatCtx st; st.closest = st.shadow = st.nodes = st.tris = st.vertices = 0;
+    for (;;) {
+        bool idle = !ps.active;
+        unsigned idle_mask = __ballot_sync(0xffffffffu, idle);
+        bool refill = MODE == 0 ? idle_mask == 0xffffffffu : (__popc(idle_mask) >= AM_REGEN_MIN || idle_mask == 0xffffffffu);
+        if (refill) {
+            if (idle) {
+                // splat finished lanes (imageblock.h:185-215: value = spec * ray_weight (1), weight channel += 1)
+                unsigned m = idle_mask;
+                V3 L = ps.valid_ray ? ps.result : v3(0.f);
+                splat_aggregated(m, has_result && ls.in_film, ls.pixel, make_float4(L.x, L.y, L.z, 1.f), p.film, p.moments);
+                has_result = false;
+                if (!exhausted) {
+                    unsigned long long base = 0;
+                    unsigned leader = __ffs(m) - 1;
+                    if (lane_id == leader) base = atomicAdd(p.counters + CTR_TICKET, (unsigned long long) __popc(m));
+                    base = __shfl_sync(m, base, leader);
+                    unsigned long long ticket = base + __popc(m & ((1u << lane_id) - 1u));
+                    uint32_t lane, px, py;
+                    if (ticket_to_lane(p, s, ticket, &lane, &px, &py)) {
+                        lane_setup(s, p.seed_value, lane, px, py, ps, ls);
+                        has_result = true;
+                        if (s.max_depth == 0) ps.active = false;    // mvpath_single.h:86-87
+                    } else exhausted = true;
+                }
+            }
+            if (__all_sync(0xffffffffu, !ps.active && !has_result)) break;
+        }
+        if (ps.active) path_bounce<false, STATS>(s, ps, nullptr, &st);
+    }
+    if (STATS) flush_stats(st, p.counters);
+}
+
+void launch_render_pass(const DScene &s, const RenderParams &p, int mode, int sm_count, bool stats, cudaStream_t stream) {
+    // persistent grid: a whole number of CTAs per SM
+    int ctas_per_sm = 0;
+    const void *fn = mode == 0 ? (stats ? (const void *) render_pass_kernel<0, true> : (const void *) render_pass_kernel<0, false>)
+                               : (stats ? (const void *) render_pass_kernel<1, true> : (const void *) render_pass_kernel<1, false>);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, fn, 128, 0);
+    if (ctas_per_sm < 1) ctas_per_sm = 1;
+    dim3 grid(sm_count * ctas_per_sm), block(128);
+    unsigned long long warps_needed = (p.n_lanes + 31) / 32;
+    unsigned long long ctas_needed = (warps_needed + 3) / 4;
+    if (ctas_needed < grid.x) grid.x = (unsigned) (ctas_needed ? ctas_needed : 1);
+    if (mode == 0) { if (stats) render_pass_kernel<0, true><<<grid, block, 0, stream>>>(s, p); else render_pass_kernel<0, false><<<grid, block, 0, stream>>>(s, p); }
+    else           { if (stats) render_pass_kernel<1, true><<<grid, block, 0, stream>>>(s, p); else render_pass_kernel<1, false><<<grid, block, 0, stream>>>(s, p); }
+}
+
+// ------------------------------------------------------------------------------------------------
+// HDRFilm::develop (src/films/hdrfilm.cpp:321-408): rgb = RGB / (W == 0 ? 1 : W).  Streaming, HBM-bound:
+// 16 B read + 12 B written per pixel.
+__global__ void develop_kernel(const float4 *__restrict__ film, float *__restrict__ rgb, size_t npix) {
+    size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x, stride = (size_t) gridDim.x * blockDim.x;
+    for (; i < npix; i += stride) {
+        float4 v = film[i];
+        float w = (v.w == 0.f) ? 1.f : v.w;
+        rgb[3 * i] = fdiv(v.x, w); rgb[3 * i + 1] = fdiv(v.y, w); rgb[3 * i + 2] = fdiv(v.z, w);
+    }
+}
+void launch_develop(const float4 *film, float *rgb, size_t npix, cudaStream_t st) {
+    if (!npix) return;
+    unsigned blocks = (unsigned) ((npix + 255) / 256); if (blocks > 148 * 16) blocks = 148 * 16;
+    develop_kernel<<<blocks, 256, 0, st>>>(film, rgb, npix);
+}
+
+// Adaptive allocator statistics (build-defined; the reference has no variance estimator).
+// Per tile: [0] sum over pixels of the variance of the pixel mean (relative, luminance), [1] number of pixels with
+// weight > 1, [2] sum of weights (samples traced so far), [3] sum of luminance.
+__global__ void view_stats_kernel(const float4 *__restrict__ film, const float2 *__restrict__ moments, uint32_t film_w,
+                                  const TileDesc *__restrict__ tiles, float *__restrict__ stats) {
+    const TileDesc t = tiles[blockIdx.y];
+    uint32_t npix = t.w * t.h;
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < npix; i += gridDim.x * blockDim.x) {
+        uint32_t ty = i / t.w, tx = i - ty * t.w;
+        size_t pix = (size_t) (t.y0 + ty) * film_w + (t.x0 + tx);
+        float4 f = film[pix]; float2 m = moments[pix];
+        float n = f.w;
+        if (n > 1.f) {
+            float mean = m.x / n, var = fmaxf(m.y / n - mean * mean, 0.f) / (n - 1.f);   // variance of the mean
+            a0 += var / (mean * mean + 1e-2f); a1 += 1.f;
+        }
+        a2 += n; a3 += m.x;
+    }
+    for (int o = 16; o; o >>= 1) {
+        a0 += __shfl_down_sync(0xffffffffu, a0, o); a1 += __shfl_down_sync(0xffffffffu, a1, o);
+        a2 += __shfl_down_sync(0xffffffffu, a2, o); a3 += __shfl_down_sync(0xffffffffu, a3, o);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        float *o = stats + 4 * blockIdx.y;
+        atomicAdd(o, a0); atomicAdd(o + 1, a1); atomicAdd(o + 2, a2); atomicAdd(o + 3, a3);
+    }
+}
+void launch_view_stats(const float4 *film, const float2 *moments, uint32_t film_w, const TileDesc *tiles, uint32_t n_tiles,
+                       float *stats, cudaStream_t st) {
+    if (!n_tiles) return;
+    cudaMemsetAsync(stats, 0, sizeof(float) * 4 * n_tiles, st);
+    dim3 grid(64, n_tiles);
+    view_stats_kernel<<<grid, 256, 0, st>>>(film, moments, film_w, tiles, stats);
+}
+
+// ------------------------------------------------------------------------------------------------ taps
+__global__ void trace_lanes_kernel(const DScene s, uint32_t seed_value, uint32_t spp_per_pass, uint32_t lane_begin, uint32_t n,
+                                   int trace, const LaneTaps t, unsigned long long *counters) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    StatCtx st; st.closest = st.shadow = st.nodes = st.tris = st.vertices = 0;
+    if (i < n) {
+        uint32_t lane = lane_begin + i, idx = lane / spp_per_pass, py = idx / s.film_w, px = idx - py * s.film_w;
+        PathState ps; LaneSetup ls;
+        lane_setup(s, seed_value, lane, px, py, ps, ls);
+        if (t.sample_pos) { t.sample_pos[2 * i] = ls.spx; t.sample_pos[2 * i + 1] = ls.spy; }
+        if (t.ray_o) {
+            t.ray_o[3 * i] = ps.ray.o.x; t.ray_o[3 * i + 1] = ps.ray.o.y; t.ray_o[3 * i + 2] = ps.ray.o.z;
+            t.ray_d[3 * i] = ps.ray.d.x; t.ray_d[3 * i + 1] = ps.ray.d.y; t.ray_d[3 * i + 2] = ps.ray.d.z;
+            t.ray_maxt[i] = ps.ray.maxt;
+        }
+        if (t.view) t.view[i] = ls.view;
+        if (t.pixel) t.pixel[i] = ls.in_film ? ls.pixel : 0xffffffffu;
+        TapCtx tap; tap.max_hits = t.max_hits; tap.n_iter = 0;
+        tap.hit_prim = t.hit_prim + (size_t) i * t.max_hits; tap.hit_t = t.hit_t + (size_t) i * t.max_hits;
+        for (uint32_t k = 0; k < t.max_hits; ++k) { tap.hit_prim[k] = 0xfffffffeu; tap.hit_t[k] = 0.f; }
+        if (!trace || s.max_depth == 0) ps.active = false;
+        while (ps.active) path_bounce<true, true>(s, ps, &tap, &st);
+        if (t.radiance) {
+            V3 L = ps.valid_ray ? ps.result : v3(0.f);
+            t.radiance[4 * i] = L.x; t.radiance[4 * i + 1] = L.y; t.radiance[4 * i + 2] = L.z; t.radiance[4 * i + 3] = ps.valid_ray ? 1.f : 0.f;
+        }
+    }
+    if (counters) flush_stats(st, counters);
+}
+void launch_trace_lanes(const DScene &s, uint32_t seed_value, uint32_t spp_per_pass, uint32_t lane_begin, uint32_t n, int trace,
+                        const LaneTaps &taps, unsigned long long *counters, cudaStream_t st) {
+    if (!n) return;
+    trace_lanes_kernel<<<(n + 127) / 128, 128, 0, st>>>(s, seed_value, spp_per_pass, lane_begin, n, trace, taps, counters);
+}
+
+__global__ void intersect_kernel(const DScene s, const float *o, const float *d, const float *maxt, uint32_t n, int any,
+                                 uint32_t *prim, float *tuv, unsigned long long *counters) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    StatCtx st; st.closest = st.shadow = st.nodes = st.tris = st.vertices = 0;
+    if (i < n) {
+        Ray r; r.o = v3(o[3 * i], o[3 * i + 1], o[3 * i + 2]); r.d = v3(d[3 * i], d[3 * i + 1], d[3 * i + 2]); r.maxt = maxt[i];
+        Hit h = any ? intersect<true>(s, r, &st.nodes, &st.tris) : intersect<false>(s, r, &st.nodes, &st.tris);
+        prim[i] = h.tri == AM_NO_HIT ? AM_NO_HIT : __float_as_uint(s.tris[3 * (size_t) h.tri].w);
+        if (tuv) { tuv[3 * i] = h.t; tuv[3 * i + 1] = h.u; tuv[3 * i + 2] = h.v; }
+        if (any) st.shadow++; else st.closest++;
+    }
+    if (counters) flush_stats(st, counters);
+}
+void launch_intersect(const DScene &s, const float *o, const float *d, const float *maxt, uint32_t n, int any,
+                      uint32_t *prim, float *tuv, unsigned long long *counters, cudaStream_t st) {
+    if (!n) return;
+    intersect_kernel<<<(n + 127) / 128, 128, 0, st>>>(s, o, d, maxt, n, any, prim, tuv, counters);
+}
+
+// out[16 * i + ...] = f[3], pdf, wo[3], bs_pdf, bs_eta, bits(bs_type), weight[3], pad[3]
+__global__ void bsdf_tap_kernel(const DScene s, int bsdf, const float *wi, const float *wo, const float *s1, const float *s2, uint32_t n, float *out) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; if (i >= n) return;
+    BsdfResult r = bsdf_eval_pdf_sample(s.bsdfs[bsdf], v3(wi[3 * i], wi[3 * i + 1], wi[3 * i + 2]), v3(wo[3 * i], wo[3 * i + 1], wo[3 * i + 2]),
+                                        s1[i], v2(s2[2 * i], s2[2 * i + 1]));
+    float *q = out + 16 * (size_t) i;
+    q[0] = r.f.x; q[1] = r.f.y; q[2] = r.f.z; q[3] = r.pdf; q[4] = r.bs.wo.x; q[5] = r.bs.wo.y; q[6] = r.bs.wo.z; q[7] = r.bs.pdf;
+    q[8] = r.bs.eta; q[9] = __uint_as_float(r.bs.type); q[10] = r.weight.x; q[11] = r.weight.y; q[12] = r.weight.z; q[13] = q[14] = q[15] = 0.f;
+}
+void launch_bsdf_tap(const DScene &s, int bsdf, const float *wi, const float *wo, const float *s1, const float *s2, uint32_t n, float *out, cudaStream_t st) {
+    if (!n) return;
+    bsdf_tap_kernel<<<(n + 127) / 128, 128, 0, st>>>(s, bsdf, wi, wo, s1, s2, n, out);
+}
+
+// op: 0 sin 1 cos 2 exp 3 log 4 erf 5 erfinv 6 exp2 7 sqrt 8 rcp 9 rsqrt 10 safe_sqrt 11 tan
+__global__ void math_tap_kernel(int op, const float *in, uint32_t n, float *out) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; if (i >= n) return;
+    float x = in[i], r = x, sn, cs;
+    switch (op) {
+        case 0: sincos_(x, &sn, &cs); r = sn; break; case 1: sincos_(x, &sn, &cs); r = cs; break;
+        case 2: r = exp_(x); break; case 3: r = log_(x); break; case 4: r = erf_(x); break; case 5: r = erfinv_(x); break;
+        case 6: r = exp2_(x); break; case 7: r = fsqrt(x); break; case 8: r = rcp(x); break; case 9: r = rsqrt(x); break;
+        case 10: r = safe_sqrt(x); break; case 11: r = tan_(x); break;
+    }
+    out[i] = r;
+}
+void launch_math_tap(int op, const float *in, uint32_t n, float *out, cudaStream_t st) {
+    if (!n) return;
+    math_tap_kernel<<<(n + 127) / 128, 128, 0, st>>>(op, in, n, out);
+}
+__global__ void sampler_tap_kernel(uint32_t seed_value, uint32_t lane, uint32_t n, float *out) {
+    if (blockIdx.x || threadIdx.x) return;
+    Pcg32 r = sampler_seed(seed_value, lane);
+    for (uint32_t i = 0; i < n; ++i) out[i] = r.next_f32();
+}
+void launch_sampler_tap(uint32_t seed_value, uint32_t lane, uint32_t n, float *out, cudaStream_t st) {
+    sampler_tap_kernel<<<1, 32, 0, st>>>(seed_value, lane, n, out);
+}
+__global__ void l2_flush_kernel(float *buf, size_t n) {
+    size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x, stride = (size_t) gridDim.x * blockDim.x;
+    for (; i < n; i += stride) buf[i] = buf[i] + 1.f;
+}
+void launch_l2_flush(float *buf, size_t n, cudaStream_t st) { if (n) l2_flush_kernel<<<148 * 8, 256, 0, st>>>(buf, n); }
+
+} // namespace amvpt

@@ -1,0 +1,48 @@
+// kernels.cuh -- launch parameter blocks shared by kernels.cu (device) and render.cpp / capi.cpp (host).
+#pragma once
+#include "dtypes.h"
+
+namespace amvpt {
+
+// One rectangle of the quilt traced this pass with `spp` samples per pixel (<= lane stride spp_per_pass).
+// lane_begin = prefix sum of w*h*spp over the preceding tiles of the launch.
+struct TileDesc { uint32_t x0, y0, w, h; uint32_t spp, pad; unsigned long long lane_begin; };
+
+struct RenderParams {
+    uint32_t seed_value;       // sampler seed + spp_per_pass * pass + render seed (mvpath.cpp:226-231, sampler.cpp:129)
+    uint32_t spp_per_pass;     // lane stride of the reference's lane -> pixel map (mvpath.cpp:174-190)
+    uint32_t n_tiles, pad0;
+    const TileDesc *tiles;
+    unsigned long long n_lanes;
+    float4 *film;              // RGBW, film_w * film_h
+    float2 *moments;           // optional (sum lum, sum lum^2) per pixel for the adaptive allocator, or nullptr
+    unsigned long long *counters;   // [0] next-lane ticket, [1] closest rays, [2] shadow rays, [3] nodes, [4] tris, [5] path vertices
+};
+
+// Per-lane debug taps of the parity tests (mirrors oracle/amvpt_oracle.cpp orc_trace_lanes)
+struct LaneTaps {
+    float *sample_pos, *ray_o, *ray_d, *ray_maxt; uint32_t *view; float *radiance; uint32_t *pixel;
+    uint32_t max_hits; uint32_t *hit_prim; float *hit_t;
+};
+
+enum Counter { CTR_TICKET = 0, CTR_CLOSEST = 1, CTR_SHADOW = 2, CTR_NODES = 3, CTR_TRIS = 4, CTR_VERTICES = 5, CTR_COUNT = 8 };
+
+// host-callable launchers (kernels.cu)
+void launch_render_pass(const DScene &s, const RenderParams &p, int mode, int sm_count, bool stats, cudaStream_t st);
+void launch_trace_lanes(const DScene &s, uint32_t seed_value, uint32_t spp_per_pass, uint32_t lane_begin, uint32_t n, int trace,
+                        const LaneTaps &taps, unsigned long long *counters, cudaStream_t st);
+void launch_develop(const float4 *film, float *rgb, size_t npix, cudaStream_t st);
+void launch_view_stats(const float4 *film, const float2 *moments, uint32_t film_w, const TileDesc *tiles, uint32_t n_tiles,
+                       float *stats /* n_tiles * 4 */, cudaStream_t st);
+void launch_intersect(const DScene &s, const float *o, const float *d, const float *maxt, uint32_t n, int any,
+                      uint32_t *prim, float *tuv, unsigned long long *counters, cudaStream_t st);
+void launch_bsdf_tap(const DScene &s, int bsdf, const float *wi, const float *wo, const float *s1, const float *s2, uint32_t n,
+                     float *out /* n * 16 */, cudaStream_t st);
+void launch_math_tap(int op, const float *in, uint32_t n, float *out, cudaStream_t st);
+void launch_sampler_tap(uint32_t seed_value, uint32_t lane, uint32_t n, float *out, cudaStream_t st);
+void launch_l2_flush(float *buf, size_t n, cudaStream_t st);
+
+// Wavefront scheduler (stage kernels + stream compaction)
+struct WavefrontBuffers;   // defined in kernels.cu
+
+} // namespace amvpt

@@ -1,0 +1,167 @@
+// render.cpp -- host side of MVPathIntegrator::render() (src/integrators/mvpath.cpp:7-278, wavefront branch):
+// sample-count rounding, pass loop, per-pass sampler seeding, film hand-off; plus the build-defined pieces the
+// reference does not have: view sharding across ranks and the adaptive per-view allocator.
+#include "host.h"
+#include <algorithm>
+#include <cmath>
+
+namespace amvpt {
+
+// Work units of one rank.  world == 1: the whole quilt as one rectangle, lanes in the reference's row-major order.
+// Otherwise the quilt is cut into view tiles (and, when there are fewer views than ranks, horizontal bands of a
+// view); unit u goes to rank u mod world.  Lane indices stay global, so any partition reproduces the same samples.
+static std::vector<TileDesc> rank_tiles(const Scene &s, const Shard &sh, bool per_view) {
+    std::vector<TileDesc> out;
+    if (sh.world <= 1 && !per_view) {
+        TileDesc t{}; t.x0 = 0; t.y0 = 0; t.w = s.film_w; t.h = s.film_h; t.pad = 0; out.push_back(t); return out;
+    }
+    Shard all; std::vector<TileDesc> views = s.view_tiles(all);
+    uint32_t n_views = (uint32_t) views.size(), bands = 1;
+    if (n_views < sh.world) bands = (sh.world + n_views - 1) / n_views;
+    bands = std::min(bands, std::max(s.res_y, 1u));
+    for (uint32_t v = 0; v < n_views; ++v) for (uint32_t b = 0; b < bands; ++b) {
+        uint32_t unit = v * bands + b;
+        if (unit % sh.world != sh.rank) continue;
+        TileDesc t = views[v];
+        uint32_t y0 = (uint32_t) ((uint64_t) t.h * b / bands), y1 = (uint32_t) ((uint64_t) t.h * (b + 1) / bands);
+        t.y0 += y0; t.h = y1 - y0;
+        if (t.h) out.push_back(t);
+    }
+    return out;
+}
+static unsigned long long finish_tiles(std::vector<TileDesc> &tiles) {
+    unsigned long long lanes = 0; std::vector<TileDesc> keep;
+    for (auto &t : tiles) { if (!t.spp) continue; t.lane_begin = lanes; lanes += (unsigned long long) t.w * t.h * t.spp; keep.push_back(t); }
+    tiles.swap(keep); return lanes;
+}
+
+void render(Scene &s, const RenderOptions &opt) {
+    if (!s.committed) AM_THROW("render: scene not committed to a device");
+    if (s.integrator.is_mvpath && !s.multi_sensor) AM_THROW("This integrator can only be used with MultiSensor !");
+    if (s.integrator.sa_reuse && s.sensors.size() > 1 && s.integrator.reuse_count != 1)
+        AM_THROW("mvpath: cross-view sample reuse (sa_reuse) is not implemented in this build");
+    if (opt.shard.world == 0 || opt.shard.rank >= opt.shard.world) AM_THROW("render: invalid shard %u/%u", opt.shard.rank, opt.shard.world);
+    AM_CUDA(cudaSetDevice(s.device));
+    cudaStream_t st = opt.stream;
+    s.stop = false;
+    // mvpath.cpp:33-41
+    uint32_t spp = opt.spp ? opt.spp : s.sample_count;
+    if (!spp) AM_THROW("render: sample count is zero");
+    uint32_t lim = s.integrator.spp_pass_lim;
+    uint32_t spp_per_pass = lim ? std::min(lim, spp) : spp;
+    uint32_t n_passes = spp / spp_per_pass;
+    spp = n_passes * spp_per_pass;
+    s.sample_count = spp;
+    // mvpath.cpp:133-147
+    unsigned long long wavefront = (unsigned long long) s.film_w * s.film_h * spp_per_pass, limit = 0xffffffffull;
+    if (wavefront > limit) {
+        spp_per_pass /= (uint32_t) ((wavefront + limit - 1) / limit);
+        if (!spp_per_pass) AM_THROW("render: film too large for a 32-bit wavefront");
+        n_passes = spp / spp_per_pass;
+    }
+    bool adaptive = opt.adaptive;
+    std::vector<TileDesc> base = rank_tiles(s, opt.shard, adaptive);
+    if (base.size() > s.tiles_cap) {
+        s.tiles_cap = (uint32_t) base.size(); s.tiles_dev = (TileDesc *) s.dalloc(sizeof(TileDesc) * s.tiles_cap);
+    }
+    uint32_t n_views = s.grid_x * s.grid_y;
+    RenderStats rs;
+    cudaEvent_t e0, e1; AM_CUDA(cudaEventCreate(&e0)); AM_CUDA(cudaEventCreate(&e1));
+    AM_CUDA(cudaMemsetAsync(s.counters, 0, sizeof(unsigned long long) * CTR_COUNT, st));
+
+    RenderParams p{};
+    p.spp_per_pass = spp_per_pass; p.tiles = s.tiles_dev; p.film = s.film; p.moments = adaptive ? s.moments : nullptr; p.counters = s.counters;
+    auto launch = [&](std::vector<TileDesc> &tiles, uint32_t pass) {
+        unsigned long long lanes = finish_tiles(tiles);
+        if (!lanes) return;
+        AM_CUDA(cudaMemcpyAsync(s.tiles_dev, tiles.data(), sizeof(TileDesc) * tiles.size(), cudaMemcpyHostToDevice, st));
+        AM_CUDA(cudaMemsetAsync(s.counters + CTR_TICKET, 0, sizeof(unsigned long long), st));
+        p.seed_value = s.sampler_seed + (spp_per_pass * pass + opt.seed);     // mvpath.cpp:226-231, sampler.cpp:129
+        p.n_tiles = (uint32_t) tiles.size(); p.n_lanes = lanes;
+        launch_render_pass(s.d, p, opt.scheduler == SCHED_WARP_BATCH ? 0 : 1, s.sm_count, opt.stats, st);
+        AM_CUDA(cudaGetLastError());
+        rs.paths += lanes; rs.launches++;
+    };
+
+    AM_CUDA(cudaEventRecord(e0, st));
+    if (!adaptive) {
+        for (uint32_t pass = 0; pass < n_passes && !s.stop; ++pass) {
+            std::vector<TileDesc> tiles = base; for (auto &t : tiles) t.spp = spp_per_pass;
+            launch(tiles, pass); rs.passes++;
+        }
+        rs.spp_done = spp;
+    } else {
+        // Adaptive allocation (build-defined).  Budget: spp * (pixels of the whole quilt) samples.  Warm-up passes give
+        // every view adaptive_min_spp; then each pass hands view v a sample count n_v <= spp_per_pass proportional to its
+        // error estimate (mean relative variance of the pixel means), recomputed from all-reduced statistics so that every
+        // rank derives the same allocation.
+        unsigned long long view_px = (unsigned long long) s.res_x * s.res_y, budget = (unsigned long long) spp * view_px * n_views, used = 0;
+        uint32_t warm = std::max(1u, (std::min(opt.adaptive_min_spp, spp) + spp_per_pass - 1) / spp_per_pass);
+        std::vector<float> hstats(4 * (size_t) n_views), err(n_views, 1.f);
+        if (4 * n_views > 4 * s.tiles_cap) s.view_stats_dev = (float *) s.dalloc(sizeof(float) * 4 * n_views);
+        Shard all; std::vector<TileDesc> all_views = s.view_tiles(all);
+        std::vector<uint32_t> alloc(n_views, spp_per_pass);
+        // the reference's lane map allows spp / spp_per_pass passes of distinct seeds; adaptive passes keep going with
+        // fresh seeds (pass index) until the budget is spent
+        uint32_t max_passes = 4 * n_passes + 16;
+        for (uint32_t pass = 0; pass < max_passes && used < budget && !s.stop; ++pass) {
+            if (pass >= warm) {
+                // statistics of the views this rank owns, summed over ranks
+                std::vector<TileDesc> mine = base; for (auto &t : mine) t.spp = 1;
+                AM_CUDA(cudaMemsetAsync(s.view_stats_dev, 0, sizeof(float) * 4 * n_views, st));
+                std::vector<TileDesc> per_view(n_views);
+                for (auto &t : all_views) { per_view[t.pad] = t; per_view[t.pad].w = 0; per_view[t.pad].h = 0; }
+                // bands of the same view accumulate into the view's slot (launch once per owned tile list)
+                for (auto &t : mine) {
+                    TileDesc one = t; AM_CUDA(cudaMemcpyAsync(s.tiles_dev, &one, sizeof(TileDesc), cudaMemcpyHostToDevice, st));
+                    launch_view_stats(s.film, s.moments, s.film_w, s.tiles_dev, 1, s.view_stats_dev + 4 * (size_t) n_views, st);
+                    AM_CUDA(cudaStreamSynchronize(st));
+                    float tmp[4]; AM_CUDA(cudaMemcpy(tmp, s.view_stats_dev + 4 * (size_t) n_views, sizeof(tmp), cudaMemcpyDeviceToHost));
+                    for (int k = 0; k < 4; ++k) hstats[4 * (size_t) t.pad + k] += tmp[k];
+                }
+                AM_CUDA(cudaMemcpyAsync(s.view_stats_dev, hstats.data(), sizeof(float) * 4 * n_views, cudaMemcpyHostToDevice, st));
+                if (opt.allreduce) opt.allreduce(s.view_stats_dev, 4 * n_views, opt.allreduce_user);
+                AM_CUDA(cudaMemcpyAsync(hstats.data(), s.view_stats_dev, sizeof(float) * 4 * n_views, cudaMemcpyDeviceToHost, st));
+                AM_CUDA(cudaStreamSynchronize(st));
+                double total = 0.0; bool any = false;
+                for (uint32_t v = 0; v < n_views; ++v) {
+                    float e = hstats[4 * v + 1] > 0.f ? hstats[4 * v] / hstats[4 * v + 1] : 0.f;
+                    if (opt.adaptive_threshold > 0.f && e <= opt.adaptive_threshold) e = 0.f;
+                    err[v] = e; total += e; any |= e > 0.f;
+                }
+                std::fill(hstats.begin(), hstats.end(), 0.f);
+                if (!any) break;
+                unsigned long long remaining = budget - used;
+                double pass_budget = std::min<double>((double) remaining / (double) view_px, (double) spp_per_pass * n_views);
+                unsigned long long give = 0;
+                for (uint32_t v = 0; v < n_views; ++v) {
+                    uint32_t n = (uint32_t) std::llround(pass_budget * err[v] / total);
+                    n = std::min(n, spp_per_pass);
+                    if (give + (unsigned long long) n * view_px > remaining) n = (uint32_t) ((remaining - give) / view_px);
+                    alloc[v] = n; give += (unsigned long long) n * view_px;
+                }
+                if (!give) break;
+            } else {
+                unsigned long long remaining = budget - used, give = 0;
+                for (uint32_t v = 0; v < n_views; ++v) {
+                    uint32_t n = spp_per_pass;
+                    if (give + (unsigned long long) n * view_px > remaining) n = (uint32_t) ((remaining - give) / view_px);
+                    alloc[v] = n; give += (unsigned long long) n * view_px;
+                }
+            }
+            for (uint32_t v = 0; v < n_views; ++v) used += (unsigned long long) alloc[v] * view_px;
+            std::vector<TileDesc> tiles = base; for (auto &t : tiles) t.spp = alloc[t.pad];
+            launch(tiles, pass); rs.passes++;
+        }
+        rs.spp_done = (uint32_t) (used / (view_px * n_views));
+    }
+    AM_CUDA(cudaEventRecord(e1, st));
+    AM_CUDA(cudaEventSynchronize(e1));
+    float ms = 0.f; AM_CUDA(cudaEventElapsedTime(&ms, e0, e1)); rs.seconds = ms * 1e-3;
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    unsigned long long c[CTR_COUNT]; AM_CUDA(cudaMemcpy(c, s.counters, sizeof(c), cudaMemcpyDeviceToHost));
+    rs.closest_rays = c[CTR_CLOSEST]; rs.shadow_rays = c[CTR_SHADOW]; rs.nodes = c[CTR_NODES]; rs.tris = c[CTR_TRIS]; rs.vertices = c[CTR_VERTICES];
+    s.last = rs;
+}
+
+} // namespace amvpt

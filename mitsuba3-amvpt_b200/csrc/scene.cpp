@@ -1,0 +1,273 @@
+// scene.cpp -- host scene objects of the AMVPT path and their upload into HBM.
+#include "host.h"
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+
+namespace amvpt {
+
+std::string strfmt(const char *fmt, ...) {
+    char buf[2048]; va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof(buf), fmt, ap); va_end(ap); return buf;
+}
+void cuda_check(cudaError_t e, const char *what) {
+    if (e != cudaSuccess) AM_THROW("CUDA error %s: %s", what, cudaGetErrorString(e));
+}
+
+// ---------------------------------------------------------------- double-precision description transforms
+M4d m4d_translate(double x, double y, double z) { M4d r = m4d_identity(); r.m[0][3] = x; r.m[1][3] = y; r.m[2][3] = z; return r; }
+M4d m4d_scale(double x, double y, double z) { M4d r = m4d_identity(); r.m[0][0] = x; r.m[1][1] = y; r.m[2][2] = z; return r; }
+// dr::rotate<Matrix4>(axis, angle) (ext/drjit/include/drjit/transform.h:43-65); axis is normalised by the XML loader
+M4d m4d_rotate(double ax, double ay, double az, double angle_deg) {
+    double len = std::sqrt(ax * ax + ay * ay + az * az); ax /= len; ay /= len; az /= len;
+    double th = angle_deg * (3.14159265358979323846 / 180.0), s = std::sin(th), c = std::cos(th), cm = 1.0 - c;
+    double a[3] = { ax, ay, az }, s1[3] = { ay, az, ax }, s2[3] = { az, ax, ay }, t0[3], t1[3], t2[3];
+    for (int i = 0; i < 3; ++i) {
+        t0[i] = std::fma(a[i] * a[i], cm, c);
+        t1[i] = std::fma(a[i] * s1[i], cm, s2[i] * s);
+        t2[i] = std::fma(a[i] * s2[i], cm, -(s1[i] * s));
+    }
+    M4d r = m4d_identity();
+    r.m[0][0] = t0[0]; r.m[0][1] = t2[1]; r.m[0][2] = t1[2];
+    r.m[1][0] = t1[0]; r.m[1][1] = t0[1]; r.m[1][2] = t2[2];
+    r.m[2][0] = t2[0]; r.m[2][1] = t1[1]; r.m[2][2] = t0[2];
+    return r;
+}
+// Transform::look_at (include/mitsuba/core/transform.h:269-300)
+M4d m4d_look_at(const double *o, const double *t, const double *up) {
+    auto nrm = [](double *v) { double l = 1.0 / std::sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]); v[0] *= l; v[1] *= l; v[2] *= l; };
+    auto crs = [](const double *a, const double *b, double *r) { r[0] = a[1] * b[2] - a[2] * b[1]; r[1] = a[2] * b[0] - a[0] * b[2]; r[2] = a[0] * b[1] - a[1] * b[0]; };
+    double dir[3] = { t[0] - o[0], t[1] - o[1], t[2] - o[2] }, left[3], nup[3];
+    nrm(dir); crs(up, dir, left); nrm(left); crs(dir, left, nup);
+    M4d r = m4d_identity();
+    for (int i = 0; i < 3; ++i) { r.m[i][0] = left[i]; r.m[i][1] = nup[i]; r.m[i][2] = dir[i]; r.m[i][3] = o[i]; }
+    return r;
+}
+M4d m4d_inverse(const M4d &m) {
+    double a[4][8];
+    for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) { a[i][j] = m.m[i][j]; a[i][4 + j] = i == j ? 1.0 : 0.0; }
+    for (int c = 0; c < 4; ++c) {
+        int p = c; for (int r = c + 1; r < 4; ++r) if (std::fabs(a[r][c]) > std::fabs(a[p][c])) p = r;
+        if (a[p][c] == 0.0) AM_THROW("singular transform");
+        if (p != c) for (int j = 0; j < 8; ++j) std::swap(a[p][j], a[c][j]);
+        double inv = 1.0 / a[c][c]; for (int j = 0; j < 8; ++j) a[c][j] *= inv;
+        for (int r = 0; r < 4; ++r) if (r != c) { double f = a[r][c]; if (f != 0.0) for (int j = 0; j < 8; ++j) a[r][j] -= f * a[c][j]; }
+    }
+    M4d r; for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) r.m[i][j] = a[i][4 + j];
+    return r;
+}
+
+// ---------------------------------------------------------------- meshes
+// Mesh::build_pmf (src/render/mesh.cpp:444-486): table[i] = 0.5 * |cross(p1 - p0, p2 - p0)|; DiscreteDistribution::update
+// (include/mitsuba/core/distr_1d.h:233-264): cdf accumulated in double, stored as float; normalization = 1 / sum
+void HMesh::build_area_distr() {
+    uint32_t nf = nfaces(); pmf.resize(nf); cdf.resize(nf); double acc = 0.0;
+    for (uint32_t i = 0; i < nf; ++i) {
+        const float *a = &pos[3 * faces[3 * i]], *b = &pos[3 * faces[3 * i + 1]], *c = &pos[3 * faces[3 * i + 2]];
+        V3 p0 = v3(a[0], a[1], a[2]), p1 = v3(b[0], b[1], b[2]), p2 = v3(c[0], c[1], c[2]);
+        pmf[i] = .5f * norm(cross(p1 - p0, p2 - p0)); acc += (double) pmf[i]; cdf[i] = (float) acc;
+    }
+    sum = nf ? cdf[nf - 1] : 0.f; normalization = rcp(sum);
+}
+
+// ---------------------------------------------------------------- BSDF preparation
+// include/mitsuba/core/quad.h:27-86 gauss_legendre (double recurrences, float nodes / weights)
+static void legendre_pd(int l, double x, double *p, double *d) {
+    if (l == 0) { *p = 1; *d = 0; return; }
+    if (l == 1) { *p = x; *d = 1; return; }
+    double l_ppred = 1, l_pred = x, l_cur = 0, d_ppred = 0, d_pred = 1, d_cur = 0, k0 = 3, k1 = 2, k2 = 1;
+    for (int k = 2; k <= l; ++k) {
+        l_cur = (k0 * x * l_pred - k2 * l_ppred) / k1; d_cur = d_ppred + k0 * l_pred;
+        l_ppred = l_pred; l_pred = l_cur; d_ppred = d_pred; d_pred = d_cur; k2 = k1; k0 += 2; k1 += 1;
+    }
+    *p = l_cur; *d = d_cur;
+}
+static void gauss_legendre(int n, std::vector<float> &nodes, std::vector<float> &weights) {
+    nodes.assign(n, 0.f); weights.assign(n, 0.f); n--;
+    if (n == 0) { nodes[0] = 0; weights[0] = 2; }
+    else if (n == 1) { nodes[0] = (float) -std::sqrt(1.0 / 3.0); nodes[1] = -nodes[0]; weights[0] = weights[1] = 1; }
+    int m = (n + 1) / 2;
+    for (int i = 0; i < m; ++i) {
+        double x = -std::cos((double) (2 * i + 1) / (double) (2 * n + 2) * 3.14159265358979323846);
+        int it = 0;
+        while (true) {
+            if (++it > 20) break;
+            double p, d; legendre_pd(n + 1, x, &p, &d);
+            double step = p / d; x -= step;
+            if (std::fabs(step) <= 4 * std::fabs(x) * 0x1p-53) break;
+        }
+        double p, d; legendre_pd(n + 1, x, &p, &d);
+        weights[i] = weights[n - i] = (float) (2 / ((1 - x * x) * (d * d)));
+        nodes[i] = (float) x; nodes[n - i] = (float) -x;
+    }
+    if ((n % 2) == 0) { double p, d; legendre_pd(n + 1, 0.0, &p, &d); weights[n / 2] = (float) (2.0 / (d * d)); nodes[n / 2] = 0; }
+}
+// MicrofacetDistribution eval_reflectance / eval_transmittance (include/mitsuba/render/microfacet.h:464-560)
+static float mf_quadrature(const Microfacet &d, V3 wi, float eta, bool transmit) {
+    int res = eta > 1 ? 32 : 128;
+    std::vector<float> nodes, weights; gauss_legendre(res, nodes, weights);
+    float result = 0.f;
+    for (int jy = 0; jy < res; ++jy) for (int jx = 0; jx < res; ++jx) {
+        V2 node = v2(fmadd(nodes[jx], 0.5f, 0.5f), fmadd(nodes[jy], 0.5f, 0.5f));
+        float pdf; V3 m = d.sample(wi, node, &pdf);
+        float f, ct, eit, eti; fresnel(dot(wi, m), eta, &f, &ct, &eit, &eti);
+        float smith;
+        if (transmit) { V3 wo = refract(wi, m, ct, eti); smith = d.smith_g1(wo, m) * (1.f - f); if (wo.z * wi.z >= 0.f) smith = 0.f; }
+        else { V3 wo = reflect(wi, m); smith = d.smith_g1(wo, m) * f; if (wo.z <= 0.f || wi.z <= 0.f) smith = 0.f; }
+        result += smith * (weights[jx] * weights[jy]) * 0.25f;
+    }
+    return result;
+}
+void bsdf_prepare(DBsdf &b) {
+    b.flags = bsdf_flags(b.type);
+    if (b.type != BSDF_ROUGHPLASTIC) return;
+    b.inv_eta_2 = 1.f / (b.ior_eta * b.ior_eta);
+    float d_mean = (b.reflectance[0] + b.reflectance[1] + b.reflectance[2]) / 3.f;
+    float s_mean = (b.spec_refl[0] + b.spec_refl[1] + b.spec_refl[2]) / 3.f;
+    b.spec_sampling_weight = s_mean / (d_mean + s_mean);
+    Microfacet d(b.distr, b.alpha_u, b.alpha_u);
+    float acc = 0.f;
+    for (int i = 0; i < AM_ROUGH_TRANSMITTANCE_RES; ++i) {
+        float mu = max_(1e-6f, fmadd((float) i, 1.f / (float) (AM_ROUGH_TRANSMITTANCE_RES - 1), 0.f));
+        V3 wi = v3(fsqrt(1.f - mu * mu), 0.f, mu);
+        b.ext_transmittance[i] = mf_quadrature(d, wi, b.ior_eta, true);
+        acc += mf_quadrature(d, wi, 1.f / b.ior_eta, false) * wi.z;
+    }
+    b.internal_reflectance = acc / (float) AM_ROUGH_TRANSMITTANCE_RES * 2.f;
+}
+
+// ---------------------------------------------------------------- Scene
+Scene::~Scene() {
+    if (device >= 0) { cudaSetDevice(device); for (void *p : allocs) cudaFree(p); }
+}
+void *Scene::dalloc(size_t bytes) {
+    void *p = nullptr; AM_CUDA(cudaMalloc(&p, bytes ? bytes : 16)); allocs.push_back(p); return p;
+}
+int Scene::add_bsdf(const DBsdf &b_, const std::string &id) {
+    DBsdf b = b_; bsdf_prepare(b); bsdfs.push_back(b); bsdf_ids.push_back(id); committed = false;
+    return (int) bsdfs.size() - 1;
+}
+int Scene::add_mesh(HMesh &&m, const float *radiance) {
+    if (m.bsdf < 0 || m.bsdf >= (int) bsdfs.size()) AM_THROW("add_mesh: invalid BSDF index %d", m.bsdf);
+    uint32_t nv = (uint32_t) (m.pos.size() / 3);
+    for (uint32_t f : m.faces) if (f >= nv) AM_THROW("add_mesh: face index %u out of range (%u vertices)", f, nv);
+    if (!m.nrm.empty() && m.nrm.size() != m.pos.size()) AM_THROW("add_mesh: normal count does not match vertex count");
+    m.prim_offset = nprims();
+    int id = (int) meshes.size();
+    if (radiance) { m.emitter = (int) emitters.size(); DEmitter e; e.mesh = id; e.radiance[0] = radiance[0]; e.radiance[1] = radiance[1]; e.radiance[2] = radiance[2]; emitters.push_back(e); }
+    else m.emitter = -1;
+    m.build_area_distr();
+    meshes.push_back(std::move(m)); committed = false;
+    return id;
+}
+// GridSensor ctor placement loop (src/sensors/grid.cpp:182-226) + PerspectiveCamera / ThinLensCamera ctor and
+// update_camera_transforms (src/sensors/perspective.cpp:139-181, src/sensors/thinlens.cpp:152-187)
+void Scene::set_sensor_grid(const GridSensorParams &g) {
+    if (g.grid_x == 0 || g.grid_y == 0) AM_THROW("grid: grid_x / grid_y must be positive");
+    if (g.res_x == 0 || g.res_y == 0 || g.res_x % g.grid_x || g.res_y % g.grid_y) AM_THROW("Film size must be divisible by grid dimensions !");
+    grid_x = g.grid_x; grid_y = g.grid_y; reverse_x = g.reverse_x; reverse_y = g.reverse_y; thinlens = g.thinlens; multi_sensor = true;
+    film_w = g.res_x; film_h = g.res_y; res_x = g.res_x / g.grid_x; res_y = g.res_y / g.grid_y;
+    double sub_asp = res_x / (double) res_y;
+    double fov_x = parse_fov_x(g.fov, g.fov_axis, sub_asp);
+    M4d inv_d = m4d_inverse(g.to_world);
+    M4 inv_t = m4_transpose(m4_from_d(inv_d));          // to_world.inverse_transpose, cast to float
+    uint32_t n = grid_x * grid_y;
+    float off_y = -g.cam_off[1], off_z = -g.cam_off[2];
+    sensors.clear();
+    for (uint32_t i = 0; i < n; ++i) {
+        float dt = (float) i / (float) (n - 1), lens_shift = 0.f;
+        M4 itrafo = inv_t;
+        if (g.use_cone) {
+            float tan_off = tan_((dt - 0.5f) * (g.cone_deg * (AM_PI / 180.f)));
+            float offset = g.focus_distance * tan_off;
+            double shift = 0.5 * (double) tan_off / std::tan((fov_x * (3.14159265358979323846 / 180.0)) * 0.5);
+            itrafo.m[3][0] += offset + g.cam_off[0]; itrafo.m[3][1] += off_y; itrafo.m[3][2] += off_z;
+            lens_shift = (float) shift;
+        } else {
+            float sc = g.cam_dist * (dt - 0.5f * (float) (g.cam_center ? 1 : 0));
+            itrafo.m[3][0] += g.cam_off[0] + g.cam_dir[0] * sc;
+            itrafo.m[3][1] += off_y + g.cam_dir[1] * sc;
+            itrafo.m[3][2] += off_z + g.cam_dir[2] * sc;
+        }
+        M4 tw = m4_inverse(m4_transpose(itrafo));
+        M4 s2c = sample_to_camera((int) res_x, (int) res_y, (float) fov_x, g.near_clip, g.far_clip, lens_shift);
+        DSensor c;
+        for (int r = 0; r < 4; ++r) for (int k = 0; k < 4; ++k) c.s2c[4 * r + k] = s2c.m[r][k];
+        for (int r = 0; r < 3; ++r) for (int k = 0; k < 4; ++k) c.to_world[4 * r + k] = tw.m[r][k];
+        c.near_clip = g.near_clip; c.far_clip = g.far_clip; c.aperture_radius = g.aperture_radius; c.focus_distance = g.focus_distance;
+        sensors.push_back(c);
+    }
+    committed = false;
+}
+// BatchSensor (src/sensors/batch.cpp:94-130): n explicit sub-cameras side by side
+void Scene::set_sensor_explicit(uint32_t n, uint32_t rx, uint32_t ry, const float *s2c, const float *to_world,
+                                float near_clip, float far_clip, bool rev_x) {
+    if (!n || !rx || !ry) AM_THROW("batch: need at least one sub-sensor and a non-empty film");
+    grid_x = n; grid_y = 1; reverse_x = rev_x; reverse_y = false; thinlens = false; multi_sensor = true;
+    res_x = rx; res_y = ry; film_w = rx * n; film_h = ry; sensors.clear();
+    for (uint32_t i = 0; i < n; ++i) {
+        DSensor c; memcpy(c.s2c, s2c + 16 * i, 64); memcpy(c.to_world, to_world + 16 * i, 48);
+        c.near_clip = near_clip; c.far_clip = far_clip; c.aperture_radius = 0.f; c.focus_distance = far_clip; sensors.push_back(c);
+    }
+    committed = false;
+}
+// View tiles of the quilt owned by one rank: view v = ix + grid_x * iy (sub-sensor index), tile position follows
+// GridSensor::sample_ray's axis reversal (grid.cpp:246-255).
+std::vector<TileDesc> Scene::view_tiles(const Shard &sh) const {
+    std::vector<TileDesc> out;
+    for (uint32_t ty = 0; ty < grid_y; ++ty) for (uint32_t tx = 0; tx < grid_x; ++tx) {
+        uint32_t ix = reverse_x ? grid_x - 1 - tx : tx, iy = reverse_y ? grid_y - 1 - ty : ty, view = ix + grid_x * iy;
+        if (view % sh.world != sh.rank) continue;
+        TileDesc t{}; t.x0 = tx * res_x; t.y0 = ty * res_y; t.w = res_x; t.h = res_y; t.spp = 0; t.pad = view; t.lane_begin = 0;
+        out.push_back(t);
+    }
+    std::sort(out.begin(), out.end(), [](const TileDesc &a, const TileDesc &b) { return a.pad < b.pad; });
+    return out;
+}
+void Scene::film_clear(cudaStream_t st) {
+    if (!committed) AM_THROW("film_clear: scene not committed");
+    AM_CUDA(cudaMemsetAsync(film, 0, sizeof(float4) * (size_t) film_w * film_h, st));
+    AM_CUDA(cudaMemsetAsync(moments, 0, sizeof(float2) * (size_t) film_w * film_h, st));
+}
+void Scene::commit(int dev) {
+    if (sensors.empty()) AM_THROW("commit: no sensor");
+    if ((unsigned long long) film_w * film_h * 4ull >= (1ull << 32)) AM_THROW("commit: film index exceeds 32 bits");
+    if (device >= 0 && device != dev) AM_THROW("commit: scene already lives on device %d", device);
+    AM_CUDA(cudaSetDevice(dev)); device = dev;
+    for (void *p : allocs) cudaFree(p);
+    allocs.clear();
+    cudaDeviceProp prop; AM_CUDA(cudaGetDeviceProperties(&prop, dev)); sm_count = prop.multiProcessorCount;
+    // scene scale for the conservative box padding: largest absolute coordinate of geometry and camera origins
+    float scale = 0.f;
+    for (auto &m : meshes) for (float v : m.pos) scale = std::max(scale, std::fabs(v));
+    for (auto &c : sensors) for (int r = 0; r < 3; ++r) scale = std::max(scale, std::fabs(c.to_world[4 * r + 3]));
+    BvhOut bvh; build_bvh(*this, scale, bvh);
+    n_nodes = (uint32_t) (bvh.nodes.size() / 4); n_tris = (uint32_t) (bvh.tris.size() / 3);
+    std::vector<DMesh> dm; std::vector<float> cdf_all, pmf_all; bool any_nrm = false;
+    for (auto &m : meshes) {
+        DMesh q{}; q.bsdf = m.bsdf; q.emitter = m.emitter; q.flip_normals = m.flip_normals; q.has_normals = m.nrm.empty() ? 0 : 1;
+        q.prim_offset = m.prim_offset; q.nfaces = m.nfaces(); q.normalization = m.normalization; q.sum = m.sum; q.cdf_offset = 0;
+        if (m.emitter >= 0) { q.cdf_offset = (uint32_t) cdf_all.size(); cdf_all.insert(cdf_all.end(), m.cdf.begin(), m.cdf.end()); pmf_all.insert(pmf_all.end(), m.pmf.begin(), m.pmf.end()); }
+        any_nrm |= !m.nrm.empty(); dm.push_back(q);
+    }
+    d = DScene{};
+    d.nodes = upload(bvh.nodes); d.tris = upload(bvh.tris); d.tri_nrm = any_nrm ? upload(bvh.tri_nrm) : nullptr;
+    d.prim_to_tri = upload(bvh.prim_to_tri); d.meshes = upload(dm); d.bsdfs = upload(bsdfs); d.emitters = upload(emitters);
+    d.sensors = upload(sensors); d.area_cdf = upload(cdf_all); d.area_pmf = upload(pmf_all);
+    d.n_tris = n_tris; d.n_nodes = n_nodes; d.n_emitters = (uint32_t) emitters.size(); d.n_sensors = (uint32_t) sensors.size();
+    d.grid_x = grid_x; d.grid_y = grid_y; d.reverse_x = reverse_x; d.reverse_y = reverse_y; d.thinlens = thinlens;
+    d.film_w = film_w; d.film_h = film_h;
+    d.max_depth = integrator.max_depth < 0 ? 0xffffffffu : (uint32_t) integrator.max_depth;   // integrator.cpp:503-520
+    d.rr_depth = integrator.rr_depth;
+    size_t npix = (size_t) film_w * film_h;
+    film = (float4 *) dalloc(npix * sizeof(float4)); moments = (float2 *) dalloc(npix * sizeof(float2)); rgb = nullptr;
+    counters = (unsigned long long *) dalloc(sizeof(unsigned long long) * CTR_COUNT);
+    tiles_cap = std::max<uint32_t>(grid_x * grid_y, 1u) + 1; tiles_dev = (TileDesc *) dalloc(sizeof(TileDesc) * tiles_cap);
+    view_stats_dev = (float *) dalloc(sizeof(float) * 4 * tiles_cap);
+    h_nodes = std::move(bvh.nodes); h_tris = std::move(bvh.tris);
+    committed = true;
+    film_clear(nullptr);
+    AM_CUDA(cudaMemset(counters, 0, sizeof(unsigned long long) * CTR_COUNT));
+    AM_CUDA(cudaDeviceSynchronize());
+}
+
+} // namespace amvpt
