@@ -1,0 +1,285 @@
+"""mitsuba3-amvpt_b200 -- Python binding of the B200-native AMVPT render path (ctypes over include/amvpt.h).
+
+The product is the C++/CUDA library ``libamvpt_b200.so``; this module only mirrors the part of the reference's
+Python surface that drives the path (``load_file`` / ``Scene`` / ``integrator.render(scene, seed=, spp=, develop=)``,
+reference: src/render/python/integrator_v.cpp, src/python/python/util.py) so that tests and bench read like the
+reference's own.  There is no CPU fallback: without the built extension the import fails, and every compute call
+fails without a CUDA device.
+"""
+import ctypes as C
+import importlib
+import os
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libamvpt_b200.so")
+
+
+class AmvptError(RuntimeError):
+    pass
+
+
+def _load():
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                          "(the CUDA extension is the product; there is no fallback path)")
+    return C.CDLL(LIB_PATH)
+
+
+lib = _load()
+f32p, u32p, u64p = C.POINTER(C.c_float), C.POINTER(C.c_uint32), C.POINTER(C.c_uint64)
+
+
+class BsdfDesc(C.Structure):
+    _fields_ = [("type", C.c_int32), ("twosided", C.c_int32), ("distr", C.c_int32), ("nonlinear", C.c_int32),
+                ("reflectance", C.c_float * 3), ("eta", C.c_float * 3), ("k", C.c_float * 3),
+                ("specular_reflectance", C.c_float * 3), ("specular_transmittance", C.c_float * 3),
+                ("int_ior", C.c_float), ("ext_ior", C.c_float), ("alpha_u", C.c_float), ("alpha_v", C.c_float)]
+
+
+class GridSensorDesc(C.Structure):
+    _fields_ = [("thinlens", C.c_int32), ("fov_axis", C.c_int32), ("grid_x", C.c_uint32), ("grid_y", C.c_uint32),
+                ("res_x", C.c_uint32), ("res_y", C.c_uint32), ("reverse_x", C.c_int32), ("reverse_y", C.c_int32),
+                ("use_cone", C.c_int32), ("cam_center", C.c_int32), ("to_world", C.c_double * 16), ("fov", C.c_double),
+                ("near_clip", C.c_float), ("far_clip", C.c_float), ("focus_distance", C.c_float), ("aperture_radius", C.c_float),
+                ("cone_deg", C.c_float), ("cam_dist", C.c_float), ("cam_dir", C.c_float * 3), ("cam_off", C.c_float * 3)]
+
+
+class IntegratorDesc(C.Structure):
+    _fields_ = [("max_depth", C.c_int64), ("rr_depth", C.c_uint32), ("hide_emitters", C.c_int32), ("spp_pass_lim", C.c_uint32),
+                ("sampler_seed", C.c_uint32), ("sample_count", C.c_uint32)]
+
+
+ALLREDUCE_FN = C.CFUNCTYPE(None, C.c_void_p, C.c_uint32, C.c_void_p)
+
+
+class RenderDesc(C.Structure):
+    _fields_ = [("seed", C.c_uint32), ("spp", C.c_uint32), ("scheduler", C.c_int32), ("collect_stats", C.c_int32),
+                ("rank", C.c_uint32), ("world", C.c_uint32), ("adaptive", C.c_int32), ("adaptive_threshold", C.c_float),
+                ("adaptive_min_spp", C.c_uint32), ("stream", C.c_void_p), ("allreduce", ALLREDUCE_FN), ("allreduce_user", C.c_void_p)]
+
+
+class RenderStats(C.Structure):
+    _fields_ = [("seconds", C.c_double), ("paths", C.c_uint64), ("closest_rays", C.c_uint64), ("shadow_rays", C.c_uint64),
+                ("bvh_nodes", C.c_uint64), ("tri_tests", C.c_uint64), ("path_vertices", C.c_uint64),
+                ("passes", C.c_uint32), ("launches", C.c_uint32), ("spp_done", C.c_uint32), ("pad", C.c_uint32)]
+
+
+lib.amvpt_last_error.restype = C.c_char_p
+EXPORTS = ["amvpt_last_error", "amvpt_device_count", "amvpt_scene_create", "amvpt_scene_destroy", "amvpt_scene_from_xml",
+           "amvpt_scene_from_xml_string", "amvpt_scene_add_bsdf", "amvpt_scene_add_mesh", "amvpt_scene_set_sensor_grid",
+           "amvpt_scene_set_sensor_batch", "amvpt_scene_set_integrator", "amvpt_scene_commit", "amvpt_scene_info",
+           "amvpt_scene_get_sensor", "amvpt_scene_get_bsdf_tables", "amvpt_render", "amvpt_cancel", "amvpt_film_clear",
+           "amvpt_film_raw", "amvpt_film_develop", "amvpt_film_develop_device", "amvpt_film_device_ptr", "amvpt_film_add_host",
+           "amvpt_trace_lanes", "amvpt_intersect", "amvpt_bsdf_eval_pdf_sample", "amvpt_math1", "amvpt_sampler_stream",
+           "amvpt_bvh_validate"]
+lib.amvpt_scene_destroy.restype = None
+lib.amvpt_scene_destroy.argtypes = [C.c_void_p]
+
+
+def _chk(rc):
+    if rc < 0:
+        raise AmvptError(lib.amvpt_last_error().decode())
+    return rc
+
+
+def _p(a, t=f32p):
+    return None if a is None else a.ctypes.data_as(t)
+
+
+def _f32(a, shape=None):
+    a = np.ascontiguousarray(a, dtype=np.float32)
+    return a if shape is None else a.reshape(shape)
+
+
+BSDF_TYPES = {"diffuse": 0, "conductor": 1, "dielectric": 2, "roughconductor": 3, "roughdielectric": 4, "roughplastic": 5}
+FOV_AXES = {"x": 0, "y": 1, "diagonal": 2, "smaller": 3, "larger": 4}
+SCHEDULERS = {"warp_batch": 0, "regenerate": 1, "wavefront": 2}
+
+
+def bsdf_desc(type, twosided=False, distribution="beckmann", nonlinear=False, reflectance=(.5, .5, .5), eta=(0., 0., 0.),
+              k=(1., 1., 1.), specular_reflectance=(1., 1., 1.), specular_transmittance=(1., 1., 1.), int_ior=1.5046,
+              ext_ior=1.000277, alpha=0.1, alpha_u=None, alpha_v=None):
+    """Parameter names and defaults follow the reference's BSDF plugin constructors (src/bsdfs/*.cpp)."""
+    d = BsdfDesc()
+    d.type = BSDF_TYPES[type]; d.twosided = int(twosided); d.distr = {"beckmann": 0, "ggx": 1}[distribution]; d.nonlinear = int(nonlinear)
+    for name, val in (("reflectance", reflectance), ("eta", eta), ("k", k), ("specular_reflectance", specular_reflectance),
+                      ("specular_transmittance", specular_transmittance)):
+        v = np.broadcast_to(np.asarray(val, dtype=np.float32), (3,))
+        setattr(d, name, (C.c_float * 3)(*v))
+    d.int_ior = int_ior; d.ext_ior = ext_ior
+    d.alpha_u = alpha if alpha_u is None else alpha_u; d.alpha_v = alpha if alpha_v is None else alpha_v
+    return d
+
+
+class Scene:
+    """Scene + MultiSensor + Film + Sampler + Integrator of one render job (the objects Scene::Scene collects in
+    src/render/scene.cpp:22-96).  Built either from XML (load_file / load_string) or programmatically."""
+
+    def __init__(self, handle=None):
+        if handle is None:
+            handle = C.c_void_p()
+            _chk(lib.amvpt_scene_create(C.byref(handle)))
+        self._h = handle
+        self._keep = []
+
+    def __del__(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            lib.amvpt_scene_destroy(h)
+
+    # ---- construction
+    def add_bsdf(self, desc=None, **kw):
+        desc = desc if desc is not None else bsdf_desc(**kw)
+        return _chk(lib.amvpt_scene_add_bsdf(self._h, C.byref(desc)))
+
+    def add_mesh(self, positions, faces, bsdf, normals=None, radiance=None, flip_normals=False):
+        pos = _f32(positions, (-1, 3)); fc = np.ascontiguousarray(faces, dtype=np.uint32).reshape(-1, 3)
+        nrm = None if normals is None else _f32(normals, (-1, 3))
+        rad = None if radiance is None else _f32(np.broadcast_to(np.asarray(radiance, dtype=np.float32), (3,)))
+        return _chk(lib.amvpt_scene_add_mesh(self._h, _p(pos), C.c_uint32(len(pos)), _p(fc, u32p), C.c_uint32(len(fc)), _p(nrm),
+                                             C.c_int(bsdf), _p(rad), C.c_int(int(flip_normals))))
+
+    def set_sensor_grid(self, grid_x, grid_y, res_x, res_y, to_world, fov, fov_axis="x", near_clip=1e-2, far_clip=1e4,
+                        focus_distance=1.0, thinlens=False, aperture_radius=0.0, reverse_x=False, reverse_y=True, cone_deg=None,
+                        cam_dir=(1., 0., 0.), cam_dist=None, cam_center=True, cam_off=(0., 0., 0.)):
+        """`grid` sensor (src/sensors/grid.cpp:84-180); res_x / res_y are the quilt size."""
+        d = GridSensorDesc()
+        d.thinlens = int(thinlens); d.fov_axis = FOV_AXES[fov_axis]; d.grid_x = grid_x; d.grid_y = grid_y; d.res_x = res_x; d.res_y = res_y
+        d.reverse_x = int(reverse_x); d.reverse_y = int(reverse_y); d.use_cone = int(cone_deg is not None); d.cam_center = int(cam_center)
+        d.to_world = (C.c_double * 16)(*np.asarray(to_world, dtype=np.float64).reshape(16))
+        d.fov = fov; d.near_clip = near_clip; d.far_clip = far_clip; d.focus_distance = focus_distance; d.aperture_radius = aperture_radius
+        d.cone_deg = 0.0 if cone_deg is None else cone_deg
+        cd = np.asarray(cam_dir, dtype=np.float32)
+        d.cam_dist = float(np.float32(np.sqrt(np.float32(cd[0] * cd[0] + cd[1] * cd[1] + cd[2] * cd[2])))) if cam_dist is None else cam_dist
+        d.cam_dir = (C.c_float * 3)(*cd); d.cam_off = (C.c_float * 3)(*np.asarray(cam_off, dtype=np.float32))
+        _chk(lib.amvpt_scene_set_sensor_grid(self._h, C.byref(d)))
+
+    def set_sensor_batch(self, res_x, res_y, sample_to_camera, to_world, near_clip, far_clip, reverse_x=False):
+        s2c = _f32(sample_to_camera, (-1, 16)); tw = _f32(to_world, (-1, 16))
+        _chk(lib.amvpt_scene_set_sensor_batch(self._h, C.c_uint32(len(s2c)), C.c_uint32(res_x), C.c_uint32(res_y), _p(s2c), _p(tw),
+                                              C.c_float(near_clip), C.c_float(far_clip), C.c_int(int(reverse_x))))
+
+    def set_integrator(self, max_depth=-1, rr_depth=5, hide_emitters=False, spp_pass_lim=16, sampler_seed=0, sample_count=0):
+        d = IntegratorDesc(max_depth, rr_depth, int(hide_emitters), spp_pass_lim, sampler_seed, sample_count)
+        _chk(lib.amvpt_scene_set_integrator(self._h, C.byref(d)))
+
+    def commit(self, device=0):
+        _chk(lib.amvpt_scene_commit(self._h, C.c_int(device)))
+        return self
+
+    # ---- queries
+    def info(self):
+        v = [C.c_uint32() for _ in range(6)]
+        _chk(lib.amvpt_scene_info(self._h, *[C.byref(x) for x in v]))
+        return dict(zip(("film_w", "film_h", "n_views", "n_prims", "n_bvh_nodes", "sample_count"), [x.value for x in v]))
+
+    def sensor(self, index):
+        s2c = np.zeros(16, np.float32); tw = np.zeros(16, np.float32)
+        _chk(lib.amvpt_scene_get_sensor(self._h, C.c_uint32(index), _p(s2c), _p(tw)))
+        return s2c.reshape(4, 4), tw.reshape(4, 4)
+
+    def bsdf_tables(self, bsdf):
+        t = np.zeros(64, np.float32); s = np.zeros(3, np.float32)
+        _chk(lib.amvpt_scene_get_bsdf_tables(self._h, C.c_int(bsdf), _p(t), _p(s)))
+        return t, s
+
+    def bvh_validate(self):
+        d, n = C.c_uint32(), C.c_uint32()
+        _chk(lib.amvpt_bvh_validate(self._h, C.byref(d), C.byref(n)))
+        return d.value, n.value
+
+    # ---- the hot path: Integrator.render(scene, sensor, seed, spp, develop, evaluate)
+    def render(self, seed=0, spp=0, develop=True, scheduler="regenerate", stats=False, rank=0, world=1, adaptive=False,
+               adaptive_threshold=0.0, adaptive_min_spp=16, stream=None, allreduce=None, clear=True):
+        """Mirrors MVPathIntegrator::render (src/integrators/mvpath.cpp:7-278): accumulates `spp` samples per pixel into the
+        film and returns the developed (H, W, 3) image if `develop` (else None).  `clear=False` keeps accumulating."""
+        if clear:
+            self.film_clear()
+        d = RenderDesc()
+        d.seed = seed; d.spp = spp; d.scheduler = SCHEDULERS[scheduler] if isinstance(scheduler, str) else scheduler
+        d.collect_stats = int(stats); d.rank = rank; d.world = world; d.adaptive = int(adaptive)
+        d.adaptive_threshold = adaptive_threshold; d.adaptive_min_spp = adaptive_min_spp; d.stream = stream
+        if allreduce is not None:
+            cb = ALLREDUCE_FN(lambda dev, n, user: allreduce(dev, n)); self._keep = [cb]; d.allreduce = cb
+        st = RenderStats()
+        _chk(lib.amvpt_render(self._h, C.byref(d), C.byref(st)))
+        self.last_stats = {k: getattr(st, k) for k, _ in RenderStats._fields_ if k != "pad"}
+        return self.develop() if develop else None
+
+    def film_clear(self):
+        _chk(lib.amvpt_film_clear(self._h))
+
+    def film_raw(self):
+        i = self.info(); out = np.zeros((i["film_h"], i["film_w"], 4), np.float32)
+        _chk(lib.amvpt_film_raw(self._h, _p(out))); return out
+
+    def develop(self):
+        i = self.info(); out = np.zeros((i["film_h"], i["film_w"], 3), np.float32)
+        _chk(lib.amvpt_film_develop(self._h, _p(out))); return out
+
+    def film_device_ptr(self):
+        a, b = C.c_void_p(), C.c_void_p()
+        _chk(lib.amvpt_film_device_ptr(self._h, C.byref(a), C.byref(b))); return a.value, b.value
+
+    def film_add(self, rgbw):
+        _chk(lib.amvpt_film_add_host(self._h, _p(_f32(rgbw))))
+
+    # ---- parity taps
+    def trace_lanes(self, seed_value, spp_per_pass, lane_begin, n, trace=True, max_hits=0):
+        o = dict(sample_pos=np.zeros((n, 2), np.float32), ray_o=np.zeros((n, 3), np.float32), ray_d=np.zeros((n, 3), np.float32),
+                 ray_maxt=np.zeros(n, np.float32), view=np.zeros(n, np.uint32), radiance=np.zeros((n, 4), np.float32),
+                 pixel=np.zeros(n, np.uint32), hit_prim=np.zeros((n, max(max_hits, 1)), np.uint32), hit_t=np.zeros((n, max(max_hits, 1)), np.float32))
+        stats = np.zeros(2, np.uint64)
+        _chk(lib.amvpt_trace_lanes(self._h, C.c_uint32(seed_value), C.c_uint32(spp_per_pass), C.c_uint32(lane_begin), C.c_uint32(n), C.c_int(int(trace)),
+                                   _p(o["sample_pos"]), _p(o["ray_o"]), _p(o["ray_d"]), _p(o["ray_maxt"]), _p(o["view"], u32p), _p(o["radiance"]),
+                                   _p(o["pixel"], u32p), C.c_uint32(max_hits), _p(o["hit_prim"], u32p), _p(o["hit_t"]), _p(stats, u64p)))
+        o["stats"] = stats
+        return o
+
+    def intersect(self, o, d, maxt, any_hit=False):
+        o = _f32(o, (-1, 3)); d = _f32(d, (-1, 3)); maxt = _f32(maxt, (-1,)); n = len(o)
+        prim = np.zeros(n, np.uint32); tuv = np.zeros((n, 3), np.float32); stats = np.zeros(2, np.uint64)
+        _chk(lib.amvpt_intersect(self._h, _p(o), _p(d), _p(maxt), C.c_uint32(n), C.c_int(int(any_hit)), _p(prim, u32p), _p(tuv), _p(stats, u64p)))
+        return prim, tuv, stats
+
+    def bsdf_eval_pdf_sample(self, bsdf, wi, wo, s1, s2):
+        wi = _f32(wi, (-1, 3)); wo = _f32(wo, (-1, 3)); s1 = _f32(s1, (-1,)); s2 = _f32(s2, (-1, 2)); n = len(wi)
+        r = dict(f=np.zeros((n, 3), np.float32), pdf=np.zeros(n, np.float32), bs_wo=np.zeros((n, 3), np.float32), bs_pdf=np.zeros(n, np.float32),
+                 bs_eta=np.zeros(n, np.float32), bs_type=np.zeros(n, np.uint32), weight=np.zeros((n, 3), np.float32))
+        _chk(lib.amvpt_bsdf_eval_pdf_sample(self._h, C.c_int(bsdf), _p(wi), _p(wo), _p(s1), _p(s2), C.c_uint32(n), _p(r["f"]), _p(r["pdf"]),
+                                            _p(r["bs_wo"]), _p(r["bs_pdf"]), _p(r["bs_eta"]), _p(r["bs_type"], u32p), _p(r["weight"])))
+        return r
+
+
+def _defines(kw):
+    items = [f"{k}={v}".encode() for k, v in kw.items()]
+    arr = (C.c_char_p * max(len(items), 1))(*items)
+    return arr, len(items)
+
+
+def load_file(path, **defines):
+    """mi.load_file(path, **kwargs) (reference: src/core/python/xml.cpp): kwargs substitute $name parameters."""
+    h = C.c_void_p(); arr, n = _defines(defines)
+    _chk(lib.amvpt_scene_from_xml(str(path).encode(), arr, n, C.byref(h)))
+    return Scene(h)
+
+
+def load_string(xml, base_dir=".", **defines):
+    h = C.c_void_p(); arr, n = _defines(defines)
+    _chk(lib.amvpt_scene_from_xml_string(xml.encode(), str(base_dir).encode(), arr, n, C.byref(h)))
+    return Scene(h)
+
+
+def device_count():
+    return lib.amvpt_device_count()
+
+
+def math1(op, x, device=0):
+    x = _f32(x, (-1,)); out = np.zeros_like(x)
+    _chk(lib.amvpt_math1(C.c_int(device), C.c_int(op), _p(x), C.c_uint32(len(x)), _p(out))); return out
+
+
+def sampler_stream(seed_value, lane, n, device=0):
+    out = np.zeros(n, np.float32)
+    _chk(lib.amvpt_sampler_stream(C.c_int(device), C.c_uint32(seed_value), C.c_uint32(lane), C.c_uint32(n), _p(out))); return out

@@ -227,21 +227,21 @@ int amvpt_sampler_stream(int device, uint32_t seed_value, uint32_t lane, uint32_
 }
 // Host-side structural check of the tree that was uploaded (no GPU work): containment of triangles and child boxes.
 int amvpt_bvh_validate(amvpt_scene *h, uint32_t *max_depth, uint32_t *n_leaves) {
-    return guard([&] { NEED(h); Scene &s = *h->s; if (s.h_nodes.empty()) AM_THROW("scene not committed");
+    return guard([&] { NEED(h); Scene &s = *h->s; s.prepare_host();
         struct B { float lo[3], hi[3]; };
-        uint32_t leaves = 0, maxd = 0; std::vector<uint8_t> seen(s.h_tris.size() / 3, 0);
+        uint32_t leaves = 0, maxd = 0; std::vector<uint8_t> seen(s.bvh.tris.size() / 3, 0);
         std::function<void(int32_t, const B *, uint32_t)> rec = [&](int32_t ref, const B *box, uint32_t depth) {
             maxd = std::max(maxd, depth);
             if (ref < 0) {
                 uint32_t code = ~(uint32_t) ref, first = code >> 3, count = code & 7u; leaves++;
                 for (uint32_t i = first; i < first + count; ++i) {
                     if (seen[i]++) AM_THROW("bvh: triangle %u referenced twice", i);
-                    for (int k = 0; k < 3; ++k) { const float4 &v = s.h_tris[3 * (size_t) i + k]; float p[3] = { v.x, v.y, v.z };
+                    for (int k = 0; k < 3; ++k) { const float4 &v = s.bvh.tris[3 * (size_t) i + k]; float p[3] = { v.x, v.y, v.z };
                         for (int a = 0; a < 3; ++a) if (box && (p[a] < box->lo[a] || p[a] > box->hi[a])) AM_THROW("bvh: triangle %u outside its leaf box", i); }
                 }
                 return;
             }
-            const float4 *n = &s.h_nodes[4 * (size_t) ref];
+            const float4 *n = &s.bvh.nodes[4 * (size_t) ref];
             B a = { { n[0].x, n[0].z, n[2].x }, { n[0].y, n[0].w, n[2].y } }, b = { { n[1].x, n[1].z, n[2].z }, { n[1].y, n[1].w, n[2].w } };
             int32_t ca, cb; memcpy(&ca, &n[3].x, 4); memcpy(&cb, &n[3].y, 4);
             bool a_empty = ca == -1, b_empty = cb == -1;

@@ -47,6 +47,7 @@ struct GridSensorParams {
 };
 enum SchedulerMode { SCHED_WARP_BATCH = 0, SCHED_REGENERATE = 1, SCHED_WAVEFRONT = 2 };
 
+struct BvhOut { std::vector<float4> nodes, tris, tri_nrm; std::vector<uint32_t> prim_to_tri; };
 struct RenderStats {
     double seconds = 0.0;            // device time of the pass loop (CUDA events)
     unsigned long long paths = 0, closest_rays = 0, shadow_rays = 0, nodes = 0, tris = 0, vertices = 0;
@@ -74,8 +75,8 @@ struct Scene {
     uint32_t n_nodes = 0, n_tris = 0;
     volatile bool stop = false;
     RenderStats last;
-    // oracle-visible copies for the parity tests of the BVH (same tree the kernels traverse)
-    std::vector<float4> h_nodes, h_tris;
+    // host copy of the tree the kernels traverse (built by prepare_host, checked by amvpt_bvh_validate)
+    BvhOut bvh; bool host_ready = false;
 
     ~Scene();
     int add_bsdf(const DBsdf &b, const std::string &id = "");
@@ -83,6 +84,7 @@ struct Scene {
     void set_sensor_grid(const GridSensorParams &g);
     void set_sensor_explicit(uint32_t n, uint32_t res_x, uint32_t res_y, const float *s2c, const float *to_world,
                              float near_clip, float far_clip, bool reverse_x);
+    void prepare_host();
     void commit(int device);
     void film_clear(cudaStream_t st);
     void *dalloc(size_t bytes);
@@ -99,7 +101,6 @@ struct Scene {
 void bsdf_prepare(DBsdf &b);
 
 // bvh.cpp
-struct BvhOut { std::vector<float4> nodes, tris, tri_nrm; std::vector<uint32_t> prim_to_tri; };
 void build_bvh(const Scene &s, float scene_scale, BvhOut &out);
 
 // render.cpp -- MVPathIntegrator::render() (src/integrators/mvpath.cpp:7-278), wavefront branch

@@ -156,7 +156,7 @@ int Scene::add_mesh(HMesh &&m, const float *radiance) {
     if (radiance) { m.emitter = (int) emitters.size(); DEmitter e; e.mesh = id; e.radiance[0] = radiance[0]; e.radiance[1] = radiance[1]; e.radiance[2] = radiance[2]; emitters.push_back(e); }
     else m.emitter = -1;
     m.build_area_distr();
-    meshes.push_back(std::move(m)); committed = false;
+    meshes.push_back(std::move(m)); committed = false; host_ready = false;
     return id;
 }
 // GridSensor ctor placement loop (src/sensors/grid.cpp:182-226) + PerspectiveCamera / ThinLensCamera ctor and
@@ -196,7 +196,7 @@ void Scene::set_sensor_grid(const GridSensorParams &g) {
         c.near_clip = g.near_clip; c.far_clip = g.far_clip; c.aperture_radius = g.aperture_radius; c.focus_distance = g.focus_distance;
         sensors.push_back(c);
     }
-    committed = false;
+    committed = false; host_ready = false;
 }
 // BatchSensor (src/sensors/batch.cpp:94-130): n explicit sub-cameras side by side
 void Scene::set_sensor_explicit(uint32_t n, uint32_t rx, uint32_t ry, const float *s2c, const float *to_world,
@@ -228,6 +228,14 @@ void Scene::film_clear(cudaStream_t st) {
     AM_CUDA(cudaMemsetAsync(film, 0, sizeof(float4) * (size_t) film_w * film_h, st));
     AM_CUDA(cudaMemsetAsync(moments, 0, sizeof(float2) * (size_t) film_w * film_h, st));
 }
+void Scene::prepare_host() {
+    if (host_ready && !bvh.nodes.empty()) return;
+    // scene scale for the conservative box padding: largest absolute coordinate of geometry and camera origins
+    float scale = 0.f;
+    for (auto &m : meshes) for (float v : m.pos) scale = std::max(scale, std::fabs(v));
+    for (auto &c : sensors) for (int r = 0; r < 3; ++r) scale = std::max(scale, std::fabs(c.to_world[4 * r + 3]));
+    bvh = BvhOut(); build_bvh(*this, scale, bvh); host_ready = true;
+}
 void Scene::commit(int dev) {
     if (sensors.empty()) AM_THROW("commit: no sensor");
     if ((unsigned long long) film_w * film_h * 4ull >= (1ull << 32)) AM_THROW("commit: film index exceeds 32 bits");
@@ -236,11 +244,7 @@ void Scene::commit(int dev) {
     for (void *p : allocs) cudaFree(p);
     allocs.clear();
     cudaDeviceProp prop; AM_CUDA(cudaGetDeviceProperties(&prop, dev)); sm_count = prop.multiProcessorCount;
-    // scene scale for the conservative box padding: largest absolute coordinate of geometry and camera origins
-    float scale = 0.f;
-    for (auto &m : meshes) for (float v : m.pos) scale = std::max(scale, std::fabs(v));
-    for (auto &c : sensors) for (int r = 0; r < 3; ++r) scale = std::max(scale, std::fabs(c.to_world[4 * r + 3]));
-    BvhOut bvh; build_bvh(*this, scale, bvh);
+    prepare_host();
     n_nodes = (uint32_t) (bvh.nodes.size() / 4); n_tris = (uint32_t) (bvh.tris.size() / 3);
     std::vector<DMesh> dm; std::vector<float> cdf_all, pmf_all; bool any_nrm = false;
     for (auto &m : meshes) {
@@ -263,7 +267,6 @@ void Scene::commit(int dev) {
     counters = (unsigned long long *) dalloc(sizeof(unsigned long long) * CTR_COUNT);
     tiles_cap = std::max<uint32_t>(grid_x * grid_y, 1u) + 1; tiles_dev = (TileDesc *) dalloc(sizeof(TileDesc) * tiles_cap);
     view_stats_dev = (float *) dalloc(sizeof(float) * 4 * tiles_cap);
-    h_nodes = std::move(bvh.nodes); h_tris = std::move(bvh.tris);
     committed = true;
     film_clear(nullptr);
     AM_CUDA(cudaMemset(counters, 0, sizeof(unsigned long long) * CTR_COUNT));

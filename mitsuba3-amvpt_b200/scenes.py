@@ -1,0 +1,139 @@
+"""Synthetic scene descriptions for BASELINE.json's configurations, as plain dictionaries that
+both the product (`build`) and the CPU oracle (tests/oracle_binding.py) consume, so both sides see identical bytes.
+
+S1: the Cornell box from the published Cornell measurements (quads split into two triangles; 32 triangles, diffuse
+    BSDFs with the reflectances of the reference's resources/data/scenes/cbox/fragments/bsdfs-rgb.xml, one area light
+    of radiance (18.387, 10.9873, 2.75357) lowered by 0.5 like the reference's shapes.xml), seen by a `grid` sensor
+    whose sub-camera is the cbox perspective camera (fov 39.3077 smaller axis, near 10, far 2800, origin (278,273,-800)).
+S2: procedural height field z = 0.15 sin(7x) cos(5y) + 0.05 sin(31x + 17y) over [-1,1]^2, n x n quads (n = 708 gives
+    1 002 528 triangles), four meshes with roughconductor / roughdielectric / roughplastic / diffuse BSDFs, inside a
+    12-triangle diffuse box with a 2-triangle area light of radiance 10.
+"""
+import numpy as np
+
+CBOX_QUADS = {
+    "floor": [[(552.8, 0, 0), (0, 0, 0), (0, 0, 559.2), (549.6, 0, 559.2)]],
+    "ceiling": [[(556, 548.8, 0), (556, 548.8, 559.2), (0, 548.8, 559.2), (0, 548.8, 0)]],
+    "back": [[(549.6, 0, 559.2), (0, 0, 559.2), (0, 548.8, 559.2), (556, 548.8, 559.2)]],
+    "greenwall": [[(0, 0, 559.2), (0, 0, 0), (0, 548.8, 0), (0, 548.8, 559.2)]],
+    "redwall": [[(552.8, 0, 0), (549.6, 0, 559.2), (556, 548.8, 559.2), (556, 548.8, 0)]],
+    "luminaire": [[(343, 548.8, 227), (343, 548.8, 332), (213, 548.8, 332), (213, 548.8, 227)]],
+    "smallbox": [[(130, 165, 65), (82, 165, 225), (240, 165, 272), (290, 165, 114)],
+                 [(290, 0, 114), (290, 165, 114), (240, 165, 272), (240, 0, 272)],
+                 [(130, 0, 65), (130, 165, 65), (290, 165, 114), (290, 0, 114)],
+                 [(82, 0, 225), (82, 165, 225), (130, 165, 65), (130, 0, 65)],
+                 [(240, 0, 272), (240, 165, 272), (82, 165, 225), (82, 0, 225)]],
+    "largebox": [[(423, 330, 247), (265, 330, 296), (314, 330, 456), (472, 330, 406)],
+                 [(423, 0, 247), (423, 330, 247), (472, 330, 406), (472, 0, 406)],
+                 [(472, 0, 406), (472, 330, 406), (314, 330, 456), (314, 0, 456)],
+                 [(314, 0, 456), (314, 330, 456), (265, 330, 296), (265, 0, 296)],
+                 [(265, 0, 296), (265, 330, 296), (423, 330, 247), (423, 0, 247)]],
+}
+CBOX_BSDFS = {"box": (0.45, 0.30, 0.90), "white": (0.885809, 0.698859, 0.666422), "red": (0.570068, 0.0430135, 0.0443706),
+              "green": (0.105421, 0.37798, 0.076425), "light": (0.936461, 0.740433, 0.705267)}
+CBOX_SHAPES = [("luminaire", "light"), ("floor", "white"), ("ceiling", "white"), ("back", "white"), ("greenwall", "green"),
+               ("redwall", "red"), ("smallbox", "box"), ("largebox", "box")]
+CBOX_RADIANCE = (18.387, 10.9873, 2.75357)
+
+
+def quads_to_mesh(quads, offset=(0.0, 0.0, 0.0)):
+    pos, faces = [], []
+    for q in quads:
+        b = len(pos)
+        pos += [tuple(np.float32(c) + np.float32(o) for c, o in zip(v, offset)) for v in q]
+        faces += [(b, b + 1, b + 2), (b, b + 2, b + 3)]
+    return np.asarray(pos, np.float32), np.asarray(faces, np.uint32)
+
+
+def look_at(origin, target, up):
+    """Transform4d::look_at (reference include/mitsuba/core/transform.h:269-300), double precision."""
+    o, t, u = (np.asarray(v, np.float64) for v in (origin, target, up))
+    d = (t - o) / np.linalg.norm(t - o); left = np.cross(u, d); left /= np.linalg.norm(left); nu = np.cross(d, left)
+    m = np.eye(4); m[:3, 0] = left; m[:3, 1] = nu; m[:3, 2] = d; m[:3, 3] = o
+    return m
+
+
+def cornell_box(grid_x=4, grid_y=1, view_res=256, cam_dist=200.0, max_depth=6, rr_depth=5, spp_pass_lim=16, sample_count=64,
+                sampler_seed=0, bsdf_overrides=None, thinlens=False, aperture_radius=0.0, cone_deg=None):
+    bsdfs, ids = [], {}
+    for name, refl in CBOX_BSDFS.items():
+        kw = dict(type="diffuse", reflectance=refl)
+        if bsdf_overrides and name in bsdf_overrides:
+            kw = dict(bsdf_overrides[name])
+        ids[name] = len(bsdfs); bsdfs.append(kw)
+    meshes = []
+    for shape, bsdf in CBOX_SHAPES:
+        pos, faces = quads_to_mesh(CBOX_QUADS[shape], (0.0, -0.5, 0.0) if shape == "luminaire" else (0.0, 0.0, 0.0))
+        meshes.append(dict(name=shape, positions=pos, faces=faces, normals=None, bsdf=ids[bsdf],
+                           radiance=CBOX_RADIANCE if shape == "luminaire" else None, flip_normals=False))
+    sensor = dict(grid_x=grid_x, grid_y=grid_y, res_x=grid_x * view_res, res_y=grid_y * view_res,
+                  to_world=look_at((278, 273, -800), (278, 273, -799), (0, 1, 0)), fov=39.3077, fov_axis="smaller", near_clip=10.0,
+                  far_clip=2800.0, focus_distance=1000.0, thinlens=thinlens, aperture_radius=aperture_radius, reverse_x=False,
+                  reverse_y=True, cone_deg=cone_deg, cam_dir=(1.0, 0.0, 0.0), cam_dist=cam_dist, cam_center=True, cam_off=(0.0, 0.0, 0.0))
+    integrator = dict(max_depth=max_depth, rr_depth=rr_depth, hide_emitters=False, spp_pass_lim=spp_pass_lim,
+                      sampler_seed=sampler_seed, sample_count=sample_count)
+    return dict(name=f"cbox_{grid_x}x{grid_y}_{view_res}", bsdfs=bsdfs, meshes=meshes, sensor=sensor, integrator=integrator)
+
+
+def height_field(n=708, grid_x=4, grid_y=4, view_res=1024, max_depth=8, rr_depth=5, spp_pass_lim=16, sample_count=64,
+                 sampler_seed=0, smooth_normals=True):
+    """S2 of SURVEY.md sec.8d.  Vertex data are float32 functions of integer grid indices (no RNG)."""
+    bsdfs = [dict(type="roughconductor", distribution="ggx", alpha=0.15, eta=(0.2, 0.92, 1.1), k=(3.9, 2.45, 2.14)),
+             dict(type="roughdielectric", distribution="beckmann", alpha=0.1, int_ior=1.5046, ext_ior=1.000277),
+             dict(type="roughplastic", distribution="beckmann", alpha=0.1, reflectance=(0.5, 0.5, 0.5)),
+             dict(type="diffuse", reflectance=(0.5, 0.5, 0.5)),
+             dict(type="diffuse", reflectance=(0.7, 0.7, 0.7)),      # enclosure
+             dict(type="diffuse", reflectance=(0.0, 0.0, 0.0))]      # light
+    meshes = []
+    h = n // 2
+    i = np.arange(n + 1, dtype=np.float64)
+    xs = -1.0 + 2.0 * i / n
+    X, Y = np.meshgrid(xs, xs, indexing="xy")             # vertex (iy, ix)
+    Z = 0.15 * np.sin(7 * X) * np.cos(5 * Y) + 0.05 * np.sin(31 * X + 17 * Y)
+    dZdx = 0.15 * 7 * np.cos(7 * X) * np.cos(5 * Y) + 0.05 * 31 * np.cos(31 * X + 17 * Y)
+    dZdy = -0.15 * 5 * np.sin(7 * X) * np.sin(5 * Y) + 0.05 * 17 * np.cos(31 * X + 17 * Y)
+    N = np.stack([-dZdx, -dZdy, np.ones_like(Z)], -1); N /= np.linalg.norm(N, axis=-1, keepdims=True)
+    P = np.stack([X, Y, Z], -1)
+    quads = [(0, h, 0, h), (h, n, 0, h), (0, h, h, n), (h, n, h, n)]     # (x0, x1, y0, y1) in quad indices
+    for q, (x0, x1, y0, y1) in enumerate(quads):
+        px = P[y0:y1 + 1, x0:x1 + 1].reshape(-1, 3).astype(np.float32)
+        nx = N[y0:y1 + 1, x0:x1 + 1].reshape(-1, 3).astype(np.float32)
+        w = x1 - x0 + 1
+        jy, jx = np.meshgrid(np.arange(y1 - y0), np.arange(x1 - x0), indexing="ij")
+        v00 = (jy * w + jx).reshape(-1); v10 = v00 + 1; v01 = v00 + w; v11 = v01 + 1
+        faces = np.empty((2 * len(v00), 3), np.uint32)
+        faces[0::2] = np.stack([v00, v10, v11], -1); faces[1::2] = np.stack([v00, v11, v01], -1)      # normal +z
+        meshes.append(dict(name=f"field{q}", positions=px, faces=faces, normals=nx if smooth_normals else None, bsdf=q,
+                           radiance=None, flip_normals=False))
+    # enclosure [-1.6,1.6]^2 x [-0.6,2.4], inward-facing normals
+    a, z0, z1 = 1.6, -0.6, 2.4
+    c = [(-a, -a, z0), (a, -a, z0), (a, a, z0), (-a, a, z0), (-a, -a, z1), (a, -a, z1), (a, a, z1), (-a, a, z1)]
+    box_quads = [[c[0], c[1], c[2], c[3]], [c[4], c[7], c[6], c[5]], [c[0], c[4], c[5], c[1]], [c[1], c[5], c[6], c[2]],
+                 [c[2], c[6], c[7], c[3]], [c[3], c[7], c[4], c[0]]]
+    pos, faces = quads_to_mesh(box_quads)
+    meshes.append(dict(name="enclosure", positions=pos, faces=faces, normals=None, bsdf=4, radiance=None, flip_normals=False))
+    l, zl = 0.5, 2.39
+    pos, faces = quads_to_mesh([[(-l, -l, zl), (-l, l, zl), (l, l, zl), (l, -l, zl)]])       # normal -z
+    meshes.append(dict(name="light", positions=pos, faces=faces, normals=None, bsdf=5, radiance=(10.0, 10.0, 10.0), flip_normals=False))
+    sensor = dict(grid_x=grid_x, grid_y=grid_y, res_x=grid_x * view_res, res_y=grid_y * view_res,
+                  to_world=look_at((0.0, -1.45, 1.6), (0.0, 0.0, 0.0), (0, 0, 1)), fov=60.0, fov_axis="x", near_clip=0.01, far_clip=100.0,
+                  focus_distance=2.0, thinlens=False, aperture_radius=0.0, reverse_x=False, reverse_y=True, cone_deg=None,
+                  cam_dir=(1.0, 0.0, 0.0), cam_dist=1.0, cam_center=True, cam_off=(0.0, 0.0, 0.0))
+    integrator = dict(max_depth=max_depth, rr_depth=rr_depth, hide_emitters=False, spp_pass_lim=spp_pass_lim,
+                      sampler_seed=sampler_seed, sample_count=sample_count)
+    return dict(name=f"hfield{n}_{grid_x}x{grid_y}_{view_res}", bsdfs=bsdfs, meshes=meshes, sensor=sensor, integrator=integrator)
+
+
+def build(desc, device=0, commit=True):
+    """Instantiate a description in the product library."""
+    from . import Scene
+    s = Scene()
+    for b in desc["bsdfs"]:
+        s.add_bsdf(**b)
+    for m in desc["meshes"]:
+        s.add_mesh(m["positions"], m["faces"], m["bsdf"], normals=m["normals"], radiance=m["radiance"], flip_normals=m["flip_normals"])
+    s.set_sensor_grid(**desc["sensor"])
+    s.set_integrator(**desc["integrator"])
+    if commit:
+        s.commit(device)
+    return s

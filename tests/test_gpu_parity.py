@@ -1,0 +1,222 @@
+"""Parity of the CUDA path against the CPU oracle, through the C ABI (include/amvpt.h), on seeded inputs.
+Bar (BASELINE.json north_star): sampler streams, camera rays and hit primitive IDs bit-exact; per-lane radiance is
+also compared bit-for-bit (same canonical arithmetic on both sides); the film, which is accumulated with atomics in
+a different order than the oracle's sequential sum, within a stated relative tolerance."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+FILM_RTOL = 2e-5      # order of fp32 summation of <= 64 samples per pixel; stated tolerance for the film compare
+
+
+def bits(a):
+    return np.ascontiguousarray(a).view(np.uint32)
+
+
+def assert_bits(a, b, what):
+    a, b = bits(a), bits(b)
+    bad = np.flatnonzero((a != b).reshape(len(a), -1).any(axis=1)) if a.ndim > 1 else np.flatnonzero(a != b)
+    assert bad.size == 0, f"{what}: {bad.size} of {len(a)} rows differ, first {bad[:5]}"
+
+
+@pytest.fixture(scope="module")
+def cbox(scenes, ob, gpu):
+    desc = scenes.cornell_box(grid_x=4, grid_y=1, view_res=64, sample_count=32)
+    return desc, scenes.build(desc, device=gpu), ob.OracleScene(desc)
+
+
+@pytest.fixture(scope="module")
+def hfield(scenes, ob, gpu):
+    desc = scenes.height_field(n=24, grid_x=2, grid_y=2, view_res=32, sample_count=16)
+    return desc, scenes.build(desc, device=gpu), ob.OracleScene(desc)
+
+
+def test_sampler_stream_bit_exact(pkg, ob, gpu):
+    # PCG32Sampler::seed wavefront seeding + next_float32 (reference sampler.cpp:125-144, drjit/random.h:59-150)
+    for seed, lane in [(0, 0), (0, 1), (16, 4194303), (0xdeadbeef, 0xffffffff), (48, 123456789)]:
+        assert_bits(pkg.sampler_stream(seed, lane, 64, gpu), ob.sampler_stream(seed, lane, 64), f"stream {seed},{lane}")
+
+
+@pytest.mark.parametrize("op,lo,hi", [(0, -20, 20), (1, -20, 20), (2, -80, 80), (3, 1e-30, 1e30), (4, -4, 4), (5, -0.999999, 0.999999),
+                                      (6, -120, 120), (7, 0, 1e6), (8, -1e3, 1e3), (9, 1e-6, 1e6), (10, -1, 1), (11, -1.5, 1.5)])
+def test_leaf_math_bit_exact(pkg, ob, gpu, op, lo, hi):
+    rng = np.random.default_rng(op)
+    x = rng.uniform(lo, hi, 20000).astype(np.float32)
+    if op == 3:
+        x = np.exp(rng.uniform(-60, 60, 20000)).astype(np.float32)
+    x[:6] = [lo, hi, 0.0 if lo <= 0 <= hi else lo, 1.0 if lo <= 1 <= hi else hi, lo / 2, hi / 2]
+    assert_bits(pkg.math1(op, x, gpu), ob.math1(op, x), f"math op {op}")
+
+
+BSDFS = [dict(type="diffuse", reflectance=(0.2, 0.5, 0.8)),
+         dict(type="diffuse", reflectance=(0.2, 0.5, 0.8), twosided=True),
+         dict(type="conductor", eta=(0.2, 0.92, 1.1), k=(3.9, 2.45, 2.14)),
+         dict(type="dielectric", int_ior=1.5046, ext_ior=1.000277),
+         dict(type="roughconductor", distribution="ggx", alpha=0.15, eta=(0.2, 0.92, 1.1), k=(3.9, 2.45, 2.14)),
+         dict(type="roughconductor", distribution="beckmann", alpha_u=0.05, alpha_v=0.3, eta=(0.2, 0.92, 1.1), k=(3.9, 2.45, 2.14), twosided=True),
+         dict(type="roughdielectric", distribution="beckmann", alpha=0.1),
+         dict(type="roughdielectric", distribution="ggx", alpha=0.3, int_ior=1.33, ext_ior=1.0),
+         dict(type="roughplastic", distribution="beckmann", alpha=0.1, reflectance=(0.5, 0.3, 0.1)),
+         dict(type="roughplastic", distribution="ggx", alpha=0.2, reflectance=(0.5, 0.3, 0.1), nonlinear=True)]
+
+
+def test_bsdf_eval_pdf_sample_bit_exact(pkg, scenes, ob, gpu):
+    desc = scenes.cornell_box(grid_x=2, grid_y=1, view_res=8)
+    desc["bsdfs"] = BSDFS
+    for m in desc["meshes"]:
+        m["bsdf"] = 0
+    s = scenes.build(desc, device=gpu); o = ob.OracleScene(desc)
+    rng = np.random.default_rng(7); n = 20000
+
+    def dirs(k):
+        v = rng.normal(size=(k, 3)); v /= np.linalg.norm(v, axis=1, keepdims=True); return v.astype(np.float32)
+    wi, wo = dirs(n), dirs(n)
+    wi[:10, 2] = [0, 1, -1, 1e-8, -1e-8, 0.5, 0.5, 0.5, 0.5, 0.5]      # grazing / normal incidence edge cases
+    s1 = rng.uniform(size=n).astype(np.float32); s2 = rng.uniform(size=(n, 2)).astype(np.float32)
+    s2[:4] = [[0, 0], [0.5, 0.5], [0.99999994, 0.99999994], [0, 0.99999994]]
+    for i, b in enumerate(BSDFS):
+        a = s.bsdf_eval_pdf_sample(i, wi, wo, s1, s2); r = o.bsdf_eval_pdf_sample(i, wi, wo, s1, s2)
+        for k in ("f", "pdf", "bs_wo", "bs_pdf", "bs_eta", "bs_type", "weight"):
+            assert_bits(a[k], r[k], f"bsdf {i} ({b['type']}) field {k}")
+        if b["type"] == "roughplastic":
+            ta, sa = s.bsdf_tables(i); tb, sb = o.bsdf_tables(i)
+            assert_bits(ta, tb, "roughplastic transmittance table"); assert_bits(sa, sb, "roughplastic scalars")
+
+
+def test_camera_rays_bit_exact(cbox):
+    desc, s, o = cbox
+    w = desc["sensor"]["res_x"]; h = desc["sensor"]["res_y"]
+    total = w * h * 16
+    for seed_value, begin in [(0, 0), (16, total // 2 - 5000), (0, total - 20000)]:
+        a = s.trace_lanes(seed_value, 16, begin, 20000, trace=False); b = o.trace_lanes(seed_value, 16, begin, 20000, trace=False)
+        for k in ("sample_pos", "ray_o", "ray_d", "ray_maxt", "view", "pixel"):
+            assert_bits(a[k], b[k], f"camera tap {k} (seed {seed_value}, lane {begin})")
+    assert set(np.unique(a["view"])) <= {0, 1, 2, 3}
+
+
+def test_thinlens_rays_bit_exact(scenes, ob, gpu):
+    desc = scenes.cornell_box(grid_x=3, grid_y=2, view_res=16, thinlens=True, aperture_radius=5.0, cone_deg=20.0)
+    s = scenes.build(desc, device=gpu); o = ob.OracleScene(desc)
+    n = 3 * 2 * 16 * 16 * 4
+    a = s.trace_lanes(3, 4, 0, n, trace=False); b = o.trace_lanes(3, 4, 0, n, trace=False)
+    for k in ("sample_pos", "ray_o", "ray_d", "ray_maxt", "view", "pixel"):
+        assert_bits(a[k], b[k], f"thinlens/cone tap {k}")
+    assert len(np.unique(a["view"])) == 6
+
+
+def random_rays(rng, n, lo, hi):
+    o = rng.uniform(lo, hi, (n, 3)).astype(np.float32)
+    d = rng.normal(size=(n, 3)); d /= np.linalg.norm(d, axis=1, keepdims=True)
+    d = d.astype(np.float32)
+    d[: n // 50] = np.eye(3, dtype=np.float32)[rng.integers(0, 3, n // 50)] * np.float32(1) * rng.choice([-1, 1], (n // 50, 1)).astype(np.float32)
+    maxt = np.full(n, np.finfo(np.float32).max, np.float32); maxt[::7] = rng.uniform(0, hi - lo, len(maxt[::7])).astype(np.float32)
+    return o, d, maxt
+
+
+def test_bvh_equals_brute_force_cbox(cbox):
+    # kd-tree == brute force is the reference's own test (src/render/tests/test_kdtrees.py:49-115)
+    _, s, o = cbox
+    ro, rd, mt = random_rays(np.random.default_rng(1), 60000, -50, 600)
+    prim, tuv, _ = s.intersect(ro, rd, mt); rprim, rtuv, _ = o.intersect(ro, rd, mt, brute=True)
+    assert_bits(prim, rprim, "closest-hit primitive"); hit = rprim != 0xffffffff
+    assert hit.sum() > 10000
+    assert_bits(tuv[hit], rtuv[hit], "closest-hit t,u,v")
+    occ, _, _ = s.intersect(ro, rd, mt, any_hit=True); rocc = o.ray_test(ro, rd, mt, brute=True)
+    assert np.array_equal(occ != 0xffffffff, rocc != 0), "shadow-ray occlusion"
+
+
+def test_bvh_equals_brute_force_heightfield(hfield):
+    _, s, o = hfield
+    ro, rd, mt = random_rays(np.random.default_rng(2), 20000, -1.5, 1.5)
+    prim, tuv, _ = s.intersect(ro, rd, mt); rprim, rtuv, _ = o.intersect(ro, rd, mt, brute=True)
+    assert_bits(prim, rprim, "closest-hit primitive"); hit = rprim != 0xffffffff
+    assert_bits(tuv[hit], rtuv[hit], "closest-hit t,u,v")
+    occ, _, _ = s.intersect(ro, rd, mt, any_hit=True); rocc = o.ray_test(ro, rd, mt, brute=True)
+    assert np.array_equal(occ != 0xffffffff, rocc != 0)
+
+
+def test_shared_edge_tie_rule(cbox):
+    # rays aimed exactly at shared edges / vertices of the floor quad: the larger primitive index must win
+    _, s, o = cbox
+    t = np.linspace(0.05, 0.95, 200, dtype=np.float32)
+    target = np.stack([552.8 * (1 - t) + 0.0 * t, np.zeros_like(t), 0.0 * (1 - t) + 559.2 * t], 1).astype(np.float32)   # diagonal p0->p2
+    origin = np.tile(np.array([278, 273, 280], np.float32), (len(t), 1))
+    d = target - origin; d = (d / np.linalg.norm(d, axis=1, keepdims=True)).astype(np.float32)
+    mt = np.full(len(t), np.finfo(np.float32).max, np.float32)
+    prim, tuv, _ = s.intersect(origin, d, mt); rprim, rtuv, _ = o.intersect(origin, d, mt, brute=True)
+    assert_bits(prim, rprim, "tie rule primitive"); assert_bits(tuv, rtuv, "tie rule tuv")
+
+
+@pytest.mark.parametrize("which", ["cbox", "hfield"])
+def test_paths_bit_exact(which, cbox, hfield):
+    desc, s, o = cbox if which == "cbox" else hfield
+    spp = 16; total = desc["sensor"]["res_x"] * desc["sensor"]["res_y"] * spp
+    n = 30000 if which == "cbox" else 8000
+    for seed_value, begin in [(0, 0), (16, max(total // 2 - n, 0))]:
+        a = s.trace_lanes(seed_value, spp, begin, n, max_hits=8)
+        b = o.trace_lanes(seed_value, spp, begin, n, max_hits=8, brute=(which == "cbox"))
+        assert_bits(a["hit_prim"], b["hit_prim"], f"{which}: hit primitive IDs per bounce")
+        assert_bits(a["hit_t"], b["hit_t"], f"{which}: hit distances per bounce")
+        assert_bits(a["radiance"], b["radiance"], f"{which}: per-lane radiance")
+        assert (a["radiance"][:, :3].sum(1) > 0).mean() > 0.2
+
+
+def test_film_matches_oracle(cbox):
+    desc, s, o = cbox
+    img = s.render(seed=0, spp=32)
+    film = s.film_raw(); ofilm, _, _ = o.render(seed=0, spp=32, brute=True)
+    assert np.array_equal(film[..., 3], ofilm[..., 3]), "weight channel (samples per pixel) must match exactly"
+    scale = ofilm[..., :3].max()
+    assert np.abs(film[..., :3] - ofilm[..., :3]).max() <= FILM_RTOL * scale
+    assert np.allclose(img, ob_develop(ofilm), rtol=0, atol=FILM_RTOL * scale / 32 * 4)
+    assert s.last_stats["paths"] == film.shape[0] * film.shape[1] * 32 and s.last_stats["passes"] == 2
+
+
+def ob_develop(rgbw):
+    w = rgbw[..., 3:4]
+    return rgbw[..., :3] / np.where(w == 0, 1, w)
+
+
+def test_film_matches_oracle_heightfield(hfield):
+    desc, s, o = hfield
+    s.render(seed=5, spp=16, develop=False)
+    film = s.film_raw(); ofilm, _, _ = o.render(seed=5, spp=16, brute=False)
+    assert np.array_equal(film[..., 3], ofilm[..., 3])
+    scale = max(ofilm[..., :3].max(), 1e-6)
+    assert np.abs(film[..., :3] - ofilm[..., :3]).max() <= FILM_RTOL * scale
+
+
+def test_schedulers_agree_and_accumulate(cbox):
+    _, s, _ = cbox
+    s.render(seed=1, spp=32, scheduler="warp_batch", develop=False); a = s.film_raw()
+    s.render(seed=1, spp=32, scheduler="regenerate", develop=False); b = s.film_raw()
+    assert np.array_equal(a[..., 3], b[..., 3])
+    assert np.abs(a - b).max() <= FILM_RTOL * a[..., :3].max()
+    # spp rounding (mvpath.cpp:36-41): 40 spp with spp_pass_lim 16 -> 2 passes of 16
+    s.render(seed=1, spp=40, develop=False)
+    assert s.last_stats["passes"] == 2 and np.all(s.film_raw()[..., 3] == 32)
+    # accumulation without clearing doubles the weights (Film accumulates across render() calls, hdrfilm.cpp:293-297)
+    s.render(seed=2, spp=32, develop=False, clear=False)
+    assert np.all(s.film_raw()[..., 3] == 64)
+
+
+def test_view_sharding_reproduces_single_gpu_film(cbox, scenes, gpu):
+    desc, s, _ = cbox
+    s.render(seed=3, spp=16, develop=False); full = s.film_raw()
+    for world in (2, 4, 8):            # 8 ranks > 4 views: views are cut into bands
+        acc = np.zeros_like(full)
+        for rank in range(world):
+            s.render(seed=3, spp=16, develop=False, rank=rank, world=world)
+            part = s.film_raw()
+            acc += part
+        assert np.array_equal(acc[..., 3], full[..., 3])
+        assert np.abs(acc - full).max() <= FILM_RTOL * full[..., :3].max()
+
+
+def test_max_depth_and_rr_edge_cases(scenes, ob, gpu):
+    for md, rr in [(0, 5), (1, 5), (2, 1), (-1, 2)]:
+        desc = scenes.cornell_box(grid_x=2, grid_y=1, view_res=16, max_depth=md, rr_depth=rr)
+        s = scenes.build(desc, device=gpu); o = ob.OracleScene(desc)
+        a = s.trace_lanes(0, 16, 0, 2 * 16 * 16 * 16, max_hits=4); b = o.trace_lanes(0, 16, 0, 2 * 16 * 16 * 16, max_hits=4, brute=True)
+        assert_bits(a["radiance"], b["radiance"], f"max_depth={md} rr_depth={rr}")
+        assert_bits(a["hit_prim"], b["hit_prim"], f"max_depth={md} rr_depth={rr} prims")
