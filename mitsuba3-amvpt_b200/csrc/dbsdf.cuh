@@ -125,7 +125,8 @@ AM_HD V3 fresnel_conductor3(float c, const DBsdf &b) {
 // roughplastic.cpp:365-376
 AM_HD float lerp_gather(const float *data, float x, int size) {
     x *= (float) (size - 1);
-    uint32_t index = (uint32_t) x; if (index > (uint32_t) (size - 2)) index = size - 2;
+    uint32_t index = x > 0.f ? (uint32_t) x : 0u;      // negative / NaN saturate to 0 (cvt.rzi.u32.f32 semantics)
+    if (index > (uint32_t) (size - 2)) index = size - 2;
     float v0 = data[index], v1 = data[index + 1];
     return lerp_(v0, v1, x - (float) index);
 }

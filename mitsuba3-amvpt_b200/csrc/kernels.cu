@@ -178,12 +178,13 @@ render_pass_kernel(const DScene s, const RenderParams p) {
                 V3 L = ps.valid_ray ? ps.result : v3(0.f);
                 splat_aggregated(m, has_result && ls.in_film, ls.pixel, make_float4(L.x, L.y, L.z, 1.f), p.film, p.moments);
                 has_result = false;
+                unsigned fm = __ballot_sync(m, !exhausted);     // idle lanes that may still draw a ticket
                 if (!exhausted) {
                     unsigned long long base = 0;
-                    unsigned leader = __ffs(m) - 1;
-                    if (lane_id == leader) base = atomicAdd(p.counters + CTR_TICKET, (unsigned long long) __popc(m));
-                    base = __shfl_sync(m, base, leader);
-                    unsigned long long ticket = base + __popc(m & ((1u << lane_id) - 1u));
+                    unsigned leader = __ffs(fm) - 1;
+                    if (lane_id == leader) base = atomicAdd(p.counters + CTR_TICKET, (unsigned long long) __popc(fm));
+                    base = __shfl_sync(fm, base, leader);
+                    unsigned long long ticket = base + __popc(fm & ((1u << lane_id) - 1u));
                     uint32_t lane, px, py;
                     if (ticket_to_lane(p, s, ticket, &lane, &px, &py)) {
                         lane_setup(s, p.seed_value, lane, px, py, ps, ls);

@@ -65,7 +65,9 @@ static inline V3 mask3(V3 v, bool m) { return m ? v : V3(0.f); }
 // roughplastic.cpp:365-376
 static inline float lerp_gather(const float *data, float x, int size) {
     x *= (float) (size - 1);
-    uint32_t index = (uint32_t) x; if (index > (uint32_t) (size - 2)) index = size - 2;
+    // float -> uint32 of a negative / NaN value is undefined in C++; the reference's CUDA variant saturates it to 0
+    // (cvt.rzi.u32.f32).  Only reachable for wi.z < 0, where every observable output is masked to zero.
+    uint32_t index = x > 0.f ? (uint32_t) x : 0u; if (index > (uint32_t) (size - 2)) index = size - 2;
     float v0 = data[index], v1 = data[index + 1];
     return lerp(v0, v1, x - (float) index);
 }

@@ -10,7 +10,13 @@ FILM_RTOL = 2e-5      # order of fp32 summation of <= 64 samples per pixel; stat
 
 
 def bits(a):
-    return np.ascontiguousarray(a).view(np.uint32)
+    """Bit patterns, with every NaN mapped to one canonical pattern (x86 and sm_100 produce different NaN payloads /
+    signs for the same invalid operation; the reference's own variants do too)."""
+    a = np.ascontiguousarray(a)
+    u = a.view(np.uint32).copy()
+    if a.dtype == np.float32:
+        u[np.isnan(a)] = 0x7fc00000
+    return u
 
 
 def assert_bits(a, b, what):
@@ -194,10 +200,12 @@ def test_schedulers_agree_and_accumulate(cbox):
     assert np.abs(a - b).max() <= FILM_RTOL * a[..., :3].max()
     # spp rounding (mvpath.cpp:36-41): 40 spp with spp_pass_lim 16 -> 2 passes of 16
     s.render(seed=1, spp=40, develop=False)
-    assert s.last_stats["passes"] == 2 and np.all(s.film_raw()[..., 3] == 32)
+    w = s.film_raw()[..., 3]     # a jittered position can round up into the next pixel (float32(px + 0.99999994) == px + 1), so a few
+    assert s.last_stats["passes"] == 2 and w.sum() == 32 * w.size and (w == 32).mean() > 0.999      # pixels hold 31 / 33
     # accumulation without clearing doubles the weights (Film accumulates across render() calls, hdrfilm.cpp:293-297)
     s.render(seed=2, spp=32, develop=False, clear=False)
-    assert np.all(s.film_raw()[..., 3] == 64)
+    w = s.film_raw()[..., 3]
+    assert w.sum() == 64 * w.size and (w == 64).mean() > 0.998
 
 
 def test_view_sharding_reproduces_single_gpu_film(cbox, scenes, gpu):
