@@ -97,6 +97,9 @@ int amvpt_scene_get_bsdf_tables(amvpt_scene *s, int bsdf, float *ext_transmittan
 /* ---- the hot path ----------------------------------------------------------------------------------------------- */
 /* MVPathIntegrator::render (src/integrators/mvpath.cpp:7-278): accumulates into the scene's film (RGBW, float32) */
 int amvpt_render(amvpt_scene *s, const amvpt_render_desc *d, amvpt_render_stats *stats_out);
+/* rectangles of the quilt that `rank` of `world` renders (view sharding, build-defined): fills up to `cap`
+ * records of 5 uint32 {x0, y0, w, h, view} and returns the number of rectangles */
+int amvpt_shard_tiles(amvpt_scene *s, uint32_t rank, uint32_t world, uint32_t *out5, uint32_t cap);
 int amvpt_cancel(amvpt_scene *s);                                        /* Integrator::cancel (integrator.h:303-306) */
 int amvpt_film_clear(amvpt_scene *s);                                    /* Film::prepare / clear (hdrfilm.cpp:245-273) */
 int amvpt_film_raw(amvpt_scene *s, float *rgbw_host);                    /* film storage, H*W*4 floats to host */

@@ -69,7 +69,7 @@ lib.amvpt_last_error.restype = C.c_char_p
 EXPORTS = ["amvpt_last_error", "amvpt_device_count", "amvpt_scene_create", "amvpt_scene_destroy", "amvpt_scene_from_xml",
            "amvpt_scene_from_xml_string", "amvpt_scene_add_bsdf", "amvpt_scene_add_mesh", "amvpt_scene_set_sensor_grid",
            "amvpt_scene_set_sensor_batch", "amvpt_scene_set_integrator", "amvpt_scene_commit", "amvpt_scene_info",
-           "amvpt_scene_get_sensor", "amvpt_scene_get_bsdf_tables", "amvpt_render", "amvpt_cancel", "amvpt_film_clear",
+           "amvpt_scene_get_sensor", "amvpt_scene_get_bsdf_tables", "amvpt_render", "amvpt_shard_tiles", "amvpt_cancel", "amvpt_film_clear",
            "amvpt_film_raw", "amvpt_film_develop", "amvpt_film_develop_device", "amvpt_film_device_ptr", "amvpt_film_add_host",
            "amvpt_trace_lanes", "amvpt_intersect", "amvpt_bsdf_eval_pdf_sample", "amvpt_math1", "amvpt_sampler_stream",
            "amvpt_bvh_validate"]
@@ -206,6 +206,12 @@ class Scene:
         _chk(lib.amvpt_render(self._h, C.byref(d), C.byref(st)))
         self.last_stats = {k: getattr(st, k) for k, _ in RenderStats._fields_ if k != "pad"}
         return self.develop() if develop else None
+
+    def shard_tiles(self, rank, world):
+        """Rectangles (x0, y0, w, h, view) of the quilt that `rank` of `world` renders."""
+        buf = np.zeros((4096, 5), np.uint32)
+        n = _chk(lib.amvpt_shard_tiles(self._h, C.c_uint32(rank), C.c_uint32(world), _p(buf, u32p), C.c_uint32(len(buf))))
+        return buf[:n].copy()
 
     def film_clear(self):
         _chk(lib.amvpt_film_clear(self._h))

@@ -142,6 +142,12 @@ int amvpt_render(amvpt_scene *h, const amvpt_render_desc *d, amvpt_render_stats 
             out->bvh_nodes = r.nodes; out->tri_tests = r.tris; out->path_vertices = r.vertices; out->passes = r.passes; out->launches = r.launches; out->spp_done = r.spp_done; out->pad = 0; }
         return AMVPT_OK; });
 }
+int amvpt_shard_tiles(amvpt_scene *h, uint32_t rank, uint32_t world, uint32_t *out5, uint32_t cap) {
+    return guard([&] { NEED(h); NEED(world > 0 && rank < world); if (h->s->sensors.empty()) AM_THROW("no sensor");
+        Shard sh; sh.rank = rank; sh.world = world; std::vector<TileDesc> t = rank_tiles(*h->s, sh, false);
+        for (size_t i = 0; i < t.size() && i < cap && out5; ++i) { uint32_t *o = out5 + 5 * i; o[0] = t[i].x0; o[1] = t[i].y0; o[2] = t[i].w; o[3] = t[i].h; o[4] = t[i].pad; }
+        return (int) t.size(); });
+}
 int amvpt_cancel(amvpt_scene *h) { return guard([&] { NEED(h); h->s->stop = true; return AMVPT_OK; }); }
 int amvpt_film_clear(amvpt_scene *h) { return guard([&] { Scene &s = committed(h); s.film_clear(nullptr); AM_CUDA(cudaDeviceSynchronize()); return AMVPT_OK; }); }
 int amvpt_film_raw(amvpt_scene *h, float *rgbw) {

@@ -113,6 +113,7 @@ struct RenderOptions {
     void (*allreduce)(float *dev, uint32_t n, void *user) = nullptr; void *allreduce_user = nullptr;
 };
 void render(Scene &s, const RenderOptions &opt);
+std::vector<TileDesc> rank_tiles(const Scene &s, const Shard &sh, bool per_view);
 
 // xml.cpp
 Scene *load_xml_file(const std::string &path, const std::vector<std::pair<std::string, std::string>> &defines);

@@ -10,7 +10,7 @@ namespace amvpt {
 // Work units of one rank.  world == 1: the whole quilt as one rectangle, lanes in the reference's row-major order.
 // Otherwise the quilt is cut into view tiles (and, when there are fewer views than ranks, horizontal bands of a
 // view); unit u goes to rank u mod world.  Lane indices stay global, so any partition reproduces the same samples.
-static std::vector<TileDesc> rank_tiles(const Scene &s, const Shard &sh, bool per_view) {
+std::vector<TileDesc> rank_tiles(const Scene &s, const Shard &sh, bool per_view) {
     std::vector<TileDesc> out;
     if (sh.world <= 1 && !per_view) {
         TileDesc t{}; t.x0 = 0; t.y0 = 0; t.w = s.film_w; t.h = s.film_h; t.pad = 0; out.push_back(t); return out;

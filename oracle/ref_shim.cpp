@@ -44,6 +44,16 @@ using ST4  = Transform<Point<float, 4>>;
 using Fr   = Frame<F>;
 using MF   = MicrofacetDistribution<F, Spec>;
 
+// The two symbols below live in libmitsuba-core (src/core/class.cpp, src/core/logger.cpp), which is not built here
+// (SURVEY.md F6); the header-only code reaches them only on error paths.  Minimal stand-ins so the shim links.
+#include <stdexcept>
+namespace mitsuba {
+const Class *m_class = nullptr;
+namespace detail {
+void (Throw)(LogLevel, const Class *, const char *, int, const std::string &msg) { throw std::runtime_error(msg); }
+}
+}
+
 static inline float g(const F &v) { return v.entry(0); }
 static inline V3 ld3(const float *p) { return V3(F(p[0]), F(p[1]), F(p[2])); }
 static inline void st3(float *p, const V3 &v) { p[0] = g(v.x()); p[1] = g(v.y()); p[2] = g(v.z()); }

@@ -1,0 +1,149 @@
+"""CPU-only tests of the product's host side: C-ABI surface, scene construction logic, error behaviour, view sharding
+(with a world_size-2 gloo run of the film reduction used by bench.py).  No compute entry point is called: without a GPU
+they must fail loudly, which is itself tested."""
+import ctypes as C
+import os
+import re
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_exports_every_declared_symbol(pkg):
+    hdr = open(os.path.join(ROOT, "include", "amvpt.h")).read()
+    declared = sorted(set(re.findall(r"\b(amvpt_[a-z0-9_]+)\s*\(", hdr)))
+    assert len(declared) >= 29
+    for name in declared:
+        assert hasattr(pkg.lib, name), f"{name} is declared in include/amvpt.h but not exported by libamvpt_b200.so"
+    assert set(pkg.EXPORTS) == set(declared)
+
+
+def test_sensor_matrices_match_oracle(pkg, scenes, ob):
+    for kw in (dict(grid_x=4, grid_y=1, view_res=64), dict(grid_x=8, grid_y=8, view_res=32, cam_dist=400.0),
+               dict(grid_x=3, grid_y=2, view_res=16, thinlens=True, aperture_radius=5.0, cone_deg=20.0)):
+        desc = scenes.cornell_box(**kw)
+        s = scenes.build(desc, commit=False); o = ob.OracleScene(desc)
+        info = s.info(); assert (info["film_w"], info["film_h"]) == o.film_size()
+        for i in range(info["n_views"]):
+            a, b = s.sensor(i); c, d = o.sensor(i)
+            assert np.array_equal(a.view(np.uint32), c.view(np.uint32)), f"sample_to_camera of view {i}"
+            assert np.array_equal(b[:3].view(np.uint32), d[:3].view(np.uint32)), f"to_world of view {i}"
+    # the camera line: sub-cameras sit on the x axis, cam_dist apart end to end, centred (grid.cpp:208-226)
+    desc = scenes.cornell_box(grid_x=4, grid_y=1, view_res=8, cam_dist=200.0); s = scenes.build(desc, commit=False)
+    xs = [s.sensor(i)[1][0, 3] for i in range(4)]
+    assert np.allclose(np.diff(xs), -200.0 / 3, atol=1e-3) and np.isclose(np.mean(xs), 278.0, atol=1e-3)
+
+
+def test_roughplastic_tables_match_oracle(pkg, scenes, ob):
+    desc = scenes.cornell_box(grid_x=2, grid_y=1, view_res=8)
+    desc["bsdfs"] = [dict(type="roughplastic", distribution="beckmann", alpha=0.1, reflectance=(0.5, 0.3, 0.1)),
+                     dict(type="roughplastic", distribution="ggx", alpha=0.25, reflectance=(0.2, 0.2, 0.7), int_ior=1.33, ext_ior=1.0, nonlinear=True)]
+    for m in desc["meshes"]:
+        m["bsdf"] = 0
+    s = scenes.build(desc, commit=False); o = ob.OracleScene(desc)
+    for i in range(2):
+        ta, sa = s.bsdf_tables(i); tb, sb = o.bsdf_tables(i)
+        assert np.array_equal(ta.view(np.uint32), tb.view(np.uint32)) and np.array_equal(sa.view(np.uint32), sb.view(np.uint32))
+        assert 0 < ta.min() and ta.max() < 1 and np.all(np.diff(ta) > -1e-3)      # transmittance grows with cos(theta)
+
+
+def test_bvh_structure(pkg, scenes):
+    for desc in (scenes.cornell_box(grid_x=2, grid_y=1, view_res=8), scenes.height_field(n=64, grid_x=2, grid_y=2, view_res=8)):
+        s = scenes.build(desc, commit=False)
+        depth, leaves = s.bvh_validate()       # throws if a triangle leaves its leaf box, a child leaves its parent, or a triangle is lost
+        n = s.info()["n_prims"]
+        assert leaves * 4 >= n and depth <= 62 and depth >= int(np.log2(max(n / 4, 1)))
+    # degenerate inputs: one triangle, coincident triangles, zero-area triangle
+    s = pkg.Scene(); b = s.add_bsdf(type="diffuse")
+    tri = np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0]], np.float32)
+    s.add_mesh(tri, [[0, 1, 2]], b)
+    s.set_sensor_grid(2, 1, 16, 8, np.eye(4), 45.0); assert s.bvh_validate()[1] >= 1
+    for _ in range(9):
+        s.add_mesh(tri, [[0, 1, 2]], b)
+    s.add_mesh(np.zeros((3, 3), np.float32), [[0, 1, 2]], b)
+    assert s.bvh_validate()[1] >= 3 and s.info()["n_prims"] == 11
+
+
+def test_error_behaviour(pkg, scenes):
+    s = pkg.Scene(); b = s.add_bsdf(type="diffuse")
+    with pytest.raises(pkg.AmvptError, match="out of range"):
+        s.add_mesh(np.zeros((3, 3), np.float32), [[0, 1, 3]], b)
+    with pytest.raises(pkg.AmvptError, match="BSDF"):
+        s.add_mesh(np.zeros((3, 3), np.float32), [[0, 1, 2]], 7)
+    with pytest.raises(pkg.AmvptError, match="divisible"):          # grid.cpp:100-101
+        s.set_sensor_grid(3, 1, 64, 64, np.eye(4), 45.0)
+    with pytest.raises(pkg.AmvptError, match="max_depth"):          # integrator.cpp:510-512
+        s.set_integrator(max_depth=-2)
+    with pytest.raises(pkg.AmvptError, match="rr_depth"):           # integrator.cpp:517-518
+        s.set_integrator(rr_depth=0)
+    with pytest.raises(pkg.AmvptError, match="not committed"):
+        s.render(spp=16)
+    with pytest.raises(KeyError):
+        s.add_bsdf(type="plastic")                                   # not on the path: rejected, not approximated
+
+
+def test_compute_fails_loudly_without_gpu(pkg, scenes):
+    if pkg.device_count() > 0:
+        pytest.skip("a GPU is present")
+    s = scenes.build(scenes.cornell_box(grid_x=2, grid_y=1, view_res=8), commit=False)
+    with pytest.raises(pkg.AmvptError, match="no CUDA device"):
+        s.commit(0)
+    with pytest.raises(pkg.AmvptError, match="no CUDA device"):
+        pkg.math1(0, np.zeros(4, np.float32))
+
+
+def test_shard_tiles_partition_the_quilt(pkg, scenes):
+    for gx, gy, res in ((8, 8, 16), (4, 1, 32), (3, 2, 8)):
+        s = scenes.build(scenes.cornell_box(grid_x=gx, grid_y=gy, view_res=res), commit=False)
+        for world in (1, 2, 3, 4, 8, 16):
+            cover = np.zeros((gy * res, gx * res), np.int32); px = []
+            for rank in range(world):
+                t = s.shard_tiles(rank, world); n = 0
+                for x0, y0, w, h, view in t:
+                    cover[y0:y0 + h, x0:x0 + w] += 1; n += w * h
+                    # the tile of view v sits where GridSensor::sample_ray routes it (reverse_y = true, grid.cpp:246-255)
+                    if world > 1:
+                        assert view == (x0 // res) + gx * (gy - 1 - y0 // res)
+                px.append(n)
+            assert np.all(cover == 1), f"world {world}: tiles must cover every pixel exactly once"
+            assert max(px) - min(px) <= (gx * gy * res * res) // world // 2 + res * res, f"world {world}: unbalanced {px}"
+
+
+GLOO_WORKER = r"""
+import os, sys, importlib, numpy as np, torch, torch.distributed as dist
+sys.path.insert(0, {root!r})
+pkg = importlib.import_module('mitsuba3-amvpt_b200'); scenes = importlib.import_module('mitsuba3-amvpt_b200.scenes')
+mg = importlib.import_module('mitsuba3-amvpt_b200.multigpu')
+dist.init_process_group('gloo', rank=int(os.environ['RANK']), world_size=int(os.environ['WORLD_SIZE']))
+rank, world = dist.get_rank(), dist.get_world_size()
+s = scenes.build(scenes.cornell_box(grid_x=4, grid_y=2, view_res=8), commit=False)
+H, W = 16, 32
+# every rank fills its own tiles with (rank + 1) and leaves the rest at zero, as the sharded render does
+film = torch.zeros(H, W, 4)
+for x0, y0, w, h, view in s.shard_tiles(rank, world):
+    film[y0:y0 + h, x0:x0 + w] = float(view + 1)
+mg.reduce_film(film, dst=0)
+stats = torch.zeros(8 * 4); stats[4 * rank:4 * rank + 4] = rank + 1.0     # per-view statistics, summed so that every rank derives the same allocation
+mg.allreduce_stats(stats)
+assert torch.equal(stats[:8], torch.tensor([1., 1., 1., 1., 2., 2., 2., 2.]))
+if rank == 0:
+    want = torch.zeros(H, W)
+    for r in range(world):
+        for x0, y0, w, h, view in s.shard_tiles(r, world):
+            want[y0:y0 + h, x0:x0 + w] = float(view + 1)
+    assert torch.equal(film[..., 0], want) and (want > 0).all()
+dist.destroy_process_group()
+print('ok', rank)
+"""
+
+
+def test_film_reduce_world_size_2_gloo(pkg, tmp_path):
+    script = tmp_path / "worker.py"; script.write_text(GLOO_WORKER.format(root=ROOT))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+                        "--master-port", "29591", str(script)], capture_output=True, text=True, timeout=240)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert "ok 0" in r.stdout and "ok 1" in r.stdout
