@@ -8,6 +8,7 @@
 #include <algorithm>
 #include <cfloat>
 #include <cmath>
+#include <cstdlib>
 
 namespace amvpt {
 
@@ -21,7 +22,13 @@ struct Box {
 struct Prim { Box b; float c[3]; uint32_t prim; };
 struct TNode { Box b; int32_t left = -1, right = -1; uint32_t first = 0, count = 0; };
 
-const int kBins = 16, kMaxLeaf = 4, kSahDepth = 40;
+const int kBins = 16, kSahDepth = 40;
+// Leaf policy: at most kMaxLeaf triangles (<= 7 by the leaf encoding); a range that already fits becomes a leaf unless
+// the best SAH split is cheaper (cost of one node step kCostNode vs. one triangle test kCostTri, measured on sm_100a:
+// the IEEE-exact Moeller-Trumbore test costs about 1.5 box-pair steps).  AMVPT_MAX_LEAF / AMVPT_SAH_CT override for tuning.
+static int env_int(const char *k, int d) { const char *v = getenv(k); return v ? atoi(v) : d; }
+static float env_float(const char *k, float d) { const char *v = getenv(k); return v ? (float) atof(v) : d; }
+static int kMaxLeaf = 4; static float kCostTri = 1.5f, kCostNode = 1.f;
 
 struct Builder {
     std::vector<Prim> &prims; std::vector<TNode> nodes;
@@ -31,7 +38,8 @@ struct Builder {
         for (uint32_t i = begin; i < end; ++i) { n.b.grow(prims[i].b); cb.grow(prims[i].c); }
         n.first = begin; n.count = end - begin;
         int32_t self = (int32_t) nodes.size(); nodes.push_back(n);
-        if (end - begin <= (uint32_t) kMaxLeaf) return self;
+        if (end - begin <= 1) return self;
+        bool fits = end - begin <= (uint32_t) kMaxLeaf;
         int axis = 0; float ext = cb.hi[0] - cb.lo[0];
         for (int a = 1; a < 3; ++a) if (cb.hi[a] - cb.lo[a] > ext) { ext = cb.hi[a] - cb.lo[a]; axis = a; }
         uint32_t mid = (begin + end) / 2; bool split = false;
@@ -49,11 +57,13 @@ struct Builder {
                 float c = la[i] * (float) ln[i] + ra[i + 1] * (float) rn[i + 1];
                 if (c < best_cost) { best_cost = c; best = i; }
             }
+            if (fits && (best < 0 || kCostTri * (float) (end - begin) * n.b.half_area() <= kCostNode * n.b.half_area() + kCostTri * best_cost)) return self;
             if (best >= 0) {
                 uint32_t m = (uint32_t) (std::partition(prims.begin() + begin, prims.begin() + end, [&](const Prim &p) { return binof(p) <= best; }) - prims.begin());
                 if (m != begin && m != end) { mid = m; split = true; }
             }
         }
+        if (!split && fits) return self;
         if (!split) {   // object median along the widest axis: guarantees termination and bounded depth
             std::nth_element(prims.begin() + begin, prims.begin() + mid, prims.begin() + end,
                              [axis](const Prim &a, const Prim &b) { return a.c[axis] < b.c[axis] || (a.c[axis] == b.c[axis] && a.prim < b.prim); });
@@ -87,6 +97,7 @@ void build_bvh(const Scene &s, float scene_scale, BvhOut &out) {
             p.b = b;
         }
     }
+    kMaxLeaf = std::min(std::max(env_int("AMVPT_MAX_LEAF", 4), 1), 7); kCostTri = env_float("AMVPT_SAH_CT", 1.5f);
     Builder bl(prims);
     if (np) bl.build(0, np, 0);
     if (np && bl.depth_of(0) > AM_STACK_SIZE - 2) AM_THROW("BVH depth %d exceeds the traversal stack", bl.depth_of(0));

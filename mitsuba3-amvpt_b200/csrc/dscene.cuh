@@ -73,21 +73,23 @@ AM_D Ray sensor_sample_ray(const DScene &s, V2 pos, V2 aperture, uint32_t *view_
 }
 
 // ---------------------------------------------------------------- ray / triangle, BVH traversal
-// Mesh::moeller_trumbore (include/mitsuba/render/mesh.h:467-488)
+// Mesh::moeller_trumbore (include/mitsuba/render/mesh.h:467-488).  The reference evaluates u, v, t unconditionally and
+// combines the masks; leaving as soon as one test fails skips the remaining products without changing any value that
+// is observed (t, u, v are only read when every test passed).
 AM_D bool moeller_trumbore(const Ray &ray, V3 p0, V3 p1, V3 p2, float *t_o, float *u_o, float *v_o) {
     V3 e1 = p1 - p0, e2 = p2 - p0;
     V3 pvec = cross(ray.d, e2);
     float inv_det = rcp(dot(e1, pvec));
     V3 tvec = ray.o - p0;
     float u = dot(tvec, pvec) * inv_det;
-    bool active = u >= 0.f && u <= 1.f;
+    if (!(u >= 0.f && u <= 1.f)) return false;
     V3 qvec = cross(tvec, e1);
     float v = dot(ray.d, qvec) * inv_det;
-    active = active && v >= 0.f && u + v <= 1.f;
+    if (!(v >= 0.f && u + v <= 1.f)) return false;
     float t = dot(e2, qvec) * inv_det;
-    active = active && t >= 0.f && t <= ray.maxt;
+    if (!(t >= 0.f && t <= ray.maxt)) return false;
     *t_o = t; *u_o = u; *v_o = v;
-    return active;
+    return true;
 }
 
 #define AM_SLAB_EPS 1e-6f
@@ -107,6 +109,9 @@ AM_D bool slab(float lox, float hix, float loy, float hiy, float loz, float hiz,
 // Closest hit (ANY = false) with the tie rule of ShapeKDTree::ray_intersect_naive
 // (include/mitsuba/render/kdtree.h:2445-2468): among equal t the primitive with the larger global index
 // wins.  ANY = true: Scene::ray_test semantics, first accepted triangle ends the traversal.
+// "while-while" traversal: every lane first descends through inner nodes until it holds a leaf, the warp reconverges,
+// then the lanes intersect their leaves together -- the triangle test is the expensive, divergence-sensitive part.
+#define AM_TRAVERSAL_DONE ((int32_t) 0x80000000)      /* not a valid leaf code: first would be 2^28 - 1 */
 template <bool ANY> AM_D Hit intersect(const DScene &s, const Ray &ray, uint32_t *n_nodes = nullptr, uint32_t *n_tris = nullptr) {
     Hit h; h.t = AM_INF; h.u = 0.f; h.v = 0.f; h.tri = AM_NO_HIT;
     uint32_t best_prim = 0;
@@ -114,10 +119,9 @@ template <bool ANY> AM_D Hit intersect(const DScene &s, const Ray &ray, uint32_t
     V3 id = v3(rcp(ray.d.x), rcp(ray.d.y), rcp(ray.d.z));
     int32_t stack[AM_STACK_SIZE]; int sp = 0;
     int32_t node = 0;
-    const int32_t SENTINEL = 0x7fffffff;
-    stack[sp++] = SENTINEL;
-    while (node != SENTINEL) {
-        if (node >= 0) {
+    stack[sp++] = AM_TRAVERSAL_DONE;
+    for (;;) {
+        while (node >= 0) {
             const float4 *np = s.nodes + 4 * (size_t) node;
             float4 n0 = ldg4(np), n1 = ldg4(np + 1), n2 = ldg4(np + 2), n3 = ldg4(np + 3);
             if (n_nodes) (*n_nodes)++;
@@ -127,28 +131,26 @@ template <bool ANY> AM_D Hit intersect(const DScene &s, const Ray &ray, uint32_t
             int32_t ca = __float_as_int(n3.x), cb = __float_as_int(n3.y);
             if (ha && hb) {
                 bool swap = tb < ta;
-                int32_t nearc = swap ? cb : ca, farc = swap ? ca : cb;
-                stack[sp++] = farc; node = nearc;
-            } else if (ha) node = ca;
-            else if (hb) node = cb;
+                stack[sp++] = swap ? ca : cb; node = swap ? cb : ca;
+            } else if (ha || hb) node = ha ? ca : cb;
             else node = stack[--sp];
-        } else {
-            uint32_t code = ~(uint32_t) node, first = code >> 3, count = code & 7u;
-            for (uint32_t i = 0; i < count; ++i) {
-                const float4 *tp = s.tris + 3 * (size_t) (first + i);
-                float4 a = ldg4(tp), b = ldg4(tp + 1), c = ldg4(tp + 2);
-                if (n_tris) (*n_tris)++;
-                float t, u, v;
-                if (moeller_trumbore(ray, v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), v3(c.x, c.y, c.z), &t, &u, &v)) {
-                    uint32_t prim = __float_as_uint(a.w);
-                    if (ANY) { h.t = t; h.u = u; h.v = v; h.tri = first + i; return h; }
-                    if (h.tri == AM_NO_HIT || t < h.t || (t == h.t && prim > best_prim)) {
-                        h.t = t; h.u = u; h.v = v; h.tri = first + i; best_prim = prim; best = t;
-                    }
+        }
+        if (node == AM_TRAVERSAL_DONE) break;
+        uint32_t code = ~(uint32_t) node, first = code >> 3, count = code & 7u;
+        for (uint32_t i = 0; i < count; ++i) {
+            const float4 *tp = s.tris + 3 * (size_t) (first + i);
+            float4 a = ldg4(tp), b = ldg4(tp + 1), c = ldg4(tp + 2);
+            if (n_tris) (*n_tris)++;
+            float t, u, v;
+            if (moeller_trumbore(ray, v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), v3(c.x, c.y, c.z), &t, &u, &v)) {
+                uint32_t prim = __float_as_uint(a.w);
+                if (ANY) { h.t = t; h.u = u; h.v = v; h.tri = first + i; return h; }
+                if (h.tri == AM_NO_HIT || t < h.t || (t == h.t && prim > best_prim)) {
+                    h.t = t; h.u = u; h.v = v; h.tri = first + i; best_prim = prim; best = t;
                 }
             }
-            node = stack[--sp];
         }
+        node = stack[--sp];
     }
     return h;
 }

@@ -105,7 +105,7 @@ void build_bvh(const Scene &s, float scene_scale, BvhOut &out);
 
 // render.cpp -- MVPathIntegrator::render() (src/integrators/mvpath.cpp:7-278), wavefront branch
 struct RenderOptions {
-    uint32_t seed = 0, spp = 0; int scheduler = SCHED_REGENERATE; bool stats = false;
+    uint32_t seed = 0, spp = 0; int scheduler = SCHED_REGENERATE; bool stats = false; uint32_t regen_min = 0;
     Shard shard; cudaStream_t stream = nullptr;
     // adaptive allocator (build-defined): 0 = fixed spp; otherwise spp is the mean budget per pixel
     bool adaptive = false; float adaptive_threshold = 0.f; uint32_t adaptive_min_spp = 16;

@@ -160,7 +160,6 @@ AM_D void flush_stats(const StatCtx &st, unsigned long long *c) {
 // MODE 0: a warp takes 32 consecutive tickets and traces them to completion before taking the next 32.
 // MODE 1: path regeneration -- whenever at least REGEN_MIN lanes of the warp are idle they splat and take fresh
 //         tickets together, so the warp stays full while paths have different lengths.
-#define AM_REGEN_MIN 8
 template <int MODE, bool STATS> __global__ void __launch_bounds__(128)
 render_pass_kernel(const DScene s, const RenderParams p) {
     const unsigned lane_id = threadIdx.x & 31u;
@@ -170,7 +169,7 @@ render_pass_kernel(const DScene s, const RenderParams p) {
     for (;;) {
         bool idle = !ps.active;
         unsigned idle_mask = __ballot_sync(0xffffffffu, idle);
-        bool refill = MODE == 0 ? idle_mask == 0xffffffffu : (__popc(idle_mask) >= AM_REGEN_MIN || idle_mask == 0xffffffffu);
+        bool refill = MODE == 0 ? idle_mask == 0xffffffffu : (__popc(idle_mask) >= (int) p.regen_min || idle_mask == 0xffffffffu);
         if (refill) {
             if (idle) {
                 // splat finished lanes (imageblock.h:185-215: value = spec * ray_weight (1), weight channel += 1)

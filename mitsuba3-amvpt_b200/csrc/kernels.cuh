@@ -11,7 +11,7 @@ struct TileDesc { uint32_t x0, y0, w, h; uint32_t spp, pad; unsigned long long l
 struct RenderParams {
     uint32_t seed_value;       // sampler seed + spp_per_pass * pass + render seed (mvpath.cpp:226-231, sampler.cpp:129)
     uint32_t spp_per_pass;     // lane stride of the reference's lane -> pixel map (mvpath.cpp:174-190)
-    uint32_t n_tiles, pad0;
+    uint32_t n_tiles, regen_min;   // regen_min: idle lanes per warp that trigger a refill (scheduler 1)
     const TileDesc *tiles;
     unsigned long long n_lanes;
     float4 *film;              // RGBW, film_w * film_h

@@ -4,6 +4,7 @@
 #include "host.h"
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 
 namespace amvpt {
 
@@ -70,7 +71,7 @@ void render(Scene &s, const RenderOptions &opt) {
     AM_CUDA(cudaMemsetAsync(s.counters, 0, sizeof(unsigned long long) * CTR_COUNT, st));
 
     RenderParams p{};
-    p.spp_per_pass = spp_per_pass; p.tiles = s.tiles_dev; p.film = s.film; p.moments = adaptive ? s.moments : nullptr; p.counters = s.counters;
+    p.regen_min = opt.regen_min ? opt.regen_min : (getenv("AMVPT_REGEN_MIN") ? (uint32_t) atoi(getenv("AMVPT_REGEN_MIN")) : 8u); p.spp_per_pass = spp_per_pass; p.tiles = s.tiles_dev; p.film = s.film; p.moments = adaptive ? s.moments : nullptr; p.counters = s.counters;
     auto launch = [&](std::vector<TileDesc> &tiles, uint32_t pass) {
         unsigned long long lanes = finish_tiles(tiles);
         if (!lanes) return;
