@@ -706,18 +706,27 @@ void orc_trace_lanes(void *sp, uint32_t seed_value, uint32_t spp_per_pass, uint3
 // ---- full render (MVPT::render JIT branch, mvpath.cpp:132-272): film = RGBW float32 [H][W][4]
 // Returns seconds spent in the pass loop.  Rows of the quilt are distributed over `nthreads` threads; each pixel's
 // spp_per_pass lanes are accumulated in lane order, passes in pass order (deterministic).
+double orc_render_rows(void *sp, uint32_t seed, uint32_t spp, uint32_t spp_pass_lim, int brute, int nthreads, float *film,
+                       uint32_t row_begin, uint32_t row_end, uint32_t row_stride, uint64_t *stats);
 double orc_render(void *sp, uint32_t seed, uint32_t spp, uint32_t spp_pass_lim, int brute, int nthreads, float *film,
                   uint32_t row_begin, uint32_t row_end, uint64_t *stats) {
+    return orc_render_rows(sp, seed, spp, spp_pass_lim, brute, nthreads, film, row_begin, row_end, 1, stats);
+}
+// Same, restricted to rows row_begin, row_begin + row_stride, ... < row_end (bounded samples of a large quilt for the timed CPU baseline)
+double orc_render_rows(void *sp, uint32_t seed, uint32_t spp, uint32_t spp_pass_lim, int brute, int nthreads, float *film,
+                       uint32_t row_begin, uint32_t row_end, uint32_t row_stride, uint64_t *stats) {
     Scene &s = *(Scene *) sp;
     uint32_t spp_per_pass = spp_pass_lim ? std::min(spp_pass_lim, spp) : spp;
     uint32_t n_passes = spp / spp_per_pass;
     if (row_end > s.film_h) row_end = s.film_h;
-    std::atomic<uint32_t> next_row{ row_begin };
+    if (!row_stride) row_stride = 1;
+    std::atomic<uint32_t> next_row{ 0 };
     std::vector<TraverseStats> tstats(std::max(nthreads, 1));
     auto t0 = std::chrono::steady_clock::now();
     auto worker = [&](int tid) {
         for (;;) {
-            uint32_t y = next_row.fetch_add(1); if (y >= row_end) break;
+            uint64_t yy = (uint64_t) row_begin + (uint64_t) next_row.fetch_add(1) * row_stride; if (yy >= row_end) break;
+            uint32_t y = (uint32_t) yy;
             for (uint32_t pass = 0; pass < n_passes; ++pass) {
                 uint32_t seed_value = s.base_seed + (spp_per_pass * pass + seed);
                 for (uint32_t x = 0; x < s.film_w; ++x) for (uint32_t k = 0; k < spp_per_pass; ++k) {

@@ -36,6 +36,7 @@ def orc():
         _orc = C.CDLL(build_oracle())
         _orc.orc_scene_new.restype = C.c_void_p
         _orc.orc_render.restype = C.c_double
+        _orc.orc_render_rows.restype = C.c_double
         _orc.orc_num_prims.restype = C.c_uint32
     return _orc
 
@@ -166,13 +167,13 @@ class OracleScene:
                                         _p(r["bs_pdf"]), _p(r["bs_eta"]), _p(r["bs_type"], u32p), _p(r["weight"]))
         return r
 
-    def render(self, seed=0, spp=16, brute=False, nthreads=None, rows=None):
+    def render(self, seed=0, spp=16, brute=False, nthreads=None, rows=None, row_stride=1):
         """Returns (RGBW film [H, W, 4], seconds in the pass loop, (nodes, tris))."""
         w, h = self.film_size(); film = np.zeros((h, w, 4), np.float32); stats = np.zeros(2, np.uint64)
         r0, r1 = rows if rows is not None else (0, h)
         nthreads = nthreads or os.cpu_count() or 1
-        sec = self.o.orc_render(self.h, C.c_uint32(seed), C.c_uint32(spp), C.c_uint32(self.spp_pass_lim), C.c_int(int(brute)), C.c_int(nthreads),
-                                _p(film), C.c_uint32(r0), C.c_uint32(r1), _p(stats, u64p))
+        sec = self.o.orc_render_rows(self.h, C.c_uint32(seed), C.c_uint32(spp), C.c_uint32(self.spp_pass_lim), C.c_int(int(brute)), C.c_int(nthreads),
+                                     _p(film), C.c_uint32(r0), C.c_uint32(r1), C.c_uint32(row_stride), _p(stats, u64p))
         return film, sec, stats
 
 
