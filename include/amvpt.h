@@ -93,6 +93,13 @@ int amvpt_scene_info(amvpt_scene *s, uint32_t *film_w, uint32_t *film_h, uint32_
                      uint32_t *n_bvh_nodes, uint32_t *sample_count);
 int amvpt_scene_get_sensor(amvpt_scene *s, uint32_t index, float *sample_to_camera16, float *to_world16);
 int amvpt_scene_get_bsdf_tables(amvpt_scene *s, int bsdf, float *ext_transmittance64, float *scalars3);
+/* read-back of the host scene description (what the XML loader or the add_* calls produced; works before commit).
+ * amvpt_scene_get_mesh: pass NULL buffers to query sizes first.  amvpt_scene_get_bsdf returns int_ior = int_ior / ext_ior, ext_ior = 1. */
+int amvpt_scene_counts(amvpt_scene *s, uint32_t *n_meshes, uint32_t *n_bsdfs, uint32_t *n_emitters);
+int amvpt_scene_get_mesh(amvpt_scene *s, uint32_t index, uint32_t *n_vertices, uint32_t *n_faces, int32_t *bsdf, int32_t *has_normals,
+                         int32_t *flip_normals, int32_t *is_emitter, float *radiance3, float *positions, uint32_t *faces, float *normals);
+int amvpt_scene_get_bsdf(amvpt_scene *s, int bsdf, amvpt_bsdf_desc *d);
+int amvpt_scene_get_integrator(amvpt_scene *s, amvpt_integrator_desc *d, int32_t *is_mvpath, int32_t *sa_reuse, uint32_t *reuse_count);
 
 /* ---- the hot path ----------------------------------------------------------------------------------------------- */
 /* MVPathIntegrator::render (src/integrators/mvpath.cpp:7-278): accumulates into the scene's film (RGBW, float32) */

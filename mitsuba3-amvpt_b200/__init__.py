@@ -69,7 +69,8 @@ lib.amvpt_last_error.restype = C.c_char_p
 EXPORTS = ["amvpt_last_error", "amvpt_device_count", "amvpt_scene_create", "amvpt_scene_destroy", "amvpt_scene_from_xml",
            "amvpt_scene_from_xml_string", "amvpt_scene_add_bsdf", "amvpt_scene_add_mesh", "amvpt_scene_set_sensor_grid",
            "amvpt_scene_set_sensor_batch", "amvpt_scene_set_integrator", "amvpt_scene_commit", "amvpt_scene_info",
-           "amvpt_scene_get_sensor", "amvpt_scene_get_bsdf_tables", "amvpt_render", "amvpt_shard_tiles", "amvpt_cancel", "amvpt_film_clear",
+           "amvpt_scene_get_sensor", "amvpt_scene_get_bsdf_tables", "amvpt_scene_counts", "amvpt_scene_get_mesh",
+           "amvpt_scene_get_bsdf", "amvpt_scene_get_integrator", "amvpt_render", "amvpt_shard_tiles", "amvpt_cancel", "amvpt_film_clear",
            "amvpt_film_raw", "amvpt_film_develop", "amvpt_film_develop_device", "amvpt_film_device_ptr", "amvpt_film_add_host",
            "amvpt_trace_lanes", "amvpt_intersect", "amvpt_bsdf_eval_pdf_sample", "amvpt_math1", "amvpt_sampler_stream",
            "amvpt_bvh_validate"]
@@ -183,6 +184,37 @@ class Scene:
         t = np.zeros(64, np.float32); s = np.zeros(3, np.float32)
         _chk(lib.amvpt_scene_get_bsdf_tables(self._h, C.c_int(bsdf), _p(t), _p(s)))
         return t, s
+
+    # ---- read-back of the host description (what XML loading produced)
+    def counts(self):
+        a, b, c = C.c_uint32(), C.c_uint32(), C.c_uint32()
+        _chk(lib.amvpt_scene_counts(self._h, C.byref(a), C.byref(b), C.byref(c)))
+        return dict(n_meshes=a.value, n_bsdfs=b.value, n_emitters=c.value)
+
+    def mesh(self, index):
+        nv, nf, bsdf, hn, fl, em = C.c_uint32(), C.c_uint32(), C.c_int32(), C.c_int32(), C.c_int32(), C.c_int32()
+        rad = np.zeros(3, np.float32); null = C.c_void_p()
+        _chk(lib.amvpt_scene_get_mesh(self._h, C.c_uint32(index), C.byref(nv), C.byref(nf), C.byref(bsdf), C.byref(hn), C.byref(fl), C.byref(em),
+                                      _p(rad), null, null, null))
+        pos = np.zeros((nv.value, 3), np.float32); faces = np.zeros((nf.value, 3), np.uint32)
+        nrm = np.zeros((nv.value, 3), np.float32) if hn.value else None
+        _chk(lib.amvpt_scene_get_mesh(self._h, C.c_uint32(index), None, None, None, None, None, None, None, _p(pos), _p(faces, u32p),
+                                      _p(nrm) if nrm is not None else null))
+        return dict(positions=pos, faces=faces, normals=nrm, bsdf=bsdf.value, flip_normals=bool(fl.value),
+                    radiance=tuple(float(x) for x in rad) if em.value else None)
+
+    def bsdf(self, index):
+        d = BsdfDesc(); _chk(lib.amvpt_scene_get_bsdf(self._h, C.c_int(index), C.byref(d)))
+        inv = {v: k for k, v in BSDF_TYPES.items()}
+        return dict(type=inv[d.type], twosided=bool(d.twosided), distribution=("beckmann", "ggx")[d.distr], nonlinear=bool(d.nonlinear),
+                    reflectance=tuple(d.reflectance), eta=tuple(d.eta), k=tuple(d.k), specular_reflectance=tuple(d.specular_reflectance),
+                    specular_transmittance=tuple(d.specular_transmittance), int_ior=d.int_ior, ext_ior=d.ext_ior, alpha_u=d.alpha_u, alpha_v=d.alpha_v)
+
+    def integrator(self):
+        d = IntegratorDesc(); mv, ru, rc = C.c_int32(), C.c_int32(), C.c_uint32()
+        _chk(lib.amvpt_scene_get_integrator(self._h, C.byref(d), C.byref(mv), C.byref(ru), C.byref(rc)))
+        return dict(max_depth=d.max_depth, rr_depth=d.rr_depth, hide_emitters=bool(d.hide_emitters), spp_pass_lim=d.spp_pass_lim,
+                    sampler_seed=d.sampler_seed, sample_count=d.sample_count, is_mvpath=bool(mv.value), sa_reuse=bool(ru.value), reuse_count=rc.value)
 
     def bvh_validate(self):
         d, n = C.c_uint32(), C.c_uint32()

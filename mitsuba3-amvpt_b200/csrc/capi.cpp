@@ -129,6 +129,36 @@ int amvpt_scene_get_bsdf_tables(amvpt_scene *h, int bsdf, float *ext_t, float *s
         if (scalars) { scalars[0] = b.inv_eta_2; scalars[1] = b.spec_sampling_weight; scalars[2] = b.internal_reflectance; }
         return AMVPT_OK; });
 }
+int amvpt_scene_counts(amvpt_scene *h, uint32_t *n_meshes, uint32_t *n_bsdfs, uint32_t *n_emitters) {
+    return guard([&] { NEED(h); Scene &s = *h->s;
+        if (n_meshes) *n_meshes = (uint32_t) s.meshes.size(); if (n_bsdfs) *n_bsdfs = (uint32_t) s.bsdfs.size(); if (n_emitters) *n_emitters = (uint32_t) s.emitters.size();
+        return AMVPT_OK; });
+}
+int amvpt_scene_get_mesh(amvpt_scene *h, uint32_t index, uint32_t *n_vertices, uint32_t *n_faces, int32_t *bsdf, int32_t *has_normals, int32_t *flip_normals,
+                         int32_t *is_emitter, float *radiance3, float *positions, uint32_t *faces, float *normals) {
+    return guard([&] { NEED(h); NEED(index < h->s->meshes.size()); const HMesh &m = h->s->meshes[index];
+        if (n_vertices) *n_vertices = (uint32_t) (m.pos.size() / 3); if (n_faces) *n_faces = m.nfaces(); if (bsdf) *bsdf = m.bsdf;
+        if (has_normals) *has_normals = m.nrm.empty() ? 0 : 1; if (flip_normals) *flip_normals = m.flip_normals; if (is_emitter) *is_emitter = m.emitter >= 0;
+        if (radiance3 && m.emitter >= 0) memcpy(radiance3, h->s->emitters[m.emitter].radiance, 12);
+        if (positions) memcpy(positions, m.pos.data(), m.pos.size() * 4); if (faces) memcpy(faces, m.faces.data(), m.faces.size() * 4);
+        if (normals && !m.nrm.empty()) memcpy(normals, m.nrm.data(), m.nrm.size() * 4);
+        return AMVPT_OK; });
+}
+int amvpt_scene_get_bsdf(amvpt_scene *h, int bsdf, amvpt_bsdf_desc *d) {
+    return guard([&] { NEED(h); NEED(d); NEED(bsdf >= 0 && bsdf < (int) h->s->bsdfs.size()); const DBsdf &b = h->s->bsdfs[bsdf];
+        d->type = b.type; d->twosided = b.twosided; d->distr = b.distr; d->nonlinear = b.nonlinear;
+        for (int i = 0; i < 3; ++i) { d->reflectance[i] = b.reflectance[i]; d->eta[i] = b.eta[i]; d->k[i] = b.k[i];
+            d->specular_reflectance[i] = b.spec_refl[i]; d->specular_transmittance[i] = b.spec_trans[i]; }
+        d->int_ior = b.ior_eta; d->ext_ior = 1.f; d->alpha_u = b.alpha_u; d->alpha_v = b.alpha_v;
+        return AMVPT_OK; });
+}
+int amvpt_scene_get_integrator(amvpt_scene *h, amvpt_integrator_desc *d, int32_t *is_mvpath, int32_t *sa_reuse, uint32_t *reuse_count) {
+    return guard([&] { NEED(h); NEED(d); const IntegratorParams &ip = h->s->integrator;
+        d->max_depth = ip.max_depth; d->rr_depth = ip.rr_depth; d->hide_emitters = ip.hide_emitters; d->spp_pass_lim = ip.spp_pass_lim;
+        d->sampler_seed = h->s->sampler_seed; d->sample_count = h->s->sample_count;
+        if (is_mvpath) *is_mvpath = ip.is_mvpath; if (sa_reuse) *sa_reuse = ip.sa_reuse; if (reuse_count) *reuse_count = ip.reuse_count;
+        return AMVPT_OK; });
+}
 
 // ---- hot path
 int amvpt_render(amvpt_scene *h, const amvpt_render_desc *d, amvpt_render_stats *out) {

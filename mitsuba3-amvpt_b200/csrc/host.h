@@ -40,6 +40,7 @@ struct GridSensorParams {
     bool thinlens = false; int fov_axis = 0;   // 0 x, 1 y, 2 diagonal, 3 smaller, 4 larger
     uint32_t grid_x = 1, grid_y = 1, res_x = 0, res_y = 0; bool reverse_x = false, reverse_y = true;
     bool use_cone = false, cam_center = false;
+    bool single = false;   // a plain perspective / thinlens sensor (one view, to_world used as given)
     M4d to_world = m4d_identity();
     double fov = 45.0; bool has_focal_length = false; std::string focal_length = "50mm";
     float near_clip = 1e-2f, far_clip = 1e4f, focus_distance = 1e4f, aperture_radius = 0.f, cone_deg = 0.f, cam_dist = 0.1f;

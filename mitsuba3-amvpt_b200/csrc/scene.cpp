@@ -176,7 +176,8 @@ void Scene::set_sensor_grid(const GridSensorParams &g) {
     for (uint32_t i = 0; i < n; ++i) {
         float dt = (float) i / (float) (n - 1), lens_shift = 0.f;
         M4 itrafo = inv_t;
-        if (g.use_cone) {
+        if (g.single) {
+        } else if (g.use_cone) {
             float tan_off = tan_((dt - 0.5f) * (g.cone_deg * (AM_PI / 180.f)));
             float offset = g.focus_distance * tan_off;
             double shift = 0.5 * (double) tan_off / std::tan((fov_x * (3.14159265358979323846 / 180.0)) * 0.5);
@@ -188,7 +189,7 @@ void Scene::set_sensor_grid(const GridSensorParams &g) {
             itrafo.m[3][1] += off_y + g.cam_dir[1] * sc;
             itrafo.m[3][2] += off_z + g.cam_dir[2] * sc;
         }
-        M4 tw = m4_inverse(m4_transpose(itrafo));
+        M4 tw = g.single ? m4_from_d(g.to_world) : m4_inverse(m4_transpose(itrafo));
         M4 s2c = sample_to_camera((int) res_x, (int) res_y, (float) fov_x, g.near_clip, g.far_clip, lens_shift);
         DSensor c;
         for (int r = 0; r < 4; ++r) for (int k = 0; k < 4; ++k) c.s2c[4 * r + k] = s2c.m[r][k];

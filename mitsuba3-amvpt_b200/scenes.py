@@ -137,3 +137,140 @@ def build(desc, device=0, commit=True):
     if commit:
         s.commit(device)
     return s
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# Export of a description as a Mitsuba 3 scene (XML version 3.0.0 + OBJ / binary PLY meshes): the same file loads in the
+# reference (`mitsuba -m scalar_rgb scene.xml`) and in this library (`load_file`), which is how the synthetic workloads
+# are handed to an unmodified reference build, and how tests check the XML loader against the programmatic path.
+def _fmt(v):
+    return repr(float(v))
+
+
+def _rgb(name, v):
+    v = np.broadcast_to(np.asarray(v, np.float64), (3,))
+    return f'<rgb name="{name}" value="{_fmt(v[0])}, {_fmt(v[1])}, {_fmt(v[2])}"/>'
+
+
+def write_obj(path, positions, faces, normals=None):
+    with open(path, "w") as f:
+        f.write("# written by mitsuba3-amvpt_b200.scenes.write_obj\n")
+        for p in positions:
+            f.write("v %s %s %s\n" % tuple(repr(float(np.float32(c))) for c in p))
+        if normals is not None:
+            for n in normals:
+                f.write("vn %s %s %s\n" % tuple(repr(float(np.float32(c))) for c in n))
+            for a, b, c in np.asarray(faces, np.int64) + 1:
+                f.write(f"f {a}//{a} {b}//{b} {c}//{c}\n")
+        else:
+            for a, b, c in np.asarray(faces, np.int64) + 1:
+                f.write(f"f {a} {b} {c}\n")
+
+
+def write_ply(path, positions, faces, normals=None, binary=True):
+    positions = np.ascontiguousarray(positions, np.float32); faces = np.ascontiguousarray(faces, np.uint32)
+    props = ["x", "y", "z"] + (["nx", "ny", "nz"] if normals is not None else [])
+    hdr = ["ply", "format binary_little_endian 1.0" if binary else "format ascii 1.0", "comment written by mitsuba3-amvpt_b200",
+           f"element vertex {len(positions)}"] + [f"property float {p}" for p in props] + \
+          [f"element face {len(faces)}", "property list uchar int vertex_indices", "end_header"]
+    with open(path, "wb") as f:
+        f.write(("\n".join(hdr) + "\n").encode())
+        vtx = positions if normals is None else np.concatenate([positions, np.ascontiguousarray(normals, np.float32)], 1)
+        if binary:
+            f.write(np.ascontiguousarray(vtx, "<f4").tobytes())
+            rec = np.zeros(len(faces), dtype=np.dtype([("n", "u1"), ("i", "<i4", 3)])); rec["n"] = 3; rec["i"] = faces
+            f.write(rec.tobytes())
+        else:
+            for row in vtx:
+                f.write((" ".join(repr(float(c)) for c in row) + "\n").encode())
+            for a, b, c in faces:
+                f.write(f"3 {a} {b} {c}\n".encode())
+
+
+def _bsdf_xml(b, ident):
+    t = b["type"]; lines = []
+    if t == "diffuse":
+        lines.append(_rgb("reflectance", b.get("reflectance", 0.5)))
+    elif t in ("conductor", "roughconductor"):
+        lines += [_rgb("eta", b.get("eta", 0.0)), _rgb("k", b.get("k", 1.0))]
+        if "specular_reflectance" in b:
+            lines.append(_rgb("specular_reflectance", b["specular_reflectance"]))
+    elif t in ("dielectric", "roughdielectric"):
+        lines += [f'<float name="int_ior" value="{_fmt(b.get("int_ior", 1.5046))}"/>', f'<float name="ext_ior" value="{_fmt(b.get("ext_ior", 1.000277))}"/>']
+        for k in ("specular_reflectance", "specular_transmittance"):
+            if k in b:
+                lines.append(_rgb(k, b[k]))
+    elif t == "roughplastic":
+        lines += [f'<float name="int_ior" value="{_fmt(b.get("int_ior", 1.5046))}"/>', f'<float name="ext_ior" value="{_fmt(b.get("ext_ior", 1.000277))}"/>',
+                  _rgb("diffuse_reflectance", b.get("reflectance", 0.5)), f'<boolean name="nonlinear" value="{str(bool(b.get("nonlinear", False))).lower()}"/>']
+        if "specular_reflectance" in b:
+            lines.append(_rgb("specular_reflectance", b["specular_reflectance"]))
+    else:
+        raise KeyError(t)
+    if t.startswith("rough"):
+        lines.append(f'<string name="distribution" value="{b.get("distribution", "beckmann")}"/>')
+        if b.get("alpha_u") is not None and t != "roughplastic":
+            lines += [f'<float name="alpha_u" value="{_fmt(b["alpha_u"])}"/>', f'<float name="alpha_v" value="{_fmt(b["alpha_v"])}"/>']
+        else:
+            lines.append(f'<float name="alpha" value="{_fmt(b.get("alpha", 0.1))}"/>')
+    inner = f'<bsdf type="{t}"' + ("" if b.get("twosided") else f' id="{ident}"') + ">\n            " + "\n            ".join(lines) + "\n        </bsdf>"
+    if b.get("twosided"):
+        return f'<bsdf type="twosided" id="{ident}">\n        {inner}\n    </bsdf>'
+    return inner
+
+
+def export_xml(desc, directory, mesh_format="obj", integrator="mvpath", filename="scene.xml"):
+    """Writes `directory/scene.xml` + `directory/meshes/*`; returns the XML path."""
+    import os
+    os.makedirs(os.path.join(directory, "meshes"), exist_ok=True)
+    s, it = desc["sensor"], desc["integrator"]
+    gx, gy = s["grid_x"], s["grid_y"]
+    out = ['<scene version="3.0.0">', f'    <default name="spp" value="{it["sample_count"]}"/>',
+           f'    <integrator type="{integrator}">', f'        <integer name="max_depth" value="{it["max_depth"]}"/>',
+           f'        <integer name="rr_depth" value="{it["rr_depth"]}"/>']
+    if integrator == "mvpath":
+        out.append(f'        <integer name="spp_pass_lim" value="{it["spp_pass_lim"]}"/>')
+    out.append("    </integrator>")
+    out += ['    <wrap type="any" id="m_film">', '        <string name="wrap_class" value="film"/>', '        <string name="wrap_type" value="hdrfilm"/>',
+            f'        <integer name="width" value="{s["res_x"] // gx}"/>', f'        <integer name="height" value="{s["res_y"] // gy}"/>',
+            '        <string name="pixel_format" value="rgb"/>', '        <rfilter type="box"/>', "    </wrap>",
+            '    <wrap type="any" id="m_sampler">', '        <string name="wrap_class" value="sampler"/>', '        <string name="wrap_type" value="independent"/>',
+            '        <integer name="sample_count" value="$spp"/>', f'        <integer name="seed" value="{it["sampler_seed"]}"/>', "    </wrap>"]
+    m = np.asarray(s["to_world"], np.float64)
+    out += ['    <sensor type="grid">', f'        <integer name="grid_x" value="{gx}"/>', f'        <integer name="grid_y" value="{gy}"/>',
+            f'        <boolean name="reverse_x" value="{str(bool(s["reverse_x"])).lower()}"/>', f'        <boolean name="reverse_y" value="{str(bool(s["reverse_y"])).lower()}"/>']
+    if s.get("cone_deg") is not None:
+        out.append(f'        <float name="cone_deg" value="{_fmt(s["cone_deg"])}"/>')
+    else:
+        d = s["cam_dir"]
+        out += [f'        <vector name="cam_dir" value="{_fmt(d[0])}, {_fmt(d[1])}, {_fmt(d[2])}"/>', f'        <float name="cam_dist" value="{_fmt(s["cam_dist"])}"/>',
+                f'        <boolean name="cam_center" value="{str(bool(s["cam_center"])).lower()}"/>']
+    o = s.get("cam_off", (0, 0, 0))
+    out += [f'        <vector name="cam_off" value="{_fmt(o[0])}, {_fmt(o[1])}, {_fmt(o[2])}"/>', f'        <float name="focus_distance" value="{_fmt(s["focus_distance"])}"/>',
+            '        <transform name="to_world">', '            <matrix value="' + " ".join(repr(float(x)) for x in m.reshape(-1)) + '"/>', "        </transform>",
+            '        <wrap type="any">', '            <string name="wrap_class" value="sensor"/>',
+            f'            <string name="wrap_type" value="{"thinlens" if s.get("thinlens") else "perspective"}"/>',
+            f'            <float name="fov" value="{_fmt(s["fov"])}"/>', f'            <string name="fov_axis" value="{s["fov_axis"]}"/>',
+            f'            <float name="near_clip" value="{_fmt(s["near_clip"])}"/>', f'            <float name="far_clip" value="{_fmt(s["far_clip"])}"/>']
+    if s.get("thinlens"):
+        out.append(f'            <float name="aperture_radius" value="{_fmt(s["aperture_radius"])}"/>')
+    out += ['            <ref id="m_film"/>', '            <ref id="m_sampler"/>', "        </wrap>", '        <ref id="m_film"/>', '        <ref id="m_sampler"/>', "    </sensor>"]
+    for i, b in enumerate(desc["bsdfs"]):
+        out.append("    " + _bsdf_xml(b, f"bsdf{i}"))
+    for i, me in enumerate(desc["meshes"]):
+        fn = f"meshes/{i:02d}_{me['name']}.{mesh_format}"
+        (write_obj if mesh_format == "obj" else write_ply)(os.path.join(directory, fn), me["positions"], me["faces"], me["normals"])
+        out += [f'    <shape type="{mesh_format}">', f'        <string name="filename" value="{fn}"/>']
+        if me["normals"] is None:
+            out.append('        <boolean name="face_normals" value="true"/>')
+        if me["flip_normals"]:
+            out.append('        <boolean name="flip_normals" value="true"/>')
+        out.append(f'        <ref id="bsdf{me["bsdf"]}"/>')
+        if me["radiance"] is not None:
+            out += ['        <emitter type="area">', "            " + _rgb("radiance", me["radiance"]), "        </emitter>"]
+        out.append("    </shape>")
+    out.append("</scene>")
+    path = os.path.join(directory, filename)
+    with open(path, "w") as f:
+        f.write("\n".join(out) + "\n")
+    return path
