@@ -95,7 +95,7 @@ def _f32(a, shape=None):
 
 BSDF_TYPES = {"diffuse": 0, "conductor": 1, "dielectric": 2, "roughconductor": 3, "roughdielectric": 4, "roughplastic": 5}
 FOV_AXES = {"x": 0, "y": 1, "diagonal": 2, "smaller": 3, "larger": 4}
-SCHEDULERS = {"warp_batch": 0, "regenerate": 1, "wavefront": 2}
+SCHEDULERS = {"warp_batch": 0, "regenerate": 1, "stream": 2}
 
 
 def bsdf_desc(type, twosided=False, distribution="beckmann", nonlinear=False, reflectance=(.5, .5, .5), eta=(0., 0., 0.),
@@ -126,7 +126,7 @@ class Scene:
 
     def __del__(self):
         h, self._h = getattr(self, "_h", None), None
-        if h:
+        if h and lib is not None:          # `lib` is already gone when the interpreter shuts down
             lib.amvpt_scene_destroy(h)
 
     # ---- construction

@@ -100,7 +100,8 @@ void build_bvh(const Scene &s, float scene_scale, BvhOut &out) {
     kMaxLeaf = std::min(std::max(env_int("AMVPT_MAX_LEAF", 4), 1), 7); kCostTri = env_float("AMVPT_SAH_CT", 1.5f);
     Builder bl(prims);
     if (np) bl.build(0, np, 0);
-    if (np && bl.depth_of(0) > AM_STACK_SIZE - 2) AM_THROW("BVH depth %d exceeds the traversal stack", bl.depth_of(0));
+    out.depth = np ? (uint32_t) bl.depth_of(0) : 1u;
+    if (out.depth > AM_STACK_SIZE - 2) AM_THROW("BVH depth %u exceeds the traversal stack", out.depth);
 
     // triangles in leaf order
     out.tris.resize(3 * (size_t) np); out.prim_to_tri.resize(np);

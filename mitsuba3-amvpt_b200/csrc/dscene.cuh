@@ -92,18 +92,28 @@ AM_D bool moeller_trumbore(const Ray &ray, V3 p0, V3 p1, V3 p2, float *t_o, floa
     return true;
 }
 
-#define AM_SLAB_EPS 1e-6f
-// Slab test of one child box.  Conservative: (lo - o) is correctly rounded, so t0/t1 carry a relative
-// error of a few ulp; the interval is widened by AM_SLAB_EPS and the builder pads every box (bvh.cpp).
-// fminf/fmaxf drop the NaN of 0 * inf (origin on a slab plane of an axis-parallel ray).
-AM_D bool slab(float lox, float hix, float loy, float hiy, float loz, float hiz, V3 o, V3 id, float tbest, float *tnear) {
-    float t0x = (lox - o.x) * id.x, t1x = (hix - o.x) * id.x;
-    float t0y = (loy - o.y) * id.y, t1y = (hiy - o.y) * id.y;
-    float t0z = (loz - o.z) * id.z, t1z = (hiz - o.z) * id.z;
-    float tmin = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), 0.f));
-    float tmax = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fminf(fmaxf(t0z, t1z), tbest));
+#define AM_SLAB_EPS 2e-6f
+AM_D float fmax3(float a, float b, float c) { float r; asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c)); return r; }
+AM_D float fmin3(float a, float b, float c) { float r; asm("min.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c)); return r; }
+// Per-ray constants of the slab test: id = 1 / d (clamped to a large finite value for axis-parallel rays so that no
+// inf - inf arises) and ood = o * id, so that the plane distances are one FMA each: t = plane * id - ood.
+struct SlabRay { V3 id, ood; };
+AM_D float slab_inv(float d) { float a = fabs_(d) < 1e-20f ? copysign_(1e20f, d) : rcp(d); return a; }
+AM_D SlabRay slab_ray(V3 o, V3 d) {
+    SlabRay r; r.id = v3(slab_inv(d.x), slab_inv(d.y), slab_inv(d.z)); r.ood = v3(o.x * r.id.x, o.y * r.id.y, o.z * r.id.z); return r;
+}
+// Slab test of one child box.  It only prunes, so it is conservative rather than exact: plane * id - ood carries an
+// absolute error of about 2^-24 (|o| + |plane|) |id| (one rounding of ood, one of the FMA), i.e. 2^-24 * scene scale in
+// space, and a relative one of 2^-23; the builder pads every box by 2e-6 * scene scale + 1e-5 |coordinate| (bvh.cpp) and the
+// interval is widened by AM_SLAB_EPS.  min/max are the non-NaN-propagating PTX forms (FMNMX / FMNMX3).
+AM_D bool slab(float lox, float hix, float loy, float hiy, float loz, float hiz, const SlabRay &r, float tbest, float *tnear) {
+    float t0x = fmadd(lox, r.id.x, -r.ood.x), t1x = fmadd(hix, r.id.x, -r.ood.x);
+    float t0y = fmadd(loy, r.id.y, -r.ood.y), t1y = fmadd(hiy, r.id.y, -r.ood.y);
+    float t0z = fmadd(loz, r.id.z, -r.ood.z), t1z = fmadd(hiz, r.id.z, -r.ood.z);
+    float tmin = fmaxf(fmax3(fminf(t0x, t1x), fminf(t0y, t1y), fminf(t0z, t1z)), 0.f);
+    float tmax = fminf(fmin3(fmaxf(t0x, t1x), fmaxf(t0y, t1y), fmaxf(t0z, t1z)), tbest);
     *tnear = tmin;
-    return tmin * (1.f - AM_SLAB_EPS) <= tmax * (1.f + AM_SLAB_EPS);
+    return tmin <= tmax * (1.f + AM_SLAB_EPS);
 }
 
 // Closest hit (ANY = false) with the tie rule of ShapeKDTree::ray_intersect_naive
@@ -116,7 +126,7 @@ template <bool ANY> AM_D Hit intersect(const DScene &s, const Ray &ray, uint32_t
     Hit h; h.t = AM_INF; h.u = 0.f; h.v = 0.f; h.tri = AM_NO_HIT;
     uint32_t best_prim = 0;
     float best = ray.maxt;
-    V3 id = v3(rcp(ray.d.x), rcp(ray.d.y), rcp(ray.d.z));
+    SlabRay sr = slab_ray(ray.o, ray.d);
     int32_t stack[AM_STACK_SIZE]; int sp = 0;
     int32_t node = 0;
     stack[sp++] = AM_TRAVERSAL_DONE;
@@ -126,8 +136,8 @@ template <bool ANY> AM_D Hit intersect(const DScene &s, const Ray &ray, uint32_t
             float4 n0 = ldg4(np), n1 = ldg4(np + 1), n2 = ldg4(np + 2), n3 = ldg4(np + 3);
             if (n_nodes) (*n_nodes)++;
             float ta, tb;
-            bool ha = slab(n0.x, n0.y, n0.z, n0.w, n2.x, n2.y, ray.o, id, best, &ta);
-            bool hb = slab(n1.x, n1.y, n1.z, n1.w, n2.z, n2.w, ray.o, id, best, &tb);
+            bool ha = slab(n0.x, n0.y, n0.z, n0.w, n2.x, n2.y, sr, best, &ta);
+            bool hb = slab(n1.x, n1.y, n1.z, n1.w, n2.z, n2.w, sr, best, &tb);
             int32_t ca = __float_as_int(n3.x), cb = __float_as_int(n3.y);
             if (ha && hb) {
                 bool swap = tb < ta;
@@ -222,8 +232,10 @@ struct DirectionSample { V3 p, n, d; float pdf, dist; };
 // Scene::sample_emitter_direction (src/render/scene.cpp:295-346) + sample_emitter (:223-246) +
 // AreaLight::sample_direction (src/emitters/area.cpp:116-167) + Shape::sample_direction
 // (src/render/shape.cpp:360-377) + Mesh::sample_position (src/render/mesh.cpp:764-818) + visibility test.
-AM_D DirectionSample sample_emitter_direction(const DScene &s, const SI &ref, V2 sample, V3 *spec_out,
-                                              uint32_t *n_nodes, uint32_t *n_tris) {
+// DEFER = true leaves the visibility test to the caller: *shadow_out is the shadow ray to trace when the returned
+// ds.pdf != 0; an occluded sample then contributes nothing (the reference zeroes spec and ds.pdf, scene.cpp:333-342).
+template <bool DEFER> AM_D DirectionSample sample_emitter_direction(const DScene &s, const SI &ref, V2 sample, V3 *spec_out,
+                                              uint32_t *n_nodes, uint32_t *n_tris, Ray *shadow_out = nullptr) {
     DirectionSample ds; ds.p = v3(0.f); ds.n = v3(0.f); ds.d = v3(0.f); ds.pdf = 0.f; ds.dist = 0.f;
     *spec_out = v3(0.f);
     uint32_t ne = s.n_emitters; if (ne == 0) return ds;
@@ -265,7 +277,8 @@ AM_D DirectionSample sample_emitter_direction(const DScene &s, const SI &ref, V2
     spec = spec * emitter_weight;
     if (ds.pdf != 0.f) {
         Ray sr = spawn_ray_to(ref.p, ref.n, ds.p);
-        if (intersect<true>(s, sr, n_nodes, n_tris).tri != AM_NO_HIT) { spec = v3(0.f); ds.pdf = 0.f; }
+        if (DEFER) *shadow_out = sr;
+        else if (intersect<true>(s, sr, n_nodes, n_tris).tri != AM_NO_HIT) { spec = v3(0.f); ds.pdf = 0.f; }
     }
     *spec_out = spec;
     return ds;

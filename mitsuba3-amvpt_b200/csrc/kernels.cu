@@ -62,7 +62,7 @@ template <bool TAP, bool STATS> AM_D void path_bounce(const DScene &s, PathState
     V2 es; es.x = ps.rng.next_f32(); es.y = ps.rng.next_f32();
     DirectionSample ds; V3 em_weight = v3(0.f), wo = v3(0.f); ds.pdf = 0.f;
     if (active_em) {
-        ds = sample_emitter_direction(s, si, es, &em_weight, cn, ct);
+        ds = sample_emitter_direction<false>(s, si, es, &em_weight, cn, ct);
         if (STATS) st->shadow++;
         active_em = ds.pdf != 0.f;
         wo = si.to_local(ds.d);
@@ -199,7 +199,205 @@ render_pass_kernel(const DScene s, const RenderParams p) {
     if (STATS) flush_stats(st, p.counters);
 }
 
+// ------------------------------------------------------------------------------------------------
+// MODE 2, "stream": the same per-lane arithmetic as path_bounce, scheduled so that the BVH traversal -- two thirds of all
+// instructions -- runs with full warps.  Every lane is a small state machine
+//     IDLE  --(ticket: lane_setup)-->  TRACE  --(closest ray done)-->  SHADE  --> TRACE | IDLE
+// and the warp alternates between three converged phases:
+//   refill : when >= regen_min lanes are IDLE they splat their finished paths and take fresh tickets (ballot + popc prefix)
+//   trace  : ONE traversal loop serves shadow rays and closest-hit rays alike; a lane whose shadow ray finishes resolves
+//            its pending next-event contribution and continues straight into its next closest-hit ray; the loop is left
+//            when fewer than trace_min lanes are still traversing and somebody is waiting to be shaded or refilled
+//   shade  : lanes whose closest-hit ray finished run the vertex work of mvpath_single.h:143-275 *including* the BSDF
+//            sample and Russian roulette; the emitter sample's visibility ray is not traced here but queued in front of
+//            the next closest-hit ray, with (throughput, f * weight * mis) parked until it resolves (the fmadd into
+//            `result` then happens with the very operands the reference uses, before the next vertex adds its emission).
+// The traversal stack lives in shared memory (one column per thread), path state in registers.
+enum LanePhase : int { PH_IDLE = 0, PH_TRACE = 1, PH_SHADE = 2 };
+
+struct TravState {
+    Ray ray;                 // the ray in flight (maxt = original bound, used by the triangle test)
+    SlabRay sr; float best;  // pruning bound (closest t so far)
+    int32_t node; int sp;
+    Hit h; uint32_t best_prim;
+    bool any;                // shadow ray: first accepted triangle ends it
+};
+AM_D void trav_begin(TravState &tv, const Ray &ray, bool any) {
+    tv.ray = ray; tv.sr = slab_ray(ray.o, ray.d); tv.best = ray.maxt; tv.node = 0; tv.sp = 0;
+    tv.h.t = AM_INF; tv.h.u = 0.f; tv.h.v = 0.f; tv.h.tri = AM_NO_HIT; tv.best_prim = 0; tv.any = any;
+}
+
+// Vertex work for a finished closest-hit ray.  Returns true if a shadow ray has to be traced before the next closest ray
+// (then *shadow holds it and sT / sV the parked operands of `result = fmadd(sT, sV, result)`).
+template <bool STATS> AM_D bool shade_vertex(const DScene &s, PathState &ps, const Hit &h, Ray *shadow, V3 *sT, V3 *sV, StatCtx *st) {
+    if (STATS) { st->closest++; st->vertices++; }
+    const DMesh *mesh;
+    SI si = make_si(s, ps.ray, h, &mesh);
+    if (si.valid && mesh->emitter >= 0) {
+        V3 rel = si.p - ps.prev_p; float dist = norm(rel); V3 d = rel / dist;
+        float em_pdf = 0.f;
+        if (!ps.prev_delta) em_pdf = pdf_emitter_direction(s, mesh, d, si.sh_n, dist);
+        float mis_bsdf = mis_weight(ps.prev_bsdf_pdf, em_pdf);
+        V3 le = select3(si.wi.z > 0.f && ps.prev_bsdf_pdf > 0.f, ld3(s.emitters[mesh->emitter].radiance));
+        ps.result = fmadd(ps.throughput, le * mis_bsdf, ps.result);
+    }
+    bool active_next = (ps.depth + 1 < s.max_depth) && si.valid;
+    if (!active_next) { ps.valid_ray = ps.valid_ray || si.valid; ps.active = false; return false; }
+    const DBsdf &bsdf = s.bsdfs[mesh->bsdf];
+    bool active_em = (bsdf.flags & L_SMOOTH) != 0;
+    V2 es; es.x = ps.rng.next_f32(); es.y = ps.rng.next_f32();
+    DirectionSample ds; V3 em_weight = v3(0.f), wo = v3(0.f); ds.pdf = 0.f;
+    if (active_em) {
+        ds = sample_emitter_direction<true>(s, si, es, &em_weight, nullptr, nullptr, shadow);
+        if (STATS) st->shadow++;
+        active_em = ds.pdf != 0.f;
+        wo = si.to_local(ds.d);
+    }
+    float s1 = ps.rng.next_f32(); V2 s2; s2.x = ps.rng.next_f32(); s2.y = ps.rng.next_f32();
+    BsdfResult br = bsdf_eval_pdf_sample(bsdf, si.wi, wo, s1, s2);
+    if (active_em) {
+        float mis_em = mis_weight(ds.pdf, br.pdf);
+        *sT = ps.throughput; *sV = br.f * em_weight * mis_em;
+    }
+    ps.ray = spawn_ray(si.p, si.n, si.to_world(br.bs.wo));
+    ps.throughput = ps.throughput * br.weight;
+    ps.eta *= br.bs.eta;
+    ps.valid_ray = true;
+    ps.prev_p = si.p; ps.prev_bsdf_pdf = br.bs.pdf; ps.prev_delta = (br.bs.type & L_DELTA) != 0;
+    ps.depth += 1;
+    float tmax = hmax(ps.throughput);
+    float rr_prob = min_(tmax * sqr(ps.eta), .95f);
+    bool rr_active = ps.depth >= s.rr_depth, rr_continue = ps.rng.next_f32() < rr_prob;
+    if (rr_active) ps.throughput = ps.throughput * rcp(rr_prob);
+    ps.active = (!rr_active || rr_continue) && (tmax != 0.f);
+    return active_em;
+}
+
+template <bool STATS, int STK> __global__ void __launch_bounds__(128)
+render_stream_kernel(const DScene s, const RenderParams p) {
+    __shared__ int32_t stack[STK][128];
+    const unsigned lane_id = threadIdx.x & 31u, tid = threadIdx.x;
+    PathState ps; LaneSetup ls; TravState tv; ps.active = false;
+    V3 sT = v3(0.f), sV = v3(0.f); bool shadow_pending = false;      // parked next-event contribution
+    int phase = PH_IDLE; bool has_result = false, exhausted = false; // `exhausted` is warp-uniform
+    StatCtx st; st.closest = st.shadow = st.nodes = st.tris = st.vertices = 0;
+    tv.node = AM_TRAVERSAL_DONE; tv.sp = 0; tv.any = false; ls.pixel = 0; ls.in_film = false;
+    for (;;) {
+        // ---------------- refill
+        unsigned idle_mask = __ballot_sync(0xffffffffu, phase == PH_IDLE);
+        if (idle_mask == 0xffffffffu || (__popc(idle_mask) >= (int) p.regen_min && !exhausted) ||
+            (exhausted && __any_sync(0xffffffffu, has_result && phase == PH_IDLE))) {
+            if (phase == PH_IDLE) {
+                V3 L = ps.valid_ray ? ps.result : v3(0.f);
+                splat_aggregated(idle_mask, has_result && ls.in_film, ls.pixel, make_float4(L.x, L.y, L.z, 1.f), p.film, p.moments);
+                has_result = false;
+                bool got = false;
+                if (!exhausted) {
+                    unsigned long long base = 0; unsigned leader = __ffs(idle_mask) - 1;
+                    if (lane_id == leader) base = atomicAdd(p.counters + CTR_TICKET, (unsigned long long) __popc(idle_mask));
+                    base = __shfl_sync(idle_mask, base, leader);
+                    unsigned long long ticket = base + __popc(idle_mask & ((1u << lane_id) - 1u));
+                    uint32_t lane, px, py;
+                    if (ticket_to_lane(p, s, ticket, &lane, &px, &py)) {
+                        lane_setup(s, p.seed_value, lane, px, py, ps, ls);
+                        has_result = true; got = true;
+                        if (s.max_depth != 0) { phase = PH_TRACE; shadow_pending = false; trav_begin(tv, ps.ray, false); stack[0][tid] = AM_TRAVERSAL_DONE; tv.sp = 1; }
+                    }
+                }
+                (void) got;
+            }
+            // the ticket counter only grows: once any lane overshoots, every later ticket does
+            exhausted = exhausted || __any_sync(0xffffffffu, phase == PH_IDLE && !has_result);
+            if (__all_sync(0xffffffffu, phase == PH_IDLE && !has_result)) break;
+        }
+        // ---------------- trace
+        for (;;) {
+            bool tracing = phase == PH_TRACE;
+            unsigned tm = __ballot_sync(0xffffffffu, tracing);
+            if (tm == 0) break;
+            if (__popc(tm) < (int) p.trace_min) {
+                unsigned sm = __ballot_sync(0xffffffffu, phase == PH_SHADE);
+                unsigned im = ~(tm | sm);
+                if (sm != 0 || (!exhausted && __popc(im) >= (int) p.regen_min) || (exhausted && __any_sync(0xffffffffu, has_result && phase == PH_IDLE))) break;
+            }
+            if (tracing) {
+                // inner nodes until this lane holds a leaf (or its ray is done)
+                while (tv.node >= 0) {
+                    const float4 *np = s.nodes + 4 * (size_t) tv.node;
+                    float4 n0 = ldg4(np), n1 = ldg4(np + 1), n2 = ldg4(np + 2), n3 = ldg4(np + 3);
+                    if (STATS) st.nodes++;
+                    float ta, tb;
+                    bool ha = slab(n0.x, n0.y, n0.z, n0.w, n2.x, n2.y, tv.sr, tv.best, &ta);
+                    bool hb = slab(n1.x, n1.y, n1.z, n1.w, n2.z, n2.w, tv.sr, tv.best, &tb);
+                    int32_t ca = __float_as_int(n3.x), cb = __float_as_int(n3.y);
+                    if (ha && hb) {
+                        bool swap = tb < ta;
+                        stack[tv.sp++][tid] = swap ? ca : cb; tv.node = swap ? cb : ca;
+                    } else if (ha || hb) tv.node = ha ? ca : cb;
+                    else tv.node = stack[--tv.sp][tid];
+                }
+            }
+            if (tracing && tv.node != AM_TRAVERSAL_DONE) {
+                uint32_t code = ~(uint32_t) tv.node, first = code >> 3, count = code & 7u;
+                bool occluded = false;
+                for (uint32_t i = 0; i < count; ++i) {
+                    const float4 *tp = s.tris + 3 * (size_t) (first + i);
+                    float4 a = ldg4(tp), b = ldg4(tp + 1), c = ldg4(tp + 2);
+                    if (STATS) st.tris++;
+                    float t, u, v;
+                    if (moeller_trumbore(tv.ray, v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), v3(c.x, c.y, c.z), &t, &u, &v)) {
+                        if (tv.any) { occluded = true; break; }
+                        uint32_t prim = __float_as_uint(a.w);
+                        if (tv.h.tri == AM_NO_HIT || t < tv.h.t || (t == tv.h.t && prim > tv.best_prim)) {
+                            tv.h.t = t; tv.h.u = u; tv.h.v = v; tv.h.tri = first + i; tv.best_prim = prim; tv.best = t;
+                        }
+                    }
+                }
+                if (occluded) { tv.h.tri = 0; tv.node = AM_TRAVERSAL_DONE; }
+                else tv.node = stack[--tv.sp][tid];
+            }
+            if (tracing && tv.node == AM_TRAVERSAL_DONE) {
+                if (tv.any) {
+                    // shadow ray resolved: unoccluded -> the parked next-event contribution enters `result`
+                    if (tv.h.tri == AM_NO_HIT) ps.result = fmadd(sT, sV, ps.result);
+                    shadow_pending = false;
+                    if (ps.active) { trav_begin(tv, ps.ray, false); stack[0][tid] = AM_TRAVERSAL_DONE; tv.sp = 1; }
+                    else phase = PH_IDLE;
+                } else phase = PH_SHADE;
+            }
+        }
+        // ---------------- shade
+        if (phase == PH_SHADE) {
+            Ray shadow;
+            bool need_shadow = shade_vertex<STATS>(s, ps, tv.h, &shadow, &sT, &sV, &st);
+            if (need_shadow) { phase = PH_TRACE; shadow_pending = true; trav_begin(tv, shadow, true); stack[0][tid] = AM_TRAVERSAL_DONE; tv.sp = 1; }
+            else if (ps.active) { phase = PH_TRACE; trav_begin(tv, ps.ray, false); stack[0][tid] = AM_TRAVERSAL_DONE; tv.sp = 1; }
+            else phase = PH_IDLE;
+        }
+    }
+    (void) shadow_pending;
+    if (STATS) flush_stats(st, p.counters);
+}
+
+template <bool STATS, int STK> static void launch_stream(const DScene &s, const RenderParams &p, int sm_count, cudaStream_t stream) {
+    int ctas_per_sm = 0;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, render_stream_kernel<STATS, STK>, 128, 0);
+    if (ctas_per_sm < 1) ctas_per_sm = 1;
+    unsigned grid = (unsigned) (sm_count * ctas_per_sm);
+    unsigned long long ctas_needed = ((p.n_lanes + 31) / 32 + 3) / 4;
+    if (ctas_needed < grid) grid = (unsigned) (ctas_needed ? ctas_needed : 1);
+    render_stream_kernel<STATS, STK><<<grid, 128, 0, stream>>>(s, p);
+}
+
 void launch_render_pass(const DScene &s, const RenderParams &p, int mode, int sm_count, bool stats, cudaStream_t stream) {
+    if (mode == 2) {
+        // shared-memory traversal stack sized by the depth of the tree (depth + sentinel entries at most)
+        uint32_t need = p.bvh_depth + 2;
+        if (need <= 16) { if (stats) launch_stream<true, 16>(s, p, sm_count, stream); else launch_stream<false, 16>(s, p, sm_count, stream); }
+        else if (need <= 32) { if (stats) launch_stream<true, 32>(s, p, sm_count, stream); else launch_stream<false, 32>(s, p, sm_count, stream); }
+        else { if (stats) launch_stream<true, AM_STACK_SIZE>(s, p, sm_count, stream); else launch_stream<false, AM_STACK_SIZE>(s, p, sm_count, stream); }
+        return;
+    }
     // persistent grid: a whole number of CTAs per SM
     int ctas_per_sm = 0;
     const void *fn = mode == 0 ? (stats ? (const void *) render_pass_kernel<0, true> : (const void *) render_pass_kernel<0, false>)

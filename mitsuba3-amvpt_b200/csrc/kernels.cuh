@@ -11,7 +11,8 @@ struct TileDesc { uint32_t x0, y0, w, h; uint32_t spp, pad; unsigned long long l
 struct RenderParams {
     uint32_t seed_value;       // sampler seed + spp_per_pass * pass + render seed (mvpath.cpp:226-231, sampler.cpp:129)
     uint32_t spp_per_pass;     // lane stride of the reference's lane -> pixel map (mvpath.cpp:174-190)
-    uint32_t n_tiles, regen_min;   // regen_min: idle lanes per warp that trigger a refill (scheduler 1)
+    uint32_t n_tiles, regen_min;   // regen_min: idle lanes per warp that trigger a refill (schedulers 1, 2)
+    uint32_t trace_min, bvh_depth; // scheduler 2: the traversal loop is left when fewer lanes than this are traversing; tree depth (stack size)
     const TileDesc *tiles;
     unsigned long long n_lanes;
     float4 *film;              // RGBW, film_w * film_h
@@ -41,8 +42,5 @@ void launch_bsdf_tap(const DScene &s, int bsdf, const float *wi, const float *wo
 void launch_math_tap(int op, const float *in, uint32_t n, float *out, cudaStream_t st);
 void launch_sampler_tap(uint32_t seed_value, uint32_t lane, uint32_t n, float *out, cudaStream_t st);
 void launch_l2_flush(float *buf, size_t n, cudaStream_t st);
-
-// Wavefront scheduler (stage kernels + stream compaction)
-struct WavefrontBuffers;   // defined in kernels.cu
 
 } // namespace amvpt

@@ -72,6 +72,10 @@ void render(Scene &s, const RenderOptions &opt) {
 
     RenderParams p{};
     p.regen_min = opt.regen_min ? opt.regen_min : (getenv("AMVPT_REGEN_MIN") ? (uint32_t) atoi(getenv("AMVPT_REGEN_MIN")) : 8u); p.spp_per_pass = spp_per_pass; p.tiles = s.tiles_dev; p.film = s.film; p.moments = adaptive ? s.moments : nullptr; p.counters = s.counters;
+    p.trace_min = opt.trace_min ? opt.trace_min : (getenv("AMVPT_TRACE_MIN") ? (uint32_t) atoi(getenv("AMVPT_TRACE_MIN")) : 20u);
+    p.bvh_depth = s.bvh.depth;
+    int mode = opt.scheduler == SCHED_WARP_BATCH ? 0 : (opt.scheduler == SCHED_STREAM ? 2 : 1);
+    if (getenv("AMVPT_SCHEDULER")) mode = atoi(getenv("AMVPT_SCHEDULER"));
     auto launch = [&](std::vector<TileDesc> &tiles, uint32_t pass) {
         unsigned long long lanes = finish_tiles(tiles);
         if (!lanes) return;
@@ -79,7 +83,7 @@ void render(Scene &s, const RenderOptions &opt) {
         AM_CUDA(cudaMemsetAsync(s.counters + CTR_TICKET, 0, sizeof(unsigned long long), st));
         p.seed_value = s.sampler_seed + (spp_per_pass * pass + opt.seed);     // mvpath.cpp:226-231, sampler.cpp:129
         p.n_tiles = (uint32_t) tiles.size(); p.n_lanes = lanes;
-        launch_render_pass(s.d, p, opt.scheduler == SCHED_WARP_BATCH ? 0 : 1, s.sm_count, opt.stats, st);
+        launch_render_pass(s.d, p, mode, s.sm_count, opt.stats, st);
         AM_CUDA(cudaGetLastError());
         rs.paths += lanes; rs.launches++;
     };

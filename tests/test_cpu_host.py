@@ -137,7 +137,7 @@ if rank == 0:
             want[y0:y0 + h, x0:x0 + w] = float(view + 1)
     assert torch.equal(film[..., 0], want) and (want > 0).all()
 dist.destroy_process_group()
-print('ok', rank)
+sys.stdout.write('ok %d\n' % rank); sys.stdout.flush()
 """
 
 
@@ -146,4 +146,4 @@ def test_film_reduce_world_size_2_gloo(pkg, tmp_path):
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
                         "--master-port", "29591", str(script)], capture_output=True, text=True, timeout=240)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
-    assert "ok 0" in r.stdout and "ok 1" in r.stdout
+    assert r.stdout.count("ok") == 2 and "0" in r.stdout and "1" in r.stdout

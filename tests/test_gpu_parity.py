@@ -196,8 +196,10 @@ def test_schedulers_agree_and_accumulate(cbox):
     _, s, _ = cbox
     s.render(seed=1, spp=32, scheduler="warp_batch", develop=False); a = s.film_raw()
     s.render(seed=1, spp=32, scheduler="regenerate", develop=False); b = s.film_raw()
-    assert np.array_equal(a[..., 3], b[..., 3])
+    s.render(seed=1, spp=32, scheduler="stream", develop=False); c = s.film_raw()
+    assert np.array_equal(a[..., 3], b[..., 3]) and np.array_equal(a[..., 3], c[..., 3])
     assert np.abs(a - b).max() <= FILM_RTOL * a[..., :3].max()
+    assert np.abs(a - c).max() <= FILM_RTOL * a[..., :3].max()
     # spp rounding (mvpath.cpp:36-41): 40 spp with spp_pass_lim 16 -> 2 passes of 16
     s.render(seed=1, spp=40, develop=False)
     w = s.film_raw()[..., 3]     # a jittered position can round up into the next pixel (float32(px + 0.99999994) == px + 1), so a few
@@ -228,3 +230,52 @@ def test_max_depth_and_rr_edge_cases(scenes, ob, gpu):
         a = s.trace_lanes(0, 16, 0, 2 * 16 * 16 * 16, max_hits=4); b = o.trace_lanes(0, 16, 0, 2 * 16 * 16 * 16, max_hits=4, brute=True)
         assert_bits(a["radiance"], b["radiance"], f"max_depth={md} rr_depth={rr}")
         assert_bits(a["hit_prim"], b["hit_prim"], f"max_depth={md} rr_depth={rr} prims")
+
+
+@pytest.mark.parametrize("which", ["cbox", "hfield", "cbox_glass"])
+def test_stream_scheduler_bit_exact_per_sample(which, scenes, gpu):
+    """One sample per pixel (spp_pass_lim = 1): every film pixel with weight 1 holds exactly one path's radiance, so the
+    films of two schedulers can be compared bit for bit -- the stream scheduler (unified traversal loop, deferred shadow
+    rays) must produce the very radiance of the per-lane path loop that test_paths_bit_exact pins to the oracle.  The ray
+    and traversal counters must agree too (same rays, same BVH steps)."""
+    if which == "cbox":
+        desc = scenes.cornell_box(grid_x=4, grid_y=2, view_res=64, spp_pass_lim=1, sample_count=1)
+    elif which == "cbox_glass":
+        desc = scenes.cornell_box(grid_x=2, grid_y=1, view_res=96, spp_pass_lim=1, sample_count=1, max_depth=12, rr_depth=3,
+                                  bsdf_overrides={"box": dict(type="dielectric"), "white": dict(type="roughplastic", reflectance=(.7, .6, .5), alpha=0.2),
+                                                  "red": dict(type="conductor", eta=(0.2, 0.92, 1.1), k=(3.9, 2.45, 2.14))})
+    else:
+        desc = scenes.height_field(n=48, grid_x=2, grid_y=2, view_res=64, spp_pass_lim=1, sample_count=1)
+    s = scenes.build(desc, device=gpu)
+    films, stats = {}, {}
+    for sched in ("regenerate", "stream", "warp_batch"):
+        for seed in (0, 7):
+            s.render(seed=seed, spp=1, scheduler=sched, develop=False, stats=True)
+            films[sched, seed] = s.film_raw(); stats[sched, seed] = dict(s.last_stats)
+    for seed in (0, 7):
+        ref = films["regenerate", seed]; one = ref[..., 3] == 1
+        assert one.mean() > 0.99
+        for sched in ("stream", "warp_batch"):
+            f = films[sched, seed]
+            assert np.array_equal(f[..., 3], ref[..., 3])
+            assert_bits(f[one], ref[one], f"{which} seed {seed}: {sched} vs regenerate, single-sample pixels")
+            assert np.abs(f - ref).max() <= FILM_RTOL * max(ref[..., :3].max(), 1e-6)
+            for k in ("paths", "closest_rays", "shadow_rays", "bvh_nodes", "tri_tests", "path_vertices"):
+                assert stats[sched, seed][k] == stats["regenerate", seed][k], f"{which} {sched} {k}"
+        assert (ref[..., :3].sum(-1) > 0).mean() > 0.2
+
+
+def test_stream_scheduler_depth_edge_cases_and_thresholds(scenes, gpu):
+    import os
+    for md, rr in [(0, 5), (1, 5), (2, 1), (-1, 2)]:
+        desc = scenes.cornell_box(grid_x=2, grid_y=1, view_res=32, max_depth=md, rr_depth=rr, spp_pass_lim=1, sample_count=1)
+        s = scenes.build(desc, device=gpu)
+        s.render(seed=3, spp=1, scheduler="regenerate", develop=False); a = s.film_raw()
+        for tm, rm in ((20, 8), (1, 1), (32, 32), (33, 1), (8, 24)):       # any threshold setting is only a schedule
+            os.environ["AMVPT_TRACE_MIN"], os.environ["AMVPT_REGEN_MIN"] = str(tm), str(rm)
+            try:
+                s.render(seed=3, spp=1, scheduler="stream", develop=False); b = s.film_raw()
+            finally:
+                del os.environ["AMVPT_TRACE_MIN"], os.environ["AMVPT_REGEN_MIN"]
+            one = a[..., 3] == 1
+            assert np.array_equal(a[..., 3], b[..., 3]) and np.array_equal(bits(a[one]), bits(b[one])), f"max_depth={md} rr={rr} trace_min={tm} regen_min={rm}"
