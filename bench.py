@@ -29,6 +29,7 @@ WORKLOADS = {
     # name: (scene factory name, kwargs, spp)
     "cbox8x8": ("cornell_box", dict(grid_x=8, grid_y=8, view_res=512, cam_dist=400.0, max_depth=6, sample_count=256), 256),
     "cbox4": ("cornell_box", dict(grid_x=4, grid_y=1, view_res=256, cam_dist=200.0, max_depth=6, sample_count=64), 64),
+    "hfield4": ("height_field", dict(n=708, grid_x=2, grid_y=2, view_res=512, max_depth=8, sample_count=16), 16),      # profiling size of hfield16
     "hfield16": ("height_field", dict(n=708, grid_x=4, grid_y=4, view_res=1024, max_depth=8, sample_count=64), 64),
 }
 
@@ -80,12 +81,14 @@ def cpu_reference_run(desc, spp_per_pass, target_seconds, threads):
     import oracle_binding as ob
     o = ob.OracleScene(desc)
     w, h = o.film_size()
-    probe = max(1, h // 64)
-    _, sec, _ = o.render(seed=0, spp=spp_per_pass, brute=False, nthreads=threads, row_stride=probe * 8 if h >= probe * 8 else 1)
-    n_probe = len(range(0, h, probe * 8 if h >= probe * 8 else 1))
-    rate = n_probe * w * spp_per_pass / max(sec, 1e-9)
-    rows = int(max(1, min(h, rate * target_seconds / (w * spp_per_pass))))
-    stride = max(1, h // rows)
+
+    def odd(n):           # odd strides are coprime with the power-of-two tile heights, so every image region is sampled
+        n = max(1, int(n)); return n if n % 2 or n == 1 else n + 1
+    stride = odd(h / 48)
+    _, sec, _ = o.render(seed=0, spp=spp_per_pass, brute=False, nthreads=threads, row_stride=stride)
+    rate = len(range(0, h, stride)) * w * spp_per_pass / max(sec, 1e-9)
+    rows = max(1.0, min(float(h), rate * target_seconds / (w * spp_per_pass)))
+    stride = odd(h / rows) if rows < h else 1
     _, sec, _ = o.render(seed=0, spp=spp_per_pass, brute=False, nthreads=threads, row_stride=stride)
     rows = len(range(0, h, stride)); paths = rows * w * spp_per_pass
     return paths / sec / 1e6, (f"every {stride}th row of the {w}x{h} quilt ({rows} rows) x {spp_per_pass} spp = {paths} paths in {sec:.2f} s on {threads} threads "

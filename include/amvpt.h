@@ -55,7 +55,8 @@ typedef struct amvpt_integrator_desc {
  * plus the build-defined extensions (view sharding, scheduler choice, adaptive allocation). */
 typedef struct amvpt_render_desc {
     uint32_t seed, spp;
-    int32_t scheduler;             /* 0 warp batches, 1 persistent + path regeneration, 2 stream (unified traversal loop, ballot-compacted refill) */
+    int32_t scheduler;             /* 0 warp batches, 1 persistent + path regeneration, 2 stream (unified traversal loop, ballot-compacted refill),
+                                    * 3 wavefront (regen / trace / shade-per-BSDF-type stages over a pool of path slots) */
     int32_t collect_stats;         /* count rays / BVH nodes / triangle tests (slower) */
     uint32_t rank, world;          /* this process renders the view tiles v with v mod world == rank */
     int32_t adaptive; float adaptive_threshold; uint32_t adaptive_min_spp;

@@ -95,7 +95,7 @@ def _f32(a, shape=None):
 
 BSDF_TYPES = {"diffuse": 0, "conductor": 1, "dielectric": 2, "roughconductor": 3, "roughdielectric": 4, "roughplastic": 5}
 FOV_AXES = {"x": 0, "y": 1, "diagonal": 2, "smaller": 3, "larger": 4}
-SCHEDULERS = {"warp_batch": 0, "regenerate": 1, "stream": 2}
+SCHEDULERS = {"warp_batch": 0, "regenerate": 1, "stream": 2, "wavefront": 3}
 
 
 def bsdf_desc(type, twosided=False, distribution="beckmann", nonlinear=False, reflectance=(.5, .5, .5), eta=(0., 0., 0.),

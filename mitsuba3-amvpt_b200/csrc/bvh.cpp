@@ -112,7 +112,7 @@ void build_bvh(const Scene &s, float scene_scale, BvhOut &out) {
         out.prim_to_tri[prim] = i;
         for (int k = 0; k < 3; ++k) {
             const float *p = &m.pos[3 * m.faces[3 * f + k]];
-            uint32_t w = k == 0 ? prim : (k == 1 ? mi : 0u); float wf; memcpy(&wf, &w, 4);
+            uint32_t w = k == 0 ? prim : (k == 1 ? mi : (uint32_t) s.bsdfs[m.bsdf].type); float wf; memcpy(&wf, &w, 4);   // third word: BSDF plugin type (wavefront sort key)
             out.tris[3 * (size_t) i + k] = make_float4(p[0], p[1], p[2], wf);
             if (!m.nrm.empty()) { const float *n = &m.nrm[3 * m.faces[3 * f + k]]; out.tri_nrm[3 * (size_t) i + k] = make_float4(n[0], n[1], n[2], 0.f); }
         }

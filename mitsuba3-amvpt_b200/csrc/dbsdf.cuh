@@ -323,5 +323,21 @@ AM_HD BsdfResult bsdf_eval_pdf_sample(const DBsdf &b, V3 wi_, V3 wo_em, float s1
     if (b.twosided) r.bs.wo.z = mulsign(r.bs.wo.z, wi_.z);
     return r;
 }
+// Same with the plugin type known at compile time (the wavefront scheduler sorts vertices by BSDF type and runs one
+// specialised kernel per type); TYPE < 0 = dispatch at run time.
+template <int TYPE> AM_HD BsdfResult bsdf_eval_pdf_sample_t(const DBsdf &b, V3 wi_, V3 wo_em, float s1, V2 s2) {
+    if (TYPE < 0) return bsdf_eval_pdf_sample(b, wi_, wo_em, s1, s2);
+    BsdfResult r;
+    V3 wi = wi_, wo = wo_em;
+    if (b.twosided) { wo.z = mulsign(wo.z, wi.z); wi.z = fabs_(wi.z); }
+    if (TYPE == BSDF_DIFFUSE) diffuse_all(b, wi, wo, s2, r);
+    else if (TYPE == BSDF_CONDUCTOR) conductor_all(b, wi, r);
+    else if (TYPE == BSDF_DIELECTRIC) dielectric_all(b, wi, s1, r);
+    else if (TYPE == BSDF_ROUGHCONDUCTOR) roughconductor_all(b, wi, wo, s2, r);
+    else if (TYPE == BSDF_ROUGHDIELECTRIC) roughdielectric_all(b, wi, wo, s1, s2, r);
+    else roughplastic_all(b, wi, wo, s1, s2, r);
+    if (b.twosided) r.bs.wo.z = mulsign(r.bs.wo.z, wi_.z);
+    return r;
+}
 
 } // namespace amvpt

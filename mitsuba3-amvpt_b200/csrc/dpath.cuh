@@ -1,0 +1,153 @@
+// dpath.cuh -- per-lane device code of the AMVPT path loop shared by the schedulers (kernels.cu: persistent megakernels,
+// wavefront.cu: staged wavefront): path state, lane -> (pixel, sampler, camera ray), ticket map, the vertex work of
+// MVPT::sample_single with deferred next-event visibility, the traversal state machine, the aggregated film splat.
+#pragma once
+#include "kernels.cuh"
+#include "dscene.cuh"
+
+namespace amvpt {
+
+// ------------------------------------------------------------------------------------------------
+struct PathState {
+    Ray ray; V3 throughput, result, prev_p; float eta, prev_bsdf_pdf; uint32_t depth;
+    bool prev_delta, valid_ray, active;
+    Pcg32 rng;
+};
+struct TapCtx { uint32_t max_hits, n_iter; uint32_t *hit_prim; float *hit_t; };
+struct StatCtx { uint32_t closest, shadow, nodes, tris, vertices; };
+
+AM_D void path_init(PathState &ps, const Ray &ray) {
+    ps.ray = ray; ps.throughput = v3(1.f); ps.result = v3(0.f); ps.prev_p = v3(0.f); ps.eta = 1.f; ps.prev_bsdf_pdf = 1.f;
+    ps.depth = 0; ps.prev_delta = true; ps.valid_ray = false;   // no environment emitter on this path (mvpath_single.h:98)
+    ps.active = true;
+}
+
+// Lane -> (pixel, sampler, camera ray): MVPT::render lane map (src/integrators/mvpath.cpp:174-190) and
+// MVPT::render_sample (src/integrators/mvpath_single.h:50-75).
+struct LaneSetup { float spx, spy; uint32_t view, pixel; bool in_film; };
+AM_D void lane_setup(const DScene &s, uint32_t seed_value, uint32_t lane, uint32_t px, uint32_t py, PathState &ps, LaneSetup &ls) {
+    ps.rng = sampler_seed(seed_value, lane);
+    float sx = rcp((float) s.film_w), sy = rcp((float) s.film_h);
+    float jx = ps.rng.next_f32(), jy = ps.rng.next_f32();
+    ls.spx = (float) (int32_t) px + jx; ls.spy = (float) (int32_t) py + jy;
+    V2 adjusted = v2(fmadd(ls.spx, sx, -0.f * sx), fmadd(ls.spy, sy, -0.f * sy));
+    V2 aperture = v2(.5f, .5f);
+    if (s.thinlens) { aperture.x = ps.rng.next_f32(); aperture.y = ps.rng.next_f32(); }
+    Ray ray = sensor_sample_ray(s, adjusted, aperture, &ls.view);
+    path_init(ps, ray);
+    // ImageBlock::put, box filter (src/render/imageblock.cpp:210-233): pixel = floor(sample_pos)
+    uint32_t ux = (uint32_t) (int32_t) floorf(ls.spx), uy = (uint32_t) (int32_t) floorf(ls.spy);
+    ls.in_film = ux < s.film_w && uy < s.film_h;
+    ls.pixel = uy * s.film_w + ux;
+}
+
+// Map a launch-local lane ticket to (global lane, pixel) through the tile list.
+AM_D bool ticket_to_lane(const RenderParams &p, const DScene &s, unsigned long long ticket, uint32_t *lane, uint32_t *px, uint32_t *py) {
+    if (ticket >= p.n_lanes) return false;
+    uint32_t lo = 0, hi = p.n_tiles - 1;
+    while (lo < hi) {                       // last tile whose lane_begin <= ticket
+        uint32_t mid = (lo + hi + 1) >> 1;
+        if (p.tiles[mid].lane_begin <= ticket) lo = mid; else hi = mid - 1;
+    }
+    const TileDesc &t = p.tiles[lo];
+    unsigned long long r = ticket - t.lane_begin;
+    uint32_t k = (uint32_t) (r % t.spp), pl = (uint32_t) (r / t.spp);
+    uint32_t ty = pl / t.w, tx = pl - ty * t.w;
+    *px = t.x0 + tx; *py = t.y0 + ty;
+    *lane = (*py * s.film_w + *px) * p.spp_per_pass + k;
+    return true;
+}
+
+// Film splat with warp-aggregated atomics: lanes of the (converged) group `mask` that target the same pixel are
+// summed in lane order with shuffles and the lowest lane issues one 16-byte vector reduction (RED.128) per pixel.
+AM_D void splat_aggregated(unsigned mask, bool do_put, uint32_t pixel, float4 val, float4 *film, float2 *moments) {
+    unsigned lane = threadIdx.x & 31u;
+    uint32_t key = do_put ? pixel : 0xffffffffu;
+    unsigned peers = __match_any_sync(mask, key);
+    int iters = __reduce_max_sync(mask, do_put ? __popc(peers) : 0);
+    unsigned rem = peers;
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f); float m2 = 0.f;
+    float lum = 0.2126f * val.x + 0.7152f * val.y + 0.0722f * val.z, lum2 = lum * lum;
+    for (int i = 0; i < iters; ++i) {
+        int src = rem ? (__ffs(rem) - 1) : (int) lane;
+        float vx = __shfl_sync(mask, val.x, src), vy = __shfl_sync(mask, val.y, src),
+              vz = __shfl_sync(mask, val.z, src), vw = __shfl_sync(mask, val.w, src);
+        float vm = moments ? __shfl_sync(mask, lum2, src) : 0.f;
+        if (rem) { acc.x += vx; acc.y += vy; acc.z += vz; acc.w += vw; m2 += vm; }
+        rem &= rem - 1;
+    }
+    if (do_put && lane == (unsigned) (__ffs(peers) - 1)) {
+        atomicAdd(film + pixel, acc);
+        if (moments) atomicAdd(moments + pixel, make_float2(0.2126f * acc.x + 0.7152f * acc.y + 0.0722f * acc.z, m2));
+    }
+}
+
+AM_D void flush_stats(const StatCtx &st, unsigned long long *c) {
+    // warp-reduce, one atomic per counter per warp
+    uint32_t v[5] = { st.closest, st.shadow, st.nodes, st.tris, st.vertices };
+    #pragma unroll
+    for (int i = 0; i < 5; ++i) {
+        uint32_t x = __reduce_add_sync(0xffffffffu, v[i]);
+        if ((threadIdx.x & 31u) == 0 && x) atomicAdd(c + CTR_CLOSEST + i, (unsigned long long) x);
+    }
+}
+
+struct TravState {
+    Ray ray;                 // the ray in flight (maxt = original bound, used by the triangle test)
+    SlabRay sr; float best;  // pruning bound (closest t so far)
+    int32_t node; int sp;
+    Hit h; uint32_t best_prim;
+    bool any;                // shadow ray: first accepted triangle ends it
+};
+AM_D void trav_begin(TravState &tv, const Ray &ray, bool any) {
+    tv.ray = ray; tv.sr = slab_ray(ray.o, ray.d); tv.best = ray.maxt; tv.node = 0; tv.sp = 0;
+    tv.h.t = AM_INF; tv.h.u = 0.f; tv.h.v = 0.f; tv.h.tri = AM_NO_HIT; tv.best_prim = 0; tv.any = any;
+}
+
+// Vertex work for a finished closest-hit ray.  Returns true if a shadow ray has to be traced before the next closest ray
+// (then *shadow holds it and sT / sV the parked operands of `result = fmadd(sT, sV, result)`).
+template <bool STATS, int TYPE = -1> AM_D bool shade_vertex(const DScene &s, PathState &ps, const Hit &h, Ray *shadow, V3 *sT, V3 *sV, StatCtx *st) {
+    if (STATS) { st->closest++; st->vertices++; }
+    const DMesh *mesh;
+    SI si = make_si(s, ps.ray, h, &mesh);
+    if (si.valid && mesh->emitter >= 0) {
+        V3 rel = si.p - ps.prev_p; float dist = norm(rel); V3 d = rel / dist;
+        float em_pdf = 0.f;
+        if (!ps.prev_delta) em_pdf = pdf_emitter_direction(s, mesh, d, si.sh_n, dist);
+        float mis_bsdf = mis_weight(ps.prev_bsdf_pdf, em_pdf);
+        V3 le = select3(si.wi.z > 0.f && ps.prev_bsdf_pdf > 0.f, ld3(s.emitters[mesh->emitter].radiance));
+        ps.result = fmadd(ps.throughput, le * mis_bsdf, ps.result);
+    }
+    bool active_next = (ps.depth + 1 < s.max_depth) && si.valid;
+    if (!active_next) { ps.valid_ray = ps.valid_ray || si.valid; ps.active = false; return false; }
+    const DBsdf &bsdf = s.bsdfs[mesh->bsdf];
+    bool active_em = (bsdf.flags & L_SMOOTH) != 0;
+    V2 es; es.x = ps.rng.next_f32(); es.y = ps.rng.next_f32();
+    DirectionSample ds; V3 em_weight = v3(0.f), wo = v3(0.f); ds.pdf = 0.f;
+    if (active_em) {
+        ds = sample_emitter_direction<true>(s, si, es, &em_weight, nullptr, nullptr, shadow);
+        if (STATS) st->shadow++;
+        active_em = ds.pdf != 0.f;
+        wo = si.to_local(ds.d);
+    }
+    float s1 = ps.rng.next_f32(); V2 s2; s2.x = ps.rng.next_f32(); s2.y = ps.rng.next_f32();
+    BsdfResult br = bsdf_eval_pdf_sample_t<TYPE>(bsdf, si.wi, wo, s1, s2);
+    if (active_em) {
+        float mis_em = mis_weight(ds.pdf, br.pdf);
+        *sT = ps.throughput; *sV = br.f * em_weight * mis_em;
+    }
+    ps.ray = spawn_ray(si.p, si.n, si.to_world(br.bs.wo));
+    ps.throughput = ps.throughput * br.weight;
+    ps.eta *= br.bs.eta;
+    ps.valid_ray = true;
+    ps.prev_p = si.p; ps.prev_bsdf_pdf = br.bs.pdf; ps.prev_delta = (br.bs.type & L_DELTA) != 0;
+    ps.depth += 1;
+    float tmax = hmax(ps.throughput);
+    float rr_prob = min_(tmax * sqr(ps.eta), .95f);
+    bool rr_active = ps.depth >= s.rr_depth, rr_continue = ps.rng.next_f32() < rr_prob;
+    if (rr_active) ps.throughput = ps.throughput * rcp(rr_prob);
+    ps.active = (!rr_active || rr_continue) && (tmax != 0.f);
+    return active_em;
+}
+
+} // namespace amvpt

@@ -46,7 +46,7 @@ struct GridSensorParams {
     float near_clip = 1e-2f, far_clip = 1e4f, focus_distance = 1e4f, aperture_radius = 0.f, cone_deg = 0.f, cam_dist = 0.1f;
     float cam_dir[3] = { 1.f, 0.f, 0.f }, cam_off[3] = { 0.f, 0.f, 0.f };
 };
-enum SchedulerMode { SCHED_WARP_BATCH = 0, SCHED_REGENERATE = 1, SCHED_STREAM = 2 };
+enum SchedulerMode { SCHED_WARP_BATCH = 0, SCHED_REGENERATE = 1, SCHED_STREAM = 2, SCHED_WAVEFRONT = 3 };
 
 struct BvhOut { std::vector<float4> nodes, tris, tri_nrm; std::vector<uint32_t> prim_to_tri; uint32_t depth = 0; };
 struct RenderStats {
@@ -73,6 +73,7 @@ struct Scene {
     float4 *film = nullptr; float2 *moments = nullptr; float *rgb = nullptr;
     unsigned long long *counters = nullptr; TileDesc *tiles_dev = nullptr; float *view_stats_dev = nullptr;
     uint32_t tiles_cap = 0;
+    WfPool wf{}; uint32_t wf_type_mask = 0;     // wavefront scheduler pool (allocated on first use)
     uint32_t n_nodes = 0, n_tris = 0;
     volatile bool stop = false;
     RenderStats last;

@@ -28,6 +28,21 @@ struct LaneTaps {
 
 enum Counter { CTR_TICKET = 0, CTR_CLOSEST = 1, CTR_SHADOW = 2, CTR_NODES = 3, CTR_TRIS = 4, CTR_VERTICES = 5, CTR_COUNT = 8 };
 
+// Path-slot pool of the wavefront scheduler (wavefront.cu): structure of arrays, n_slots entries each.
+struct WfPool {
+    float4 *ro, *rd;        // next closest-hit ray: (o, maxt), (d, eta)
+    float4 *tp, *res, *pp;  // (throughput, prev_bsdf_pdf), (result, bits pixel), (prev_p, bits depth)
+    uint4 *rng;             // PCG32 state, inc
+    float4 *hit;            // (t, u, v, bits tri) of the last closest-hit ray
+    float4 *so, *sd, *sT, *sV;   // pending next-event shadow ray and the parked operands of result = fmadd(sT, sV, result)
+    uint32_t *flags;        // WF_* bits
+    uint32_t *queue;        // [6][n_slots] slot indices per BSDF plugin type
+    uint32_t *qcount;       // [6]
+    uint32_t *live;         // [64] live-slot counters, one per iteration (ring)
+    uint32_t n_slots;
+};
+uint32_t run_wavefront_pass(const DScene &s, const RenderParams &p, const WfPool &w, uint32_t type_mask, int sm_count, bool stats, cudaStream_t st);
+
 // host-callable launchers (kernels.cu)
 void launch_render_pass(const DScene &s, const RenderParams &p, int mode, int sm_count, bool stats, cudaStream_t st);
 void launch_trace_lanes(const DScene &s, uint32_t seed_value, uint32_t spp_per_pass, uint32_t lane_begin, uint32_t n, int trace,

@@ -74,7 +74,7 @@ void render(Scene &s, const RenderOptions &opt) {
     p.regen_min = opt.regen_min ? opt.regen_min : (getenv("AMVPT_REGEN_MIN") ? (uint32_t) atoi(getenv("AMVPT_REGEN_MIN")) : 8u); p.spp_per_pass = spp_per_pass; p.tiles = s.tiles_dev; p.film = s.film; p.moments = adaptive ? s.moments : nullptr; p.counters = s.counters;
     p.trace_min = opt.trace_min ? opt.trace_min : (getenv("AMVPT_TRACE_MIN") ? (uint32_t) atoi(getenv("AMVPT_TRACE_MIN")) : 20u);
     p.bvh_depth = s.bvh.depth;
-    int mode = opt.scheduler == SCHED_WARP_BATCH ? 0 : (opt.scheduler == SCHED_STREAM ? 2 : 1);
+    int mode = opt.scheduler == SCHED_WARP_BATCH ? 0 : (opt.scheduler == SCHED_STREAM ? 2 : (opt.scheduler == SCHED_WAVEFRONT ? 3 : 1));
     if (getenv("AMVPT_SCHEDULER")) mode = atoi(getenv("AMVPT_SCHEDULER"));
     auto launch = [&](std::vector<TileDesc> &tiles, uint32_t pass) {
         unsigned long long lanes = finish_tiles(tiles);
@@ -83,9 +83,26 @@ void render(Scene &s, const RenderOptions &opt) {
         AM_CUDA(cudaMemsetAsync(s.counters + CTR_TICKET, 0, sizeof(unsigned long long), st));
         p.seed_value = s.sampler_seed + (spp_per_pass * pass + opt.seed);     // mvpath.cpp:226-231, sampler.cpp:129
         p.n_tiles = (uint32_t) tiles.size(); p.n_lanes = lanes;
-        launch_render_pass(s.d, p, mode, s.sm_count, opt.stats, st);
-        AM_CUDA(cudaGetLastError());
-        rs.paths += lanes; rs.launches++;
+        if (mode == 3) {
+            if (!s.wf.n_slots) {
+                // pool size: a multiple of the CTA size; 2^20 slots (~190 MB of state) keep 148 SMs busy for several waves
+                uint32_t n = getenv("AMVPT_WF_POOL") ? (uint32_t) atoi(getenv("AMVPT_WF_POOL")) : (1u << 20);
+                n = std::max(128u, (n + 127u) / 128u * 128u);
+                WfPool &w = s.wf; w.n_slots = n;
+                float4 **f4s[] = { &w.ro, &w.rd, &w.tp, &w.res, &w.pp, &w.hit, &w.so, &w.sd, &w.sT, &w.sV };
+                for (float4 **a : f4s) *a = (float4 *) s.dalloc(sizeof(float4) * n);
+                w.rng = (uint4 *) s.dalloc(sizeof(uint4) * n); w.flags = (uint32_t *) s.dalloc(sizeof(uint32_t) * n);
+                w.queue = (uint32_t *) s.dalloc(sizeof(uint32_t) * 6 * (size_t) n); w.qcount = (uint32_t *) s.dalloc(sizeof(uint32_t) * 8);
+                w.live = (uint32_t *) s.dalloc(sizeof(uint32_t) * 64);
+                s.wf_type_mask = 0; for (auto &m : s.meshes) s.wf_type_mask |= 1u << s.bsdfs[m.bsdf].type;
+            }
+            rs.launches += run_wavefront_pass(s.d, p, s.wf, s.wf_type_mask, s.sm_count, opt.stats, st);
+        } else {
+            launch_render_pass(s.d, p, mode, s.sm_count, opt.stats, st);
+            AM_CUDA(cudaGetLastError());
+            rs.launches++;
+        }
+        rs.paths += lanes;
     };
 
     AM_CUDA(cudaEventRecord(e0, st));

@@ -243,7 +243,7 @@ void Scene::commit(int dev) {
     if (device >= 0 && device != dev) AM_THROW("commit: scene already lives on device %d", device);
     AM_CUDA(cudaSetDevice(dev)); device = dev;
     for (void *p : allocs) cudaFree(p);
-    allocs.clear();
+    allocs.clear(); wf = WfPool{};
     cudaDeviceProp prop; AM_CUDA(cudaGetDeviceProperties(&prop, dev)); sm_count = prop.multiProcessorCount;
     prepare_host();
     n_nodes = (uint32_t) (bvh.nodes.size() / 4); n_tris = (uint32_t) (bvh.tris.size() / 3);

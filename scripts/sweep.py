@@ -12,6 +12,7 @@ t0 = time.time(); s = scenes.build(desc, device=0); print(f"build {time.time() -
 
 
 def run(tag, sched):
+    global s
     s.render(seed=0, spp=spp, develop=False, scheduler=sched)
     best = 1e9
     for _ in range(3):
@@ -19,7 +20,13 @@ def run(tag, sched):
     print(f"{tag:44s} {s.last_stats['paths'] / best / 1e6:9.1f} Mpaths/s", flush=True)
 
 
-for sched in os.environ.get('SCHEDS', 'regenerate,stream').split(','):
+for sched in os.environ.get('SCHEDS', 'regenerate,wavefront,stream').split(','):
+    if sched == 'wavefront':
+        for pool in os.environ.get('POOLS', '524288,1048576,2097152').split(','):
+            os.environ['AMVPT_WF_POOL'] = pool
+            s2 = scenes.build(desc, device=0); s, s_old = s2, s
+            run(f"wavefront pool {pool}", 'wavefront'); s = s_old
+        continue
     if sched != 'stream':
         run(sched, sched); continue
     for tm in os.environ.get('TMS', '12,16,20,24,28').split(','):

@@ -197,9 +197,10 @@ def test_schedulers_agree_and_accumulate(cbox):
     s.render(seed=1, spp=32, scheduler="warp_batch", develop=False); a = s.film_raw()
     s.render(seed=1, spp=32, scheduler="regenerate", develop=False); b = s.film_raw()
     s.render(seed=1, spp=32, scheduler="stream", develop=False); c = s.film_raw()
-    assert np.array_equal(a[..., 3], b[..., 3]) and np.array_equal(a[..., 3], c[..., 3])
-    assert np.abs(a - b).max() <= FILM_RTOL * a[..., :3].max()
-    assert np.abs(a - c).max() <= FILM_RTOL * a[..., :3].max()
+    s.render(seed=1, spp=32, scheduler="wavefront", develop=False); d = s.film_raw()
+    assert np.array_equal(a[..., 3], b[..., 3]) and np.array_equal(a[..., 3], c[..., 3]) and np.array_equal(a[..., 3], d[..., 3])
+    for other in (b, c, d):
+        assert np.abs(a - other).max() <= FILM_RTOL * a[..., :3].max()
     # spp rounding (mvpath.cpp:36-41): 40 spp with spp_pass_lim 16 -> 2 passes of 16
     s.render(seed=1, spp=40, develop=False)
     w = s.film_raw()[..., 3]     # a jittered position can round up into the next pixel (float32(px + 0.99999994) == px + 1), so a few
@@ -248,14 +249,14 @@ def test_stream_scheduler_bit_exact_per_sample(which, scenes, gpu):
         desc = scenes.height_field(n=48, grid_x=2, grid_y=2, view_res=64, spp_pass_lim=1, sample_count=1)
     s = scenes.build(desc, device=gpu)
     films, stats = {}, {}
-    for sched in ("regenerate", "stream", "warp_batch"):
+    for sched in ("regenerate", "stream", "warp_batch", "wavefront"):
         for seed in (0, 7):
             s.render(seed=seed, spp=1, scheduler=sched, develop=False, stats=True)
             films[sched, seed] = s.film_raw(); stats[sched, seed] = dict(s.last_stats)
     for seed in (0, 7):
         ref = films["regenerate", seed]; one = ref[..., 3] == 1
         assert one.mean() > 0.99
-        for sched in ("stream", "warp_batch"):
+        for sched in ("stream", "warp_batch", "wavefront"):
             f = films[sched, seed]
             assert np.array_equal(f[..., 3], ref[..., 3])
             assert_bits(f[one], ref[one], f"{which} seed {seed}: {sched} vs regenerate, single-sample pixels")
@@ -279,3 +280,10 @@ def test_stream_scheduler_depth_edge_cases_and_thresholds(scenes, gpu):
                 del os.environ["AMVPT_TRACE_MIN"], os.environ["AMVPT_REGEN_MIN"]
             one = a[..., 3] == 1
             assert np.array_equal(a[..., 3], b[..., 3]) and np.array_equal(bits(a[one]), bits(b[one])), f"max_depth={md} rr={rr} trace_min={tm} regen_min={rm}"
+        for pool in (128, 4096, 1 << 20):                                   # wavefront pool smaller / larger than the pass
+            os.environ["AMVPT_WF_POOL"] = str(pool)
+            try:
+                s2 = scenes.build(desc, device=gpu); s2.render(seed=3, spp=1, scheduler="wavefront", develop=False); b = s2.film_raw()
+            finally:
+                del os.environ["AMVPT_WF_POOL"]
+            assert np.array_equal(a[..., 3], b[..., 3]) and np.array_equal(bits(a[one]), bits(b[one])), f"max_depth={md} rr={rr} wavefront pool={pool}"
