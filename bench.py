@@ -99,7 +99,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1); ap.add_argument("--steps", type=int, default=3); ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200"); ap.add_argument("--workload", default="cbox8x8")
-    ap.add_argument("--scheduler", default="regenerate"); ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--scheduler", default="auto"); ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
     scenes = None
@@ -207,26 +207,35 @@ def main():
         if dist is not None:
             dist.destroy_process_group()
         return
-    # ---- roofline of the dominant kernel (render_pass_kernel): algorithmic bytes per path from the kernel's own counters
+    # ---- roofline of the dominant kernel: algorithmic bytes from the kernels' own counters (one 16-spp pass with counters)
     s.render(seed=0, spp=16, develop=False, scheduler=args.scheduler, stats=True)
     cs = s.last_stats
     rays = cs["closest_rays"] + cs["shadow_rays"]
-    b_path = 16.0 + (cs["bvh_nodes"] * 64.0 + cs["tri_tests"] * 48.0) / cs["paths"]
-    s.render(seed=0, spp=spp, develop=False, scheduler=args.scheduler); ks = s.last_stats
-    per_launch_s = ks["seconds"] / ks["launches"]; paths_per_launch = ks["paths"] / ks["launches"]
+    bvh_bytes_per_path = (cs["bvh_nodes"] * 64.0 + cs["tri_tests"] * 48.0) / cs["paths"]
+    s.render(seed=0, spp=spp, develop=False, scheduler=args.scheduler, time_stages=True); ks = s.last_stats
     peak, peak_src = peaks()
+    sched = {0: "warp_batch", 1: "regenerate", 2: "stream", 3: "wavefront"}[ks["scheduler_used"]]
+    if sched == "wavefront":
+        # dominant kernel: wf_trace_kernel.  Per ray: BVH nodes (64 B) + triangles (48 B) + ray read (32 B) + hit / flag traffic (24 B)
+        kernel = "wf_trace_kernel"; b_path = bvh_bytes_per_path + 56.0 * rays / cs["paths"]
+        per_launch_s = ks["trace_seconds"] / max(ks["trace_launches"], 1); paths_per_launch = ks["paths"] / max(ks["trace_launches"], 1)
+        note = "staged wavefront: trace stage = %.0f%% of the device time; the BVH (~130 MB at 1M triangles) straddles L2, latency-bound traversal" % (100 * ks["trace_seconds"] / ks["seconds"])
+    else:
+        kernel = "render_pass_kernel"; b_path = 16.0 + bvh_bytes_per_path
+        per_launch_s = ks["seconds"] / ks["launches"]; paths_per_launch = ks["paths"] / ks["launches"]
+        note = "scene is cache-resident for the Cornell box: the megakernel is issue-bound (SIMD efficiency / issue slots), see profiles/"
     achieved = paths_per_launch * b_path / per_launch_s / 1e9
     out = {"metric": "Mpaths/s (all views, device-timed)", "value": value, "unit": "Mpaths/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
            "ms_per_step": dev_s / args.steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-           "config": {"workload": args.workload, **kw, "spp": spp, "scheduler": args.scheduler, "quilt": [W, H], "paths_per_step": n_paths,
+           "config": {"workload": args.workload, **kw, "spp": spp, "scheduler": args.scheduler, "scheduler_used": sched, "quilt": [W, H], "paths_per_step": n_paths,
                       "l2_policy": f"film {W * H * 16 / 1e6:.0f} MB > 126 MB L2 rewritten every pass" if W * H * 16 > 126e6 else "film smaller than L2 (small workload)",
                       "parallelism": f"views sharded over {world} rank(s), NCCL film reduce to rank 0" if world > 1 else "single GPU"},
            "clocks": clk, "gpu_launches": launches, "wall_s": wall,
            "e2e": {"value": e2e_val, "unit": "Mpaths/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
-                        "peak_source": peak_src, "kernel": "render_pass_kernel", "bytes_per_path": b_path, "rays_per_path": rays / cs["paths"],
+                        "peak_source": peak_src, "kernel": kernel, "bytes_per_path": b_path, "rays_per_path": rays / cs["paths"],
                         "nodes_per_ray": cs["bvh_nodes"] / max(rays, 1), "tris_per_ray": cs["tri_tests"] / max(rays, 1),
-                        "launch_ms": per_launch_s * 1e3, "note": "scene is cache-resident for the Cornell box: the kernel is issue-bound, see profiles/"}}
+                        "launch_ms": per_launch_s * 1e3, "note": note}}
     if world == 1 and not args.no_cpu_baseline:
         v, sample = cpu_reference_run(desc, 16, 15.0, threads)
         out["cpu_baseline"] = {"value": v, "unit": "Mpaths/s", "cores": threads, "kind": "port", "sample": sample}

@@ -56,8 +56,9 @@ typedef struct amvpt_integrator_desc {
 typedef struct amvpt_render_desc {
     uint32_t seed, spp;
     int32_t scheduler;             /* 0 warp batches, 1 persistent + path regeneration, 2 stream (unified traversal loop, ballot-compacted refill),
-                                    * 3 wavefront (regen / trace / shade-per-BSDF-type stages over a pool of path slots) */
-    int32_t collect_stats;         /* count rays / BVH nodes / triangle tests (slower) */
+                                    * 3 wavefront (regen / trace / shade-per-BSDF-type stages over a pool of path slots),
+                                    * 4 auto (default): wavefront for scenes with >= 3 BSDF plugin types or >= 32768 triangles, else 1 */
+    int32_t collect_stats;         /* bit 0: count rays / BVH nodes / triangle tests (slower); bit 1: time the wavefront trace stage */
     uint32_t rank, world;          /* this process renders the view tiles v with v mod world == rank */
     int32_t adaptive; float adaptive_threshold; uint32_t adaptive_min_spp;
     void *stream;                  /* cudaStream_t or NULL */
@@ -67,7 +68,9 @@ typedef struct amvpt_render_desc {
 typedef struct amvpt_render_stats {
     double seconds;                /* device time of the pass loop (CUDA events) */
     uint64_t paths, closest_rays, shadow_rays, bvh_nodes, tri_tests, path_vertices;
-    uint32_t passes, launches, spp_done, pad;
+    uint32_t passes, launches, spp_done, scheduler_used;   /* scheduler_used: what `auto` resolved to */
+    double trace_seconds;          /* wavefront only, if timed: device time of the trace stage kernels */
+    uint32_t trace_launches, pad;
 } amvpt_render_stats;
 
 const char *amvpt_last_error(void);

@@ -62,7 +62,8 @@ class RenderDesc(C.Structure):
 class RenderStats(C.Structure):
     _fields_ = [("seconds", C.c_double), ("paths", C.c_uint64), ("closest_rays", C.c_uint64), ("shadow_rays", C.c_uint64),
                 ("bvh_nodes", C.c_uint64), ("tri_tests", C.c_uint64), ("path_vertices", C.c_uint64),
-                ("passes", C.c_uint32), ("launches", C.c_uint32), ("spp_done", C.c_uint32), ("pad", C.c_uint32)]
+                ("passes", C.c_uint32), ("launches", C.c_uint32), ("spp_done", C.c_uint32), ("scheduler_used", C.c_uint32),
+                ("trace_seconds", C.c_double), ("trace_launches", C.c_uint32), ("pad", C.c_uint32)]
 
 
 lib.amvpt_last_error.restype = C.c_char_p
@@ -95,7 +96,7 @@ def _f32(a, shape=None):
 
 BSDF_TYPES = {"diffuse": 0, "conductor": 1, "dielectric": 2, "roughconductor": 3, "roughdielectric": 4, "roughplastic": 5}
 FOV_AXES = {"x": 0, "y": 1, "diagonal": 2, "smaller": 3, "larger": 4}
-SCHEDULERS = {"warp_batch": 0, "regenerate": 1, "stream": 2, "wavefront": 3}
+SCHEDULERS = {"warp_batch": 0, "regenerate": 1, "stream": 2, "wavefront": 3, "auto": 4}
 
 
 def bsdf_desc(type, twosided=False, distribution="beckmann", nonlinear=False, reflectance=(.5, .5, .5), eta=(0., 0., 0.),
@@ -222,15 +223,15 @@ class Scene:
         return d.value, n.value
 
     # ---- the hot path: Integrator.render(scene, sensor, seed, spp, develop, evaluate)
-    def render(self, seed=0, spp=0, develop=True, scheduler="regenerate", stats=False, rank=0, world=1, adaptive=False,
-               adaptive_threshold=0.0, adaptive_min_spp=16, stream=None, allreduce=None, clear=True):
+    def render(self, seed=0, spp=0, develop=True, scheduler="auto", stats=False, rank=0, world=1, adaptive=False,
+               adaptive_threshold=0.0, adaptive_min_spp=16, stream=None, allreduce=None, clear=True, time_stages=False):
         """Mirrors MVPathIntegrator::render (src/integrators/mvpath.cpp:7-278): accumulates `spp` samples per pixel into the
         film and returns the developed (H, W, 3) image if `develop` (else None).  `clear=False` keeps accumulating."""
         if clear:
             self.film_clear()
         d = RenderDesc()
         d.seed = seed; d.spp = spp; d.scheduler = SCHEDULERS[scheduler] if isinstance(scheduler, str) else scheduler
-        d.collect_stats = int(stats); d.rank = rank; d.world = world; d.adaptive = int(adaptive)
+        d.collect_stats = int(stats) | (2 if time_stages else 0); d.rank = rank; d.world = world; d.adaptive = int(adaptive)
         d.adaptive_threshold = adaptive_threshold; d.adaptive_min_spp = adaptive_min_spp; d.stream = stream
         if allreduce is not None:
             cb = ALLREDUCE_FN(lambda dev, n, user: allreduce(dev, n)); self._keep = [cb]; d.allreduce = cb

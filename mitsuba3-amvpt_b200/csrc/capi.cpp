@@ -163,13 +163,14 @@ int amvpt_scene_get_integrator(amvpt_scene *h, amvpt_integrator_desc *d, int32_t
 // ---- hot path
 int amvpt_render(amvpt_scene *h, const amvpt_render_desc *d, amvpt_render_stats *out) {
     return guard([&] { NEED(d); Scene &s = committed(h);
-        RenderOptions o; o.seed = d->seed; o.spp = d->spp; o.scheduler = d->scheduler; o.stats = d->collect_stats != 0;
+        RenderOptions o; o.seed = d->seed; o.spp = d->spp; o.scheduler = d->scheduler; o.stats = (d->collect_stats & 1) != 0; o.time_stages = (d->collect_stats & 2) != 0;
         o.shard.rank = d->rank; o.shard.world = d->world ? d->world : 1; o.stream = (cudaStream_t) d->stream;
         o.adaptive = d->adaptive != 0; o.adaptive_threshold = d->adaptive_threshold; o.adaptive_min_spp = d->adaptive_min_spp ? d->adaptive_min_spp : 16;
         o.allreduce = d->allreduce; o.allreduce_user = d->allreduce_user;
         render(s, o);
         if (out) { const RenderStats &r = s.last; out->seconds = r.seconds; out->paths = r.paths; out->closest_rays = r.closest_rays; out->shadow_rays = r.shadow_rays;
-            out->bvh_nodes = r.nodes; out->tri_tests = r.tris; out->path_vertices = r.vertices; out->passes = r.passes; out->launches = r.launches; out->spp_done = r.spp_done; out->pad = 0; }
+            out->bvh_nodes = r.nodes; out->tri_tests = r.tris; out->path_vertices = r.vertices; out->passes = r.passes; out->launches = r.launches; out->spp_done = r.spp_done; out->scheduler_used = r.scheduler_used;
+            out->trace_seconds = r.trace_seconds; out->trace_launches = r.trace_launches; out->pad = 0; }
         return AMVPT_OK; });
 }
 int amvpt_shard_tiles(amvpt_scene *h, uint32_t rank, uint32_t world, uint32_t *out5, uint32_t cap) {

@@ -46,13 +46,14 @@ struct GridSensorParams {
     float near_clip = 1e-2f, far_clip = 1e4f, focus_distance = 1e4f, aperture_radius = 0.f, cone_deg = 0.f, cam_dist = 0.1f;
     float cam_dir[3] = { 1.f, 0.f, 0.f }, cam_off[3] = { 0.f, 0.f, 0.f };
 };
-enum SchedulerMode { SCHED_WARP_BATCH = 0, SCHED_REGENERATE = 1, SCHED_STREAM = 2, SCHED_WAVEFRONT = 3 };
+enum SchedulerMode { SCHED_WARP_BATCH = 0, SCHED_REGENERATE = 1, SCHED_STREAM = 2, SCHED_WAVEFRONT = 3, SCHED_AUTO = 4 };
 
 struct BvhOut { std::vector<float4> nodes, tris, tri_nrm; std::vector<uint32_t> prim_to_tri; uint32_t depth = 0; };
 struct RenderStats {
     double seconds = 0.0;            // device time of the pass loop (CUDA events)
     unsigned long long paths = 0, closest_rays = 0, shadow_rays = 0, nodes = 0, tris = 0, vertices = 0;
     uint32_t passes = 0, launches = 0, spp_done = 0;
+    double trace_seconds = 0.0; uint32_t trace_launches = 0, scheduler_used = 0;   // wavefront: device time of the trace stage (if timed)
 };
 struct Shard { uint32_t rank = 0, world = 1; };   // view tiles owned: {v : v mod world == rank}
 
@@ -107,7 +108,7 @@ void build_bvh(const Scene &s, float scene_scale, BvhOut &out);
 
 // render.cpp -- MVPathIntegrator::render() (src/integrators/mvpath.cpp:7-278), wavefront branch
 struct RenderOptions {
-    uint32_t seed = 0, spp = 0; int scheduler = SCHED_REGENERATE; bool stats = false; uint32_t regen_min = 0, trace_min = 0;
+    uint32_t seed = 0, spp = 0; int scheduler = SCHED_AUTO; bool stats = false, time_stages = false; uint32_t regen_min = 0, trace_min = 0;
     Shard shard; cudaStream_t stream = nullptr;
     // adaptive allocator (build-defined): 0 = fixed spp; otherwise spp is the mean budget per pixel
     bool adaptive = false; float adaptive_threshold = 0.f; uint32_t adaptive_min_spp = 16;

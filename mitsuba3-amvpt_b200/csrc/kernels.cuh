@@ -41,7 +41,8 @@ struct WfPool {
     uint32_t *live;         // [64] live-slot counters, one per iteration (ring)
     uint32_t n_slots;
 };
-uint32_t run_wavefront_pass(const DScene &s, const RenderParams &p, const WfPool &w, uint32_t type_mask, int sm_count, bool stats, cudaStream_t st);
+uint32_t run_wavefront_pass(const DScene &s, const RenderParams &p, const WfPool &w, uint32_t type_mask, int sm_count, bool stats, cudaStream_t st,
+                            double *trace_seconds, uint32_t *trace_launches);
 
 // host-callable launchers (kernels.cu)
 void launch_render_pass(const DScene &s, const RenderParams &p, int mode, int sm_count, bool stats, cudaStream_t st);

@@ -75,7 +75,16 @@ void render(Scene &s, const RenderOptions &opt) {
     p.trace_min = opt.trace_min ? opt.trace_min : (getenv("AMVPT_TRACE_MIN") ? (uint32_t) atoi(getenv("AMVPT_TRACE_MIN")) : 20u);
     p.bvh_depth = s.bvh.depth;
     int mode = opt.scheduler == SCHED_WARP_BATCH ? 0 : (opt.scheduler == SCHED_STREAM ? 2 : (opt.scheduler == SCHED_WAVEFRONT ? 3 : 1));
+    if (opt.scheduler == SCHED_AUTO) {
+        // Measured on B200 (profiles/): the persistent megakernel wins while its working code stays small and rays are short
+        // (Cornell box: 1.7 vs 0.8-1.1 Gpaths/s); with several BSDF plugin types or a deep tree its warps stall on
+        // instruction fetch and run a handful of lanes, and the wavefront is about twice as fast (1M triangles: 222 vs 116).
+        uint32_t types = 0, n_types = 0; for (auto &m : s.meshes) types |= 1u << s.bsdfs[m.bsdf].type;
+        for (uint32_t t = types; t; t &= t - 1) n_types++;
+        mode = (n_types >= 3 || s.n_tris >= 32768u) ? 3 : 1;
+    }
     if (getenv("AMVPT_SCHEDULER")) mode = atoi(getenv("AMVPT_SCHEDULER"));
+    rs.scheduler_used = (uint32_t) mode;
     auto launch = [&](std::vector<TileDesc> &tiles, uint32_t pass) {
         unsigned long long lanes = finish_tiles(tiles);
         if (!lanes) return;
@@ -85,8 +94,8 @@ void render(Scene &s, const RenderOptions &opt) {
         p.n_tiles = (uint32_t) tiles.size(); p.n_lanes = lanes;
         if (mode == 3) {
             if (!s.wf.n_slots) {
-                // pool size: a multiple of the CTA size; 2^20 slots (~190 MB of state) keep 148 SMs busy for several waves
-                uint32_t n = getenv("AMVPT_WF_POOL") ? (uint32_t) atoi(getenv("AMVPT_WF_POOL")) : (1u << 20);
+                // pool size: a multiple of the CTA size; 2^21 slots (~420 MB of state and queues) = several resident waves of 148 SMs
+                uint32_t n = getenv("AMVPT_WF_POOL") ? (uint32_t) atoi(getenv("AMVPT_WF_POOL")) : (1u << 21);
                 n = std::max(128u, (n + 127u) / 128u * 128u);
                 WfPool &w = s.wf; w.n_slots = n;
                 float4 **f4s[] = { &w.ro, &w.rd, &w.tp, &w.res, &w.pp, &w.hit, &w.so, &w.sd, &w.sT, &w.sV };
@@ -96,7 +105,7 @@ void render(Scene &s, const RenderOptions &opt) {
                 w.live = (uint32_t *) s.dalloc(sizeof(uint32_t) * 64);
                 s.wf_type_mask = 0; for (auto &m : s.meshes) s.wf_type_mask |= 1u << s.bsdfs[m.bsdf].type;
             }
-            rs.launches += run_wavefront_pass(s.d, p, s.wf, s.wf_type_mask, s.sm_count, opt.stats, st);
+            rs.launches += run_wavefront_pass(s.d, p, s.wf, s.wf_type_mask, s.sm_count, opt.stats, st, opt.time_stages ? &rs.trace_seconds : nullptr, &rs.trace_launches);
         } else {
             launch_render_pass(s.d, p, mode, s.sm_count, opt.stats, st);
             AM_CUDA(cudaGetLastError());

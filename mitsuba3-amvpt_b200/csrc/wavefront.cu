@@ -12,6 +12,9 @@
 // the megakernels, so the results are the same bit for bit; only the order of the film atomics differs.
 #include "dpath.cuh"
 #include "host.h"
+#include <algorithm>
+#include <cstdlib>
+#include <vector>
 
 namespace amvpt {
 
@@ -52,47 +55,116 @@ wf_regen_kernel(const DScene s, const RenderParams p, const WfPool w, uint32_t i
     unsigned live = __ballot_sync(0xffffffffu, (f & (WF_ALIVE | WF_SHADOW | WF_HAS_RESULT)) != 0);
     if (lane_id == 0 && live) atomicAdd(w.live + (iter & 63u), (uint32_t) __popc(live));
     if (i == 0) {
-        for (int k = 0; k < WF_N_TYPES; ++k) w.qcount[k] = 0;
+        for (int k = 0; k <= WF_N_TYPES; ++k) w.qcount[k] = 0;      // type queues + the ray-task counter
         w.live[(iter + 32u) & 63u] = 0;
     }
 }
 
+// Ray tasks of one iteration: task 2 i = the pending shadow ray of slot i, task 2 i + 1 = its closest-hit ray (a task exists
+// if the slot's flag says so).  Persistent warps pull tasks from one counter: whenever at least fetch_min lanes of a warp have
+// finished their ray they take the next task ids together (one atomic per warp, ballot + popc prefix), so the traversal loop
+// keeps running with nearly full warps although rays differ widely in length (Aila & Laine's dynamic fetch).
 template <bool STATS> __global__ void __launch_bounds__(128)
-wf_trace_kernel(const DScene s, const RenderParams p, const WfPool w) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+wf_trace_kernel(const DScene s, const RenderParams p, const WfPool w, uint32_t fetch_min, uint32_t leaf_min) {
     const unsigned lane_id = threadIdx.x & 31u;
-    uint32_t f = w.flags[i], f0 = f, key = 0xffu;
+    const uint32_t n_tasks = 2u * w.n_slots;
     StatCtx st; st.closest = st.shadow = st.nodes = st.tris = st.vertices = 0;
-    uint32_t *cn = STATS ? &st.nodes : nullptr, *ct = STATS ? &st.tris : nullptr;
-    if (f & WF_SHADOW) {
-        float4 o = w.so[i], d = w.sd[i];
-        Ray r; r.o = xyz(o); r.d = xyz(d); r.maxt = o.w;
-        if (intersect<true>(s, r, cn, ct).tri == AM_NO_HIT) {
-            // unoccluded: the parked next-event contribution enters `result` (mvpath_single.h:199)
-            float4 res = w.res[i]; V3 nr = fmadd(xyz(w.sT[i]), xyz(w.sV[i]), xyz(res));
-            w.res[i] = f4(nr, res.w);
+    int32_t stack[AM_STACK_SIZE];
+    TravState tv; tv.node = AM_TRAVERSAL_DONE; tv.sp = 0; tv.any = false;
+    uint32_t slot = 0; bool busy = false, exhausted = false;
+    for (;;) {
+        unsigned idle = __ballot_sync(0xffffffffu, !busy);
+        if (idle == 0xffffffffu || (!exhausted && __popc(idle) >= (int) fetch_min)) {
+            if (exhausted) break;                       // every lane idle and no task left
+            uint32_t t = n_tasks;
+            if (!busy) {
+                uint32_t base = 0; unsigned leader = __ffs(idle) - 1;
+                if (lane_id == leader) base = atomicAdd(w.qcount + WF_N_TYPES, (uint32_t) __popc(idle));
+                base = __shfl_sync(idle, base, leader);
+                t = base + __popc(idle & ((1u << lane_id) - 1u));
+                if (t < n_tasks) {
+                    slot = t >> 1; uint32_t f = w.flags[slot];
+                    if ((t & 1u) == 0) {
+                        if (f & WF_SHADOW) { float4 o = w.so[slot], d = w.sd[slot]; Ray r; r.o = xyz(o); r.d = xyz(d); r.maxt = o.w; trav_begin(tv, r, true); busy = true; }
+                    } else if (f & WF_ALIVE) { float4 o = w.ro[slot], d = w.rd[slot]; Ray r; r.o = xyz(o); r.d = xyz(d); r.maxt = o.w; trav_begin(tv, r, false); busy = true; }
+                    if (busy) { stack[0] = AM_TRAVERSAL_DONE; tv.sp = 1; }
+                }
+            }
+            exhausted = __any_sync(0xffffffffu, !busy && t >= n_tasks && (idle >> lane_id & 1u));
+            continue;
         }
-        f &= ~WF_SHADOW;
-    }
-    if (f & WF_ALIVE) {
-        float4 o = w.ro[i], d = w.rd[i];
-        Ray r; r.o = xyz(o); r.d = xyz(d); r.maxt = o.w;
-        Hit h = intersect<false>(s, r, cn, ct);
-        if (h.tri == AM_NO_HIT) {
-            f &= ~WF_ALIVE;                 // no environment emitter: the path ends, valid_ray stays as it is
-            if (STATS) { st.closest++; st.vertices++; }
-        } else {
-            w.hit[i] = make_float4(h.t, h.u, h.v, __uint_as_float(h.tri));
-            key = __float_as_uint(ldg4(s.tris + 3 * (size_t) h.tri + 2).w) & 7u;
+        uint32_t key = 0xffu;
+        // descend: lanes holding an inner node step through the tree together; the loop is left as soon as at least leaf_min
+        // lanes hold a leaf (or a finished ray), so that no lane waits long with a leaf while a few others wander through
+        // inner nodes, and the few that are interrupted resume after the leaf phase
+        {
+            const unsigned bm = __ballot_sync(0xffffffffu, busy);
+            for (;;) {
+                const bool desc = busy && tv.node >= 0;
+                const unsigned dm = __ballot_sync(0xffffffffu, desc);
+                if (dm == 0 || __popc(bm & ~dm) >= (int) leaf_min) break;
+                if (desc) {
+                    const float4 *np = s.nodes + 4 * (size_t) tv.node;
+                    float4 n0 = ldg4(np), n1 = ldg4(np + 1), n2 = ldg4(np + 2), n3 = ldg4(np + 3);
+                    if (STATS) st.nodes++;
+                    float ta, tb;
+                    bool ha = slab(n0.x, n0.y, n0.z, n0.w, n2.x, n2.y, tv.sr, tv.best, &ta);
+                    bool hb = slab(n1.x, n1.y, n1.z, n1.w, n2.z, n2.w, tv.sr, tv.best, &tb);
+                    int32_t ca = __float_as_int(n3.x), cb = __float_as_int(n3.y);
+                    if (ha && hb) { bool swap = tb < ta; stack[tv.sp++] = swap ? ca : cb; tv.node = swap ? cb : ca; }
+                    else if (ha || hb) tv.node = ha ? ca : cb;
+                    else tv.node = stack[--tv.sp];
+                }
+            }
+        }
+        if (busy && tv.node < 0) {
+            if (tv.node != AM_TRAVERSAL_DONE) {
+                uint32_t code = ~(uint32_t) tv.node, first = code >> 3, count = code & 7u;
+                bool occluded = false;
+                for (uint32_t k = 0; k < count; ++k) {
+                    const float4 *tp = s.tris + 3 * (size_t) (first + k);
+                    float4 a = ldg4(tp), b = ldg4(tp + 1), c = ldg4(tp + 2);
+                    if (STATS) st.tris++;
+                    float t, u, v;
+                    if (moeller_trumbore(tv.ray, v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), v3(c.x, c.y, c.z), &t, &u, &v)) {
+                        if (tv.any) { occluded = true; break; }
+                        uint32_t prim = __float_as_uint(a.w);
+                        if (tv.h.tri == AM_NO_HIT || t < tv.h.t || (t == tv.h.t && prim > tv.best_prim)) {
+                            tv.h.t = t; tv.h.u = u; tv.h.v = v; tv.h.tri = first + k; tv.best_prim = prim; tv.best = t;
+                        }
+                    }
+                }
+                if (occluded) { tv.h.tri = 0; tv.node = AM_TRAVERSAL_DONE; }
+                else tv.node = stack[--tv.sp];
+            }
+            if (tv.node == AM_TRAVERSAL_DONE) {
+                busy = false;
+                if (tv.any) {
+                    if (tv.h.tri == AM_NO_HIT) {
+                        // unoccluded: the parked next-event contribution enters `result` (mvpath_single.h:199)
+                        float4 res = w.res[slot]; V3 nr = fmadd(xyz(w.sT[slot]), xyz(w.sV[slot]), xyz(res));
+                        w.res[slot] = f4(nr, res.w);
+                    }
+                    atomicAnd(w.flags + slot, ~WF_SHADOW);
+                } else if (tv.h.tri == AM_NO_HIT) {
+                    atomicAnd(w.flags + slot, ~WF_ALIVE);      // no environment emitter: the path ends, valid_ray stays as it is
+                    if (STATS) { st.closest++; st.vertices++; }
+                } else {
+                    w.hit[slot] = make_float4(tv.h.t, tv.h.u, tv.h.v, __uint_as_float(tv.h.tri));
+                    key = __float_as_uint(ldg4(s.tris + 3 * (size_t) tv.h.tri + 2).w) & 7u;
+                }
+            }
+        }
+        // closest hits found in this step: append to the queue of the surface's BSDF plugin type, one atomic per (warp, type)
+        unsigned fin = __ballot_sync(0xffffffffu, key != 0xffu);
+        if (fin) {
+            unsigned peers = __match_any_sync(0xffffffffu, key);
+            unsigned leader = __ffs(peers) - 1; uint32_t base = 0;
+            if (lane_id == leader && key != 0xffu) base = atomicAdd(w.qcount + key, (uint32_t) __popc(peers));
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (key != 0xffu) w.queue[(size_t) key * w.n_slots + base + __popc(peers & ((1u << lane_id) - 1u))] = slot;
         }
     }
-    if (f != f0) w.flags[i] = f;
-    // append to the queue of the hit surface's BSDF plugin type: one atomic per (warp, type)
-    unsigned peers = __match_any_sync(0xffffffffu, key);
-    unsigned leader = __ffs(peers) - 1; uint32_t base = 0;
-    if (lane_id == leader && key != 0xffu) base = atomicAdd(w.qcount + key, (uint32_t) __popc(peers));
-    base = __shfl_sync(0xffffffffu, base, leader);
-    if (key != 0xffu) w.queue[(size_t) key * w.n_slots + base + __popc(peers & ((1u << lane_id) - 1u))] = i;
     if (STATS) flush_stats(st, p.counters);
 }
 
@@ -139,14 +211,23 @@ template <bool STATS> static void launch_shade(int type, const DScene &s, const 
 }
 
 // One pass (p.n_lanes lane tickets) through the pool.  Returns the number of kernel launches.
-uint32_t run_wavefront_pass(const DScene &s, const RenderParams &p, const WfPool &w, uint32_t type_mask, int sm_count, bool stats, cudaStream_t st) {
+uint32_t run_wavefront_pass(const DScene &s, const RenderParams &p, const WfPool &w, uint32_t type_mask, int sm_count, bool stats, cudaStream_t st,
+                            double *trace_seconds, uint32_t *trace_launches) {
     AM_CUDA(cudaMemsetAsync(w.flags, 0, sizeof(uint32_t) * w.n_slots, st));
     AM_CUDA(cudaMemsetAsync(w.live, 0, sizeof(uint32_t) * 64, st));
     const unsigned grid = w.n_slots / 128, sgrid = (unsigned) sm_count * 16;
+    static int trace_ctas = 0;
+    if (!trace_ctas) { cudaOccupancyMaxActiveBlocksPerMultiprocessor(&trace_ctas, wf_trace_kernel<false>, 128, 0); if (trace_ctas < 1) trace_ctas = 1; }
+    const unsigned tgrid = std::min<unsigned>((unsigned) (sm_count * trace_ctas), grid);      // persistent: one resident wave
+    const uint32_t fetch_min = getenv("AMVPT_FETCH_MIN") ? (uint32_t) atoi(getenv("AMVPT_FETCH_MIN")) : 16u;
+    const uint32_t leaf_min = getenv("AMVPT_LEAF_MIN") ? (uint32_t) atoi(getenv("AMVPT_LEAF_MIN")) : 12u;
     uint32_t launches = 0, next_check = (uint32_t) (p.n_lanes / w.n_slots) + 1;
+    std::vector<cudaEvent_t> ev;        // optional: device time of the trace stage (bench.py roofline)
     for (uint32_t iter = 0;; ++iter) {
         if (stats) wf_regen_kernel<true><<<grid, 128, 0, st>>>(s, p, w, iter); else wf_regen_kernel<false><<<grid, 128, 0, st>>>(s, p, w, iter);
-        if (stats) wf_trace_kernel<true><<<grid, 128, 0, st>>>(s, p, w); else wf_trace_kernel<false><<<grid, 128, 0, st>>>(s, p, w);
+        if (trace_seconds) { cudaEvent_t a, b; cudaEventCreate(&a); cudaEventCreate(&b); ev.push_back(a); ev.push_back(b); cudaEventRecord(a, st); }
+        if (stats) wf_trace_kernel<true><<<tgrid, 128, 0, st>>>(s, p, w, fetch_min, leaf_min); else wf_trace_kernel<false><<<tgrid, 128, 0, st>>>(s, p, w, fetch_min, leaf_min);
+        if (trace_seconds) cudaEventRecord(ev.back(), st);
         launches += 2;
         for (int t = 0; t < WF_N_TYPES; ++t) if (type_mask & (1u << t)) {
             if (stats) launch_shade<true>(t, s, p, w, sgrid, st); else launch_shade<false>(t, s, p, w, sgrid, st);
@@ -162,6 +243,11 @@ uint32_t run_wavefront_pass(const DScene &s, const RenderParams &p, const WfPool
         }
     }
     AM_CUDA(cudaGetLastError());
+    if (trace_seconds) {
+        AM_CUDA(cudaStreamSynchronize(st));
+        for (size_t k = 0; k + 1 < ev.size(); k += 2) { float ms = 0.f; cudaEventElapsedTime(&ms, ev[k], ev[k + 1]); *trace_seconds += ms * 1e-3; cudaEventDestroy(ev[k]); cudaEventDestroy(ev[k + 1]); }
+        if (trace_launches) *trace_launches += (uint32_t) (ev.size() / 2);
+    }
     return launches;
 }
 

@@ -25,7 +25,11 @@ for sched in os.environ.get('SCHEDS', 'regenerate,wavefront,stream').split(','):
         for pool in os.environ.get('POOLS', '524288,1048576,2097152').split(','):
             os.environ['AMVPT_WF_POOL'] = pool
             s2 = scenes.build(desc, device=0); s, s_old = s2, s
-            run(f"wavefront pool {pool}", 'wavefront'); s = s_old
+            for fm in os.environ.get('FMS', '8,16').split(','):
+                for lm in os.environ.get('LMS', '1,4,8,12,16,24,33').split(','):
+                    os.environ['AMVPT_FETCH_MIN'] = fm; os.environ['AMVPT_LEAF_MIN'] = lm
+                    run(f"wavefront pool {pool} fetch_min {fm} leaf_min {lm}", 'wavefront')
+            s = s_old
         continue
     if sched != 'stream':
         run(sched, sched); continue
