@@ -69,7 +69,7 @@ class RenderStats(C.Structure):
 lib.amvpt_last_error.restype = C.c_char_p
 EXPORTS = ["amvpt_last_error", "amvpt_device_count", "amvpt_scene_create", "amvpt_scene_destroy", "amvpt_scene_from_xml",
            "amvpt_scene_from_xml_string", "amvpt_scene_add_bsdf", "amvpt_scene_add_mesh", "amvpt_scene_set_sensor_grid",
-           "amvpt_scene_set_sensor_batch", "amvpt_scene_set_integrator", "amvpt_scene_commit", "amvpt_scene_info",
+           "amvpt_scene_set_sensor_batch", "amvpt_scene_set_integrator", "amvpt_scene_set_rfilter", "amvpt_scene_commit", "amvpt_scene_info",
            "amvpt_scene_get_sensor", "amvpt_scene_get_bsdf_tables", "amvpt_scene_counts", "amvpt_scene_get_mesh",
            "amvpt_scene_get_bsdf", "amvpt_scene_get_integrator", "amvpt_render", "amvpt_shard_tiles", "amvpt_cancel", "amvpt_film_clear",
            "amvpt_film_raw", "amvpt_film_develop", "amvpt_film_develop_device", "amvpt_film_device_ptr", "amvpt_film_add_host",
@@ -165,6 +165,10 @@ class Scene:
     def set_integrator(self, max_depth=-1, rr_depth=5, hide_emitters=False, spp_pass_lim=16, sampler_seed=0, sample_count=0):
         d = IntegratorDesc(max_depth, rr_depth, int(hide_emitters), spp_pass_lim, sampler_seed, sample_count)
         _chk(lib.amvpt_scene_set_integrator(self._h, C.byref(d)))
+
+    def set_rfilter(self, type="box", param=0.5):
+        """Film reconstruction filter: 'box', 'gaussian' (param = stddev) or 'tent' (param = radius)."""
+        _chk(lib.amvpt_scene_set_rfilter(self._h, C.c_int({"box": 0, "gaussian": 1, "tent": 2}[type]), C.c_float(param)))
 
     def commit(self, device=0):
         _chk(lib.amvpt_scene_commit(self._h, C.c_int(device)))

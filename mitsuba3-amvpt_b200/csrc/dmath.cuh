@@ -124,6 +124,14 @@ AM_HD float estrin9(float x, const float *c) {
     float h = fmadd(x4, g, f);                          // level 3: 3 values -> (h, t)
     return fmadd(x8, t, h);
 }
+AM_HD float estrin10(float x, const float *c) {
+    float x2 = x * x;
+    float r0 = fmadd(x, c[1], c[0]), r1 = fmadd(x, c[3], c[2]), r2 = fmadd(x, c[5], c[4]), r3 = fmadd(x, c[7], c[6]), r4 = fmadd(x, c[9], c[8]);
+    float x4 = x2 * x2;
+    float q0 = fmadd(x2, r1, r0), q1 = fmadd(x2, r3, r2);      // level 2: 5 values -> (q0, q1, r4)
+    float x8 = x4 * x4;
+    return fmadd(x8, r4, fmadd(x4, q1, q0));                   // level 3: 3 values -> (s0, r4); level 4
+}
 AM_HD float estrin12(float x, const float *c) {
     float x2 = x * x;
     float p0 = fmadd(x, c[1], c[0]), p1 = fmadd(x, c[3], c[2]), p2 = fmadd(x, c[5], c[4]),

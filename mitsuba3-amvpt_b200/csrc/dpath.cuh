@@ -82,6 +82,30 @@ AM_D void splat_aggregated(unsigned mask, bool do_put, uint32_t pixel, float4 va
     }
 }
 
+// ImageBlock::put for a reconstruction filter other than the box: coalesced accumulation (src/render/imageblock.cpp:433-505)
+// into a block without border, normalize = false.  The footprint is (2n + 1)^2 pixels, n = ceil(radius - 1/2), around
+// floor(pos) - n; every covered pixel inside the film receives {R, G, B, 1} * w_y * w_x as one 16-byte reduction.
+AM_D float filter_eval(const DScene &s, float x) {
+    if (s.filter_type == 1) return max_(estrin10(x * x, s.filter_coeff), 0.f);        // gaussian.cpp:94-97
+    return max_(0.f, 1.f - fabs_(x * s.filter_inv_radius));                            // tent.cpp:54-56
+}
+AM_D void splat_filtered(const DScene &s, float spx, float spy, V3 L, float4 *film) {
+    const uint32_t n = (uint32_t) (int32_t) ceilf(s.filter_radius - .5f), count = 2 * n + 1;
+    const int32_t pix = (int32_t) floorf(spx) - (int32_t) n, piy = (int32_t) floorf(spy) - (int32_t) n;
+    float rx0 = ((float) pix + .5f) - spx, ry = ((float) piy + .5f) - spy;
+    uint32_t y = (uint32_t) piy;
+    for (uint32_t ys = 0; ys < count; ++ys, ++y, ry += 1.f) {
+        if (!(y < s.film_h)) continue;
+        const float wy = filter_eval(s, ry);
+        float rx = rx0;
+        for (uint32_t xs = 0; xs < count; ++xs, rx += 1.f) {
+            const uint32_t x = (uint32_t) pix + xs; if (!(x < s.film_w)) continue;
+            const float w = wy * filter_eval(s, rx);
+            atomicAdd(film + (size_t) y * s.film_w + x, make_float4(L.x * w, L.y * w, L.z * w, 1.f * w));
+        }
+    }
+}
+
 AM_D void flush_stats(const StatCtx &st, unsigned long long *c) {
     // warp-reduce, one atomic per counter per warp
     uint32_t v[5] = { st.closest, st.shadow, st.nodes, st.tris, st.vertices };

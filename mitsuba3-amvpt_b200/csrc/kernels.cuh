@@ -36,6 +36,7 @@ struct WfPool {
     float4 *hit;            // (t, u, v, bits tri) of the last closest-hit ray
     float4 *so, *sd, *sT, *sV;   // pending next-event shadow ray and the parked operands of result = fmadd(sT, sV, result)
     uint32_t *flags;        // WF_* bits
+    float2 *spos;           // sample position on the film (read by the splat when the reconstruction filter is not the box)
     uint32_t *queue;        // [6][n_slots] slot indices per BSDF plugin type
     uint32_t *qcount;       // [6]
     uint32_t *live;         // [64] live-slot counters, one per iteration (ring)

@@ -61,6 +61,7 @@ void render(Scene &s, const RenderOptions &opt) {
         n_passes = spp / spp_per_pass;
     }
     bool adaptive = opt.adaptive;
+    if (adaptive && s.rfilter_type != 0) AM_THROW("render: the adaptive allocator keeps per-pixel moments and needs the box reconstruction filter");
     std::vector<TileDesc> base = rank_tiles(s, opt.shard, adaptive);
     if (base.size() > s.tiles_cap) {
         s.tiles_cap = (uint32_t) base.size(); s.tiles_dev = (TileDesc *) s.dalloc(sizeof(TileDesc) * s.tiles_cap);
@@ -100,7 +101,7 @@ void render(Scene &s, const RenderOptions &opt) {
                 WfPool &w = s.wf; w.n_slots = n;
                 float4 **f4s[] = { &w.ro, &w.rd, &w.tp, &w.res, &w.pp, &w.hit, &w.so, &w.sd, &w.sT, &w.sV };
                 for (float4 **a : f4s) *a = (float4 *) s.dalloc(sizeof(float4) * n);
-                w.rng = (uint4 *) s.dalloc(sizeof(uint4) * n); w.flags = (uint32_t *) s.dalloc(sizeof(uint32_t) * n);
+                w.rng = (uint4 *) s.dalloc(sizeof(uint4) * n); w.flags = (uint32_t *) s.dalloc(sizeof(uint32_t) * n); w.spos = (float2 *) s.dalloc(sizeof(float2) * n);
                 w.queue = (uint32_t *) s.dalloc(sizeof(uint32_t) * 6 * (size_t) n); w.qcount = (uint32_t *) s.dalloc(sizeof(uint32_t) * 8);
                 w.live = (uint32_t *) s.dalloc(sizeof(uint32_t) * 64);
                 s.wf_type_mask = 0; for (auto &m : s.meshes) s.wf_type_mask |= 1u << s.bsdfs[m.bsdf].type;

@@ -211,6 +211,14 @@ void Scene::set_sensor_explicit(uint32_t n, uint32_t rx, uint32_t ry, const floa
     }
     committed = false;
 }
+// ReconstructionFilter plugins of the film (src/rfilters/{box,gaussian,tent}.cpp)
+void Scene::set_rfilter(int type, float param) {
+    if (type < 0 || type > 2) AM_THROW("rfilter: unknown filter type %d (0 box, 1 gaussian, 2 tent)", type);
+    if (type != 0 && !(param > 0.f)) AM_THROW("rfilter: the %s must be positive", type == 1 ? "standard deviation" : "radius");
+    float radius = type == 1 ? 4.f * param : (type == 2 ? param : .5f);
+    if (std::ceil(radius - .5f) > 7.f) AM_THROW("rfilter: radius %g is too large (footprint limited to 15 x 15 pixels)", radius);
+    rfilter_type = type; rfilter_param = param; committed = false;
+}
 // View tiles of the quilt owned by one rank: view v = ix + grid_x * iy (sub-sensor index), tile position follows
 // GridSensor::sample_ray's axis reversal (grid.cpp:246-255).
 std::vector<TileDesc> Scene::view_tiles(const Shard &sh) const {
@@ -263,6 +271,14 @@ void Scene::commit(int dev) {
     d.film_w = film_w; d.film_h = film_h;
     d.max_depth = integrator.max_depth < 0 ? 0xffffffffu : (uint32_t) integrator.max_depth;   // integrator.cpp:503-520
     d.rr_depth = integrator.rr_depth;
+    d.filter_type = rfilter_type; d.filter_radius = .5f; d.filter_inv_radius = 1.f;
+    if (rfilter_type == 1) {          // GaussianFilter ctor (gaussian.cpp:41-88): Remez fit to exp(-x / 2), rescaled by 1 / stddev^2 per degree
+        static const double coeff[10] = { 9.992604880e-1, -4.977025247e-1, 1.222248550e-1, -1.932406282e-2, 2.136713061e-3,
+                                          -1.679873860e-4, 9.202145248e-6, -3.329417433e-7, 7.128382794e-9, -6.821193280e-11 };
+        float stddev = rfilter_param; d.filter_radius = 4 * stddev; double scale = 1;
+        for (int i = 0; i < 10; ++i) { d.filter_coeff[i] = (float) (coeff[i] * scale); scale /= (double) stddev * (double) stddev; }
+        d.filter_coeff[0] -= estrin10(d.filter_radius * d.filter_radius, d.filter_coeff);
+    } else if (rfilter_type == 2) { d.filter_radius = rfilter_param; d.filter_inv_radius = 1.f / rfilter_param; }
     size_t npix = (size_t) film_w * film_h;
     film = (float4 *) dalloc(npix * sizeof(float4)); moments = (float2 *) dalloc(npix * sizeof(float2)); rgb = nullptr;
     counters = (unsigned long long *) dalloc(sizeof(unsigned long long) * CTR_COUNT);

@@ -35,7 +35,8 @@ wf_regen_kernel(const DScene s, const RenderParams p, const WfPool w, uint32_t i
     if (dead) {
         bool put = (f & WF_HAS_RESULT) != 0; uint32_t pixel = WF_NO_PIXEL; V3 L = v3(0.f);
         if (put) { float4 r = w.res[i]; pixel = __float_as_uint(r.w); if (f & WF_VALID_RAY) L = xyz(r); }
-        splat_aggregated(dm, put && pixel != WF_NO_PIXEL, pixel, make_float4(L.x, L.y, L.z, 1.f), p.film, p.moments);
+        if (s.filter_type == 0) splat_aggregated(dm, put && pixel != WF_NO_PIXEL, pixel, make_float4(L.x, L.y, L.z, 1.f), p.film, p.moments);
+        else if (put) { float2 sp = w.spos[i]; splat_filtered(s, sp.x, sp.y, L, p.film); }
         f = 0;
         unsigned long long base = 0; unsigned leader = __ffs(dm) - 1;
         if (lane_id == leader) base = atomicAdd(p.counters + CTR_TICKET, (unsigned long long) __popc(dm));
@@ -48,6 +49,7 @@ wf_regen_kernel(const DScene s, const RenderParams p, const WfPool w, uint32_t i
             w.ro[i] = f4(ps.ray.o, ps.ray.maxt); w.rd[i] = f4(ps.ray.d, ps.eta); w.tp[i] = f4(ps.throughput, ps.prev_bsdf_pdf);
             w.res[i] = f4(ps.result, __uint_as_float(ls.in_film ? ls.pixel : WF_NO_PIXEL)); w.pp[i] = f4(ps.prev_p, __uint_as_float(0u));
             w.rng[i] = make_uint4((uint32_t) ps.rng.state, (uint32_t) (ps.rng.state >> 32), (uint32_t) ps.rng.inc, (uint32_t) (ps.rng.inc >> 32));
+            if (s.filter_type != 0) w.spos[i] = make_float2(ls.spx, ls.spy);
             f = WF_HAS_RESULT | WF_PREV_DELTA | (s.max_depth != 0 ? WF_ALIVE : 0u);      // mvpath_single.h:86-87
         }
         w.flags[i] = f;

@@ -425,13 +425,18 @@ struct Builder {
         if (pf != "rgb") AM_THROW("%s: pixel_format \"%s\": only \"rgb\" is supported on this path", f->where.c_str(), pf.c_str());
         f->s("component_format", "float16"); f->s("file_format", "openexr"); f->b("sample_border", false); f->b("compensate", false);
         for (const char *c : { "crop_offset_x", "crop_offset_y", "crop_width", "crop_height" }) if (f->has(c)) AM_THROW("%s: film crop windows are not supported on this path", f->where.c_str());
-        bool have_filter = false;
+        // hdrfilm's default reconstruction filter is the gaussian with stddev 0.5 (src/render/film.cpp:34-40)
+        int ftype = 1; float fparam = 0.5f; bool have_filter = false;
         for (auto &k : f->children()) {
             if (k->cls != "rfilter") AM_THROW("%s: unexpected child <%s> of a film", f->where.c_str(), k->cls.c_str());
-            if (k->type != "box") AM_THROW("%s: reconstruction filter \"%s\": only the box filter is built so far (SURVEY.md sec.8f next-2)", k->where.c_str(), k->type.c_str());
+            if (have_filter) AM_THROW("%s: A film can only have one reconstruction filter.", f->where.c_str());
+            if (k->type == "box") { ftype = 0; fparam = 0.5f; }
+            else if (k->type == "gaussian") { ftype = 1; fparam = (float) k->f("stddev", 0.5); }
+            else if (k->type == "tent") { ftype = 2; fparam = (float) k->f("radius", 1.0); }
+            else AM_THROW("%s: reconstruction filter \"%s\" is not part of the AMVPT path (supported: box, gaussian, tent)", k->where.c_str(), k->type.c_str());
             k->check_unqueried(); f->mark(k); have_filter = true;
         }
-        if (!have_filter) AM_THROW("%s: the film has no <rfilter>; hdrfilm's default is the gaussian filter, which is not built yet -- add <rfilter type=\"box\"/>", f->where.c_str());
+        sc.set_rfilter(ftype, fparam);
         f->check_unqueried();
     }
     void sampler(Obj *s) {

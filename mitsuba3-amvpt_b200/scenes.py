@@ -134,6 +134,8 @@ def build(desc, device=0, commit=True):
         s.add_mesh(m["positions"], m["faces"], m["bsdf"], normals=m["normals"], radiance=m["radiance"], flip_normals=m["flip_normals"])
     s.set_sensor_grid(**desc["sensor"])
     s.set_integrator(**desc["integrator"])
+    if desc.get("rfilter"):
+        s.set_rfilter(*desc["rfilter"])
     if commit:
         s.commit(device)
     return s
@@ -187,6 +189,13 @@ def write_ply(path, positions, faces, normals=None, binary=True):
                 f.write(f"3 {a} {b} {c}\n".encode())
 
 
+def _rfilter_xml(rf):
+    if not rf or rf[0] == "box":
+        return '<rfilter type="box"/>'
+    key = "stddev" if rf[0] == "gaussian" else "radius"
+    return f'<rfilter type="{rf[0]}"><float name="{key}" value="{_fmt(rf[1])}"/></rfilter>'
+
+
 def _bsdf_xml(b, ident):
     t = b["type"]; lines = []
     if t == "diffuse":
@@ -233,7 +242,7 @@ def export_xml(desc, directory, mesh_format="obj", integrator="mvpath", filename
     out.append("    </integrator>")
     out += ['    <wrap type="any" id="m_film">', '        <string name="wrap_class" value="film"/>', '        <string name="wrap_type" value="hdrfilm"/>',
             f'        <integer name="width" value="{s["res_x"] // gx}"/>', f'        <integer name="height" value="{s["res_y"] // gy}"/>',
-            '        <string name="pixel_format" value="rgb"/>', '        <rfilter type="box"/>', "    </wrap>",
+            '        <string name="pixel_format" value="rgb"/>', '        ' + _rfilter_xml(desc.get("rfilter")), "    </wrap>",
             '    <wrap type="any" id="m_sampler">', '        <string name="wrap_class" value="sampler"/>', '        <string name="wrap_type" value="independent"/>',
             '        <integer name="sample_count" value="$spp"/>', f'        <integer name="seed" value="{it["sampler_seed"]}"/>', "    </wrap>"]
     m = np.asarray(s["to_world"], np.float64)

@@ -77,6 +77,8 @@ struct Scene {
     uint32_t film_w = 0, film_h = 0;    // quilt size
     uint32_t max_depth = 0xffffffffu, rr_depth = 5; int hide_emitters = 0;
     uint32_t base_seed = 0;
+    // reconstruction filter of the film: 0 box, 1 gaussian (src/rfilters/gaussian.cpp), 2 tent (src/rfilters/tent.cpp)
+    int filter_type = 0; float filter_radius = 0.5f, filter_coeff[10] = { 0 }, filter_inv_radius = 1.f;
     // flattened primitives
     std::vector<uint32_t> prim_mesh;    // global prim -> mesh
     std::vector<BvhNode> nodes; std::vector<uint32_t> bvh_prims;
@@ -491,6 +493,45 @@ static LaneOut render_lane(const Scene &s, uint32_t seed_value, uint32_t lane, u
     return o;
 }
 
+// ReconstructionFilter::eval: GaussianFilter (gaussian.cpp:94-103, the non-CUDA branch: a degree-9 polynomial in x^2 fitted
+// to exp(-x^2 / (2 stddev^2)), shifted so that it reaches zero at the radius, :52-88) and TentFilter (tent.cpp:54-56)
+static void filter_setup(Scene &s, int type, float param) {
+    s.filter_type = type;
+    if (type == 1) {
+        static const double coeff[10] = { 9.992604880e-1, -4.977025247e-1, 1.222248550e-1, -1.932406282e-2, 2.136713061e-3,
+                                          -1.679873860e-4, 9.202145248e-6, -3.329417433e-7, 7.128382794e-9, -6.821193280e-11 };
+        float stddev = param; s.filter_radius = 4 * stddev;
+        double scale = 1;
+        for (int i = 0; i < 10; ++i) { s.filter_coeff[i] = (float) (coeff[i] * scale); scale /= (double) stddev * (double) stddev; }
+        s.filter_coeff[0] -= estrin(s.filter_radius * s.filter_radius, s.filter_coeff, 10);
+    } else if (type == 2) { s.filter_radius = param; s.filter_inv_radius = 1.f / param; }
+    else s.filter_radius = 0.5f;
+}
+static inline float filter_eval(const Scene &s, float x) {
+    if (s.filter_type == 1) return std::max(estrin(x * x, s.filter_coeff, 10), 0.f);
+    return std::max(0.f, 1.f - std::fabs(x * s.filter_inv_radius));
+}
+// ImageBlock::put, coalesced accumulation (src/render/imageblock.cpp:433-505) into a block without border (film->create_block()
+// defaults, hdrfilm.cpp:276-291), normalize = false: the footprint (2n+1)^2, n = ceil(radius - 1/2), around floor(pos) - n
+static void filter_put(const Scene &s, float *film, float spx, float spy, V3 L) {
+    uint32_t n = (uint32_t) (int32_t) std::ceil(s.filter_radius - .5f), count = 2 * n + 1;
+    int32_t pix = (int32_t) std::floor(spx) - (int32_t) n, piy = (int32_t) std::floor(spy) - (int32_t) n;
+    uint32_t x = (uint32_t) pix, y = (uint32_t) piy;
+    float rx = ((float) pix + .5f) - spx, ry = ((float) piy + .5f) - spy;
+    float wx[16], wy[16];
+    for (uint32_t i = 0; i < count; ++i) { wx[i] = filter_eval(s, rx); wy[i] = filter_eval(s, ry); rx += 1.f; ry += 1.f; }
+    float values[4] = { L.x, L.y, L.z, 1.f };
+    for (uint32_t ys = 0; ys < count; ++ys, ++y) {
+        if (!(y < s.film_h)) continue;
+        for (uint32_t xs = 0; xs < count; ++xs) {
+            uint32_t xx = x + xs; if (!(xx < s.film_w)) continue;
+            float weight = wy[ys] * wx[xs];
+            float *px = film + 4 * ((size_t) y * s.film_w + xx);
+            for (int k = 0; k < 4; ++k) px[k] += values[k] * weight;
+        }
+    }
+}
+
 } // namespace orc
 
 // ====================================================================== C interface (ctypes)
@@ -582,6 +623,9 @@ void orc_set_integrator(void *sp, int64_t max_depth, uint32_t rr_depth, int hide
     s.max_depth = max_depth < 0 ? 0xffffffffu : (uint32_t) max_depth;        // integrator.cpp:503-520
     s.rr_depth = rr_depth; s.hide_emitters = hide_emitters; s.base_seed = sampler_seed;
 }
+// film reconstruction filter: type 0 box, 1 gaussian (param = stddev), 2 tent (param = radius)
+void orc_set_rfilter(void *sp, int type, float param) { filter_setup(*(Scene *) sp, type, param); }
+void orc_filter_eval(int type, float param, const float *x, int n, float *out) { Scene s; filter_setup(s, type, param); for (int i = 0; i < n; ++i) out[i] = filter_eval(s, x[i]); }
 void orc_prepare(void *sp) { bvh_build(*(Scene *) sp); }
 void orc_film_size(void *sp, uint32_t *w, uint32_t *h) { Scene &s = *(Scene *) sp; *w = s.film_w; *h = s.film_h; }
 uint32_t orc_num_prims(void *sp) { return ((Scene *) sp)->nprims(); }
@@ -722,6 +766,9 @@ double orc_render_rows(void *sp, uint32_t seed, uint32_t spp, uint32_t spp_pass_
     if (!row_stride) row_stride = 1;
     std::atomic<uint32_t> next_row{ 0 };
     std::vector<TraverseStats> tstats(std::max(nthreads, 1));
+    // a wider filter splats across rows: every thread then accumulates into its own film, summed in thread order at the end
+    size_t film_floats = 4 * (size_t) s.film_w * s.film_h;
+    std::vector<std::vector<float>> tfilm; if (s.filter_type != 0 && nthreads > 1) tfilm.assign(nthreads, std::vector<float>(film_floats, 0.f));
     auto t0 = std::chrono::steady_clock::now();
     auto worker = [&](int tid) {
         for (;;) {
@@ -733,6 +780,7 @@ double orc_render_rows(void *sp, uint32_t seed, uint32_t spp, uint32_t spp_pass_
                     uint32_t lane = (y * s.film_w + x) * spp_per_pass + k;
                     LaneOut o = render_lane(s, seed_value, lane, spp_per_pass, brute != 0, nullptr, &tstats[tid]);
                     // a jittered position that rounds up into the next pixel/row is extremely rare; handled with the same index rule
+                    if (s.filter_type != 0) { filter_put(s, tfilm.empty() ? film : tfilm[tid].data(), o.sample_pos[0], o.sample_pos[1], o.r.L); continue; }
                     if (!o.in_film) continue;
                     float *px = film + 4 * (size_t) o.pixel;
                     px[0] += o.r.L.x; px[1] += o.r.L.y; px[2] += o.r.L.z; px[3] += 1.f;
@@ -742,6 +790,7 @@ double orc_render_rows(void *sp, uint32_t seed, uint32_t spp, uint32_t spp_pass_
     };
     if (nthreads <= 1) worker(0);
     else { std::vector<std::thread> th; for (int i = 0; i < nthreads; ++i) th.emplace_back(worker, i); for (auto &t : th) t.join(); }
+    for (auto &tf : tfilm) for (size_t i = 0; i < film_floats; ++i) film[i] += tf[i];
     double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     if (stats) { stats[0] = stats[1] = 0; for (auto &t : tstats) { stats[0] += t.nodes; stats[1] += t.tris; } }
     return sec;

@@ -87,7 +87,10 @@ class OracleScene:
                 self.add_bsdf(**b)
             for m in desc["meshes"]:
                 self.add_mesh(m["positions"], m["faces"], m["bsdf"], m["normals"], m["radiance"], m["flip_normals"])
-            self.set_sensor_grid(**desc["sensor"]); self.set_integrator(**desc["integrator"]); self.prepare()
+            self.set_sensor_grid(**desc["sensor"]); self.set_integrator(**desc["integrator"])
+            if desc.get("rfilter"):
+                self.set_rfilter(*desc["rfilter"])
+            self.prepare()
 
     def __del__(self):
         if getattr(self, "h", None):
@@ -121,6 +124,9 @@ class OracleScene:
     def set_integrator(self, max_depth=-1, rr_depth=5, hide_emitters=False, spp_pass_lim=16, sampler_seed=0, sample_count=0):
         self.spp_pass_lim = spp_pass_lim
         self.o.orc_set_integrator(self.h, C.c_int64(max_depth), C.c_uint32(rr_depth), C.c_int(int(hide_emitters)), C.c_uint32(sampler_seed))
+
+    def set_rfilter(self, type="box", param=0.5):
+        self.o.orc_set_rfilter(self.h, C.c_int({"box": 0, "gaussian": 1, "tent": 2}[type]), C.c_float(param))
 
     def prepare(self):
         self.o.orc_prepare(self.h)
@@ -188,3 +194,8 @@ def math1(op, x):
 
 def sampler_stream(seed_value, lane, n):
     out = np.zeros(n, np.float32); orc().orc_sampler_stream(C.c_uint32(seed_value), C.c_uint32(lane), C.c_int(n), _p(out)); return out
+
+
+def filter_eval(type, param, x):
+    x = np.ascontiguousarray(x, np.float32); out = np.zeros_like(x)
+    orc().orc_filter_eval(C.c_int({"box": 0, "gaussian": 1, "tent": 2}[type]), C.c_float(param), _p(x), C.c_int(len(x)), _p(out)); return out

@@ -172,3 +172,31 @@ def test_golden_vectors_still_match_reference_headers_when_available(ob):
     for op in (0, 1, 2, 4, 6):
         out = np.zeros_like(x); ref.ref_math1(C.c_int(op), x.ctypes.data_as(ob.f32p), C.c_int(len(x)), out.ctypes.data_as(ob.f32p))
         same(ob.math1(op, x), out.view(np.uint32), f"live reference math op {op}")
+
+
+def test_reconstruction_filters_known_answers_and_film(ob, scenes):
+    """Known answers of the reference's src/rfilters/tests/test_rfilter.py:14-18, 42-46, and the footprint rule of the coalesced
+    ImageBlock::put (src/render/imageblock.cpp:433-505): the weight channel of the film equals the sum over samples of the
+    separable filter weights that fall inside the film."""
+    g = ob.filter_eval("gaussian", 0.5, [0.2, 2.1, 0.0, 2.0, -0.2]); t = ob.filter_eval("tent", 1.0, [0.1, 1.1, -0.5])
+    assert abs(g[0] - 0.9227) < 8e-3 and g[1] == 0 and abs(g[2] - 1.0) < 2e-3 and g[3] < 1e-5 and g[0] == g[4]
+    assert abs(t[0] - 0.903) < 5e-2 and t[1] == 0 and t[2] == 0.5
+    for rf in (("gaussian", 0.5), ("tent", 1.0)):
+        desc = scenes.cornell_box(grid_x=2, grid_y=1, view_res=12, spp_pass_lim=4, sample_count=4); desc["rfilter"] = rf
+        o = ob.OracleScene(desc); film, _, _ = o.render(seed=0, spp=4, brute=True, nthreads=3)
+        film1, _, _ = o.render(seed=0, spp=4, brute=True, nthreads=1)
+        assert np.allclose(film, film1, rtol=0, atol=1e-5 * film1.max())            # per-thread films summed = sequential film
+        W, H = o.film_size(); pos = o.trace_lanes(0, 4, 0, W * H * 4, trace=False)["sample_pos"]
+        radius = 2.0 if rf[0] == "gaussian" else 1.0; n = int(np.ceil(radius - 0.5)); want = np.zeros((H, W))
+        for sx, sy in pos.astype(np.float64):
+            ix, iy = int(np.floor(sx)) - n, int(np.floor(sy)) - n
+            wx = ob.filter_eval(rf[0], rf[1], np.float32(ix + 0.5 - sx) + np.arange(2 * n + 1, dtype=np.float32))
+            wy = ob.filter_eval(rf[0], rf[1], np.float32(iy + 0.5 - sy) + np.arange(2 * n + 1, dtype=np.float32))
+            for j in range(2 * n + 1):
+                for i in range(2 * n + 1):
+                    if 0 <= ix + i < W and 0 <= iy + j < H:
+                        want[iy + j, ix + i] += float(wy[j]) * float(wx[i])
+        assert np.allclose(film[..., 3], want, rtol=1e-4, atol=1e-5)
+        box = dict(desc); box["rfilter"] = ("box", 0.5); fb, _, _ = ob.OracleScene(box).render(seed=0, spp=4, brute=True)
+        a, b = ob.develop(film), ob.develop(fb)
+        assert abs(a.mean() - b.mean()) < 0.05 * b.mean()                           # the filter redistributes, it does not add energy

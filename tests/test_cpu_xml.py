@@ -122,6 +122,10 @@ def test_xml_errors(pkg, tmp_path):
               '<rfilter type="box"/></film></sensor>')
     shape = '<shape type="cube"/>'
     assert load(sensor + shape).info()["n_prims"] == 12
+    assert load(sensor.replace('<rfilter type="box"/>', '') + shape).info()["n_prims"] == 12      # hdrfilm default: gaussian, stddev 0.5
+    assert load(sensor.replace('<rfilter type="box"/>', '<rfilter type="tent"><float name="radius" value="1.5"/></rfilter>') + shape).info()["n_prims"] == 12
+    with pytest.raises(pkg.AmvptError, match="not part of the AMVPT path"):
+        load(sensor.replace('type="box"', 'type="lanczos"') + shape)
     with pytest.raises(pkg.AmvptError, match="requires MultiSensor"):           # mvpath.cpp:15-17
         load('<integrator type="mvpath"/>' + sensor + shape)
     with pytest.raises(pkg.AmvptError, match="undefined parameter"):

@@ -287,3 +287,19 @@ def test_stream_scheduler_depth_edge_cases_and_thresholds(scenes, gpu):
             finally:
                 del os.environ["AMVPT_WF_POOL"]
             assert np.array_equal(a[..., 3], b[..., 3]) and np.array_equal(bits(a[one]), bits(b[one])), f"max_depth={md} rr={rr} wavefront pool={pool}"
+
+
+@pytest.mark.parametrize("rf", [("gaussian", 0.5), ("tent", 1.0), ("gaussian", 0.3)])
+def test_reconstruction_filter_film_matches_oracle(rf, scenes, ob, gpu):
+    """ImageBlock::put with a non-box filter (coalesced path, src/render/imageblock.cpp:433-505): every sample is spread over
+    (2n+1)^2 pixels with separable weights, across view-tile boundaries of the quilt and clipped at the film border."""
+    desc = scenes.cornell_box(grid_x=2, grid_y=2, view_res=24, sample_count=16); desc["rfilter"] = rf
+    s = scenes.build(desc, device=gpu); o = ob.OracleScene(desc)
+    ofilm, _, _ = o.render(seed=2, spp=16, brute=True, nthreads=4); scale = ofilm[..., :3].max()
+    for sched in ("regenerate", "wavefront", "stream", "warp_batch"):
+        s.render(seed=2, spp=16, scheduler=sched, develop=False); film = s.film_raw()
+        assert np.allclose(film[..., 3], ofilm[..., 3], rtol=1e-5, atol=1e-5), sched
+        assert np.abs(film[..., :3] - ofilm[..., :3]).max() <= 5 * FILM_RTOL * scale, sched
+    assert ofilm[..., 3].min() > 0 and abs(ofilm[..., 3].mean() / 16 - (ofilm[..., 3].mean() / 16)) == 0
+    with pytest.raises(Exception, match="box reconstruction filter"):
+        s.render(seed=2, spp=16, adaptive=True)
