@@ -225,6 +225,15 @@ def main():
         per_launch_s = ks["seconds"] / ks["launches"]; paths_per_launch = ks["paths"] / ks["launches"]
         note = "scene is cache-resident for the Cornell box: the megakernel is issue-bound (SIMD efficiency / issue slots), see profiles/"
     achieved = paths_per_launch * b_path / per_launch_s / 1e9
+    # DRAM bytes per launch of that kernel from the committed ncu --set full capture, scaled from the profiled launch size
+    traffic, traffic_src = None, None
+    try:
+        tr = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json")))[kernel]
+        units = ks["paths"] / ks["launches"] if kernel == "render_pass_kernel" else float(s.info().get("wf_pool", 1 << 21))
+        traffic = tr["dram_bytes_per_launch"] * units / tr.get("paths_per_launch", tr.get("slots_per_launch"))
+        traffic_src = f'{tr["source"]} ({tr["workload"]}), scaled by launch size'
+    except Exception:
+        pass
     out = {"metric": "Mpaths/s (all views, device-timed)", "value": value, "unit": "Mpaths/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
            "ms_per_step": dev_s / args.steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
            "config": {"workload": args.workload, **kw, "spp": spp, "scheduler": args.scheduler, "scheduler_used": sched, "quilt": [W, H], "paths_per_step": n_paths,
@@ -232,7 +241,7 @@ def main():
                       "parallelism": f"views sharded over {world} rank(s), NCCL film reduce to rank 0" if world > 1 else "single GPU"},
            "clocks": clk, "gpu_launches": launches, "wall_s": wall,
            "e2e": {"value": e2e_val, "unit": "Mpaths/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
-           "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+           "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "algorithmic_bytes_per_launch": paths_per_launch * b_path,
                         "peak_source": peak_src, "kernel": kernel, "bytes_per_path": b_path, "rays_per_path": rays / cs["paths"],
                         "nodes_per_ray": cs["bvh_nodes"] / max(rays, 1), "tris_per_ray": cs["tri_tests"] / max(rays, 1),
                         "launch_ms": per_launch_s * 1e3, "note": note}}
