@@ -167,18 +167,26 @@ def main():
     for _ in range(args.warmup):
         step()
     clocks = ClockSampler(local); barrier(); clocks.start()
-    dev_s, launches = 0.0, 0
+    dev_s, launches, render_s = 0.0, 0, 0.0
     t0 = time.perf_counter()
     for _ in range(args.steps):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(); st = step(); e1.record(); e1.synchronize()
         dev_s += e0.elapsed_time(e1) * 1e-3; launches += st["launches"]
-        kernel_s = st["seconds"]
+        render_s += st["seconds"]
     barrier(); wall = time.perf_counter() - t0
     clk = clocks.stop()
     tmax = torch.tensor([dev_s], dtype=torch.float64, device=f"cuda:{local}")
     if dist is not None:
         dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+    # per-rank breakdown (diagnostic): device seconds inside render() vs. the whole step (render + NCCL film reduce)
+    mine = torch.tensor([render_s, dev_s], dtype=torch.float64, device=f"cuda:{local}")
+    per_rank = [torch.zeros_like(mine) for _ in range(world)]
+    if dist is not None:
+        dist.all_gather(per_rank, mine)
+    else:
+        per_rank = [mine]
+    rank_ms = [[round(float(x) / args.steps * 1e3, 2) for x in t.tolist()] for t in per_rank]
     dev_s = float(tmax.item())
     value = n_paths * args.steps / dev_s / 1e6
 
@@ -239,7 +247,7 @@ def main():
            "config": {"workload": args.workload, **kw, "spp": spp, "scheduler": args.scheduler, "scheduler_used": sched, "quilt": [W, H], "paths_per_step": n_paths,
                       "l2_policy": f"film {W * H * 16 / 1e6:.0f} MB > 126 MB L2 rewritten every pass" if W * H * 16 > 126e6 else "film smaller than L2 (small workload)",
                       "parallelism": f"views sharded over {world} rank(s), NCCL film reduce to rank 0" if world > 1 else "single GPU"},
-           "clocks": clk, "gpu_launches": launches, "wall_s": wall,
+           "clocks": clk, "gpu_launches": launches, "wall_s": wall, "rank_ms_render_step": rank_ms,
            "e2e": {"value": e2e_val, "unit": "Mpaths/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "algorithmic_bytes_per_launch": paths_per_launch * b_path,
                         "peak_source": peak_src, "kernel": kernel, "bytes_per_path": b_path, "rays_per_path": rays / cs["paths"],

@@ -89,8 +89,7 @@ render_pass_kernel(const DScene s, const RenderParams p) {
                 // splat finished lanes (imageblock.h:185-215: value = spec * ray_weight (1), weight channel += 1)
                 unsigned m = idle_mask;
                 V3 L = ps.valid_ray ? ps.result : v3(0.f);
-                if (s.filter_type == 0) splat_aggregated(m, has_result && ls.in_film, ls.pixel, make_float4(L.x, L.y, L.z, 1.f), p.film, p.moments);
-                else if (has_result) splat_filtered(s, ls.spx, ls.spy, L, p.film);
+                splat_aggregated(m, has_result && ls.in_film, ls.pixel, make_float4(L.x, L.y, L.z, 1.f), p.film, p.moments);
                 has_result = false;
                 unsigned fm = __ballot_sync(m, !exhausted);     // idle lanes that may still draw a ticket
                 if (!exhausted) {
@@ -145,8 +144,7 @@ render_stream_kernel(const DScene s, const RenderParams p) {
             (exhausted && __any_sync(0xffffffffu, has_result && phase == PH_IDLE))) {
             if (phase == PH_IDLE) {
                 V3 L = ps.valid_ray ? ps.result : v3(0.f);
-                if (s.filter_type == 0) splat_aggregated(idle_mask, has_result && ls.in_film, ls.pixel, make_float4(L.x, L.y, L.z, 1.f), p.film, p.moments);
-                else if (has_result) splat_filtered(s, ls.spx, ls.spy, L, p.film);
+                splat_aggregated(idle_mask, has_result && ls.in_film, ls.pixel, make_float4(L.x, L.y, L.z, 1.f), p.film, p.moments);
                 has_result = false;
                 bool got = false;
                 if (!exhausted) {

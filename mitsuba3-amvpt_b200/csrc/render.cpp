@@ -85,6 +85,9 @@ void render(Scene &s, const RenderOptions &opt) {
         mode = (n_types >= 3 || s.n_tris >= 32768u) ? 3 : 1;
     }
     if (getenv("AMVPT_SCHEDULER")) mode = atoi(getenv("AMVPT_SCHEDULER"));
+    // a reconstruction filter other than the box is splatted by the wavefront's regen stage only: carrying the sample position
+    // and the footprint loop through the persistent megakernels costs them 8 % on the box-filter path (measured, profiles/)
+    if (s.rfilter_type != 0) mode = 3;
     rs.scheduler_used = (uint32_t) mode;
     auto launch = [&](std::vector<TileDesc> &tiles, uint32_t pass) {
         unsigned long long lanes = finish_tiles(tiles);
