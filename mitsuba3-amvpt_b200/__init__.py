@@ -12,7 +12,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libamvpt_b200.so")
+LIB_PATH = os.environ.get("AMVPT_LIB", os.path.join(_HERE, "libamvpt_b200.so"))
 
 
 class AmvptError(RuntimeError):

@@ -3,12 +3,12 @@ import os, subprocess, sys, hashlib
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-OUT = os.path.join(HERE, "libamvpt_b200.so")
-OBJ = os.path.join(HERE, "build")
+OUT = os.environ.get("AMVPT_OUT", os.path.join(HERE, "libamvpt_b200.so"))
+OBJ = os.environ.get("AMVPT_OBJ", os.path.join(HERE, "build"))
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 # canonical arithmetic: no FMA contraction on device (-fmad=false) or host (-ffp-contract=off); FMA only where written
-COMMON = ["-std=c++17", "-O3", "-lineinfo", "-fmad=false", "-Xcompiler", "-fPIC,-mfma,-ffp-contract=off,-fno-fast-math,-pthread"]
+COMMON = os.environ.get("AMVPT_CFLAGS", "").split() + ["-std=c++17", "-O3", "-lineinfo", "-fmad=false", "-Xcompiler", "-fPIC,-mfma,-ffp-contract=off,-fno-fast-math,-pthread"]
 SOURCES = ["kernels.cu", "wavefront.cu", "scene.cpp", "bvh.cpp", "render.cpp", "xml.cpp", "meshio.cpp", "capi.cpp"]
 
 

@@ -74,7 +74,10 @@ template <bool TAP, bool STATS> AM_D void path_bounce(const DScene &s, PathState
 // MODE 0: a warp takes 32 consecutive tickets and traces them to completion before taking the next 32.
 // MODE 1: path regeneration -- whenever at least REGEN_MIN lanes of the warp are idle they splat and take fresh
 //         tickets together, so the warp stays full while paths have different lengths.
-template <int MODE, bool STATS> __global__ void __launch_bounds__(128)
+#ifndef AM_RP_MIN_CTAS
+#define AM_RP_MIN_CTAS 1
+#endif
+template <int MODE, bool STATS> __global__ void __launch_bounds__(128, AM_RP_MIN_CTAS)
 render_pass_kernel(const DScene s, const RenderParams p) {
     const unsigned lane_id = threadIdx.x & 31u;
     PathState ps; LaneSetup ls; ps.active = false;

@@ -121,6 +121,10 @@ class OracleScene:
                           near_clip, far_clip, focus_distance, aperture_radius, 0.0 if cone_deg is None else cone_deg, dist, _v3(cd), _v3(cam_off))
         self.o.orc_set_sensor_grid(self.h, C.byref(d))
 
+    def set_sensor_batch(self, res_x, res_y, sample_to_camera, to_world, near_clip, far_clip):
+        s2c = np.ascontiguousarray(sample_to_camera, np.float32).reshape(-1, 16); tw = np.ascontiguousarray(to_world, np.float32).reshape(-1, 16)
+        self.o.orc_set_sensor_explicit(self.h, C.c_uint32(len(s2c)), C.c_uint32(res_x), C.c_uint32(res_y), _p(s2c), _p(tw), C.c_float(near_clip), C.c_float(far_clip))
+
     def set_integrator(self, max_depth=-1, rr_depth=5, hide_emitters=False, spp_pass_lim=16, sampler_seed=0, sample_count=0):
         self.spp_pass_lim = spp_pass_lim
         self.o.orc_set_integrator(self.h, C.c_int64(max_depth), C.c_uint32(rr_depth), C.c_int(int(hide_emitters)), C.c_uint32(sampler_seed))
