@@ -9,6 +9,7 @@
 #include <cfloat>
 #include <cmath>
 #include <cstdlib>
+#include <functional>
 
 namespace amvpt {
 
@@ -101,7 +102,7 @@ void build_bvh(const Scene &s, float scene_scale, BvhOut &out) {
     Builder bl(prims);
     if (np) bl.build(0, np, 0);
     out.depth = np ? (uint32_t) bl.depth_of(0) : 1u;
-    if (out.depth > AM_STACK_SIZE - 2) AM_THROW("BVH depth %u exceeds the traversal stack", out.depth);
+    if (AM_BVH_WIDTH == 2 && out.depth > AM_STACK_SIZE - 2) AM_THROW("BVH depth %u exceeds the traversal stack", out.depth);
 
     // triangles in leaf order
     out.tris.resize(3 * (size_t) np); out.prim_to_tri.resize(np);
@@ -117,10 +118,59 @@ void build_bvh(const Scene &s, float scene_scale, BvhOut &out) {
             if (!m.nrm.empty()) { const float *n = &m.nrm[3 * m.faces[3 * f + k]]; out.tri_nrm[3 * (size_t) i + k] = make_float4(n[0], n[1], n[2], 0.f); }
         }
     }
+    auto leaf_code = [&](const TNode &n) -> int32_t { return (int32_t) ~((n.first << 3) | n.count); };
+#if AM_BVH_WIDTH == 4
+    // Collapse the binary tree into 4-wide nodes: start from a node's two children and keep replacing the inner child with
+    // the largest surface by its own two children until four slots are used (or only leaves remain).  Nodes are numbered in
+    // pre-order, so the root is node 0 and a child reference 0 can mark an empty slot.
+    struct Wide { int32_t kid[4]; int n; };
+    std::vector<Wide> wide; uint32_t depth4 = 0;
+    std::function<int32_t(int32_t, uint32_t)> widen = [&](int32_t t, uint32_t depth) -> int32_t {
+        depth4 = std::max(depth4, depth + 1);
+        int32_t id = (int32_t) wide.size(); wide.push_back(Wide{ { -1, -1, -1, -1 }, 0 });
+        int32_t kids[4]; int n = 0;
+        if (bl.nodes[t].left < 0) kids[n++] = t;             // a tree that is a single leaf: one slot
+        else { kids[n++] = bl.nodes[t].left; kids[n++] = bl.nodes[t].right; }
+        while (n < 4) {
+            int best = -1; float area = -1.f;
+            for (int i = 0; i < n; ++i) if (bl.nodes[kids[i]].left >= 0 && bl.nodes[kids[i]].b.half_area() > area) { area = bl.nodes[kids[i]].b.half_area(); best = i; }
+            if (best < 0) break;
+            int32_t k = kids[best]; kids[best] = bl.nodes[k].left; kids[n++] = bl.nodes[k].right;
+        }
+        Wide w; w.n = n; for (int i = 0; i < 4; ++i) w.kid[i] = i < n ? kids[i] : -1;
+        wide[id] = w;
+        return id;
+    };
+    // breadth of recursion = tree depth (<= kSahDepth + log2 of the largest median-split range), fine for the host stack
+    std::vector<int32_t> wide_of(bl.nodes.size(), -1);
+    std::function<void(int32_t, uint32_t)> build_wide = [&](int32_t t, uint32_t depth) {
+        int32_t id = widen(t, depth); wide_of[t] = id;
+        Wide w = wide[id];
+        for (int i = 0; i < w.n; ++i) if (bl.nodes[w.kid[i]].left >= 0) build_wide(w.kid[i], depth + 1);
+    };
+    if (np) build_wide(0, 0); else wide.push_back(Wide{ { -1, -1, -1, -1 }, 0 });
+    out.depth = std::max(depth4, 1u);
+    if (3 * out.depth + 2 > AM_STACK_SIZE) AM_THROW("BVH depth %u exceeds the traversal stack", out.depth);
+    out.nodes.assign(8 * wide.size(), make_float4(0.f, 0.f, 0.f, 0.f));
+    for (size_t id = 0; id < wide.size(); ++id) {
+        const Wide &w = wide[id]; float lo[3][4], hi[3][4]; int32_t ref[4];
+        for (int i = 0; i < 4; ++i) {
+            for (int a = 0; a < 3; ++a) { lo[a][i] = 0.f; hi[a][i] = 0.f; }
+            ref[i] = 0;
+            if (i >= w.n) continue;
+            const TNode &k = bl.nodes[w.kid[i]];
+            for (int a = 0; a < 3; ++a) { lo[a][i] = k.b.lo[a]; hi[a][i] = k.b.hi[a]; }
+            ref[i] = k.left < 0 ? leaf_code(k) : wide_of[w.kid[i]];
+        }
+        float4 *o = &out.nodes[8 * id];
+        for (int a = 0; a < 3; ++a) { o[2 * a] = make_float4(lo[a][0], lo[a][1], lo[a][2], lo[a][3]); o[2 * a + 1] = make_float4(hi[a][0], hi[a][1], hi[a][2], hi[a][3]); }
+        float rf[4]; memcpy(rf, ref, 16); o[6] = make_float4(rf[0], rf[1], rf[2], rf[3]);
+    }
+#else
     // flatten: inner nodes numbered in depth-first order, each holding its two children's boxes
     auto child_ref = [&](const std::vector<int32_t> &inner_id, int32_t c) -> int32_t {
         const TNode &n = bl.nodes[c];
-        if (n.left < 0) return (int32_t) ~((n.first << 3) | n.count);
+        if (n.left < 0) return leaf_code(n);
         return inner_id[c];
     };
     std::vector<int32_t> inner_id(bl.nodes.size(), -1); int32_t n_inner = 0;
@@ -145,6 +195,7 @@ void build_bvh(const Scene &s, float scene_scale, BvhOut &out) {
         const TNode &n = bl.nodes[i]; if (n.left < 0) continue;
         put(inner_id[i], bl.nodes[n.left].b, child_ref(inner_id, n.left), bl.nodes[n.right].b, child_ref(inner_id, n.right));
     }
+#endif
 }
 
 } // namespace amvpt

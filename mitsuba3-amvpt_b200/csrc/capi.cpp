@@ -281,6 +281,18 @@ int amvpt_bvh_validate(amvpt_scene *h, uint32_t *max_depth, uint32_t *n_leaves) 
                 }
                 return;
             }
+#if AM_BVH_WIDTH == 4
+            const float4 *n = &s.bvh.nodes[8 * (size_t) ref];
+            const float *lo[3] = { &n[0].x, &n[2].x, &n[4].x }, *hi[3] = { &n[1].x, &n[3].x, &n[5].x };
+            int32_t c[4]; memcpy(c, &n[6].x, 16);
+            for (int i = 0; i < 4; ++i) {
+                if (c[i] == 0) continue;                 // empty slot
+                if (c[i] > 0 && c[i] <= ref) AM_THROW("bvh: child %d of node %d is not numbered after its parent", c[i], ref);
+                B b = { { lo[0][i], lo[1][i], lo[2][i] }, { hi[0][i], hi[1][i], hi[2][i] } };
+                if (box) for (int k = 0; k < 3; ++k) if (b.lo[k] < box->lo[k] || b.hi[k] > box->hi[k]) AM_THROW("bvh: child box outside parent at node %d", ref);
+                rec(c[i], &b, depth + 1);
+            }
+#else
             const float4 *n = &s.bvh.nodes[4 * (size_t) ref];
             B a = { { n[0].x, n[0].z, n[2].x }, { n[0].y, n[0].w, n[2].y } }, b = { { n[1].x, n[1].z, n[2].z }, { n[1].y, n[1].w, n[2].w } };
             int32_t ca, cb; memcpy(&ca, &n[3].x, 4); memcpy(&cb, &n[3].y, 4);
@@ -290,6 +302,7 @@ int amvpt_bvh_validate(amvpt_scene *h, uint32_t *max_depth, uint32_t *n_leaves) 
                 if (!b_empty && (b.lo[k] < box->lo[k] || b.hi[k] > box->hi[k])) AM_THROW("bvh: child box outside parent at node %d", ref);
             }
             rec(ca, &a, depth + 1); rec(cb, &b, depth + 1);
+#endif
         };
         rec(0, nullptr, 0);
         for (size_t i = 0; i < seen.size(); ++i) if (!seen[i]) AM_THROW("bvh: triangle %zu not referenced", i);

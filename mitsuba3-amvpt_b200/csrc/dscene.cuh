@@ -117,6 +117,50 @@ AM_D bool slab(float lox, float hix, float loy, float hiy, float loz, float hiz,
     return tmin <= tmax * (1.f + AM_SLAB_EPS);
 }
 
+// One inner-node step of the traversal: tests the children's boxes, continues with the nearest hit child and pushes the
+// others so that the nearer one is popped first; pops when nothing is hit.  Returns the next node reference.
+#if AM_BVH_WIDTH == 4
+AM_D int32_t node_step(const DScene &s, const SlabRay &r, float best, int32_t node, int32_t *stack, int &sp) {
+    const float4 *np = s.nodes + 8 * (size_t) node;
+    const float4 lx = ldg4(np), hx = ldg4(np + 1), ly = ldg4(np + 2), hy = ldg4(np + 3), lz = ldg4(np + 4), hz = ldg4(np + 5), cf = ldg4(np + 6);
+    const int32_t c0 = __float_as_int(cf.x), c1 = __float_as_int(cf.y), c2 = __float_as_int(cf.z), c3 = __float_as_int(cf.w);
+    float t0, t1, t2, t3;
+    const bool h0 = slab(lx.x, hx.x, ly.x, hy.x, lz.x, hz.x, r, best, &t0) && c0 != 0;
+    const bool h1 = slab(lx.y, hx.y, ly.y, hy.y, lz.y, hz.y, r, best, &t1) && c1 != 0;
+    const bool h2 = slab(lx.z, hx.z, ly.z, hy.z, lz.z, hz.z, r, best, &t2) && c2 != 0;
+    const bool h3 = slab(lx.w, hx.w, ly.w, hy.w, lz.w, hz.w, r, best, &t3) && c3 != 0;
+    const int n = (int) h0 + (int) h1 + (int) h2 + (int) h3;
+    if (n == 0) return stack[--sp];
+    if (n == 1) return h0 ? c0 : (h1 ? c1 : (h2 ? c2 : c3));
+    // rank of a hit child = number of hit children nearer than it (ties: lower slot first); rank 0 is visited next, the others
+    // are pushed so that rank 1 ends on top of the stack
+    t0 = h0 ? t0 : AM_INF; t1 = h1 ? t1 : AM_INF; t2 = h2 ? t2 : AM_INF; t3 = h3 ? t3 : AM_INF;
+    const int r0 = (int) (t1 < t0) + (int) (t2 < t0) + (int) (t3 < t0);
+    const int r1 = (int) (t0 <= t1) + (int) (t2 < t1) + (int) (t3 < t1);
+    const int r2 = (int) (t0 <= t2) + (int) (t1 <= t2) + (int) (t3 < t2);
+    const int r3 = (int) (t0 <= t3) + (int) (t1 <= t3) + (int) (t2 <= t3);
+    int32_t next = c3; const int top = sp + n - 1;
+    if (h0) { if (r0 == 0) next = c0; else stack[top - r0] = c0; }
+    if (h1) { if (r1 == 0) next = c1; else stack[top - r1] = c1; }
+    if (h2) { if (r2 == 0) next = c2; else stack[top - r2] = c2; }
+    if (h3 && r3 != 0) stack[top - r3] = c3;
+    sp = top;
+    return next;
+}
+#else
+AM_D int32_t node_step(const DScene &s, const SlabRay &r, float best, int32_t node, int32_t *stack, int &sp) {
+    const float4 *np = s.nodes + 4 * (size_t) node;
+    float4 n0 = ldg4(np), n1 = ldg4(np + 1), n2 = ldg4(np + 2), n3 = ldg4(np + 3);
+    float ta, tb;
+    bool ha = slab(n0.x, n0.y, n0.z, n0.w, n2.x, n2.y, r, best, &ta);
+    bool hb = slab(n1.x, n1.y, n1.z, n1.w, n2.z, n2.w, r, best, &tb);
+    int32_t ca = __float_as_int(n3.x), cb = __float_as_int(n3.y);
+    if (ha && hb) { bool swap = tb < ta; stack[sp++] = swap ? ca : cb; return swap ? cb : ca; }
+    if (ha || hb) return ha ? ca : cb;
+    return stack[--sp];
+}
+#endif
+
 // Closest hit (ANY = false) with the tie rule of ShapeKDTree::ray_intersect_naive
 // (include/mitsuba/render/kdtree.h:2445-2468): among equal t the primitive with the larger global index
 // wins.  ANY = true: Scene::ray_test semantics, first accepted triangle ends the traversal.
@@ -133,18 +177,8 @@ template <bool ANY> AM_D Hit intersect(const DScene &s, const Ray &ray, uint32_t
     stack[sp++] = AM_TRAVERSAL_DONE;
     for (;;) {
         while (node >= 0) {
-            const float4 *np = s.nodes + 4 * (size_t) node;
-            float4 n0 = ldg4(np), n1 = ldg4(np + 1), n2 = ldg4(np + 2), n3 = ldg4(np + 3);
             if (n_nodes) (*n_nodes)++;
-            float ta, tb;
-            bool ha = slab(n0.x, n0.y, n0.z, n0.w, n2.x, n2.y, sr, best, &ta);
-            bool hb = slab(n1.x, n1.y, n1.z, n1.w, n2.z, n2.w, sr, best, &tb);
-            int32_t ca = __float_as_int(n3.x), cb = __float_as_int(n3.y);
-            if (ha && hb) {
-                bool swap = tb < ta;
-                stack[sp++] = swap ? ca : cb; node = swap ? cb : ca;
-            } else if (ha || hb) node = ha ? ca : cb;
-            else node = stack[--sp];
+            node = node_step(s, sr, best, node, stack, sp);
         }
         if (node == AM_TRAVERSAL_DONE) break;
         uint32_t code = ~(uint32_t) node, first = code >> 3, count = code & 7u;

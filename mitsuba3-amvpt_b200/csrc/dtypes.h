@@ -3,7 +3,11 @@
 #include <cuda_runtime.h>
 #include "dbsdf.cuh"
 
-#define AM_STACK_SIZE 64   /* per-thread traversal stack entries; the builder bounds the tree depth accordingly */
+#ifndef AM_BVH_WIDTH
+#define AM_BVH_WIDTH 2     /* children per BVH node: 2 (default) or 4 (build with -DAM_BVH_WIDTH=4; measured slower on B200); host builder and kernels share the value */
+#endif
+#define AM_STACK_SIZE (AM_BVH_WIDTH == 4 ? 96 : 64)   /* per-thread traversal stack entries; the builder checks the tree against it */
+#define AM_NODE_F4 (AM_BVH_WIDTH == 4 ? 8 : 4)         /* float4 per node */
 
 namespace amvpt {
 
@@ -23,7 +27,9 @@ struct DMesh {
 struct DEmitter { int32_t mesh; float radiance[3]; };
 
 struct DScene {
-    // BVH2, 64 B per node = 4 x float4 (Aila-Laine layout):
+    // AM_BVH_WIDTH == 4: 128 B per node = 8 x float4: lo.x[4], hi.x[4], lo.y[4], hi.y[4], lo.z[4], hi.z[4], child refs[4], pad;
+    //   child ref 0 = empty slot (the root, node 0, is never a child), > 0 inner node, < 0 leaf as below.
+    // AM_BVH_WIDTH == 2: 64 B per node = 4 x float4 (Aila-Laine layout):
     //   n0 = (c0.lo.x, c0.hi.x, c0.lo.y, c0.hi.y)  n1 = (c1.lo.x, c1.hi.x, c1.lo.y, c1.hi.y)
     //   n2 = (c0.lo.z, c0.hi.z, c1.lo.z, c1.hi.z)  n3 = (bits c0, bits c1, -, -)
     // child >= 0: inner node index; child < 0: leaf, ~child = (first_tri << 3) | count (count <= 7)

@@ -129,12 +129,12 @@ render_pass_kernel(const DScene s, const RenderParams p) {
 //            sample and Russian roulette; the emitter sample's visibility ray is not traced here but queued in front of
 //            the next closest-hit ray, with (throughput, f * weight * mis) parked until it resolves (the fmadd into
 //            `result` then happens with the very operands the reference uses, before the next vertex adds its emission).
-// The traversal stack lives in shared memory (one column per thread), path state in registers.
-template <bool STATS, int STK> __global__ void __launch_bounds__(128)
+// Path state and the traversal stack are per thread (registers / local memory).
+template <bool STATS> __global__ void __launch_bounds__(128)
 render_stream_kernel(const DScene s, const RenderParams p) {
     enum LanePhase : int { PH_IDLE = 0, PH_TRACE = 1, PH_SHADE = 2 };
-    __shared__ int32_t stack[STK][128];
-    const unsigned lane_id = threadIdx.x & 31u, tid = threadIdx.x;
+    int32_t stack[AM_STACK_SIZE];
+    const unsigned lane_id = threadIdx.x & 31u;
     PathState ps; LaneSetup ls; TravState tv; ps.active = false;
     V3 sT = v3(0.f), sV = v3(0.f); bool shadow_pending = false;      // parked next-event contribution
     int phase = PH_IDLE; bool has_result = false, exhausted = false; // `exhausted` is warp-uniform
@@ -159,7 +159,7 @@ render_stream_kernel(const DScene s, const RenderParams p) {
                     if (ticket_to_lane(p, s, ticket, &lane, &px, &py)) {
                         lane_setup(s, p.seed_value, lane, px, py, ps, ls);
                         has_result = true; got = true;
-                        if (s.max_depth != 0) { phase = PH_TRACE; shadow_pending = false; trav_begin(tv, ps.ray, false); stack[0][tid] = AM_TRAVERSAL_DONE; tv.sp = 1; }
+                        if (s.max_depth != 0) { phase = PH_TRACE; shadow_pending = false; trav_begin(tv, ps.ray, false); stack[0] = AM_TRAVERSAL_DONE; tv.sp = 1; }
                     }
                 }
                 (void) got;
@@ -181,18 +181,8 @@ render_stream_kernel(const DScene s, const RenderParams p) {
             if (tracing) {
                 // inner nodes until this lane holds a leaf (or its ray is done)
                 while (tv.node >= 0) {
-                    const float4 *np = s.nodes + 4 * (size_t) tv.node;
-                    float4 n0 = ldg4(np), n1 = ldg4(np + 1), n2 = ldg4(np + 2), n3 = ldg4(np + 3);
                     if (STATS) st.nodes++;
-                    float ta, tb;
-                    bool ha = slab(n0.x, n0.y, n0.z, n0.w, n2.x, n2.y, tv.sr, tv.best, &ta);
-                    bool hb = slab(n1.x, n1.y, n1.z, n1.w, n2.z, n2.w, tv.sr, tv.best, &tb);
-                    int32_t ca = __float_as_int(n3.x), cb = __float_as_int(n3.y);
-                    if (ha && hb) {
-                        bool swap = tb < ta;
-                        stack[tv.sp++][tid] = swap ? ca : cb; tv.node = swap ? cb : ca;
-                    } else if (ha || hb) tv.node = ha ? ca : cb;
-                    else tv.node = stack[--tv.sp][tid];
+                    tv.node = node_step(s, tv.sr, tv.best, tv.node, stack, tv.sp);
                 }
             }
             if (tracing && tv.node != AM_TRAVERSAL_DONE) {
@@ -212,14 +202,14 @@ render_stream_kernel(const DScene s, const RenderParams p) {
                     }
                 }
                 if (occluded) { tv.h.tri = 0; tv.node = AM_TRAVERSAL_DONE; }
-                else tv.node = stack[--tv.sp][tid];
+                else tv.node = stack[--tv.sp];
             }
             if (tracing && tv.node == AM_TRAVERSAL_DONE) {
                 if (tv.any) {
                     // shadow ray resolved: unoccluded -> the parked next-event contribution enters `result`
                     if (tv.h.tri == AM_NO_HIT) ps.result = fmadd(sT, sV, ps.result);
                     shadow_pending = false;
-                    if (ps.active) { trav_begin(tv, ps.ray, false); stack[0][tid] = AM_TRAVERSAL_DONE; tv.sp = 1; }
+                    if (ps.active) { trav_begin(tv, ps.ray, false); stack[0] = AM_TRAVERSAL_DONE; tv.sp = 1; }
                     else phase = PH_IDLE;
                 } else phase = PH_SHADE;
             }
@@ -228,8 +218,8 @@ render_stream_kernel(const DScene s, const RenderParams p) {
         if (phase == PH_SHADE) {
             Ray shadow;
             bool need_shadow = shade_vertex<STATS>(s, ps, tv.h, &shadow, &sT, &sV, &st);
-            if (need_shadow) { phase = PH_TRACE; shadow_pending = true; trav_begin(tv, shadow, true); stack[0][tid] = AM_TRAVERSAL_DONE; tv.sp = 1; }
-            else if (ps.active) { phase = PH_TRACE; trav_begin(tv, ps.ray, false); stack[0][tid] = AM_TRAVERSAL_DONE; tv.sp = 1; }
+            if (need_shadow) { phase = PH_TRACE; shadow_pending = true; trav_begin(tv, shadow, true); stack[0] = AM_TRAVERSAL_DONE; tv.sp = 1; }
+            else if (ps.active) { phase = PH_TRACE; trav_begin(tv, ps.ray, false); stack[0] = AM_TRAVERSAL_DONE; tv.sp = 1; }
             else phase = PH_IDLE;
         }
     }
@@ -237,23 +227,19 @@ render_stream_kernel(const DScene s, const RenderParams p) {
     if (STATS) flush_stats(st, p.counters);
 }
 
-template <bool STATS, int STK> static void launch_stream(const DScene &s, const RenderParams &p, int sm_count, cudaStream_t stream) {
+template <bool STATS> static void launch_stream(const DScene &s, const RenderParams &p, int sm_count, cudaStream_t stream) {
     int ctas_per_sm = 0;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, render_stream_kernel<STATS, STK>, 128, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, render_stream_kernel<STATS>, 128, 0);
     if (ctas_per_sm < 1) ctas_per_sm = 1;
     unsigned grid = (unsigned) (sm_count * ctas_per_sm);
     unsigned long long ctas_needed = ((p.n_lanes + 31) / 32 + 3) / 4;
     if (ctas_needed < grid) grid = (unsigned) (ctas_needed ? ctas_needed : 1);
-    render_stream_kernel<STATS, STK><<<grid, 128, 0, stream>>>(s, p);
+    render_stream_kernel<STATS><<<grid, 128, 0, stream>>>(s, p);
 }
 
 void launch_render_pass(const DScene &s, const RenderParams &p, int mode, int sm_count, bool stats, cudaStream_t stream) {
     if (mode == 2) {
-        // shared-memory traversal stack sized by the depth of the tree (depth + sentinel entries at most)
-        uint32_t need = p.bvh_depth + 2;
-        if (need <= 16) { if (stats) launch_stream<true, 16>(s, p, sm_count, stream); else launch_stream<false, 16>(s, p, sm_count, stream); }
-        else if (need <= 32) { if (stats) launch_stream<true, 32>(s, p, sm_count, stream); else launch_stream<false, 32>(s, p, sm_count, stream); }
-        else { if (stats) launch_stream<true, AM_STACK_SIZE>(s, p, sm_count, stream); else launch_stream<false, AM_STACK_SIZE>(s, p, sm_count, stream); }
+        if (stats) launch_stream<true>(s, p, sm_count, stream); else launch_stream<false>(s, p, sm_count, stream);
         return;
     }
     // persistent grid: a whole number of CTAs per SM

@@ -254,7 +254,7 @@ void Scene::commit(int dev) {
     allocs.clear(); wf = WfPool{};
     cudaDeviceProp prop; AM_CUDA(cudaGetDeviceProperties(&prop, dev)); sm_count = prop.multiProcessorCount;
     prepare_host();
-    n_nodes = (uint32_t) (bvh.nodes.size() / 4); n_tris = (uint32_t) (bvh.tris.size() / 3);
+    n_nodes = (uint32_t) (bvh.nodes.size() / AM_NODE_F4); n_tris = (uint32_t) (bvh.tris.size() / 3);
     std::vector<DMesh> dm; std::vector<float> cdf_all, pmf_all; bool any_nrm = false;
     for (auto &m : meshes) {
         DMesh q{}; q.bsdf = m.bsdf; q.emitter = m.emitter; q.flip_normals = m.flip_normals; q.has_normals = m.nrm.empty() ? 0 : 1;

@@ -106,16 +106,8 @@ wf_trace_kernel(const DScene s, const RenderParams p, const WfPool w, uint32_t f
                 const unsigned dm = __ballot_sync(0xffffffffu, desc);
                 if (dm == 0 || __popc(bm & ~dm) >= (int) leaf_min) break;
                 if (desc) {
-                    const float4 *np = s.nodes + 4 * (size_t) tv.node;
-                    float4 n0 = ldg4(np), n1 = ldg4(np + 1), n2 = ldg4(np + 2), n3 = ldg4(np + 3);
                     if (STATS) st.nodes++;
-                    float ta, tb;
-                    bool ha = slab(n0.x, n0.y, n0.z, n0.w, n2.x, n2.y, tv.sr, tv.best, &ta);
-                    bool hb = slab(n1.x, n1.y, n1.z, n1.w, n2.z, n2.w, tv.sr, tv.best, &tb);
-                    int32_t ca = __float_as_int(n3.x), cb = __float_as_int(n3.y);
-                    if (ha && hb) { bool swap = tb < ta; stack[tv.sp++] = swap ? ca : cb; tv.node = swap ? cb : ca; }
-                    else if (ha || hb) tv.node = ha ? ca : cb;
-                    else tv.node = stack[--tv.sp];
+                    tv.node = node_step(s, tv.sr, tv.best, tv.node, stack, tv.sp);
                 }
             }
         }

@@ -56,7 +56,7 @@ def test_bvh_structure(pkg, scenes):
         s = scenes.build(desc, commit=False)
         depth, leaves = s.bvh_validate()       # throws if a triangle leaves its leaf box, a child leaves its parent, or a triangle is lost
         n = s.info()["n_prims"]
-        assert leaves * 4 >= n and depth <= 62 and depth >= int(np.log2(max(n / 4, 1)))
+        assert leaves * 4 >= n and depth <= 62 and depth >= int(np.log2(max(n / 4, 1)) / 2)      # nodes are 4-wide (or 2-wide) 
     # degenerate inputs: one triangle, coincident triangles, zero-area triangle
     s = pkg.Scene(); b = s.add_bsdf(type="diffuse")
     tri = np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0]], np.float32)
