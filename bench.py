@@ -237,7 +237,7 @@ def main():
     traffic, traffic_src = None, None
     try:
         tr = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json")))[kernel]
-        units = ks["paths"] / ks["launches"] if kernel == "render_pass_kernel" else float(s.info().get("wf_pool", 1 << 21))
+        units = ks["paths"] / ks["launches"] if kernel == "render_pass_kernel" else float(int(os.environ.get("AMVPT_WF_POOL", 1 << 22)))
         traffic = tr["dram_bytes_per_launch"] * units / tr.get("paths_per_launch", tr.get("slots_per_launch"))
         traffic_src = f'{tr["source"]} ({tr["workload"]}), scaled by launch size'
     except Exception:

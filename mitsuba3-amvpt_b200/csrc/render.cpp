@@ -98,8 +98,8 @@ void render(Scene &s, const RenderOptions &opt) {
         p.n_tiles = (uint32_t) tiles.size(); p.n_lanes = lanes;
         if (mode == 3) {
             if (!s.wf.n_slots) {
-                // pool size: a multiple of the CTA size; 2^21 slots (~420 MB of state and queues) = several resident waves of 148 SMs
-                uint32_t n = getenv("AMVPT_WF_POOL") ? (uint32_t) atoi(getenv("AMVPT_WF_POOL")) : (1u << 21);
+                // pool size: a multiple of the CTA size; 2^22 slots (~860 MB of state and queues; measured 193 / 209 / 217 Mpaths/s at 2^20 / 2^21 / 2^22 on the 1M-triangle scene)
+                uint32_t n = getenv("AMVPT_WF_POOL") ? (uint32_t) atoi(getenv("AMVPT_WF_POOL")) : (1u << 22);
                 n = std::max(128u, (n + 127u) / 128u * 128u);
                 WfPool &w = s.wf; w.n_slots = n;
                 float4 **f4s[] = { &w.ro, &w.rd, &w.tp, &w.res, &w.pp, &w.hit, &w.so, &w.sd, &w.sT, &w.sV };

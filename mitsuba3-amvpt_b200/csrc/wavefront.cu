@@ -66,7 +66,10 @@ wf_regen_kernel(const DScene s, const RenderParams p, const WfPool w, uint32_t i
 // if the slot's flag says so).  Persistent warps pull tasks from one counter: whenever at least fetch_min lanes of a warp have
 // finished their ray they take the next task ids together (one atomic per warp, ballot + popc prefix), so the traversal loop
 // keeps running with nearly full warps although rays differ widely in length (Aila & Laine's dynamic fetch).
-template <bool STATS> __global__ void __launch_bounds__(128)
+#ifndef AM_WT_MIN_CTAS
+#define AM_WT_MIN_CTAS 10   /* 51 registers: +2 % on the 1M-triangle scene; 12 (40 registers) spills and loses 3 % */
+#endif
+template <bool STATS> __global__ void __launch_bounds__(128, AM_WT_MIN_CTAS)
 wf_trace_kernel(const DScene s, const RenderParams p, const WfPool w, uint32_t fetch_min, uint32_t leaf_min) {
     const unsigned lane_id = threadIdx.x & 31u;
     const uint32_t n_tasks = 2u * w.n_slots;
