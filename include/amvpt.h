@@ -91,9 +91,11 @@ int amvpt_scene_set_sensor_grid(amvpt_scene *s, const amvpt_grid_sensor_desc *d)
 int amvpt_scene_set_sensor_batch(amvpt_scene *s, uint32_t n, uint32_t res_x, uint32_t res_y, const float *sample_to_camera,
                                  const float *to_world, float near_clip, float far_clip, int reverse_x);
 int amvpt_scene_set_integrator(amvpt_scene *s, const amvpt_integrator_desc *d);
-/* reconstruction filter of the film (src/rfilters/{box,gaussian,tent}.cpp; ImageBlock::put, src/render/imageblock.cpp:174-558):
- * type 0 box (default of this API), 1 gaussian (param = stddev, Mitsuba's default filter with stddev 0.5), 2 tent (param = radius) */
-int amvpt_scene_set_rfilter(amvpt_scene *s, int type, float param);
+/* reconstruction filter of the film (src/rfilters/{box,gaussian,tent,mitchell,catmullrom,lanczos}.cpp; ImageBlock::put,
+ * src/render/imageblock.cpp:174-558): type 0 box (default of this API), 1 gaussian (param = stddev, Mitsuba's default filter with
+ * stddev 0.5), 2 tent (param = radius), 3 mitchell (param = B, param2 = C; both default to 1/3 in the reference), 4 catmullrom,
+ * 5 lanczos (param = lobes, a positive integer; reference default 3).  param2 is ignored by every type but 3. */
+int amvpt_scene_set_rfilter(amvpt_scene *s, int type, float param, float param2);
 /* builds the BVH and uploads everything to `device` (Scene::Scene accel_init, src/render/scene.cpp:70-73) */
 int amvpt_scene_commit(amvpt_scene *s, int device);
 int amvpt_scene_info(amvpt_scene *s, uint32_t *film_w, uint32_t *film_h, uint32_t *n_views, uint32_t *n_prims,

@@ -96,6 +96,7 @@ def _f32(a, shape=None):
 
 BSDF_TYPES = {"diffuse": 0, "conductor": 1, "dielectric": 2, "roughconductor": 3, "roughdielectric": 4, "roughplastic": 5}
 FOV_AXES = {"x": 0, "y": 1, "diagonal": 2, "smaller": 3, "larger": 4}
+RFILTERS = {"box": 0, "gaussian": 1, "tent": 2, "mitchell": 3, "catmullrom": 4, "lanczos": 5}
 SCHEDULERS = {"warp_batch": 0, "regenerate": 1, "stream": 2, "wavefront": 3, "auto": 4}
 
 
@@ -166,9 +167,10 @@ class Scene:
         d = IntegratorDesc(max_depth, rr_depth, int(hide_emitters), spp_pass_lim, sampler_seed, sample_count)
         _chk(lib.amvpt_scene_set_integrator(self._h, C.byref(d)))
 
-    def set_rfilter(self, type="box", param=0.5):
-        """Film reconstruction filter: 'box', 'gaussian' (param = stddev) or 'tent' (param = radius)."""
-        _chk(lib.amvpt_scene_set_rfilter(self._h, C.c_int({"box": 0, "gaussian": 1, "tent": 2}[type]), C.c_float(param)))
+    def set_rfilter(self, type="box", param=0.5, param2=0.0):
+        """Film reconstruction filter: 'box', 'gaussian' (param = stddev), 'tent' (param = radius), 'mitchell' (param = B,
+        param2 = C), 'catmullrom' or 'lanczos' (param = lobes)."""
+        _chk(lib.amvpt_scene_set_rfilter(self._h, C.c_int(RFILTERS[type]), C.c_float(param), C.c_float(param2)))
 
     def commit(self, device=0):
         _chk(lib.amvpt_scene_commit(self._h, C.c_int(device)))

@@ -108,8 +108,8 @@ int amvpt_scene_set_integrator(amvpt_scene *h, const amvpt_integrator_desc *d) {
         if (h->s->committed) { h->s->d.max_depth = ip.max_depth < 0 ? 0xffffffffu : (uint32_t) ip.max_depth; h->s->d.rr_depth = ip.rr_depth; }
         return AMVPT_OK; });
 }
-int amvpt_scene_set_rfilter(amvpt_scene *h, int type, float param) {
-    return guard([&] { NEED(h); h->s->set_rfilter(type, param); return AMVPT_OK; });
+int amvpt_scene_set_rfilter(amvpt_scene *h, int type, float param, float param2) {
+    return guard([&] { NEED(h); h->s->set_rfilter(type, param, param2); return AMVPT_OK; });
 }
 int amvpt_scene_commit(amvpt_scene *h, int device) {
     return guard([&] { NEED(h); need_device(device); h->s->commit(device); return AMVPT_OK; });

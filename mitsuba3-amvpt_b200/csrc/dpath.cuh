@@ -87,7 +87,21 @@ AM_D void splat_aggregated(unsigned mask, bool do_put, uint32_t pixel, float4 va
 // floor(pos) - n; every covered pixel inside the film receives {R, G, B, 1} * w_y * w_x as one 16-byte reduction.
 AM_D float filter_eval(const DScene &s, float x) {
     if (s.filter_type == 1) return max_(estrin10(x * x, s.filter_coeff), 0.f);        // gaussian.cpp:94-97
-    return max_(0.f, 1.f - fabs_(x * s.filter_inv_radius));                            // tent.cpp:54-56
+    if (s.filter_type == 2) return max_(0.f, 1.f - fabs_(x * s.filter_inv_radius));   // tent.cpp:54-56
+    x = fabs_(x);
+    if (s.filter_type == 5) {                                                          // lanczos.cpp:57-67
+        float x1 = AM_PI * x, x2 = fdiv(x1, s.filter_radius), s1, s2, c;
+        sincos_(x1, &s1, &c); sincos_(x2, &s2, &c);
+        const float result = fdiv(s1 * s2, x1 * x2);
+        return x < AM_EPSILON ? 1.f : (x > s.filter_radius ? 0.f : result);
+    }
+    const float x2 = x * x, x3 = x2 * x; const float *k = s.filter_coeff; float r;
+    if (s.filter_type == 3)                                                            // mitchell.cpp:59-78, coefficients set at commit
+        r = x < 1.f ? fmadd(k[0], x3, fmadd(k[1], x2, k[2])) : fmadd(k[3], x3, fmadd(k[4], x2, fmadd(k[5], x, k[6])));
+    else                                                                               // catmullrom.cpp:39-53 with B = 0, C = 1/2 folded
+        r = x < 1.f ? (9.f * x3 + -15.f * x2) + 6.f : ((-3.f * x3 + 15.f * x2) + -24.f * x) + 12.f;
+    r = (1.f / 6.f) * r;
+    return x < 2.f ? r : 0.f;
 }
 AM_D void splat_filtered(const DScene &s, float spx, float spy, V3 L, float4 *film) {
     const uint32_t n = (uint32_t) (int32_t) ceilf(s.filter_radius - .5f), count = 2 * n + 1;

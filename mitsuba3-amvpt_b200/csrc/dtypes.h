@@ -48,7 +48,8 @@ struct DScene {
     int32_t reverse_x, reverse_y, thinlens, pad0;
     uint32_t film_w, film_h;
     uint32_t max_depth, rr_depth;
-    // film reconstruction filter: 0 box, 1 gaussian (polynomial of src/rfilters/gaussian.cpp:52-103), 2 tent (tent.cpp:48-56)
+    // film reconstruction filter: 0 box, 1 gaussian (polynomial of src/rfilters/gaussian.cpp:52-103), 2 tent (tent.cpp:48-56),
+    // 3 mitchell (coeff[0..6] = a3 a2 a0 b3 b2 b1 b0, mitchell.cpp:63-69), 4 catmullrom, 5 lanczos (radius = lobes)
     int32_t filter_type; float filter_radius, filter_inv_radius; float filter_coeff[10];
 };
 

@@ -65,8 +65,9 @@ struct Scene {
     bool multi_sensor = false;
     uint32_t film_w = 0, film_h = 0;
     uint32_t sample_count = 4, sampler_seed = 0;
-    int rfilter_type = 0; float rfilter_param = 0.5f;    // film reconstruction filter: 0 box, 1 gaussian (stddev), 2 tent (radius)
-    void set_rfilter(int type, float param);
+    // film reconstruction filter: 0 box, 1 gaussian (stddev), 2 tent (radius), 3 mitchell (B, C), 4 catmullrom, 5 lanczos (lobes)
+    int rfilter_type = 0; float rfilter_param = 0.5f, rfilter_param2 = 0.f;
+    void set_rfilter(int type, float param, float param2 = 0.f);
     IntegratorParams integrator;
     // ---- device mirror
     int device = -1, sm_count = 148;

@@ -211,13 +211,15 @@ void Scene::set_sensor_explicit(uint32_t n, uint32_t rx, uint32_t ry, const floa
     }
     committed = false;
 }
-// ReconstructionFilter plugins of the film (src/rfilters/{box,gaussian,tent}.cpp)
-void Scene::set_rfilter(int type, float param) {
-    if (type < 0 || type > 2) AM_THROW("rfilter: unknown filter type %d (0 box, 1 gaussian, 2 tent)", type);
-    if (type != 0 && !(param > 0.f)) AM_THROW("rfilter: the %s must be positive", type == 1 ? "standard deviation" : "radius");
-    float radius = type == 1 ? 4.f * param : (type == 2 ? param : .5f);
+// ReconstructionFilter plugins of the film (src/rfilters/{box,gaussian,tent,mitchell,catmullrom,lanczos}.cpp)
+void Scene::set_rfilter(int type, float param, float param2) {
+    if (type < 0 || type > 5) AM_THROW("rfilter: unknown filter type %d (0 box, 1 gaussian, 2 tent, 3 mitchell, 4 catmullrom, 5 lanczos)", type);
+    if ((type == 1 || type == 2) && !(param > 0.f)) AM_THROW("rfilter: the %s must be positive", type == 1 ? "standard deviation" : "radius");
+    if (type == 3 && !(std::isfinite(param) && std::isfinite(param2))) AM_THROW("rfilter: mitchell B and C must be finite");
+    if (type == 5 && !(param >= 1.f && param == std::floor(param))) AM_THROW("rfilter: lanczos lobes must be a positive integer");
+    float radius = type == 1 ? 4.f * param : (type == 2 || type == 5 ? param : (type == 3 || type == 4 ? 2.f : .5f));
     if (std::ceil(radius - .5f) > 7.f) AM_THROW("rfilter: radius %g is too large (footprint limited to 15 x 15 pixels)", radius);
-    rfilter_type = type; rfilter_param = param; committed = false;
+    rfilter_type = type; rfilter_param = param; rfilter_param2 = param2; committed = false;
 }
 // View tiles of the quilt owned by one rank: view v = ix + grid_x * iy (sub-sensor index), tile position follows
 // GridSensor::sample_ray's axis reversal (grid.cpp:246-255).
@@ -279,6 +281,13 @@ void Scene::commit(int dev) {
         for (int i = 0; i < 10; ++i) { d.filter_coeff[i] = (float) (coeff[i] * scale); scale /= (double) stddev * (double) stddev; }
         d.filter_coeff[0] -= estrin10(d.filter_radius * d.filter_radius, d.filter_coeff);
     } else if (rfilter_type == 2) { d.filter_radius = rfilter_param; d.filter_inv_radius = 1.f / rfilter_param; }
+    else if (rfilter_type == 3) {     // MitchellNetravaliFilter::eval's scalar coefficients (mitchell.cpp:63-69)
+        const float B = rfilter_param, C = rfilter_param2; d.filter_radius = 2.f;
+        const float c[7] = { 12.f - 9.f * B - 6.f * C, -18.f + 12.f * B + 6.f * C, 6.f - 2.f * B,
+                             -B - 6.f * C, 6.f * B + 30.f * C, -12.f * B - 48.f * C, 8.f * B + 24.f * C };
+        for (int i = 0; i < 7; ++i) d.filter_coeff[i] = c[i];
+    } else if (rfilter_type == 4) d.filter_radius = 2.f;
+    else if (rfilter_type == 5) d.filter_radius = rfilter_param;
     size_t npix = (size_t) film_w * film_h;
     film = (float4 *) dalloc(npix * sizeof(float4)); moments = (float2 *) dalloc(npix * sizeof(float2)); rgb = nullptr;
     counters = (unsigned long long *) dalloc(sizeof(unsigned long long) * CTR_COUNT);

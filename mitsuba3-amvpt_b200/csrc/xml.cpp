@@ -426,17 +426,20 @@ struct Builder {
         f->s("component_format", "float16"); f->s("file_format", "openexr"); f->b("sample_border", false); f->b("compensate", false);
         for (const char *c : { "crop_offset_x", "crop_offset_y", "crop_width", "crop_height" }) if (f->has(c)) AM_THROW("%s: film crop windows are not supported on this path", f->where.c_str());
         // hdrfilm's default reconstruction filter is the gaussian with stddev 0.5 (src/render/film.cpp:34-40)
-        int ftype = 1; float fparam = 0.5f; bool have_filter = false;
+        int ftype = 1; float fparam = 0.5f, fparam2 = 0.f; bool have_filter = false;
         for (auto &k : f->children()) {
             if (k->cls != "rfilter") AM_THROW("%s: unexpected child <%s> of a film", f->where.c_str(), k->cls.c_str());
             if (have_filter) AM_THROW("%s: A film can only have one reconstruction filter.", f->where.c_str());
             if (k->type == "box") { ftype = 0; fparam = 0.5f; }
             else if (k->type == "gaussian") { ftype = 1; fparam = (float) k->f("stddev", 0.5); }
             else if (k->type == "tent") { ftype = 2; fparam = (float) k->f("radius", 1.0); }
-            else AM_THROW("%s: reconstruction filter \"%s\" is not part of the AMVPT path (supported: box, gaussian, tent)", k->where.c_str(), k->type.c_str());
+            else if (k->type == "mitchell") { ftype = 3; fparam = (float) k->f("B", 1.0 / 3.0); fparam2 = (float) k->f("C", 1.0 / 3.0); }
+            else if (k->type == "catmullrom") { ftype = 4; fparam = 0.f; }
+            else if (k->type == "lanczos") { ftype = 5; fparam = (float) k->i("lobes", 3); }
+            else AM_THROW("%s: unknown reconstruction filter \"%s\" (box, gaussian, tent, mitchell, catmullrom, lanczos)", k->where.c_str(), k->type.c_str());
             k->check_unqueried(); f->mark(k); have_filter = true;
         }
-        sc.set_rfilter(ftype, fparam);
+        sc.set_rfilter(ftype, fparam, fparam2);
         f->check_unqueried();
     }
     void sampler(Obj *s) {

@@ -192,6 +192,12 @@ def write_ply(path, positions, faces, normals=None, binary=True):
 def _rfilter_xml(rf):
     if not rf or rf[0] == "box":
         return '<rfilter type="box"/>'
+    if rf[0] == "catmullrom":
+        return '<rfilter type="catmullrom"/>'
+    if rf[0] == "lanczos":
+        return f'<rfilter type="lanczos"><integer name="lobes" value="{int(rf[1])}"/></rfilter>'
+    if rf[0] == "mitchell":
+        return f'<rfilter type="mitchell"><float name="B" value="{_fmt(rf[1])}"/><float name="C" value="{_fmt(rf[2])}"/></rfilter>'
     key = "stddev" if rf[0] == "gaussian" else "radius"
     return f'<rfilter type="{rf[0]}"><float name="{key}" value="{_fmt(rf[1])}"/></rfilter>'
 

@@ -494,8 +494,10 @@ static LaneOut render_lane(const Scene &s, uint32_t seed_value, uint32_t lane, u
 }
 
 // ReconstructionFilter::eval: GaussianFilter (gaussian.cpp:94-103, the non-CUDA branch: a degree-9 polynomial in x^2 fitted
-// to exp(-x^2 / (2 stddev^2)), shifted so that it reaches zero at the radius, :52-88) and TentFilter (tent.cpp:54-56)
-static void filter_setup(Scene &s, int type, float param) {
+// to exp(-x^2 / (2 stddev^2)), shifted so that it reaches zero at the radius, :52-88), TentFilter (tent.cpp:54-56),
+// MitchellNetravaliFilter (mitchell.cpp:50-78; param = B, param2 = C), CatmullRomFilter (catmullrom.cpp:34-53) and
+// LanczosSincFilter (lanczos.cpp:52-67; param = lobes)
+static void filter_setup(Scene &s, int type, float param, float param2) {
     s.filter_type = type;
     if (type == 1) {
         static const double coeff[10] = { 9.992604880e-1, -4.977025247e-1, 1.222248550e-1, -1.932406282e-2, 2.136713061e-3,
@@ -505,11 +507,31 @@ static void filter_setup(Scene &s, int type, float param) {
         for (int i = 0; i < 10; ++i) { s.filter_coeff[i] = (float) (coeff[i] * scale); scale /= (double) stddev * (double) stddev; }
         s.filter_coeff[0] -= estrin(s.filter_radius * s.filter_radius, s.filter_coeff, 10);
     } else if (type == 2) { s.filter_radius = param; s.filter_inv_radius = 1.f / param; }
+    else if (type == 3) {
+        float B = param, C = param2; s.filter_radius = 2.f;
+        float c[7] = { 12.f - 9.f * B - 6.f * C, -18.f + 12.f * B + 6.f * C, 6.f - 2.f * B,
+                       -B - 6.f * C, 6.f * B + 30.f * C, -12.f * B - 48.f * C, 8.f * B + 24.f * C };
+        for (int i = 0; i < 7; ++i) s.filter_coeff[i] = c[i];
+    } else if (type == 4) s.filter_radius = 2.f;
+    else if (type == 5) s.filter_radius = param;
     else s.filter_radius = 0.5f;
 }
 static inline float filter_eval(const Scene &s, float x) {
     if (s.filter_type == 1) return std::max(estrin(x * x, s.filter_coeff, 10), 0.f);
-    return std::max(0.f, 1.f - std::fabs(x * s.filter_inv_radius));
+    if (s.filter_type == 2) return std::max(0.f, 1.f - std::fabs(x * s.filter_inv_radius));
+    x = std::fabs(x);
+    if (s.filter_type == 5) {
+        float x1 = Pi * x, x2 = x1 / s.filter_radius, s1, s2, c;
+        sincos(x1, &s1, &c); sincos(x2, &s2, &c);
+        float result = (s1 * s2) / (x1 * x2);
+        return x < Epsilon ? 1.f : (x > s.filter_radius ? 0.f : result);
+    }
+    float x2 = x * x, x3 = x2 * x, r;
+    const float *k = s.filter_coeff;
+    if (s.filter_type == 3) r = x < 1.f ? fmadd(k[0], x3, fmadd(k[1], x2, k[2])) : fmadd(k[3], x3, fmadd(k[4], x2, fmadd(k[5], x, k[6])));
+    else r = x < 1.f ? (9.f * x3 + -15.f * x2) + 6.f : ((-3.f * x3 + 15.f * x2) + -24.f * x) + 12.f;
+    r = (1.f / 6.f) * r;
+    return x < 2.f ? r : 0.f;
 }
 // ImageBlock::put, coalesced accumulation (src/render/imageblock.cpp:433-505) into a block without border (film->create_block()
 // defaults, hdrfilm.cpp:276-291), normalize = false: the footprint (2n+1)^2, n = ceil(radius - 1/2), around floor(pos) - n
@@ -623,9 +645,10 @@ void orc_set_integrator(void *sp, int64_t max_depth, uint32_t rr_depth, int hide
     s.max_depth = max_depth < 0 ? 0xffffffffu : (uint32_t) max_depth;        // integrator.cpp:503-520
     s.rr_depth = rr_depth; s.hide_emitters = hide_emitters; s.base_seed = sampler_seed;
 }
-// film reconstruction filter: type 0 box, 1 gaussian (param = stddev), 2 tent (param = radius)
-void orc_set_rfilter(void *sp, int type, float param) { filter_setup(*(Scene *) sp, type, param); }
-void orc_filter_eval(int type, float param, const float *x, int n, float *out) { Scene s; filter_setup(s, type, param); for (int i = 0; i < n; ++i) out[i] = filter_eval(s, x[i]); }
+// film reconstruction filter: type 0 box, 1 gaussian (param = stddev), 2 tent (param = radius), 3 mitchell (param = B, param2 = C),
+// 4 catmullrom, 5 lanczos (param = lobes)
+void orc_set_rfilter(void *sp, int type, float param, float param2) { filter_setup(*(Scene *) sp, type, param, param2); }
+void orc_filter_eval(int type, float param, float param2, const float *x, int n, float *out) { Scene s; filter_setup(s, type, param, param2); for (int i = 0; i < n; ++i) out[i] = filter_eval(s, x[i]); }
 void orc_prepare(void *sp) { bvh_build(*(Scene *) sp); }
 void orc_film_size(void *sp, uint32_t *w, uint32_t *h) { Scene &s = *(Scene *) sp; *w = s.film_w; *h = s.film_h; }
 uint32_t orc_num_prims(void *sp) { return ((Scene *) sp)->nprims(); }

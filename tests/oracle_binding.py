@@ -6,6 +6,8 @@ import os
 import subprocess
 import numpy as np
 
+RFILTERS = {"box": 0, "gaussian": 1, "tent": 2, "mitchell": 3, "catmullrom": 4, "lanczos": 5}
+
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 ORACLE_DIR = os.path.join(ROOT, "oracle")
 ORACLE_SO = os.path.join(ORACLE_DIR, "libamvpt_oracle.so")
@@ -129,8 +131,8 @@ class OracleScene:
         self.spp_pass_lim = spp_pass_lim
         self.o.orc_set_integrator(self.h, C.c_int64(max_depth), C.c_uint32(rr_depth), C.c_int(int(hide_emitters)), C.c_uint32(sampler_seed))
 
-    def set_rfilter(self, type="box", param=0.5):
-        self.o.orc_set_rfilter(self.h, C.c_int({"box": 0, "gaussian": 1, "tent": 2}[type]), C.c_float(param))
+    def set_rfilter(self, type="box", param=0.5, param2=0.0):
+        self.o.orc_set_rfilter(self.h, C.c_int(RFILTERS[type]), C.c_float(param), C.c_float(param2))
 
     def prepare(self):
         self.o.orc_prepare(self.h)
@@ -200,6 +202,6 @@ def sampler_stream(seed_value, lane, n):
     out = np.zeros(n, np.float32); orc().orc_sampler_stream(C.c_uint32(seed_value), C.c_uint32(lane), C.c_int(n), _p(out)); return out
 
 
-def filter_eval(type, param, x):
+def filter_eval(type, param, x, param2=0.0):
     x = np.ascontiguousarray(x, np.float32); out = np.zeros_like(x)
-    orc().orc_filter_eval(C.c_int({"box": 0, "gaussian": 1, "tent": 2}[type]), C.c_float(param), _p(x), C.c_int(len(x)), _p(out)); return out
+    orc().orc_filter_eval(C.c_int(RFILTERS[type]), C.c_float(param), C.c_float(param2), _p(x), C.c_int(len(x)), _p(out)); return out

@@ -181,17 +181,26 @@ def test_reconstruction_filters_known_answers_and_film(ob, scenes):
     g = ob.filter_eval("gaussian", 0.5, [0.2, 2.1, 0.0, 2.0, -0.2]); t = ob.filter_eval("tent", 1.0, [0.1, 1.1, -0.5])
     assert abs(g[0] - 0.9227) < 8e-3 and g[1] == 0 and abs(g[2] - 1.0) < 2e-3 and g[3] < 1e-5 and g[0] == g[4]
     assert abs(t[0] - 0.903) < 5e-2 and t[1] == 0 and t[2] == 0.5
-    for rf in (("gaussian", 0.5), ("tent", 1.0)):
+    # test_rfilter.py:48-52 (mitchell), :54-58 (catmullrom), :60-64 (lanczos)
+    m = ob.filter_eval("mitchell", 1 / 3, [0.0, 2.1, 1.0, -1.5], 1 / 3); c = ob.filter_eval("catmullrom", 0, [0.0, 2.1, 1.0, 0.5])
+    z = ob.filter_eval("lanczos", 3, [1.4, 3.1, 0.0, 1.0, -1.4])
+    assert abs(m[0] - 0.8888) < 1e-3 and m[1] == 0 and abs(m[2] - 1 / 18) < 1e-6 and abs(m[3] - (-7 / 3 * 3.375 + 12 * 2.25 - 20 * 1.5 + 32 / 3) / 6) < 1e-6
+    assert abs(c[0] - 0.9765) < 5e-2 and c[0] == 1.0 and c[1] == 0 and c[2] == 0 and c[3] == np.float32(0.5625)
+    assert abs(z[0] - (-0.14668)) < 1e-2 and z[1] == 0 and z[2] == 1 and abs(z[3]) < 1e-6 and z[0] == z[4]
+    x = np.linspace(0, 3, 7, dtype=np.float32)[1:-1]; want = np.sinc(x.astype(np.float64)) * np.sinc(x.astype(np.float64) / 3)
+    assert np.allclose(ob.filter_eval("lanczos", 3, x), want, atol=2e-6)
+    radii = {"gaussian": 2.0, "tent": 1.0, "mitchell": 2.0, "catmullrom": 2.0, "lanczos": 2.0}
+    for rf in (("gaussian", 0.5), ("tent", 1.0), ("mitchell", 1 / 3, 1 / 3), ("catmullrom", 0.0), ("lanczos", 2)):
         desc = scenes.cornell_box(grid_x=2, grid_y=1, view_res=12, spp_pass_lim=4, sample_count=4); desc["rfilter"] = rf
         o = ob.OracleScene(desc); film, _, _ = o.render(seed=0, spp=4, brute=True, nthreads=3)
         film1, _, _ = o.render(seed=0, spp=4, brute=True, nthreads=1)
         assert np.allclose(film, film1, rtol=0, atol=1e-5 * film1.max())            # per-thread films summed = sequential film
         W, H = o.film_size(); pos = o.trace_lanes(0, 4, 0, W * H * 4, trace=False)["sample_pos"]
-        radius = 2.0 if rf[0] == "gaussian" else 1.0; n = int(np.ceil(radius - 0.5)); want = np.zeros((H, W))
+        radius = radii[rf[0]]; n = int(np.ceil(radius - 0.5)); want = np.zeros((H, W)); p2 = rf[2] if len(rf) > 2 else 0.0
         for sx, sy in pos.astype(np.float64):
             ix, iy = int(np.floor(sx)) - n, int(np.floor(sy)) - n
-            wx = ob.filter_eval(rf[0], rf[1], np.float32(ix + 0.5 - sx) + np.arange(2 * n + 1, dtype=np.float32))
-            wy = ob.filter_eval(rf[0], rf[1], np.float32(iy + 0.5 - sy) + np.arange(2 * n + 1, dtype=np.float32))
+            wx = ob.filter_eval(rf[0], rf[1], np.float32(ix + 0.5 - sx) + np.arange(2 * n + 1, dtype=np.float32), p2)
+            wy = ob.filter_eval(rf[0], rf[1], np.float32(iy + 0.5 - sy) + np.arange(2 * n + 1, dtype=np.float32), p2)
             for j in range(2 * n + 1):
                 for i in range(2 * n + 1):
                     if 0 <= ix + i < W and 0 <= iy + j < H:

@@ -124,8 +124,13 @@ def test_xml_errors(pkg, tmp_path):
     assert load(sensor + shape).info()["n_prims"] == 12
     assert load(sensor.replace('<rfilter type="box"/>', '') + shape).info()["n_prims"] == 12      # hdrfilm default: gaussian, stddev 0.5
     assert load(sensor.replace('<rfilter type="box"/>', '<rfilter type="tent"><float name="radius" value="1.5"/></rfilter>') + shape).info()["n_prims"] == 12
-    with pytest.raises(pkg.AmvptError, match="not part of the AMVPT path"):
-        load(sensor.replace('type="box"', 'type="lanczos"') + shape)
+    for rf in ('<rfilter type="lanczos"><integer name="lobes" value="4"/></rfilter>', '<rfilter type="catmullrom"/>', '<rfilter type="mitchell"/>',
+               '<rfilter type="mitchell"><float name="B" value="0.55"/><float name="C" value="0.2"/></rfilter>'):
+        assert load(sensor.replace('<rfilter type="box"/>', rf) + shape).info()["n_prims"] == 12
+    with pytest.raises(pkg.AmvptError, match="unknown reconstruction filter"):
+        load(sensor.replace('type="box"', 'type="sinc"') + shape)
+    with pytest.raises(pkg.AmvptError, match="too large"):
+        load(sensor.replace('<rfilter type="box"/>', '<rfilter type="lanczos"><integer name="lobes" value="9"/></rfilter>') + shape)
     with pytest.raises(pkg.AmvptError, match="requires MultiSensor"):           # mvpath.cpp:15-17
         load('<integrator type="mvpath"/>' + sensor + shape)
     with pytest.raises(pkg.AmvptError, match="undefined parameter"):

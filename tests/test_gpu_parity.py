@@ -289,7 +289,8 @@ def test_stream_scheduler_depth_edge_cases_and_thresholds(scenes, gpu):
             assert np.array_equal(a[..., 3], b[..., 3]) and np.array_equal(bits(a[one]), bits(b[one])), f"max_depth={md} rr={rr} wavefront pool={pool}"
 
 
-@pytest.mark.parametrize("rf", [("gaussian", 0.5), ("tent", 1.0), ("gaussian", 0.3)])
+@pytest.mark.parametrize("rf", [("gaussian", 0.5), ("tent", 1.0), ("gaussian", 0.3), ("mitchell", 1 / 3, 1 / 3), ("mitchell", 0.55, 0.2),
+                                ("catmullrom", 0.0), ("lanczos", 3)])
 def test_reconstruction_filter_film_matches_oracle(rf, scenes, ob, gpu):
     """ImageBlock::put with a non-box filter (coalesced path, src/render/imageblock.cpp:433-505): every sample is spread over
     (2n+1)^2 pixels with separable weights, across view-tile boundaries of the quilt and clipped at the film border."""
