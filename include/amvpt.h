@@ -91,6 +91,11 @@ int amvpt_scene_set_sensor_grid(amvpt_scene *s, const amvpt_grid_sensor_desc *d)
 int amvpt_scene_set_sensor_batch(amvpt_scene *s, uint32_t n, uint32_t res_x, uint32_t res_y, const float *sample_to_camera,
                                  const float *to_world, float near_clip, float far_clip, int reverse_x);
 int amvpt_scene_set_integrator(amvpt_scene *s, const amvpt_integrator_desc *d);
+/* cross-view sample reuse of the mvpath integrator (src/integrators/mvpath.h:120-129: sa_reuse, sa_mis, fast_mis, reuse_count,
+ * adaptive; render_multisample / sample_multi, mvpath_multi.h:8-358).  Reuse is active when sa_reuse, more than one sub-sensor
+ * and reuse_count != 1; *n_samples receives the number of cameras per group after the divisor rule of mvpath.cpp:192-218
+ * (0 = off).  `adaptive` > 0 (the fill-in pass, mvpath_multi.h:79-115) is rejected at render time. */
+int amvpt_scene_set_reuse(amvpt_scene *s, int sa_reuse, int sa_mis, int fast_mis, uint32_t reuse_count, uint32_t adaptive, uint32_t *n_samples);
 /* reconstruction filter of the film (src/rfilters/{box,gaussian,tent,mitchell,catmullrom,lanczos}.cpp; ImageBlock::put,
  * src/render/imageblock.cpp:174-558): type 0 box (default of this API), 1 gaussian (param = stddev, Mitsuba's default filter with
  * stddev 0.5), 2 tent (param = radius), 3 mitchell (param = B, param2 = C; both default to 1/3 in the reference), 4 catmullrom,
@@ -109,6 +114,10 @@ int amvpt_scene_get_mesh(amvpt_scene *s, uint32_t index, uint32_t *n_vertices, u
                          int32_t *flip_normals, int32_t *is_emitter, float *radiance3, float *positions, uint32_t *faces, float *normals);
 int amvpt_scene_get_bsdf(amvpt_scene *s, int bsdf, amvpt_bsdf_desc *d);
 int amvpt_scene_get_integrator(amvpt_scene *s, amvpt_integrator_desc *d, int32_t *is_mvpath, int32_t *sa_reuse, uint32_t *reuse_count);
+
+/* parity tap of the reuse branch: for lanes [lane_begin, lane_begin + n) the n_samples records of render_multisample, 9 floats
+ * each = { pos.x, pos.y, weight, result.rgb, valid, indirect, sensor index } (mirrors oracle orc_trace_lanes_multi) */
+int amvpt_trace_lanes_multi(amvpt_scene *s, uint32_t seed_value, uint32_t spp_per_pass, uint32_t lane_begin, uint32_t n, float *out9);
 
 /* ---- the hot path ----------------------------------------------------------------------------------------------- */
 /* MVPathIntegrator::render (src/integrators/mvpath.cpp:7-278): accumulates into the scene's film (RGBW, float32) */

@@ -69,11 +69,11 @@ class RenderStats(C.Structure):
 lib.amvpt_last_error.restype = C.c_char_p
 EXPORTS = ["amvpt_last_error", "amvpt_device_count", "amvpt_scene_create", "amvpt_scene_destroy", "amvpt_scene_from_xml",
            "amvpt_scene_from_xml_string", "amvpt_scene_add_bsdf", "amvpt_scene_add_mesh", "amvpt_scene_set_sensor_grid",
-           "amvpt_scene_set_sensor_batch", "amvpt_scene_set_integrator", "amvpt_scene_set_rfilter", "amvpt_scene_commit", "amvpt_scene_info",
+           "amvpt_scene_set_sensor_batch", "amvpt_scene_set_integrator", "amvpt_scene_set_rfilter", "amvpt_scene_set_reuse", "amvpt_scene_commit", "amvpt_scene_info",
            "amvpt_scene_get_sensor", "amvpt_scene_get_bsdf_tables", "amvpt_scene_counts", "amvpt_scene_get_mesh",
            "amvpt_scene_get_bsdf", "amvpt_scene_get_integrator", "amvpt_render", "amvpt_shard_tiles", "amvpt_cancel", "amvpt_film_clear",
            "amvpt_film_raw", "amvpt_film_develop", "amvpt_film_develop_device", "amvpt_film_device_ptr", "amvpt_film_add_host",
-           "amvpt_trace_lanes", "amvpt_intersect", "amvpt_bsdf_eval_pdf_sample", "amvpt_math1", "amvpt_sampler_stream",
+           "amvpt_trace_lanes", "amvpt_trace_lanes_multi", "amvpt_intersect", "amvpt_bsdf_eval_pdf_sample", "amvpt_math1", "amvpt_sampler_stream",
            "amvpt_bvh_validate"]
 lib.amvpt_scene_destroy.restype = None
 lib.amvpt_scene_destroy.argtypes = [C.c_void_p]
@@ -98,6 +98,7 @@ BSDF_TYPES = {"diffuse": 0, "conductor": 1, "dielectric": 2, "roughconductor": 3
 FOV_AXES = {"x": 0, "y": 1, "diagonal": 2, "smaller": 3, "larger": 4}
 RFILTERS = {"box": 0, "gaussian": 1, "tent": 2, "mitchell": 3, "catmullrom": 4, "lanczos": 5}
 SCHEDULERS = {"warp_batch": 0, "regenerate": 1, "stream": 2, "wavefront": 3, "auto": 4}
+SCHEDULER_NAMES = {0: "warp_batch", 1: "regenerate", 2: "stream", 3: "wavefront", 5: "reuse"}
 
 
 def bsdf_desc(type, twosided=False, distribution="beckmann", nonlinear=False, reflectance=(.5, .5, .5), eta=(0., 0., 0.),
@@ -166,6 +167,21 @@ class Scene:
     def set_integrator(self, max_depth=-1, rr_depth=5, hide_emitters=False, spp_pass_lim=16, sampler_seed=0, sample_count=0):
         d = IntegratorDesc(max_depth, rr_depth, int(hide_emitters), spp_pass_lim, sampler_seed, sample_count)
         _chk(lib.amvpt_scene_set_integrator(self._h, C.byref(d)))
+
+    def set_reuse(self, sa_reuse=True, sa_mis=False, fast_mis=False, reuse_count=0, adaptive=0):
+        """Cross-view sample reuse of the mvpath integrator (sa_reuse / sa_mis / fast_mis / reuse_count, mvpath.h:120-129).
+        Returns the number of cameras per reuse group (0 = reuse off)."""
+        n = C.c_uint32(0)
+        _chk(lib.amvpt_scene_set_reuse(self._h, C.c_int(int(sa_reuse)), C.c_int(int(sa_mis)), C.c_int(int(fast_mis)), C.c_uint32(reuse_count),
+                                       C.c_uint32(adaptive), C.byref(n)))
+        self.n_reuse = n.value
+        return n.value
+
+    def trace_lanes_multi(self, seed_value, spp_per_pass, lane_begin, n):
+        """Reuse-branch tap: (n, n_reuse, 9) = pos.xy, weight, result.rgb, valid, indirect, sensor index."""
+        out = np.zeros((n, self.n_reuse, 9), np.float32)
+        _chk(lib.amvpt_trace_lanes_multi(self._h, C.c_uint32(seed_value), C.c_uint32(spp_per_pass), C.c_uint32(lane_begin), C.c_uint32(n), _p(out)))
+        return out
 
     def set_rfilter(self, type="box", param=0.5, param2=0.0):
         """Film reconstruction filter: 'box', 'gaussian' (param = stddev), 'tent' (param = radius), 'mitchell' (param = B,

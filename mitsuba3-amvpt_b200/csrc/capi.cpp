@@ -108,6 +108,10 @@ int amvpt_scene_set_integrator(amvpt_scene *h, const amvpt_integrator_desc *d) {
         if (h->s->committed) { h->s->d.max_depth = ip.max_depth < 0 ? 0xffffffffu : (uint32_t) ip.max_depth; h->s->d.rr_depth = ip.rr_depth; }
         return AMVPT_OK; });
 }
+int amvpt_scene_set_reuse(amvpt_scene *h, int sa_reuse, int sa_mis, int fast_mis, uint32_t reuse_count, uint32_t adaptive, uint32_t *n_samples) {
+    return guard([&] { NEED(h); h->s->set_reuse(sa_reuse != 0, sa_mis != 0, fast_mis != 0, reuse_count, adaptive);
+        if (n_samples) *n_samples = h->s->reuse_samples(); return AMVPT_OK; });
+}
 int amvpt_scene_set_rfilter(amvpt_scene *h, int type, float param, float param2) {
     return guard([&] { NEED(h); h->s->set_rfilter(type, param, param2); return AMVPT_OK; });
 }
@@ -209,6 +213,14 @@ int amvpt_film_add_host(amvpt_scene *h, const float *rgbw) {
 }
 
 // ---- parity taps
+int amvpt_trace_lanes_multi(amvpt_scene *h, uint32_t seed_value, uint32_t spp_per_pass, uint32_t lane_begin, uint32_t n, float *out9) {
+    return guard([&] { Scene &s = committed(h); NEED(spp_per_pass > 0); NEED(out9);
+        if (!s.d.n_reuse) AM_THROW("trace_lanes_multi: sample reuse is off");
+        size_t bytes = (size_t) n * s.d.n_reuse * 9 * 4; DBuf b(bytes);
+        launch_reuse_tap(s.d, seed_value, spp_per_pass, lane_begin, n, b.as<float>(), nullptr);
+        AM_CUDA(cudaGetLastError()); AM_CUDA(cudaDeviceSynchronize());
+        b.down(out9, bytes); return AMVPT_OK; });
+}
 int amvpt_trace_lanes(amvpt_scene *h, uint32_t seed_value, uint32_t spp_per_pass, uint32_t lane_begin, uint32_t n, int trace,
                       float *sample_pos, float *ray_o, float *ray_d, float *ray_maxt, uint32_t *view, float *radiance,
                       uint32_t *pixel, uint32_t max_hits, uint32_t *hit_prim, float *hit_t, uint64_t *stats2) {

@@ -25,7 +25,7 @@ AM_D void path_init(PathState &ps, const Ray &ray) {
 // Lane -> (pixel, sampler, camera ray): MVPT::render lane map (src/integrators/mvpath.cpp:174-190) and
 // MVPT::render_sample (src/integrators/mvpath_single.h:50-75).
 struct LaneSetup { float spx, spy; uint32_t view, pixel; bool in_film; };
-AM_D void lane_setup(const DScene &s, uint32_t seed_value, uint32_t lane, uint32_t px, uint32_t py, PathState &ps, LaneSetup &ls) {
+AM_D void lane_setup(const DScene &s, uint32_t seed_value, uint32_t lane, uint32_t px, uint32_t py, PathState &ps, LaneSetup &ls, V2 *aperture_out = nullptr) {
     ps.rng = sampler_seed(seed_value, lane);
     float sx = rcp((float) s.film_w), sy = rcp((float) s.film_h);
     float jx = ps.rng.next_f32(), jy = ps.rng.next_f32();
@@ -34,6 +34,7 @@ AM_D void lane_setup(const DScene &s, uint32_t seed_value, uint32_t lane, uint32
     V2 aperture = v2(.5f, .5f);
     if (s.thinlens) { aperture.x = ps.rng.next_f32(); aperture.y = ps.rng.next_f32(); }
     Ray ray = sensor_sample_ray(s, adjusted, aperture, &ls.view);
+    if (aperture_out) *aperture_out = aperture;
     path_init(ps, ray);
     // ImageBlock::put, box filter (src/render/imageblock.cpp:210-233): pixel = floor(sample_pos)
     uint32_t ux = (uint32_t) (int32_t) floorf(ls.spx), uy = (uint32_t) (int32_t) floorf(ls.spy);
@@ -186,6 +187,65 @@ template <bool STATS, int TYPE = -1> AM_D bool shade_vertex(const DScene &s, Pat
     if (rr_active) ps.throughput = ps.throughput * rcp(rr_prob);
     ps.active = (!rr_active || rr_continue) && (tmax != 0.f);
     return active_em;
+}
+
+// One iteration of the while-loop of MVPT::sample_single (src/integrators/mvpath_single.h:130-275), wavefront
+// (JIT) semantics: every lane active at the top of the iteration draws 2 + 1 + 2 + 1 random numbers.
+template <bool TAP, bool STATS> AM_D void path_bounce(const DScene &s, PathState &ps, TapCtx *tap, StatCtx *st) {
+    uint32_t *cn = STATS ? &st->nodes : nullptr, *ct = STATS ? &st->tris : nullptr;
+    Hit h = intersect<false>(s, ps.ray, cn, ct);
+    if (STATS) { st->closest++; st->vertices++; }
+    const DMesh *mesh;
+    SI si = make_si(s, ps.ray, h, &mesh);
+    if (TAP) {
+        if (tap->n_iter < tap->max_hits) { tap->hit_prim[tap->n_iter] = si.prim; tap->hit_t[tap->n_iter] = h.t; }
+        tap->n_iter++;
+    }
+    // direct emission (:148-163); DirectionSample(scene, si, prev_si) records.h:141-149
+    if (si.valid && mesh->emitter >= 0) {
+        V3 rel = si.p - ps.prev_p; float dist = norm(rel); V3 d = rel / dist;
+        float em_pdf = 0.f;
+        if (!ps.prev_delta) em_pdf = pdf_emitter_direction(s, mesh, d, si.sh_n, dist);
+        float mis_bsdf = mis_weight(ps.prev_bsdf_pdf, em_pdf);
+        V3 le = select3(si.wi.z > 0.f && ps.prev_bsdf_pdf > 0.f, ld3(s.emitters[mesh->emitter].radiance));   // area.cpp:82-86
+        ps.result = fmadd(ps.throughput, le * mis_bsdf, ps.result);
+    }
+    bool active_next = (ps.depth + 1 < s.max_depth) && si.valid;
+    if (!active_next) {
+        // the lane finishes this iteration (its six draws and the BSDF call are unobservable) and leaves the loop
+        ps.valid_ray = ps.valid_ray || si.valid;     // :252
+        ps.active = false;
+        return;
+    }
+    const DBsdf &bsdf = s.bsdfs[mesh->bsdf];
+    // emitter sampling (:179-201)
+    bool active_em = (bsdf.flags & L_SMOOTH) != 0;
+    V2 es; es.x = ps.rng.next_f32(); es.y = ps.rng.next_f32();
+    DirectionSample ds; V3 em_weight = v3(0.f), wo = v3(0.f); ds.pdf = 0.f;
+    if (active_em) {
+        ds = sample_emitter_direction<false>(s, si, es, &em_weight, cn, ct);
+        if (STATS) st->shadow++;
+        active_em = ds.pdf != 0.f;
+        wo = si.to_local(ds.d);
+    }
+    float s1 = ps.rng.next_f32(); V2 s2; s2.x = ps.rng.next_f32(); s2.y = ps.rng.next_f32();
+    BsdfResult br = bsdf_eval_pdf_sample(bsdf, si.wi, wo, s1, s2);
+    if (active_em) {
+        float mis_em = mis_weight(ds.pdf, br.pdf);
+        ps.result = fmadd(ps.throughput, br.f * em_weight * mis_em, ps.result);
+    }
+    ps.ray = spawn_ray(si.p, si.n, si.to_world(br.bs.wo));
+    ps.throughput = ps.throughput * br.weight;
+    ps.eta *= br.bs.eta;
+    ps.valid_ray = true;
+    ps.prev_p = si.p; ps.prev_bsdf_pdf = br.bs.pdf; ps.prev_delta = (br.bs.type & L_DELTA) != 0;
+    ps.depth += 1;
+    // Russian roulette (:264-274)
+    float tmax = hmax(ps.throughput);
+    float rr_prob = min_(tmax * sqr(ps.eta), .95f);
+    bool rr_active = ps.depth >= s.rr_depth, rr_continue = ps.rng.next_f32() < rr_prob;
+    if (rr_active) ps.throughput = ps.throughput * rcp(rr_prob);
+    ps.active = (!rr_active || rr_continue) && (tmax != 0.f);
 }
 
 } // namespace amvpt

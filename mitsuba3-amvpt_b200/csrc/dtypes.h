@@ -18,6 +18,13 @@ struct DSensor {
     float to_world[12];   // first three rows of to_world.matrix
     float near_clip, far_clip, aperture_radius, focus_distance;
 };
+// 128 B per sub-camera, read only by the sample-reuse branch (Perspective/ThinLens::sample_surface,
+// src/sensors/perspective.cpp:327-385, thinlens.cpp:358-418): camera_to_sample, inverse of to_world, 1 / image-rectangle area
+struct DSensorAux {
+    float c2s[16];
+    float w2c[12];
+    float normalization, pad[3];
+};
 struct DMesh {
     int32_t bsdf, emitter, flip_normals, has_normals;
     uint32_t prim_offset, nfaces;
@@ -51,6 +58,9 @@ struct DScene {
     // film reconstruction filter: 0 box, 1 gaussian (polynomial of src/rfilters/gaussian.cpp:52-103), 2 tent (tent.cpp:48-56),
     // 3 mitchell (coeff[0..6] = a3 a2 a0 b3 b2 b1 b0, mitchell.cpp:63-69), 4 catmullrom, 5 lanczos (radius = lobes)
     int32_t filter_type; float filter_radius, filter_inv_radius; float filter_coeff[10];
+    // cross-view sample reuse (mvpath.h:120-129): n_reuse = samples per primary sample after mvpath.cpp:192-218, 0 = off
+    const DSensorAux *sensor_aux;
+    uint32_t n_reuse; int32_t sa_mis, fast_mis, pad1;
 };
 
 } // namespace amvpt

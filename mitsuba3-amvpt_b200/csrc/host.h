@@ -31,7 +31,7 @@ struct HMesh {
 // src/integrators/mvpath.h:120-129 + MonteCarloIntegrator (src/render/integrator.cpp:503-520)
 struct IntegratorParams {
     int64_t max_depth = -1; uint32_t rr_depth = 5; bool hide_emitters = false;
-    uint32_t spp_pass_lim = 16; bool sa_reuse = false, sa_mis = true, fast_mis = false, force_eval = true, debug = false;
+    uint32_t spp_pass_lim = 16; bool sa_reuse = false, sa_mis = false, fast_mis = false, force_eval = true, debug = false;
     uint32_t reuse_count = 1, adaptive = 0, block_size = 0; float timeout = -1.f;
     bool is_mvpath = true;
 };
@@ -46,7 +46,7 @@ struct GridSensorParams {
     float near_clip = 1e-2f, far_clip = 1e4f, focus_distance = 1e4f, aperture_radius = 0.f, cone_deg = 0.f, cam_dist = 0.1f;
     float cam_dir[3] = { 1.f, 0.f, 0.f }, cam_off[3] = { 0.f, 0.f, 0.f };
 };
-enum SchedulerMode { SCHED_WARP_BATCH = 0, SCHED_REGENERATE = 1, SCHED_STREAM = 2, SCHED_WAVEFRONT = 3, SCHED_AUTO = 4 };
+enum SchedulerMode { SCHED_WARP_BATCH = 0, SCHED_REGENERATE = 1, SCHED_STREAM = 2, SCHED_WAVEFRONT = 3, SCHED_AUTO = 4, SCHED_REUSE = 5 /* reported only */ };
 
 struct BvhOut { std::vector<float4> nodes, tris, tri_nrm; std::vector<uint32_t> prim_to_tri; uint32_t depth = 0; };
 struct RenderStats {
@@ -69,6 +69,9 @@ struct Scene {
     int rfilter_type = 0; float rfilter_param = 0.5f, rfilter_param2 = 0.f;
     void set_rfilter(int type, float param, float param2 = 0.f);
     IntegratorParams integrator;
+    // samples per primary sample of the reuse branch (MVPT::render, mvpath.cpp:17-22 + 192-218), 0 = reuse off
+    uint32_t reuse_samples() const;
+    void set_reuse(bool sa_reuse, bool sa_mis, bool fast_mis, uint32_t reuse_count, uint32_t adaptive);
     // ---- device mirror
     int device = -1, sm_count = 148;
     bool committed = false;

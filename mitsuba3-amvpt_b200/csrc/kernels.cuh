@@ -45,6 +45,10 @@ struct WfPool {
 uint32_t run_wavefront_pass(const DScene &s, const RenderParams &p, const WfPool &w, uint32_t type_mask, int sm_count, bool stats, cudaStream_t st,
                             double *trace_seconds, uint32_t *trace_launches);
 
+// sample-reuse branch (reuse.cu)
+void launch_reuse_pass(const DScene &s, const RenderParams &p, int sm_count, bool stats, cudaStream_t st);
+void launch_reuse_tap(const DScene &s, uint32_t seed_value, uint32_t spp_per_pass, uint32_t lane_begin, uint32_t n, float *out /* n * n_reuse * 9 */, cudaStream_t st);
+
 // host-callable launchers (kernels.cu)
 void launch_render_pass(const DScene &s, const RenderParams &p, int mode, int sm_count, bool stats, cudaStream_t st);
 void launch_trace_lanes(const DScene &s, uint32_t seed_value, uint32_t spp_per_pass, uint32_t lane_begin, uint32_t n, int trace,

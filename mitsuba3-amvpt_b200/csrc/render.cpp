@@ -39,8 +39,14 @@ static unsigned long long finish_tiles(std::vector<TileDesc> &tiles) {
 void render(Scene &s, const RenderOptions &opt) {
     if (!s.committed) AM_THROW("render: scene not committed to a device");
     if (s.integrator.is_mvpath && !s.multi_sensor) AM_THROW("This integrator can only be used with MultiSensor !");
-    if (s.integrator.sa_reuse && s.sensors.size() > 1 && s.integrator.reuse_count != 1)
-        AM_THROW("mvpath: cross-view sample reuse (sa_reuse) is not implemented in this build");
+    const bool reuse = s.reuse_samples() > 0;      // mvpath.cpp:17
+    if (reuse) {
+        if (s.integrator.adaptive) AM_THROW("mvpath: the `adaptive` fill-in of the reuse branch (mvpath_multi.h:79-115) is not built");
+        if (s.integrator.debug) AM_THROW("mvpath: the `debug` output of the reuse branch is not built");
+        if (s.rfilter_type != 0) AM_THROW("mvpath: sample reuse needs the box reconstruction filter in this build");
+        if (opt.adaptive) AM_THROW("render: the adaptive allocator keeps per-pixel moments of the owning view; it cannot be combined with sample reuse");
+        if (s.d.n_reuse != s.reuse_samples()) AM_THROW("render: integrator parameters changed after commit");
+    }
     if (opt.shard.world == 0 || opt.shard.rank >= opt.shard.world) AM_THROW("render: invalid shard %u/%u", opt.shard.rank, opt.shard.world);
     AM_CUDA(cudaSetDevice(s.device));
     cudaStream_t st = opt.stream;
@@ -88,6 +94,7 @@ void render(Scene &s, const RenderOptions &opt) {
     // a reconstruction filter other than the box is splatted by the wavefront's regen stage only: carrying the sample position
     // and the footprint loop through the persistent megakernels costs them 8 % on the box-filter path (measured, profiles/)
     if (s.rfilter_type != 0) mode = 3;
+    if (reuse) mode = SCHED_REUSE;                 // the reuse branch has its own kernel (reuse.cu)
     rs.scheduler_used = (uint32_t) mode;
     auto launch = [&](std::vector<TileDesc> &tiles, uint32_t pass) {
         unsigned long long lanes = finish_tiles(tiles);
@@ -110,6 +117,10 @@ void render(Scene &s, const RenderOptions &opt) {
                 s.wf_type_mask = 0; for (auto &m : s.meshes) s.wf_type_mask |= 1u << s.bsdfs[m.bsdf].type;
             }
             rs.launches += run_wavefront_pass(s.d, p, s.wf, s.wf_type_mask, s.sm_count, opt.stats, st, opt.time_stages ? &rs.trace_seconds : nullptr, &rs.trace_launches);
+        } else if (mode == SCHED_REUSE) {
+            launch_reuse_pass(s.d, p, s.sm_count, opt.stats, st);
+            AM_CUDA(cudaGetLastError());
+            rs.launches++;
         } else {
             launch_render_pass(s.d, p, mode, s.sm_count, opt.stats, st);
             AM_CUDA(cudaGetLastError());

@@ -221,6 +221,23 @@ void Scene::set_rfilter(int type, float param, float param2) {
     if (std::ceil(radius - .5f) > 7.f) AM_THROW("rfilter: radius %g is too large (footprint limited to 15 x 15 pixels)", radius);
     rfilter_type = type; rfilter_param = param; rfilter_param2 = param2; committed = false;
 }
+uint32_t Scene::reuse_samples() const {
+    const uint32_t n_sensors = (uint32_t) sensors.size();
+    if (!(integrator.sa_reuse && n_sensors > 1 && integrator.reuse_count != 1)) return 0;
+    uint32_t n = std::min(integrator.reuse_count, n_sensors);
+    if (n == 0 || n_sensors % n) {        // "The number of sensors should be divisible by reused samples count!" (mvpath.cpp:196-217)
+        n = 0;
+        for (uint32_t p = 8; p < n_sensors; ++p) if (n_sensors % p == 0) { n = p; break; }
+        if (!n) { for (uint32_t p = 8; p > 1; --p) if (n_sensors % p == 0) { n = p; break; } n = n ? n : n_sensors; }
+    }
+    return n;
+}
+void Scene::set_reuse(bool sa_reuse, bool sa_mis, bool fast_mis, uint32_t reuse_count, uint32_t adaptive) {
+    integrator.sa_reuse = sa_reuse; integrator.sa_mis = sa_mis; integrator.fast_mis = fast_mis; integrator.reuse_count = reuse_count;
+    integrator.adaptive = adaptive;
+    if (reuse_samples() > 64) AM_THROW("mvpath: reuse_count %u exceeds the 64 cameras per group this build keeps per lane", reuse_samples());
+    if (committed) { d.n_reuse = reuse_samples(); d.sa_mis = sa_mis; d.fast_mis = fast_mis; }
+}
 // View tiles of the quilt owned by one rank: view v = ix + grid_x * iy (sub-sensor index), tile position follows
 // GridSensor::sample_ray's axis reversal (grid.cpp:246-255).
 std::vector<TileDesc> Scene::view_tiles(const Shard &sh) const {
@@ -267,6 +284,27 @@ void Scene::commit(int dev) {
     d = DScene{};
     d.nodes = upload(bvh.nodes); d.tris = upload(bvh.tris); d.tri_nrm = any_nrm ? upload(bvh.tri_nrm) : nullptr;
     d.prim_to_tri = upload(bvh.prim_to_tri); d.meshes = upload(dm); d.bsdfs = upload(bsdfs); d.emitters = upload(emitters);
+    // PerspectiveCamera::update_camera_transforms (perspective.cpp:173-199) members read by sample_surface: camera_to_sample
+    // (inverse of sample_to_camera), Transform4f::inverse of to_world, normalization = 1 / area of the near-plane image rectangle
+    std::vector<DSensorAux> aux;
+    for (auto &c : sensors) {
+        DSensorAux a{}; M4 s2c, tw = m4_identity();
+        std::memcpy(s2c.m, c.s2c, 64); std::memcpy(tw.m, c.to_world, 48);
+        M4 c2s = m4_inverse(s2c), w2c = m4_inverse(tw);
+        std::memcpy(a.c2s, c2s.m, 64); std::memcpy(a.w2c, w2c.m, 48);
+        auto proj = [&](float x, float y, float z, float *o) {
+            float r[4]; for (int i = 0; i < 4; ++i) r[i] = s2c.m[i][3];
+            for (int i = 0; i < 4; ++i) r[i] = fmadd(s2c.m[i][0], x, r[i]);
+            for (int i = 0; i < 4; ++i) r[i] = fmadd(s2c.m[i][1], y, r[i]);
+            for (int i = 0; i < 4; ++i) r[i] = fmadd(s2c.m[i][2], z, r[i]);
+            float iw = 1.f / r[3]; o[0] = r[0] * iw; o[1] = r[1] * iw; o[2] = r[2] * iw; };
+        float pmin[3], pmax[3]; proj(0.f, 0.f, 0.f, pmin); proj(1.f, 1.f, 0.f, pmax);
+        float ia = 1.f / pmin[2], ib = 1.f / pmax[2], ax = pmin[0] * ia, ay = pmin[1] * ia, bx = pmax[0] * ib, by = pmax[1] * ib;
+        float lox = std::min(ax, bx), hix = std::max(ax, bx), loy = std::min(ay, by), hiy = std::max(ay, by);
+        a.normalization = 1.f / ((hix - lox) * (hiy - loy));
+        aux.push_back(a);
+    }
+    d.sensor_aux = upload(aux); d.n_reuse = reuse_samples(); d.sa_mis = integrator.sa_mis; d.fast_mis = integrator.fast_mis;
     d.sensors = upload(sensors); d.area_cdf = upload(cdf_all); d.area_pmf = upload(pmf_all);
     d.n_tris = n_tris; d.n_nodes = n_nodes; d.n_emitters = (uint32_t) emitters.size(); d.n_sensors = (uint32_t) sensors.size();
     d.grid_x = grid_x; d.grid_y = grid_y; d.reverse_x = reverse_x; d.reverse_y = reverse_y; d.thinlens = thinlens;

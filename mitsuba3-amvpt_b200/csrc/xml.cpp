@@ -551,7 +551,7 @@ struct Builder {
         if ((long long) o.i("rr_depth", 5) <= 0) AM_THROW("%s: \"rr_depth\" must be set to a value greater than zero!", o.where.c_str());
         ip.timeout = (float) o.f("timeout", -1.0); ip.block_size = (uint32_t) o.i("block_size", 0); o.i("samples_per_pass", -1);
         if (ip.is_mvpath) {          // mvpath.h:120-129
-            ip.spp_pass_lim = (uint32_t) o.i("spp_pass_lim", 16); ip.sa_reuse = o.b("sa_reuse", false); ip.sa_mis = o.b("sa_mis", true);
+            ip.spp_pass_lim = (uint32_t) o.i("spp_pass_lim", 16); ip.sa_reuse = o.b("sa_reuse", false); ip.sa_mis = o.b("sa_mis", false);
             ip.fast_mis = o.b("fast_mis", false); ip.reuse_count = (uint32_t) o.i("reuse_count", 1); ip.adaptive = (uint32_t) o.i("adaptive", 0);
             ip.force_eval = o.b("force_eval", true); ip.debug = o.b("debug", false);
             if (ip.spp_pass_lim == 0) AM_THROW("%s: spp_pass_lim must be positive", o.where.c_str());

@@ -136,6 +136,8 @@ def build(desc, device=0, commit=True):
     s.set_integrator(**desc["integrator"])
     if desc.get("rfilter"):
         s.set_rfilter(*desc["rfilter"])
+    if desc.get("reuse"):
+        s.set_reuse(**desc["reuse"])
     if commit:
         s.commit(device)
     return s
@@ -245,6 +247,11 @@ def export_xml(desc, directory, mesh_format="obj", integrator="mvpath", filename
            f'        <integer name="rr_depth" value="{it["rr_depth"]}"/>']
     if integrator == "mvpath":
         out.append(f'        <integer name="spp_pass_lim" value="{it["spp_pass_lim"]}"/>')
+        ru = desc.get("reuse")
+        if ru:
+            for key in ("sa_reuse", "sa_mis", "fast_mis"):
+                out.append(f'        <boolean name="{key}" value="{str(bool(ru.get(key, key == "sa_reuse"))).lower()}"/>')
+            out.append(f'        <integer name="reuse_count" value="{int(ru.get("reuse_count", 0))}"/>')
     out.append("    </integrator>")
     out += ['    <wrap type="any" id="m_film">', '        <string name="wrap_class" value="film"/>', '        <string name="wrap_type" value="hdrfilm"/>',
             f'        <integer name="width" value="{s["res_x"] // gx}"/>', f'        <integer name="height" value="{s["res_y"] // gy}"/>',

@@ -66,7 +66,11 @@ struct Mesh {
     V3 vn(uint32_t i) const { return V3(nrm[3 * i], nrm[3 * i + 1], nrm[3 * i + 2]); }
 };
 struct Emitter { int mesh; V3 radiance; };
-struct SubSensor { M4 s2c, to_world; float near_clip, far_clip, aperture_radius, focus_distance; };
+struct SubSensor {
+    M4 s2c, to_world; float near_clip, far_clip, aperture_radius, focus_distance;
+    // sample reuse (sample_surface): camera_to_sample, inverse of to_world, 1 / area of the image rectangle (perspective.cpp:173-199)
+    M4 c2s, w2c; float normalization = 0.f;
+};
 
 struct BvhNode { float lo[3], hi[3]; int32_t left, right; uint32_t first, count; };
 
@@ -77,6 +81,8 @@ struct Scene {
     uint32_t film_w = 0, film_h = 0;    // quilt size
     uint32_t max_depth = 0xffffffffu, rr_depth = 5; int hide_emitters = 0;
     uint32_t base_seed = 0;
+    // cross-view sample reuse (mvpath.h:120-129): n_reuse = samples per primary sample after mvpath.cpp:192-218 (0 = off)
+    int sa_mis = 0, fast_mis = 0; uint32_t n_reuse = 0;
     // reconstruction filter of the film: 0 box, 1 gaussian (src/rfilters/gaussian.cpp), 2 tent (src/rfilters/tent.cpp)
     int filter_type = 0; float filter_radius = 0.5f, filter_coeff[10] = { 0 }, filter_inv_radius = 1.f;
     // flattened primitives
@@ -468,6 +474,8 @@ static PathResult sample_single(const Scene &s, Pcg32 &rng, Ray ray, bool brute,
     return { valid_ray ? result : V3(0.f), valid_ray };
 }
 
+#include "o_reuse.h"
+
 struct LaneOut { float sample_pos[2]; Ray ray; uint32_t view; PathResult r; uint32_t pixel; bool in_film; };
 // MVPT::render JIT branch lane mapping (src/integrators/mvpath.cpp:174-190) + render_sample
 // (src/integrators/mvpath_single.h:50-80)
@@ -558,6 +566,19 @@ static void filter_put(const Scene &s, float *film, float spx, float spy, V3 L) 
 
 // ====================================================================== C interface (ctypes)
 using namespace orc;
+namespace orc {
+// PerspectiveCamera::update_camera_transforms (perspective.cpp:173-199): camera_to_sample = inverse of sample_to_camera,
+// image rectangle of the near plane -> normalization; Transform4f::inverse of to_world for sample_surface
+static void sensor_finish(SubSensor &c) {
+    c.c2s = m4_inverse(c.s2c); c.w2c = m4_inverse(c.to_world);
+    V3 pmin = xf_point(c.s2c, V3(0.f, 0.f, 0.f)), pmax = xf_point(c.s2c, V3(1.f, 1.f, 0.f));
+    V3 a = pmin / pmin.z, b = pmax / pmax.z;
+    float lox = fmin_(a.x, b.x), hix = fmax_(a.x, b.x), loy = fmin_(a.y, b.y), hiy = fmax_(a.y, b.y);
+    c.normalization = 1.f / ((hix - lox) * (hiy - loy));
+}
+} // namespace orc
+using namespace orc;
+
 extern "C" {
 
 struct OrcBsdfDesc {        // mirrors the XML parameters of the reference BSDF plugins
@@ -624,7 +645,7 @@ void orc_set_sensor_grid(void *sp, const OrcSensorDesc *d) {
         grid_sub_camera(g, inv_t, fov_x, i, &c.to_world, &lens_shift);
         c.s2c = sample_to_camera((int) sub_w, (int) sub_h, (float) fov_x, d->near_clip, d->far_clip, lens_shift);
         c.near_clip = d->near_clip; c.far_clip = d->far_clip; c.aperture_radius = d->aperture_radius; c.focus_distance = d->focus_distance;
-        s.sensors.push_back(c);
+        sensor_finish(c); s.sensors.push_back(c);
     }
 }
 // BatchSensor-style explicit sub-cameras (src/sensors/batch.cpp:94-130): n views side by side
@@ -634,7 +655,7 @@ void orc_set_sensor_explicit(void *sp, uint32_t n, uint32_t res_x, uint32_t res_
     s.film_w = res_x * n; s.film_h = res_y; s.sensors.clear();
     for (uint32_t i = 0; i < n; ++i) {
         SubSensor c; std::memcpy(c.s2c.m, s2c + 16 * i, 64); std::memcpy(c.to_world.m, to_world + 16 * i, 64);
-        c.near_clip = near_clip; c.far_clip = far_clip; c.aperture_radius = 0; c.focus_distance = far_clip; s.sensors.push_back(c);
+        c.near_clip = near_clip; c.far_clip = far_clip; c.aperture_radius = 0; c.focus_distance = far_clip; sensor_finish(c); s.sensors.push_back(c);
     }
 }
 void orc_get_sensor(void *sp, uint32_t i, float *s2c, float *to_world) {
@@ -644,6 +665,21 @@ void orc_set_integrator(void *sp, int64_t max_depth, uint32_t rr_depth, int hide
     Scene &s = *(Scene *) sp;
     s.max_depth = max_depth < 0 ? 0xffffffffu : (uint32_t) max_depth;        // integrator.cpp:503-520
     s.rr_depth = rr_depth; s.hide_emitters = hide_emitters; s.base_seed = sampler_seed;
+}
+// MVPathIntegrator sample reuse (mvpath.h:121-128) + the sample-size rule of MVPT::render (mvpath.cpp:17-22, 192-218).
+// Returns the number of samples per primary sample (0 = reuse off).
+uint32_t orc_set_reuse(void *sp, int sa_reuse, int sa_mis, int fast_mis, uint32_t reuse_count) {
+    Scene &s = *(Scene *) sp; uint32_t n_sensors = (uint32_t) s.sensors.size();
+    s.sa_mis = sa_mis; s.fast_mis = fast_mis; s.n_reuse = 0;
+    bool reuse = sa_reuse && n_sensors > 1 && reuse_count != 1;
+    if (!reuse) return 0;
+    uint32_t n = std::min(reuse_count, n_sensors);
+    if (n == 0 || n_sensors % n) {
+        n = 0;
+        for (uint32_t p = 8; p < n_sensors; ++p) if (n_sensors % p == 0) { n = p; break; }
+        if (!n) { for (uint32_t p = 8; p > 1; --p) if (n_sensors % p == 0) { n = p; break; } n = n ? n : n_sensors; }
+    }
+    s.n_reuse = n; return n;
 }
 // film reconstruction filter: type 0 box, 1 gaussian (param = stddev), 2 tent (param = radius), 3 mitchell (param = B, param2 = C),
 // 4 catmullrom, 5 lanczos (param = lobes)
@@ -791,7 +827,7 @@ double orc_render_rows(void *sp, uint32_t seed, uint32_t spp, uint32_t spp_pass_
     std::vector<TraverseStats> tstats(std::max(nthreads, 1));
     // a wider filter splats across rows: every thread then accumulates into its own film, summed in thread order at the end
     size_t film_floats = 4 * (size_t) s.film_w * s.film_h;
-    std::vector<std::vector<float>> tfilm; if (s.filter_type != 0 && nthreads > 1) tfilm.assign(nthreads, std::vector<float>(film_floats, 0.f));
+    std::vector<std::vector<float>> tfilm; if ((s.filter_type != 0 || s.n_reuse) && nthreads > 1) tfilm.assign(nthreads, std::vector<float>(film_floats, 0.f));
     auto t0 = std::chrono::steady_clock::now();
     auto worker = [&](int tid) {
         for (;;) {
@@ -801,6 +837,12 @@ double orc_render_rows(void *sp, uint32_t seed, uint32_t spp, uint32_t spp_pass_
                 uint32_t seed_value = s.base_seed + (spp_per_pass * pass + seed);
                 for (uint32_t x = 0; x < s.film_w; ++x) for (uint32_t k = 0; k < spp_per_pass; ++k) {
                     uint32_t lane = (y * s.film_w + x) * spp_per_pass + k;
+                    if (s.n_reuse) {          // reused samples land in other view tiles: per-thread films, as with a wide filter
+                        float *f = tfilm.empty() ? film : tfilm[tid].data();
+                        render_lane_multi(s, seed_value, lane, spp_per_pass, s.n_reuse, brute != 0, nullptr, &tstats[tid],
+                                          [&](uint32_t ux, uint32_t uy, V3 v, float w) { float *px = f + 4 * ((size_t) uy * s.film_w + ux); px[0] += v.x; px[1] += v.y; px[2] += v.z; px[3] += w; });
+                        continue;
+                    }
                     LaneOut o = render_lane(s, seed_value, lane, spp_per_pass, brute != 0, nullptr, &tstats[tid]);
                     // a jittered position that rounds up into the next pixel/row is extremely rare; handled with the same index rule
                     if (s.filter_type != 0) { filter_put(s, tfilm.empty() ? film : tfilm[tid].data(), o.sample_pos[0], o.sample_pos[1], o.r.L); continue; }
@@ -817,6 +859,20 @@ double orc_render_rows(void *sp, uint32_t seed, uint32_t spp, uint32_t spp_pass_
     double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     if (stats) { stats[0] = stats[1] = 0; for (auto &t : tstats) { stats[0] += t.nodes; stats[1] += t.tris; } }
     return sec;
+}
+// Per-lane tap of the reuse branch: for lanes [lane_begin, lane_begin + n) the n_reuse SampleData records after
+// render_multisample's tile offset: out[lane][k] = { pos.x, pos.y, weight, result.rgb, valid, indirect, idx } (9 floats)
+void orc_trace_lanes_multi(void *sp, uint32_t seed_value, uint32_t spp_per_pass, uint32_t lane_begin, uint32_t n, int brute, float *out) {
+    Scene &s = *(Scene *) sp; uint32_t nr = s.n_reuse; if (!nr) return;
+    for (uint32_t i = 0; i < n; ++i) {
+        SampleData sd[MaxReuse];
+        render_lane_multi(s, seed_value, lane_begin + i, spp_per_pass, nr, brute != 0, nullptr, nullptr, [](uint32_t, uint32_t, V3, float) {}, sd);
+        for (uint32_t k = 0; k < nr; ++k) {
+            float *o = out + 9 * ((size_t) i * nr + k);
+            o[0] = sd[k].pos.x; o[1] = sd[k].pos.y; o[2] = sd[k].weight; o[3] = sd[k].result.x; o[4] = sd[k].result.y; o[5] = sd[k].result.z;
+            o[6] = sd[k].valid ? 1.f : 0.f; o[7] = sd[k].indirect ? 1.f : 0.f; o[8] = (float) sd[k].idx;
+        }
+    }
 }
 // HDRFilm::develop (src/films/hdrfilm.cpp:321-408): rgb = RGB / (W == 0 ? 1 : W)
 void orc_develop(const float *rgbw, uint64_t npix, float *rgb) {

@@ -92,6 +92,8 @@ class OracleScene:
             self.set_sensor_grid(**desc["sensor"]); self.set_integrator(**desc["integrator"])
             if desc.get("rfilter"):
                 self.set_rfilter(*desc["rfilter"])
+            if desc.get("reuse"):
+                self.set_reuse(**desc["reuse"])
             self.prepare()
 
     def __del__(self):
@@ -130,6 +132,18 @@ class OracleScene:
     def set_integrator(self, max_depth=-1, rr_depth=5, hide_emitters=False, spp_pass_lim=16, sampler_seed=0, sample_count=0):
         self.spp_pass_lim = spp_pass_lim
         self.o.orc_set_integrator(self.h, C.c_int64(max_depth), C.c_uint32(rr_depth), C.c_int(int(hide_emitters)), C.c_uint32(sampler_seed))
+
+    def set_reuse(self, sa_reuse=True, sa_mis=False, fast_mis=False, reuse_count=0):
+        """MVPathIntegrator sa_reuse / sa_mis / fast_mis / reuse_count; returns the samples per primary sample (0 = off)."""
+        self.o.orc_set_reuse.restype = C.c_uint32
+        self.n_reuse = self.o.orc_set_reuse(self.h, C.c_int(int(sa_reuse)), C.c_int(int(sa_mis)), C.c_int(int(fast_mis)), C.c_uint32(reuse_count))
+        return self.n_reuse
+
+    def trace_lanes_multi(self, seed_value, spp_per_pass, lane_begin, n, brute=True):
+        """Reuse-branch tap: (n, n_reuse, 9) = pos.xy, weight, result.rgb, valid, indirect, sensor index."""
+        out = np.zeros((n, self.n_reuse, 9), np.float32)
+        self.o.orc_trace_lanes_multi(self.h, C.c_uint32(seed_value), C.c_uint32(spp_per_pass), C.c_uint32(lane_begin), C.c_uint32(n), C.c_int(int(brute)), _p(out))
+        return out
 
     def set_rfilter(self, type="box", param=0.5, param2=0.0):
         self.o.orc_set_rfilter(self.h, C.c_int(RFILTERS[type]), C.c_float(param), C.c_float(param2))
