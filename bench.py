@@ -31,7 +31,16 @@ WORKLOADS = {
     "cbox4": ("cornell_box", dict(grid_x=4, grid_y=1, view_res=256, cam_dist=200.0, max_depth=6, sample_count=64), 64),
     "hfield4": ("height_field", dict(n=708, grid_x=2, grid_y=2, view_res=512, max_depth=8, sample_count=16), 16),      # profiling size of hfield16
     "hfield16": ("height_field", dict(n=708, grid_x=4, grid_y=4, view_res=1024, max_depth=8, sample_count=64), 64),
+    # BASELINE config 5 geometry (64 views of 1024^2 on the 1M-triangle scene); its 1024-spp adaptive budget is reached with --adaptive --spp 1024
+    "hfield64": ("height_field", dict(n=708, grid_x=8, grid_y=8, view_res=1024, max_depth=8, sample_count=64), 64),
+    # the same light field with cross-view sample reuse + MIS, 8 cameras per group (one row of the 8x8 array)
+    "cbox8x8_reuse": ("cornell_box", dict(grid_x=8, grid_y=8, view_res=512, cam_dist=400.0, max_depth=6, sample_count=64), 64),
+    "cbox4_reuse": ("cornell_box", dict(grid_x=4, grid_y=1, view_res=256, cam_dist=200.0, max_depth=6, sample_count=64), 64),   # profiling size
+    "hfield16_reuse": ("height_field", dict(n=708, grid_x=4, grid_y=4, view_res=1024, max_depth=8, sample_count=16), 16),
 }
+EXTRA = {"cbox8x8_reuse": dict(reuse=dict(sa_reuse=True, sa_mis=True, fast_mis=False, reuse_count=8)),
+         "cbox4_reuse": dict(reuse=dict(sa_reuse=True, sa_mis=True, fast_mis=False, reuse_count=4)),
+         "hfield16_reuse": dict(reuse=dict(sa_reuse=True, sa_mis=True, fast_mis=False, reuse_count=4))}
 
 
 def peaks():
@@ -100,10 +109,14 @@ def main():
     ap.add_argument("--gpus", type=int, default=1); ap.add_argument("--steps", type=int, default=3); ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200"); ap.add_argument("--workload", default="cbox8x8")
     ap.add_argument("--scheduler", default="auto"); ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--adaptive", action="store_true", help="BASELINE configs 3 / 5: allocate spp per view from the variance statistics (all-reduced across ranks)")
+    ap.add_argument("--spp", type=int, default=0, help="override the workload's samples per pixel (mean budget with --adaptive)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
     scenes = None
     factory, kw, spp = WORKLOADS[args.workload]
+    if args.spp:
+        spp = args.spp; kw = dict(kw, sample_count=spp)
     threads = os.cpu_count() or 1
 
     if args.impl == "reference":
@@ -112,7 +125,7 @@ def main():
             return
         spec = importlib.util.spec_from_file_location("amvpt_scenes", os.path.join(ROOT, "mitsuba3-amvpt_b200", "scenes.py"))
         scenes = importlib.util.module_from_spec(spec); spec.loader.exec_module(scenes)
-        desc = getattr(scenes, factory)(**kw)
+        desc = getattr(scenes, factory)(**kw); desc.update(EXTRA.get(args.workload, {}))
         per_step = max(2.0, min(20.0, 120.0 / max(args.steps + args.warmup, 1)))
         vals = []
         for i in range(args.warmup + args.steps):
@@ -134,7 +147,7 @@ def main():
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    desc = getattr(scenes, factory)(**kw)
+    desc = getattr(scenes, factory)(**kw); desc.update(EXTRA.get(args.workload, {}))
     s = scenes.build(desc, device=local)
     info = s.info(); W, H = info["film_w"], info["film_h"]
     n_paths = W * H * spp
@@ -159,21 +172,25 @@ def main():
     def film_tensor():
         return torch.as_tensor(_Ptr(film_ptr, W * H * 4), device=f"cuda:{local}")
 
+    hook = None
+    if args.adaptive and world > 1:
+        hook = importlib.import_module("mitsuba3-amvpt_b200.multigpu").make_allreduce_hook(f"cuda:{local}")
+
     def step():
-        s.render(seed=0, spp=spp, develop=False, scheduler=args.scheduler, rank=rank, world=world)
+        s.render(seed=0, spp=spp, develop=False, scheduler=args.scheduler, rank=rank, world=world, adaptive=args.adaptive, allreduce=hook)
         gather_film()
         return s.last_stats
 
     for _ in range(args.warmup):
         step()
     clocks = ClockSampler(local); barrier(); clocks.start()
-    dev_s, launches, render_s = 0.0, 0, 0.0
+    dev_s, launches, render_s, traced = 0.0, 0, 0.0, 0
     t0 = time.perf_counter()
     for _ in range(args.steps):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(); st = step(); e1.record(); e1.synchronize()
         dev_s += e0.elapsed_time(e1) * 1e-3; launches += st["launches"]
-        render_s += st["seconds"]
+        render_s += st["seconds"]; traced += st["paths"]
     barrier(); wall = time.perf_counter() - t0
     clk = clocks.stop()
     tmax = torch.tensor([dev_s], dtype=torch.float64, device=f"cuda:{local}")
@@ -188,12 +205,17 @@ def main():
         per_rank = [mine]
     rank_ms = [[round(float(x) / args.steps * 1e3, 2) for x in t.tolist()] for t in per_rank]
     dev_s = float(tmax.item())
+    tr = torch.tensor([float(traced)], dtype=torch.float64, device=f"cuda:{local}")
+    if dist is not None:
+        dist.all_reduce(tr, op=dist.ReduceOp.SUM)
+    if args.adaptive:                       # the allocator spends the budget in whole passes: count the paths actually traced
+        n_paths = int(tr.item()) // max(args.steps, 1)
     value = n_paths * args.steps / dev_s / 1e6
 
     # ---- end to end through the C ABI with host buffers (scene upload + render + develop + D2H every step)
     def e2e_step():
         sc = scenes.build(desc, device=local)          # host description -> BVH build -> H2D
-        img = sc.render(seed=0, spp=spp, develop=(world == 1), scheduler=args.scheduler, rank=rank, world=world)
+        img = sc.render(seed=0, spp=spp, develop=(world == 1), scheduler=args.scheduler, rank=rank, world=world, adaptive=args.adaptive, allreduce=hook)
         if world > 1:
             fp, _ = sc.film_device_ptr(); t = torch.as_tensor(_Ptr(fp, W * H * 4), device=f"cuda:{local}")
             dist.reduce(t, dst=0, op=dist.ReduceOp.SUM)
@@ -222,12 +244,18 @@ def main():
     bvh_bytes_per_path = (cs["bvh_nodes"] * 64.0 + cs["tri_tests"] * 48.0) / cs["paths"]
     s.render(seed=0, spp=spp, develop=False, scheduler=args.scheduler, time_stages=True); ks = s.last_stats
     peak, peak_src = peaks()
-    sched = {0: "warp_batch", 1: "regenerate", 2: "stream", 3: "wavefront"}[ks["scheduler_used"]]
+    sched = {0: "warp_batch", 1: "regenerate", 2: "stream", 3: "wavefront", 5: "reuse"}[ks["scheduler_used"]]
     if sched == "wavefront":
         # dominant kernel: wf_trace_kernel.  Per ray: BVH nodes (64 B) + triangles (48 B) + ray read (32 B) + hit / flag traffic (24 B)
         kernel = "wf_trace_kernel"; b_path = bvh_bytes_per_path + 56.0 * rays / cs["paths"]
         per_launch_s = ks["trace_seconds"] / max(ks["trace_launches"], 1); paths_per_launch = ks["paths"] / max(ks["trace_launches"], 1)
         note = "staged wavefront: trace stage = %.0f%% of the device time; the BVH (~130 MB at 1M triangles) straddles L2, latency-bound traversal" % (100 * ks["trace_seconds"] / ks["seconds"])
+    elif sched == "reuse":
+        # one primary path = prefix (1 closest ray, 1 light ray, n - 1 camera visibility rays) + the shared suffix + up to n splats of 16 B
+        film_w = float(torch.as_tensor(_Ptr(film_ptr, W * H * 4), device=f"cuda:{local}").view(-1, 4)[:, 3].sum().item())
+        kernel = "render_reuse_kernel"; b_path = 16.0 * max(1.0, film_w / max(ks["paths"], 1) * s.n_reuse / 2) + bvh_bytes_per_path
+        per_launch_s = ks["seconds"] / ks["launches"]; paths_per_launch = ks["paths"] / ks["launches"]
+        note = "sample reuse: Mpaths/s counts PRIMARY paths; every primary path also feeds up to n - 1 other views (config.reuse_samples)"
     else:
         kernel = "render_pass_kernel"; b_path = 16.0 + bvh_bytes_per_path
         per_launch_s = ks["seconds"] / ks["launches"]; paths_per_launch = ks["paths"] / ks["launches"]
@@ -244,7 +272,7 @@ def main():
         pass
     out = {"metric": "Mpaths/s (all views, device-timed)", "value": value, "unit": "Mpaths/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
            "ms_per_step": dev_s / args.steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-           "config": {"workload": args.workload, **kw, "spp": spp, "scheduler": args.scheduler, "scheduler_used": sched, "quilt": [W, H], "paths_per_step": n_paths,
+           "config": {"workload": args.workload, **kw, **({"reuse": EXTRA[args.workload]["reuse"], "reuse_samples": s.n_reuse} if args.workload in EXTRA else {}), "spp": spp, "adaptive": bool(args.adaptive), "scheduler": args.scheduler, "scheduler_used": sched, "quilt": [W, H], "paths_per_step": n_paths,
                       "l2_policy": f"film {W * H * 16 / 1e6:.0f} MB > 126 MB L2 rewritten every pass" if W * H * 16 > 126e6 else "film smaller than L2 (small workload)",
                       "parallelism": f"views sharded over {world} rank(s), NCCL film reduce to rank 0" if world > 1 else "single GPU"},
            "clocks": clk, "gpu_launches": launches, "wall_s": wall, "rank_ms_render_step": rank_ms,

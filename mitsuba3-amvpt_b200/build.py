@@ -23,19 +23,23 @@ def build(force=False, verbose=False):
     os.makedirs(OBJ, exist_ok=True)
     headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".h", ".cuh"))] + [os.path.join(HERE, "..", "include", "amvpt.h")]
     hstamp = _stamp(headers)
-    objs, rebuilt = [], False
+    objs, jobs = [], []
     for src in SOURCES:
         sp = os.path.join(CSRC, src)
         if not os.path.exists(sp):
             continue
         op = os.path.join(OBJ, src + ".o"); st = op + ".stamp"
-        want = hstamp + _stamp([sp])
+        want = hstamp + _stamp([sp]) + " ".join(COMMON)
         if force or not os.path.exists(op) or not os.path.exists(st) or open(st).read() != want:
             cmd = [NVCC] + ARCH + COMMON + ["-x", "cu", "-c", sp, "-o", op]
             if verbose: print(" ".join(cmd), file=sys.stderr)
-            subprocess.run(cmd, check=True)
-            open(st, "w").write(want); rebuilt = True
+            jobs.append((subprocess.Popen(cmd), st, want))      # translation units compile side by side
         objs.append(op)
+    rebuilt = bool(jobs)
+    for proc, st, want in jobs:
+        if proc.wait() != 0:
+            raise subprocess.CalledProcessError(proc.returncode, proc.args)
+        open(st, "w").write(want)
     if rebuilt or not os.path.exists(OUT):
         cmd = [NVCC] + ARCH + ["-shared", "-o", OUT] + objs + ["-lcudart_static", "-lpthread", "-ldl", "-lrt"]
         subprocess.run(cmd, check=True)

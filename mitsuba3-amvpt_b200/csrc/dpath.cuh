@@ -189,11 +189,31 @@ template <bool STATS, int TYPE = -1> AM_D bool shade_vertex(const DScene &s, Pat
     return active_em;
 }
 
+// Optional out-of-line copies of the ray caster, the emitter sampler and the BSDF dispatch for kernels that call them from many
+// places (reuse.cu: per camera, per pair of cameras, and in the suffix loop; -DAM_REUSE_OUTLINE=1).  Inlined everywhere, that kernel is 616 KB of SASS and its warps wait for instruction fetch (ncu: stall_no_instruction 8.9 per issue); these
+// out-of-line copies keep one body each.  The scene record stays in the kernel parameter bank (__grid_constant__), so
+// passing it by reference costs no local copy.
+#ifndef AM_REUSE_OUTLINE
+#define AM_REUSE_OUTLINE 0     /* measured on B200 (profiles/r01_reuse_variants.txt): inlined + 8 CTAs/SM 490 / 51 Mpaths/s (Cornell 8x8 / 1M triangles), out-of-line + 6 CTAs/SM 339 / 48 */
+#endif
+#if AM_REUSE_OUTLINE
+#define AM_NOINLINE static __device__ __noinline__
+#else
+#define AM_NOINLINE static __device__ __forceinline__
+#endif
+AM_NOINLINE Hit trace_closest(const DScene &s, const Ray &ray, StatCtx *st) { return intersect<false>(s, ray, st ? &st->nodes : nullptr, st ? &st->tris : nullptr); }
+AM_NOINLINE bool trace_occluded(const DScene &s, const Ray &ray, StatCtx *st) { return intersect<true>(s, ray, st ? &st->nodes : nullptr, st ? &st->tris : nullptr).tri != AM_NO_HIT; }
+AM_NOINLINE BsdfResult bsdf_call(const DBsdf &b, V3 wi, V3 wo, float s1, V2 s2) { return bsdf_eval_pdf_sample(b, wi, wo, s1, s2); }
+AM_NOINLINE DirectionSample emitter_call(const DScene &s, const SI &si, V2 u, V3 *w, StatCtx *st) {
+    return sample_emitter_direction<false>(s, si, u, w, st ? &st->nodes : nullptr, st ? &st->tris : nullptr);
+}
+
 // One iteration of the while-loop of MVPT::sample_single (src/integrators/mvpath_single.h:130-275), wavefront
 // (JIT) semantics: every lane active at the top of the iteration draws 2 + 1 + 2 + 1 random numbers.
-template <bool TAP, bool STATS> AM_D void path_bounce(const DScene &s, PathState &ps, TapCtx *tap, StatCtx *st) {
+// OUTLINE = true calls the out-of-line copies above instead of inlining ray caster, emitter sampler and BSDF dispatch.
+template <bool TAP, bool STATS, bool OUTLINE = false> AM_D void path_bounce(const DScene &s, PathState &ps, TapCtx *tap, StatCtx *st) {
     uint32_t *cn = STATS ? &st->nodes : nullptr, *ct = STATS ? &st->tris : nullptr;
-    Hit h = intersect<false>(s, ps.ray, cn, ct);
+    Hit h = OUTLINE ? trace_closest(s, ps.ray, STATS ? st : nullptr) : intersect<false>(s, ps.ray, cn, ct);
     if (STATS) { st->closest++; st->vertices++; }
     const DMesh *mesh;
     SI si = make_si(s, ps.ray, h, &mesh);
@@ -223,13 +243,13 @@ template <bool TAP, bool STATS> AM_D void path_bounce(const DScene &s, PathState
     V2 es; es.x = ps.rng.next_f32(); es.y = ps.rng.next_f32();
     DirectionSample ds; V3 em_weight = v3(0.f), wo = v3(0.f); ds.pdf = 0.f;
     if (active_em) {
-        ds = sample_emitter_direction<false>(s, si, es, &em_weight, cn, ct);
+        ds = OUTLINE ? emitter_call(s, si, es, &em_weight, STATS ? st : nullptr) : sample_emitter_direction<false>(s, si, es, &em_weight, cn, ct);
         if (STATS) st->shadow++;
         active_em = ds.pdf != 0.f;
         wo = si.to_local(ds.d);
     }
     float s1 = ps.rng.next_f32(); V2 s2; s2.x = ps.rng.next_f32(); s2.y = ps.rng.next_f32();
-    BsdfResult br = bsdf_eval_pdf_sample(bsdf, si.wi, wo, s1, s2);
+    BsdfResult br = OUTLINE ? bsdf_call(bsdf, si.wi, wo, s1, s2) : bsdf_eval_pdf_sample(bsdf, si.wi, wo, s1, s2);
     if (active_em) {
         float mis_em = mis_weight(ds.pdf, br.pdf);
         ps.result = fmadd(ps.throughput, br.f * em_weight * mis_em, ps.result);

@@ -11,7 +11,7 @@
 // statement, in the JIT variants' semantics (masked virtual calls return zeros; every lane that reaches a draw draws).
 //
 // Schedule: a persistent kernel, one lane per thread, 32 tickets per warp fetch.  The per-camera records (92 B each) live
-// in local memory; the kernel is instantiated for group sizes up to 4 / 8 / 16 / 64 so that small groups keep a small frame.
+// in local memory; the kernel is instantiated for group sizes up to 8 / 64 so that small groups keep a small frame.
 // Not built: the `adaptive` fill-in of mvpath_multi.h:79-115 (the host rejects adaptive > 0) and the `debug` output.
 #include "dpath.cuh"
 
@@ -68,8 +68,7 @@ template <bool PRIMARY, bool STATS> AM_D SurfSample sensors_visible(const DScene
         r.active = r.active && (r.face == prim_face) && r.Jp > 0.f;
         if (r.active) {                       // the visibility test of a masked-out lane is unobservable
             if (STATS) st->shadow++;
-            Hit h = intersect<true>(s, spawn_ray_to(si.p, si.n, r.p), STATS ? &st->nodes : nullptr, STATS ? &st->tris : nullptr);
-            r.active = h.tri == AM_NO_HIT;
+            r.active = !trace_occluded(s, spawn_ray_to(si.p, si.n, r.p), STATS ? st : nullptr);
         }
     }
     return r;
@@ -87,11 +86,11 @@ AM_D float bsdf_roughness(const DBsdf &b) {
 AM_D void bsdf_eval_pdf(const DBsdf *b, V3 wi, V3 wo, bool active, V3 &f, float &pdf) {
     f = v3(0.f); pdf = 0.f; if (!active || !b) return;
     if ((b->flags & L_SMOOTH) == 0) return;          // delta BSDFs: eval = pdf = 0
-    BsdfResult r = bsdf_eval_pdf_sample(*b, wi, wo, .5f, v2(.5f, .5f));
+    BsdfResult r = bsdf_call(*b, wi, wo, .5f, v2(.5f, .5f));
     f = r.f; pdf = r.pdf;
 }
 // BSDF::pdf with BSDFContext(Radiance, Glossy): diffuse lobes are disabled (mvpath_multi.h:371, mvpath.h:277)
-AM_D float bsdf_pdf_glossy(const DBsdf *b, V3 wi, V3 wo, bool active) {
+AM_NOINLINE float bsdf_pdf_glossy(const DBsdf *b, V3 wi, V3 wo, bool active) {
     if (!active || !b) return 0.f;
     if (b->type == BSDF_ROUGHCONDUCTOR || b->type == BSDF_ROUGHDIELECTRIC) { V3 f; float pdf; bsdf_eval_pdf(b, wi, wo, true, f, pdf); return pdf; }
     if (b->type != BSDF_ROUGHPLASTIC) return 0.f;
@@ -157,7 +156,7 @@ template <bool STATS> AM_D void camera_selection(const DScene &s, Pcg32 &rng, DS
         bool indirect = valid, direct = valid;
         const bool replace = n_indir * rng.next_f32() < 1.f;
         BsdfResult br = bsdf_zero();                       // masked virtual call: zeros when !valid
-        if (valid) br = bsdf_eval_pdf_sample(*bd.bsdf, sk.wi, wo, rand_1, rand_2);
+        if (valid) br = bsdf_call(*bd.bsdf, sk.wi, wo, rand_1, rand_2);
         direct = direct && br.pdf > 0.f;
         sk.bsdf_val = br.f;
         direct_pdf += direct ? br.pdf : 0.f;
@@ -205,7 +204,7 @@ template <bool STATS> AM_D void sample_multi(const DScene &s, PathState &ps, DSa
     if (s.max_depth == 0) return;
     DSample &p0 = samples[0];
     const Ray p_ray = ps.ray;
-    Hit h = intersect<false>(s, p_ray, STATS ? &st->nodes : nullptr, STATS ? &st->tris : nullptr);
+    Hit h = trace_closest(s, p_ray, STATS ? st : nullptr);
     if (STATS) { st->closest++; st->vertices++; }
     const DMesh *mesh;
     SI si = make_si(s, p_ray, h, &mesh);
@@ -219,12 +218,12 @@ template <bool STATS> AM_D void sample_multi(const DScene &s, PathState &ps, DSa
     DirectionSample ds; ds.pdf = 0.f; ds.d = v3(0.f); V3 em_weight = v3(0.f), wo = v3(0.f);
     if (active_em) {
         if (STATS) st->shadow++;
-        ds = sample_emitter_direction<false>(s, si, es, &em_weight, STATS ? &st->nodes : nullptr, STATS ? &st->tris : nullptr);
+        ds = emitter_call(s, si, es, &em_weight, STATS ? st : nullptr);
         active_em = ds.pdf != 0.f; wo = si.to_local(ds.d);
     }
     const float rand_1 = ps.rng.next_f32(); V2 rand_2; rand_2.x = ps.rng.next_f32(); rand_2.y = ps.rng.next_f32();
     BsdfResult br = bsdf_zero();
-    if (bsdf) br = bsdf_eval_pdf_sample(*bsdf, si.wi, wo, rand_1, rand_2);
+    if (bsdf) br = bsdf_call(*bsdf, si.wi, wo, rand_1, rand_2);
     const V3 bsdf_val = br.f, bsdf_weight = br.weight; float direct_pdf = br.pdf; BSDFSample bsdf_sample = br.bs;
     const bool flag_delta = (bsdf_sample.type & L_DELTA) != 0, flag_null = (bsdf_sample.type & L_NULL) != 0, flag_diff = (bsdf_sample.type & L_DIFFUSE_R) != 0;
     const bool delta = flag_delta || flag_null, p_not_delta = !delta && p_hit;
@@ -274,8 +273,8 @@ template <bool STATS> AM_D void sample_multi(const DScene &s, PathState &ps, DSa
     ps.active = p_hit;
     if (!should_mis) ps.active = ps.active && hmax(ps.throughput) != 0.f;
     if (s.max_depth <= 1) ps.active = false;
-    if (tap) { while (ps.active) path_bounce<true, STATS>(s, ps, tap, st); }
-    else { while (ps.active) path_bounce<false, STATS>(s, ps, nullptr, st); }
+    if (tap) { while (ps.active) path_bounce<true, STATS, true>(s, ps, tap, st); }
+    else { while (ps.active) path_bounce<false, STATS, true>(s, ps, nullptr, st); }
     const V3 indirect = ps.result;
     if (should_mis) {
         const float pdfW = p_not_delta ? rcp(bsdf_sample.pdf) : 1.f;
@@ -313,8 +312,11 @@ template <bool STATS> AM_D void lane_multi(const DScene &s, uint32_t seed_value,
 }
 
 // ------------------------------------------------------------------------------------------------
-template <int NMAX, bool STATS> __global__ void __launch_bounds__(128)
-render_reuse_kernel(const DScene s, const RenderParams p) {
+#ifndef AM_REUSE_MIN_CTAS
+#define AM_REUSE_MIN_CTAS 8     /* 64 registers per thread: occupancy beats spills here (4 / 6 / 8 CTAs per SM: 404 / 439 / 490 Mpaths/s) */
+#endif
+template <int NMAX, bool STATS> __global__ void __launch_bounds__(128, AM_REUSE_MIN_CTAS)
+render_reuse_kernel(const __grid_constant__ DScene s, const __grid_constant__ RenderParams p) {
     DSample samples[NMAX];
     const unsigned lane_id = threadIdx.x & 31u;
     const uint32_t n = s.n_reuse;
@@ -340,7 +342,7 @@ render_reuse_kernel(const DScene s, const RenderParams p) {
     if (STATS) flush_stats(st, p.counters);
 }
 // Parity tap: the n records of each lane after the tile offset, 9 floats each (mirrors orc_trace_lanes_multi)
-template <int NMAX> __global__ void reuse_tap_kernel(const DScene s, uint32_t seed_value, uint32_t spp_per_pass, uint32_t lane_begin, uint32_t count, float *out) {
+template <int NMAX> __global__ void reuse_tap_kernel(const __grid_constant__ DScene s, uint32_t seed_value, uint32_t spp_per_pass, uint32_t lane_begin, uint32_t count, float *out) {
     DSample samples[NMAX];
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; if (i >= count) return;
     const uint32_t n = s.n_reuse, lane = lane_begin + i, idx = lane / spp_per_pass, py = idx / s.film_w, px = idx - s.film_w * py;
@@ -353,27 +355,21 @@ template <int NMAX> __global__ void reuse_tap_kernel(const DScene s, uint32_t se
     }
 }
 
-template <int NMAX> static void launch_reuse_n(const DScene &s, const RenderParams &p, int sm_count, bool stats, cudaStream_t st) {
+// Instantiations are kept few (each is ~0.6 MB of SASS and minutes of ptxas): group sizes <= 8 and <= 64; the counting
+// variant and the parity tap exist for 64 only.
+template <int NMAX, bool STATS> static void launch_reuse_n(const DScene &s, const RenderParams &p, int sm_count, cudaStream_t st) {
     int per_sm = 0;
-    if (stats) {
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, render_reuse_kernel<NMAX, true>, 128, 0);
-        render_reuse_kernel<NMAX, true><<<sm_count * (per_sm > 0 ? per_sm : 1), 128, 0, st>>>(s, p);
-    } else {
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, render_reuse_kernel<NMAX, false>, 128, 0);
-        render_reuse_kernel<NMAX, false><<<sm_count * (per_sm > 0 ? per_sm : 1), 128, 0, st>>>(s, p);
-    }
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, render_reuse_kernel<NMAX, STATS>, 128, 0);
+    render_reuse_kernel<NMAX, STATS><<<sm_count * (per_sm > 0 ? per_sm : 1), 128, 0, st>>>(s, p);
 }
 void launch_reuse_pass(const DScene &s, const RenderParams &p, int sm_count, bool stats, cudaStream_t st) {
-    if (s.n_reuse <= 4) launch_reuse_n<4>(s, p, sm_count, stats, st);
-    else if (s.n_reuse <= 8) launch_reuse_n<8>(s, p, sm_count, stats, st);
-    else if (s.n_reuse <= 16) launch_reuse_n<16>(s, p, sm_count, stats, st);
-    else launch_reuse_n<64>(s, p, sm_count, stats, st);
+    if (stats) launch_reuse_n<64, true>(s, p, sm_count, st);
+    else if (s.n_reuse <= 8) launch_reuse_n<8, false>(s, p, sm_count, st);
+    else launch_reuse_n<64, false>(s, p, sm_count, st);
 }
 void launch_reuse_tap(const DScene &s, uint32_t seed_value, uint32_t spp_per_pass, uint32_t lane_begin, uint32_t n, float *out, cudaStream_t st) {
     if (!n) return;
-    const uint32_t blocks = (n + 63) / 64;
-    if (s.n_reuse <= 8) reuse_tap_kernel<8><<<blocks, 64, 0, st>>>(s, seed_value, spp_per_pass, lane_begin, n, out);
-    else reuse_tap_kernel<64><<<blocks, 64, 0, st>>>(s, seed_value, spp_per_pass, lane_begin, n, out);
+    reuse_tap_kernel<64><<<(n + 63) / 64, 64, 0, st>>>(s, seed_value, spp_per_pass, lane_begin, n, out);
 }
 
 } // namespace amvpt

@@ -827,7 +827,7 @@ double orc_render_rows(void *sp, uint32_t seed, uint32_t spp, uint32_t spp_pass_
     std::vector<TraverseStats> tstats(std::max(nthreads, 1));
     // a wider filter splats across rows: every thread then accumulates into its own film, summed in thread order at the end
     size_t film_floats = 4 * (size_t) s.film_w * s.film_h;
-    std::vector<std::vector<float>> tfilm; if ((s.filter_type != 0 || s.n_reuse) && nthreads > 1) tfilm.assign(nthreads, std::vector<float>(film_floats, 0.f));
+    std::vector<std::vector<float>> tfilm; if (s.filter_type != 0 && nthreads > 1) tfilm.assign(nthreads, std::vector<float>(film_floats, 0.f));
     auto t0 = std::chrono::steady_clock::now();
     auto worker = [&](int tid) {
         for (;;) {
@@ -837,10 +837,12 @@ double orc_render_rows(void *sp, uint32_t seed, uint32_t spp, uint32_t spp_pass_
                 uint32_t seed_value = s.base_seed + (spp_per_pass * pass + seed);
                 for (uint32_t x = 0; x < s.film_w; ++x) for (uint32_t k = 0; k < spp_per_pass; ++k) {
                     uint32_t lane = (y * s.film_w + x) * spp_per_pass + k;
-                    if (s.n_reuse) {          // reused samples land in other view tiles: per-thread films, as with a wide filter
-                        float *f = tfilm.empty() ? film : tfilm[tid].data();
+                    if (s.n_reuse) {          // reused samples land in other view tiles (other threads' rows): atomic float adds
+                        auto add = [](float *p, float v) { uint32_t o, n; std::memcpy(&o, p, 4);
+                            do { float f; std::memcpy(&f, &o, 4); f += v; std::memcpy(&n, &f, 4); } while (!__atomic_compare_exchange_n((uint32_t *) p, &o, n, true, __ATOMIC_RELAXED, __ATOMIC_RELAXED)); };
                         render_lane_multi(s, seed_value, lane, spp_per_pass, s.n_reuse, brute != 0, nullptr, &tstats[tid],
-                                          [&](uint32_t ux, uint32_t uy, V3 v, float w) { float *px = f + 4 * ((size_t) uy * s.film_w + ux); px[0] += v.x; px[1] += v.y; px[2] += v.z; px[3] += w; });
+                                          [&](uint32_t ux, uint32_t uy, V3 v, float w) { float *px = film + 4 * ((size_t) uy * s.film_w + ux);
+                                              if (nthreads > 1) { add(px, v.x); add(px + 1, v.y); add(px + 2, v.z); add(px + 3, w); } else { px[0] += v.x; px[1] += v.y; px[2] += v.z; px[3] += w; } });
                         continue;
                     }
                     LaneOut o = render_lane(s, seed_value, lane, spp_per_pass, brute != 0, nullptr, &tstats[tid]);
