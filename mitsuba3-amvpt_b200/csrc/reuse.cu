@@ -313,7 +313,7 @@ template <bool STATS> AM_D void lane_multi(const DScene &s, uint32_t seed_value,
 
 // ------------------------------------------------------------------------------------------------
 #ifndef AM_REUSE_MIN_CTAS
-#define AM_REUSE_MIN_CTAS 8     /* 64 registers per thread: occupancy beats spills here (4 / 6 / 8 CTAs per SM: 404 / 439 / 490 Mpaths/s) */
+#define AM_REUSE_MIN_CTAS 16    /* 32 registers per thread: the kernel is latency-bound and occupancy beats spills (4 / 8 / 12 / 16 CTAs per SM: 404 / 490 / 568 / 590 Mpaths/s on the Cornell 8x8 quilt, 45 / 51 / 57 / 66 on 1M triangles) */
 #endif
 template <int NMAX, bool STATS> __global__ void __launch_bounds__(128, AM_REUSE_MIN_CTAS)
 render_reuse_kernel(const __grid_constant__ DScene s, const __grid_constant__ RenderParams p) {

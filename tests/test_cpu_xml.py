@@ -50,6 +50,14 @@ def test_xml_matches_programmatic_cbox(pkg, scenes, tmp_path, fmt):
     assert a.integrator()["is_mvpath"] and a.integrator()["sample_count"] == 48
     c = pkg.load_file(path, spp=16)          # -Dspp=16 overrides <default>
     assert c.info()["sample_count"] == 16
+    # mvpath's sample-reuse parameters (mvpath.h:120-129) travel through the XML like through set_reuse
+    desc["reuse"] = dict(sa_reuse=True, sa_mis=True, fast_mis=True, reuse_count=4)
+    path = scenes.export_xml(desc, str(tmp_path), mesh_format=fmt, filename="reuse.xml")
+    a = pkg.load_file(path); b = scenes.build(desc, commit=False)
+    same_scene(a, b)
+    assert a.integrator()["sa_reuse"] and a.integrator()["reuse_count"] == 4 and b.n_reuse == 4
+    assert b.set_reuse(sa_reuse=True, reuse_count=3) == 8       # 3 does not divide 8 sub-sensors: first divisor >= 8 (mvpath.cpp:196-217)
+    assert b.set_reuse(sa_reuse=True, reuse_count=1) == 0 and b.set_reuse(sa_reuse=False, reuse_count=4) == 0
 
 
 def test_xml_materials_thinlens_cone_and_normals(pkg, scenes, tmp_path):
