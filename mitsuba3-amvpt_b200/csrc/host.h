@@ -80,6 +80,7 @@ struct Scene {
     float4 *film = nullptr; float2 *moments = nullptr; float *rgb = nullptr;
     unsigned long long *counters = nullptr; TileDesc *tiles_dev = nullptr; float *view_stats_dev = nullptr;
     uint32_t tiles_cap = 0;
+    float4 *reuse_buf = nullptr; uint32_t reuse_cap = 0;   // staged sample-reuse schedule: per-chunk hit + projection records
     WfPool wf{}; uint32_t wf_type_mask = 0;     // wavefront scheduler pool (allocated on first use)
     uint32_t n_nodes = 0, n_tris = 0;
     volatile bool stop = false;

@@ -47,6 +47,8 @@ uint32_t run_wavefront_pass(const DScene &s, const RenderParams &p, const WfPool
 
 // sample-reuse branch (reuse.cu)
 void launch_reuse_pass(const DScene &s, const RenderParams &p, int sm_count, bool stats, cudaStream_t st);
+size_t reuse_staged_float4s(uint32_t n_reuse, uint32_t m_cap);    // size of `buf` below
+uint32_t run_reuse_staged(const DScene &s, const RenderParams &p, float4 *buf, uint32_t m_cap, int schedule /* 1 staged, 2 pipeline */, int sm_count, cudaStream_t st);
 void launch_reuse_tap(const DScene &s, uint32_t seed_value, uint32_t spp_per_pass, uint32_t lane_begin, uint32_t n, float *out /* n * n_reuse * 9 */, cudaStream_t st);
 
 // host-callable launchers (kernels.cu)

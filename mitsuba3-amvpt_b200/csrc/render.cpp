@@ -118,9 +118,20 @@ void render(Scene &s, const RenderOptions &opt) {
             }
             rs.launches += run_wavefront_pass(s.d, p, s.wf, s.wf_type_mask, s.sm_count, opt.stats, st, opt.time_stages ? &rs.trace_seconds : nullptr, &rs.trace_launches);
         } else if (mode == SCHED_REUSE) {
-            launch_reuse_pass(s.d, p, s.sm_count, opt.stats, st);
+            // 0: one persistent kernel; 1: primary / project / shade kernels per chunk; 2 (default): primary / project / select / suffix / finish
+            const int schedule = opt.stats ? 0 : (getenv("AMVPT_REUSE_STAGED") ? atoi(getenv("AMVPT_REUSE_STAGED")) : 2);
+            if (schedule) {
+                // chunk size: 2^22 lanes, less for large groups so that the projection records stay near 1 GB
+                const uint32_t nk = s.d.n_reuse - 1u;
+                uint32_t m_cap = getenv("AMVPT_REUSE_CHUNK") ? (uint32_t) atoi(getenv("AMVPT_REUSE_CHUNK")) : std::min(1u << 22, (1u << 25) / nk);
+                m_cap = std::max(128u, m_cap / 128u * 128u);
+                if (!s.reuse_buf || s.reuse_cap != m_cap) { s.reuse_buf = (float4 *) s.dalloc(sizeof(float4) * reuse_staged_float4s(s.d.n_reuse, m_cap)); s.reuse_cap = m_cap; }
+                rs.launches += run_reuse_staged(s.d, p, s.reuse_buf, m_cap, schedule, s.sm_count, st);
+            } else {
+                launch_reuse_pass(s.d, p, s.sm_count, opt.stats, st);
+                rs.launches++;
+            }
             AM_CUDA(cudaGetLastError());
-            rs.launches++;
         } else {
             launch_render_pass(s.d, p, mode, s.sm_count, opt.stats, st);
             AM_CUDA(cudaGetLastError());

@@ -22,6 +22,19 @@ struct DSample {             // mvpath.h:150-167
 };
 struct SurfSample { V3 p, d; float uvx, uvy, pdf, Jp; bool face, active; };
 struct BsdfData { const DBsdf *bsdf; float alpha, sqr_a, rsqrt_a; bool diffuse, reuse; };
+// Staged schedule: results of the primary-ray stage (hit record) and of the projection stage (one record per candidate
+// camera) of this lane, written by reuse_primary_kernel / reuse_project_kernel (below)
+struct Staged { const float4 *prim, *proj; uint32_t m, i, nk; };
+AM_D Hit staged_hit(const Staged &g) { float4 a = g.prim[g.i]; Hit h; h.t = a.x; h.u = a.y; h.v = a.z; h.tri = __float_as_uint(a.w); return h; }
+AM_D SurfSample staged_proj(const Staged &g, uint32_t k, bool active) {
+    SurfSample r; r.p = v3(0.f); r.d = v3(0.f); r.uvx = r.uvy = r.pdf = r.Jp = 0.f; r.face = false; r.active = false;
+    if (!active) return r;                       // masked virtual call (grid.cpp:331-336): zeros
+    const size_t o = (size_t) (k - 1) * g.m + g.i;
+    float4 e = g.proj[o], f = g.proj[(size_t) g.nk * g.m + o];
+    r.uvx = e.x; r.uvy = e.y; r.pdf = e.z; r.Jp = e.w; r.d = v3(f.x, f.y, f.z);
+    const uint32_t fl = __float_as_uint(f.w); r.active = (fl & 1u) != 0; r.face = (fl & 2u) != 0;
+    return r;
+}
 
 // sample_surface behind the masked virtual call of GridSensor::sample_surface (grid.cpp:331-336)
 AM_D SurfSample sensor_sample_surface(const DScene &s, uint32_t idx, V3 it_p, V3 it_n, V2 sample, bool active) {
@@ -125,8 +138,8 @@ AM_D BsdfResult bsdf_zero() {
 }
 
 // MVPT::camera_selection (mvpath_multi.h:360-462)
-template <bool STATS> AM_D void camera_selection(const DScene &s, Pcg32 &rng, DSample *samples, uint32_t n, const SI &si, const BsdfData &bd, V3 wo, V2 p_app,
-                                                 V2 rand_2, float rand_1, bool p_hit, BSDFSample &bsdf_sample, float &direct_pdf, StatCtx *st) {
+template <bool STATS, int STAGED> AM_D void camera_selection(const DScene &s, Pcg32 &rng, DSample *samples, uint32_t n, const SI &si, const BsdfData &bd, V3 wo, V2 p_app,
+                                                 V2 rand_2, float rand_1, bool p_hit, BSDFSample &bsdf_sample, float &direct_pdf, StatCtx *st, const Staged *stg) {
     DSample &p = samples[0];
     const bool p_face = si.wi.z > 0.f;
     SurfSample pds = sensors_visible<true, STATS>(s, p_app, si, p_face, p.idx, p_hit, st);
@@ -138,7 +151,7 @@ template <bool STATS> AM_D void camera_selection(const DScene &s, Pcg32 &rng, DS
     float n_direct = 1.f, n_indir = 2.f;
     for (uint32_t k = 1; k < n; ++k) {
         DSample &sk = samples[k];
-        SurfSample ds = sensors_visible<false, STATS>(s, p_app, si, p_face, sk.idx, bd.reuse, st);
+        SurfSample ds = STAGED >= 1 ? staged_proj(*stg, k, bd.reuse) : sensors_visible<false, STATS>(s, p_app, si, p_face, sk.idx, bd.reuse, st);
         bool valid = ds.active;
         sk.wi = si.to_local(ds.d); sk.wo_r = reflect(sk.wi);
         sk.pdfM = pdf_material(s, bd, sk.wi, sk.wo_r, valid);
@@ -200,11 +213,11 @@ AM_D void mis_weights(const DScene &s, DSample *samples, uint32_t n, const BsdfD
 
 // MVPT::sample_multi (mvpath_multi.h:133-358).  `ps` arrives from lane_setup (sampler state, primary ray) and leaves as the
 // state of the finished suffix path.
-template <bool STATS> AM_D void sample_multi(const DScene &s, PathState &ps, DSample *samples, uint32_t n, V2 p_app, StatCtx *st, TapCtx *tap) {
+template <bool STATS, int STAGED> AM_D void sample_multi(const DScene &s, PathState &ps, DSample *samples, uint32_t n, V2 p_app, StatCtx *st, TapCtx *tap, const Staged *stg, bool *mis_out = nullptr) {
     if (s.max_depth == 0) return;
     DSample &p0 = samples[0];
     const Ray p_ray = ps.ray;
-    Hit h = trace_closest(s, p_ray, STATS ? st : nullptr);
+    Hit h = STAGED >= 1 ? staged_hit(*stg) : trace_closest(s, p_ray, STATS ? st : nullptr);
     if (STATS) { st->closest++; st->vertices++; }
     const DMesh *mesh;
     SI si = make_si(s, p_ray, h, &mesh);
@@ -218,7 +231,8 @@ template <bool STATS> AM_D void sample_multi(const DScene &s, PathState &ps, DSa
     DirectionSample ds; ds.pdf = 0.f; ds.d = v3(0.f); V3 em_weight = v3(0.f), wo = v3(0.f);
     if (active_em) {
         if (STATS) st->shadow++;
-        ds = emitter_call(s, si, es, &em_weight, STATS ? st : nullptr);
+        if (STAGED == 2) { float4 a = stg->prim[4 * (size_t) stg->m + stg->i], b = stg->prim[5 * (size_t) stg->m + stg->i]; em_weight = v3(a.x, a.y, a.z); ds.pdf = a.w; ds.d = v3(b.x, b.y, b.z); }
+        else ds = emitter_call(s, si, es, &em_weight, STATS ? st : nullptr);
         active_em = ds.pdf != 0.f; wo = si.to_local(ds.d);
     }
     const float rand_1 = ps.rng.next_f32(); V2 rand_2; rand_2.x = ps.rng.next_f32(); rand_2.y = ps.rng.next_f32();
@@ -233,12 +247,12 @@ template <bool STATS> AM_D void sample_multi(const DScene &s, PathState &ps, DSa
         BsdfData bd; bd.bsdf = bsdf; bd.alpha = bsdf ? bsdf_roughness(*bsdf) : 0.f;
         bd.sqr_a = fmsub(bd.alpha, bd.alpha, 1.f); bd.rsqrt_a = rsqrt(bd.alpha); bd.diffuse = flag_diff; bd.reuse = reuse;
         p0.bsdf_val = bsdf_val;
-        camera_selection<STATS>(s, ps.rng, samples, n, si, bd, wo, p_app, rand_2, rand_1, p_hit, bsdf_sample, direct_pdf, st);
+        camera_selection<STATS, STAGED>(s, ps.rng, samples, n, si, bd, wo, p_app, rand_2, rand_1, p_hit, bsdf_sample, direct_pdf, st, stg);
         mis_weights(s, samples, n, bd);
     } else if (should_reuse) {
         p0.valid = p_hit; const bool p_face = si.wi.z > 0.f;
         for (uint32_t k = 1; k < n; ++k) {
-            SurfSample sd = sensors_visible<false, STATS>(s, p_app, si, p_face, samples[k].idx, reuse, st);
+            SurfSample sd = STAGED >= 1 ? staged_proj(*stg, k, reuse) : sensors_visible<false, STATS>(s, p_app, si, p_face, samples[k].idx, reuse, st);
             samples[k].px = sd.uvx; samples[k].py = sd.uvy; samples[k].valid = sd.active;
         }
     }
@@ -273,6 +287,16 @@ template <bool STATS> AM_D void sample_multi(const DScene &s, PathState &ps, DSa
     ps.active = p_hit;
     if (!should_mis) ps.active = ps.active && hmax(ps.throughput) != 0.f;
     if (s.max_depth <= 1) ps.active = false;
+    if (STAGED == 2) {
+        // pipeline schedule: the suffix path runs in reuse_suffix_kernel and enters the samples in reuse_finish_kernel as
+        // result = fmadd(coef, indirect, result) (MIS) or result0 + indirect (no MIS); coef = bsdf_val * pdfW is left in bsdf_val
+        if (should_mis) {
+            const float pdfW = p_not_delta ? rcp(bsdf_sample.pdf) : 1.f;
+            for (uint32_t k = 0; k < n; ++k) if (samples[k].indirect) samples[k].bsdf_val = samples[k].bsdf_val * pdfW;
+        } else { p0.weight = 1.f; for (uint32_t k = 1; k < n; ++k) samples[k].weight = 1.f; }
+        p0.weight = p_hit ? p0.weight : 1.f; p0.valid = true; *mis_out = should_mis;
+        return;
+    }
     if (tap) { while (ps.active) path_bounce<true, STATS, true>(s, ps, tap, st); }
     else { while (ps.active) path_bounce<false, STATS, true>(s, ps, nullptr, st); }
     const V3 indirect = ps.result;
@@ -288,8 +312,8 @@ template <bool STATS> AM_D void sample_multi(const DScene &s, PathState &ps, DSa
 }
 
 // MVPT::render_multisample (mvpath_multi.h:8-78) for one lane: camera group, sample_multi, tile offsets of the reused samples
-template <bool STATS> AM_D void lane_multi(const DScene &s, uint32_t seed_value, uint32_t lane, uint32_t px, uint32_t py, DSample *samples, uint32_t n,
-                                           StatCtx *st, TapCtx *tap) {
+template <bool STATS, int STAGED = 0> AM_D void lane_multi(const DScene &s, uint32_t seed_value, uint32_t lane, uint32_t px, uint32_t py, DSample *samples, uint32_t n,
+                                           StatCtx *st, TapCtx *tap, const Staged *stg = nullptr, PathState *ps_out = nullptr, bool *mis_out = nullptr) {
     PathState ps; LaneSetup ls; V2 aperture;
     lane_setup(s, seed_value, lane, px, py, ps, ls, &aperture);
     const uint32_t p_idx = ls.view, max_idx = n * (p_idx / n + 1u);
@@ -300,7 +324,8 @@ template <bool STATS> AM_D void lane_multi(const DScene &s, uint32_t seed_value,
         const uint32_t i = p_idx + k; d.idx = i < max_idx ? i : i - n;
     }
     samples[0].px = ls.spx; samples[0].py = ls.spy;
-    sample_multi<STATS>(s, ps, samples, n, aperture, st, tap);
+    sample_multi<STATS, STAGED>(s, ps, samples, n, aperture, st, tap, stg, mis_out);
+    if (ps_out) *ps_out = ps;
     const uint32_t sres_x = s.film_w / s.grid_x, sres_y = s.film_h / s.grid_y;
     for (uint32_t k = 1; k < n; ++k) {
         DSample &d = samples[k];
@@ -309,6 +334,163 @@ template <bool STATS> AM_D void lane_multi(const DScene &s, uint32_t seed_value,
         if (s.reverse_y) y = (s.grid_y - 1) - y;
         d.px += (float) (x * sres_x); d.py += (float) (y * sres_y);
     }
+}
+
+// ImageBlock::put, box path (imageblock.cpp:210-233): values = { weight * ray_weight * result, weight }
+AM_D void splat_samples(const DScene &s, float4 *film, const DSample *samples, uint32_t n) {
+    for (uint32_t k = 0; k < n; ++k) {
+        const DSample &d = samples[k];
+        if (!d.valid) continue;
+        const uint32_t ux = (uint32_t) (int32_t) floorf(d.px), uy = (uint32_t) (int32_t) floorf(d.py);
+        if (!(ux < s.film_w && uy < s.film_h)) continue;
+        const float w = d.weight * 1.f;
+        atomicAdd(film + (size_t) uy * s.film_w + ux, make_float4(w * d.result.x, w * d.result.y, w * d.result.z, d.weight));
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Staged schedule (default): the pass is cut into chunks of m lanes and each chunk runs three small kernels instead of the
+// one big persistent kernel.  (1) primary: camera ray + closest hit + the hit point's position / geometric normal / side;
+// (2) project: ONE THREAD PER (lane, candidate camera) evaluates sample_surface and traces the visibility ray -- these rays
+// are 60 % of all rays of the branch, and here they run with full warps through 10 KB of code; (3) shade: everything else
+// (light sample, BSDF calls, camera selection with the sampler's draws in the reference's order, MIS weights, mixture pdf,
+// the suffix path, splat), reading the hit and the projection records instead of tracing.  Same arithmetic, same bits.
+#ifndef AM_REUSE_SHADE_MIN_CTAS
+#define AM_REUSE_SHADE_MIN_CTAS 12
+#endif
+#ifndef AM_REUSE_SUFFIX_MIN_CTAS
+#define AM_REUSE_SUFFIX_MIN_CTAS 5
+#endif
+__global__ void __launch_bounds__(128)
+reuse_primary_kernel(const __grid_constant__ DScene s, const __grid_constant__ RenderParams p, unsigned long long c0, uint32_t m, float4 *prim) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; if (i >= m) return;
+    uint32_t lane, px, py; if (!ticket_to_lane(p, s, c0 + i, &lane, &px, &py)) return;
+    PathState ps; LaneSetup ls; V2 ap;
+    lane_setup(s, p.seed_value, lane, px, py, ps, ls, &ap);
+    Hit h = intersect<false>(s, ps.ray);
+    const DMesh *mesh; SI si = make_si(s, ps.ray, h, &mesh);
+    const bool cand = si.valid && mesh->emitter < 0 && (s.bsdfs[mesh->bsdf].flags & L_SMOOTH) != 0;
+    const uint32_t fl = ls.view | (cand ? 1u << 16 : 0u) | (si.wi.z > 0.f ? 1u << 17 : 0u);
+    prim[i] = make_float4(h.t, h.u, h.v, __uint_as_float(h.tri));
+    prim[(size_t) m + i] = make_float4(si.p.x, si.p.y, si.p.z, __uint_as_float(fl));
+    prim[2 * (size_t) m + i] = make_float4(si.n.x, si.n.y, si.n.z, 0.f);
+    prim[3 * (size_t) m + i] = make_float4(ap.x, ap.y, 0.f, 0.f);
+    // light sample of the primary vertex (mvpath_multi.h:176-189): the sampler's next two numbers, visibility ray included
+    V3 em_weight = v3(0.f); DirectionSample ds; ds.pdf = 0.f; ds.d = v3(0.f);
+    if (si.valid && (s.bsdfs[mesh->bsdf].flags & L_SMOOTH) != 0 && s.max_depth != 0) {
+        V2 es; es.x = ps.rng.next_f32(); es.y = ps.rng.next_f32();
+        ds = sample_emitter_direction<false>(s, si, es, &em_weight, nullptr, nullptr);
+    }
+    prim[4 * (size_t) m + i] = make_float4(em_weight.x, em_weight.y, em_weight.z, ds.pdf);
+    prim[5 * (size_t) m + i] = make_float4(ds.d.x, ds.d.y, ds.d.z, 0.f);
+}
+__global__ void __launch_bounds__(128)
+reuse_project_kernel(const __grid_constant__ DScene s, uint32_t m, uint32_t nk, const float4 *prim, float4 *proj) {
+    const size_t j = (size_t) blockIdx.x * blockDim.x + threadIdx.x; if (j >= (size_t) m * nk) return;
+    const uint32_t i = (uint32_t) (j % m), k = (uint32_t) (j / m) + 1u, n = nk + 1u;
+    const float4 b = prim[(size_t) m + i], c = prim[2 * (size_t) m + i], d = prim[3 * (size_t) m + i];
+    const uint32_t fl = __float_as_uint(b.w), view = fl & 0xffffu; const bool cand = (fl >> 16) & 1u, p_face = (fl >> 17) & 1u;
+    const uint32_t max_idx = n * (view / n + 1u); uint32_t idx = view + k; idx = idx < max_idx ? idx : idx - n;
+    SI si; si.p = v3(b.x, b.y, b.z); si.n = v3(c.x, c.y, c.z);
+    SurfSample r = sensors_visible<false, false>(s, v2(d.x, d.y), si, p_face, idx, cand, nullptr);
+    proj[j] = make_float4(r.uvx, r.uvy, r.pdf, r.Jp);
+    proj[(size_t) nk * m + j] = make_float4(r.d.x, r.d.y, r.d.z, __uint_as_float((r.active ? 1u : 0u) | (r.face ? 2u : 0u)));
+}
+template <int NMAX> __global__ void __launch_bounds__(128, AM_REUSE_SHADE_MIN_CTAS)
+reuse_shade_kernel(const __grid_constant__ DScene s, const __grid_constant__ RenderParams p, unsigned long long c0, uint32_t m, const float4 *prim, const float4 *proj) {
+    DSample samples[NMAX];
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; if (i >= m) return;
+    uint32_t lane, px, py; if (!ticket_to_lane(p, s, c0 + i, &lane, &px, &py)) return;
+    const uint32_t n = s.n_reuse;
+    Staged g; g.prim = prim; g.proj = proj; g.m = m; g.i = i; g.nk = n - 1u;
+    StatCtx st; st.closest = st.shadow = st.nodes = st.tris = st.vertices = 0;
+    lane_multi<false, 1>(s, p.seed_value, lane, px, py, samples, n, &st, nullptr, &g);
+    splat_samples(s, p.film, samples, n);
+}
+
+// Pipeline schedule (AMVPT_REUSE_STAGED=2, default): the shade stage is cut once more.  (3a) select: as (3) but neither the
+// light's visibility ray (done by the primary stage) nor the suffix path: it leaves the suffix's start state and, per
+// camera, { film position, weight, flags }, the radiance so far and the coefficient of the suffix radiance; (3b) suffix: the
+// persistent path-regeneration loop of render_pass_kernel over the stored states; (3c) finish: one thread per
+// (lane, camera): result = fmadd(coef, indirect, result) (or result0 + indirect without MIS) and the 16-byte film RED.
+struct PipeBufs { float4 *state; uint4 *rng; float4 *ind; float4 *rec; };    // state: 4 m, rng: m, ind: m, rec: 3 n m
+template <int NMAX> __global__ void __launch_bounds__(128, AM_REUSE_SHADE_MIN_CTAS)
+reuse_select_kernel(const __grid_constant__ DScene s, const __grid_constant__ RenderParams p, unsigned long long c0, uint32_t m, const float4 *prim, const float4 *proj, PipeBufs b) {
+    DSample samples[NMAX];
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; if (i >= m) return;
+    uint32_t lane, px, py; if (!ticket_to_lane(p, s, c0 + i, &lane, &px, &py)) return;
+    const uint32_t n = s.n_reuse;
+    Staged g; g.prim = prim; g.proj = proj; g.m = m; g.i = i; g.nk = n - 1u;
+    StatCtx st; PathState ps; bool mis = false; ps.active = false; ps.depth = 0; ps.prev_delta = false;
+    ps.ray.o = ps.ray.d = ps.throughput = ps.prev_p = v3(0.f); ps.eta = ps.prev_bsdf_pdf = 0.f; ps.rng.state = ps.rng.inc = 0;
+    lane_multi<false, 2>(s, p.seed_value, lane, px, py, samples, n, &st, nullptr, &g, &ps, &mis);
+    const bool act = ps.active && s.max_depth != 0;
+    b.state[i] = make_float4(ps.ray.o.x, ps.ray.o.y, ps.ray.o.z, ps.prev_bsdf_pdf);
+    b.state[(size_t) m + i] = make_float4(ps.ray.d.x, ps.ray.d.y, ps.ray.d.z, ps.eta);
+    b.state[2 * (size_t) m + i] = make_float4(ps.throughput.x, ps.throughput.y, ps.throughput.z, __uint_as_float(ps.depth | (ps.prev_delta ? 1u << 30 : 0u) | (act ? 1u << 31 : 0u)));
+    b.state[3 * (size_t) m + i] = make_float4(ps.prev_p.x, ps.prev_p.y, ps.prev_p.z, __uint_as_float(mis ? 1u : 0u));
+    b.rng[i] = make_uint4((uint32_t) ps.rng.state, (uint32_t) (ps.rng.state >> 32), (uint32_t) ps.rng.inc, (uint32_t) (ps.rng.inc >> 32));
+    b.ind[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    const size_t nm = (size_t) n * m;
+    for (uint32_t k = 0; k < n; ++k) {
+        const DSample &d = samples[k]; const size_t o = (size_t) k * m + i;
+        b.rec[o] = make_float4(d.px, d.py, d.weight, __uint_as_float((d.valid ? 1u : 0u) | (d.indirect ? 2u : 0u)));
+        b.rec[nm + o] = make_float4(d.result.x, d.result.y, d.result.z, 0.f);
+        b.rec[2 * nm + o] = make_float4(d.bsdf_val.x, d.bsdf_val.y, d.bsdf_val.z, 0.f);
+    }
+}
+__global__ void __launch_bounds__(128, AM_REUSE_SUFFIX_MIN_CTAS)
+reuse_suffix_kernel(const __grid_constant__ DScene s, uint32_t m, uint32_t regen_min, PipeBufs b, unsigned long long *ticket_ctr) {
+    const unsigned lane_id = threadIdx.x & 31u;
+    PathState ps; ps.active = false; uint32_t slot = 0xffffffffu; bool exhausted = false;
+    StatCtx st;
+    for (;;) {
+        const bool idle = !ps.active;
+        const unsigned idle_mask = __ballot_sync(0xffffffffu, idle);
+        if (__popc(idle_mask) >= (int) regen_min || idle_mask == 0xffffffffu) {
+            if (idle) {
+                if (slot != 0xffffffffu) { b.ind[slot] = make_float4(ps.result.x, ps.result.y, ps.result.z, 0.f); slot = 0xffffffffu; }
+                const unsigned fm = __ballot_sync(idle_mask, !exhausted);
+                if (!exhausted) {
+                    unsigned long long base = 0; const unsigned leader = __ffs(fm) - 1;
+                    if (lane_id == leader) base = atomicAdd(ticket_ctr, (unsigned long long) __popc(fm));
+                    base = __shfl_sync(fm, base, leader);
+                    const unsigned long long ticket = base + __popc(fm & ((1u << lane_id) - 1u));
+                    if (ticket < m) {
+                        const uint32_t i = (uint32_t) ticket;
+                        const float4 c = b.state[2 * (size_t) m + i]; const uint32_t fl = __float_as_uint(c.w);
+                        if (fl >> 31) {                    // paths without a suffix (miss, max_depth, zero throughput) keep ind = 0
+                            const float4 a = b.state[i], d = b.state[(size_t) m + i], e = b.state[3 * (size_t) m + i]; const uint4 g = b.rng[i];
+                            ps.ray.o = v3(a.x, a.y, a.z); ps.ray.d = v3(d.x, d.y, d.z); ps.ray.maxt = AM_LARGEST; ps.prev_bsdf_pdf = a.w; ps.eta = d.w;
+                            ps.throughput = v3(c.x, c.y, c.z); ps.depth = fl & 0x3fffffffu; ps.prev_delta = (fl >> 30) & 1u; ps.prev_p = v3(e.x, e.y, e.z);
+                            ps.result = v3(0.f); ps.valid_ray = false; ps.active = true;
+                            ps.rng.state = (uint64_t) g.x | ((uint64_t) g.y << 32); ps.rng.inc = (uint64_t) g.z | ((uint64_t) g.w << 32);
+                            slot = i;
+                        }
+                    } else exhausted = true;
+                }
+            }
+            if (__all_sync(0xffffffffu, !ps.active && exhausted)) break;
+        }
+        if (ps.active) path_bounce<false, false>(s, ps, nullptr, &st);
+    }
+}
+__global__ void __launch_bounds__(256)
+reuse_finish_kernel(const __grid_constant__ DScene s, uint32_t m, uint32_t n, PipeBufs b, float4 *film) {
+    const size_t j = (size_t) blockIdx.x * blockDim.x + threadIdx.x, nm = (size_t) n * m; if (j >= nm) return;
+    const uint32_t i = (uint32_t) (j % m), k = (uint32_t) (j / m);
+    const float4 r0 = b.rec[j]; const uint32_t fl = __float_as_uint(r0.w);
+    if (!(fl & 1u)) return;
+    const float4 ind = b.ind[i]; const bool mis = __float_as_uint(b.state[3 * (size_t) m + i].w) & 1u;
+    V3 result;
+    if (mis) {
+        const float4 r1 = b.rec[nm + j]; result = v3(r1.x, r1.y, r1.z);
+        if (fl & 2u) { const float4 r2 = b.rec[2 * nm + j]; result = fmadd(v3(r2.x, r2.y, r2.z), v3(ind.x, ind.y, ind.z), result); }
+    } else { const float4 r1 = b.rec[nm + i]; result = v3(r1.x, r1.y, r1.z) + v3(ind.x, ind.y, ind.z); }     // every camera takes the primary's radiance (mvpath_multi.h:343-350)
+    const uint32_t ux = (uint32_t) (int32_t) floorf(r0.x), uy = (uint32_t) (int32_t) floorf(r0.y);
+    if (!(ux < s.film_w && uy < s.film_h)) return;
+    const float w = r0.z * 1.f;
+    atomicAdd(film + (size_t) uy * s.film_w + ux, make_float4(w * result.x, w * result.y, w * result.z, r0.z));
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -329,15 +511,7 @@ render_reuse_kernel(const __grid_constant__ DScene s, const __grid_constant__ Re
         uint32_t lane, px, py;
         if (!ticket_to_lane(p, s, base + lane_id, &lane, &px, &py)) continue;
         lane_multi<STATS>(s, p.seed_value, lane, px, py, samples, n, &st, nullptr);
-        // ImageBlock::put, box path (imageblock.cpp:210-233): values = { weight * ray_weight * result, weight }
-        for (uint32_t k = 0; k < n; ++k) {
-            const DSample &d = samples[k];
-            if (!d.valid) continue;
-            const uint32_t ux = (uint32_t) (int32_t) floorf(d.px), uy = (uint32_t) (int32_t) floorf(d.py);
-            if (!(ux < s.film_w && uy < s.film_h)) continue;
-            const float w = d.weight * 1.f;
-            atomicAdd(p.film + (size_t) uy * s.film_w + ux, make_float4(w * d.result.x, w * d.result.y, w * d.result.z, d.weight));
-        }
+        splat_samples(s, p.film, samples, n);
     }
     if (STATS) flush_stats(st, p.counters);
 }
@@ -366,6 +540,37 @@ void launch_reuse_pass(const DScene &s, const RenderParams &p, int sm_count, boo
     if (stats) launch_reuse_n<64, true>(s, p, sm_count, st);
     else if (s.n_reuse <= 8) launch_reuse_n<8, false>(s, p, sm_count, st);
     else launch_reuse_n<64, false>(s, p, sm_count, st);
+}
+// Staged pass: chunks of m lanes, three launches each.  `buf` holds 4 m + 2 (n - 1) m float4.  Returns the number of launches.
+size_t reuse_staged_float4s(uint32_t n, uint32_t m_cap) { return (size_t) m_cap * (6 + 2 * (size_t) (n - 1) + 4 + 1 + 1 + 3 * (size_t) n); }
+uint32_t run_reuse_staged(const DScene &s, const RenderParams &p, float4 *buf, uint32_t m_cap, int schedule, int sm_count, cudaStream_t st) {
+    const uint32_t n = s.n_reuse, nk = n - 1u; uint32_t launches = 0;
+    for (unsigned long long c0 = 0; c0 < p.n_lanes; c0 += m_cap) {
+        const uint32_t m = (uint32_t) (p.n_lanes - c0 < m_cap ? p.n_lanes - c0 : m_cap);
+        float4 *prim = buf, *proj = buf + 6 * (size_t) m_cap;
+        if (schedule == 2) {
+            PipeBufs b; b.state = proj + 2 * (size_t) nk * m_cap; b.rng = (uint4 *) (b.state + 4 * (size_t) m_cap); b.ind = (float4 *) (b.rng + m_cap); b.rec = b.ind + m_cap;
+            reuse_primary_kernel<<<(m + 127) / 128, 128, 0, st>>>(s, p, c0, m, prim);
+            const size_t pairs = (size_t) m * nk;
+            reuse_project_kernel<<<(unsigned) ((pairs + 127) / 128), 128, 0, st>>>(s, m, nk, prim, proj);
+            if (n <= 8) reuse_select_kernel<8><<<(m + 127) / 128, 128, 0, st>>>(s, p, c0, m, prim, proj, b);
+            else reuse_select_kernel<64><<<(m + 127) / 128, 128, 0, st>>>(s, p, c0, m, prim, proj, b);
+            cudaMemsetAsync(p.counters + CTR_TICKET, 0, sizeof(unsigned long long), st);
+            int per_sm = 0; cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, reuse_suffix_kernel, 128, 0);
+            reuse_suffix_kernel<<<sm_count * (per_sm > 0 ? per_sm : 1), 128, 0, st>>>(s, m, p.regen_min, b, p.counters + CTR_TICKET);
+            const size_t nm = (size_t) n * m;
+            reuse_finish_kernel<<<(unsigned) ((nm + 255) / 256), 256, 0, st>>>(s, m, n, b, p.film);
+            launches += 5;
+            continue;
+        }
+        reuse_primary_kernel<<<(m + 127) / 128, 128, 0, st>>>(s, p, c0, m, prim);
+        const size_t pairs = (size_t) m * nk;
+        reuse_project_kernel<<<(unsigned) ((pairs + 127) / 128), 128, 0, st>>>(s, m, nk, prim, proj);
+        if (n <= 8) reuse_shade_kernel<8><<<(m + 127) / 128, 128, 0, st>>>(s, p, c0, m, prim, proj);
+        else reuse_shade_kernel<64><<<(m + 127) / 128, 128, 0, st>>>(s, p, c0, m, prim, proj);
+        launches += 3;
+    }
+    return launches;
 }
 void launch_reuse_tap(const DScene &s, uint32_t seed_value, uint32_t spp_per_pass, uint32_t lane_begin, uint32_t n, float *out, cudaStream_t st) {
     if (!n) return;

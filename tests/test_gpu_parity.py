@@ -2,6 +2,8 @@
 Bar (BASELINE.json north_star): sampler streams, camera rays and hit primitive IDs bit-exact; per-lane radiance is
 also compared bit-for-bit (same canonical arithmetic on both sides); the film, which is accumulated with atomics in
 a different order than the oracle's sequential sum, within a stated relative tolerance."""
+import os
+
 import numpy as np
 import pytest
 
@@ -465,6 +467,18 @@ def test_sample_reuse_lanes_and_film_match_oracle(name, ov, cfg, scenes, ob, gpu
     scale = ofilm[..., :3].max()
     assert np.allclose(film[..., 3], ofilm[..., 3], rtol=1e-5, atol=1e-5)
     assert np.abs(film[..., :3] - ofilm[..., :3]).max() <= 5 * FILM_RTOL * scale
+    # the pipeline schedule (default: primary / project / select / suffix / finish kernels per chunk) with small ragged chunks, the
+    # three-kernel staged schedule, and the
+    # single persistent kernel accumulate the same samples (differences: order of the float atomics only)
+    for env in (dict(AMVPT_REUSE_CHUNK="1000"), dict(AMVPT_REUSE_STAGED="1", AMVPT_REUSE_CHUNK="1500"), dict(AMVPT_REUSE_STAGED="0")):
+        os.environ.update(env)
+        try:
+            s.render(seed=3, spp=16, develop=False); other = s.film_raw()
+        finally:
+            for k in env:
+                del os.environ[k]
+        assert np.allclose(other[..., 3], film[..., 3], rtol=1e-5, atol=1e-5), env
+        assert np.abs(other[..., :3] - film[..., :3]).max() <= 5 * FILM_RTOL * scale, env
 
 
 def test_sample_reuse_is_consistent_with_plain_path_tracing(scenes, gpu):
