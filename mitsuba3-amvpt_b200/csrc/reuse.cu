@@ -356,7 +356,7 @@ AM_D void splat_samples(const DScene &s, float4 *film, const DSample *samples, u
 // (light sample, BSDF calls, camera selection with the sampler's draws in the reference's order, MIS weights, mixture pdf,
 // the suffix path, splat), reading the hit and the projection records instead of tracing.  Same arithmetic, same bits.
 #ifndef AM_REUSE_SHADE_MIN_CTAS
-#define AM_REUSE_SHADE_MIN_CTAS 12
+#define AM_REUSE_SHADE_MIN_CTAS 4     /* the select kernel keeps n 92-byte camera records per thread in local memory: at 12 CTAs/SM they spill to DRAM (ncu: 7.4 GB per 4M-lane launch, long-scoreboard 25); 3 / 4 / 6 / 8 / 12 CTAs: 782 / 783 / 755 / 720 / 698 Mpaths/s */
 #endif
 #ifndef AM_REUSE_SUFFIX_MIN_CTAS
 #define AM_REUSE_SUFFIX_MIN_CTAS 5
@@ -553,7 +553,9 @@ uint32_t run_reuse_staged(const DScene &s, const RenderParams &p, float4 *buf, u
             reuse_primary_kernel<<<(m + 127) / 128, 128, 0, st>>>(s, p, c0, m, prim);
             const size_t pairs = (size_t) m * nk;
             reuse_project_kernel<<<(unsigned) ((pairs + 127) / 128), 128, 0, st>>>(s, m, nk, prim, proj);
-            if (n <= 8) reuse_select_kernel<8><<<(m + 127) / 128, 128, 0, st>>>(s, p, c0, m, prim, proj, b);
+            if (n <= 4) reuse_select_kernel<4><<<(m + 127) / 128, 128, 0, st>>>(s, p, c0, m, prim, proj, b);
+            else if (n <= 8) reuse_select_kernel<8><<<(m + 127) / 128, 128, 0, st>>>(s, p, c0, m, prim, proj, b);
+            else if (n <= 16) reuse_select_kernel<16><<<(m + 127) / 128, 128, 0, st>>>(s, p, c0, m, prim, proj, b);
             else reuse_select_kernel<64><<<(m + 127) / 128, 128, 0, st>>>(s, p, c0, m, prim, proj, b);
             cudaMemsetAsync(p.counters + CTR_TICKET, 0, sizeof(unsigned long long), st);
             int per_sm = 0; cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, reuse_suffix_kernel, 128, 0);
