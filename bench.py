@@ -244,7 +244,7 @@ def main():
     bvh_bytes_per_path = (cs["bvh_nodes"] * 64.0 + cs["tri_tests"] * 48.0) / cs["paths"]
     s.render(seed=0, spp=spp, develop=False, scheduler=args.scheduler, time_stages=True); ks = s.last_stats
     peak, peak_src = peaks()
-    sched = {0: "warp_batch", 1: "regenerate", 2: "stream", 3: "wavefront", 5: "reuse"}[ks["scheduler_used"]]
+    sched = {0: "warp_batch", 1: "regenerate", 2: "stream", 3: "wavefront", 5: "reuse", 6: "split"}[ks["scheduler_used"]]
     if sched == "wavefront":
         # dominant kernel: wf_trace_kernel.  Per ray: BVH nodes (64 B) + triangles (48 B) + ray read (32 B) + hit / flag traffic (24 B)
         kernel = "wf_trace_kernel"; b_path = bvh_bytes_per_path + 56.0 * rays / cs["paths"]

@@ -97,8 +97,8 @@ def _f32(a, shape=None):
 BSDF_TYPES = {"diffuse": 0, "conductor": 1, "dielectric": 2, "roughconductor": 3, "roughdielectric": 4, "roughplastic": 5}
 FOV_AXES = {"x": 0, "y": 1, "diagonal": 2, "smaller": 3, "larger": 4}
 RFILTERS = {"box": 0, "gaussian": 1, "tent": 2, "mitchell": 3, "catmullrom": 4, "lanczos": 5}
-SCHEDULERS = {"warp_batch": 0, "regenerate": 1, "stream": 2, "wavefront": 3, "auto": 4}
-SCHEDULER_NAMES = {0: "warp_batch", 1: "regenerate", 2: "stream", 3: "wavefront", 5: "reuse"}
+SCHEDULERS = {"warp_batch": 0, "regenerate": 1, "stream": 2, "wavefront": 3, "auto": 4, "split": 6}
+SCHEDULER_NAMES = {0: "warp_batch", 1: "regenerate", 2: "stream", 3: "wavefront", 5: "reuse", 6: "split"}
 
 
 def bsdf_desc(type, twosided=False, distribution="beckmann", nonlinear=False, reflectance=(.5, .5, .5), eta=(0., 0., 0.),

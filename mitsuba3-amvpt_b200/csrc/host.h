@@ -46,7 +46,7 @@ struct GridSensorParams {
     float near_clip = 1e-2f, far_clip = 1e4f, focus_distance = 1e4f, aperture_radius = 0.f, cone_deg = 0.f, cam_dist = 0.1f;
     float cam_dir[3] = { 1.f, 0.f, 0.f }, cam_off[3] = { 0.f, 0.f, 0.f };
 };
-enum SchedulerMode { SCHED_WARP_BATCH = 0, SCHED_REGENERATE = 1, SCHED_STREAM = 2, SCHED_WAVEFRONT = 3, SCHED_AUTO = 4, SCHED_REUSE = 5 /* reported only */ };
+enum SchedulerMode { SCHED_WARP_BATCH = 0, SCHED_REGENERATE = 1, SCHED_STREAM = 2, SCHED_WAVEFRONT = 3, SCHED_AUTO = 4, SCHED_REUSE = 5 /* reported only */, SCHED_SPLIT = 6 };
 
 struct BvhOut { std::vector<float4> nodes, tris, tri_nrm; std::vector<uint32_t> prim_to_tri; uint32_t depth = 0; };
 struct RenderStats {
@@ -80,6 +80,7 @@ struct Scene {
     float4 *film = nullptr; float2 *moments = nullptr; float *rgb = nullptr;
     unsigned long long *counters = nullptr; TileDesc *tiles_dev = nullptr; float *view_stats_dev = nullptr;
     uint32_t tiles_cap = 0;
+    float4 *split_buf = nullptr; uint32_t split_cap = 0;   // "split" scheduler: first-vertex records of one chunk
     float4 *reuse_buf = nullptr; uint32_t reuse_cap = 0;   // staged sample-reuse schedule: per-chunk hit + projection records
     WfPool wf{}; uint32_t wf_type_mask = 0;     // wavefront scheduler pool (allocated on first use)
     uint32_t n_nodes = 0, n_tris = 0;

@@ -16,6 +16,9 @@ namespace amvpt {
 // MODE 0: a warp takes 32 consecutive tickets and traces them to completion before taking the next 32.
 // MODE 1: path regeneration -- whenever at least REGEN_MIN lanes of the warp are idle they splat and take fresh
 //         tickets together, so the warp stays full while paths have different lengths.
+// MODE 3: as MODE 1 over one chunk of tickets whose first vertex was prepared by primary_vertex_kernel ("split" scheduler):
+//         camera rays and first-vertex light rays are the coherent third of all rays; traced there by a 10 KB kernel with
+//         full warps they cost a fraction of what they cost inside this loop.
 #ifndef AM_RP_MIN_CTAS
 #define AM_RP_MIN_CTAS 1
 #endif
@@ -44,10 +47,11 @@ render_pass_kernel(const DScene s, const RenderParams p) {
                     base = __shfl_sync(fm, base, leader);
                     unsigned long long ticket = base + __popc(fm & ((1u << lane_id) - 1u));
                     uint32_t lane, px, py;
-                    if (ticket_to_lane(p, s, ticket, &lane, &px, &py)) {
+                    if ((MODE != 3 || ticket < p.prim_m) && ticket_to_lane(p, s, (MODE == 3 ? p.ticket_base : 0ull) + ticket, &lane, &px, &py)) {
                         lane_setup(s, p.seed_value, lane, px, py, ps, ls);
                         has_result = true;
                         if (s.max_depth == 0) ps.active = false;    // mvpath_single.h:86-87
+                        if (MODE == 3 && ps.active) path_bounce<false, STATS, false, true>(s, ps, nullptr, &st, p.prim, p.prim_m, (uint32_t) ticket);
                     } else exhausted = true;
                 }
             }
@@ -179,6 +183,40 @@ template <bool STATS> static void launch_stream(const DScene &s, const RenderPar
     render_stream_kernel<STATS><<<grid, 128, 0, stream>>>(s, p);
 }
 
+// First vertex of every lane of a chunk: camera ray -> closest hit, and the light sample of that vertex (the sampler's first two
+// numbers after the camera ray's) with its visibility ray.  Mirrors the head of path_bounce for depth 0.
+__global__ void __launch_bounds__(128)
+primary_vertex_kernel(const __grid_constant__ DScene s, const __grid_constant__ RenderParams p, float4 *prim) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x, m = p.prim_m; if (i >= m) return;
+    uint32_t lane, px, py; if (!ticket_to_lane(p, s, p.ticket_base + i, &lane, &px, &py)) return;
+    PathState ps; LaneSetup ls;
+    lane_setup(s, p.seed_value, lane, px, py, ps, ls);
+    Hit h = intersect<false>(s, ps.ray);
+    const DMesh *mesh; SI si = make_si(s, ps.ray, h, &mesh);
+    V3 em_weight = v3(0.f); DirectionSample ds; ds.pdf = 0.f; ds.d = v3(0.f);
+    if (1u < s.max_depth && si.valid && (s.bsdfs[mesh->bsdf].flags & L_SMOOTH) != 0) {
+        V2 es; es.x = ps.rng.next_f32(); es.y = ps.rng.next_f32();
+        ds = sample_emitter_direction<false>(s, si, es, &em_weight, nullptr, nullptr);
+    }
+    prim[i] = make_float4(h.t, h.u, h.v, __uint_as_float(h.tri));
+    prim[(size_t) m + i] = make_float4(em_weight.x, em_weight.y, em_weight.z, ds.pdf);
+    prim[2 * (size_t) m + i] = make_float4(ds.d.x, ds.d.y, ds.d.z, 0.f);
+}
+uint32_t run_split_pass(const DScene &s, RenderParams p, float4 *prim, uint32_t m_cap, int sm_count, cudaStream_t st) {
+    int per_sm = 0; cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, render_pass_kernel<3, false>, 128, 0);
+    if (per_sm < 1) per_sm = 1;
+    const unsigned long long n_lanes = p.n_lanes; uint32_t launches = 0;
+    for (unsigned long long c0 = 0; c0 < n_lanes; c0 += m_cap) {
+        const uint32_t m = (uint32_t) (n_lanes - c0 < m_cap ? n_lanes - c0 : m_cap);
+        p.prim = prim; p.prim_m = m; p.ticket_base = c0;
+        cudaMemsetAsync(p.counters + CTR_TICKET, 0, sizeof(unsigned long long), st);
+        primary_vertex_kernel<<<(m + 127) / 128, 128, 0, st>>>(s, p, prim);
+        unsigned grid = (unsigned) (sm_count * per_sm), need = (m + 127) / 128; if (need < grid) grid = need;
+        render_pass_kernel<3, false><<<grid, 128, 0, st>>>(s, p);
+        launches += 2;
+    }
+    return launches;
+}
 void launch_render_pass(const DScene &s, const RenderParams &p, int mode, int sm_count, bool stats, cudaStream_t stream) {
     if (mode == 2) {
         if (stats) launch_stream<true>(s, p, sm_count, stream); else launch_stream<false>(s, p, sm_count, stream);

@@ -17,6 +17,9 @@ struct RenderParams {
     unsigned long long n_lanes;
     float4 *film;              // RGBW, film_w * film_h
     float2 *moments;           // optional (sum lum, sum lum^2) per pixel for the adaptive allocator, or nullptr
+    // scheduler 6 ("split"): the launch covers tickets [ticket_base, ticket_base + prim_m); prim holds 3 * prim_m float4 written by
+    // primary_vertex_kernel: closest hit of the camera ray, (light weight, pdf), light direction of the first vertex
+    const float4 *prim; uint32_t prim_m, pad2; unsigned long long ticket_base;
     unsigned long long *counters;   // [0] next-lane ticket, [1] closest rays, [2] shadow rays, [3] nodes, [4] tris, [5] path vertices
 };
 
@@ -52,6 +55,7 @@ uint32_t run_reuse_staged(const DScene &s, const RenderParams &p, float4 *buf, u
 void launch_reuse_tap(const DScene &s, uint32_t seed_value, uint32_t spp_per_pass, uint32_t lane_begin, uint32_t n, float *out /* n * n_reuse * 9 */, cudaStream_t st);
 
 // host-callable launchers (kernels.cu)
+uint32_t run_split_pass(const DScene &s, RenderParams p, float4 *prim /* 3 * m_cap */, uint32_t m_cap, int sm_count, cudaStream_t st);
 void launch_render_pass(const DScene &s, const RenderParams &p, int mode, int sm_count, bool stats, cudaStream_t st);
 void launch_trace_lanes(const DScene &s, uint32_t seed_value, uint32_t spp_per_pass, uint32_t lane_begin, uint32_t n, int trace,
                         const LaneTaps &taps, unsigned long long *counters, cudaStream_t st);

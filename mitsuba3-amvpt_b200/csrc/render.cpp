@@ -81,7 +81,7 @@ void render(Scene &s, const RenderOptions &opt) {
     p.regen_min = opt.regen_min ? opt.regen_min : (getenv("AMVPT_REGEN_MIN") ? (uint32_t) atoi(getenv("AMVPT_REGEN_MIN")) : 8u); p.spp_per_pass = spp_per_pass; p.tiles = s.tiles_dev; p.film = s.film; p.moments = adaptive ? s.moments : nullptr; p.counters = s.counters;
     p.trace_min = opt.trace_min ? opt.trace_min : (getenv("AMVPT_TRACE_MIN") ? (uint32_t) atoi(getenv("AMVPT_TRACE_MIN")) : 20u);
     p.bvh_depth = s.bvh.depth;
-    int mode = opt.scheduler == SCHED_WARP_BATCH ? 0 : (opt.scheduler == SCHED_STREAM ? 2 : (opt.scheduler == SCHED_WAVEFRONT ? 3 : 1));
+    int mode = opt.scheduler == SCHED_WARP_BATCH ? 0 : (opt.scheduler == SCHED_STREAM ? 2 : (opt.scheduler == SCHED_WAVEFRONT ? 3 : (opt.scheduler == SCHED_SPLIT ? 6 : 1)));
     if (opt.scheduler == SCHED_AUTO) {
         // Measured on B200 (profiles/): the persistent megakernel wins while its working code stays small and rays are short
         // (Cornell box: 1.7 vs 0.8-1.1 Gpaths/s); with several BSDF plugin types or a deep tree its warps stall on
@@ -94,6 +94,7 @@ void render(Scene &s, const RenderOptions &opt) {
     // a reconstruction filter other than the box is splatted by the wavefront's regen stage only: carrying the sample position
     // and the footprint loop through the persistent megakernels costs them 8 % on the box-filter path (measured, profiles/)
     if (s.rfilter_type != 0) mode = 3;
+    if (mode == SCHED_SPLIT && (opt.stats || adaptive)) mode = 1;   // the counting pass and the moment film use the unsplit megakernel
     if (reuse) mode = SCHED_REUSE;                 // the reuse branch has its own kernel (reuse.cu)
     rs.scheduler_used = (uint32_t) mode;
     auto launch = [&](std::vector<TileDesc> &tiles, uint32_t pass) {
@@ -117,6 +118,11 @@ void render(Scene &s, const RenderOptions &opt) {
                 s.wf_type_mask = 0; for (auto &m : s.meshes) s.wf_type_mask |= 1u << s.bsdfs[m.bsdf].type;
             }
             rs.launches += run_wavefront_pass(s.d, p, s.wf, s.wf_type_mask, s.sm_count, opt.stats, st, opt.time_stages ? &rs.trace_seconds : nullptr, &rs.trace_launches);
+        } else if (mode == SCHED_SPLIT) {
+            const uint32_t m_cap = getenv("AMVPT_SPLIT_CHUNK") ? std::max(128u, (uint32_t) atoi(getenv("AMVPT_SPLIT_CHUNK"))) : (1u << 23);
+            if (!s.split_buf || s.split_cap != m_cap) { s.split_buf = (float4 *) s.dalloc(sizeof(float4) * 3 * (size_t) m_cap); s.split_cap = m_cap; }
+            rs.launches += run_split_pass(s.d, p, s.split_buf, m_cap, s.sm_count, st);
+            AM_CUDA(cudaGetLastError());
         } else if (mode == SCHED_REUSE) {
             // 0: one persistent kernel; 1: primary / project / shade kernels per chunk; 2 (default): primary / project / select / suffix / finish
             const int schedule = opt.stats ? 0 : (getenv("AMVPT_REUSE_STAGED") ? atoi(getenv("AMVPT_REUSE_STAGED")) : 2);

@@ -478,7 +478,7 @@ reuse_suffix_kernel(const __grid_constant__ DScene s, uint32_t m, uint32_t regen
 __global__ void __launch_bounds__(256)
 reuse_finish_kernel(const __grid_constant__ DScene s, uint32_t m, uint32_t n, PipeBufs b, float4 *film) {
     const size_t j = (size_t) blockIdx.x * blockDim.x + threadIdx.x, nm = (size_t) n * m; if (j >= nm) return;
-    const uint32_t i = (uint32_t) (j % m), k = (uint32_t) (j / m);
+    const uint32_t i = (uint32_t) (j % m);
     const float4 r0 = b.rec[j]; const uint32_t fl = __float_as_uint(r0.w);
     if (!(fl & 1u)) return;
     const float4 ind = b.ind[i]; const bool mis = __float_as_uint(b.state[3 * (size_t) m + i].w) & 1u;

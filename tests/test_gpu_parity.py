@@ -251,19 +251,21 @@ def test_stream_scheduler_bit_exact_per_sample(which, scenes, gpu):
         desc = scenes.height_field(n=48, grid_x=2, grid_y=2, view_res=64, spp_pass_lim=1, sample_count=1)
     s = scenes.build(desc, device=gpu)
     films, stats = {}, {}
-    for sched in ("regenerate", "stream", "warp_batch", "wavefront"):
+    for sched in ("regenerate", "stream", "warp_batch", "wavefront", "split"):
         for seed in (0, 7):
-            s.render(seed=seed, spp=1, scheduler=sched, develop=False, stats=True)
+            # the split scheduler has no counting variant (it falls back to regenerate under stats=True): render it plain
+            s.render(seed=seed, spp=1, scheduler=sched, develop=False, stats=sched != "split")
             films[sched, seed] = s.film_raw(); stats[sched, seed] = dict(s.last_stats)
+            assert s.last_stats["scheduler_used"] == {"regenerate": 1, "stream": 2, "warp_batch": 0, "wavefront": 3, "split": 6}[sched]
     for seed in (0, 7):
         ref = films["regenerate", seed]; one = ref[..., 3] == 1
         assert one.mean() > 0.99
-        for sched in ("stream", "warp_batch", "wavefront"):
+        for sched in ("stream", "warp_batch", "wavefront", "split"):
             f = films[sched, seed]
             assert np.array_equal(f[..., 3], ref[..., 3])
             assert_bits(f[one], ref[one], f"{which} seed {seed}: {sched} vs regenerate, single-sample pixels")
             assert np.abs(f - ref).max() <= FILM_RTOL * max(ref[..., :3].max(), 1e-6)
-            for k in ("paths", "closest_rays", "shadow_rays", "bvh_nodes", "tri_tests", "path_vertices"):
+            for k in ("paths",) if sched == "split" else ("paths", "closest_rays", "shadow_rays", "bvh_nodes", "tri_tests", "path_vertices"):
                 assert stats[sched, seed][k] == stats["regenerate", seed][k], f"{which} {sched} {k}"
         assert (ref[..., :3].sum(-1) > 0).mean() > 0.2
 
