@@ -133,6 +133,25 @@ int amvpt_film_develop_device(amvpt_scene *s, float *rgb_dev, void *stream);
 int amvpt_film_device_ptr(amvpt_scene *s, void **rgbw_dev, void **moments_dev);   /* for the NCCL film gather */
 int amvpt_film_add_host(amvpt_scene *s, const float *rgbw_host);         /* ImageBlock::put_block (imageblock.cpp:135-172) */
 
+/* ---- output path and display step --------------------------------------------------- */
+/* HDRFilm::write with file_format = pfm (hdrfilm.cpp:420-560 -> Bitmap::write_pfm, src/core/bitmap.cpp:2270-2299): the developed
+ * quilt (view < 0) or one view's tile of it (the per-view split of the reference's to_gif.py), RGB float32, bottom row first */
+int amvpt_film_write_pfm(amvpt_scene *s, const char *path, int32_t view);
+/* what the viewer does to a rendered quilt when it loads it: Bitmap::convert(PixelFormat::RGB, Struct::Type::UInt8, srgb_gamma)
+ * (src/mitsuba/program.h:55; per component src/core/struct.cpp:1645-1662 + dr::linear_to_srgb).  The 8-bit quilt stays on the
+ * device for amvpt_interlace; rgb8_host (H*W*3) may be NULL */
+int amvpt_film_to_srgb8(amvpt_scene *s, uint8_t *rgb8_host);
+/* lenticular display calibration (src/mitsuba/preset.h:12-17) + the viewer toggles "Display quilt" / "Nearest scaling"
+ * (src/mitsuba/program.cpp:130-132) */
+typedef struct amvpt_preset { float center, focus, pitch, tilt, subp, view[2]; int32_t grid[2]; int32_t flip_rgb, quilt, nearest; } amvpt_preset;
+/* Program::display_image (src/mitsuba/program.cpp:199-272): quilt -> interlaced image for a slanted-lens display, dst_ch = 3
+ * (the screenshot path; pass flip_rgb = 1 as the reference does) or 4 (the window surface, alpha = 255).  src_host = NULL uses the
+ * scene's own 8-bit quilt; otherwise any src_h * src_w * src_ch image (src_ch >= 3).  The window itself is unavailable on this
+ * box: dst_host (dst_h * dst_w * dst_ch bytes) is the headless surface */
+int amvpt_interlace(amvpt_scene *s, const uint8_t *src_host, uint32_t src_w, uint32_t src_h, uint32_t src_ch, const amvpt_preset *p,
+                    uint32_t dst_w, uint32_t dst_h, uint32_t dst_ch, uint8_t *dst_host);
+int amvpt_display_last_ms(amvpt_scene *s, float *srgb8_ms, float *interlace_ms);   /* device time of the last two kernels above */
+
 /* ---- parity taps (used by tests/; same meaning as the oracle's orc_* entry points) ------------------------------ */
 int amvpt_trace_lanes(amvpt_scene *s, uint32_t seed_value, uint32_t spp_per_pass, uint32_t lane_begin, uint32_t n, int trace,
                       float *sample_pos, float *ray_o, float *ray_d, float *ray_maxt, uint32_t *view, float *radiance,

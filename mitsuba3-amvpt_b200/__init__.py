@@ -27,7 +27,12 @@ def _load():
 
 
 lib = _load()
-f32p, u32p, u64p = C.POINTER(C.c_float), C.POINTER(C.c_uint32), C.POINTER(C.c_uint64)
+f32p, u32p, u64p, u8p = C.POINTER(C.c_float), C.POINTER(C.c_uint32), C.POINTER(C.c_uint64), C.POINTER(C.c_uint8)
+
+
+class Preset(C.Structure):      # amvpt_preset (include/amvpt.h); src/mitsuba/preset.h:12-17
+    _fields_ = [("center", C.c_float), ("focus", C.c_float), ("pitch", C.c_float), ("tilt", C.c_float), ("subp", C.c_float), ("view", C.c_float * 2),
+                ("grid", C.c_int32 * 2), ("flip_rgb", C.c_int32), ("quilt", C.c_int32), ("nearest", C.c_int32)]
 
 
 class BsdfDesc(C.Structure):
@@ -74,7 +79,7 @@ EXPORTS = ["amvpt_last_error", "amvpt_device_count", "amvpt_scene_create", "amvp
            "amvpt_scene_get_bsdf", "amvpt_scene_get_integrator", "amvpt_render", "amvpt_shard_tiles", "amvpt_cancel", "amvpt_film_clear",
            "amvpt_film_raw", "amvpt_film_develop", "amvpt_film_develop_device", "amvpt_film_device_ptr", "amvpt_film_add_host",
            "amvpt_trace_lanes", "amvpt_trace_lanes_multi", "amvpt_intersect", "amvpt_bsdf_eval_pdf_sample", "amvpt_math1", "amvpt_sampler_stream",
-           "amvpt_bvh_validate"]
+           "amvpt_bvh_validate", "amvpt_film_write_pfm", "amvpt_film_to_srgb8", "amvpt_interlace", "amvpt_display_last_ms"]
 lib.amvpt_scene_destroy.restype = None
 lib.amvpt_scene_destroy.argtypes = [C.c_void_p]
 
@@ -285,6 +290,33 @@ class Scene:
 
     def film_add(self, rgbw):
         _chk(lib.amvpt_film_add_host(self._h, _p(_f32(rgbw))))
+
+    # ---- output path and display step
+    def write_pfm(self, path, view=-1):
+        """HDRFilm::write, file_format = pfm (Bitmap::write_pfm, src/core/bitmap.cpp:2270-2299); view >= 0 writes that view's tile only."""
+        _chk(lib.amvpt_film_write_pfm(self._h, str(path).encode(), C.c_int32(view)))
+
+    def to_srgb8(self, fetch=True):
+        """The developed quilt as the viewer loads it: Bitmap::convert(RGB, UInt8, srgb) (src/mitsuba/program.h:55). Stays on the device for interlace()."""
+        i = self.info(); out = np.zeros((i["film_h"], i["film_w"], 3), np.uint8) if fetch else None
+        _chk(lib.amvpt_film_to_srgb8(self._h, _p(out, u8p))); return out
+
+    def interlace(self, preset, dst_w, dst_h, dst_ch=3, src=None):
+        """Program::display_image (src/mitsuba/program.cpp:199-272). preset: dict with center, focus, pitch, tilt, subp, view, grid and
+        optionally flip_rgb, quilt, nearest (src/mitsuba/preset.h:12-17); src: optional (H, W, C >= 3) uint8 image instead of the film."""
+        pr = Preset(center=preset["center"], focus=preset["focus"], pitch=preset["pitch"], tilt=preset["tilt"], subp=preset["subp"],
+                    view=(C.c_float * 2)(*preset["view"]), grid=(C.c_int32 * 2)(*preset["grid"]), flip_rgb=int(preset.get("flip_rgb", dst_ch == 3)),
+                    quilt=int(preset.get("quilt", False)), nearest=int(preset.get("nearest", False)))
+        out = np.zeros((dst_h, dst_w, dst_ch), np.uint8)
+        if src is not None:
+            src = np.ascontiguousarray(src, np.uint8); sh, sw, sc = src.shape
+        else:
+            sh = sw = sc = 0
+        _chk(lib.amvpt_interlace(self._h, _p(src, u8p), C.c_uint32(sw), C.c_uint32(sh), C.c_uint32(sc), C.byref(pr), C.c_uint32(dst_w), C.c_uint32(dst_h), C.c_uint32(dst_ch), _p(out, u8p)))
+        return out
+
+    def display_last_ms(self):
+        a, b = C.c_float(), C.c_float(); _chk(lib.amvpt_display_last_ms(self._h, C.byref(a), C.byref(b))); return a.value, b.value
 
     # ---- parity taps
     def trace_lanes(self, seed_value, spp_per_pass, lane_begin, n, trace=True, max_hits=0):

@@ -212,6 +212,56 @@ int amvpt_film_add_host(amvpt_scene *h, const float *rgbw) {
         AM_CUDA(cudaMemcpy(s.film, cur.data(), n * 4, cudaMemcpyHostToDevice)); return AMVPT_OK; });
 }
 
+// ---- output path and display step
+namespace {
+struct EventTimer {     // device time of the kernels launched between the constructor and stop() on the null stream
+    cudaEvent_t a, b; EventTimer() { cudaEventCreate(&a); cudaEventCreate(&b); cudaEventRecord(a, nullptr); }
+    float stop() { float ms = 0.f; cudaEventRecord(b, nullptr); cudaEventSynchronize(b); cudaEventElapsedTime(&ms, a, b); return ms; }
+    ~EventTimer() { cudaEventDestroy(a); cudaEventDestroy(b); }
+};
+}
+int amvpt_film_to_srgb8(amvpt_scene *h, uint8_t *rgb8) {
+    return guard([&] { Scene &s = committed(h); size_t npix = (size_t) s.film_w * s.film_h;
+        if (!s.srgb8) s.srgb8 = (uint8_t *) s.dalloc(npix * 3 + 16);
+        { EventTimer t; launch_srgb8(s.film, s.srgb8, npix, s.sm_count, nullptr); AM_CUDA(cudaGetLastError()); s.display_ms[0] = t.stop(); }
+        if (rgb8) AM_CUDA(cudaMemcpy(rgb8, s.srgb8, npix * 3, cudaMemcpyDeviceToHost));
+        return AMVPT_OK; });
+}
+int amvpt_interlace(amvpt_scene *h, const uint8_t *src, uint32_t src_w, uint32_t src_h, uint32_t src_ch, const amvpt_preset *p,
+                    uint32_t dst_w, uint32_t dst_h, uint32_t dst_ch, uint8_t *dst) {
+    return guard([&] { Scene &s = committed(h); NEED(p); NEED(dst); NEED(dst_ch == 3 || dst_ch == 4); NEED(dst_w >= 2 && dst_h >= 2);
+        NEED(p->grid[0] > 0 && p->grid[1] > 0);
+        static_assert(sizeof(DisplayPreset) == sizeof(amvpt_preset), "preset layouts differ");
+        DisplayPreset dp; memcpy(&dp, p, sizeof(dp));
+        const uint8_t *dsrc; DBuf up(0);
+        if (src) { NEED(src_w >= 1 && src_h >= 1 && src_ch >= 3); size_t n = (size_t) src_w * src_h * src_ch; DBuf b(n); b.up(src, n); std::swap(up.p, b.p); dsrc = up.as<uint8_t>(); }
+        else { if (!s.srgb8) AM_THROW("interlace: no source image and amvpt_film_to_srgb8 has not been called"); dsrc = s.srgb8; src_w = s.film_w; src_h = s.film_h; src_ch = 3; }
+        size_t nd = (size_t) dst_w * dst_h * dst_ch; DBuf out(nd);
+        { EventTimer t; launch_interlace(dsrc, src_w, src_h, src_ch, dp, out.as<uint8_t>(), dst_w, dst_h, dst_ch, nullptr); AM_CUDA(cudaGetLastError()); s.display_ms[1] = t.stop(); }
+        AM_CUDA(cudaMemcpy(dst, out.p, nd, cudaMemcpyDeviceToHost)); return AMVPT_OK; });
+}
+int amvpt_display_last_ms(amvpt_scene *h, float *srgb8_ms, float *interlace_ms) {
+    return guard([&] { Scene &s = committed(h); if (srgb8_ms) *srgb8_ms = s.display_ms[0]; if (interlace_ms) *interlace_ms = s.display_ms[1]; return AMVPT_OK; });
+}
+int amvpt_film_write_pfm(amvpt_scene *h, const char *path, int32_t view) {
+    return guard([&] { NEED(path); Scene &s = committed(h); size_t npix = (size_t) s.film_w * s.film_h;
+        if (!s.rgb) s.rgb = (float *) s.dalloc(npix * 3 * sizeof(float));
+        launch_develop(s.film, s.rgb, npix, nullptr); AM_CUDA(cudaGetLastError());
+        std::vector<float> rgb(npix * 3); AM_CUDA(cudaMemcpy(rgb.data(), s.rgb, npix * 3 * sizeof(float), cudaMemcpyDeviceToHost));
+        uint32_t x0 = 0, y0 = 0, w = s.film_w, hh = s.film_h;
+        if (view >= 0) {
+            Shard sh; std::vector<TileDesc> t = rank_tiles(s, sh, false); bool found = false;
+            for (auto &r : t) if ((int32_t) r.pad == view) { x0 = r.x0; y0 = r.y0; w = r.w; hh = r.h; found = true; break; }
+            if (!found) AM_THROW("write_pfm: view %d out of range (%zu views)", view, t.size());
+        }
+        FILE *f = fopen(path, "wb"); if (!f) AM_THROW("write_pfm: cannot open %s", path);
+        fprintf(f, "PF\n%u %u\n-1\n", w, hh);                        // Bitmap::write_pfm (src/core/bitmap.cpp:2270-2299): little endian, bottom row first
+        bool ok = true;
+        for (uint32_t y = 0; y < hh && ok; ++y) ok = fwrite(rgb.data() + ((size_t) (y0 + hh - 1 - y) * s.film_w + x0) * 3, sizeof(float), (size_t) w * 3, f) == (size_t) w * 3;
+        ok = (fclose(f) == 0) && ok; if (!ok) AM_THROW("write_pfm: short write to %s", path);
+        return AMVPT_OK; });
+}
+
 // ---- parity taps
 int amvpt_trace_lanes_multi(amvpt_scene *h, uint32_t seed_value, uint32_t spp_per_pass, uint32_t lane_begin, uint32_t n, float *out9) {
     return guard([&] { Scene &s = committed(h); NEED(spp_per_pass > 0); NEED(out9);

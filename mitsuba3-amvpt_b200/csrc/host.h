@@ -80,6 +80,8 @@ struct Scene {
     float4 *film = nullptr; float2 *moments = nullptr; float *rgb = nullptr;
     unsigned long long *counters = nullptr; TileDesc *tiles_dev = nullptr; float *view_stats_dev = nullptr;
     uint32_t tiles_cap = 0;
+    uint8_t *srgb8 = nullptr;                              // display step: the developed quilt as 8-bit sRGB (allocated on first use)
+    float display_ms[2] = { 0.f, 0.f };                    // device time of the last srgb8 / interlace kernel
     float4 *split_buf = nullptr; uint32_t split_cap = 0;   // "split" scheduler: first-vertex records of one chunk
     float4 *reuse_buf = nullptr; uint32_t reuse_cap = 0;   // staged sample-reuse schedule: per-chunk hit + projection records
     WfPool wf{}; uint32_t wf_type_mask = 0;     // wavefront scheduler pool (allocated on first use)

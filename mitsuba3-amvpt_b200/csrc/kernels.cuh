@@ -60,6 +60,11 @@ void launch_render_pass(const DScene &s, const RenderParams &p, int mode, int sm
 void launch_trace_lanes(const DScene &s, uint32_t seed_value, uint32_t spp_per_pass, uint32_t lane_begin, uint32_t n, int trace,
                         const LaneTaps &taps, unsigned long long *counters, cudaStream_t st);
 void launch_develop(const float4 *film, float *rgb, size_t npix, cudaStream_t st);
+// display step (display.cu): same layout as amvpt_preset of include/amvpt.h (src/mitsuba/preset.h:12-17 + the viewer's two toggles)
+struct DisplayPreset { float center, focus, pitch, tilt, subp, view[2]; int32_t grid[2]; int32_t flip_rgb, quilt, nearest; };
+void launch_srgb8(const float4 *film, uint8_t *rgb8, size_t npix, int sm_count, cudaStream_t st);
+void launch_interlace(const uint8_t *src, uint32_t src_w, uint32_t src_h, uint32_t src_ch, const DisplayPreset &p,
+                      uint8_t *dst, uint32_t dst_w, uint32_t dst_h, uint32_t dst_ch, cudaStream_t st);
 void launch_view_stats(const float4 *film, const float2 *moments, uint32_t film_w, const TileDesc *tiles, uint32_t n_tiles,
                        float *stats /* n_tiles * 4 */, cudaStream_t st);
 void launch_intersect(const DScene &s, const float *o, const float *d, const float *maxt, uint32_t n, int any,

@@ -270,7 +270,7 @@ void Scene::commit(int dev) {
     if (device >= 0 && device != dev) AM_THROW("commit: scene already lives on device %d", device);
     AM_CUDA(cudaSetDevice(dev)); device = dev;
     for (void *p : allocs) cudaFree(p);
-    allocs.clear(); wf = WfPool{}; reuse_buf = nullptr; reuse_cap = 0; split_buf = nullptr; split_cap = 0;
+    allocs.clear(); wf = WfPool{}; reuse_buf = nullptr; reuse_cap = 0; split_buf = nullptr; split_cap = 0; srgb8 = nullptr;
     cudaDeviceProp prop; AM_CUDA(cudaGetDeviceProperties(&prop, dev)); sm_count = prop.multiProcessorCount;
     prepare_host();
     n_nodes = (uint32_t) (bvh.nodes.size() / AM_NODE_F4); n_tris = (uint32_t) (bvh.tris.size() / 3);

@@ -13,6 +13,7 @@
 // Build: make -C oracle oracle   (g++ -O2 -mfma -ffp-contract=off)
 #include "o_bsdf.h"
 #include "o_transform.h"
+#include "o_display.h"
 #include <algorithm>
 #include <atomic>
 #include <chrono>
@@ -880,6 +881,22 @@ void orc_trace_lanes_multi(void *sp, uint32_t seed_value, uint32_t spp_per_pass,
 void orc_develop(const float *rgbw, uint64_t npix, float *rgb) {
     for (uint64_t i = 0; i < npix; ++i) { float w = rgbw[4 * i + 3]; float iw = (w == 0.f ? 1.f : w);
         rgb[3 * i] = rgbw[4 * i] / iw; rgb[3 * i + 1] = rgbw[4 * i + 1] / iw; rgb[3 * i + 2] = rgbw[4 * i + 2] / iw; }
+}
+
+// display step, see o_display.h: Bitmap::convert(RGB, UInt8, srgb) and Program::display_image
+void orc_linear_to_srgb(const float *in, uint64_t n, float *out) { for (uint64_t i = 0; i < n; ++i) out[i] = odisp::linear_to_srgb(in[i]); }
+void orc_to_srgb8(const float *in, uint64_t n, uint8_t *out) { for (uint64_t i = 0; i < n; ++i) out[i] = odisp::to_srgb8(in[i]); }
+void orc_clip_mod(const float *x, const float *y, int n, float *out_clip, float *out_mod) {
+    for (int i = 0; i < n; ++i) { out_clip[i] = odisp::clip(x[i]); out_mod[i] = odisp::mod(x[i], y[i]); }
+}
+void orc_interpolate2d_u8(const uint8_t *data, uint32_t w, uint32_t h, uint32_t nch, const float *xy, int n, uint32_t c, int nearest, uint8_t *out) {
+    for (int i = 0; i < n; ++i) out[i] = odisp::interpolate2d(data, xy[2 * i], xy[2 * i + 1], w, h, c, nch, nearest != 0);
+}
+// preset: 7 floats (center, focus, pitch, tilt, subp, view x, view y) + 5 ints (grid x, grid y, flip_rgb, quilt, nearest)
+void orc_interlace(const uint8_t *src, uint32_t src_w, uint32_t src_h, uint32_t src_ch, const float *pf, const int32_t *pi,
+                   uint8_t *dst, uint32_t dst_w, uint32_t dst_h, uint32_t dst_ch) {
+    odisp::Preset p{ pf[0], pf[1], pf[2], pf[3], pf[4], { pf[5], pf[6] }, { pi[0], pi[1] }, pi[2], pi[3], pi[4] };
+    odisp::interlace(src, src_w, src_h, src_ch, p, dst, dst_w, dst_h, dst_ch);
 }
 
 } // extern "C"

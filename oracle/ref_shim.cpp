@@ -27,6 +27,8 @@
 #include <mitsuba/render/sensor.h>
 #include <drjit/random.h>
 #include <drjit/packet.h>
+#include <drjit/color.h>
+#include AMVPT_REF_UTIL_H      // src/mitsuba/util.h of the reference (viewer helpers: clip, mod, lerp2, interpolate2d), path given by the Makefile
 
 using namespace mitsuba;
 namespace dr = drjit;
@@ -311,6 +313,18 @@ float ref_const(int which) {
         case 5: return dr::Pi<float>;
     }
     return 0.f;
+}
+
+// ---- display step leaves: dr::linear_to_srgb (ext/drjit/include/drjit/color.h:19-53), viewer helpers (src/mitsuba/util.h:47-49, 104-128)
+void ref_linear_to_srgb(const float *in, int n, float *out) {
+    for (int i = 0; i < n; ++i) { F x(in[i]); F r = dr::linear_to_srgb(x); out[i] = r[0]; }
+}
+void ref_clip_mod(const float *x, const float *y, int n, float *out_clip, float *out_mod) {
+    for (int i = 0; i < n; ++i) { out_clip[i] = mitsuba::clip(x[i]); out_mod[i] = mitsuba::mod(x[i], y[i]); }
+}
+void ref_interpolate2d_u8(const uint8_t *data, uint32_t w, uint32_t h, uint32_t nch, const float *xy, int n, uint32_t c, int nearest, uint8_t *out) {
+    for (int i = 0; i < n; ++i)
+        out[i] = mitsuba::interpolate2d<uint8_t>(data, mitsuba::vec2f(xy[2 * i], xy[2 * i + 1]), mitsuba::vec2u(w, h), c, nch, nearest != 0);
 }
 
 } // extern "C"

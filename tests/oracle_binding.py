@@ -208,6 +208,27 @@ def develop(rgbw):
     return rgbw[..., :3] / np.where(w == 0, 1, w)
 
 
+# ---- display step (oracle/o_display.h)
+u8p = C.POINTER(C.c_uint8)
+
+
+def to_srgb8(rgb):
+    x = np.ascontiguousarray(rgb, np.float32); out = np.zeros(x.shape, np.uint8); orc().orc_to_srgb8(_p(x), C.c_uint64(x.size), _p(out, u8p)); return out
+
+
+def preset_arrays(preset, dst_ch):
+    pf = np.array([preset["center"], preset["focus"], preset["pitch"], preset["tilt"], preset["subp"], *preset["view"]], np.float32)
+    pi = np.array([*preset["grid"], int(preset.get("flip_rgb", dst_ch == 3)), int(preset.get("quilt", False)), int(preset.get("nearest", False))], np.int32)
+    return pf, pi
+
+
+def interlace(src, preset, dst_w, dst_h, dst_ch=3):
+    src = np.ascontiguousarray(src, np.uint8); h, w, c = src.shape; pf, pi = preset_arrays(preset, dst_ch)
+    out = np.zeros((dst_h, dst_w, dst_ch), np.uint8)
+    orc().orc_interlace(_p(src, u8p), C.c_uint32(w), C.c_uint32(h), C.c_uint32(c), _p(pf), _p(pi, C.POINTER(C.c_int32)), _p(out, u8p), C.c_uint32(dst_w), C.c_uint32(dst_h), C.c_uint32(dst_ch))
+    return out
+
+
 def math1(op, x):
     x = np.ascontiguousarray(x, np.float32); out = np.zeros_like(x); orc().orc_math1(C.c_int(op), _p(x), C.c_int(len(x)), _p(out)); return out
 

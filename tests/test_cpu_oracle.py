@@ -209,3 +209,65 @@ def test_reconstruction_filters_known_answers_and_film(ob, scenes):
         box = dict(desc); box["rfilter"] = ("box", 0.5); fb, _, _ = ob.OracleScene(box).render(seed=0, spp=4, brute=True)
         a, b = ob.develop(film), ob.develop(fb)
         assert abs(a.mean() - b.mean()) < 0.05 * b.mean()                           # the filter redistributes, it does not add energy
+
+
+# ------------------------------------------------------------------ display step: oracle/o_display.h
+DISPLAY = json.load(open(os.path.join(ROOT, "tests", "golden", "display_vectors.json")))
+LKG4x8 = dict(center=-0.5, focus=-0.05, pitch=354.548, tilt=-0.114, subp=0.00013, view=(1.0, 1.0), grid=(4, 8))   # src/mitsuba/program.h:74-75
+
+
+def _display_leaves(lib, prefix, g):
+    P = lambda a: a.ctypes.data_as(C.c_void_p)
+    x = np.array(g["linear_to_srgb"]["x"], np.uint32).view(np.float32); y = np.zeros_like(x)
+    if prefix == "orc": lib.orc_linear_to_srgb(P(x), C.c_uint64(len(x)), P(y))
+    else: lib.ref_linear_to_srgb(P(x), C.c_int(len(x)), P(y))
+    assert np.array_equal(y.view(np.uint32), np.array(g["linear_to_srgb"]["y"], np.uint32)), "linear_to_srgb"
+    a = np.array(g["clip_mod"]["x"], np.uint32).view(np.float32); b = np.array(g["clip_mod"]["y"], np.uint32).view(np.float32)
+    c = np.zeros_like(a); m = np.zeros_like(a); getattr(lib, prefix + "_clip_mod")(P(a), P(b), C.c_int(len(a)), P(c), P(m))
+    assert np.array_equal(c.view(np.uint32), np.array(g["clip_mod"]["clip"], np.uint32)) and np.array_equal(m.view(np.uint32), np.array(g["clip_mod"]["mod"], np.uint32))
+    gi = g["interpolate2d"]; img = np.array(gi["img"], np.uint8); xy = np.array(gi["xy"], np.uint32).view(np.float32); n = len(xy) // 2
+    for key, want in gi["out"].items():
+        near, ch = map(int, key.split("_")); o = np.zeros(n, np.uint8)
+        getattr(lib, prefix + "_interpolate2d_u8")(P(img), gi["w"], gi["h"], gi["nch"], P(xy), n, ch, near, P(o))
+        assert np.array_equal(o, np.array(want, np.uint8)), f"interpolate2d {key}"
+
+
+def test_display_leaves_match_reference_golden(ob):
+    """dr::linear_to_srgb, clip, mod and interpolate2d<uint8_t> of the oracle, bit for bit against vectors made from the reference's headers."""
+    _display_leaves(ob.orc(), "orc", DISPLAY)
+
+
+def test_display_golden_still_matches_reference_headers_when_available(ob):
+    ref = ob.ref()
+    if ref is None:
+        pytest.skip("oracle/_ref not built (no /root/reference on this machine)")
+    _display_leaves(ref, "ref", DISPLAY)
+
+
+def test_srgb8_known_values_and_rounding(ob):
+    """Bitmap::convert(RGB, UInt8, srgb): 0 -> 0, 1 -> 255, mid grey 0.2140 -> 127/128 boundary, clamping above 1; monotone."""
+    x = np.array([0.0, 1.0, 2.5, 0.0031308, 0.001, 0.18, 0.5], np.float32)
+    got = ob.to_srgb8(x)
+    want = np.rint(np.clip(np.where(x <= 0.0031308, 12.92 * x, 1.055 * np.power(x, 1 / 2.4) - 0.055), 0, 1) * 255).astype(np.uint8)
+    assert np.abs(got.astype(int) - want.astype(int)).max() <= 1 and got[0] == 0 and got[1] == 255 and got[2] == 255
+    ramp = ob.to_srgb8(np.linspace(0, 1.2, 5000, dtype=np.float32))
+    assert (np.diff(ramp.astype(int)) >= 0).all() and set(np.unique(ramp)) == set(range(256))
+
+
+def test_interlace_oracle_properties(ob):
+    rng = np.random.default_rng(5)
+    quilt = rng.integers(0, 256, (64, 48, 3), dtype=np.uint8)
+    # "Display quilt" + nearest scaling at the quilt's own size: rows map to themselves; x0 = dx / (row_bytes - 1) with dx the BYTE offset
+    # (program.cpp:213-215, 241), so only the first column is the identity -- a quirk of the reference that the oracle keeps
+    q = ob.interlace(quilt, dict(LKG4x8, quilt=True, nearest=True, flip_rgb=True), 48, 64, 3)
+    assert q.shape == (64, 48, 3) and np.array_equal(q[:, 0], quilt[:, 0])
+    assert np.array_equal(q[0], ob.interlace(quilt[:1].repeat(2, 0), dict(LKG4x8, quilt=True, nearest=True, flip_rgb=True), 48, 2, 3)[0])
+    # flip_rgb = false writes channel c to 2 - c (BGR surface, program.cpp:245); the fourth channel is opaque
+    a = ob.interlace(quilt, dict(LKG4x8, flip_rgb=True), 40, 30, 4); b = ob.interlace(quilt, dict(LKG4x8, flip_rgb=False), 40, 30, 4)
+    assert np.array_equal(a[..., :3], b[..., 2::-1]) and (a[..., 3] == 255).all()
+    # a quilt whose views are flat colours: each interlaced sub-pixel is exactly one view's colour (nearest), and several views show up
+    gx, gy = LKG4x8["grid"]; flat = np.zeros((8 * gy, 8 * gx, 3), np.uint8)
+    for v in range(gx * gy):
+        flat[(v // gx) * 8:(v // gx + 1) * 8, (v % gx) * 8:(v % gx + 1) * 8] = 8 * v + 3
+    il = ob.interlace(flat, dict(LKG4x8, nearest=True, focus=0.0), 200, 120, 3)
+    assert set(np.unique(il)) <= {8 * v + 3 for v in range(gx * gy)} and len(np.unique(il)) > gx * gy // 2

@@ -502,3 +502,59 @@ def test_sample_reuse_is_consistent_with_plain_path_tracing(scenes, gpu):
     assert np.allclose(parts, film, rtol=1e-4, atol=1e-4 * film[..., :3].max())
     with pytest.raises(Exception, match="adaptive"):
         s1.render(seed=1, spp=64, adaptive=True)
+
+
+# ------------------------------------------------------------------ output path and display step
+LKG4x8 = dict(center=-0.5, focus=-0.05, pitch=354.548, tilt=-0.114, subp=0.00013, view=(1.0, 1.0), grid=(4, 8))   # src/mitsuba/program.h:74-75
+
+
+def _read_pfm(path):
+    with open(path, "rb") as f:
+        assert f.readline() == b"PF\n"; w, h = map(int, f.readline().split()); assert f.readline().strip() == b"-1"
+        return np.frombuffer(f.read(), "<f4").reshape(h, w, 3)[::-1]
+
+
+def test_pfm_output_quilt_and_per_view_split(scenes, gpu, tmp_path):
+    """HDRFilm::write (file_format = pfm): the file holds the developed film bit for bit, bottom row first; view >= 0 cuts that view's tile."""
+    s = scenes.build(scenes.cornell_box(grid_x=3, grid_y=2, view_res=40, sample_count=4), device=gpu)
+    img = s.render(seed=2, spp=4)
+    s.write_pfm(tmp_path / "quilt.pfm"); assert_bits(_read_pfm(tmp_path / "quilt.pfm").reshape(-1, 3), img.reshape(-1, 3), "quilt pfm")
+    for x0, y0, w, h, v in s.shard_tiles(0, 1):
+        s.write_pfm(tmp_path / f"v{v}.pfm", view=v)
+        assert_bits(_read_pfm(tmp_path / f"v{v}.pfm").reshape(-1, 3), img[y0:y0 + h, x0:x0 + w].reshape(-1, 3), f"view {v} pfm")
+    with pytest.raises(Exception, match="out of range"):
+        s.write_pfm(tmp_path / "x.pfm", view=6)
+
+
+@pytest.mark.parametrize("res", [40, 37])           # 37: film pixel count not a multiple of four (ragged tail of the 4-pixel kernel)
+def test_srgb8_quilt_bit_exact(res, scenes, ob, gpu):
+    s = scenes.build(scenes.cornell_box(grid_x=3, grid_y=1, view_res=res, sample_count=4), device=gpu)
+    s.render(seed=1, spp=4, develop=False)
+    # widen the value range beyond what the box produces: dark, bright (clamped), zero-weight pixels
+    rng = np.random.default_rng(res); extra = np.zeros_like(s.film_raw()); m = rng.uniform(size=extra.shape[:2]) < 0.3
+    extra[m, :3] = np.exp(rng.uniform(-12, 4, (int(m.sum()), 3))).astype(np.float32); s.film_add(extra)
+    got = s.to_srgb8(); want = ob.to_srgb8(ob.develop(s.film_raw()).astype(np.float32))
+    assert np.array_equal(s.develop().view(np.uint32), ob.develop(s.film_raw()).astype(np.float32).view(np.uint32))
+    assert got.shape == want.shape and np.array_equal(got, want), f"{(got != want).sum()} sub-pixels differ"
+    assert len(np.unique(got)) > 200
+
+
+@pytest.mark.parametrize("mode", ["lkg", "lkg_bgr4", "nearest", "quilt", "extern_rgba", "fine_pitch"])
+def test_interlace_bit_exact(mode, scenes, ob, gpu):
+    """Program::display_image as a kernel against the oracle restatement: every destination byte equal."""
+    s = scenes.build(scenes.cornell_box(grid_x=4, grid_y=8, view_res=48, sample_count=4), device=gpu)
+    s.render(seed=0, spp=4, develop=False); quilt = s.to_srgb8()
+    preset, dst, ch, src = dict(LKG4x8), (301, 173), 3, None
+    if mode == "lkg_bgr4": preset["flip_rgb"] = False; ch = 4
+    if mode == "nearest": preset["nearest"] = True; preset["focus"] = 0.3
+    if mode == "quilt": preset["quilt"] = True; dst = (150, 97)
+    if mode == "extern_rgba":
+        rng = np.random.default_rng(3); src = rng.integers(0, 256, (211, 163, 4), dtype=np.uint8); preset.update(grid=(5, 9), view=(0.9, 0.8)); ch = 4
+    if mode == "fine_pitch": preset.update(pitch=52.3, tilt=0.31, center=0.2, subp=0.0021, focus=0.12); dst = (640, 360)
+    got = s.interlace(preset, dst[0], dst[1], ch, src=src)
+    want = ob.interlace(quilt if src is None else src, preset, dst[0], dst[1], ch)
+    assert np.array_equal(got, want), f"{mode}: {(got != want).sum()} of {got.size} bytes differ"
+    assert len(np.unique(got[..., :3])) > 20
+    srgb_ms, il_ms = s.display_last_ms(); assert il_ms > 0
+    with pytest.raises(Exception):
+        s.interlace(preset, dst[0], 1, ch)
