@@ -27,30 +27,36 @@ AM_D float linear_to_srgb(float x) {
 // round to nearest even.  The reference clamps and rounds in double; v * 255 is a float, so rounding it in float is the same number.
 AM_D uint32_t to_srgb8(float v) { return (uint32_t) __float2int_rn(fminf(fmaxf(linear_to_srgb(v) * 255.f, 0.f), 255.f)); }
 
-// HDRFilm::develop + Bitmap::convert(RGB, UInt8, srgb): four pixels per thread, 64 B read and three 32-bit words written.
-// Streaming and HBM-bound: 16 B + 3 B per pixel.
+// HDRFilm::develop + Bitmap::convert(RGB, UInt8, srgb).  A CTA converts tiles of 1024 pixels: four coalesced 16-byte loads per thread
+// (all issued before the arithmetic), the 3 bytes of each pixel staged in shared memory, the tile's 3072 bytes stored as three
+// coalesced 32-bit words per thread.  Streaming: 16 B read + 3 B written per pixel.
 __global__ void __launch_bounds__(256) srgb8_kernel(const float4 *__restrict__ film, uint8_t *__restrict__ out, size_t npix) {
-    const size_t nq = npix / 4, stride = (size_t) gridDim.x * blockDim.x;
-    for (size_t q = (size_t) blockIdx.x * blockDim.x + threadIdx.x; q < nq; q += stride) {
-        uint32_t b[12];
+    __shared__ uint32_t sm[768];
+    uint8_t *smb = reinterpret_cast<uint8_t *>(sm);
+    const size_t n_tiles = (npix + 1023) / 1024; const uint32_t tid = threadIdx.x;
+    for (size_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const size_t base = tile * 1024; const uint32_t rem = (uint32_t) (npix - base < 1024 ? npix - base : 1024);
+        float4 v[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { const uint32_t i = k * 256 + tid; v[k] = i < rem ? __ldcs(film + base + i) : make_float4(0.f, 0.f, 0.f, 0.f); }
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-            const float4 v = film[4 * q + k]; const float w = (v.w == 0.f) ? 1.f : v.w;
-            b[3 * k] = to_srgb8(fdiv(v.x, w)); b[3 * k + 1] = to_srgb8(fdiv(v.y, w)); b[3 * k + 2] = to_srgb8(fdiv(v.z, w));
+            const float w = (v[k].w == 0.f) ? 1.f : v[k].w; uint8_t *o = smb + 3 * (k * 256 + tid);
+            o[0] = (uint8_t) to_srgb8(fdiv(v[k].x, w)); o[1] = (uint8_t) to_srgb8(fdiv(v[k].y, w)); o[2] = (uint8_t) to_srgb8(fdiv(v[k].z, w));
         }
-        uint32_t *o = reinterpret_cast<uint32_t *>(out) + 3 * q;
+        __syncthreads();
+        if (rem == 1024) {
+            uint32_t *o = reinterpret_cast<uint32_t *>(out) + tile * 768;      // 3 * base bytes: a multiple of four
 #pragma unroll
-        for (int k = 0; k < 3; ++k) o[k] = b[4 * k] | (b[4 * k + 1] << 8) | (b[4 * k + 2] << 16) | (b[4 * k + 3] << 24);
-    }
-    if (blockIdx.x == 0 && threadIdx.x < (npix & 3)) {       // ragged tail
-        const size_t i = nq * 4 + threadIdx.x; const float4 v = film[i]; const float w = (v.w == 0.f) ? 1.f : v.w;
-        out[3 * i] = (uint8_t) to_srgb8(fdiv(v.x, w)); out[3 * i + 1] = (uint8_t) to_srgb8(fdiv(v.y, w)); out[3 * i + 2] = (uint8_t) to_srgb8(fdiv(v.z, w));
+            for (int j = 0; j < 3; ++j) o[j * 256 + tid] = sm[j * 256 + tid];
+        } else for (uint32_t j = tid; j < 3 * rem; j += 256) out[3 * base + j] = smb[j];    // ragged last tile
+        __syncthreads();
     }
 }
 void launch_srgb8(const float4 *film, uint8_t *out, size_t npix, int sm_count, cudaStream_t st) {
     if (!npix) return;
-    size_t need = (npix / 4 + 255) / 256; unsigned blocks = (unsigned) (need < 1 ? 1 : need), cap = (unsigned) sm_count * 8;
-    srgb8_kernel<<<blocks > cap ? cap : blocks, 256, 0, st>>>(film, out, npix);
+    const size_t n_tiles = (npix + 1023) / 1024; const unsigned cap = (unsigned) sm_count * 8;
+    srgb8_kernel<<<n_tiles < cap ? (unsigned) n_tiles : cap, 256, 0, st>>>(film, out, npix);
 }
 
 // src/mitsuba/util.h:47-49, 104-128

@@ -147,3 +147,17 @@ def test_film_reduce_world_size_2_gloo(pkg, tmp_path):
                         "--master-port", "29591", str(script)], capture_output=True, text=True, timeout=240)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert r.stdout.count("ok") == 2 and "0" in r.stdout and "1" in r.stdout
+
+
+def test_cli_arguments_mirror_the_reference_executable(pkg):
+    """python -m mitsuba3-amvpt_b200: the options of src/mitsuba/mitsuba_render.cpp:165-184 that reach this path (-D -s -n -o -m -t)."""
+    import importlib
+    cli = importlib.import_module("mitsuba3-amvpt_b200.__main__")
+    a = cli.parse_args(["a.xml", "b.xml", "-D", "spp=64", "--define", "res=256", "-n", "32", "-s", "0", "-m", "cuda_rgb", "-t", "8", "-o", "x.exr"])
+    assert a.scenes == ["a.xml", "b.xml"] and a.define == {"spp": "64", "res": "256"} and a.nspp == 32 and a.sensor == 0
+    assert cli.output_path("dir/scene.xml", None, 1) == ("dir/scene.pfm", False)
+    assert cli.output_path("scene.xml", "out/img.exr", 1) == ("out/img.pfm", True)      # OpenEXR is unavailable: PFM is written and reported
+    assert cli.output_path("a.xml", "ignored.pfm", 2) == ("a.pfm", False)               # several scenes: one output per scene name
+    for bad in (["a.xml", "-D", "novalue"], ["a.xml", "-m", "scalar_spectral"], []):
+        with pytest.raises(SystemExit):
+            cli.parse_args(bad)

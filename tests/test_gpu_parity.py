@@ -7,6 +7,8 @@ import os
 import numpy as np
 import pytest
 
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
 pytestmark = pytest.mark.gpu
 FILM_RTOL = 2e-5      # order of fp32 summation of <= 64 samples per pixel; stated tolerance for the film compare
 
@@ -558,3 +560,23 @@ def test_interlace_bit_exact(mode, scenes, ob, gpu):
     srgb_ms, il_ms = s.display_last_ms(); assert il_ms > 0
     with pytest.raises(Exception):
         s.interlace(preset, dst[0], 1, ch)
+
+
+def test_cli_renders_writes_pfm_views_and_interlace(pkg, scenes, gpu, tmp_path):
+    """`python -m mitsuba3-amvpt_b200 scene.xml -n 4 -o out.exr --views --interlace W H` = render_internal of the reference's CLI
+    (src/mitsuba/mitsuba_render.cpp:105-133): render with seed 0, then film->write -- same bits as the API calls."""
+    import subprocess, sys
+    desc = scenes.cornell_box(grid_x=2, grid_y=2, view_res=32, sample_count=4)
+    xml = scenes.export_xml(desc, str(tmp_path))
+    out = tmp_path / "img.exr"
+    r = subprocess.run([sys.executable, "-m", "mitsuba3-amvpt_b200", str(xml), "-n", "4", "-o", str(out), "--views", "--interlace", "96", "64"],
+                       cwd=ROOT, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    assert "Rendering finished." in r.stdout and "img.pfm" in r.stdout and "OpenEXR output is unavailable" in r.stdout
+    s = scenes.build(desc, device=gpu); img = s.render(seed=0, spp=4)
+    assert_bits(_read_pfm(tmp_path / "img.pfm").reshape(-1, 3), img.reshape(-1, 3), "CLI quilt")
+    for x0, y0, w, h, v in s.shard_tiles(0, 1):
+        assert_bits(_read_pfm(tmp_path / f"img_v{v}.pfm").reshape(-1, 3), img[y0:y0 + h, x0:x0 + w].reshape(-1, 3), f"CLI view {v}")
+    s.to_srgb8(fetch=False); want = s.interlace(dict(LKG4x8, grid=(2, 2)), 96, 64, 3)
+    ppm = open(tmp_path / "img_interlaced.ppm", "rb").read()
+    assert ppm.startswith(b"P6\n96 64\n255\n") and np.array_equal(np.frombuffer(ppm[len(b"P6\n96 64\n255\n"):], np.uint8).reshape(64, 96, 3), want)
