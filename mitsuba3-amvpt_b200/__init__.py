@@ -79,7 +79,7 @@ EXPORTS = ["amvpt_last_error", "amvpt_device_count", "amvpt_scene_create", "amvp
            "amvpt_scene_get_bsdf", "amvpt_scene_get_integrator", "amvpt_render", "amvpt_shard_tiles", "amvpt_cancel", "amvpt_film_clear",
            "amvpt_film_raw", "amvpt_film_develop", "amvpt_film_develop_device", "amvpt_film_device_ptr", "amvpt_film_add_host",
            "amvpt_trace_lanes", "amvpt_trace_lanes_multi", "amvpt_intersect", "amvpt_bsdf_eval_pdf_sample", "amvpt_math1", "amvpt_sampler_stream",
-           "amvpt_bvh_validate", "amvpt_film_write_pfm", "amvpt_film_to_srgb8", "amvpt_interlace", "amvpt_display_last_ms"]
+           "amvpt_bvh_validate", "amvpt_film_write_pfm", "amvpt_film_write_exr", "amvpt_f32_to_f16", "amvpt_film_to_srgb8", "amvpt_interlace", "amvpt_display_last_ms"]
 lib.amvpt_scene_destroy.restype = None
 lib.amvpt_scene_destroy.argtypes = [C.c_void_p]
 
@@ -296,6 +296,13 @@ class Scene:
         """HDRFilm::write, file_format = pfm (Bitmap::write_pfm, src/core/bitmap.cpp:2270-2299); view >= 0 writes that view's tile only."""
         _chk(lib.amvpt_film_write_pfm(self._h, str(path).encode(), C.c_int32(view)))
 
+    def write_exr(self, path, view=-1, component_format="float16"):
+        """HDRFilm::write, file_format = openexr (hdrfilm.cpp:420-560; component_format as hdrfilm.cpp:146-147, 191-196): RGB half or
+        float, uncompressed scan lines; view >= 0 writes that view's tile only."""
+        if component_format not in ("float16", "float32"):
+            raise ValueError(f"component_format must be float16 or float32, not {component_format!r}")
+        _chk(lib.amvpt_film_write_exr(self._h, str(path).encode(), C.c_int32(view), C.c_int32(component_format == "float16")))
+
     def to_srgb8(self, fetch=True):
         """The developed quilt as the viewer loads it: Bitmap::convert(RGB, UInt8, srgb) (src/mitsuba/program.h:55). Stays on the device for interlace()."""
         i = self.info(); out = np.zeros((i["film_h"], i["film_w"], 3), np.uint8) if fetch else None
@@ -362,6 +369,12 @@ def load_string(xml, base_dir=".", **defines):
     h = C.c_void_p(); arr, n = _defines(defines)
     _chk(lib.amvpt_scene_from_xml_string(xml.encode(), str(base_dir).encode(), arr, n, C.byref(h)))
     return Scene(h)
+
+
+def f32_to_f16(x):
+    """Float32 -> float16 bits as write_exr stores them (Struct conversion to Float16 for hdrfilm's component_format = float16)."""
+    x = np.ascontiguousarray(x, np.float32); out = np.empty(x.shape, np.uint16)
+    _chk(lib.amvpt_f32_to_f16(_p(x), out.ctypes.data_as(C.c_void_p), C.c_uint64(x.size))); return out
 
 
 def device_count():

@@ -4,8 +4,9 @@ spp, develop = false) followed by film->write(filename)).
 
     python -m mitsuba3-amvpt_b200 scene.xml [-n SPP] [-o OUT] [-D key=value ...] [-s 0] [--views] [--interlace W H]
 
-The output is PFM (OpenEXR is not in this tree): `-o foo.exr` writes `foo.pfm` and says so.  `--views` also writes one file per
-view of the quilt (`foo_v<k>.pfm`); `--interlace W H` writes the lenticular interlace of the quilt as a binary PPM."""
+The output follows the extension of `-o`: `.exr` (the default, as the reference; float16 RGB unless `--component-format float32`,
+written as an uncompressed scan-line OpenEXR file) or `.pfm`.  `--views` also writes one file per view of the quilt
+(`foo_v<k>.<ext>`); `--interlace W H` writes the lenticular interlace of the quilt as a binary PPM."""
 import argparse
 import os
 import sys
@@ -18,14 +19,15 @@ def parse_args(argv):
     ap.add_argument("-D", "--define", action="append", default=[], metavar="key=value", help="substitute $key in the scene file")
     ap.add_argument("-s", "--sensor", type=int, default=0, help="sensor index (the grid / batch sensor is sensor 0)")
     ap.add_argument("-n", "--nspp", type=int, default=0, help="samples per pixel (0 = the sampler's sample_count)")
-    ap.add_argument("-o", "--output", default=None, help="output file (default: scene name with .pfm)")
+    ap.add_argument("-o", "--output", default=None, help="output file, .exr or .pfm (default: scene name with .exr)")
     ap.add_argument("-m", "--mode", default="cuda_rgb", help="accepted for compatibility; this build is the CUDA RGB path")
     ap.add_argument("-t", "--threads", type=int, default=0, help="accepted for compatibility (host threads are not used by the render loop)")
     ap.add_argument("-v", "--verbose", action="count", default=0)
     ap.add_argument("--seed", type=int, default=0)
     ap.add_argument("--device", type=int, default=0)
     ap.add_argument("--scheduler", default="auto")
-    ap.add_argument("--views", action="store_true", help="also write one PFM per view of the quilt")
+    ap.add_argument("--views", action="store_true", help="also write one file per view of the quilt")
+    ap.add_argument("--component-format", default="float16", choices=("float16", "float32"), help="OpenEXR component format (hdrfilm.cpp:146-147)")
     ap.add_argument("--interlace", nargs=2, type=int, metavar=("W", "H"), help="also write the lenticular interlace (default LKG preset, the scene's grid) as PPM")
     a = ap.parse_args(argv)
     defines = {}
@@ -42,8 +44,10 @@ def parse_args(argv):
 def output_path(scene, output, n_scenes):
     base = output if (output and n_scenes == 1) else os.path.splitext(scene)[0]
     root, ext = os.path.splitext(base)
-    note = ext.lower() not in ("", ".pfm")
-    return root + ".pfm", note
+    ext = ext.lower()
+    if ext == ".pfm":
+        return root + ".pfm", False
+    return root + ".exr", ext not in ("", ".exr")                   # film->write replaces any other extension (hdrfilm.cpp:432-440)
 
 
 def main(argv=None):
@@ -59,11 +63,13 @@ def main(argv=None):
         st = s.last_stats
         print(f"Rendering finished. (took {st['seconds'] * 1e3:.1f} ms on the device, {st['paths'] / max(st['seconds'], 1e-12) / 1e6:.1f} Mpaths/s, "
               f"{st['spp_done']} spp, {time.perf_counter() - t0:.2f} s wall)")
-        s.write_pfm(out)
-        print(f"Writing \"{out}\"" + (" (PFM: OpenEXR output is unavailable in this build)" if note else ""))
+        root, ext = os.path.splitext(out)
+        write = (lambda p, view=-1: s.write_pfm(p, view=view)) if ext == ".pfm" else (lambda p, view=-1: s.write_exr(p, view=view, component_format=a.component_format))
+        write(out)
+        print(f"Writing \"{out}\"" + (" (extension replaced by .exr)" if note else ""))
         if a.views:
             for *_, v in s.shard_tiles(0, 1):
-                s.write_pfm(f"{os.path.splitext(out)[0]}_v{int(v)}.pfm", view=int(v))
+                write(f"{root}_v{int(v)}{ext}", view=int(v))
         if a.interlace:
             s.to_srgb8(fetch=False); tiles = s.shard_tiles(0, 1)      # the grid of the quilt from its view rectangles
             gx, gy = len({int(r[0]) for r in tiles}), len({int(r[1]) for r in tiles})

@@ -243,22 +243,78 @@ int amvpt_interlace(amvpt_scene *h, const uint8_t *src, uint32_t src_w, uint32_t
 int amvpt_display_last_ms(amvpt_scene *h, float *srgb8_ms, float *interlace_ms) {
     return guard([&] { Scene &s = committed(h); if (srgb8_ms) *srgb8_ms = s.display_ms[0]; if (interlace_ms) *interlace_ms = s.display_ms[1]; return AMVPT_OK; });
 }
+// developed quilt on the host + the rectangle `view` selects (view < 0: the whole quilt)
+struct Developed { std::vector<float> rgb; uint32_t x0 = 0, y0 = 0, w = 0, h = 0, stride = 0; };
+static Developed develop_view(Scene &s, int32_t view, const char *who) {
+    size_t npix = (size_t) s.film_w * s.film_h; Developed d;
+    if (!s.rgb) s.rgb = (float *) s.dalloc(npix * 3 * sizeof(float));
+    launch_develop(s.film, s.rgb, npix, nullptr); AM_CUDA(cudaGetLastError());
+    d.rgb.resize(npix * 3); AM_CUDA(cudaMemcpy(d.rgb.data(), s.rgb, npix * 3 * sizeof(float), cudaMemcpyDeviceToHost));
+    d.w = d.stride = s.film_w; d.h = s.film_h;
+    if (view >= 0) {
+        Shard sh; std::vector<TileDesc> t = rank_tiles(s, sh, false); bool found = false;
+        for (auto &r : t) if ((int32_t) r.pad == view) { d.x0 = r.x0; d.y0 = r.y0; d.w = r.w; d.h = r.h; found = true; break; }
+        if (!found) AM_THROW("%s: view %d out of range (%zu views)", who, view, t.size());
+    }
+    return d;
+}
 int amvpt_film_write_pfm(amvpt_scene *h, const char *path, int32_t view) {
-    return guard([&] { NEED(path); Scene &s = committed(h); size_t npix = (size_t) s.film_w * s.film_h;
-        if (!s.rgb) s.rgb = (float *) s.dalloc(npix * 3 * sizeof(float));
-        launch_develop(s.film, s.rgb, npix, nullptr); AM_CUDA(cudaGetLastError());
-        std::vector<float> rgb(npix * 3); AM_CUDA(cudaMemcpy(rgb.data(), s.rgb, npix * 3 * sizeof(float), cudaMemcpyDeviceToHost));
-        uint32_t x0 = 0, y0 = 0, w = s.film_w, hh = s.film_h;
-        if (view >= 0) {
-            Shard sh; std::vector<TileDesc> t = rank_tiles(s, sh, false); bool found = false;
-            for (auto &r : t) if ((int32_t) r.pad == view) { x0 = r.x0; y0 = r.y0; w = r.w; hh = r.h; found = true; break; }
-            if (!found) AM_THROW("write_pfm: view %d out of range (%zu views)", view, t.size());
-        }
+    return guard([&] { NEED(path); Scene &s = committed(h); Developed d = develop_view(s, view, "write_pfm");
         FILE *f = fopen(path, "wb"); if (!f) AM_THROW("write_pfm: cannot open %s", path);
-        fprintf(f, "PF\n%u %u\n-1\n", w, hh);                        // Bitmap::write_pfm (src/core/bitmap.cpp:2270-2299): little endian, bottom row first
+        fprintf(f, "PF\n%u %u\n-1\n", d.w, d.h);                      // Bitmap::write_pfm (src/core/bitmap.cpp:2270-2299): little endian, bottom row first
         bool ok = true;
-        for (uint32_t y = 0; y < hh && ok; ++y) ok = fwrite(rgb.data() + ((size_t) (y0 + hh - 1 - y) * s.film_w + x0) * 3, sizeof(float), (size_t) w * 3, f) == (size_t) w * 3;
+        for (uint32_t y = 0; y < d.h && ok; ++y) ok = fwrite(d.rgb.data() + ((size_t) (d.y0 + d.h - 1 - y) * d.stride + d.x0) * 3, sizeof(float), (size_t) d.w * 3, f) == (size_t) d.w * 3;
         ok = (fclose(f) == 0) && ok; if (!ok) AM_THROW("write_pfm: short write to %s", path);
+        return AMVPT_OK; });
+}
+// float32 -> float16, round to nearest even (what dr::half / Struct conversion to Float16 does; overflow -> inf, NaN kept quiet)
+static uint16_t f32_to_f16(float v) {
+    uint32_t x; memcpy(&x, &v, 4); uint32_t sign = (x >> 16) & 0x8000u; x &= 0x7fffffffu;
+    if (x >= 0x7f800000u) return (uint16_t) (sign | 0x7c00u | (x > 0x7f800000u ? 0x200u | ((x >> 13) & 0x3ffu) : 0u));
+    if (x >= 0x477ff000u) return (uint16_t) (sign | 0x7c00u);          // rounds to >= 65520 -> inf
+    if (x < 0x33000001u) return (uint16_t) sign;                        // <= 2^-25 -> +-0 (ties to even)
+    uint32_t e = x >> 23, m = (x & 0x7fffffu) | 0x800000u, shift, hbits;
+    if (e < 113) { shift = 126 - e; hbits = 0; } else { shift = 13; hbits = (e - 112) << 10; m &= 0x7fffffu; }
+    uint32_t q = m >> shift, rem = m & ((1u << shift) - 1), half = 1u << (shift - 1);
+    q += (rem > half) || (rem == half && (q & 1u));
+    return (uint16_t) (sign | (hbits + q));                             // a mantissa carry moves into the exponent, as it should
+}
+int amvpt_f32_to_f16(const float *src, uint16_t *dst, uint64_t n) {
+    return guard([&] { if (n) { NEED(src); NEED(dst); } for (uint64_t i = 0; i < n; ++i) dst[i] = f32_to_f16(src[i]); return AMVPT_OK; });
+}
+int amvpt_film_write_exr(amvpt_scene *h, const char *path, int32_t view, int32_t half_float) {
+    return guard([&] { NEED(path); Scene &s = committed(h); Developed d = develop_view(s, view, "write_exr");
+        // OpenEXR 2 single-part scan-line file, NO_COMPRESSION, channels B G R (alphabetical, as the format requires), top row first
+        std::vector<uint8_t> hd; auto put = [&](const void *p, size_t n) { hd.insert(hd.end(), (const uint8_t *) p, (const uint8_t *) p + n); };
+        auto str = [&](const char *z) { put(z, strlen(z) + 1); }; auto i32 = [&](int32_t v) { put(&v, 4); }; auto f32 = [&](float v) { put(&v, 4); };
+        auto attr = [&](const char *name, const char *type, int32_t size) { str(name); str(type); i32(size); };
+        i32(20000630); i32(2);
+        attr("channels", "chlist", 3 * 18 + 1);
+        for (const char *c : { "B", "G", "R" }) { str(c); i32(half_float ? 1 : 2); uint8_t z4[4] = { 0, 0, 0, 0 }; put(z4, 4); i32(1); i32(1); }
+        hd.push_back(0);
+        attr("compression", "compression", 1); hd.push_back(0);
+        attr("dataWindow", "box2i", 16); i32(0); i32(0); i32((int32_t) d.w - 1); i32((int32_t) d.h - 1);
+        attr("displayWindow", "box2i", 16); i32(0); i32(0); i32((int32_t) d.w - 1); i32((int32_t) d.h - 1);
+        attr("lineOrder", "lineOrder", 1); hd.push_back(0);
+        attr("pixelAspectRatio", "float", 4); f32(1.f);
+        attr("screenWindowCenter", "v2f", 8); f32(0.f); f32(0.f);
+        attr("screenWindowWidth", "float", 4); f32(1.f);
+        hd.push_back(0);
+        size_t bpc = half_float ? 2 : 4, row = (size_t) d.w * 3 * bpc; uint64_t off = hd.size() + (uint64_t) d.h * 8;
+        for (uint32_t y = 0; y < d.h; ++y) { uint64_t o = off + (uint64_t) y * (8 + row); put(&o, 8); }
+        FILE *f = fopen(path, "wb"); if (!f) AM_THROW("write_exr: cannot open %s", path);
+        bool ok = fwrite(hd.data(), 1, hd.size(), f) == hd.size(); std::vector<uint8_t> line(8 + row);
+        for (uint32_t y = 0; y < d.h && ok; ++y) {
+            int32_t yy = (int32_t) y, n = (int32_t) row; memcpy(line.data(), &yy, 4); memcpy(line.data() + 4, &n, 4);
+            const float *src = d.rgb.data() + ((size_t) (d.y0 + y) * d.stride + d.x0) * 3;
+            for (int c = 0; c < 3; ++c) {                               // file channel c = B, G, R <- source component 2 - c
+                uint8_t *dst = line.data() + 8 + (size_t) c * d.w * bpc;
+                for (uint32_t x = 0; x < d.w; ++x) { float v = src[(size_t) x * 3 + (2 - c)];
+                    if (half_float) { uint16_t hv = f32_to_f16(v); memcpy(dst + (size_t) x * 2, &hv, 2); } else memcpy(dst + (size_t) x * 4, &v, 4); }
+            }
+            ok = fwrite(line.data(), 1, line.size(), f) == line.size();
+        }
+        ok = (fclose(f) == 0) && ok; if (!ok) AM_THROW("write_exr: short write to %s", path);
         return AMVPT_OK; });
 }
 

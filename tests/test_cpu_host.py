@@ -155,9 +155,29 @@ def test_cli_arguments_mirror_the_reference_executable(pkg):
     cli = importlib.import_module("mitsuba3-amvpt_b200.__main__")
     a = cli.parse_args(["a.xml", "b.xml", "-D", "spp=64", "--define", "res=256", "-n", "32", "-s", "0", "-m", "cuda_rgb", "-t", "8", "-o", "x.exr"])
     assert a.scenes == ["a.xml", "b.xml"] and a.define == {"spp": "64", "res": "256"} and a.nspp == 32 and a.sensor == 0
-    assert cli.output_path("dir/scene.xml", None, 1) == ("dir/scene.pfm", False)
-    assert cli.output_path("scene.xml", "out/img.exr", 1) == ("out/img.pfm", True)      # OpenEXR is unavailable: PFM is written and reported
-    assert cli.output_path("a.xml", "ignored.pfm", 2) == ("a.pfm", False)               # several scenes: one output per scene name
+    assert cli.output_path("dir/scene.xml", None, 1) == ("dir/scene.exr", False)        # hdrfilm's default file_format is openexr
+    assert cli.output_path("scene.xml", "out/img.exr", 1) == ("out/img.exr", False)
+    assert cli.output_path("scene.xml", "out/img.pfm", 1) == ("out/img.pfm", False)
+    assert cli.output_path("scene.xml", "out/img.png", 1) == ("out/img.exr", True)      # film->write replaces a foreign extension
+    assert cli.output_path("a.xml", "ignored.pfm", 2) == ("a.exr", False)               # several scenes: one output per scene name
     for bad in (["a.xml", "-D", "novalue"], ["a.xml", "-m", "scalar_spectral"], []):
         with pytest.raises(SystemExit):
             cli.parse_args(bad)
+
+
+def test_exr_half_conversion_is_round_to_nearest_even(pkg):
+    """amvpt_f32_to_f16 (the component conversion of amvpt_film_write_exr) against numpy's IEEE conversion: every float16 value, the
+    midpoints between neighbours and their float32 neighbours, the overflow / underflow thresholds, infinities, NaN stays NaN."""
+    h = np.arange(0x10000, dtype=np.uint32).astype(np.uint16); f = h.view(np.float16).astype(np.float32)
+    fin = np.isfinite(f); assert np.array_equal(pkg.f32_to_f16(f)[fin | np.isinf(f)], h[fin | np.isinf(f)])
+    nan = pkg.f32_to_f16(f[np.isnan(f)]).view(np.float16); assert np.isnan(nan).all()
+    pos = np.sort(f[fin & (f >= 0)]); mid = ((pos[:-1].astype(np.float64) + pos[1:].astype(np.float64)) * 0.5).astype(np.float32)   # exact in float32
+    cases = np.concatenate([mid, np.nextafter(mid, np.float32(np.inf)), np.nextafter(mid, np.float32(-np.inf)),
+                            np.array([65519.996, 65520.0, 65536.0, 3.4e38, 2.0 ** -25, 2.0 ** -26, 1e-45, 0.0], np.float32),
+                            np.random.default_rng(3).standard_normal(200000).astype(np.float32) * np.float32(300.0),
+                            np.exp(np.random.default_rng(4).uniform(-25.0, 13.0, 200000)).astype(np.float32)])
+    cases = np.concatenate([cases, -cases])
+    with np.errstate(over="ignore"):
+        want = cases.astype(np.float16).view(np.uint16)
+    assert np.array_equal(pkg.f32_to_f16(cases), want)
+    assert pkg.f32_to_f16(np.zeros(0, np.float32)).size == 0

@@ -516,6 +516,61 @@ def _read_pfm(path):
         return np.frombuffer(f.read(), "<f4").reshape(h, w, 3)[::-1]
 
 
+def _read_exr(path):
+    """Minimal reader for single-part, uncompressed scan-line OpenEXR files (the layout of the OpenEXR 2 file format document)."""
+    import struct
+    b = open(path, "rb").read(); assert struct.unpack_from("<ii", b, 0) == (20000630, 2); o = 8; attrs = {}
+    def cstr(o):
+        e = b.index(b"\0", o); return b[o:e].decode(), e + 1
+    while b[o] != 0:
+        name, o = cstr(o); typ, o = cstr(o); n, = struct.unpack_from("<i", b, o); o += 4; attrs[name] = (typ, b[o:o + n]); o += n
+    o += 1
+    assert attrs["compression"] == ("compression", b"\0") and attrs["lineOrder"] == ("lineOrder", b"\0")
+    x0, y0, x1, y1 = struct.unpack("<4i", attrs["dataWindow"][1]); w, h = x1 - x0 + 1, y1 - y0 + 1
+    assert attrs["displayWindow"] == attrs["dataWindow"] and attrs["pixelAspectRatio"][1] == struct.pack("<f", 1.0)
+    ch, c, names, types = attrs["channels"][1], 0, [], []
+    while ch[c] != 0:
+        e = ch.index(b"\0", c); names.append(ch[c:e].decode()); t, lin, xs, ys = struct.unpack_from("<iB3xii", ch, e + 1); types.append(t); assert (xs, ys) == (1, 1); c = e + 17
+    assert names == sorted(names) == ["B", "G", "R"] and len(set(types)) == 1 and types[0] in (1, 2)
+    dt = np.dtype("<f2") if types[0] == 1 else np.dtype("<f4"); row = w * 3 * dt.itemsize
+    offs = struct.unpack_from(f"<{h}Q", b, o); assert o + 8 * h == offs[0] and len(b) == offs[0] + h * (8 + row)
+    img = np.zeros((h, w, 3), dt)
+    for y in range(h):
+        yy, n = struct.unpack_from("<ii", b, offs[y]); assert (yy, n) == (y, row)
+        img[y] = np.frombuffer(b, dt, 3 * w, offs[y] + 8).reshape(3, w)[::-1].T          # file order B, G, R
+    return img
+
+
+def test_exr_output_half_and_float_quilt_and_views(scenes, gpu, tmp_path):
+    """HDRFilm::write (file_format = openexr, hdrfilm.cpp:420-560): float32 holds the developed film bit for bit; float16 (the film's
+    default component_format) is its round-to-nearest-even conversion; view >= 0 cuts that view's tile."""
+    s = scenes.build(scenes.cornell_box(grid_x=3, grid_y=2, view_res=40, sample_count=4), device=gpu)
+    img = s.render(seed=2, spp=4)
+    s.write_exr(tmp_path / "q32.exr", component_format="float32"); got = _read_exr(tmp_path / "q32.exr")
+    assert got.dtype == np.float32; assert_bits(got.reshape(-1, 3), img.reshape(-1, 3), "quilt exr f32")
+    s.write_exr(tmp_path / "q16.exr"); got = _read_exr(tmp_path / "q16.exr")
+    assert got.dtype == np.float16 and np.array_equal(got.view(np.uint16), img.astype(np.float16).view(np.uint16))
+    for x0, y0, w, h, v in s.shard_tiles(0, 1):
+        s.write_exr(tmp_path / f"v{v}.exr", view=v)
+        assert np.array_equal(_read_exr(tmp_path / f"v{v}.exr").view(np.uint16), img[y0:y0 + h, x0:x0 + w].astype(np.float16).view(np.uint16))
+    # the conversion at its edges: film_add puts chosen values into the film (weight 1 -> develop returns them unchanged)
+    i = s.info(); n = i["film_h"] * i["film_w"] * 3
+    edge = np.array([0.0, -0.0, 65504.0, 65519.99, 65520.0, 1e9, np.inf, -np.inf, 2.0 ** -24, 2.0 ** -25, 2.0 ** -25 * 1.0001, 2.0 ** -14, 2.0 ** -14 * 0.9999,
+                     6.1e-5, 1.0009765625, 1.00048828125, 1.00146484375, 0.333333, -2.7182817, 1023.75, 2047.5, 5.9e-8, 3e-8, 1e-10], np.float32)
+    vals = np.resize(np.concatenate([edge, np.random.default_rng(5).standard_normal(4096).astype(np.float32) * np.float32(100.0),
+                                     np.exp(np.random.default_rng(6).uniform(-20, 12, 4096)).astype(np.float32)]), n).reshape(i["film_h"], i["film_w"], 3)
+    film = np.concatenate([vals, np.ones_like(vals[..., :1])], axis=-1)
+    s.film_clear(); s.film_add(film); dev = s.develop(); assert_bits(dev.reshape(-1, 3), vals.reshape(-1, 3), "film_add round trip")
+    s.write_exr(tmp_path / "edge.exr"); got = _read_exr(tmp_path / "edge.exr")
+    with np.errstate(over="ignore"):
+        want = vals.astype(np.float16)
+    assert np.array_equal(got.view(np.uint16), want.view(np.uint16))
+    with pytest.raises(Exception, match="out of range"):
+        s.write_exr(tmp_path / "x.exr", view=6)
+    with pytest.raises(ValueError):
+        s.write_exr(tmp_path / "x.exr", component_format="uint32")
+
+
 def test_pfm_output_quilt_and_per_view_split(scenes, gpu, tmp_path):
     """HDRFilm::write (file_format = pfm): the file holds the developed film bit for bit, bottom row first; view >= 0 cuts that view's tile."""
     s = scenes.build(scenes.cornell_box(grid_x=3, grid_y=2, view_res=40, sample_count=4), device=gpu)
@@ -562,17 +617,31 @@ def test_interlace_bit_exact(mode, scenes, ob, gpu):
         s.interlace(preset, dst[0], 1, ch)
 
 
+def test_cli_default_output_is_half_float_exr(pkg, scenes, gpu, tmp_path):
+    """`-o img.exr` (and no -o at all) writes OpenEXR with float16 components as the reference's hdrfilm does by default."""
+    import subprocess, sys
+    desc = scenes.cornell_box(grid_x=2, grid_y=1, view_res=24, sample_count=2)
+    xml = scenes.export_xml(desc, str(tmp_path))
+    r = subprocess.run([sys.executable, "-m", "mitsuba3-amvpt_b200", str(xml), "-n", "2", "--views"], cwd=ROOT, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    out = os.path.splitext(str(xml))[0] + ".exr"; assert out in r.stdout
+    s = scenes.build(desc, device=gpu); img = s.render(seed=0, spp=2)
+    assert np.array_equal(_read_exr(out).view(np.uint16), img.astype(np.float16).view(np.uint16))
+    for x0, y0, w, h, v in s.shard_tiles(0, 1):
+        assert np.array_equal(_read_exr(os.path.splitext(out)[0] + f"_v{v}.exr").view(np.uint16), img[y0:y0 + h, x0:x0 + w].astype(np.float16).view(np.uint16))
+
+
 def test_cli_renders_writes_pfm_views_and_interlace(pkg, scenes, gpu, tmp_path):
-    """`python -m mitsuba3-amvpt_b200 scene.xml -n 4 -o out.exr --views --interlace W H` = render_internal of the reference's CLI
+    """`python -m mitsuba3-amvpt_b200 scene.xml -n 4 -o out.pfm --views --interlace W H` = render_internal of the reference's CLI
     (src/mitsuba/mitsuba_render.cpp:105-133): render with seed 0, then film->write -- same bits as the API calls."""
     import subprocess, sys
     desc = scenes.cornell_box(grid_x=2, grid_y=2, view_res=32, sample_count=4)
     xml = scenes.export_xml(desc, str(tmp_path))
-    out = tmp_path / "img.exr"
+    out = tmp_path / "img.pfm"
     r = subprocess.run([sys.executable, "-m", "mitsuba3-amvpt_b200", str(xml), "-n", "4", "-o", str(out), "--views", "--interlace", "96", "64"],
                        cwd=ROOT, capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stderr
-    assert "Rendering finished." in r.stdout and "img.pfm" in r.stdout and "OpenEXR output is unavailable" in r.stdout
+    assert "Rendering finished." in r.stdout and "img.pfm" in r.stdout
     s = scenes.build(desc, device=gpu); img = s.render(seed=0, spp=4)
     assert_bits(_read_pfm(tmp_path / "img.pfm").reshape(-1, 3), img.reshape(-1, 3), "CLI quilt")
     for x0, y0, w, h, v in s.shard_tiles(0, 1):
