@@ -137,7 +137,7 @@ int amvpt_film_add_host(amvpt_scene *s, const float *rgbw_host);         /* Imag
 /* HDRFilm::write with file_format = pfm (hdrfilm.cpp:420-560 -> Bitmap::write_pfm, src/core/bitmap.cpp:2270-2299): the developed
  * quilt (view < 0) or one view's tile of it (the per-view split of the reference's to_gif.py), RGB float32, bottom row first */
 int amvpt_film_write_pfm(amvpt_scene *s, const char *path, int32_t view);
-/* HDRFilm::write with file_format = openexr (hdrfilm.cpp:420-560 -> Bitmap::write_openexr, src/core/bitmap.cpp:1268-1420): same
+/* HDRFilm::write with file_format = openexr (hdrfilm.cpp:420-560 -> Bitmap::write_exr, src/core/bitmap.cpp:1332-1440): same
  * image and view selection as above, channels R G B, half_float != 0 stores float16 (hdrfilm's default component_format,
  * hdrfilm.cpp:146-147, 191-192; round to nearest even), 0 stores float32.  The OpenEXR library is not in this tree, so the file is
  * written directly as a single-part scan-line OpenEXR 2 file with NO_COMPRESSION (the reference compresses with PIZ,
