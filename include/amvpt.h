@@ -125,6 +125,10 @@ int amvpt_render(amvpt_scene *s, const amvpt_render_desc *d, amvpt_render_stats 
 /* rectangles of the quilt that `rank` of `world` renders (view sharding, build-defined): fills up to `cap`
  * records of 5 uint32 {x0, y0, w, h, view} and returns the number of rectangles */
 int amvpt_shard_tiles(amvpt_scene *s, uint32_t rank, uint32_t world, uint32_t *out5, uint32_t cap);
+/* the rectangle of every view (sub-sensor) in the quilt, ordered by view index = ix + grid_x * iy with the tile position following
+ * GridSensor::sample_ray's axis reversal (src/sensors/grid.cpp:246-255): same 5-uint32 records, returns their number.  This is
+ * the per-view split amvpt_film_write_pfm / _exr(view) cut by */
+int amvpt_view_tiles(amvpt_scene *s, uint32_t *out5, uint32_t cap);
 int amvpt_cancel(amvpt_scene *s);                                        /* Integrator::cancel (integrator.h:303-306) */
 int amvpt_film_clear(amvpt_scene *s);                                    /* Film::prepare / clear (hdrfilm.cpp:245-273) */
 int amvpt_film_raw(amvpt_scene *s, float *rgbw_host);                    /* film storage, H*W*4 floats to host */

@@ -76,7 +76,7 @@ EXPORTS = ["amvpt_last_error", "amvpt_device_count", "amvpt_scene_create", "amvp
            "amvpt_scene_from_xml_string", "amvpt_scene_add_bsdf", "amvpt_scene_add_mesh", "amvpt_scene_set_sensor_grid",
            "amvpt_scene_set_sensor_batch", "amvpt_scene_set_integrator", "amvpt_scene_set_rfilter", "amvpt_scene_set_reuse", "amvpt_scene_commit", "amvpt_scene_info",
            "amvpt_scene_get_sensor", "amvpt_scene_get_bsdf_tables", "amvpt_scene_counts", "amvpt_scene_get_mesh",
-           "amvpt_scene_get_bsdf", "amvpt_scene_get_integrator", "amvpt_render", "amvpt_shard_tiles", "amvpt_cancel", "amvpt_film_clear",
+           "amvpt_scene_get_bsdf", "amvpt_scene_get_integrator", "amvpt_render", "amvpt_shard_tiles", "amvpt_view_tiles", "amvpt_cancel", "amvpt_film_clear",
            "amvpt_film_raw", "amvpt_film_develop", "amvpt_film_develop_device", "amvpt_film_device_ptr", "amvpt_film_add_host",
            "amvpt_trace_lanes", "amvpt_trace_lanes_multi", "amvpt_intersect", "amvpt_bsdf_eval_pdf_sample", "amvpt_math1", "amvpt_sampler_stream",
            "amvpt_bvh_validate", "amvpt_film_write_pfm", "amvpt_film_write_exr", "amvpt_f32_to_f16", "amvpt_film_to_srgb8", "amvpt_interlace", "amvpt_display_last_ms"]
@@ -271,6 +271,12 @@ class Scene:
         """Rectangles (x0, y0, w, h, view) of the quilt that `rank` of `world` renders."""
         buf = np.zeros((4096, 5), np.uint32)
         n = _chk(lib.amvpt_shard_tiles(self._h, C.c_uint32(rank), C.c_uint32(world), _p(buf, u32p), C.c_uint32(len(buf))))
+        return buf[:n].copy()
+
+    def view_tiles(self):
+        """Rectangle (x0, y0, w, h, view) of every view of the quilt, by view index (the per-view split of write_pfm / write_exr)."""
+        buf = np.zeros((65536, 5), np.uint32)
+        n = _chk(lib.amvpt_view_tiles(self._h, _p(buf, u32p), C.c_uint32(len(buf))))
         return buf[:n].copy()
 
     def film_clear(self):

@@ -68,10 +68,10 @@ def main(argv=None):
         write(out)
         print(f"Writing \"{out}\"" + (" (extension replaced by .exr)" if note else ""))
         if a.views:
-            for *_, v in s.shard_tiles(0, 1):
+            for *_, v in s.view_tiles():
                 write(f"{root}_v{int(v)}{ext}", view=int(v))
         if a.interlace:
-            s.to_srgb8(fetch=False); tiles = s.shard_tiles(0, 1)      # the grid of the quilt from its view rectangles
+            s.to_srgb8(fetch=False); tiles = s.view_tiles()           # the grid of the quilt from its view rectangles
             gx, gy = len({int(r[0]) for r in tiles}), len({int(r[1]) for r in tiles})
             img = s.interlace(dict(center=-0.5, focus=-0.05, pitch=354.548, tilt=-0.114, subp=0.00013, view=(1.0, 1.0), grid=(gx, gy)), a.interlace[0], a.interlace[1], 3)
             with open(os.path.splitext(out)[0] + "_interlaced.ppm", "wb") as f:

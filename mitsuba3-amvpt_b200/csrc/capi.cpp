@@ -186,6 +186,12 @@ int amvpt_shard_tiles(amvpt_scene *h, uint32_t rank, uint32_t world, uint32_t *o
         for (size_t i = 0; i < t.size() && i < cap && out5; ++i) { uint32_t *o = out5 + 5 * i; o[0] = t[i].x0; o[1] = t[i].y0; o[2] = t[i].w; o[3] = t[i].h; o[4] = t[i].pad; }
         return (int) t.size(); });
 }
+int amvpt_view_tiles(amvpt_scene *h, uint32_t *out5, uint32_t cap) {
+    return guard([&] { NEED(h); if (h->s->sensors.empty()) AM_THROW("no sensor");
+        Shard all; std::vector<TileDesc> t = h->s->view_tiles(all);
+        for (size_t i = 0; i < t.size() && i < cap && out5; ++i) { uint32_t *o = out5 + 5 * i; o[0] = t[i].x0; o[1] = t[i].y0; o[2] = t[i].w; o[3] = t[i].h; o[4] = t[i].pad; }
+        return (int) t.size(); });
+}
 int amvpt_cancel(amvpt_scene *h) { return guard([&] { NEED(h); h->s->stop = true; return AMVPT_OK; }); }
 int amvpt_film_clear(amvpt_scene *h) { return guard([&] { Scene &s = committed(h); s.film_clear(nullptr); AM_CUDA(cudaDeviceSynchronize()); return AMVPT_OK; }); }
 int amvpt_film_raw(amvpt_scene *h, float *rgbw) {
@@ -252,7 +258,7 @@ static Developed develop_view(Scene &s, int32_t view, const char *who) {
     d.rgb.resize(npix * 3); AM_CUDA(cudaMemcpy(d.rgb.data(), s.rgb, npix * 3 * sizeof(float), cudaMemcpyDeviceToHost));
     d.w = d.stride = s.film_w; d.h = s.film_h;
     if (view >= 0) {
-        Shard sh; std::vector<TileDesc> t = rank_tiles(s, sh, false); bool found = false;
+        Shard all; std::vector<TileDesc> t = s.view_tiles(all); bool found = false;      // one rectangle per sub-sensor, pad = view index
         for (auto &r : t) if ((int32_t) r.pad == view) { d.x0 = r.x0; d.y0 = r.y0; d.w = r.w; d.h = r.h; found = true; break; }
         if (!found) AM_THROW("%s: view %d out of range (%zu views)", who, view, t.size());
     }

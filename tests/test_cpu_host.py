@@ -181,3 +181,19 @@ def test_exr_half_conversion_is_round_to_nearest_even(pkg):
         want = cases.astype(np.float16).view(np.uint16)
     assert np.array_equal(pkg.f32_to_f16(cases), want)
     assert pkg.f32_to_f16(np.zeros(0, np.float32)).size == 0
+
+
+def test_view_tiles_are_the_per_view_split_of_the_quilt(pkg, scenes):
+    """amvpt_view_tiles: one rectangle per sub-sensor, view indices 0..n-1 in order, disjoint cover of the quilt, and the same
+    rectangles the view sharding hands out when there are as many ranks as views."""
+    for gx, gy, res in ((2, 2, 32), (3, 2, 40), (1, 1, 16), (8, 1, 8)):
+        s = scenes.build(scenes.cornell_box(grid_x=gx, grid_y=gy, view_res=res), commit=False)
+        t = s.view_tiles(); n = gx * gy
+        assert t.shape == (n, 5) and t[:, 4].tolist() == list(range(n))
+        cover = np.zeros((gy * res, gx * res), np.int32)
+        for x0, y0, w, h, v in t:
+            assert (w, h) == (res, res); cover[y0:y0 + h, x0:x0 + w] += 1
+        assert (cover == 1).all()
+        if n > 1:
+            sharded = sorted(tuple(int(x) for x in r) for rank in range(n) for r in s.shard_tiles(rank, n))
+            assert sharded == sorted(tuple(int(x) for x in r) for r in t)

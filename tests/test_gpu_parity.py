@@ -550,7 +550,8 @@ def test_exr_output_half_and_float_quilt_and_views(scenes, gpu, tmp_path):
     assert got.dtype == np.float32; assert_bits(got.reshape(-1, 3), img.reshape(-1, 3), "quilt exr f32")
     s.write_exr(tmp_path / "q16.exr"); got = _read_exr(tmp_path / "q16.exr")
     assert got.dtype == np.float16 and np.array_equal(got.view(np.uint16), img.astype(np.float16).view(np.uint16))
-    for x0, y0, w, h, v in s.shard_tiles(0, 1):
+    tiles = s.view_tiles(); assert sorted(int(t[4]) for t in tiles) == list(range(6))
+    for x0, y0, w, h, v in tiles:
         s.write_exr(tmp_path / f"v{v}.exr", view=v)
         assert np.array_equal(_read_exr(tmp_path / f"v{v}.exr").view(np.uint16), img[y0:y0 + h, x0:x0 + w].astype(np.float16).view(np.uint16))
     # the conversion at its edges: film_add puts chosen values into the film (weight 1 -> develop returns them unchanged)
@@ -576,7 +577,8 @@ def test_pfm_output_quilt_and_per_view_split(scenes, gpu, tmp_path):
     s = scenes.build(scenes.cornell_box(grid_x=3, grid_y=2, view_res=40, sample_count=4), device=gpu)
     img = s.render(seed=2, spp=4)
     s.write_pfm(tmp_path / "quilt.pfm"); assert_bits(_read_pfm(tmp_path / "quilt.pfm").reshape(-1, 3), img.reshape(-1, 3), "quilt pfm")
-    for x0, y0, w, h, v in s.shard_tiles(0, 1):
+    tiles = s.view_tiles(); assert sorted(int(t[4]) for t in tiles) == list(range(6))
+    for x0, y0, w, h, v in tiles:
         s.write_pfm(tmp_path / f"v{v}.pfm", view=v)
         assert_bits(_read_pfm(tmp_path / f"v{v}.pfm").reshape(-1, 3), img[y0:y0 + h, x0:x0 + w].reshape(-1, 3), f"view {v} pfm")
     with pytest.raises(Exception, match="out of range"):
@@ -627,7 +629,8 @@ def test_cli_default_output_is_half_float_exr(pkg, scenes, gpu, tmp_path):
     out = os.path.splitext(str(xml))[0] + ".exr"; assert out in r.stdout
     s = scenes.build(desc, device=gpu); img = s.render(seed=0, spp=2)
     assert np.array_equal(_read_exr(out).view(np.uint16), img.astype(np.float16).view(np.uint16))
-    for x0, y0, w, h, v in s.shard_tiles(0, 1):
+    tiles = s.view_tiles(); assert sorted(int(t[4]) for t in tiles) == list(range(2))
+    for x0, y0, w, h, v in tiles:
         assert np.array_equal(_read_exr(os.path.splitext(out)[0] + f"_v{v}.exr").view(np.uint16), img[y0:y0 + h, x0:x0 + w].astype(np.float16).view(np.uint16))
 
 
@@ -644,7 +647,8 @@ def test_cli_renders_writes_pfm_views_and_interlace(pkg, scenes, gpu, tmp_path):
     assert "Rendering finished." in r.stdout and "img.pfm" in r.stdout
     s = scenes.build(desc, device=gpu); img = s.render(seed=0, spp=4)
     assert_bits(_read_pfm(tmp_path / "img.pfm").reshape(-1, 3), img.reshape(-1, 3), "CLI quilt")
-    for x0, y0, w, h, v in s.shard_tiles(0, 1):
+    tiles = s.view_tiles(); assert sorted(int(t[4]) for t in tiles) == list(range(4))
+    for x0, y0, w, h, v in tiles:
         assert_bits(_read_pfm(tmp_path / f"img_v{v}.pfm").reshape(-1, 3), img[y0:y0 + h, x0:x0 + w].reshape(-1, 3), f"CLI view {v}")
     s.to_srgb8(fetch=False); want = s.interlace(dict(LKG4x8, grid=(2, 2)), 96, 64, 3)
     ppm = open(tmp_path / "img_interlaced.ppm", "rb").read()
