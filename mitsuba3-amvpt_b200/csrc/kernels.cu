@@ -20,7 +20,7 @@ namespace amvpt {
 //         camera rays and first-vertex light rays are the coherent third of all rays; traced there by a 10 KB kernel with
 //         full warps they cost a fraction of what they cost inside this loop.
 #ifndef AM_RP_MIN_CTAS
-#define AM_RP_MIN_CTAS 1
+#define AM_RP_MIN_CTAS 5      // 96 registers -> 5 CTAs per SM: same-box A/B 1690 vs 1566 Mpaths/s on the Cornell quilt (profiles/r01_ab_min_ctas.txt)
 #endif
 template <int MODE, bool STATS> __global__ void __launch_bounds__(128, AM_RP_MIN_CTAS)
 render_pass_kernel(const DScene s, const RenderParams p) {
