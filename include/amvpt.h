@@ -174,6 +174,10 @@ int amvpt_bsdf_eval_pdf_sample(amvpt_scene *s, int bsdf, const float *wi, const 
                                float *f, float *pdf, float *bs_wo, float *bs_pdf, float *bs_eta, uint32_t *bs_type, float *weight);
 int amvpt_math1(int device, int op, const float *in, uint32_t n, float *out);
 int amvpt_sampler_stream(int device, uint32_t seed_value, uint32_t lane, uint32_t n, float *out);
+/* memory-system micro-benchmark used by bench.py for the L2 line of the roofline ("L2 bandwidth to be measured by
+ * a builder micro-benchmark"): kind 0 = every thread streams 16-byte ld.global.cg loads over a zero-filled buffer of `bytes`,
+ * `iters` times after a warm-up sweep; returns GB/s.  bytes well below the 126 MB L2 -> L2 read bandwidth, several L2 sizes -> HBM */
+int amvpt_membench(int device, int kind, uint64_t bytes, uint32_t iters, double *gb_per_s);
 /* host-side checks of the BVH the kernels traverse: every triangle inside its leaf box, every child box inside its parent */
 int amvpt_bvh_validate(amvpt_scene *s, uint32_t *max_depth, uint32_t *n_leaves);
 

@@ -79,7 +79,7 @@ EXPORTS = ["amvpt_last_error", "amvpt_device_count", "amvpt_scene_create", "amvp
            "amvpt_scene_get_bsdf", "amvpt_scene_get_integrator", "amvpt_render", "amvpt_shard_tiles", "amvpt_view_tiles", "amvpt_cancel", "amvpt_film_clear",
            "amvpt_film_raw", "amvpt_film_develop", "amvpt_film_develop_device", "amvpt_film_device_ptr", "amvpt_film_add_host",
            "amvpt_trace_lanes", "amvpt_trace_lanes_multi", "amvpt_intersect", "amvpt_bsdf_eval_pdf_sample", "amvpt_math1", "amvpt_sampler_stream",
-           "amvpt_bvh_validate", "amvpt_film_write_pfm", "amvpt_film_write_exr", "amvpt_f32_to_f16", "amvpt_film_to_srgb8", "amvpt_interlace", "amvpt_display_last_ms"]
+           "amvpt_bvh_validate", "amvpt_membench", "amvpt_film_write_pfm", "amvpt_film_write_exr", "amvpt_f32_to_f16", "amvpt_film_to_srgb8", "amvpt_interlace", "amvpt_display_last_ms"]
 lib.amvpt_scene_destroy.restype = None
 lib.amvpt_scene_destroy.argtypes = [C.c_void_p]
 
@@ -381,6 +381,11 @@ def f32_to_f16(x):
     """Float32 -> float16 bits as write_exr stores them (Struct conversion to Float16 for hdrfilm's component_format = float16)."""
     x = np.ascontiguousarray(x, np.float32); out = np.empty(x.shape, np.uint16)
     _chk(lib.amvpt_f32_to_f16(_p(x), out.ctypes.data_as(C.c_void_p), C.c_uint64(x.size))); return out
+
+
+def membench(bytes, iters=20, device=0, kind=0):
+    """GB/s of 16-byte loads over a buffer of `bytes` (L2 when it fits, else HBM); bench.py's L2 roofline denominator."""
+    out = C.c_double(); _chk(lib.amvpt_membench(C.c_int(device), C.c_int(kind), C.c_uint64(bytes), C.c_uint32(iters), C.byref(out))); return out.value
 
 
 def device_count():

@@ -390,6 +390,14 @@ int amvpt_sampler_stream(int device, uint32_t seed_value, uint32_t lane, uint32_
         launch_sampler_tap(seed_value, lane, n, b.as<float>(), nullptr); AM_CUDA(cudaGetLastError()); AM_CUDA(cudaDeviceSynchronize()); b.down(out, (size_t) n * 4); return AMVPT_OK; });
 }
 // Host-side structural check of the tree that was uploaded (no GPU work): containment of triangles and child boxes.
+int amvpt_membench(int device, int kind, uint64_t bytes, uint32_t iters, double *gb_per_s) {
+    return guard([&] { NEED(gb_per_s); need_device(device);
+        if (kind != 0) AM_THROW("amvpt_membench: unknown kind %d (0 = 16-byte reads)", kind);
+        int sms = 148; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+        const double v = run_membench_read((size_t) bytes, iters, sms, nullptr);
+        if (v < 0.0) AM_THROW("CUDA error: membench failed (%s)", cudaGetErrorString(cudaGetLastError()));
+        *gb_per_s = v; return AMVPT_OK; });
+}
 int amvpt_bvh_validate(amvpt_scene *h, uint32_t *max_depth, uint32_t *n_leaves) {
     return guard([&] { NEED(h); Scene &s = *h->s; s.prepare_host();
         struct B { float lo[3], hi[3]; };

@@ -387,4 +387,35 @@ __global__ void l2_flush_kernel(float *buf, size_t n) {
 }
 void launch_l2_flush(float *buf, size_t n, cudaStream_t st) { if (n) l2_flush_kernel<<<148 * 8, 256, 0, st>>>(buf, n); }
 
+// Memory-system micro-benchmark behind amvpt_membench (SURVEY.md sec.8d asks for a measured L2 figure next to the driver's HBM
+// copy figure): every thread streams 16-byte loads (ld.global.cg: L2, not L1) over the whole buffer `iters` times.  With a buffer
+// well below the 126 MB L2 the steady state is L2 read bandwidth; with a buffer of several L2 sizes it is HBM read bandwidth.
+__global__ void __launch_bounds__(256) membench_read_kernel(const float4 *__restrict__ buf, size_t n, uint32_t iters, float4 *sink) {
+    const size_t stride = (size_t) gridDim.x * blockDim.x, i0 = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (uint32_t it = 0; it < iters; ++it) {
+        size_t i = i0;
+        for (; i + 3 * stride < n; i += 4 * stride) {      // four independent loads in flight per thread
+            const float4 a = __ldcg(buf + i), b = __ldcg(buf + i + stride), c = __ldcg(buf + i + 2 * stride), d = __ldcg(buf + i + 3 * stride);
+            acc.x += a.x + b.x; acc.y += a.y + b.y; acc.z += c.z + d.z; acc.w += c.w + d.w;
+        }
+        for (; i < n; i += stride) { const float4 a = __ldcg(buf + i); acc.x += a.x; acc.y += a.y; acc.z += a.z; acc.w += a.w; }
+    }
+    if (acc.x == 12345.678f && acc.y == 1.f) sink[0] = acc;    // keeps the loads alive; never true for the zero-filled buffer
+}
+double run_membench_read(size_t bytes, uint32_t iters, int sm_count, cudaStream_t st) {
+    const size_t n = bytes / sizeof(float4); if (!n || !iters) return 0.0;
+    float4 *buf = nullptr; if (cudaMalloc(&buf, n * sizeof(float4) + sizeof(float4)) != cudaSuccess) return -1.0;
+    cudaMemsetAsync(buf, 0, n * sizeof(float4) + sizeof(float4), st);
+    const unsigned grid = (unsigned) sm_count * 8u;
+    membench_read_kernel<<<grid, 256, 0, st>>>(buf, n, 2, buf + n);       // warm-up: fills L2 when the buffer fits
+    cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+    cudaEventRecord(e0, st);
+    membench_read_kernel<<<grid, 256, 0, st>>>(buf, n, iters, buf + n);
+    cudaEventRecord(e1, st); cudaEventSynchronize(e1);
+    float ms = 0.f; cudaEventElapsedTime(&ms, e0, e1);
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(buf);
+    return cudaGetLastError() == cudaSuccess && ms > 0.f ? (double) (n * sizeof(float4)) * iters / (ms * 1e-3) / 1e9 : -1.0;
+}
+
 } // namespace amvpt
