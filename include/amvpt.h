@@ -86,6 +86,13 @@ int amvpt_scene_add_bsdf(amvpt_scene *s, const amvpt_bsdf_desc *d);             
 /* Mesh (src/render/mesh.cpp) with optional vertex normals and optional area emitter radiance (src/emitters/area.cpp) */
 int amvpt_scene_add_mesh(amvpt_scene *s, const float *positions, uint32_t n_vertices, const uint32_t *faces, uint32_t n_faces,
                          const float *normals, int bsdf, const float *radiance, int flip_normals);   /* returns mesh index */
+/* emitters that are not attached to a shape, appended to the scene's emitter list in call order like Scene::Scene does
+ * (src/render/scene.cpp:22-63); each returns the emitter index.  PointLight (src/emitters/point.cpp:65-85), ConstantBackgroundEmitter
+ * (src/emitters/constant.cpp:55-68), EnvironmentMapEmitter (src/emitters/envmap.cpp:111-214: rgb = the bitmap as linear RGB float32,
+ * h rows of w pixels, top row first; to_world16 may be NULL = identity).  At most one environment emitter (constant or envmap) */
+int amvpt_scene_add_emitter_point(amvpt_scene *s, const float *position3, const float *intensity3);
+int amvpt_scene_add_emitter_constant(amvpt_scene *s, const float *radiance3);
+int amvpt_scene_add_emitter_envmap(amvpt_scene *s, const float *rgb, uint32_t w, uint32_t h, float scale, const float *to_world16);
 int amvpt_scene_set_sensor_grid(amvpt_scene *s, const amvpt_grid_sensor_desc *d);
 /* `batch` multi-sensor (src/sensors/batch.cpp:94-180): n explicit perspective sub-cameras, film = n*res_x by res_y */
 int amvpt_scene_set_sensor_batch(amvpt_scene *s, uint32_t n, uint32_t res_x, uint32_t res_y, const float *sample_to_camera,
@@ -106,6 +113,8 @@ int amvpt_scene_commit(amvpt_scene *s, int device);
 int amvpt_scene_info(amvpt_scene *s, uint32_t *film_w, uint32_t *film_h, uint32_t *n_views, uint32_t *n_prims,
                      uint32_t *n_bvh_nodes, uint32_t *sample_count);
 int amvpt_scene_get_sensor(amvpt_scene *s, uint32_t index, float *sample_to_camera16, float *to_world16);
+/* scalars4 = { near_clip, far_clip, aperture_radius, focus_distance } of sub-sensor `index`; layout5 = { grid_x, grid_y, reverse_x, reverse_y, thinlens } */
+int amvpt_scene_get_sensor_params(amvpt_scene *s, uint32_t index, float *scalars4, int32_t *layout5);
 int amvpt_scene_get_bsdf_tables(amvpt_scene *s, int bsdf, float *ext_transmittance64, float *scalars3);
 /* read-back of the host scene description (what the XML loader or the add_* calls produced; works before commit).
  * amvpt_scene_get_mesh: pass NULL buffers to query sizes first.  amvpt_scene_get_bsdf returns int_ior = int_ior / ext_ior, ext_ior = 1. */
@@ -113,6 +122,13 @@ int amvpt_scene_counts(amvpt_scene *s, uint32_t *n_meshes, uint32_t *n_bsdfs, ui
 int amvpt_scene_get_mesh(amvpt_scene *s, uint32_t index, uint32_t *n_vertices, uint32_t *n_faces, int32_t *bsdf, int32_t *has_normals,
                          int32_t *flip_normals, int32_t *is_emitter, float *radiance3, float *positions, uint32_t *faces, float *normals);
 int amvpt_scene_get_bsdf(amvpt_scene *s, int bsdf, amvpt_bsdf_desc *d);
+/* emitter `index` of the scene's emitter list: type 0 area (mesh = its shape), 1 point, 2 constant, 3 envmap */
+int amvpt_scene_get_emitter(amvpt_scene *s, uint32_t index, int32_t *type, int32_t *mesh, float *radiance3, float *position3);
+/* the environment map as loaded (rgb may be NULL to query the size), its scale and to_world; *w = 0 if the scene has none */
+int amvpt_scene_get_envmap(amvpt_scene *s, uint32_t *w, uint32_t *h, float *scale, float *to_world16, float *rgb);
+/* sensor flag that changes the sampler stream: 1 if every sample draws a shutter time (shutter_close > shutter_open, mvpath_single.h:66-68) */
+int amvpt_scene_get_shutter_draw(amvpt_scene *s, int32_t *draw);
+int amvpt_scene_set_shutter(amvpt_scene *s, float shutter_open, float shutter_close);
 int amvpt_scene_get_integrator(amvpt_scene *s, amvpt_integrator_desc *d, int32_t *is_mvpath, int32_t *sa_reuse, uint32_t *reuse_count);
 
 /* parity tap of the reuse branch: for lanes [lane_begin, lane_begin + n) the n_samples records of render_multisample, 9 floats
@@ -173,6 +189,14 @@ int amvpt_intersect(amvpt_scene *s, const float *o, const float *d, const float 
 int amvpt_bsdf_eval_pdf_sample(amvpt_scene *s, int bsdf, const float *wi, const float *wo, const float *s1, const float *s2, uint32_t n,
                                float *f, float *pdf, float *bs_wo, float *bs_pdf, float *bs_eta, uint32_t *bs_type, float *weight);
 int amvpt_math1(int device, int op, const float *in, uint32_t n, float *out);
+/* Hierarchical2D<Float, 0>::sample / eval of the scene's environment map on the device (include/mitsuba/core/distr_2d.h:490-575, 668-698):
+ * u = n x 2 uniform numbers -> uv (n x 2), pdf (n), and eval(uv) (n) */
+int amvpt_env_warp(amvpt_scene *s, const float *u, uint32_t n, float *uv, float *pdf, float *eval_back);
+/* host-side readers of the scene loader, exposed for the tests: Bitmap(path) -> linear RGB float32 (OpenEXR scan-line none / PIZ, PFM;
+ * rgb may be NULL to query the size), and <spectrum value="wavelength:value ..."> -> linear sRGB (src/core/spectrum.cpp:85-130 behind
+ * src/core/xml.cpp:1170-1268; n = 1 is the uniform case) */
+int amvpt_image_read(const char *path, uint32_t *w, uint32_t *h, float *rgb);
+int amvpt_spectrum_to_srgb(const double *wavelengths, const double *values, uint32_t n, int within_emitter, int unbounded_name, double *rgb3);
 int amvpt_sampler_stream(int device, uint32_t seed_value, uint32_t lane, uint32_t n, float *out);
 /* memory-system micro-benchmark used by bench.py for the L2 line of the roofline ("L2 bandwidth to be measured by
  * a builder micro-benchmark"): kind 0 = every thread streams 16-byte ld.global.cg loads over a zero-filled buffer of `bytes`,

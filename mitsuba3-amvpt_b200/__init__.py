@@ -74,7 +74,7 @@ class RenderStats(C.Structure):
 lib.amvpt_last_error.restype = C.c_char_p
 EXPORTS = ["amvpt_last_error", "amvpt_device_count", "amvpt_scene_create", "amvpt_scene_destroy", "amvpt_scene_from_xml",
            "amvpt_scene_from_xml_string", "amvpt_scene_add_bsdf", "amvpt_scene_add_mesh", "amvpt_scene_set_sensor_grid",
-           "amvpt_scene_set_sensor_batch", "amvpt_scene_set_integrator", "amvpt_scene_set_rfilter", "amvpt_scene_set_reuse", "amvpt_scene_commit", "amvpt_scene_info",
+           "amvpt_scene_set_sensor_batch", "amvpt_scene_add_emitter_point", "amvpt_scene_add_emitter_constant", "amvpt_scene_add_emitter_envmap", "amvpt_scene_get_emitter", "amvpt_scene_get_sensor_params", "amvpt_scene_get_envmap", "amvpt_scene_get_shutter_draw", "amvpt_scene_set_shutter", "amvpt_env_warp", "amvpt_image_read", "amvpt_spectrum_to_srgb", "amvpt_scene_set_integrator", "amvpt_scene_set_rfilter", "amvpt_scene_set_reuse", "amvpt_scene_commit", "amvpt_scene_info",
            "amvpt_scene_get_sensor", "amvpt_scene_get_bsdf_tables", "amvpt_scene_counts", "amvpt_scene_get_mesh",
            "amvpt_scene_get_bsdf", "amvpt_scene_get_integrator", "amvpt_render", "amvpt_shard_tiles", "amvpt_view_tiles", "amvpt_cancel", "amvpt_film_clear",
            "amvpt_film_raw", "amvpt_film_develop", "amvpt_film_develop_device", "amvpt_film_device_ptr", "amvpt_film_add_host",
@@ -149,6 +149,47 @@ class Scene:
         return _chk(lib.amvpt_scene_add_mesh(self._h, _p(pos), C.c_uint32(len(pos)), _p(fc, u32p), C.c_uint32(len(fc)), _p(nrm),
                                              C.c_int(bsdf), _p(rad), C.c_int(int(flip_normals))))
 
+    def add_emitter_point(self, position, intensity):
+        """PointLight (src/emitters/point.cpp): `position`, `intensity` (RGB)."""
+        return _chk(lib.amvpt_scene_add_emitter_point(self._h, _p(_f32(position, (3,))), _p(_f32(np.broadcast_to(np.asarray(intensity, np.float32), (3,))))))
+
+    def add_emitter_constant(self, radiance=1.0):
+        """ConstantBackgroundEmitter (src/emitters/constant.cpp)."""
+        return _chk(lib.amvpt_scene_add_emitter_constant(self._h, _p(_f32(np.broadcast_to(np.asarray(radiance, np.float32), (3,))))))
+
+    def add_emitter_envmap(self, rgb, scale=1.0, to_world=None):
+        """EnvironmentMapEmitter (src/emitters/envmap.cpp): rgb = (H, W, 3) linear radiance, latitude-longitude."""
+        img = _f32(rgb); h, w = img.shape[:2]; tw = None if to_world is None else _f32(to_world, (16,))
+        return _chk(lib.amvpt_scene_add_emitter_envmap(self._h, _p(img), C.c_uint32(w), C.c_uint32(h), C.c_float(scale), _p(tw)))
+
+    def set_shutter(self, shutter_open=0.0, shutter_close=0.0):
+        _chk(lib.amvpt_scene_set_shutter(self._h, C.c_float(shutter_open), C.c_float(shutter_close)))
+
+    def emitters(self):
+        """The scene's emitter list: dicts with type ('area' | 'point' | 'constant' | 'envmap'), mesh, radiance, position."""
+        out = []
+        for i in range(self.counts()["n_emitters"]):
+            t, m = C.c_int32(), C.c_int32(); rad = np.zeros(3, np.float32); pos = np.zeros(3, np.float32)
+            _chk(lib.amvpt_scene_get_emitter(self._h, C.c_uint32(i), C.byref(t), C.byref(m), _p(rad), _p(pos)))
+            out.append(dict(type=("area", "point", "constant", "envmap")[t.value], mesh=m.value, radiance=rad, position=pos))
+        return out
+
+    def envmap(self):
+        w, h, sc = C.c_uint32(), C.c_uint32(), C.c_float(); tw = np.zeros(16, np.float32)
+        _chk(lib.amvpt_scene_get_envmap(self._h, C.byref(w), C.byref(h), C.byref(sc), _p(tw), None))
+        if w.value == 0:
+            return None
+        rgb = np.zeros((h.value, w.value, 3), np.float32)
+        _chk(lib.amvpt_scene_get_envmap(self._h, C.byref(w), C.byref(h), C.byref(sc), _p(tw), _p(rgb)))
+        return dict(rgb=rgb, scale=sc.value, to_world=tw.reshape(4, 4))
+
+    def shutter_draw(self):
+        d = C.c_int32(); _chk(lib.amvpt_scene_get_shutter_draw(self._h, C.byref(d))); return bool(d.value)
+
+    def env_warp(self, u):
+        u = _f32(u, (-1, 2)); n = len(u); uv = np.zeros((n, 2), np.float32); pdf = np.zeros(n, np.float32); ev = np.zeros(n, np.float32)
+        _chk(lib.amvpt_env_warp(self._h, _p(u), C.c_uint32(n), _p(uv), _p(pdf), _p(ev))); return uv, pdf, ev
+
     def set_sensor_grid(self, grid_x, grid_y, res_x, res_y, to_world, fov, fov_axis="x", near_clip=1e-2, far_clip=1e4,
                         focus_distance=1.0, thinlens=False, aperture_radius=0.0, reverse_x=False, reverse_y=True, cone_deg=None,
                         cam_dir=(1., 0., 0.), cam_dist=None, cam_center=True, cam_off=(0., 0., 0.)):
@@ -207,6 +248,12 @@ class Scene:
         s2c = np.zeros(16, np.float32); tw = np.zeros(16, np.float32)
         _chk(lib.amvpt_scene_get_sensor(self._h, C.c_uint32(index), _p(s2c), _p(tw)))
         return s2c.reshape(4, 4), tw.reshape(4, 4)
+
+    def sensor_params(self, index=0):
+        sc = np.zeros(4, np.float32); lay = np.zeros(5, np.int32)
+        _chk(lib.amvpt_scene_get_sensor_params(self._h, C.c_uint32(index), _p(sc), lay.ctypes.data_as(C.POINTER(C.c_int32))))
+        return dict(near_clip=float(sc[0]), far_clip=float(sc[1]), aperture_radius=float(sc[2]), focus_distance=float(sc[3]),
+                    grid_x=int(lay[0]), grid_y=int(lay[1]), reverse_x=bool(lay[2]), reverse_y=bool(lay[3]), thinlens=bool(lay[4]))
 
     def bsdf_tables(self, bsdf):
         t = np.zeros(64, np.float32); s = np.zeros(3, np.float32)
@@ -386,6 +433,20 @@ def f32_to_f16(x):
 def membench(bytes, iters=20, device=0, kind=0):
     """GB/s of 16-byte loads over a buffer of `bytes` (L2 when it fits, else HBM); bench.py's L2 roofline denominator."""
     out = C.c_double(); _chk(lib.amvpt_membench(C.c_int(device), C.c_int(kind), C.c_uint64(bytes), C.c_uint32(iters), C.byref(out))); return out.value
+
+
+def image_read(path):
+    """Bitmap(path) -> linear RGB float32 (H, W, 3) through the scene loader's readers (OpenEXR scan-line none / PIZ, PFM)."""
+    w, h = C.c_uint32(), C.c_uint32(); _chk(lib.amvpt_image_read(str(path).encode(), C.byref(w), C.byref(h), None))
+    out = np.zeros((h.value, w.value, 3), np.float32); _chk(lib.amvpt_image_read(str(path).encode(), C.byref(w), C.byref(h), _p(out))); return out
+
+
+def spectrum_to_srgb(wavelengths, values, within_emitter=False, unbounded_name=False):
+    """<spectrum value="wavelength:value ..."> (or a single uniform value) -> linear sRGB as the XML loader converts it."""
+    wl = np.ascontiguousarray(wavelengths, np.float64); v = np.ascontiguousarray(values, np.float64); out = np.zeros(3, np.float64)
+    dp = C.POINTER(C.c_double)
+    _chk(lib.amvpt_spectrum_to_srgb(wl.ctypes.data_as(dp), v.ctypes.data_as(dp), C.c_uint32(len(v)), C.c_int(int(within_emitter)), C.c_int(int(unbounded_name)), out.ctypes.data_as(dp)))
+    return out
 
 
 def device_count():

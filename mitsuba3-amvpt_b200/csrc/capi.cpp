@@ -83,6 +83,64 @@ int amvpt_scene_add_mesh(amvpt_scene *h, const float *pos, uint32_t nv, const ui
         m.bsdf = bsdf; m.flip_normals = flip_normals;
         return h->s->add_mesh(std::move(m), radiance); });
 }
+int amvpt_scene_add_emitter_point(amvpt_scene *h, const float *position, const float *intensity) {
+    return guard([&] { NEED(h); NEED(position); NEED(intensity); return h->s->add_emitter_point(position, intensity); });
+}
+int amvpt_scene_add_emitter_constant(amvpt_scene *h, const float *radiance) {
+    return guard([&] { NEED(h); NEED(radiance); return h->s->add_emitter_constant(radiance); });
+}
+int amvpt_scene_add_emitter_envmap(amvpt_scene *h, const float *rgb, uint32_t w, uint32_t hh, float scale, const float *to_world16) {
+    return guard([&] { NEED(h); NEED(rgb); M4d tw = m4d_identity();
+        if (to_world16) for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) tw.m[i][j] = to_world16[4 * i + j];
+        return h->s->add_emitter_envmap(rgb, w, hh, scale, tw); });
+}
+int amvpt_scene_get_emitter(amvpt_scene *h, uint32_t index, int32_t *type, int32_t *mesh, float *radiance3, float *position3) {
+    return guard([&] { NEED(h); Scene &s = *h->s; if (index >= s.emitters.size()) AM_THROW("emitter index %u out of range", index);
+        const DEmitter &e = s.emitters[index]; if (type) *type = e.type; if (mesh) *mesh = e.mesh;
+        for (int k = 0; k < 3; ++k) { if (radiance3) radiance3[k] = e.radiance[k]; if (position3) position3[k] = e.position[k]; }
+        return AMVPT_OK; });
+}
+int amvpt_scene_get_envmap(amvpt_scene *h, uint32_t *w, uint32_t *hh, float *scale, float *to_world16, float *rgb) {
+    return guard([&] { NEED(h); NEED(w); NEED(hh); Scene &s = *h->s;
+        if (!s.env.present) { *w = *hh = 0; return AMVPT_OK; }
+        *w = s.env.src_w; *hh = s.env.src_h; if (scale) *scale = s.env.scale;
+        if (to_world16) std::memcpy(to_world16, s.env.to_world.m, 64);
+        if (rgb) std::memcpy(rgb, s.env.src_rgb.data(), s.env.src_rgb.size() * sizeof(float));
+        return AMVPT_OK; });
+}
+int amvpt_scene_get_sensor_params(amvpt_scene *h, uint32_t index, float *scalars4, int32_t *layout5) {
+    return guard([&] { NEED(h); Scene &s = *h->s; if (index >= s.sensors.size()) AM_THROW("sensor index %u out of range", index);
+        const DSensor &c = s.sensors[index];
+        if (scalars4) { scalars4[0] = c.near_clip; scalars4[1] = c.far_clip; scalars4[2] = c.aperture_radius; scalars4[3] = c.focus_distance; }
+        if (layout5) { layout5[0] = (int32_t) s.grid_x; layout5[1] = (int32_t) s.grid_y; layout5[2] = s.reverse_x; layout5[3] = s.reverse_y; layout5[4] = s.thinlens; }
+        return AMVPT_OK; });
+}
+int amvpt_scene_get_shutter_draw(amvpt_scene *h, int32_t *draw) { return guard([&] { NEED(h); NEED(draw); *draw = h->s->shutter_draw ? 1 : 0; return AMVPT_OK; }); }
+int amvpt_scene_set_shutter(amvpt_scene *h, float shutter_open, float shutter_close) {
+    return guard([&] { NEED(h); const float t = shutter_close - shutter_open;
+        if (t < 0.f) AM_THROW("Shutter opening time must be less than or equal to the shutter closing time!");
+        h->s->shutter_draw = t > 0.f; if (h->s->committed) h->s->d.shutter_draw = t > 0.f; return AMVPT_OK; });
+}
+int amvpt_image_read(const char *path, uint32_t *w, uint32_t *hh, float *rgb) {
+    return guard([&] { NEED(path); NEED(w); NEED(hh); std::vector<float> px; load_image_rgb(path, w, hh, px);
+        if (rgb) std::memcpy(rgb, px.data(), px.size() * sizeof(float)); return AMVPT_OK; });
+}
+int amvpt_spectrum_to_srgb(const double *wavelengths, const double *values, uint32_t n, int within_emitter, int unbounded_name, double *rgb3) {
+    return guard([&] { NEED(values); NEED(rgb3); NEED(n >= 1);
+        if (n == 1) { if (within_emitter && !unbounded_name) uniform_emitter_spectrum_to_srgb(values[0], rgb3); else rgb3[0] = rgb3[1] = rgb3[2] = values[0]; return AMVPT_OK; }
+        NEED(wavelengths);
+        spectrum_to_srgb(std::vector<double>(wavelengths, wavelengths + n), std::vector<double>(values, values + n), within_emitter != 0, unbounded_name != 0, rgb3);
+        return AMVPT_OK; });
+}
+int amvpt_env_warp(amvpt_scene *h, const float *u, uint32_t n, float *uv, float *pdf, float *eval_back) {
+    return guard([&] { Scene &s = committed(h); NEED(u); NEED(uv); NEED(pdf); NEED(eval_back);
+        if (!s.d.env_is_map) AM_THROW("amvpt_env_warp: the scene has no environment map");
+        DBuf du(sizeof(float) * 2 * n), dout(sizeof(float) * 4 * n); du.up(u, sizeof(float) * 2 * n);
+        launch_env_warp_tap(s.d, du.as<float>(), n, dout.as<float>(), nullptr); AM_CUDA(cudaDeviceSynchronize());
+        std::vector<float> out(4 * (size_t) n); dout.down(out.data(), sizeof(float) * 4 * n);
+        for (uint32_t i = 0; i < n; ++i) { uv[2 * i] = out[4 * i]; uv[2 * i + 1] = out[4 * i + 1]; pdf[i] = out[4 * i + 2]; eval_back[i] = out[4 * i + 3]; }
+        return AMVPT_OK; });
+}
 int amvpt_scene_set_sensor_grid(amvpt_scene *h, const amvpt_grid_sensor_desc *d) {
     return guard([&] { NEED(h); NEED(d);
         GridSensorParams g; g.thinlens = d->thinlens; g.fov_axis = d->fov_axis; g.grid_x = d->grid_x; g.grid_y = d->grid_y;

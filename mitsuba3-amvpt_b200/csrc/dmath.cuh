@@ -143,6 +143,44 @@ AM_HD float estrin12(float x, const float *c) {
     return fmadd(x8, q2, r0);
 }
 
+// generic form of math.h:26-41 estrin_impl (pairwise fmadd per level, an odd tail coefficient is carried up unchanged)
+template <int N> AM_HD float estrin_n(float x, const float *c) {
+    float v[N]; for (int i = 0; i < N; ++i) v[i] = c[i];
+    int n = N;
+    while (n > 1) {
+        const int n_fma = n / 2, n_rec = (n - 1) / 2;
+        for (int i = 0; i < n_fma; ++i) v[i] = fmadd(x, v[2 * i + 1], v[2 * i]);
+        if (n_rec == n_fma) v[n_rec] = v[n - 1];
+        n = n_rec + 1; x = x * x;
+    }
+    return v[0];
+}
+// math.h:458-510 acos (single precision branch) and array_router.h:1775 safe_acos
+AM_HD float acos_(float x) {
+    const float xa = fabs_(x), x2 = x * x;
+    const bool big = xa > 0.5f;
+    const float x1 = 0.5f * (1.f - xa), x3 = big ? x1 : x2, x4 = big ? fsqrt(x1) : xa;
+    const float c[5] = { 1.666675242e-1f, 7.4953002686e-2f, 4.5470025998e-2f, 2.4181311049e-2f, 4.2163199048e-2f };
+    float z1 = estrin_n<5>(x3, c);
+    z1 = fmadd(z1, x3 * x4, x4);
+    float z2 = z1 + z1;
+    z2 = x < 0.f ? AM_PI - z2 : z2;
+    const float z3 = (AM_PI * .5f) - copysign_(z1, x);
+    return big ? z2 : z3;
+}
+AM_HD float safe_acos_(float x) { return acos_(clip_(x, -1.f, 1.f)); }
+// math.h:512-597 atan2 (single precision branch: MiniMax fit of atan(sqrt(x)) / sqrt(x))
+AM_HD float atan2_(float y, float x) {
+    const float ax = fabs_(x), ay = fabs_(y), mn = min_(ay, ax), mx = max_(ax, ay), sm = fdiv(mn, mx), z = sm * sm;
+    const float c[7] = { 0.99999934166683966009f, -0.33326497518773606976f, 0.19881342388439013552f, -0.13486708938456973185f,
+                         0.083863120428809689910f, -0.037006525670417265220f, 0.0078613793713198150252f };
+    float t = estrin_n<7>(z, c) * sm;
+    t = ay > ax ? AM_PI * .5f - t : t;
+    t = x < 0.f ? AM_PI - t : t;
+    const float r = y < 0.f ? -t : t;
+    return mx != 0.f ? r : 0.f;
+}
+
 // math.h:76-175 detail::sincos (single precision branch)
 AM_HD void sincos_(float x, float *s_out, float *c_out) {
     float xa = fabs_(x);
@@ -289,6 +327,32 @@ AM_HD float square_to_cosine_hemisphere_pdf(V3 v) { return AM_INV_PI * v.z; }
 AM_HD V2 square_to_uniform_triangle(V2 u) {
     float t = safe_sqrt(1.f - u.x);
     return v2(1.f - t, t * u.y);
+}
+
+// warp.h:23, 250-255, 267-276
+AM_HD float circ_(float x) { return safe_sqrt(fnmadd(x, x, 1.f)); }
+AM_HD V3 square_to_uniform_sphere(V2 u) {
+    const float z = fnmadd(2.f, u.y, 1.f), r = circ_(z);
+    float s, c; sincos_(2.f * AM_PI * u.x, &s, &c);
+    return v3(r * c, r * s, z);
+}
+#define AM_INV_FOUR_PI 0.07957747154594766788f
+#define AM_INV_TWO_PI 0.15915494309189533577f
+// warp.h:446-453, 478-494, 515-521: importance sampling of a linear / bilinear interpolant
+AM_HD float interval_to_linear(float v0, float v1, float sample) {
+    const float r = fdiv(v0 - safe_sqrt(lerp_(sqr(v0), sqr(v1), sample)), v0 - v1);
+    return fabs_(v0 - v1) > 1e-4f * (v0 + v1) ? r : sample;
+}
+AM_HD V2 square_to_bilinear(float v00, float v10, float v01, float v11, V2 sample, float *pdf) {
+    const float r0 = v00 + v10, r1 = v01 + v11;
+    sample.y = interval_to_linear(r0, r1, sample.y);
+    const float c0 = lerp_(v00, v01, sample.y), c1 = lerp_(v10, v11, sample.y);
+    sample.x = interval_to_linear(c0, c1, sample.x);
+    *pdf = lerp_(c0, c1, sample.x);
+    return sample;
+}
+AM_HD float square_to_bilinear_pdf(float v00, float v10, float v01, float v11, V2 sample) {
+    return lerp_(lerp_(v00, v10, sample.x), lerp_(v01, v11, sample.x), sample.y);
 }
 
 // include/mitsuba/render/fresnel.h:30-73

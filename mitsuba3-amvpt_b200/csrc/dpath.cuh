@@ -16,10 +16,31 @@ struct PathState {
 struct TapCtx { uint32_t max_hits, n_iter; uint32_t *hit_prim; float *hit_t; };
 struct StatCtx { uint32_t closest, shadow, nodes, tris, vertices; };
 
-AM_D void path_init(PathState &ps, const Ray &ray) {
+AM_D void path_init(const DScene &s, PathState &ps, const Ray &ray) {
     ps.ray = ray; ps.throughput = v3(1.f); ps.result = v3(0.f); ps.prev_p = v3(0.f); ps.eta = 1.f; ps.prev_bsdf_pdf = 1.f;
-    ps.depth = 0; ps.prev_delta = true; ps.valid_ray = false;   // no environment emitter on this path (mvpath_single.h:98)
+    ps.depth = 0; ps.prev_delta = true;
+    ps.valid_ray = !s.hide_emitters && s.env_emitter >= 0;      // mvpath_single.h:98
     ps.active = true;
+}
+// Direct emission of one loop iteration (mvpath_single.h:148-163): the emitter of the intersected shape, or -- GEN only -- the
+// environment emitter when the ray left the scene (SurfaceInteraction::emitter, scene.h:647-657; DirectionSample(scene, si, prev_si),
+// records.h:172-179: d = -si.wi for an invalid interaction)
+template <bool GEN> AM_D void add_emission(const DScene &s, PathState &ps, const SI &si, const DMesh *mesh) {
+    if (si.valid && mesh->emitter >= 0) {
+        V3 rel = si.p - ps.prev_p; float dist = norm(rel); V3 d = rel / dist;
+        float em_pdf = 0.f;
+        if (!ps.prev_delta) em_pdf = pdf_emitter_direction(s, mesh, d, si.sh_n, dist);
+        float mis_bsdf = mis_weight(ps.prev_bsdf_pdf, em_pdf);
+        V3 le = select3(si.wi.z > 0.f && ps.prev_bsdf_pdf > 0.f, ld3(s.emitters[mesh->emitter].radiance));   // area.cpp:82-86
+        ps.result = fmadd(ps.throughput, le * mis_bsdf, ps.result);
+    } else if (GEN && !si.valid && s.env_emitter >= 0) {
+        const V3 d = ps.ray.d;
+        float em_pdf = 0.f;
+        if (!ps.prev_delta) em_pdf = env_pdf_direction(s, d) * rcp((float) s.n_emitters);      // scene.cpp:351-360
+        float mis_bsdf = mis_weight(ps.prev_bsdf_pdf, em_pdf);
+        V3 le = select3(ps.prev_bsdf_pdf > 0.f, env_eval(s, d));
+        ps.result = fmadd(ps.throughput, le * mis_bsdf, ps.result);
+    }
 }
 
 // Lane -> (pixel, sampler, camera ray): MVPT::render lane map (src/integrators/mvpath.cpp:174-190) and
@@ -33,9 +54,10 @@ AM_D void lane_setup(const DScene &s, uint32_t seed_value, uint32_t lane, uint32
     V2 adjusted = v2(fmadd(ls.spx, sx, -0.f * sx), fmadd(ls.spy, sy, -0.f * sy));
     V2 aperture = v2(.5f, .5f);
     if (s.thinlens) { aperture.x = ps.rng.next_f32(); aperture.y = ps.rng.next_f32(); }
+    if (s.shutter_draw) (void) ps.rng.next_f32();      // time = shutter_open + next_1d() * shutter_open_time (:66-68); the scene is static, the draw is what matters
     Ray ray = sensor_sample_ray(s, adjusted, aperture, &ls.view);
     if (aperture_out) *aperture_out = aperture;
-    path_init(ps, ray);
+    path_init(s, ps, ray);
     // ImageBlock::put, box filter (src/render/imageblock.cpp:210-233): pixel = floor(sample_pos)
     uint32_t ux = (uint32_t) (int32_t) floorf(ls.spx), uy = (uint32_t) (int32_t) floorf(ls.spy);
     ls.in_film = ux < s.film_w && uy < s.film_h;
@@ -145,26 +167,19 @@ AM_D void trav_begin(TravState &tv, const Ray &ray, bool any) {
 
 // Vertex work for a finished closest-hit ray.  Returns true if a shadow ray has to be traced before the next closest ray
 // (then *shadow holds it and sT / sV the parked operands of `result = fmadd(sT, sV, result)`).
-template <bool STATS, int TYPE = -1> AM_D bool shade_vertex(const DScene &s, PathState &ps, const Hit &h, Ray *shadow, V3 *sT, V3 *sV, StatCtx *st) {
+template <bool STATS, int TYPE = -1, bool GEN = false> AM_D bool shade_vertex(const DScene &s, PathState &ps, const Hit &h, Ray *shadow, V3 *sT, V3 *sV, StatCtx *st) {
     if (STATS) { st->closest++; st->vertices++; }
     const DMesh *mesh;
     SI si = make_si(s, ps.ray, h, &mesh);
-    if (si.valid && mesh->emitter >= 0) {
-        V3 rel = si.p - ps.prev_p; float dist = norm(rel); V3 d = rel / dist;
-        float em_pdf = 0.f;
-        if (!ps.prev_delta) em_pdf = pdf_emitter_direction(s, mesh, d, si.sh_n, dist);
-        float mis_bsdf = mis_weight(ps.prev_bsdf_pdf, em_pdf);
-        V3 le = select3(si.wi.z > 0.f && ps.prev_bsdf_pdf > 0.f, ld3(s.emitters[mesh->emitter].radiance));
-        ps.result = fmadd(ps.throughput, le * mis_bsdf, ps.result);
-    }
+    add_emission<GEN>(s, ps, si, mesh);
     bool active_next = (ps.depth + 1 < s.max_depth) && si.valid;
     if (!active_next) { ps.valid_ray = ps.valid_ray || si.valid; ps.active = false; return false; }
     const DBsdf &bsdf = s.bsdfs[mesh->bsdf];
     bool active_em = (bsdf.flags & L_SMOOTH) != 0;
     V2 es; es.x = ps.rng.next_f32(); es.y = ps.rng.next_f32();
-    DirectionSample ds; V3 em_weight = v3(0.f), wo = v3(0.f); ds.pdf = 0.f;
+    DirectionSample ds; V3 em_weight = v3(0.f), wo = v3(0.f); ds.pdf = 0.f; ds.delta = false;
     if (active_em) {
-        ds = sample_emitter_direction<true>(s, si, es, &em_weight, nullptr, nullptr, shadow);
+        ds = sample_emitter_direction<true, GEN>(s, si, es, &em_weight, nullptr, nullptr, shadow);
         if (STATS) st->shadow++;
         active_em = ds.pdf != 0.f;
         wo = si.to_local(ds.d);
@@ -172,7 +187,7 @@ template <bool STATS, int TYPE = -1> AM_D bool shade_vertex(const DScene &s, Pat
     float s1 = ps.rng.next_f32(); V2 s2; s2.x = ps.rng.next_f32(); s2.y = ps.rng.next_f32();
     BsdfResult br = bsdf_eval_pdf_sample_t<TYPE>(bsdf, si.wi, wo, s1, s2);
     if (active_em) {
-        float mis_em = mis_weight(ds.pdf, br.pdf);
+        float mis_em = (GEN && ds.delta) ? 1.f : mis_weight(ds.pdf, br.pdf);
         *sT = ps.throughput; *sV = br.f * em_weight * mis_em;
     }
     ps.ray = spawn_ray(si.p, si.n, si.to_world(br.bs.wo));
@@ -213,7 +228,7 @@ AM_NOINLINE DirectionSample emitter_call(const DScene &s, const SI &si, V2 u, V3
 // OUTLINE = true calls the out-of-line copies above instead of inlining ray caster, emitter sampler and BSDF dispatch.
 // FIRST = true: the camera ray's hit and the first vertex's light sample (with its visibility) were computed by
 // primary_vertex_kernel and are read from prim[i], prim[m + i], prim[2 m + i] instead of being traced here.
-template <bool TAP, bool STATS, bool OUTLINE = false, bool FIRST = false> AM_D void path_bounce(const DScene &s, PathState &ps, TapCtx *tap, StatCtx *st,
+template <bool TAP, bool STATS, bool OUTLINE = false, bool FIRST = false, bool GEN = false> AM_D void path_bounce(const DScene &s, PathState &ps, TapCtx *tap, StatCtx *st,
                                                                                              const float4 *prim = nullptr, uint32_t pm = 0, uint32_t pi = 0) {
     uint32_t *cn = STATS ? &st->nodes : nullptr, *ct = STATS ? &st->tris : nullptr;
     Hit h;
@@ -227,14 +242,7 @@ template <bool TAP, bool STATS, bool OUTLINE = false, bool FIRST = false> AM_D v
         tap->n_iter++;
     }
     // direct emission (:148-163); DirectionSample(scene, si, prev_si) records.h:141-149
-    if (si.valid && mesh->emitter >= 0) {
-        V3 rel = si.p - ps.prev_p; float dist = norm(rel); V3 d = rel / dist;
-        float em_pdf = 0.f;
-        if (!ps.prev_delta) em_pdf = pdf_emitter_direction(s, mesh, d, si.sh_n, dist);
-        float mis_bsdf = mis_weight(ps.prev_bsdf_pdf, em_pdf);
-        V3 le = select3(si.wi.z > 0.f && ps.prev_bsdf_pdf > 0.f, ld3(s.emitters[mesh->emitter].radiance));   // area.cpp:82-86
-        ps.result = fmadd(ps.throughput, le * mis_bsdf, ps.result);
-    }
+    add_emission<GEN>(s, ps, si, mesh);
     bool active_next = (ps.depth + 1 < s.max_depth) && si.valid;
     if (!active_next) {
         // the lane finishes this iteration (its six draws and the BSDF call are unobservable) and leaves the loop
@@ -246,10 +254,10 @@ template <bool TAP, bool STATS, bool OUTLINE = false, bool FIRST = false> AM_D v
     // emitter sampling (:179-201)
     bool active_em = (bsdf.flags & L_SMOOTH) != 0;
     V2 es; es.x = ps.rng.next_f32(); es.y = ps.rng.next_f32();
-    DirectionSample ds; V3 em_weight = v3(0.f), wo = v3(0.f); ds.pdf = 0.f;
+    DirectionSample ds; V3 em_weight = v3(0.f), wo = v3(0.f); ds.pdf = 0.f; ds.delta = false;
     if (active_em) {
         if (FIRST) { const float4 a = prim[(size_t) pm + pi], b = prim[2 * (size_t) pm + pi]; em_weight = v3(a.x, a.y, a.z); ds.pdf = a.w; ds.d = v3(b.x, b.y, b.z); }
-        else ds = OUTLINE ? emitter_call(s, si, es, &em_weight, STATS ? st : nullptr) : sample_emitter_direction<false>(s, si, es, &em_weight, cn, ct);
+        else ds = OUTLINE ? emitter_call(s, si, es, &em_weight, STATS ? st : nullptr) : sample_emitter_direction<false, GEN>(s, si, es, &em_weight, cn, ct);
         if (STATS) st->shadow++;
         active_em = ds.pdf != 0.f;
         wo = si.to_local(ds.d);
@@ -257,7 +265,7 @@ template <bool TAP, bool STATS, bool OUTLINE = false, bool FIRST = false> AM_D v
     float s1 = ps.rng.next_f32(); V2 s2; s2.x = ps.rng.next_f32(); s2.y = ps.rng.next_f32();
     BsdfResult br = OUTLINE ? bsdf_call(bsdf, si.wi, wo, s1, s2) : bsdf_eval_pdf_sample(bsdf, si.wi, wo, s1, s2);
     if (active_em) {
-        float mis_em = mis_weight(ds.pdf, br.pdf);
+        float mis_em = (GEN && ds.delta) ? 1.f : mis_weight(ds.pdf, br.pdf);
         ps.result = fmadd(ps.throughput, br.f * em_weight * mis_em, ps.result);
     }
     ps.ray = spawn_ray(si.p, si.n, si.to_world(br.bs.wo));

@@ -263,15 +263,92 @@ AM_D uint32_t distr_sample(const float *cdf, uint32_t n, float sum, float sample
     }
     return start;
 }
-struct DirectionSample { V3 p, n, d; float pdf, dist; };
-// Scene::sample_emitter_direction (src/render/scene.cpp:295-346) + sample_emitter (:223-246) +
-// AreaLight::sample_direction (src/emitters/area.cpp:116-167) + Shape::sample_direction
-// (src/render/shape.cpp:360-377) + Mesh::sample_position (src/render/mesh.cpp:764-818) + visibility test.
+struct DirectionSample { V3 p, n, d; float pdf, dist; bool delta; };
+
+// ---------------------------------------------------------------- emitters beyond area lights (GEN = true instantiations only)
+// Hierarchical2D<Float, 0> (include/mitsuba/core/distr_2d.h): Level::index :757-761, sample :490-575, eval :668-698
+AM_D uint32_t warp_level_index(uint32_t x, uint32_t y, uint32_t width) { return ((x & 1u) | (((x & ~1u) | (y & 1u)) << 1)) + (y & ~1u) * width; }
+AM_D float warp_lookup(const DScene &s, uint32_t level, uint32_t i) { return __ldg(s.env_warp + s.env_level_off[level] + i); }
+AM_D V2 env_warp_sample(const DScene &s, V2 sample, float *pdf) {
+    sample.x = clip_(sample.x, 0.f, 1.f); sample.y = clip_(sample.y, 0.f, 1.f);
+    uint32_t ox = 0, oy = 0;
+    for (int l = (int) s.env_n_levels - 2; l > 0; --l) {
+        ox <<= 1; oy <<= 1;
+        const uint32_t oi = warp_level_index(ox, oy, s.env_level_width[l]);
+        const float v00 = warp_lookup(s, l, oi), v10 = warp_lookup(s, l, oi + 1), v01 = warp_lookup(s, l, oi + 2), v11 = warp_lookup(s, l, oi + 3);
+        sample.x = clip_(sample.x, 0.f, 1.f); sample.y = clip_(sample.y, 0.f, 1.f);
+        const float r0 = v00 + v10, r1 = v01 + v11;
+        sample.y *= r0 + r1;
+        bool mask = sample.y > r0;
+        if (mask) { oy += 1u; sample.y -= r0; }
+        sample.y = fdiv(sample.y, mask ? r1 : r0);
+        const float c0 = mask ? v01 : v00, c1 = mask ? v11 : v10;
+        sample.x *= c0 + c1;
+        mask = sample.x > c0;
+        if (mask) sample.x -= c0;
+        sample.x = fdiv(sample.x, mask ? c1 : c0);
+        if (mask) ox += 1u;
+    }
+    const uint32_t width = s.env_level_width[0], oi = ox + oy * width;
+    const float v00 = warp_lookup(s, 0, oi), v10 = warp_lookup(s, 0, oi + 1), v01 = warp_lookup(s, 0, oi + width), v11 = warp_lookup(s, 0, oi + width + 1);
+    sample = square_to_bilinear(v00, v10, v01, v11, sample, pdf);
+    return v2(((float) (int32_t) ox + sample.x) * s.env_patch_size[0], ((float) (int32_t) oy + sample.y) * s.env_patch_size[1]);
+}
+AM_D float env_warp_eval(const DScene &s, V2 pos) {
+    pos.x = clip_(pos.x, 0.f, 1.f) * s.env_inv_patch_size[0]; pos.y = clip_(pos.y, 0.f, 1.f) * s.env_inv_patch_size[1];
+    const uint32_t ox = min((uint32_t) (int32_t) pos.x, s.env_max_patch[0]), oy = min((uint32_t) (int32_t) pos.y, s.env_max_patch[1]);
+    pos.x -= (float) (int32_t) ox; pos.y -= (float) (int32_t) oy;
+    const uint32_t width = s.env_level_width[0], oi = ox + oy * width;
+    const float v00 = warp_lookup(s, 0, oi), v10 = warp_lookup(s, 0, oi + 1), v01 = warp_lookup(s, 0, oi + width), v11 = warp_lookup(s, 0, oi + width + 1);
+    return square_to_bilinear_pdf(v00, v10, v01, v11, pos);
+}
+// EnvironmentMapEmitter::eval_spectrum (src/emitters/envmap.cpp:528-586, RGB branch): bilinear lookup, periodic in u
+AM_D V3 env_eval_uv(const DScene &s, V2 uv) {
+    uv.x -= fdiv(.5f, (float) (s.env_res_x - 1u));
+    uv.x -= floorf(uv.x); uv.y -= floorf(uv.y);
+    uv.x *= (float) (s.env_res_x - 1u); uv.y *= (float) (s.env_res_y - 1u);
+    const uint32_t px = min((uint32_t) uv.x, s.env_res_x - 2u), py = min((uint32_t) uv.y, s.env_res_y - 2u);
+    const float w1x = uv.x - (float) px, w1y = uv.y - (float) py, w0x = 1.f - w1x, w0y = 1.f - w1y;
+    const uint32_t width = s.env_res_x, index = py * width + px;
+    const float *d = s.env_data;
+    const V3 v00 = v3(__ldg(d + 3 * index), __ldg(d + 3 * index + 1), __ldg(d + 3 * index + 2)),
+             v10 = v3(__ldg(d + 3 * (index + 1)), __ldg(d + 3 * (index + 1) + 1), __ldg(d + 3 * (index + 1) + 2)),
+             v01 = v3(__ldg(d + 3 * (index + width)), __ldg(d + 3 * (index + width) + 1), __ldg(d + 3 * (index + width) + 2)),
+             v11 = v3(__ldg(d + 3 * (index + width + 1)), __ldg(d + 3 * (index + width + 1) + 1), __ldg(d + 3 * (index + width + 1) + 2));
+    const V3 v0 = fmadd(v00, w0x, v10 * w1x), v1 = fmadd(v01, w0x, v11 * w1x), v = fmadd(v0, w0y, v1 * w1y);
+    return v * s.env_scale;
+}
+// direction (world space, pointing away from the scene) -> latitude-longitude coordinates (envmap.cpp:313-318, 468-473)
+AM_D V2 env_dir_to_uv(const DScene &s, V3 d_world, V3 *d_local) {
+    const V3 v = xf_vector(s.env_from_world, d_world); *d_local = v;
+    return v2(atan2_(v.x, -v.z) * AM_INV_TWO_PI, safe_acos_(v.y) * AM_INV_PI);
+}
+// Emitter::eval for the environment emitter of the scene (constant.cpp:92-96, envmap.cpp:308-320); d = -si.wi = direction of the escaping ray
+AM_D V3 env_eval(const DScene &s, V3 d) {
+    if (!s.env_is_map) return ld3(s.emitters[s.env_emitter].radiance);
+    V3 local; const V2 uv = env_dir_to_uv(s, d, &local);
+    return env_eval_uv(s, uv);
+}
+#define AM_ENV_PDF_SCALE (1.f / (2.f * (AM_PI * AM_PI)))
+// Emitter::pdf_direction of the environment emitter (constant.cpp:152-157, envmap.cpp:464-481), without the emitter pmf
+AM_D float env_pdf_direction(const DScene &s, V3 d) {
+    if (!s.env_is_map) return AM_INV_FOUR_PI;
+    V3 v; V2 uv = env_dir_to_uv(s, d, &v);
+    uv.x -= fdiv(.5f, (float) (s.env_res_x - 1u));
+    uv.x -= floorf(uv.x); uv.y -= floorf(uv.y);
+    const float inv_sin_theta = rsqrt(max_(max_(sqr(v.x) + sqr(v.z), sqr(AM_EPSILON)), 0.f));
+    return env_warp_eval(s, uv) * inv_sin_theta * AM_ENV_PDF_SCALE;
+}
+
+// Scene::sample_emitter_direction (src/render/scene.cpp:295-346) + sample_emitter (:223-246) + the emitter's sample_direction:
+// AreaLight (src/emitters/area.cpp:116-167) + Shape::sample_direction (src/render/shape.cpp:360-377) + Mesh::sample_position
+// (src/render/mesh.cpp:764-818); with GEN also PointLight (point.cpp:117-148), ConstantBackgroundEmitter (constant.cpp:120-150) and
+// EnvironmentMapEmitter (envmap.cpp:419-462); then the visibility test.
 // DEFER = true leaves the visibility test to the caller: *shadow_out is the shadow ray to trace when the returned
 // ds.pdf != 0; an occluded sample then contributes nothing (the reference zeroes spec and ds.pdf, scene.cpp:333-342).
-template <bool DEFER> AM_D DirectionSample sample_emitter_direction(const DScene &s, const SI &ref, V2 sample, V3 *spec_out,
+template <bool DEFER, bool GEN = false> AM_D DirectionSample sample_emitter_direction(const DScene &s, const SI &ref, V2 sample, V3 *spec_out,
                                               uint32_t *n_nodes, uint32_t *n_tris, Ray *shadow_out = nullptr) {
-    DirectionSample ds; ds.p = v3(0.f); ds.n = v3(0.f); ds.d = v3(0.f); ds.pdf = 0.f; ds.dist = 0.f;
+    DirectionSample ds; ds.p = v3(0.f); ds.n = v3(0.f); ds.d = v3(0.f); ds.pdf = 0.f; ds.dist = 0.f; ds.delta = false;
     *spec_out = v3(0.f);
     uint32_t ne = s.n_emitters; if (ne == 0) return ds;
     uint32_t index = 0; float emitter_weight = 1.f;
@@ -280,34 +357,65 @@ template <bool DEFER> AM_D DirectionSample sample_emitter_direction(const DScene
         index = min((uint32_t) scaled, ne - 1u);
         emitter_weight = ecf; sample.x = scaled - (float) index;
     }
-    const DEmitter *em = s.emitters + index; const DMesh *m = s.meshes + em->mesh;
-    const float *cdf = s.area_cdf + m->cdf_offset, *pmfp = s.area_pmf + m->cdf_offset;
-    uint32_t face = distr_sample(cdf, m->nfaces, m->sum, sample.y);
-    float pmf = __ldg(pmfp + face) * m->normalization, cdf0 = face > 0 ? __ldg(cdf + face - 1) * m->normalization : 0.f;
-    sample.y = fdiv(sample.y - cdf0, pmf);
-    uint32_t tri = __ldg(s.prim_to_tri + m->prim_offset + face);
-    const float4 *tp = s.tris + 3 * (size_t) tri;
-    float4 a = ldg4(tp), b = ldg4(tp + 1), c = ldg4(tp + 2);
-    V3 p0 = v3(a.x, a.y, a.z), e0 = v3(b.x, b.y, b.z) - p0, e1 = v3(c.x, c.y, c.z) - p0;
-    V2 bc = square_to_uniform_triangle(sample);
-    ds.p = fmadd(e0, bc.x, fmadd(e1, bc.y, p0));
-    ds.pdf = m->normalization;
-    if (m->has_normals) {
-        const float4 *np = s.tri_nrm + 3 * (size_t) tri;
-        float4 na = ldg4(np), nb = ldg4(np + 1), nc = ldg4(np + 2);
-        ds.n = fmadd(v3(na.x, na.y, na.z), 1.f - bc.x - bc.y, fmadd(v3(nb.x, nb.y, nb.z), bc.x, v3(nc.x, nc.y, nc.z) * bc.y));
-    } else ds.n = cross(e0, e1);
-    ds.n = normalize(ds.n);
-    if (m->flip_normals) ds.n = -ds.n;
-    ds.d = ds.p - ref.p;
-    float dist_squared = squared_norm(ds.d);
-    ds.dist = fsqrt(dist_squared);
-    ds.d = ds.d / ds.dist;
-    float dp = fabs_(dot(ds.d, ds.n)), x = fdiv(dist_squared, dp);
-    ds.pdf *= finite_(x) ? x : 0.f;
-    bool active = dot(ds.d, ds.n) < 0.f && ds.pdf != 0.f;
-    V3 spec = ld3(em->radiance) / ds.pdf;
-    spec = select3(active, spec);
+    const DEmitter *em = s.emitters + index;
+    V3 spec;
+    if (!GEN || em->type == EMITTER_AREA) {
+        const DMesh *m = s.meshes + em->mesh;
+        const float *cdf = s.area_cdf + m->cdf_offset, *pmfp = s.area_pmf + m->cdf_offset;
+        uint32_t face = distr_sample(cdf, m->nfaces, m->sum, sample.y);
+        float pmf = __ldg(pmfp + face) * m->normalization, cdf0 = face > 0 ? __ldg(cdf + face - 1) * m->normalization : 0.f;
+        sample.y = fdiv(sample.y - cdf0, pmf);
+        uint32_t tri = __ldg(s.prim_to_tri + m->prim_offset + face);
+        const float4 *tp = s.tris + 3 * (size_t) tri;
+        float4 a = ldg4(tp), b = ldg4(tp + 1), c = ldg4(tp + 2);
+        V3 p0 = v3(a.x, a.y, a.z), e0 = v3(b.x, b.y, b.z) - p0, e1 = v3(c.x, c.y, c.z) - p0;
+        V2 bc = square_to_uniform_triangle(sample);
+        ds.p = fmadd(e0, bc.x, fmadd(e1, bc.y, p0));
+        ds.pdf = m->normalization;
+        if (m->has_normals) {
+            const float4 *np = s.tri_nrm + 3 * (size_t) tri;
+            float4 na = ldg4(np), nb = ldg4(np + 1), nc = ldg4(np + 2);
+            ds.n = fmadd(v3(na.x, na.y, na.z), 1.f - bc.x - bc.y, fmadd(v3(nb.x, nb.y, nb.z), bc.x, v3(nc.x, nc.y, nc.z) * bc.y));
+        } else ds.n = cross(e0, e1);
+        ds.n = normalize(ds.n);
+        if (m->flip_normals) ds.n = -ds.n;
+        ds.d = ds.p - ref.p;
+        float dist_squared = squared_norm(ds.d);
+        ds.dist = fsqrt(dist_squared);
+        ds.d = ds.d / ds.dist;
+        float dp = fabs_(dot(ds.d, ds.n)), x = fdiv(dist_squared, dp);
+        ds.pdf *= finite_(x) ? x : 0.f;
+        bool active = dot(ds.d, ds.n) < 0.f && ds.pdf != 0.f;
+        spec = ld3(em->radiance) / ds.pdf;
+        spec = select3(active, spec);
+    } else if (em->type == EMITTER_POINT) {
+        ds.p = ld3(em->position); ds.pdf = 1.f; ds.delta = true;
+        ds.d = ds.p - ref.p;
+        const float dist2 = squared_norm(ds.d), inv_dist = rsqrt(dist2);
+        ds.dist = fsqrt(dist2); ds.d = ds.d * inv_dist;
+        spec = ld3(em->radiance) * sqr(inv_dist);
+    } else if (em->type == EMITTER_CONSTANT) {
+        const V3 d = square_to_uniform_sphere(sample), center = ld3(s.bsphere);
+        const float radius = max_(s.bsphere[3], norm(ref.p - center)), dist = 2.f * radius;
+        ds.p = fmadd(d, dist, ref.p); ds.n = -d; ds.pdf = AM_INV_FOUR_PI; ds.d = d; ds.dist = dist;
+        spec = ld3(em->radiance) / ds.pdf;
+    } else {
+        float pdf; V2 uv = env_warp_sample(s, sample, &pdf);
+        uv.x += fdiv(.5f, (float) (s.env_res_x - 1u));
+        const bool active = pdf > 0.f;
+        const float theta = uv.y * AM_PI, phi = uv.x * (2.f * AM_PI);
+        float st, ct, sp, cp; sincos_(theta, &st, &ct); sincos_(phi, &sp, &cp);
+        V3 d = v3(cp * st, sp * st, ct);          // dr::sphdir
+        d = v3(d.y, d.z, -d.x);
+        const V3 center = ld3(s.bsphere);
+        const float radius = max_(s.bsphere[3], norm(ref.p - center)), dist = 2.f * radius;
+        const float inv_sin_theta = rsqrt(max_(max_(sqr(d.x) + sqr(d.z), sqr(AM_EPSILON)), 0.f));
+        d = xf_vector(s.env_to_world, d);
+        ds.p = ref.p + d * dist;
+        ds.n = -d; ds.d = d; ds.dist = dist;
+        ds.pdf = active ? pdf * inv_sin_theta * AM_ENV_PDF_SCALE : 0.f;
+        spec = select3(active, env_eval_uv(s, uv) / ds.pdf);
+    }
     ds.pdf *= rcp((float) ne);
     spec = spec * emitter_weight;
     if (ds.pdf != 0.f) {

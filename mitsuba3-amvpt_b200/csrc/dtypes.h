@@ -31,7 +31,12 @@ struct DMesh {
     float normalization, sum;      // 1 / area and unnormalised area (DiscreteDistribution, distr_1d.h:233-264)
     uint32_t cdf_offset, pad[3];   // into DScene::area_cdf / area_pmf
 };
-struct DEmitter { int32_t mesh; float radiance[3]; };
+// One record per scene emitter in the order Scene::Scene collects them (src/render/scene.cpp:22-63): area lights when their shape is added,
+// the others where they stand in the scene description.  type: 0 area (src/emitters/area.cpp; `mesh` = its shape), 1 point
+// (src/emitters/point.cpp; `radiance` = intensity, `position`), 2 constant environment (src/emitters/constant.cpp), 3 envmap
+// (src/emitters/envmap.cpp; pixels and sampling hierarchy live in DScene::env_*)
+enum EmitterType : int32_t { EMITTER_AREA = 0, EMITTER_POINT = 1, EMITTER_CONSTANT = 2, EMITTER_ENVMAP = 3 };
+struct DEmitter { int32_t mesh; float radiance[3]; int32_t type; float position[3]; };
 
 struct DScene {
     // AM_BVH_WIDTH == 4: 128 B per node = 8 x float4: lo.x[4], hi.x[4], lo.y[4], hi.y[4], lo.z[4], hi.z[4], child refs[4], pad;
@@ -52,7 +57,7 @@ struct DScene {
     const float *area_cdf, *area_pmf;
     uint32_t n_tris, n_nodes, n_emitters, n_sensors;
     uint32_t grid_x, grid_y;
-    int32_t reverse_x, reverse_y, thinlens, pad0;
+    int32_t reverse_x, reverse_y, thinlens, shutter_draw;   // shutter_draw: the sensor's shutter interval is non-empty, every sample draws a time (mvpath_single.h:66-68)
     uint32_t film_w, film_h;
     uint32_t max_depth, rr_depth;
     // film reconstruction filter: 0 box, 1 gaussian (polynomial of src/rfilters/gaussian.cpp:52-103), 2 tent (tent.cpp:48-56),
@@ -61,6 +66,16 @@ struct DScene {
     // cross-view sample reuse (mvpath.h:120-129): n_reuse = samples per primary sample after mvpath.cpp:192-218, 0 = off
     const DSensorAux *sensor_aux;
     uint32_t n_reuse; int32_t sa_mis, fast_mis, pad1;
+    // emitters other than area lights.  gen_emitters != 0 selects the general emitter code (kernels are instantiated for both cases, so
+    // that scenes lit by area lights only keep the short path); env_emitter = index of the environment emitter in `emitters` or -1
+    int32_t gen_emitters, env_emitter, hide_emitters, env_is_map;
+    float bsphere[4];                 // centre, radius of the scene as Emitter::set_scene sees it (constant.cpp:73-88, envmap.cpp:290-304)
+    const float *env_data;            // envmap: res_y x res_x x 3 floats, last column = first (envmap.cpp:146-207)
+    const float *env_warp;            // Hierarchical2D<Float, 0> levels, concatenated (include/mitsuba/core/distr_2d.h:376-482)
+    uint32_t env_res_x, env_res_y, env_n_levels, pad2;
+    uint32_t env_level_off[12], env_level_width[12];
+    float env_scale, env_patch_size[2], env_inv_patch_size[2]; uint32_t env_max_patch[2], pad3;
+    float env_to_world[12], env_from_world[12];      // first three rows of to_world and of its inverse
 };
 
 } // namespace amvpt

@@ -46,6 +46,23 @@ struct GridSensorParams {
     float near_clip = 1e-2f, far_clip = 1e4f, focus_distance = 1e4f, aperture_radius = 0.f, cone_deg = 0.f, cam_dist = 0.1f;
     float cam_dir[3] = { 1.f, 0.f, 0.f }, cam_off[3] = { 0.f, 0.f, 0.f };
 };
+// EnvironmentMapEmitter (src/emitters/envmap.cpp:111-214): the bitmap as loaded, the radiance array with its periodic extra column and
+// the luminance * sin(theta) hierarchy that importance-samples it (Hierarchical2D<Float, 0>, include/mitsuba/core/distr_2d.h:376-482)
+struct EnvMap {
+    bool present = false; uint32_t src_w = 0, src_h = 0; std::vector<float> src_rgb;
+    uint32_t res_x = 0, res_y = 0; std::vector<float> data;
+    float scale = 1.f; M4 to_world = m4_identity(), from_world = m4_identity();
+    std::vector<float> warp; std::vector<uint32_t> level_off, level_width;
+    float patch_size[2] = { 0, 0 }, inv_patch_size[2] = { 0, 0 }; uint32_t max_patch[2] = { 0, 0 };
+    void build(const float *rgb, uint32_t w, uint32_t h, float scale, const M4d &to_world);
+};
+// xml.cpp create_texture_from_spectrum (src/core/xml.cpp:1170-1268) in an RGB variant: wavelength:value pairs -> linear sRGB
+// (spectrum_list_to_srgb, src/core/spectrum.cpp:85-130), a uniform value inside an emitter -> value * xyz_to_srgb(1, 1, 1)
+void spectrum_to_srgb(std::vector<double> wavelengths, std::vector<double> values, bool within_emitter, bool unbounded_name, double *rgb);
+void uniform_emitter_spectrum_to_srgb(double value, double *rgb);
+// imageio.cpp: Bitmap(path) -> convert(RGB, Float32, linear), top row first
+void load_image_rgb(const std::string &path, uint32_t *w, uint32_t *h, std::vector<float> &rgb);
+
 enum SchedulerMode { SCHED_WARP_BATCH = 0, SCHED_REGENERATE = 1, SCHED_STREAM = 2, SCHED_WAVEFRONT = 3, SCHED_AUTO = 4, SCHED_REUSE = 5 /* reported only */, SCHED_SPLIT = 6 };
 
 struct BvhOut { std::vector<float4> nodes, tris, tri_nrm; std::vector<uint32_t> prim_to_tri; uint32_t depth = 0; };
@@ -62,7 +79,7 @@ struct Scene {
     std::vector<HMesh> meshes; std::vector<DBsdf> bsdfs; std::vector<DEmitter> emitters; std::vector<DSensor> sensors;
     std::vector<std::string> bsdf_ids;
     uint32_t grid_x = 1, grid_y = 1, res_x = 0, res_y = 0; bool reverse_x = false, reverse_y = true, thinlens = false;
-    bool multi_sensor = false;
+    bool multi_sensor = false, shutter_draw = false;   // shutter_draw: shutter_close > shutter_open (Sensor ctor, src/render/sensor.cpp:18-22)
     uint32_t film_w = 0, film_h = 0;
     uint32_t sample_count = 4, sampler_seed = 0;
     // film reconstruction filter: 0 box, 1 gaussian (stddev), 2 tent (radius), 3 mitchell (B, C), 4 catmullrom, 5 lanczos (lobes)
@@ -94,6 +111,13 @@ struct Scene {
     ~Scene();
     int add_bsdf(const DBsdf &b, const std::string &id = "");
     int add_mesh(HMesh &&m, const float *radiance);
+    // scene-level emitters (src/emitters/{point,constant,envmap}.cpp); each returns the emitter index
+    EnvMap env; int env_emitter = -1;
+    int add_emitter_point(const float *position, const float *intensity);
+    int add_emitter_constant(const float *radiance);
+    int add_emitter_envmap(const float *rgb, uint32_t w, uint32_t h, float scale, const M4d &to_world);
+    bool general_emitters() const { for (auto &e : emitters) if (e.type != EMITTER_AREA) return true; return false; }
+    void bounding_sphere(float *center3, float *radius) const;
     void set_sensor_grid(const GridSensorParams &g);
     void set_sensor_explicit(uint32_t n, uint32_t res_x, uint32_t res_y, const float *s2c, const float *to_world,
                              float near_clip, float far_clip, bool reverse_x);

@@ -22,7 +22,8 @@ namespace amvpt {
 #ifndef AM_RP_MIN_CTAS
 #define AM_RP_MIN_CTAS 5      // 96 registers -> 5 CTAs per SM: same-box A/B 1690 vs 1566 Mpaths/s on the Cornell quilt (profiles/r01_ab_min_ctas.txt)
 #endif
-template <int MODE, bool STATS> __global__ void __launch_bounds__(128, AM_RP_MIN_CTAS)
+// GEN = true: scenes with point / constant / environment-map emitters (dscene.cuh); the area-light-only instantiation keeps the short path.
+template <int MODE, bool STATS, bool GEN = false> __global__ void __launch_bounds__(128, AM_RP_MIN_CTAS)
 render_pass_kernel(const DScene s, const RenderParams p) {
     const unsigned lane_id = threadIdx.x & 31u;
     PathState ps; LaneSetup ls; ps.active = false;
@@ -57,7 +58,7 @@ render_pass_kernel(const DScene s, const RenderParams p) {
             }
             if (__all_sync(0xffffffffu, !ps.active && !has_result)) break;
         }
-        if (ps.active) path_bounce<false, STATS>(s, ps, nullptr, &st);
+        if (ps.active) path_bounce<false, STATS, false, false, GEN>(s, ps, nullptr, &st);
     }
     if (STATS) flush_stats(st, p.counters);
 }
@@ -222,6 +223,13 @@ void launch_render_pass(const DScene &s, const RenderParams &p, int mode, int sm
         if (stats) launch_stream<true>(s, p, sm_count, stream); else launch_stream<false>(s, p, sm_count, stream);
         return;
     }
+    if (s.gen_emitters) {         // general emitters: the regenerating megakernel only
+        int per_sm = 0; const void *gfn = stats ? (const void *) render_pass_kernel<1, true, true> : (const void *) render_pass_kernel<1, false, true>;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, gfn, 128, 0); if (per_sm < 1) per_sm = 1;
+        unsigned long long need = ((p.n_lanes + 31) / 32 + 3) / 4; unsigned g = (unsigned) (sm_count * per_sm); if (need < g) g = (unsigned) (need ? need : 1);
+        if (stats) render_pass_kernel<1, true, true><<<g, 128, 0, stream>>>(s, p); else render_pass_kernel<1, false, true><<<g, 128, 0, stream>>>(s, p);
+        return;
+    }
     // persistent grid: a whole number of CTAs per SM
     int ctas_per_sm = 0;
     const void *fn = mode == 0 ? (stats ? (const void *) render_pass_kernel<0, true> : (const void *) render_pass_kernel<0, false>)
@@ -290,7 +298,7 @@ void launch_view_stats(const float4 *film, const float2 *moments, uint32_t film_
 }
 
 // ------------------------------------------------------------------------------------------------ taps
-__global__ void trace_lanes_kernel(const DScene s, uint32_t seed_value, uint32_t spp_per_pass, uint32_t lane_begin, uint32_t n,
+template <bool GEN> __global__ void trace_lanes_kernel(const DScene s, uint32_t seed_value, uint32_t spp_per_pass, uint32_t lane_begin, uint32_t n,
                                    int trace, const LaneTaps t, unsigned long long *counters) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     StatCtx st; st.closest = st.shadow = st.nodes = st.tris = st.vertices = 0;
@@ -310,7 +318,7 @@ __global__ void trace_lanes_kernel(const DScene s, uint32_t seed_value, uint32_t
         tap.hit_prim = t.hit_prim + (size_t) i * t.max_hits; tap.hit_t = t.hit_t + (size_t) i * t.max_hits;
         for (uint32_t k = 0; k < t.max_hits; ++k) { tap.hit_prim[k] = 0xfffffffeu; tap.hit_t[k] = 0.f; }
         if (!trace || s.max_depth == 0) ps.active = false;
-        while (ps.active) path_bounce<true, true>(s, ps, &tap, &st);
+        while (ps.active) path_bounce<true, true, false, false, GEN>(s, ps, &tap, &st);
         if (t.radiance) {
             V3 L = ps.valid_ray ? ps.result : v3(0.f);
             t.radiance[4 * i] = L.x; t.radiance[4 * i + 1] = L.y; t.radiance[4 * i + 2] = L.z; t.radiance[4 * i + 3] = ps.valid_ray ? 1.f : 0.f;
@@ -321,7 +329,8 @@ __global__ void trace_lanes_kernel(const DScene s, uint32_t seed_value, uint32_t
 void launch_trace_lanes(const DScene &s, uint32_t seed_value, uint32_t spp_per_pass, uint32_t lane_begin, uint32_t n, int trace,
                         const LaneTaps &taps, unsigned long long *counters, cudaStream_t st) {
     if (!n) return;
-    trace_lanes_kernel<<<(n + 127) / 128, 128, 0, st>>>(s, seed_value, spp_per_pass, lane_begin, n, trace, taps, counters);
+    if (s.gen_emitters) trace_lanes_kernel<true><<<(n + 127) / 128, 128, 0, st>>>(s, seed_value, spp_per_pass, lane_begin, n, trace, taps, counters);
+    else trace_lanes_kernel<false><<<(n + 127) / 128, 128, 0, st>>>(s, seed_value, spp_per_pass, lane_begin, n, trace, taps, counters);
 }
 
 __global__ void intersect_kernel(const DScene s, const float *o, const float *d, const float *maxt, uint32_t n, int any,
@@ -357,7 +366,7 @@ void launch_bsdf_tap(const DScene &s, int bsdf, const float *wi, const float *wo
     bsdf_tap_kernel<<<(n + 127) / 128, 128, 0, st>>>(s, bsdf, wi, wo, s1, s2, n, out);
 }
 
-// op: 0 sin 1 cos 2 exp 3 log 4 erf 5 erfinv 6 exp2 7 sqrt 8 rcp 9 rsqrt 10 safe_sqrt 11 tan
+// op: 0 sin 1 cos 2 exp 3 log 4 erf 5 erfinv 6 exp2 7 sqrt 8 rcp 9 rsqrt 10 safe_sqrt 11 tan 12 acos 13 atan2(x, .3) 14 atan2(.3, x) 15 atan2(x, -.3) 16 safe_acos
 __global__ void math_tap_kernel(int op, const float *in, uint32_t n, float *out) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; if (i >= n) return;
     float x = in[i], r = x, sn, cs;
@@ -366,12 +375,21 @@ __global__ void math_tap_kernel(int op, const float *in, uint32_t n, float *out)
         case 2: r = exp_(x); break; case 3: r = log_(x); break; case 4: r = erf_(x); break; case 5: r = erfinv_(x); break;
         case 6: r = exp2_(x); break; case 7: r = fsqrt(x); break; case 8: r = rcp(x); break; case 9: r = rsqrt(x); break;
         case 10: r = safe_sqrt(x); break; case 11: r = tan_(x); break;
+        case 12: r = acos_(x); break; case 13: r = atan2_(x, 0.3f); break; case 14: r = atan2_(0.3f, x); break; case 15: r = atan2_(x, -0.3f); break; case 16: r = safe_acos_(x); break;
     }
     out[i] = r;
 }
 void launch_math_tap(int op, const float *in, uint32_t n, float *out, cudaStream_t st) {
     if (!n) return;
     math_tap_kernel<<<(n + 127) / 128, 128, 0, st>>>(op, in, n, out);
+}
+__global__ void env_warp_tap_kernel(const DScene s, const float *u, uint32_t n, float *out) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; if (i >= n) return;
+    float pdf; V2 uv = env_warp_sample(s, v2(u[2 * i], u[2 * i + 1]), &pdf);
+    out[4 * i] = uv.x; out[4 * i + 1] = uv.y; out[4 * i + 2] = pdf; out[4 * i + 3] = env_warp_eval(s, uv);
+}
+void launch_env_warp_tap(const DScene &s, const float *u, uint32_t n, float *out, cudaStream_t st) {
+    if (n) env_warp_tap_kernel<<<(n + 127) / 128, 128, 0, st>>>(s, u, n, out);
 }
 __global__ void sampler_tap_kernel(uint32_t seed_value, uint32_t lane, uint32_t n, float *out) {
     if (blockIdx.x || threadIdx.x) return;

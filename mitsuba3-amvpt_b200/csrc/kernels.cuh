@@ -72,6 +72,7 @@ void launch_intersect(const DScene &s, const float *o, const float *d, const flo
 void launch_bsdf_tap(const DScene &s, int bsdf, const float *wi, const float *wo, const float *s1, const float *s2, uint32_t n,
                      float *out /* n * 16 */, cudaStream_t st);
 void launch_math_tap(int op, const float *in, uint32_t n, float *out, cudaStream_t st);
+void launch_env_warp_tap(const DScene &s, const float *u, uint32_t n, float *out /* n * 4: uv, pdf, eval(uv) */, cudaStream_t st);
 void launch_sampler_tap(uint32_t seed_value, uint32_t lane, uint32_t n, float *out, cudaStream_t st);
 void launch_l2_flush(float *buf, size_t n, cudaStream_t st);
 double run_membench_read(size_t bytes, uint32_t iters, int sm_count, cudaStream_t st);   // GB/s of 16-byte loads over `bytes`, or < 0 on failure

@@ -46,6 +46,7 @@ void render(Scene &s, const RenderOptions &opt) {
         if (s.rfilter_type != 0) AM_THROW("mvpath: sample reuse needs the box reconstruction filter in this build");
         if (opt.adaptive) AM_THROW("render: the adaptive allocator keeps per-pixel moments of the owning view; it cannot be combined with sample reuse");
         if (s.d.n_reuse != s.reuse_samples()) AM_THROW("render: integrator parameters changed after commit");
+        if (s.general_emitters()) AM_THROW("mvpath: sample reuse is built for scenes lit by area emitters; point / constant / envmap emitters need sa_reuse = false");
     }
     if (opt.shard.world == 0 || opt.shard.rank >= opt.shard.world) AM_THROW("render: invalid shard %u/%u", opt.shard.rank, opt.shard.world);
     AM_CUDA(cudaSetDevice(s.device));
@@ -94,6 +95,7 @@ void render(Scene &s, const RenderOptions &opt) {
     // a reconstruction filter other than the box is splatted by the wavefront's regen stage only: carrying the sample position
     // and the footprint loop through the persistent megakernels costs them 8 % on the box-filter path (measured, profiles/)
     if (s.rfilter_type != 0) mode = 3;
+    if (s.general_emitters() && mode != 3) mode = 1;                // point / constant / envmap emitters: regenerating megakernel or wavefront
     if (mode == SCHED_SPLIT && (opt.stats || adaptive)) mode = 1;   // the counting pass and the moment film use the unsplit megakernel
     if (reuse) mode = SCHED_REUSE;                 // the reuse branch has its own kernel (reuse.cu)
     rs.scheduler_used = (uint32_t) mode;
@@ -113,7 +115,7 @@ void render(Scene &s, const RenderOptions &opt) {
                 float4 **f4s[] = { &w.ro, &w.rd, &w.tp, &w.res, &w.pp, &w.hit, &w.so, &w.sd, &w.sT, &w.sV };
                 for (float4 **a : f4s) *a = (float4 *) s.dalloc(sizeof(float4) * n);
                 w.rng = (uint4 *) s.dalloc(sizeof(uint4) * n); w.flags = (uint32_t *) s.dalloc(sizeof(uint32_t) * n); w.spos = (float2 *) s.dalloc(sizeof(float2) * n);
-                w.queue = (uint32_t *) s.dalloc(sizeof(uint32_t) * 6 * (size_t) n); w.qcount = (uint32_t *) s.dalloc(sizeof(uint32_t) * 8);
+                w.queue = (uint32_t *) s.dalloc(sizeof(uint32_t) * 7 * (size_t) n);      // six BSDF-type queues + the escaped-ray queue w.qcount = (uint32_t *) s.dalloc(sizeof(uint32_t) * 8);
                 w.live = (uint32_t *) s.dalloc(sizeof(uint32_t) * 64);
                 s.wf_type_mask = 0; for (auto &m : s.meshes) s.wf_type_mask |= 1u << s.bsdfs[m.bsdf].type;
             }

@@ -153,7 +153,7 @@ int Scene::add_mesh(HMesh &&m, const float *radiance) {
     if (!m.nrm.empty() && m.nrm.size() != m.pos.size()) AM_THROW("add_mesh: normal count does not match vertex count");
     m.prim_offset = nprims();
     int id = (int) meshes.size();
-    if (radiance) { m.emitter = (int) emitters.size(); DEmitter e; e.mesh = id; e.radiance[0] = radiance[0]; e.radiance[1] = radiance[1]; e.radiance[2] = radiance[2]; emitters.push_back(e); }
+    if (radiance) { m.emitter = (int) emitters.size(); DEmitter e{}; e.type = EMITTER_AREA; e.mesh = id; e.radiance[0] = radiance[0]; e.radiance[1] = radiance[1]; e.radiance[2] = radiance[2]; emitters.push_back(e); }
     else m.emitter = -1;
     m.build_area_distr();
     meshes.push_back(std::move(m)); committed = false; host_ready = false;
@@ -307,10 +307,21 @@ void Scene::commit(int dev) {
     d.sensor_aux = upload(aux); d.n_reuse = reuse_samples(); d.sa_mis = integrator.sa_mis; d.fast_mis = integrator.fast_mis;
     d.sensors = upload(sensors); d.area_cdf = upload(cdf_all); d.area_pmf = upload(pmf_all);
     d.n_tris = n_tris; d.n_nodes = n_nodes; d.n_emitters = (uint32_t) emitters.size(); d.n_sensors = (uint32_t) sensors.size();
-    d.grid_x = grid_x; d.grid_y = grid_y; d.reverse_x = reverse_x; d.reverse_y = reverse_y; d.thinlens = thinlens;
+    d.grid_x = grid_x; d.grid_y = grid_y; d.reverse_x = reverse_x; d.reverse_y = reverse_y; d.thinlens = thinlens; d.shutter_draw = shutter_draw ? 1 : 0;
     d.film_w = film_w; d.film_h = film_h;
     d.max_depth = integrator.max_depth < 0 ? 0xffffffffu : (uint32_t) integrator.max_depth;   // integrator.cpp:503-520
     d.rr_depth = integrator.rr_depth;
+    // emitters that are not area lights: environment data, scene bounding sphere (Emitter::set_scene)
+    d.gen_emitters = general_emitters() ? 1 : 0; d.env_emitter = env_emitter; d.hide_emitters = integrator.hide_emitters ? 1 : 0;
+    d.env_is_map = env_emitter >= 0 && emitters[(size_t) env_emitter].type == EMITTER_ENVMAP;
+    bounding_sphere(d.bsphere, d.bsphere + 3);
+    if (d.env_is_map) {
+        d.env_data = upload(env.data); d.env_warp = upload(env.warp);
+        d.env_res_x = env.res_x; d.env_res_y = env.res_y; d.env_n_levels = (uint32_t) env.level_off.size(); d.env_scale = env.scale;
+        for (size_t i = 0; i < env.level_off.size(); ++i) { d.env_level_off[i] = env.level_off[i]; d.env_level_width[i] = env.level_width[i]; }
+        for (int k = 0; k < 2; ++k) { d.env_patch_size[k] = env.patch_size[k]; d.env_inv_patch_size[k] = env.inv_patch_size[k]; d.env_max_patch[k] = env.max_patch[k]; }
+        std::memcpy(d.env_to_world, env.to_world.m, 48); std::memcpy(d.env_from_world, env.from_world.m, 48);
+    }
     d.filter_type = rfilter_type; d.filter_radius = .5f; d.filter_inv_radius = 1.f;
     if (rfilter_type == 1) {          // GaussianFilter ctor (gaussian.cpp:41-88): Remez fit to exp(-x / 2), rescaled by 1 / stddev^2 per degree
         static const double coeff[10] = { 9.992604880e-1, -4.977025247e-1, 1.222248550e-1, -1.932406282e-2, 2.136713061e-3,

@@ -21,6 +21,7 @@ namespace amvpt {
 enum : uint32_t { WF_PREV_DELTA = 1u, WF_VALID_RAY = 2u, WF_ALIVE = 4u, WF_HAS_RESULT = 8u, WF_SHADOW = 16u };
 #define WF_NO_PIXEL 0xffffffffu
 #define WF_N_TYPES 6
+#define WF_MISS_KEY 7u     /* qcount[6] is the ray-task counter; escaped rays are counted in qcount[7] and stored in queue row 6 */
 
 AM_D float4 f4(V3 v, float w) { return make_float4(v.x, v.y, v.z, w); }
 AM_D V3 xyz(float4 v) { return v3(v.x, v.y, v.z); }
@@ -50,14 +51,14 @@ wf_regen_kernel(const DScene s, const RenderParams p, const WfPool w, uint32_t i
             w.res[i] = f4(ps.result, __uint_as_float(ls.in_film ? ls.pixel : WF_NO_PIXEL)); w.pp[i] = f4(ps.prev_p, __uint_as_float(0u));
             w.rng[i] = make_uint4((uint32_t) ps.rng.state, (uint32_t) (ps.rng.state >> 32), (uint32_t) ps.rng.inc, (uint32_t) (ps.rng.inc >> 32));
             if (s.filter_type != 0) w.spos[i] = make_float2(ls.spx, ls.spy);
-            f = WF_HAS_RESULT | WF_PREV_DELTA | (s.max_depth != 0 ? WF_ALIVE : 0u);      // mvpath_single.h:86-87
+            f = WF_HAS_RESULT | WF_PREV_DELTA | (s.max_depth != 0 ? WF_ALIVE | (ps.valid_ray ? WF_VALID_RAY : 0u) : 0u);      // mvpath_single.h:86-87, 98
         }
         w.flags[i] = f;
     }
     unsigned live = __ballot_sync(0xffffffffu, (f & (WF_ALIVE | WF_SHADOW | WF_HAS_RESULT)) != 0);
     if (lane_id == 0 && live) atomicAdd(w.live + (iter & 63u), (uint32_t) __popc(live));
     if (i == 0) {
-        for (int k = 0; k <= WF_N_TYPES; ++k) w.qcount[k] = 0;      // type queues + the ray-task counter
+        for (int k = 0; k <= WF_N_TYPES + 1; ++k) w.qcount[k] = 0;  // type queues + the ray-task counter + the escaped-ray queue
         w.live[(iter + 32u) & 63u] = 0;
     }
 }
@@ -144,7 +145,8 @@ wf_trace_kernel(const DScene s, const RenderParams p, const WfPool w, uint32_t f
                     }
                     atomicAnd(w.flags + slot, ~WF_SHADOW);
                 } else if (tv.h.tri == AM_NO_HIT) {
-                    atomicAnd(w.flags + slot, ~WF_ALIVE);      // no environment emitter: the path ends, valid_ray stays as it is
+                    atomicAnd(w.flags + slot, ~WF_ALIVE);      // the path ends, valid_ray stays as it is; with an environment
+                    if (s.env_emitter >= 0) key = WF_MISS_KEY;  // emitter the escaped ray still collects its radiance (wf_miss_kernel)
                     if (STATS) { st.closest++; st.vertices++; }
                 } else {
                     w.hit[slot] = make_float4(tv.h.t, tv.h.u, tv.h.v, __uint_as_float(tv.h.tri));
@@ -159,13 +161,28 @@ wf_trace_kernel(const DScene s, const RenderParams p, const WfPool w, uint32_t f
             unsigned leader = __ffs(peers) - 1; uint32_t base = 0;
             if (lane_id == leader && key != 0xffu) base = atomicAdd(w.qcount + key, (uint32_t) __popc(peers));
             base = __shfl_sync(0xffffffffu, base, leader);
-            if (key != 0xffu) w.queue[(size_t) key * w.n_slots + base + __popc(peers & ((1u << lane_id) - 1u))] = slot;
+            if (key != 0xffu) w.queue[(size_t) (key == WF_MISS_KEY ? WF_N_TYPES : key) * w.n_slots + base + __popc(peers & ((1u << lane_id) - 1u))] = slot;
         }
     }
     if (STATS) flush_stats(st, p.counters);
 }
 
-template <bool STATS, int TYPE> __global__ void __launch_bounds__(128)
+// Escaped rays of scenes with an environment emitter: emission of the environment with the MIS weight of the previous vertex
+// (mvpath_single.h:148-163 for an invalid interaction).  One thread per entry of the escaped-ray queue.
+__global__ void __launch_bounds__(128) wf_miss_kernel(const DScene s, const WfPool w) {
+    const uint32_t n = w.qcount[WF_MISS_KEY], stride = gridDim.x * blockDim.x;
+    const uint32_t *queue = w.queue + (size_t) WF_N_TYPES * w.n_slots;
+    for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += stride) {
+        const uint32_t i = queue[j]; const uint32_t f = w.flags[i];
+        PathState ps; const float4 b = w.rd[i], c = w.tp[i], d = w.res[i];
+        ps.ray.d = xyz(b); ps.throughput = xyz(c); ps.prev_bsdf_pdf = c.w; ps.result = xyz(d); ps.prev_delta = (f & WF_PREV_DELTA) != 0;
+        SI si; si.valid = false;
+        add_emission<true>(s, ps, si, nullptr);
+        w.res[i] = f4(ps.result, d.w);
+    }
+}
+
+template <bool STATS, int TYPE, bool GEN> __global__ void __launch_bounds__(128)
 wf_shade_kernel(const DScene s, const RenderParams p, const WfPool w) {
     const uint32_t n = w.qcount[TYPE], stride = gridDim.x * blockDim.x;
     const uint32_t *queue = w.queue + (size_t) TYPE * w.n_slots;
@@ -181,7 +198,7 @@ wf_shade_kernel(const DScene s, const RenderParams p, const WfPool w) {
           ps.prev_delta = (f & WF_PREV_DELTA) != 0; ps.valid_ray = (f & WF_VALID_RAY) != 0; ps.active = true;
           float4 hh = w.hit[i]; Hit h; h.t = hh.x; h.u = hh.y; h.v = hh.z; h.tri = __float_as_uint(hh.w);
           Ray shadow; V3 sT, sV;
-          bool need_shadow = shade_vertex<STATS, TYPE>(s, ps, h, &shadow, &sT, &sV, &st);
+          bool need_shadow = shade_vertex<STATS, TYPE, GEN>(s, ps, h, &shadow, &sT, &sV, &st);
           w.res[i] = f4(ps.result, d.w);
           f = WF_HAS_RESULT | (ps.valid_ray ? WF_VALID_RAY : 0u);
           if (need_shadow) { w.so[i] = f4(shadow.o, shadow.maxt); w.sd[i] = f4(shadow.d, 0.f); w.sT[i] = f4(sT, 0.f); w.sV[i] = f4(sV, 0.f); f |= WF_SHADOW; }
@@ -196,14 +213,14 @@ wf_shade_kernel(const DScene s, const RenderParams p, const WfPool w) {
     if (STATS) flush_stats(st, p.counters);
 }
 
-template <bool STATS> static void launch_shade(int type, const DScene &s, const RenderParams &p, const WfPool &w, unsigned grid, cudaStream_t st) {
+template <bool STATS, bool GEN> static void launch_shade(int type, const DScene &s, const RenderParams &p, const WfPool &w, unsigned grid, cudaStream_t st) {
     switch (type) {
-        case BSDF_DIFFUSE: wf_shade_kernel<STATS, BSDF_DIFFUSE><<<grid, 128, 0, st>>>(s, p, w); break;
-        case BSDF_CONDUCTOR: wf_shade_kernel<STATS, BSDF_CONDUCTOR><<<grid, 128, 0, st>>>(s, p, w); break;
-        case BSDF_DIELECTRIC: wf_shade_kernel<STATS, BSDF_DIELECTRIC><<<grid, 128, 0, st>>>(s, p, w); break;
-        case BSDF_ROUGHCONDUCTOR: wf_shade_kernel<STATS, BSDF_ROUGHCONDUCTOR><<<grid, 128, 0, st>>>(s, p, w); break;
-        case BSDF_ROUGHDIELECTRIC: wf_shade_kernel<STATS, BSDF_ROUGHDIELECTRIC><<<grid, 128, 0, st>>>(s, p, w); break;
-        default: wf_shade_kernel<STATS, BSDF_ROUGHPLASTIC><<<grid, 128, 0, st>>>(s, p, w); break;
+        case BSDF_DIFFUSE: wf_shade_kernel<STATS, BSDF_DIFFUSE, GEN><<<grid, 128, 0, st>>>(s, p, w); break;
+        case BSDF_CONDUCTOR: wf_shade_kernel<STATS, BSDF_CONDUCTOR, GEN><<<grid, 128, 0, st>>>(s, p, w); break;
+        case BSDF_DIELECTRIC: wf_shade_kernel<STATS, BSDF_DIELECTRIC, GEN><<<grid, 128, 0, st>>>(s, p, w); break;
+        case BSDF_ROUGHCONDUCTOR: wf_shade_kernel<STATS, BSDF_ROUGHCONDUCTOR, GEN><<<grid, 128, 0, st>>>(s, p, w); break;
+        case BSDF_ROUGHDIELECTRIC: wf_shade_kernel<STATS, BSDF_ROUGHDIELECTRIC, GEN><<<grid, 128, 0, st>>>(s, p, w); break;
+        default: wf_shade_kernel<STATS, BSDF_ROUGHPLASTIC, GEN><<<grid, 128, 0, st>>>(s, p, w); break;
     }
 }
 
@@ -226,8 +243,10 @@ uint32_t run_wavefront_pass(const DScene &s, const RenderParams &p, const WfPool
         if (stats) wf_trace_kernel<true><<<tgrid, 128, 0, st>>>(s, p, w, fetch_min, leaf_min); else wf_trace_kernel<false><<<tgrid, 128, 0, st>>>(s, p, w, fetch_min, leaf_min);
         if (trace_seconds) cudaEventRecord(ev.back(), st);
         launches += 2;
+        if (s.env_emitter >= 0) { wf_miss_kernel<<<sgrid, 128, 0, st>>>(s, w); launches++; }
         for (int t = 0; t < WF_N_TYPES; ++t) if (type_mask & (1u << t)) {
-            if (stats) launch_shade<true>(t, s, p, w, sgrid, st); else launch_shade<false>(t, s, p, w, sgrid, st);
+            if (s.gen_emitters) { if (stats) launch_shade<true, true>(t, s, p, w, sgrid, st); else launch_shade<false, true>(t, s, p, w, sgrid, st); }
+            else { if (stats) launch_shade<true, false>(t, s, p, w, sgrid, st); else launch_shade<false, false>(t, s, p, w, sgrid, st); }
             launches++;
         }
         if (iter >= next_check) {

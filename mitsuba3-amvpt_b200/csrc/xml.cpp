@@ -269,10 +269,25 @@ struct Loader {
             else err(k, "'rgb' tag requires one or three values (got \"" + attr(k, "value") + "\")");
         }
         else if (t == "spectrum") {
-            if (k.attr("filename")) err(k, "<spectrum filename=...> is not supported on this path (RGB rendering: give <rgb> values)");
-            auto tk = tokens(attr(k, "value"));
-            if (tk.size() != 1 || tk[0].find(':') != std::string::npos) err(k, "wavelength:value spectra are not supported on this path (RGB rendering: give a uniform value or <rgb>)");
-            v.kind = Value::Color; v.v[0] = v.v[1] = v.v[2] = to_f(k, tk[0]);
+            // src/core/xml.cpp:777-833 + create_texture_from_spectrum (:1170-1268) in an RGB variant: a uniform value stays uniform
+            // (inside an emitter it is the colour of a flat spectrum under the sRGB white point), wavelength:value pairs are integrated
+            // against the CIE 1931 observer (reflectances also against D65) and become an sRGB colour
+            if (k.attr("filename")) err(k, "<spectrum filename=...> is not supported on this path (give wavelength:value pairs, a uniform value or <rgb>)");
+            auto tk = tokens(attr(k, "value")); v.kind = Value::Color;
+            const bool within_emitter = o.cls == "emitter", unbounded = name == "eta" || name == "k" || name == "int_ior" || name == "ext_ior";
+            if (tk.empty()) err(k, "'spectrum' tag requires one of \"value\" or \"filename\" attributes");
+            if (tk.size() == 1 && tk[0].find(':') == std::string::npos) {
+                const double c = to_f(k, tk[0]);
+                if (within_emitter && !unbounded) uniform_emitter_spectrum_to_srgb(c, v.v); else v.v[0] = v.v[1] = v.v[2] = c;
+            } else {
+                std::vector<double> wl, val;
+                for (auto &tok : tk) {
+                    size_t c = tok.find(':'); if (c == std::string::npos || tok.find(':', c + 1) != std::string::npos) err(k, "invalid spectrum (expected wavelength:value pairs)");
+                    wl.push_back(to_f(k, tok.substr(0, c))); val.push_back(to_f(k, tok.substr(c + 1)));
+                }
+                if (wl.size() < 2) err(k, "invalid spectrum (expected at least two wavelength:value pairs)");
+                spectrum_to_srgb(wl, val, within_emitter, unbounded, v.v);
+            }
         }
         else if (t == "transform") { v.kind = Value::Xform; v.m = transform(k); }
         else if (t == "ref") {
@@ -423,7 +438,8 @@ struct Builder {
         *w = (uint32_t) f->i("width", 768); *h = (uint32_t) f->i("height", 576);
         std::string pf = f->s("pixel_format", "rgb"); for (auto &c : pf) c = (char) tolower(c);
         if (pf != "rgb") AM_THROW("%s: pixel_format \"%s\": only \"rgb\" is supported on this path", f->where.c_str(), pf.c_str());
-        f->s("component_format", "float16"); f->s("file_format", "openexr"); f->b("sample_border", false); f->b("compensate", false);
+        f->s("component_format", "float16"); f->s("file_format", "openexr"); f->b("compensate", false);      // compensate: Kahan-compensated accumulation, not observable beyond rounding
+        if (f->b("sample_border", false)) AM_THROW("%s: sample_border = true enlarges the film by the filter border and shifts the lane map (mvpath.cpp:29-30, 187-188); it is not supported on this path", f->where.c_str());
         for (const char *c : { "crop_offset_x", "crop_offset_y", "crop_width", "crop_height" }) if (f->has(c)) AM_THROW("%s: film crop windows are not supported on this path", f->where.c_str());
         // hdrfilm's default reconstruction filter is the gaussian with stddev 0.5 (src/render/film.cpp:34-40)
         int ftype = 1; float fparam = 0.5f, fparam2 = 0.f; bool have_filter = false;
@@ -479,7 +495,9 @@ struct Builder {
             o.mark(k);
         }
         uint32_t fw, fh; film(f, &fw, &fh); sampler(s);
-        if (o.f("shutter_close", 0.0) < o.f("shutter_open", 0.0)) AM_THROW("%s: Shutter opening time must be less than or equal to the shutter closing time!", o.where.c_str());
+        { const float so = (float) o.f("shutter_open", 0.0), open_time = (float) o.f("shutter_close", 0.0) - so;       // sensor.cpp:18-22
+          if (open_time < 0.f) AM_THROW("%s: Shutter opening time must be less than or equal to the shutter closing time!", o.where.c_str());
+          sc.shutter_draw = open_time > 0.f; }
         if (o.type == "grid") {         // grid.cpp:84-236
             if (!sub_wrap) AM_THROW("%s: Need to specify wraps for sensor, film and sampler !", o.where.c_str());
             Obj &sp = *sub_wrap; std::string cam = plugin_type(sp);
@@ -542,7 +560,36 @@ struct Builder {
         o.check_unqueried();
     }
 
-    bool integrator(Obj &o) {
+    // emitters that stand on their own in the scene (src/emitters/{point,constant,envmap}.cpp constructors)
+    void emitter(const std::shared_ptr<Obj> &op, const std::string &base, Loader &ld) {
+        Obj &o = *op;
+        if (o.type == "area") return;           // declared at the scene level with an id and attached to its shape through <ref> (scene.cpp:46-48: surface emitters join the list with their shape)
+        if (o.type == "point") {                // point.cpp:65-85
+            float pos[3] = { 0, 0, 0 }, intensity[3];
+            if (o.has("position")) { if (o.has("to_world")) AM_THROW("%s: Only one of the parameters 'position' and 'to_world' can be specified at the same time!'", o.where.c_str()); o.vec("position", pos); }
+            else { M4 tw = m4_from_d(o.xform("to_world")); pos[0] = tw.m[0][3]; pos[1] = tw.m[1][3]; pos[2] = tw.m[2][3]; }
+            o.color("intensity", 1.f, intensity); o.check_unqueried();
+            sc.add_emitter_point(pos, intensity);
+        } else if (o.type == "constant") {      // constant.cpp:55-68
+            float radiance[3]; o.color("radiance", 1.f, radiance); o.check_unqueried();
+            sc.add_emitter_constant(radiance);
+        } else if (o.type == "envmap") {        // envmap.cpp:111-214
+            if (o.b("mis_compensation", false)) AM_THROW("%s: envmap mis_compensation is not supported on this path", o.where.c_str());
+            std::string fn = ld.resolve(o.s("filename", ""), base); uint32_t w = 0, h = 0; std::vector<float> rgb;
+            load_image_rgb(fn, &w, &h, rgb);
+            const float scale = (float) o.f("scale", 1.0); M4d tw = o.xform("to_world"); o.check_unqueried();
+            sc.add_emitter_envmap(rgb.data(), w, h, scale, tw);
+        } else AM_THROW("%s: emitter plugin \"%s\" is not part of the AMVPT path (supported: area, point, constant, envmap)", o.where.c_str(), o.type.c_str());
+    }
+
+    bool integrator(Obj &o_) {
+        Obj *op = &o_;
+        if (op->type == "moment") {             // src/integrators/moment.cpp: a wrapper that adds second-moment AOVs around one nested integrator; the radiance is the nested one's
+            auto kids = op->children("integrator");
+            if (kids.size() != 1) AM_THROW("%s: the moment integrator needs exactly one nested integrator on this path", op->where.c_str());
+            op->mark(kids[0]); op->check_unqueried(); op = kids[0].get();
+        }
+        Obj &o = *op;
         IntegratorParams &ip = sc.integrator;
         if (o.type != "mvpath" && o.type != "path") AM_THROW("%s: integrator plugin \"%s\" is not part of the AMVPT path (supported: mvpath, path)", o.where.c_str(), o.type.c_str());
         ip.is_mvpath = o.type == "mvpath";
@@ -554,7 +601,6 @@ struct Builder {
             ip.spp_pass_lim = (uint32_t) o.i("spp_pass_lim", 16); ip.sa_reuse = o.b("sa_reuse", false); ip.sa_mis = o.b("sa_mis", false);
             ip.fast_mis = o.b("fast_mis", false); ip.reuse_count = (uint32_t) o.i("reuse_count", 1); ip.adaptive = (uint32_t) o.i("adaptive", 0);
             ip.force_eval = o.b("force_eval", true); ip.debug = o.b("debug", false);
-            if (ip.spp_pass_lim == 0) AM_THROW("%s: spp_pass_lim must be positive", o.where.c_str());
         }
         o.check_unqueried();
         return ip.is_mvpath;
@@ -576,7 +622,7 @@ Scene *build_scene(Loader &ld, const std::shared_ptr<Obj> &root, const std::stri
     for (auto &k : root->children()) {
         if (k->cls == "shape") b.shape(k, base, ld);
         else if (k->cls == "bsdf") b.bsdf(k);            // instantiated even if unreferenced, like the reference
-        else if (k->cls == "emitter") { if (k->type != "area") AM_THROW("%s: emitter plugin \"%s\" is not part of the AMVPT path (supported: area, attached to a shape)", k->where.c_str(), k->type.c_str()); }
+        else if (k->cls == "emitter") b.emitter(k, base, ld);
         else if (k->cls == "integrator" || k->cls == "sensor" || k->cls == "wrap" || k->cls == "film" || k->cls == "sampler") continue;
         else AM_THROW("%s: <%s> is not part of the AMVPT path", k->where.c_str(), k->cls.c_str());
     }

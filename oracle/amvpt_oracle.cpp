@@ -66,7 +66,9 @@ struct Mesh {
     V3 vp(uint32_t i) const { return V3(pos[3 * i], pos[3 * i + 1], pos[3 * i + 2]); }
     V3 vn(uint32_t i) const { return V3(nrm[3 * i], nrm[3 * i + 1], nrm[3 * i + 2]); }
 };
-struct Emitter { int mesh; V3 radiance; };
+#include "o_emitter.h"
+// emitters in the order Scene::Scene collects them (scene.cpp:22-63): type 0 area (mesh), 1 point, 2 constant, 3 envmap
+struct Emitter { int mesh; V3 radiance; int type = 0; V3 position; };
 struct SubSensor {
     M4 s2c, to_world; float near_clip, far_clip, aperture_radius, focus_distance;
     // sample reuse (sample_surface): camera_to_sample, inverse of to_world, 1 / area of the image rectangle (perspective.cpp:173-199)
@@ -77,8 +79,9 @@ struct BvhNode { float lo[3], hi[3]; int32_t left, right; uint32_t first, count;
 
 struct Scene {
     std::vector<Mesh> meshes; std::vector<Bsdf> bsdfs; std::vector<Emitter> emitters;
+    EnvMap env; int env_emitter = -1; V3 bs_center; float bs_radius = RayEpsilon;     // environment emitter, Emitter::set_scene bounding sphere
     std::vector<SubSensor> sensors;
-    uint32_t grid_x = 1, grid_y = 1; int reverse_x = 0, reverse_y = 1, thinlens = 0;
+    uint32_t grid_x = 1, grid_y = 1; int reverse_x = 0, reverse_y = 1, thinlens = 0, shutter_draw = 0;
     uint32_t film_w = 0, film_h = 0;    // quilt size
     uint32_t max_depth = 0xffffffffu, rr_depth = 5; int hide_emitters = 0;
     uint32_t base_seed = 0;
@@ -295,7 +298,7 @@ static inline uint32_t distr_sample(const Mesh &m, float sample) {
     }
     return start;
 }
-struct DirectionSample { V3 p, n, d; float pdf = 0, dist = 0; bool valid = false; };
+struct DirectionSample { V3 p, n, d; float pdf = 0, dist = 0; bool valid = false, delta = false; };
 // Mesh::sample_position (mesh.cpp:764-818) + Shape::sample_direction (shape.cpp:360-377)
 // + AreaLight::sample_direction (area.cpp:116-167) + Scene::sample_emitter_direction (scene.cpp:295-346)
 static DirectionSample sample_emitter_direction(const Scene &s, const SI &ref, V2 sample, V3 *spec_out, bool brute, TraverseStats *st) {
@@ -308,7 +311,43 @@ static DirectionSample sample_emitter_direction(const Scene &s, const SI &ref, V
         index = std::min((uint32_t) scaled, (uint32_t) ne - 1u);
         emitter_weight = ecf; sample.x = scaled - (float) index;
     }
-    const Emitter &em = s.emitters[index]; const Mesh &m = s.meshes[em.mesh];
+    const Emitter &em = s.emitters[index];
+    if (em.type != 0) {
+        V3 spec(0.f);
+        if (em.type == 1) {                     // PointLight::sample_direction (point.cpp:117-148)
+            ds.p = em.position; ds.pdf = 1.f; ds.delta = true; ds.d = ds.p - ref.p;
+            const float dist2 = squared_norm(ds.d), inv_dist = rsqrt(dist2);
+            ds.dist = std::sqrt(dist2); ds.d = ds.d * inv_dist;
+            spec = em.radiance * sqr(inv_dist);
+        } else if (em.type == 2) {              // ConstantBackgroundEmitter::sample_direction (constant.cpp:120-150)
+            const V3 d = square_to_uniform_sphere(sample);
+            const float radius = fmax_(s.bs_radius, norm(ref.p - s.bs_center)), dist = 2.f * radius;
+            ds.p = fmadd(d, dist, ref.p); ds.n = -d; ds.pdf = InvFourPi; ds.d = d; ds.dist = dist;
+            spec = em.radiance / ds.pdf;
+        } else {                                // EnvironmentMapEmitter::sample_direction (envmap.cpp:419-462)
+            float pdf; V2 uv = s.env.warp.sample(sample, &pdf);
+            uv.x += .5f / (float) (s.env.res_x - 1u);
+            const bool act = pdf > 0.f;
+            const float theta = uv.y * Pi, phi = uv.x * (2.f * Pi);
+            float st_, ct_, sp_, cp_; sincos(theta, &st_, &ct_); sincos(phi, &sp_, &cp_);
+            V3 d(cp_ * st_, sp_ * st_, ct_); d = V3(d.y, d.z, -d.x);
+            const float radius = fmax_(s.bs_radius, norm(ref.p - s.bs_center)), dist = 2.f * radius;
+            const float inv_sin_theta = rsqrt(fmax_(fmax_(sqr(d.x) + sqr(d.z), sqr(Epsilon)), 0.f));
+            d = xf_vec3(s.env.to_world, d);
+            ds.p = ref.p + d * dist; ds.n = -d; ds.d = d; ds.dist = dist;
+            ds.pdf = act ? pdf * inv_sin_theta * (1.f / (2.f * (Pi * Pi))) : 0.f;
+            spec = mask3(s.env.eval_uv(uv) / ds.pdf, act);
+        }
+        ds.pdf *= 1.f / (float) ne;
+        spec = spec * emitter_weight;
+        if (ds.pdf != 0.f) {
+            bool occluded = scene_ray_test(s, spawn_ray_to(ref.p, ref.n, ds.p), brute, st);
+            if (occluded) { spec = V3(0.f); ds.pdf = 0.f; }
+        }
+        ds.valid = true; *spec_out = spec;
+        return ds;
+    }
+    const Mesh &m = s.meshes[em.mesh];
     // Mesh::sample_position: face by area on sample.y (sample_reuse, distr_1d.h:173-182)
     uint32_t face = distr_sample(m, sample.y);
     float pmf = m.pmf[face] * m.normalization, cdf = face > 0 ? m.cdf[face - 1] * m.normalization : 0.f;
@@ -358,6 +397,26 @@ static float pdf_emitter_direction(const Scene &s, const Mesh &em_mesh, V3 d, V3
 }
 // src/integrators/mvpath.h:306-311
 static inline float mis_weight(float a, float b) { a *= a; b *= b; float w = a / (a + b); return std::isfinite(w) ? w : 0.f; }
+
+// Emitter::eval / pdf_direction of the scene's environment emitter (constant.cpp:92-96, 152-157; envmap.cpp:308-320, 464-481) for an escaped
+// ray of direction d (= -si.wi of the invalid interaction, interaction.h:514)
+static inline V2 env_dir_to_uv(const Scene &s, V3 d, V3 *local) {
+    const V3 v = xf_vec3(s.env.from_world, d); *local = v;
+    return { atan2_(v.x, -v.z) * InvTwoPi, safe_acos(v.y) * InvPi };
+}
+static inline V3 env_eval(const Scene &s, V3 d) {
+    const Emitter &em = s.emitters[(size_t) s.env_emitter];
+    if (em.type == 2) return em.radiance;
+    V3 l; return s.env.eval_uv(env_dir_to_uv(s, d, &l));
+}
+static inline float env_pdf_direction(const Scene &s, V3 d) {
+    if (s.emitters[(size_t) s.env_emitter].type == 2) return InvFourPi;
+    V3 v; V2 uv = env_dir_to_uv(s, d, &v);
+    uv.x -= .5f / (float) (s.env.res_x - 1u);
+    uv.x -= std::floor(uv.x); uv.y -= std::floor(uv.y);
+    const float inv_sin_theta = rsqrt(fmax_(fmax_(sqr(v.x) + sqr(v.z), sqr(Epsilon)), 0.f));
+    return s.env.warp.eval(uv) * inv_sin_theta * (1.f / (2.f * (Pi * Pi)));
+}
 
 // ---------------------------------------------------------------- sensors
 // GridSensor::sample_ray (src/sensors/grid.cpp:238-267) -> PerspectiveCamera::sample_ray
@@ -422,7 +481,7 @@ struct PathResult { V3 L; bool valid; };
 static PathResult sample_single(const Scene &s, Pcg32 &rng, Ray ray, bool brute, Tap *tap, TraverseStats *st) {
     if (s.max_depth == 0) return { V3(0.f), false };
     V3 throughput(1.f), result(0.f); float eta = 1.f; uint32_t depth = 0;
-    bool valid_ray = false;             // !hide_emitters && environment != nullptr: no environment emitters on this path
+    bool valid_ray = !s.hide_emitters && s.env_emitter >= 0;      // :98
     V3 prev_p(0.f); float prev_bsdf_pdf = 1.f; bool prev_bsdf_delta = true, active = true;
     while (active) {
         Hit h = scene_intersect(s, ray, brute, st);
@@ -436,6 +495,12 @@ static PathResult sample_single(const Scene &s, Pcg32 &rng, Ray ray, bool brute,
             if (!prev_bsdf_delta) em_pdf = pdf_emitter_direction(s, *si.mesh, d, si.sh_n, dist, true);
             float mis_bsdf = mis_weight(prev_bsdf_pdf, em_pdf);
             V3 le = mask3(s.emitters[si.mesh->emitter].radiance, si.wi.z > 0.f && prev_bsdf_pdf > 0.f);   // area.cpp:82-86, vcall mask :162
+            result = fmadd(throughput, le * mis_bsdf, result);
+        } else if (!si.valid && s.env_emitter >= 0) {      // si.emitter(scene) = the environment (scene.h:647-657); ds.d = -si.wi (records.h:172-179)
+            float em_pdf = 0.f;
+            if (!prev_bsdf_delta) em_pdf = env_pdf_direction(s, ray.d) * (1.f / (float) s.emitters.size());
+            float mis_bsdf = mis_weight(prev_bsdf_pdf, em_pdf);
+            V3 le = mask3(env_eval(s, ray.d), prev_bsdf_pdf > 0.f);
             result = fmadd(throughput, le * mis_bsdf, result);
         }
         bool active_next = (depth + 1 < s.max_depth) && si.valid;
@@ -457,7 +522,7 @@ static PathResult sample_single(const Scene &s, Pcg32 &rng, Ray ray, bool brute,
         float s1 = rng.next_f32(); V2 s2; s2.x = rng.next_f32(); s2.y = rng.next_f32();
         BsdfResult br = bsdf_eval_pdf_sample(bsdf, si.wi, wo, s1, s2);
         if (active_em) {
-            float mis_em = mis_weight(ds.pdf, br.pdf);
+            float mis_em = ds.delta ? 1.f : mis_weight(ds.pdf, br.pdf);       // :217
             result = fmadd(throughput, br.f * em_weight * mis_em, result);
         }
         ray = spawn_ray(si.p, si.n, si.to_world(br.bs.wo));
@@ -491,6 +556,7 @@ static LaneOut render_lane(const Scene &s, uint32_t seed_value, uint32_t lane, u
     V2 adjusted = { fmadd(spx, sx, -0.f * sx), fmadd(spy, sy, -0.f * sy) };
     V2 aperture = { .5f, .5f };
     if (s.thinlens) { aperture.x = rng.next_f32(); aperture.y = rng.next_f32(); }
+    if (s.shutter_draw) (void) rng.next_f32();       // mvpath_single.h:66-68: time += next_1d() * shutter_open_time
     o.sample_pos[0] = spx; o.sample_pos[1] = spy;
     o.ray = sensor_sample_ray(s, adjusted, aperture, &o.view);
     if (trace) o.r = sample_single(s, rng, o.ray, brute, tap, st); else o.r = { V3(0.f), false };
@@ -659,6 +725,17 @@ void orc_set_sensor_explicit(void *sp, uint32_t n, uint32_t res_x, uint32_t res_
         c.near_clip = near_clip; c.far_clip = far_clip; c.aperture_radius = 0; c.focus_distance = far_clip; sensor_finish(c); s.sensors.push_back(c);
     }
 }
+// the sub-sensor table as a scene loader produced it (for scenes read from XML by the product): n = grid_x * grid_y records
+void orc_set_sensor_raw(void *sp, uint32_t grid_x, uint32_t grid_y, uint32_t view_w, uint32_t view_h, int reverse_x, int reverse_y, int thinlens,
+                        const float *s2c, const float *to_world, const float *scalars4) {
+    Scene &s = *(Scene *) sp; s.grid_x = grid_x; s.grid_y = grid_y; s.reverse_x = reverse_x; s.reverse_y = reverse_y; s.thinlens = thinlens;
+    s.film_w = view_w * grid_x; s.film_h = view_h * grid_y; s.sensors.clear();
+    for (uint32_t i = 0; i < grid_x * grid_y; ++i) {
+        SubSensor c; std::memcpy(c.s2c.m, s2c + 16 * i, 64); std::memcpy(c.to_world.m, to_world + 16 * i, 64);
+        c.near_clip = scalars4[4 * i]; c.far_clip = scalars4[4 * i + 1]; c.aperture_radius = scalars4[4 * i + 2]; c.focus_distance = scalars4[4 * i + 3];
+        sensor_finish(c); s.sensors.push_back(c);
+    }
+}
 void orc_get_sensor(void *sp, uint32_t i, float *s2c, float *to_world) {
     Scene &s = *(Scene *) sp; std::memcpy(s2c, s.sensors[i].s2c.m, 64); std::memcpy(to_world, s.sensors[i].to_world.m, 64);
 }
@@ -666,6 +743,51 @@ void orc_set_integrator(void *sp, int64_t max_depth, uint32_t rr_depth, int hide
     Scene &s = *(Scene *) sp;
     s.max_depth = max_depth < 0 ? 0xffffffffu : (uint32_t) max_depth;        // integrator.cpp:503-520
     s.rr_depth = rr_depth; s.hide_emitters = hide_emitters; s.base_seed = sampler_seed;
+}
+void orc_set_shutter_draw(void *sp, int draw) { ((Scene *) sp)->shutter_draw = draw; }
+// scene-level emitters (src/emitters/{point,constant,envmap}.cpp); the environment map is rebuilt here from the raw RGB pixels
+int orc_add_emitter_point(void *sp, const float *pos, const float *intensity) {
+    Scene &s = *(Scene *) sp; Emitter e; e.mesh = -1; e.type = 1; e.position = V3(pos[0], pos[1], pos[2]); e.radiance = V3(intensity[0], intensity[1], intensity[2]); s.emitters.push_back(e); return (int) s.emitters.size() - 1;
+}
+int orc_add_emitter_constant(void *sp, const float *radiance) {
+    Scene &s = *(Scene *) sp; Emitter e; e.mesh = -1; e.type = 2; e.radiance = V3(radiance[0], radiance[1], radiance[2]); s.emitters.push_back(e); s.env_emitter = (int) s.emitters.size() - 1; return s.env_emitter;
+}
+int orc_add_emitter_envmap(void *sp, const float *rgb, uint32_t w, uint32_t h, float scale, const float *to_world16) {
+    Scene &s = *(Scene *) sp; M4 tw; std::memcpy(tw.m, to_world16, 64); s.env.build(rgb, w, h, scale, tw);
+    Emitter e; e.mesh = -1; e.type = 3; e.radiance = V3(scale); s.emitters.push_back(e); s.env_emitter = (int) s.emitters.size() - 1; return s.env_emitter;
+}
+// puts the emitter list into the order given by (type, mesh) pairs -- the order of the scene description the product loaded
+void orc_order_emitters(void *sp, const int32_t *type, const int32_t *mesh, uint32_t n) {
+    Scene &s = *(Scene *) sp; std::vector<Emitter> out; std::vector<bool> used(s.emitters.size(), false);
+    for (uint32_t i = 0; i < n; ++i) for (size_t j = 0; j < s.emitters.size(); ++j)
+        if (!used[j] && s.emitters[j].type == type[i] && (type[i] != 0 || s.emitters[j].mesh == mesh[i])) { used[j] = true; out.push_back(s.emitters[j]); break; }
+    if (out.size() != s.emitters.size()) return;
+    s.emitters = out; s.env_emitter = -1;
+    for (size_t j = 0; j < s.emitters.size(); ++j) { if (s.emitters[j].type == 0) s.meshes[(size_t) s.emitters[j].mesh].emitter = (int) j; else if (s.emitters[j].type >= 2) s.env_emitter = (int) j; }
+}
+void orc_square_to_uniform_sphere(const float *u, int n, float *o) { for (int i = 0; i < n; ++i) { V3 v = square_to_uniform_sphere({ u[2 * i], u[2 * i + 1] }); o[3 * i] = v.x; o[3 * i + 1] = v.y; o[3 * i + 2] = v.z; } }
+void orc_square_to_bilinear(const float *v4, const float *u, int n, float *out2, float *pdf, float *pdf_eval) {
+    for (int i = 0; i < n; ++i) { const float *v = v4 + 4 * i; V2 p = square_to_bilinear(v[0], v[1], v[2], v[3], { u[2 * i], u[2 * i + 1] }, pdf + i);
+        out2[2 * i] = p.x; out2[2 * i + 1] = p.y; pdf_eval[i] = square_to_bilinear_pdf(v[0], v[1], v[2], v[3], p); }
+}
+// DiscreteDistribution over an unnormalised pmf exactly as the area CDF of a mesh is built and sampled (orc_add_mesh, sample_emitter_direction)
+void orc_discrete_sample_reuse(const float *pmf, uint32_t n_pmf, const float *u, int n, uint32_t *index, float *reused, float *pmf_out, float *sum_o, float *norm_o) {
+    Mesh m; m.faces.assign(3 * (size_t) n_pmf, 0u); m.pmf.assign(pmf, pmf + n_pmf); m.cdf.resize(n_pmf); double sum = 0.0;
+    for (uint32_t i = 0; i < n_pmf; ++i) { sum += (double) m.pmf[i]; m.cdf[i] = (float) sum; }
+    m.sum = m.cdf[n_pmf - 1]; m.normalization = rcp(m.sum); *sum_o = m.sum; *norm_o = m.normalization;
+    for (int i = 0; i < n; ++i) {
+        const uint32_t face = distr_sample(m, u[i]);
+        const float p = m.pmf[face] * m.normalization, c = face > 0 ? m.cdf[face - 1] * m.normalization : 0.f;
+        index[i] = face; pmf_out[i] = p; reused[i] = (u[i] - c) / p;
+    }
+}
+void orc_env_warp(void *sp, const float *u, int n, float *uv, float *pdf, float *eval_back) {      // taps: Hierarchical2D sample + eval
+    Scene &s = *(Scene *) sp;
+    for (int i = 0; i < n; ++i) { V2 r = s.env.warp.sample({ u[2 * i], u[2 * i + 1] }, pdf + i); uv[2 * i] = r.x; uv[2 * i + 1] = r.y; eval_back[i] = s.env.warp.eval(r); }
+}
+void orc_hier2d(const float *data, uint32_t sx, uint32_t sy, const float *u, int n, float *uv, float *pdf, float *eval_back) {
+    Hier2D h; h.build(data, sx, sy);
+    for (int i = 0; i < n; ++i) { V2 r = h.sample({ u[2 * i], u[2 * i + 1] }, pdf + i); uv[2 * i] = r.x; uv[2 * i + 1] = r.y; eval_back[i] = h.eval(r); }
 }
 // MVPathIntegrator sample reuse (mvpath.h:121-128) + the sample-size rule of MVPT::render (mvpath.cpp:17-22, 192-218).
 // Returns the number of samples per primary sample (0 = reuse off).
@@ -686,7 +808,15 @@ uint32_t orc_set_reuse(void *sp, int sa_reuse, int sa_mis, int fast_mis, uint32_
 // 4 catmullrom, 5 lanczos (param = lobes)
 void orc_set_rfilter(void *sp, int type, float param, float param2) { filter_setup(*(Scene *) sp, type, param, param2); }
 void orc_filter_eval(int type, float param, float param2, const float *x, int n, float *out) { Scene s; filter_setup(s, type, param, param2); for (int i = 0; i < n; ++i) out[i] = filter_eval(s, x[i]); }
-void orc_prepare(void *sp) { bvh_build(*(Scene *) sp); }
+void orc_prepare(void *sp) {
+    Scene &s = *(Scene *) sp; bvh_build(s);
+    // Scene::bbox().bounding_sphere() (bbox.h:113-115, 343-346) enlarged as in Emitter::set_scene (constant.cpp:73-88)
+    float lo[3] = { Inf, Inf, Inf }, hi[3] = { -Inf, -Inf, -Inf }; bool any = false;
+    for (auto &m : s.meshes) for (size_t i = 0; i + 2 < m.pos.size(); i += 3) for (int k = 0; k < 3; ++k) { lo[k] = fmin_(lo[k], m.pos[i + k]); hi[k] = fmax_(hi[k], m.pos[i + k]); any = true; }
+    if (!any) { s.bs_center = V3(0.f); s.bs_radius = RayEpsilon; return; }
+    s.bs_center = V3((hi[0] + lo[0]) * .5f, (hi[1] + lo[1]) * .5f, (hi[2] + lo[2]) * .5f);
+    s.bs_radius = fmax_(RayEpsilon, norm(s.bs_center - V3(hi[0], hi[1], hi[2])) * (1.f + RayEpsilon));
+}
 void orc_film_size(void *sp, uint32_t *w, uint32_t *h) { Scene &s = *(Scene *) sp; *w = s.film_w; *h = s.film_h; }
 uint32_t orc_num_prims(void *sp) { return ((Scene *) sp)->nprims(); }
 void orc_bvh_info(void *sp, uint32_t *n_nodes) { *n_nodes = (uint32_t) ((Scene *) sp)->nodes.size(); }
@@ -706,6 +836,7 @@ void orc_math1(int op, const float *in, int n, float *out) {
             case 2: r = exp_(x); break; case 3: r = log_(x); break; case 4: r = erf_(x); break; case 5: r = erfinv_(x); break;
             case 6: r = exp2_(x); break; case 7: r = std::sqrt(x); break; case 8: r = rcp(x); break; case 9: r = rsqrt(x); break;
             case 10: r = safe_sqrt(x); break; case 11: r = tan_(x); break;
+            case 12: r = acos_(x); break; case 13: r = atan2_(x, 0.3f); break; case 14: r = atan2_(0.3f, x); break; case 15: r = atan2_(x, -0.3f); break; case 16: r = safe_acos(x); break;
         }
         out[i] = r;
     }

@@ -340,6 +340,7 @@ template <typename Put> static void render_lane_multi(const Scene &s, uint32_t s
     V2 adjusted = { fmadd(spx, sx, -0.f * sx), fmadd(spy, sy, -0.f * sy) };
     V2 aperture = { .5f, .5f };
     if (s.thinlens) { aperture.x = rng.next_f32(); aperture.y = rng.next_f32(); }
+    if (s.shutter_draw) (void) rng.next_f32();       // mvpath_multi.h:21-23
     uint32_t p_idx; Ray ray = sensor_sample_ray(s, adjusted, aperture, &p_idx);
     SampleData samples[MaxReuse];
     uint32_t max_idx = n * (p_idx / n + 1u);

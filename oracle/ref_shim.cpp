@@ -22,6 +22,8 @@
 #include <mitsuba/core/warp.h>
 #include <mitsuba/core/transform.h>
 #include <mitsuba/core/frame.h>
+#include <mitsuba/core/distr_1d.h>
+#include <mitsuba/core/distr_2d.h>
 #include <mitsuba/render/fresnel.h>
 #include <mitsuba/render/microfacet.h>
 #include <mitsuba/render/sensor.h>
@@ -100,6 +102,11 @@ void ref_math1(int op, const float *in, int n, float *out) {
             case 8: r = dr::rcp(x); break;
             case 9: r = dr::rsqrt(x); break;
             case 10: r = dr::safe_sqrt(x); break;
+            case 12: r = dr::acos(x); break;
+            case 13: r = dr::atan2(x, F(0.3f)); break;
+            case 14: r = dr::atan2(F(0.3f), x); break;
+            case 15: r = dr::atan2(x, F(-0.3f)); break;
+            case 16: r = dr::safe_acos(x); break;
             default: r = x;
         }
         out[i] = g(r);
@@ -109,6 +116,34 @@ void ref_sincos(const float *in, int n, float *s, float *c) {
     for (int i = 0; i < n; ++i) {
         auto [ss, cc] = dr::sincos(F(in[i]));
         s[i] = g(ss); c[i] = g(cc);
+    }
+}
+
+// ---- Hierarchical2D<Float, 0> (include/mitsuba/core/distr_2d.h:344-775): the importance sampler of the environment map
+void ref_hier2d(const float *data, uint32_t sx, uint32_t sy, const float *u, int n, float *uv, float *pdf, float *eval_back) {
+    Hierarchical2D<F, 0> h(data, Vector<uint32_t, 2>(sx, sy));
+    for (int i = 0; i < n; ++i) {
+        auto [p, d] = h.sample(P2(F(u[2 * i]), F(u[2 * i + 1])));
+        uv[2 * i] = g(p.x()); uv[2 * i + 1] = g(p.y()); pdf[i] = g(d); eval_back[i] = g(h.eval(p));
+    }
+}
+// ---- DiscreteDistribution<Float> (include/mitsuba/core/distr_1d.h:25-290): the area CDF of Mesh::sample_position (sample_reuse_pmf)
+void ref_discrete_sample_reuse(const float *pmf, uint32_t n_pmf, const float *u, int n, uint32_t *index, float *reused, float *pmf_out, float *sum, float *normalization) {
+    DiscreteDistribution<F> d(pmf, n_pmf);
+    *sum = g(F(d.sum())); *normalization = g(F(d.normalization()));
+    for (int i = 0; i < n; ++i) {
+        auto [idx, r, p] = d.sample_reuse_pmf(F(u[i]));
+        index[i] = idx.entry(0); reused[i] = g(r); pmf_out[i] = g(p);
+    }
+}
+void ref_square_to_uniform_sphere(const float *u, int n, float *out) {
+    for (int i = 0; i < n; ++i) st3(out + 3 * i, warp::square_to_uniform_sphere(P2(F(u[2 * i]), F(u[2 * i + 1]))));
+}
+void ref_square_to_bilinear(const float *v4, const float *u, int n, float *out2, float *pdf, float *pdf_eval) {
+    for (int i = 0; i < n; ++i) {
+        F a(v4[4 * i]), b(v4[4 * i + 1]), c(v4[4 * i + 2]), d(v4[4 * i + 3]);
+        auto [p, q] = warp::square_to_bilinear(a, b, c, d, P2(F(u[2 * i]), F(u[2 * i + 1])));
+        out2[2 * i] = g(p.x()); out2[2 * i + 1] = g(p.y()); pdf[i] = g(q); pdf_eval[i] = g(warp::square_to_bilinear_pdf(a, b, c, d, p));
     }
 }
 

@@ -103,6 +103,30 @@ def main():
     ref.ref_moeller_trumbore(P(oo), P(dd), P(mx), P(p0), P(p1), P(p2), C.c_int(n), P(tuv), P(hit, i32p))
     g["moeller_trumbore"] = dict(o=u(oo), d=u(dd), p0=u(p0), p1=u(p1), p2=u(p2), tuv=u(tuv), hit=hit.tolist())
     g["constants"] = [float(ref.ref_const(C.c_int(i))) for i in range(6)]
+    # ---- round 2 additions (appended so that the seeded inputs above stay what they were)
+    for op, r in {12: (-1, 1), 13: (-3, 3), 14: (-3, 3), 15: (-3, 3), 16: (-1.5, 1.5)}.items():       # acos, atan2 (three argument patterns), safe_acos
+        x = rng.uniform(r[0], r[1], n).astype(np.float32); x[:6] = [0, 1, -1, 0.5, -0.5, 0.3]
+        o = np.zeros(n, np.float32); ref.ref_math1(C.c_int(op), P(x), C.c_int(n), P(o)); g["math1"][str(op)] = dict(x=u(x), y=u(o))
+    ref.ref_square_to_uniform_sphere(P(u2), C.c_int(n), P(o3)); g["uniform_sphere"] = dict(y=u(o3))
+    v4 = np.ascontiguousarray(rng.uniform(0.01, 2, (n, 4)), np.float32); v4[:20, 1] = v4[:20, 0]; v4[:20, 3] = v4[:20, 2]      # some flat patches
+    pe = np.zeros(n, np.float32); ref.ref_square_to_bilinear(P(v4), P(u2), C.c_int(n), P(o2), P(o1), P(pe)); g["bilinear"] = dict(v=u(v4), y=u(o2), pdf=u(o1), pdf_eval=u(pe))
+    # Hierarchical2D<Float, 0> over an odd-sized positive array (the envmap's importance sampler): sample, its pdf, eval at the sample
+    sx, sy = 37, 21; data = np.ascontiguousarray(rng.uniform(0, 1, (sy, sx)) ** 4, np.float32); hu = np.ascontiguousarray(rng.uniform(size=(400, 2)), np.float32)
+    huv = np.zeros((400, 2), np.float32); hp = np.zeros(400, np.float32); he = np.zeros(400, np.float32)
+    ref.ref_hier2d(P(data), C.c_uint32(sx), C.c_uint32(sy), P(hu), C.c_int(400), P(huv), P(hp), P(he))
+    g["hier2d"] = dict(sx=sx, sy=sy, data=u(data), u=u(hu), uv=u(huv), pdf=u(hp), eval=u(he))
+    # DiscreteDistribution<Float>::sample_reuse_pmf (the area CDF of Mesh::sample_position), unnormalised pmf with zero entries
+    pmf = np.ascontiguousarray(rng.uniform(0, 3, 73) ** 2, np.float32); pmf[[0, 7, 8, 72]] = 0; du = np.ascontiguousarray(rng.uniform(size=n), np.float32); du[:3] = [0, 0.5, 0.99999994]
+    di = np.zeros(n, np.uint32); dr_ = np.zeros(n, np.float32); dp = np.zeros(n, np.float32); ds = np.zeros(1, np.float32); dn = np.zeros(1, np.float32)
+    ref.ref_discrete_sample_reuse(P(pmf), C.c_uint32(len(pmf)), P(du), C.c_int(n), P(di, u32p), P(dr_), P(dp), P(ds), P(dn))
+    g["discrete"] = dict(pmf=u(pmf), u=u(du), index=di.tolist(), reused=u(dr_), pmf_out=u(dp), sum=u(ds), normalization=u(dn))
+    # GridSensor placement (src/sensors/grid.cpp:208-226): inverse(transpose(inverse_transpose + offset row)) for 8 cameras on a line
+    tw = np.eye(4, dtype=np.float32); tw[:3, 3] = [278, 273, -800]; tw[0, 0] = tw[2, 2] = -1
+    it = np.ascontiguousarray(np.linalg.inv(tw.astype(np.float64)).T, np.float32); mats = []
+    for i in range(8):
+        dt = np.float32(i) / np.float32(7); off = np.array([np.float32(1) * (np.float32(400) * (dt - np.float32(0.5))), 0, 0], np.float32); om = np.zeros(16, np.float32)   # grid.cpp:209-210 in float32
+        ref.ref_grid_to_world(P(tw), P(it), P(off), P(om)); mats.append(dict(offset=u(off), m=u(om)))
+    g["grid_to_world"] = dict(inv_t=u(it), mats=mats)
     json.dump(g, open(os.path.join(ROOT, "tests", "golden", "reference_vectors.json"), "w"))
     print("wrote", len(g), "entries")
 

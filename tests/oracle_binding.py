@@ -96,6 +96,40 @@ class OracleScene:
                 self.set_reuse(**desc["reuse"])
             self.prepare()
 
+    @classmethod
+    def from_product(cls, scene):
+        """The same scene the product holds (e.g. loaded from XML by amvpt_scene_from_xml): meshes, BSDF parameters, emitters in scene order,
+        the raw environment-map pixels, the sub-sensor table and the integrator parameters go to the oracle, which rebuilds everything
+        derived (area CDFs, roughplastic tables, environment hierarchy, bounding sphere, its own BVH) by itself."""
+        o = cls(); c = scene.counts()
+        for i in range(c["n_bsdfs"]):
+            b = scene.bsdf(i); b["alpha_u"], b["alpha_v"] = float(b["alpha_u"]), float(b["alpha_v"]); o.add_bsdf(**b)
+        for i in range(c["n_meshes"]):
+            m = scene.mesh(i); o.add_mesh(m["positions"], m["faces"], m["bsdf"], m["normals"], m["radiance"], m["flip_normals"])
+        ems = scene.emitters(); tmap = {"area": 0, "point": 1, "constant": 2, "envmap": 3}
+        for e in ems:
+            if e["type"] == "point":
+                o.o.orc_add_emitter_point(o.h, _p(np.ascontiguousarray(e["position"], np.float32)), _p(np.ascontiguousarray(e["radiance"], np.float32)))
+            elif e["type"] == "constant":
+                o.o.orc_add_emitter_constant(o.h, _p(np.ascontiguousarray(e["radiance"], np.float32)))
+            elif e["type"] == "envmap":
+                env = scene.envmap(); rgb = np.ascontiguousarray(env["rgb"], np.float32); tw = np.ascontiguousarray(env["to_world"], np.float32)
+                o.o.orc_add_emitter_envmap(o.h, _p(rgb), C.c_uint32(rgb.shape[1]), C.c_uint32(rgb.shape[0]), C.c_float(env["scale"]), _p(tw))
+        ty = np.array([tmap[e["type"]] for e in ems], np.int32); me = np.array([e["mesh"] for e in ems], np.int32)
+        o.o.orc_order_emitters(o.h, ty.ctypes.data_as(C.POINTER(C.c_int32)), me.ctypes.data_as(C.POINTER(C.c_int32)), C.c_uint32(len(ems)))
+        info = scene.info(); sp0 = scene.sensor_params(0); n = info["n_views"]
+        s2c = np.zeros((n, 16), np.float32); tw = np.zeros((n, 16), np.float32); sc = np.zeros((n, 4), np.float32)
+        for i in range(n):
+            a, b = scene.sensor(i); s2c[i] = a.reshape(16); tw[i] = b.reshape(16); q = scene.sensor_params(i)
+            sc[i] = [q["near_clip"], q["far_clip"], q["aperture_radius"], q["focus_distance"]]
+        o.o.orc_set_sensor_raw(o.h, C.c_uint32(sp0["grid_x"]), C.c_uint32(sp0["grid_y"]), C.c_uint32(info["film_w"] // sp0["grid_x"]), C.c_uint32(info["film_h"] // sp0["grid_y"]),
+                               C.c_int(int(sp0["reverse_x"])), C.c_int(int(sp0["reverse_y"])), C.c_int(int(sp0["thinlens"])), _p(s2c), _p(tw), _p(sc))
+        ig = scene.integrator()
+        o.set_integrator(max_depth=ig["max_depth"], rr_depth=ig["rr_depth"], hide_emitters=ig["hide_emitters"], spp_pass_lim=ig["spp_pass_lim"], sampler_seed=ig["sampler_seed"])
+        o.o.orc_set_shutter_draw(o.h, C.c_int(int(scene.shutter_draw())))
+        o.prepare()
+        return o
+
     def __del__(self):
         if getattr(self, "h", None):
             self.o.orc_scene_free(self.h); self.h = None

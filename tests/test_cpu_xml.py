@@ -159,8 +159,14 @@ def test_xml_errors(pkg, tmp_path):
         pkg.load_string('<scene version="3.0.0"><shape type="cube"></scene>')
     with pytest.raises(pkg.AmvptError, match="transmission"):                   # twosided.cpp:101-102
         load(sensor + '<shape type="cube"><bsdf type="twosided"><bsdf type="dielectric"/></bsdf></shape>')
-    with pytest.raises(pkg.AmvptError, match="wavelength"):
-        load(sensor + '<shape type="cube"><bsdf type="diffuse"><spectrum name="reflectance" value="400:0.1, 700:0.2"/></bsdf></shape>')
+    # wavelength spectra are integrated to sRGB (src/core/xml.cpp:777-833, 1170-1268); malformed pairs raise
+    sp = load(sensor + '<shape type="cube"><bsdf type="diffuse"><spectrum name="reflectance" value="400:0.1, 700:0.2"/></bsdf></shape>')
+    refl = sp.bsdf(sp.mesh(0)["bsdf"])["reflectance"]
+    assert 0.1 < min(refl) and max(refl) < 0.2 and refl[0] > refl[2]                           # a ramp rising towards red
+    with pytest.raises(pkg.AmvptError, match="invalid spectrum"):
+        load(sensor + '<shape type="cube"><bsdf type="diffuse"><spectrum name="reflectance" value="400:0.1:3, 700:0.2"/></bsdf></shape>')
+    with pytest.raises(pkg.AmvptError, match="increasing order"):
+        load(sensor + '<shape type="cube"><bsdf type="diffuse"><spectrum name="reflectance" value="700:0.1, 400:0.2"/></bsdf></shape>')
     with pytest.raises(pkg.AmvptError, match="divisible"):                      # grid.cpp:100-101
         load('<sensor type="grid"><integer name="grid_x" value="3"/><integer name="res_x" value="16"/><integer name="res_y" value="8"/>'
              '<wrap type="any"><string name="wrap_class" value="sensor"/><string name="wrap_type" value="perspective"/></wrap>'
