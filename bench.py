@@ -198,7 +198,7 @@ def roofline(pkg, s, args, spp, sched_arg, clk, device):
         inst_rate = m["inst_executed"] * scale / per_launch_s / 1e9
         out.update({"issue_util": inst_rate / issue_peak, "issue_util_ncu": m.get("issue_active_pct", 0.0) / 100.0,
                     "warp_exec_eff": m["thread_inst_executed"] / m["inst_executed"] / 32.0, "lanes_per_inst": m["thread_inst_executed"] / m["inst_executed"],
-                    "l2_bytes_per_launch": m.get("lts_bytes", 0) * scale, "l2_hit_pct": m.get("l2_hit_pct"), "l1_hit_pct": m.get("l1_hit_pct"),
+                    "l2_bytes_per_launch": (m.get("lts_bytes") or 0) * scale, "l2_hit_pct": m.get("l2_hit_pct"), "l1_hit_pct": m.get("l1_hit_pct"),
                     "long_scoreboard_per_issue": m.get("long_scoreboard"), "ncu_source": m.get("source"), "ncu_workload": m.get("workload")})
         if bound == "issue":
             out.update({"achieved": inst_rate, "peak": issue_peak, "unit": "Gwarp-inst/s", "frac": inst_rate / issue_peak})

@@ -163,7 +163,7 @@ int amvpt_scene_set_integrator(amvpt_scene *h, const amvpt_integrator_desc *d) {
         ip.max_depth = d->max_depth; ip.rr_depth = d->rr_depth; ip.hide_emitters = d->hide_emitters != 0; ip.spp_pass_lim = d->spp_pass_lim;
         if (ip.rr_depth == 0) AM_THROW("\"rr_depth\" must be set to a value greater than zero!");                              // integrator.cpp:517-518
         h->s->sampler_seed = d->sampler_seed; if (d->sample_count) h->s->sample_count = d->sample_count;
-        if (h->s->committed) { h->s->d.max_depth = ip.max_depth < 0 ? 0xffffffffu : (uint32_t) ip.max_depth; h->s->d.rr_depth = ip.rr_depth; }
+        if (h->s->committed) { h->s->d.max_depth = ip.max_depth < 0 ? 0xffffffffu : (uint32_t) ip.max_depth; h->s->d.rr_depth = ip.rr_depth; h->s->d.hide_emitters = ip.hide_emitters ? 1 : 0; }
         return AMVPT_OK; });
 }
 int amvpt_scene_set_reuse(amvpt_scene *h, int sa_reuse, int sa_mis, int fast_mis, uint32_t reuse_count, uint32_t adaptive, uint32_t *n_samples) {

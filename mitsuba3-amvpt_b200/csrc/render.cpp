@@ -115,7 +115,7 @@ void render(Scene &s, const RenderOptions &opt) {
                 float4 **f4s[] = { &w.ro, &w.rd, &w.tp, &w.res, &w.pp, &w.hit, &w.so, &w.sd, &w.sT, &w.sV };
                 for (float4 **a : f4s) *a = (float4 *) s.dalloc(sizeof(float4) * n);
                 w.rng = (uint4 *) s.dalloc(sizeof(uint4) * n); w.flags = (uint32_t *) s.dalloc(sizeof(uint32_t) * n); w.spos = (float2 *) s.dalloc(sizeof(float2) * n);
-                w.queue = (uint32_t *) s.dalloc(sizeof(uint32_t) * 7 * (size_t) n);      // six BSDF-type queues + the escaped-ray queue w.qcount = (uint32_t *) s.dalloc(sizeof(uint32_t) * 8);
+                w.queue = (uint32_t *) s.dalloc(sizeof(uint32_t) * 7 * (size_t) n); w.qcount = (uint32_t *) s.dalloc(sizeof(uint32_t) * 8);      // six BSDF-type queues + the escaped-ray queue
                 w.live = (uint32_t *) s.dalloc(sizeof(uint32_t) * 64);
                 s.wf_type_mask = 0; for (auto &m : s.meshes) s.wf_type_mask |= 1u << s.bsdfs[m.bsdf].type;
             }
