@@ -186,3 +186,47 @@ def test_product_grid_placement_matches_reference_headers(pkg, scenes):
     for i, mrec in enumerate(g["mats"]):
         _, m = s.sensor(i)
         same(m[:3], np.array(mrec["m"], np.uint32).reshape(4, 4)[:3], f"product sub-camera {i} to_world")
+
+
+# ------------------------------------------------------------------ chi-square tests of BSDF sampling (the reference's own method)
+CHI2_CASES = {
+    # src/bsdfs/tests/test_diffuse.py:13-36, test_rough_conductor.py:60-96, test_rough_dielectric.py, test_rough_plastic.py:14-39
+    "diffuse": (dict(type="diffuse", reflectance=(0.5, 0.5, 0.5)), (0, 0, 1), {}),
+    "roughconductor_beckmann_iso": (dict(type="roughconductor", distribution="beckmann", alpha=0.5, eta=(0.2, 0.92, 1.1), k=(3.9, 2.45, 2.14)), (0.3, 0.1, 0.9), {}),
+    "roughconductor_ggx_aniso": (dict(type="roughconductor", distribution="ggx", alpha_u=0.25, alpha_v=0.5, eta=(0.2, 0.92, 1.1), k=(3.9, 2.45, 2.14)), (0.6, 0.0, 0.8), {}),
+    "roughdielectric_beckmann_outside": (dict(type="roughdielectric", distribution="beckmann", alpha=0.5, int_ior=1.5, ext_ior=1.0), (0.3, 0.2, 0.93), dict(ires=8, transmissive=True)),
+    "roughdielectric_ggx_inside": (dict(type="roughdielectric", distribution="ggx", alpha=0.5, int_ior=1.5, ext_ior=1.0), (0.2, 0.1, -0.97), dict(ires=8, transmissive=True)),
+    "roughplastic_beckmann": (dict(type="roughplastic", distribution="beckmann", alpha=0.25, reflectance=(0.1, 0.1, 0.1), specular_reflectance=(0.7, 0.7, 0.7)), (0, 0, 1), {}),
+    "roughplastic_ggx_slanted": (dict(type="roughplastic", distribution="ggx", alpha=0.3, reflectance=(0.5, 0.3, 0.1)), (0.7, 0.1, 0.7), {}),
+}
+
+
+def chi2_scene(scenes, cfg):
+    desc = scenes.cornell_box(grid_x=2, grid_y=1, view_res=8)
+    desc["bsdfs"] = [cfg]
+    for m in desc["meshes"]:
+        m["bsdf"] = 0
+    return desc
+
+
+@pytest.mark.parametrize("name", sorted(CHI2_CASES))
+def test_oracle_bsdf_sampling_chi2(ob, scenes, name):
+    from chi2 import bsdf_chi2
+    cfg, wi, kw = CHI2_CASES[name]
+    o = ob.OracleScene(chi2_scene(scenes, cfg))
+    p, info = bsdf_chi2(lambda a, b, c, d: o.bsdf_eval_pdf_sample(0, a, b, c, d), wi, **kw)
+    alpha = 1.0 - (1.0 - 0.01) ** (1.0 / len(CHI2_CASES))             # Sidak correction over the cases (chi2.py:239-254, test_count)
+    assert p > alpha, f"{name}: chi^2 rejects sample() against pdf(): p = {p:.3g}, {info}"
+    assert abs(info["hist_sum"] - info["pdf_sum"]) < 5e-3
+
+
+def test_chi2_has_power(ob, scenes):
+    """The harness rejects a sampler whose density is off: roughconductor sampled with alpha 0.5, density tabulated with alpha 0.45."""
+    from chi2 import bsdf_chi2
+    a = ob.OracleScene(chi2_scene(scenes, dict(type="roughconductor", distribution="ggx", alpha=0.5, eta=(0.2, 0.92, 1.1), k=(3.9, 2.45, 2.14))))
+    b = ob.OracleScene(chi2_scene(scenes, dict(type="roughconductor", distribution="ggx", alpha=0.45, eta=(0.2, 0.92, 1.1), k=(3.9, 2.45, 2.14))))
+
+    def mixed(wi, wo, s1, s2):
+        r = a.bsdf_eval_pdf_sample(0, wi, wo, s1, s2); r["pdf"] = b.bsdf_eval_pdf_sample(0, wi, wo, s1, s2)["pdf"]; return r
+    p, _ = bsdf_chi2(mixed, (0.3, 0.1, 0.9))
+    assert p < 1e-6

@@ -152,3 +152,18 @@ def test_lane_windows_of_cbox8x8_pass(scenes, ob, gpu):
     # the pass seeds of the full render: seed_value = sampler seed + spp_per_pass * pass + render seed (mvpath.cpp:226-231)
     a = s.trace_lanes(16 * 15, 16, total - n, n); b = o.trace_lanes(16 * 15, 16, total - n, n, brute=True)
     assert_bits(a["radiance"], b["radiance"], "cbox8x8 last pass, last lanes")
+
+
+# ------------------------------------------------------------------ chi-square tests of BSDF sampling through the C ABI (reference method, tests/chi2.py)
+from test_cpu_golden import CHI2_CASES, chi2_scene
+
+
+@pytest.mark.parametrize("name", sorted(CHI2_CASES))
+def test_gpu_bsdf_sampling_chi2(scenes, gpu, name):
+    from chi2 import bsdf_chi2
+    cfg, wi, kw = CHI2_CASES[name]
+    s = scenes.build(chi2_scene(scenes, cfg), device=gpu)
+    p, info = bsdf_chi2(lambda a, b, c, d: s.bsdf_eval_pdf_sample(0, a, b, c, d), wi, **kw)
+    alpha = 1.0 - (1.0 - 0.01) ** (1.0 / len(CHI2_CASES))
+    assert p > alpha, f"{name}: chi^2 rejects amvpt_bsdf_eval_pdf_sample's sample against its pdf: p = {p:.3g}, {info}"
+    assert abs(info["hist_sum"] - info["pdf_sum"]) < 5e-3
