@@ -184,6 +184,7 @@ int amvpt_display_last_ms(amvpt_scene *s, float *srgb8_ms, float *interlace_ms);
 int amvpt_trace_lanes(amvpt_scene *s, uint32_t seed_value, uint32_t spp_per_pass, uint32_t lane_begin, uint32_t n, int trace,
                       float *sample_pos, float *ray_o, float *ray_d, float *ray_maxt, uint32_t *view, float *radiance,
                       uint32_t *pixel, uint32_t max_hits, uint32_t *hit_prim, float *hit_t, uint64_t *stats2);
+/* any_hit: bit 0 = Scene::ray_test semantics (first accepted triangle), bit 1 = walk the compressed 4-wide tree of the wavefront trace stage */
 int amvpt_intersect(amvpt_scene *s, const float *o, const float *d, const float *maxt, uint32_t n, int any_hit,
                     uint32_t *prim, float *tuv, uint64_t *stats2);
 int amvpt_bsdf_eval_pdf_sample(amvpt_scene *s, int bsdf, const float *wi, const float *wo, const float *s1, const float *s2, uint32_t n,
@@ -204,6 +205,9 @@ int amvpt_sampler_stream(int device, uint32_t seed_value, uint32_t lane, uint32_
 int amvpt_membench(int device, int kind, uint64_t bytes, uint32_t iters, double *gb_per_s);
 /* host-side checks of the BVH the kernels traverse: every triangle inside its leaf box, every child box inside its parent */
 int amvpt_bvh_validate(amvpt_scene *s, uint32_t *max_depth, uint32_t *n_leaves);
+/* the same for the compressed 4-wide tree of the wavefront trace stage: every triangle inside the decoded box of every slot above it;
+ * *n_nodes = 0 when the scene has no such tree (a single leaf) */
+int amvpt_bvh_q4_validate(amvpt_scene *s, uint32_t *n_nodes, uint32_t *max_depth, uint32_t *n_leaves);
 
 #ifdef __cplusplus
 }

@@ -79,7 +79,7 @@ EXPORTS = ["amvpt_last_error", "amvpt_device_count", "amvpt_scene_create", "amvp
            "amvpt_scene_get_bsdf", "amvpt_scene_get_integrator", "amvpt_render", "amvpt_shard_tiles", "amvpt_view_tiles", "amvpt_cancel", "amvpt_film_clear",
            "amvpt_film_raw", "amvpt_film_develop", "amvpt_film_develop_device", "amvpt_film_device_ptr", "amvpt_film_add_host",
            "amvpt_trace_lanes", "amvpt_trace_lanes_multi", "amvpt_intersect", "amvpt_bsdf_eval_pdf_sample", "amvpt_math1", "amvpt_sampler_stream",
-           "amvpt_bvh_validate", "amvpt_membench", "amvpt_film_write_pfm", "amvpt_film_write_exr", "amvpt_f32_to_f16", "amvpt_film_to_srgb8", "amvpt_interlace", "amvpt_display_last_ms"]
+           "amvpt_bvh_validate", "amvpt_bvh_q4_validate", "amvpt_membench", "amvpt_film_write_pfm", "amvpt_film_write_exr", "amvpt_f32_to_f16", "amvpt_film_to_srgb8", "amvpt_interlace", "amvpt_display_last_ms"]
 lib.amvpt_scene_destroy.restype = None
 lib.amvpt_scene_destroy.argtypes = [C.c_void_p]
 
@@ -296,6 +296,11 @@ class Scene:
         _chk(lib.amvpt_bvh_validate(self._h, C.byref(d), C.byref(n)))
         return d.value, n.value
 
+    def bvh_q4_validate(self):
+        n, d, l = C.c_uint32(), C.c_uint32(), C.c_uint32()
+        _chk(lib.amvpt_bvh_q4_validate(self._h, C.byref(n), C.byref(d), C.byref(l)))
+        return n.value, d.value, l.value
+
     # ---- the hot path: Integrator.render(scene, sensor, seed, spp, develop, evaluate)
     def render(self, seed=0, spp=0, develop=True, scheduler="auto", stats=False, rank=0, world=1, adaptive=False,
                adaptive_threshold=0.0, adaptive_min_spp=16, stream=None, allreduce=None, clear=True, time_stages=False):
@@ -390,10 +395,10 @@ class Scene:
         o["stats"] = stats
         return o
 
-    def intersect(self, o, d, maxt, any_hit=False):
+    def intersect(self, o, d, maxt, any_hit=False, q4=False):
         o = _f32(o, (-1, 3)); d = _f32(d, (-1, 3)); maxt = _f32(maxt, (-1,)); n = len(o)
         prim = np.zeros(n, np.uint32); tuv = np.zeros((n, 3), np.float32); stats = np.zeros(2, np.uint64)
-        _chk(lib.amvpt_intersect(self._h, _p(o), _p(d), _p(maxt), C.c_uint32(n), C.c_int(int(any_hit)), _p(prim, u32p), _p(tuv), _p(stats, u64p)))
+        _chk(lib.amvpt_intersect(self._h, _p(o), _p(d), _p(maxt), C.c_uint32(n), C.c_int(int(any_hit) | (2 if q4 else 0)), _p(prim, u32p), _p(tuv), _p(stats, u64p)))
         return prim, tuv, stats
 
     def bsdf_eval_pdf_sample(self, bsdf, wi, wo, s1, s2):

@@ -119,6 +119,67 @@ void build_bvh(const Scene &s, float scene_scale, BvhOut &out) {
         }
     }
     auto leaf_code = [&](const TNode &n) -> int32_t { return (int32_t) ~((n.first << 3) | n.count); };
+    // ---- compressed 4-wide tree over the same leaves (DScene::nodes_q4, the wavefront trace stage): the binary tree is collapsed (a
+    // node's two children, then repeatedly the inner child with the largest surface is replaced by its own two children until four
+    // slots are used), and the child boxes are quantised to 8 bits per plane on a power-of-two grid anchored at the node's own box
+    // corner -- lower planes rounded down, upper planes rounded up, checked against the decoded value, so the boxes only grow.
+    out.nodes_q4.clear(); out.depth_q4 = 0;
+    if (np && bl.nodes[0].left >= 0) {
+        struct Wide { int32_t kid[4]; int n; };
+        std::vector<Wide> wide; std::vector<int32_t> wide_of(bl.nodes.size(), -1); uint32_t depth4 = 0;
+        std::function<void(int32_t, uint32_t)> build_wide = [&](int32_t t, uint32_t depth) {
+            depth4 = std::max(depth4, depth + 1);
+            const int32_t id = (int32_t) wide.size(); wide.push_back(Wide{ { -1, -1, -1, -1 }, 0 }); wide_of[t] = id;
+            int32_t kids[4]; int n = 0; kids[n++] = bl.nodes[t].left; kids[n++] = bl.nodes[t].right;
+            while (n < 4) {
+                int best = -1; float area = -1.f;
+                for (int i = 0; i < n; ++i) if (bl.nodes[kids[i]].left >= 0 && bl.nodes[kids[i]].b.half_area() > area) { area = bl.nodes[kids[i]].b.half_area(); best = i; }
+                if (best < 0) break;
+                const int32_t k = kids[best]; kids[best] = bl.nodes[k].left; kids[n++] = bl.nodes[k].right;
+            }
+            Wide w; w.n = n; for (int i = 0; i < 4; ++i) w.kid[i] = i < n ? kids[i] : -1;
+            wide[(size_t) id] = w;
+            for (int i = 0; i < n; ++i) if (bl.nodes[kids[i]].left >= 0) build_wide(kids[i], depth + 1);
+        };
+        build_wide(0, 0);
+        if (3 * depth4 + 2 <= AM_STACK_SIZE) {
+            out.depth_q4 = depth4; out.nodes_q4.assign(4 * wide.size(), make_uint4(0u, 0u, 0u, 0u));
+            for (size_t id = 0; id < wide.size(); ++id) {
+                const Wide &w = wide[id]; Box nb; for (int i = 0; i < w.n; ++i) nb.grow(bl.nodes[w.kid[i]].b);
+                uint32_t e[3], qlo[3][4], qhi[3][4]; int32_t ref[4] = { 0, 0, 0, 0 };
+                for (int a = 0; a < 3; ++a) {
+                    // smallest power of two with 255 * scale >= extent (one more step if rounding makes the last plane fall short)
+                    const float ext = nb.hi[a] - nb.lo[a]; int ex = 0; std::frexp(ext / 255.f, &ex);     // ext / 255 = m * 2^ex, m in [0.5, 1)
+                    if (!(ext > 0.f)) ex = -120;
+                    ex = std::min(std::max(ex, -120), 120);
+                    for (;;) {
+                        const float scale = std::ldexp(1.f, ex); bool ok = true;
+                        for (int i = 0; i < 4 && ok; ++i) {
+                            if (i >= w.n) { qlo[a][i] = 255u; qhi[a][i] = 0u; continue; }      // empty slot: inverted box, never hit
+                            const Box &kb = bl.nodes[w.kid[i]].b;
+                            float fl = std::floor((kb.lo[a] - nb.lo[a]) / scale), fh = std::ceil((kb.hi[a] - nb.lo[a]) / scale);
+                            fl = std::min(std::max(fl, 0.f), 255.f); fh = std::min(std::max(fh, 0.f), 255.f);
+                            while (fl > 0.f && std::fma(fl, scale, nb.lo[a]) > kb.lo[a]) fl -= 1.f;
+                            while (fh < 255.f && std::fma(fh, scale, nb.lo[a]) < kb.hi[a]) fh += 1.f;
+                            if (std::fma(fl, scale, nb.lo[a]) > kb.lo[a] || std::fma(fh, scale, nb.lo[a]) < kb.hi[a]) ok = false;
+                            qlo[a][i] = (uint32_t) fl; qhi[a][i] = (uint32_t) fh;
+                        }
+                        if (ok) break;
+                        ++ex;
+                    }
+                    e[a] = (uint32_t) (ex + 127);
+                }
+                for (int i = 0; i < w.n; ++i) { const TNode &k = bl.nodes[w.kid[i]]; ref[i] = k.left < 0 ? leaf_code(k) : wide_of[w.kid[i]]; }
+                auto pack = [](const uint32_t *q) { return q[0] | (q[1] << 8) | (q[2] << 16) | (q[3] << 24); };
+                uint32_t ob[3]; memcpy(ob, nb.lo, 12);
+                uint4 *o = &out.nodes_q4[4 * id];
+                o[0] = make_uint4(ob[0], ob[1], ob[2], e[0] | (e[1] << 8) | (e[2] << 16));
+                o[1] = make_uint4(pack(qlo[0]), pack(qlo[1]), pack(qlo[2]), pack(qhi[0]));
+                o[2] = make_uint4(pack(qhi[1]), pack(qhi[2]), (uint32_t) ref[0], (uint32_t) ref[1]);
+                o[3] = make_uint4((uint32_t) ref[2], (uint32_t) ref[3], 0u, 0u);
+            }
+        }
+    }
 #if AM_BVH_WIDTH == 4
     // Collapse the binary tree into 4-wide nodes: start from a node's two children and keep replacing the inner child with
     // the largest surface by its own two children until four slots are used (or only leaves remain).  Nodes are numbered in

@@ -3,6 +3,8 @@
 #include "host.h"
 #include <cstring>
 #include <functional>
+#include <cfloat>
+#include <cmath>
 
 using namespace amvpt;
 
@@ -455,6 +457,44 @@ int amvpt_membench(int device, int kind, uint64_t bytes, uint32_t iters, double 
         const double v = run_membench_read((size_t) bytes, iters, sms, nullptr);
         if (v < 0.0) AM_THROW("CUDA error: membench failed (%s)", cudaGetErrorString(cudaGetLastError()));
         *gb_per_s = v; return AMVPT_OK; });
+}
+int amvpt_bvh_q4_validate(amvpt_scene *h, uint32_t *n_nodes, uint32_t *max_depth, uint32_t *n_leaves) {
+    return guard([&] { NEED(h); Scene &s = *h->s; s.prepare_host();
+        const std::vector<uint4> &q = s.bvh.nodes_q4;
+        if (n_nodes) *n_nodes = (uint32_t) (q.size() / 4);
+        uint32_t leaves = 0, maxd = 0; std::vector<uint8_t> seen(s.bvh.tris.size() / 3, 0);
+        if (q.empty()) { if (max_depth) *max_depth = 0; if (n_leaves) *n_leaves = 0; return AMVPT_OK; }
+        // every triangle under a child slot must lie inside that slot's decoded box (origin + q * 2^(e - 127), evaluated as the kernel does)
+        struct B { float lo[3], hi[3]; };
+        std::function<B(int32_t, uint32_t)> rec = [&](int32_t ref, uint32_t depth) -> B {
+            maxd = std::max(maxd, depth); B tb; for (int a = 0; a < 3; ++a) { tb.lo[a] = FLT_MAX; tb.hi[a] = -FLT_MAX; }
+            if (ref < 0) {
+                uint32_t code = ~(uint32_t) ref, first = code >> 3, count = code & 7u; leaves++;
+                for (uint32_t i = first; i < first + count; ++i) {
+                    if (seen[i]++) AM_THROW("bvh q4: triangle %u referenced twice", i);
+                    for (int k = 0; k < 3; ++k) { const float4 &v = s.bvh.tris[3 * (size_t) i + k]; const float p[3] = { v.x, v.y, v.z };
+                        for (int a = 0; a < 3; ++a) { tb.lo[a] = std::min(tb.lo[a], p[a]); tb.hi[a] = std::max(tb.hi[a], p[a]); } }
+                }
+                return tb;
+            }
+            const uint4 *n = &q[4 * (size_t) ref]; float org[3]; memcpy(org, &n[0].x, 12);
+            const uint32_t ql[3] = { n[1].x, n[1].y, n[1].z }, qh[3] = { n[1].w, n[2].x, n[2].y }; const int32_t c[4] = { (int32_t) n[2].z, (int32_t) n[2].w, (int32_t) n[3].x, (int32_t) n[3].y };
+            for (int i = 0; i < 4; ++i) {
+                if (c[i] == 0) continue;
+                if (c[i] > 0 && c[i] <= ref) AM_THROW("bvh q4: child %d of node %d is not numbered after its parent", c[i], ref);
+                const B kb = rec(c[i], depth + 1);
+                for (int a = 0; a < 3; ++a) {
+                    uint32_t eb = ((n[0].w >> (8 * a)) & 0xffu) << 23; float scale; memcpy(&scale, &eb, 4);
+                    const float lo = std::fma((float) ((ql[a] >> (8 * i)) & 0xffu), scale, org[a]), hi = std::fma((float) ((qh[a] >> (8 * i)) & 0xffu), scale, org[a]);
+                    if (kb.lo[a] < lo || kb.hi[a] > hi) AM_THROW("bvh q4: geometry under slot %d of node %d leaves its decoded box on axis %d", i, ref, a);
+                    tb.lo[a] = std::min(tb.lo[a], kb.lo[a]); tb.hi[a] = std::max(tb.hi[a], kb.hi[a]);
+                }
+            }
+            return tb;
+        };
+        rec(0, 0);
+        for (size_t i = 0; i < seen.size(); ++i) if (!seen[i]) AM_THROW("bvh q4: triangle %zu is not referenced by any leaf", i);
+        if (max_depth) *max_depth = maxd; if (n_leaves) *n_leaves = leaves; return AMVPT_OK; });
 }
 int amvpt_bvh_validate(amvpt_scene *h, uint32_t *max_depth, uint32_t *n_leaves) {
     return guard([&] { NEED(h); Scene &s = *h->s; s.prepare_host();

@@ -161,13 +161,48 @@ AM_D int32_t node_step(const DScene &s, const SlabRay &r, float best, int32_t no
 }
 #endif
 
+// One step through the compressed 4-wide tree (DScene::nodes_q4).  The child planes are origin + q * 2^(e - 127); with the per-node
+// products sa = 2^(e - 127) * id and ca = origin * id - ood every plane distance is one FMA: t = q * sa + ca.  Children are visited
+// nearest first (rank = number of hit children nearer than this one), like the uncompressed 4-wide step above.
+AM_D float q8(uint32_t w, int i) { return (float) ((w >> (8 * i)) & 0xffu); }
+AM_D int32_t node_step_q4(const DScene &s, const SlabRay &r, float best, int32_t node, int32_t *stack, int &sp) {
+    const uint4 *np = s.nodes_q4 + 4 * (size_t) node;
+    const uint4 q0 = __ldg(np), q1 = __ldg(np + 1), q2 = __ldg(np + 2); const uint2 q3 = __ldg(reinterpret_cast<const uint2 *>(np + 3));
+    const float sx = __uint_as_float((q0.w & 0xffu) << 23) * r.id.x, sy = __uint_as_float(((q0.w >> 8) & 0xffu) << 23) * r.id.y, sz = __uint_as_float(((q0.w >> 16) & 0xffu) << 23) * r.id.z;
+    const float cx = fmadd(__uint_as_float(q0.x), r.id.x, -r.ood.x), cy = fmadd(__uint_as_float(q0.y), r.id.y, -r.ood.y), cz = fmadd(__uint_as_float(q0.z), r.id.z, -r.ood.z);
+    const int32_t c[4] = { (int32_t) q2.z, (int32_t) q2.w, (int32_t) q3.x, (int32_t) q3.y };
+    float t[4]; bool h[4]; int n = 0;
+    #pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const float t0x = fmadd(q8(q1.x, i), sx, cx), t1x = fmadd(q8(q1.w, i), sx, cx);
+        const float t0y = fmadd(q8(q1.y, i), sy, cy), t1y = fmadd(q8(q2.x, i), sy, cy);
+        const float t0z = fmadd(q8(q1.z, i), sz, cz), t1z = fmadd(q8(q2.y, i), sz, cz);
+        const float tmin = fmaxf(fmax3(fminf(t0x, t1x), fminf(t0y, t1y), fminf(t0z, t1z)), 0.f);
+        const float tmax = fminf(fmin3(fmaxf(t0x, t1x), fmaxf(t0y, t1y), fmaxf(t0z, t1z)), best);
+        h[i] = tmin <= tmax * (1.f + AM_SLAB_EPS) && c[i] != 0; t[i] = h[i] ? tmin : AM_INF; n += (int) h[i];
+    }
+    if (n == 0) return stack[--sp];
+    if (n == 1) return h[0] ? c[0] : (h[1] ? c[1] : (h[2] ? c[2] : c[3]));
+    const int r0 = (int) (t[1] < t[0]) + (int) (t[2] < t[0]) + (int) (t[3] < t[0]);
+    const int r1 = (int) (t[0] <= t[1]) + (int) (t[2] < t[1]) + (int) (t[3] < t[1]);
+    const int r2 = (int) (t[0] <= t[2]) + (int) (t[1] <= t[2]) + (int) (t[3] < t[2]);
+    const int r3 = (int) (t[0] <= t[3]) + (int) (t[1] <= t[3]) + (int) (t[2] <= t[3]);
+    int32_t next = c[3]; const int top = sp + n - 1;
+    if (h[0]) { if (r0 == 0) next = c[0]; else stack[top - r0] = c[0]; }
+    if (h[1]) { if (r1 == 0) next = c[1]; else stack[top - r1] = c[1]; }
+    if (h[2]) { if (r2 == 0) next = c[2]; else stack[top - r2] = c[2]; }
+    if (h[3] && r3 != 0) stack[top - r3] = c[3];
+    sp = top;
+    return next;
+}
+
 // Closest hit (ANY = false) with the tie rule of ShapeKDTree::ray_intersect_naive
 // (include/mitsuba/render/kdtree.h:2445-2468): among equal t the primitive with the larger global index
 // wins.  ANY = true: Scene::ray_test semantics, first accepted triangle ends the traversal.
 // "while-while" traversal: every lane first descends through inner nodes until it holds a leaf, the warp reconverges,
 // then the lanes intersect their leaves together -- the triangle test is the expensive, divergence-sensitive part.
 #define AM_TRAVERSAL_DONE ((int32_t) 0x80000000)      /* not a valid leaf code: first would be 2^28 - 1 */
-template <bool ANY> AM_D Hit intersect(const DScene &s, const Ray &ray, uint32_t *n_nodes = nullptr, uint32_t *n_tris = nullptr) {
+template <bool ANY, bool Q4 = false> AM_D Hit intersect(const DScene &s, const Ray &ray, uint32_t *n_nodes = nullptr, uint32_t *n_tris = nullptr) {
     Hit h; h.t = AM_INF; h.u = 0.f; h.v = 0.f; h.tri = AM_NO_HIT;
     uint32_t best_prim = 0;
     float best = ray.maxt;
@@ -178,7 +213,7 @@ template <bool ANY> AM_D Hit intersect(const DScene &s, const Ray &ray, uint32_t
     for (;;) {
         while (node >= 0) {
             if (n_nodes) (*n_nodes)++;
-            node = node_step(s, sr, best, node, stack, sp);
+            node = Q4 ? node_step_q4(s, sr, best, node, stack, sp) : node_step(s, sr, best, node, stack, sp);
         }
         if (node == AM_TRAVERSAL_DONE) break;
         uint32_t code = ~(uint32_t) node, first = code >> 3, count = code & 7u;

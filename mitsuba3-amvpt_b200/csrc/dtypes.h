@@ -46,6 +46,11 @@ struct DScene {
     //   n2 = (c0.lo.z, c0.hi.z, c1.lo.z, c1.hi.z)  n3 = (bits c0, bits c1, -, -)
     // child >= 0: inner node index; child < 0: leaf, ~child = (first_tri << 3) | count (count <= 7)
     const float4 *nodes;
+    // compressed 4-wide tree over the same leaves (bvh.cpp), 64 B per node = 4 x uint4, used by the wavefront trace stage; nullptr = not built:
+    //   q0 = (bits origin.x, bits origin.y, bits origin.z, ex | ey << 8 | ez << 16)      plane = origin + q * 2^(e - 127)
+    //   q1 = (qlo.x[4], qlo.y[4], qlo.z[4], qhi.x[4])   q2 = (qhi.y[4], qhi.z[4], ref0, ref1)   q3 = (ref2, ref3, -, -)
+    //   one byte per child and plane; ref 0 = empty slot, > 0 inner node, < 0 leaf code as below
+    const uint4 *nodes_q4;
     // triangles in BVH leaf order, 48 B each = 3 x float4: (p0, bits prim), (p1, bits mesh), (p2, 0)
     const float4 *tris;
     const float4 *tri_nrm;      // vertex normals in the same order (3 x float4), or nullptr
@@ -68,6 +73,7 @@ struct DScene {
     uint32_t n_reuse; int32_t sa_mis, fast_mis, pad1;
     // emitters other than area lights.  gen_emitters != 0 selects the general emitter code (kernels are instantiated for both cases, so
     // that scenes lit by area lights only keep the short path); env_emitter = index of the environment emitter in `emitters` or -1
+    float box_lo[3], box_inv[3], pad4[2];     // bounding box of the geometry and 16 / extent per axis (ray-task sort of the wavefront scheduler)
     int32_t gen_emitters, env_emitter, hide_emitters, env_is_map;
     float bsphere[4];                 // centre, radius of the scene as Emitter::set_scene sees it (constant.cpp:73-88, envmap.cpp:290-304)
     const float *env_data;            // envmap: res_y x res_x x 3 floats, last column = first (envmap.cpp:146-207)

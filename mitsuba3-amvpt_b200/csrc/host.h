@@ -65,7 +65,8 @@ void load_image_rgb(const std::string &path, uint32_t *w, uint32_t *h, std::vect
 
 enum SchedulerMode { SCHED_WARP_BATCH = 0, SCHED_REGENERATE = 1, SCHED_STREAM = 2, SCHED_WAVEFRONT = 3, SCHED_AUTO = 4, SCHED_REUSE = 5 /* reported only */, SCHED_SPLIT = 6 };
 
-struct BvhOut { std::vector<float4> nodes, tris, tri_nrm; std::vector<uint32_t> prim_to_tri; uint32_t depth = 0; };
+struct BvhOut { std::vector<float4> nodes, tris, tri_nrm; std::vector<uint32_t> prim_to_tri; uint32_t depth = 0;
+                std::vector<uint4> nodes_q4; uint32_t depth_q4 = 0; };     // nodes_q4: compressed 4-wide tree over the same leaves (empty = not built)
 struct RenderStats {
     double seconds = 0.0;            // device time of the pass loop (CUDA events)
     unsigned long long paths = 0, closest_rays = 0, shadow_rays = 0, nodes = 0, tris = 0, vertices = 0;
@@ -103,6 +104,7 @@ struct Scene {
     float4 *reuse_buf = nullptr; uint32_t reuse_cap = 0;   // staged sample-reuse schedule: per-chunk hit + projection records
     WfPool wf{}; uint32_t wf_type_mask = 0;     // wavefront scheduler pool (allocated on first use)
     uint32_t n_nodes = 0, n_tris = 0;
+    char *bvh_dev = nullptr; size_t bvh_bytes = 0, bvh_hot_bytes = 0, l2_persist_max = 0, l2_window_max = 0;   // contiguous nodes | triangles | compressed nodes; hot = the first two
     volatile bool stop = false;
     RenderStats last;
     // host copy of the tree the kernels traverse (built by prepare_host, checked by amvpt_bvh_validate)

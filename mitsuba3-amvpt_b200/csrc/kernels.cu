@@ -339,10 +339,12 @@ __global__ void intersect_kernel(const DScene s, const float *o, const float *d,
     StatCtx st; st.closest = st.shadow = st.nodes = st.tris = st.vertices = 0;
     if (i < n) {
         Ray r; r.o = v3(o[3 * i], o[3 * i + 1], o[3 * i + 2]); r.d = v3(d[3 * i], d[3 * i + 1], d[3 * i + 2]); r.maxt = maxt[i];
-        Hit h = any ? intersect<true>(s, r, &st.nodes, &st.tris) : intersect<false>(s, r, &st.nodes, &st.tris);
+        const bool q4 = (any & 2) != 0 && s.nodes_q4 != nullptr;      // bit 1 of `any`: walk the compressed 4-wide tree
+        Hit h = (any & 1) ? (q4 ? intersect<true, true>(s, r, &st.nodes, &st.tris) : intersect<true>(s, r, &st.nodes, &st.tris))
+                          : (q4 ? intersect<false, true>(s, r, &st.nodes, &st.tris) : intersect<false>(s, r, &st.nodes, &st.tris));
         prim[i] = h.tri == AM_NO_HIT ? AM_NO_HIT : __float_as_uint(s.tris[3 * (size_t) h.tri].w);
         if (tuv) { tuv[3 * i] = h.t; tuv[3 * i + 1] = h.u; tuv[3 * i + 2] = h.v; }
-        if (any) st.shadow++; else st.closest++;
+        if (any & 1) st.shadow++; else st.closest++;
     }
     if (counters) flush_stats(st, counters);
 }

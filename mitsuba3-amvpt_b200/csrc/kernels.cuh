@@ -44,7 +44,15 @@ struct WfPool {
     uint32_t *qcount;       // [6]
     uint32_t *live;         // [64] live-slot counters, one per iteration (ring)
     uint32_t n_slots;
+    // ray-task sort (wf_key / wf_scan / wf_scatter kernels): tasks of one iteration bucketed by origin cell (Morton, 4 bits per axis) and
+    // direction octant; order[] lists the existing tasks bucket by bucket, sort_total[0] = their number
+    uint32_t *sort_hist;    // [WF_SORT_BUCKETS + 1] counts, then exclusive offsets
+    uint32_t *sort_key;     // [2 * n_slots] bucket of task t, or WF_SORT_NONE
+    uint32_t *sort_rank;    // [2 * n_slots] arrival rank of task t inside its bucket
+    uint32_t *order;        // [2 * n_slots]
 };
+#define WF_SORT_BUCKETS 32768u
+#define WF_SORT_NONE 0xffffffffu
 uint32_t run_wavefront_pass(const DScene &s, const RenderParams &p, const WfPool &w, uint32_t type_mask, int sm_count, bool stats, cudaStream_t st,
                             double *trace_seconds, uint32_t *trace_launches);
 

@@ -117,6 +117,11 @@ void render(Scene &s, const RenderOptions &opt) {
                 w.rng = (uint4 *) s.dalloc(sizeof(uint4) * n); w.flags = (uint32_t *) s.dalloc(sizeof(uint32_t) * n); w.spos = (float2 *) s.dalloc(sizeof(float2) * n);
                 w.queue = (uint32_t *) s.dalloc(sizeof(uint32_t) * 7 * (size_t) n); w.qcount = (uint32_t *) s.dalloc(sizeof(uint32_t) * 8);      // six BSDF-type queues + the escaped-ray queue
                 w.live = (uint32_t *) s.dalloc(sizeof(uint32_t) * 64);
+                w.sort_hist = w.sort_key = w.sort_rank = w.order = nullptr;
+                if (getenv("AMVPT_SORT") && atoi(getenv("AMVPT_SORT")) != 0) {      // ray-task sort: measured slower on B200 (profiles/r02_hfield16_trace_experiments.txt), opt-in
+                w.sort_hist = (uint32_t *) s.dalloc(sizeof(uint32_t) * (WF_SORT_BUCKETS + 1)); w.sort_key = (uint32_t *) s.dalloc(sizeof(uint32_t) * 2 * (size_t) n);
+                w.sort_rank = (uint32_t *) s.dalloc(sizeof(uint32_t) * 2 * (size_t) n); w.order = (uint32_t *) s.dalloc(sizeof(uint32_t) * 2 * (size_t) n);
+                }
                 s.wf_type_mask = 0; for (auto &m : s.meshes) s.wf_type_mask |= 1u << s.bsdfs[m.bsdf].type;
             }
             rs.launches += run_wavefront_pass(s.d, p, s.wf, s.wf_type_mask, s.sm_count, opt.stats, st, opt.time_stages ? &rs.trace_seconds : nullptr, &rs.trace_launches);

@@ -282,7 +282,17 @@ void Scene::commit(int dev) {
         any_nrm |= !m.nrm.empty(); dm.push_back(q);
     }
     d = DScene{};
-    d.nodes = upload(bvh.nodes); d.tris = upload(bvh.tris); d.tri_nrm = any_nrm ? upload(bvh.tri_nrm) : nullptr;
+    // nodes | triangles | compressed nodes in ONE allocation: the wavefront trace stage asks L2 to keep this range resident
+    // (cudaAccessPropertyPersisting window, wavefront.cu) while the path-state pool streams through
+    { const size_t nb = bvh.nodes.size() * sizeof(float4), tb = bvh.tris.size() * sizeof(float4), qb = bvh.nodes_q4.size() * sizeof(uint4);
+      const size_t o_t = (nb + 255) / 256 * 256, o_q = o_t + (tb + 255) / 256 * 256; bvh_bytes = o_q + qb; bvh_dev = (char *) dalloc(bvh_bytes);
+      if (nb) AM_CUDA(cudaMemcpy(bvh_dev, bvh.nodes.data(), nb, cudaMemcpyHostToDevice));
+      if (tb) AM_CUDA(cudaMemcpy(bvh_dev + o_t, bvh.tris.data(), tb, cudaMemcpyHostToDevice));
+      if (qb) AM_CUDA(cudaMemcpy(bvh_dev + o_q, bvh.nodes_q4.data(), qb, cudaMemcpyHostToDevice));
+      d.nodes = (const float4 *) bvh_dev; d.tris = (const float4 *) (bvh_dev + o_t); d.nodes_q4 = qb ? (const uint4 *) (bvh_dev + o_q) : nullptr; bvh_hot_bytes = o_q; }
+    d.tri_nrm = any_nrm ? upload(bvh.tri_nrm) : nullptr;
+    { int v = 0; cudaDeviceGetAttribute(&v, cudaDevAttrMaxPersistingL2CacheSize, dev); l2_persist_max = (size_t) std::max(v, 0);
+      cudaDeviceGetAttribute(&v, cudaDevAttrMaxAccessPolicyWindowSize, dev); l2_window_max = (size_t) std::max(v, 0); }
     d.prim_to_tri = upload(bvh.prim_to_tri); d.meshes = upload(dm); d.bsdfs = upload(bsdfs); d.emitters = upload(emitters);
     // PerspectiveCamera::update_camera_transforms (perspective.cpp:173-199) members read by sample_surface: camera_to_sample
     // (inverse of sample_to_camera), Transform4f::inverse of to_world, normalization = 1 / area of the near-plane image rectangle
@@ -315,6 +325,9 @@ void Scene::commit(int dev) {
     d.gen_emitters = general_emitters() ? 1 : 0; d.env_emitter = env_emitter; d.hide_emitters = integrator.hide_emitters ? 1 : 0;
     d.env_is_map = env_emitter >= 0 && emitters[(size_t) env_emitter].type == EMITTER_ENVMAP;
     bounding_sphere(d.bsphere, d.bsphere + 3);
+    { float lo[3] = { AM_INF, AM_INF, AM_INF }, hi[3] = { -AM_INF, -AM_INF, -AM_INF };
+      for (auto &m : meshes) for (size_t i = 0; i + 2 < m.pos.size(); i += 3) for (int k = 0; k < 3; ++k) { lo[k] = std::min(lo[k], m.pos[i + k]); hi[k] = std::max(hi[k], m.pos[i + k]); }
+      for (int k = 0; k < 3; ++k) { d.box_lo[k] = lo[k] <= hi[k] ? lo[k] : 0.f; const float e = hi[k] - lo[k]; d.box_inv[k] = e > 0.f ? 16.f / e : 0.f; } }
     if (d.env_is_map) {
         d.env_data = upload(env.data); d.env_warp = upload(env.warp);
         d.env_res_x = env.res_x; d.env_res_y = env.res_y; d.env_n_levels = (uint32_t) env.level_off.size(); d.env_scale = env.scale;

@@ -70,10 +70,59 @@ wf_regen_kernel(const DScene s, const RenderParams p, const WfPool w, uint32_t i
 #ifndef AM_WT_MIN_CTAS
 #define AM_WT_MIN_CTAS 10   /* 51 registers: +2 % on the 1M-triangle scene; 12 (40 registers) spills and loses 3 % */
 #endif
-template <bool STATS> __global__ void __launch_bounds__(128, AM_WT_MIN_CTAS)
+// ---- ray-task sort.  Rays leave the shade stage in slot order, i.e. uncorrelated in space; traced that way the lanes of a warp walk
+// different parts of the tree (ncu: 16 of 32 lanes per instruction, L1 hit 67 %).  Before the trace stage the existing tasks are
+// bucketed by (Morton code of the origin's cell in a 16^3 grid over the scene box, direction octant): one pass computes the bucket
+// and takes a rank in it (match.any-aggregated atomics on a 32768-entry histogram), one CTA scans the histogram, one pass scatters
+// the task ids.  Warps then pull consecutive entries of order[]: neighbours in space, same octant.
+AM_D uint32_t morton4(uint32_t x, uint32_t y, uint32_t z) {       // 4 bits per axis -> 12 bits
+    auto spread = [](uint32_t v) { v &= 15u; v = (v | (v << 4)) & 0x0c3u; v = (v | (v << 2)) & 0x249u; return v; };
+    return spread(x) | (spread(y) << 1) | (spread(z) << 2);
+}
+AM_D uint32_t ray_bucket(const DScene &s, float4 o, float4 d) {
+    const float fx = (o.x - s.box_lo[0]) * s.box_inv[0], fy = (o.y - s.box_lo[1]) * s.box_inv[1], fz = (o.z - s.box_lo[2]) * s.box_inv[2];
+    const uint32_t cx = (uint32_t) fminf(fmaxf(fx, 0.f), 15.f), cy = (uint32_t) fminf(fmaxf(fy, 0.f), 15.f), cz = (uint32_t) fminf(fmaxf(fz, 0.f), 15.f);
+    const uint32_t oct = (d.x < 0.f ? 1u : 0u) | (d.y < 0.f ? 2u : 0u) | (d.z < 0.f ? 4u : 0u);
+    return (morton4(cx, cy, cz) << 3) | oct;
+}
+__global__ void __launch_bounds__(256) wf_key_kernel(const DScene s, const WfPool w) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;          // one thread per slot, two tasks
+    const unsigned lane_id = threadIdx.x & 31u;
+    const uint32_t f = i < w.n_slots ? w.flags[i] : 0u;
+    #pragma unroll
+    for (int kind = 0; kind < 2; ++kind) {
+        const bool exists = kind == 0 ? (f & WF_SHADOW) != 0 : (f & WF_ALIVE) != 0;
+        uint32_t key = WF_SORT_NONE;
+        if (exists) key = kind == 0 ? ray_bucket(s, w.so[i], w.sd[i]) : ray_bucket(s, w.ro[i], w.rd[i]);
+        const unsigned peers = __match_any_sync(0xffffffffu, key);
+        uint32_t base = 0; const unsigned leader = __ffs(peers) - 1;
+        if (exists && lane_id == leader) base = atomicAdd(w.sort_hist + key, (uint32_t) __popc(peers));
+        base = __shfl_sync(0xffffffffu, base, leader);
+        if (i < w.n_slots) { w.sort_key[2 * i + kind] = key; w.sort_rank[2 * i + kind] = base + __popc(peers & ((1u << lane_id) - 1u)); }
+    }
+}
+__global__ void __launch_bounds__(1024) wf_scan_kernel(const WfPool w) {      // exclusive scan of 32768 counts by one CTA; [BUCKETS] = total
+    __shared__ uint32_t part[1024];
+    const uint32_t t = threadIdx.x, per = WF_SORT_BUCKETS / 1024u; uint32_t v[WF_SORT_BUCKETS / 1024u], sum = 0;
+    for (uint32_t k = 0; k < per; ++k) { v[k] = w.sort_hist[t * per + k]; sum += v[k]; }
+    part[t] = sum; __syncthreads();
+    for (uint32_t off = 1; off < 1024u; off <<= 1) { uint32_t x = t >= off ? part[t - off] : 0u; __syncthreads(); part[t] += x; __syncthreads(); }
+    uint32_t run = part[t] - sum;
+    for (uint32_t k = 0; k < per; ++k) { w.sort_hist[t * per + k] = run; run += v[k]; }
+    if (t == 1023u) w.sort_hist[WF_SORT_BUCKETS] = part[1023];
+}
+__global__ void __launch_bounds__(256) wf_scatter_kernel(const WfPool w) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; if (t >= 2u * w.n_slots) return;
+    const uint32_t key = w.sort_key[t]; if (key == WF_SORT_NONE) return;
+    w.order[w.sort_hist[key] + w.sort_rank[t]] = t;
+}
+
+// Q4 = true walks the compressed 4-wide tree (DScene::nodes_q4: half the node steps of the binary tree at the same 64 bytes per step);
+// SORTED = true pulls tasks from order[] (all of them exist) instead of testing every slot's two task flags
+template <bool STATS, bool Q4, bool SORTED> __global__ void __launch_bounds__(128, AM_WT_MIN_CTAS)
 wf_trace_kernel(const DScene s, const RenderParams p, const WfPool w, uint32_t fetch_min, uint32_t leaf_min) {
     const unsigned lane_id = threadIdx.x & 31u;
-    const uint32_t n_tasks = 2u * w.n_slots;
+    const uint32_t n_tasks = SORTED ? w.sort_hist[WF_SORT_BUCKETS] : 2u * w.n_slots;
     StatCtx st; st.closest = st.shadow = st.nodes = st.tris = st.vertices = 0;
     int32_t stack[AM_STACK_SIZE];
     TravState tv; tv.node = AM_TRAVERSAL_DONE; tv.sp = 0; tv.any = false;
@@ -89,8 +138,9 @@ wf_trace_kernel(const DScene s, const RenderParams p, const WfPool w, uint32_t f
                 base = __shfl_sync(idle, base, leader);
                 t = base + __popc(idle & ((1u << lane_id) - 1u));
                 if (t < n_tasks) {
-                    slot = t >> 1; uint32_t f = w.flags[slot];
-                    if ((t & 1u) == 0) {
+                    const uint32_t task = SORTED ? w.order[t] : t;
+                    slot = task >> 1; const uint32_t f = SORTED ? (WF_SHADOW | WF_ALIVE) : w.flags[slot];
+                    if ((task & 1u) == 0) {
                         if (f & WF_SHADOW) { float4 o = w.so[slot], d = w.sd[slot]; Ray r; r.o = xyz(o); r.d = xyz(d); r.maxt = o.w; trav_begin(tv, r, true); busy = true; }
                     } else if (f & WF_ALIVE) { float4 o = w.ro[slot], d = w.rd[slot]; Ray r; r.o = xyz(o); r.d = xyz(d); r.maxt = o.w; trav_begin(tv, r, false); busy = true; }
                     if (busy) { stack[0] = AM_TRAVERSAL_DONE; tv.sp = 1; }
@@ -111,7 +161,7 @@ wf_trace_kernel(const DScene s, const RenderParams p, const WfPool w, uint32_t f
                 if (dm == 0 || __popc(bm & ~dm) >= (int) leaf_min) break;
                 if (desc) {
                     if (STATS) st.nodes++;
-                    tv.node = node_step(s, tv.sr, tv.best, tv.node, stack, tv.sp);
+                    tv.node = Q4 ? node_step_q4(s, tv.sr, tv.best, tv.node, stack, tv.sp) : node_step(s, tv.sr, tv.best, tv.node, stack, tv.sp);
                 }
             }
         }
@@ -230,8 +280,14 @@ uint32_t run_wavefront_pass(const DScene &s, const RenderParams &p, const WfPool
     AM_CUDA(cudaMemsetAsync(w.flags, 0, sizeof(uint32_t) * w.n_slots, st));
     AM_CUDA(cudaMemsetAsync(w.live, 0, sizeof(uint32_t) * 64, st));
     const unsigned grid = w.n_slots / 128, sgrid = (unsigned) sm_count * 16;
-    static int trace_ctas = 0;
-    if (!trace_ctas) { cudaOccupancyMaxActiveBlocksPerMultiprocessor(&trace_ctas, wf_trace_kernel<false>, 128, 0); if (trace_ctas < 1) trace_ctas = 1; }
+    // measured on B200 (profiles/r02_*): the compressed 4-wide tree and the task sort are opt-in / opt-out through the environment
+    const bool q4 = s.nodes_q4 != nullptr && getenv("AMVPT_Q4") && atoi(getenv("AMVPT_Q4")) != 0;
+    const bool sorted = w.order != nullptr;      // the sort buffers exist only when AMVPT_SORT=1 was set at pool creation (render.cpp)
+    typedef void (*TraceFn)(const DScene, const RenderParams, const WfPool, uint32_t, uint32_t);
+    const TraceFn fns[2][2][2] = { { { wf_trace_kernel<false, false, false>, wf_trace_kernel<false, false, true> }, { wf_trace_kernel<false, true, false>, wf_trace_kernel<false, true, true> } },
+                                   { { wf_trace_kernel<true, false, false>, wf_trace_kernel<true, false, true> }, { wf_trace_kernel<true, true, false>, wf_trace_kernel<true, true, true> } } };
+    const TraceFn trace_fn = fns[stats ? 1 : 0][q4 ? 1 : 0][sorted ? 1 : 0];
+    int trace_ctas = 0; cudaOccupancyMaxActiveBlocksPerMultiprocessor(&trace_ctas, trace_fn, 128, 0); if (trace_ctas < 1) trace_ctas = 1;
     const unsigned tgrid = std::min<unsigned>((unsigned) (sm_count * trace_ctas), grid);      // persistent: one resident wave
     const uint32_t fetch_min = getenv("AMVPT_FETCH_MIN") ? (uint32_t) atoi(getenv("AMVPT_FETCH_MIN")) : 16u;
     const uint32_t leaf_min = getenv("AMVPT_LEAF_MIN") ? (uint32_t) atoi(getenv("AMVPT_LEAF_MIN")) : 12u;
@@ -240,7 +296,12 @@ uint32_t run_wavefront_pass(const DScene &s, const RenderParams &p, const WfPool
     for (uint32_t iter = 0;; ++iter) {
         if (stats) wf_regen_kernel<true><<<grid, 128, 0, st>>>(s, p, w, iter); else wf_regen_kernel<false><<<grid, 128, 0, st>>>(s, p, w, iter);
         if (trace_seconds) { cudaEvent_t a, b; cudaEventCreate(&a); cudaEventCreate(&b); ev.push_back(a); ev.push_back(b); cudaEventRecord(a, st); }
-        if (stats) wf_trace_kernel<true><<<tgrid, 128, 0, st>>>(s, p, w, fetch_min, leaf_min); else wf_trace_kernel<false><<<tgrid, 128, 0, st>>>(s, p, w, fetch_min, leaf_min);
+        if (sorted) {
+            cudaMemsetAsync(w.sort_hist, 0, sizeof(uint32_t) * (WF_SORT_BUCKETS + 1), st);
+            wf_key_kernel<<<(w.n_slots + 255) / 256, 256, 0, st>>>(s, w); wf_scan_kernel<<<1, 1024, 0, st>>>(w); wf_scatter_kernel<<<(2 * w.n_slots + 255) / 256, 256, 0, st>>>(w);
+            launches += 3;
+        }
+        trace_fn<<<tgrid, 128, 0, st>>>(s, p, w, fetch_min, leaf_min);
         if (trace_seconds) cudaEventRecord(ev.back(), st);
         launches += 2;
         if (s.env_emitter >= 0) { wf_miss_kernel<<<sgrid, 128, 0, st>>>(s, w); launches++; }

@@ -127,6 +127,11 @@ def test_million_triangle_bvh_closest_and_any_hit(big_hfield):
     assert 0.5 < (prim != 0xffffffff).mean() < 1.0
     occ, _, _ = s.intersect(origin, d, mt, any_hit=True); rocc = o.ray_test(origin, d, mt)
     assert np.array_equal(occ != 0xffffffff, rocc != 0)
+    # the compressed 4-wide tree of the wavefront trace stage finds the same hits
+    nq, dq, lq = s.bvh_q4_validate(); assert nq > 200000 and lq == leaves and dq <= 20
+    qprim, qtuv, qstats = s.intersect(origin, d, mt, q4=True)
+    assert_bits(qprim, rprim, "closest-hit primitive, compressed 4-wide tree"); assert_bits(qtuv[qprim != 0xffffffff], rtuv[rprim != 0xffffffff], "t, u, v, compressed 4-wide tree")
+    qocc, _, _ = s.intersect(origin, d, mt, any_hit=True, q4=True); assert np.array_equal(qocc != 0xffffffff, rocc != 0)
     k = 3000; bprim, btuv, _ = o.intersect(origin[:k], d[:k], mt[:k], brute=True)
     assert_bits(prim[:k], bprim, "closest hit vs brute force (1M triangles)"); assert_bits(tuv[:k][bprim != 0xffffffff], btuv[bprim != 0xffffffff], "t, u, v vs brute force")
 

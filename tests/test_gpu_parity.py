@@ -145,6 +145,23 @@ def test_bvh_equals_brute_force_heightfield(hfield):
     assert np.array_equal(occ != 0xffffffff, rocc != 0)
 
 
+def test_compressed_wide_tree_equals_binary_tree(cbox, hfield):
+    """DScene::nodes_q4 (quantised 4-wide nodes, wavefront trace stage) against the binary tree and the oracle's brute force."""
+    for which, (desc, s, o) in (("cbox", cbox), ("hfield", hfield)):
+        nq, dq, lq = s.bvh_q4_validate(); d2, l2 = s.bvh_validate(); assert nq >= 1 and lq == l2
+        rng = np.random.default_rng(3); n = 20000
+        lo, hi = (np.array([-100, -100, -900]), np.array([660, 650, 660])) if which == "cbox" else (np.array([-1.4, -1.4, -0.3]), np.array([1.4, 1.4, 2.4]))
+        origin = rng.uniform(lo, hi, (n, 3)).astype(np.float32); target = rng.uniform(lo, hi, (n, 3)).astype(np.float32)
+        d = target - origin; d[:500, 0] = 0; d[500:1000, 1] = 0; d[1000:1200, :2] = 0
+        d = (d / np.maximum(np.linalg.norm(d, axis=1, keepdims=True), 1e-20)).astype(np.float32)
+        mt = np.full(n, np.finfo(np.float32).max, np.float32); mt[::5] = rng.uniform(0.01, 1.0, len(mt[::5])).astype(np.float32) * (1000 if which == "cbox" else 3)
+        p2, t2, _ = s.intersect(origin, d, mt); p4, t4, st4 = s.intersect(origin, d, mt, q4=True); pb, tb, _ = o.intersect(origin, d, mt, brute=True)
+        assert_bits(p4, pb, f"{which}: q4 primitive vs brute force"); assert_bits(p2, pb, f"{which}: binary tree vs brute force")
+        assert_bits(t4[pb != 0xffffffff], tb[pb != 0xffffffff], f"{which}: q4 t, u, v")
+        a2, _, _ = s.intersect(origin, d, mt, any_hit=True); a4, _, _ = s.intersect(origin, d, mt, any_hit=True, q4=True)
+        assert np.array_equal(a2 != 0xffffffff, a4 != 0xffffffff)
+
+
 def test_shared_edge_tie_rule(cbox):
     # rays aimed exactly at shared edges / vertices of the floor quad: the larger primitive index must win
     _, s, o = cbox
