@@ -32,16 +32,19 @@ for p in (ROOT, os.path.join(ROOT, "tests")):
 METRIC = "Mpaths/s (all views, device-timed)"     # both arms print this string (the driver divides only equal metrics)
 
 WORKLOADS = {
-    # name: (scene factory name, kwargs, spp)
-    "cbox8x8": ("cornell_box", dict(grid_x=8, grid_y=8, view_res=512, cam_dist=400.0, max_depth=6, sample_count=256), 256),
-    "cbox4": ("cornell_box", dict(grid_x=4, grid_y=1, view_res=256, cam_dist=200.0, max_depth=6, sample_count=64), 64),
+    # name: (scene factory name, kwargs, spp).  cornell_box_ref = geometry / materials of the reference's resources/data/scenes/cbox/cbox-rgb.xml
+    #  read through the product's XML loader, camera replaced by the `grid` multi-sensor; cbox8x8_synth keeps round 1's
+    # re-derived quads (32 triangles, no vertex normals) for comparison with round-1 numbers
+    "cbox8x8": ("cornell_box_ref", dict(grid_x=8, grid_y=8, view_res=512, cam_dist=400.0, max_depth=6, sample_count=256), 256),
+    "cbox4": ("cornell_box_ref", dict(grid_x=4, grid_y=1, view_res=256, cam_dist=200.0, max_depth=6, sample_count=64), 64),
+    "cbox8x8_synth": ("cornell_box", dict(grid_x=8, grid_y=8, view_res=512, cam_dist=400.0, max_depth=6, sample_count=256), 256),
     "hfield4": ("height_field", dict(n=708, grid_x=2, grid_y=2, view_res=512, max_depth=8, sample_count=16), 16),      # profiling size of hfield16
     "hfield16": ("height_field", dict(n=708, grid_x=4, grid_y=4, view_res=1024, max_depth=8, sample_count=64), 64),
     # BASELINE config 5 geometry (64 views of 1024^2 on the 1M-triangle scene); its 1024-spp adaptive budget is reached with --adaptive --spp 1024
     "hfield64": ("height_field", dict(n=708, grid_x=8, grid_y=8, view_res=1024, max_depth=8, sample_count=64), 64),
     # the same light field with cross-view sample reuse + MIS, 8 cameras per group (one row of the 8x8 array)
-    "cbox8x8_reuse": ("cornell_box", dict(grid_x=8, grid_y=8, view_res=512, cam_dist=400.0, max_depth=6, sample_count=64), 64),
-    "cbox4_reuse": ("cornell_box", dict(grid_x=4, grid_y=1, view_res=256, cam_dist=200.0, max_depth=6, sample_count=64), 64),   # profiling size
+    "cbox8x8_reuse": ("cornell_box_ref", dict(grid_x=8, grid_y=8, view_res=512, cam_dist=400.0, max_depth=6, sample_count=64), 64),
+    "cbox4_reuse": ("cornell_box_ref", dict(grid_x=4, grid_y=1, view_res=256, cam_dist=200.0, max_depth=6, sample_count=64), 64),   # profiling size
     "hfield16_reuse": ("height_field", dict(n=708, grid_x=4, grid_y=4, view_res=1024, max_depth=8, sample_count=16), 16),
 }
 EXTRA = {"cbox8x8_reuse": dict(reuse=dict(sa_reuse=True, sa_mis=True, fast_mis=False, reuse_count=8)),

@@ -101,8 +101,12 @@ int amvpt_scene_set_integrator(amvpt_scene *s, const amvpt_integrator_desc *d);
 /* cross-view sample reuse of the mvpath integrator (src/integrators/mvpath.h:120-129: sa_reuse, sa_mis, fast_mis, reuse_count,
  * adaptive; render_multisample / sample_multi, mvpath_multi.h:8-358).  Reuse is active when sa_reuse, more than one sub-sensor
  * and reuse_count != 1; *n_samples receives the number of cameras per group after the divisor rule of mvpath.cpp:192-218
- * (0 = off).  `adaptive` > 0 (the fill-in pass, mvpath_multi.h:79-115) is rejected at render time. */
+ * (0 = off).  `adaptive` = number of fill-in paths for samples that no other camera could reuse (mvpath_multi.h:52-58, 79-115; single rank);
+ * amvpt_scene_set_reuse_debug switches the `debug` output (the adapt mask instead of the image, mvpath_multi.h:54-56) */
 int amvpt_scene_set_reuse(amvpt_scene *s, int sa_reuse, int sa_mis, int fast_mis, uint32_t reuse_count, uint32_t adaptive, uint32_t *n_samples);
+int amvpt_scene_set_reuse_debug(amvpt_scene *s, int debug);
+/* number of fill-in paths the last amvpt_render traced (the reference logs it as "Adaptive samples", mvpath_multi.h:89) */
+int amvpt_last_fill_paths(amvpt_scene *s, uint64_t *n);
 /* reconstruction filter of the film (src/rfilters/{box,gaussian,tent,mitchell,catmullrom,lanczos}.cpp; ImageBlock::put,
  * src/render/imageblock.cpp:174-558): type 0 box (default of this API), 1 gaussian (param = stddev, Mitsuba's default filter with
  * stddev 0.5), 2 tent (param = radius), 3 mitchell (param = B, param2 = C; both default to 1/3 in the reference), 4 catmullrom,

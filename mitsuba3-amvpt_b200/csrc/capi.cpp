@@ -172,6 +172,10 @@ int amvpt_scene_set_reuse(amvpt_scene *h, int sa_reuse, int sa_mis, int fast_mis
     return guard([&] { NEED(h); h->s->set_reuse(sa_reuse != 0, sa_mis != 0, fast_mis != 0, reuse_count, adaptive);
         if (n_samples) *n_samples = h->s->reuse_samples(); return AMVPT_OK; });
 }
+int amvpt_scene_set_reuse_debug(amvpt_scene *h, int debug) {
+    return guard([&] { NEED(h); h->s->integrator.debug = debug != 0; if (h->s->committed) h->s->d.reuse_debug = debug != 0; return AMVPT_OK; });
+}
+int amvpt_last_fill_paths(amvpt_scene *h, uint64_t *n) { return guard([&] { NEED(h); NEED(n); *n = h->s->last_fill_paths; return AMVPT_OK; }); }
 int amvpt_scene_set_rfilter(amvpt_scene *h, int type, float param, float param2) {
     return guard([&] { NEED(h); h->s->set_rfilter(type, param, param2); return AMVPT_OK; });
 }

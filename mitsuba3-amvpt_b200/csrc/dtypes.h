@@ -70,7 +70,8 @@ struct DScene {
     int32_t filter_type; float filter_radius, filter_inv_radius; float filter_coeff[10];
     // cross-view sample reuse (mvpath.h:120-129): n_reuse = samples per primary sample after mvpath.cpp:192-218, 0 = off
     const DSensorAux *sensor_aux;
-    uint32_t n_reuse; int32_t sa_mis, fast_mis, pad1;
+    uint32_t n_reuse; int32_t sa_mis, fast_mis, reuse_debug;
+    uint32_t n_adapt; float adapt_w; uint32_t pad5[2];      // fill-in samples per masked lane = min(adaptive, n_reuse - 1), 1 / (n_adapt + 1) (mvpath_multi.h:52-53)
     // emitters other than area lights.  gen_emitters != 0 selects the general emitter code (kernels are instantiated for both cases, so
     // that scenes lit by area lights only keep the short path); env_emitter = index of the environment emitter in `emitters` or -1
     float box_lo[3], box_inv[3], pad4[2];     // bounding box of the geometry and 16 / extent per axis (ray-task sort of the wavefront scheduler)

@@ -101,6 +101,8 @@ struct Scene {
     uint8_t *srgb8 = nullptr;                              // display step: the developed quilt as 8-bit sRGB (allocated on first use)
     float display_ms[2] = { 0.f, 0.f };                    // device time of the last srgb8 / interlace kernel
     float4 *split_buf = nullptr; uint32_t split_cap = 0;   // "split" scheduler: first-vertex records of one chunk
+    uint8_t *adapt_mask = nullptr; uint32_t *adapt_scratch = nullptr, *adapt_compact = nullptr; unsigned long long adapt_cap = 0; size_t adapt_compact_cap = 0;   // reuse `adaptive` fill-in
+    unsigned long long last_fill_paths = 0;
     float4 *reuse_buf = nullptr; uint32_t reuse_cap = 0;   // staged sample-reuse schedule: per-chunk hit + projection records
     WfPool wf{}; uint32_t wf_type_mask = 0;     // wavefront scheduler pool (allocated on first use)
     uint32_t n_nodes = 0, n_tris = 0;

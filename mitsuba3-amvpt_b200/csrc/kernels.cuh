@@ -20,6 +20,7 @@ struct RenderParams {
     // scheduler 6 ("split"): the launch covers tickets [ticket_base, ticket_base + prim_m); prim holds 3 * prim_m float4 written by
     // primary_vertex_kernel: closest hit of the camera ray, (light weight, pdf), light direction of the first vertex
     const float4 *prim; uint32_t prim_m, pad2; unsigned long long ticket_base;
+    uint8_t *adapt_mask;           // reuse branch with `adaptive` > 0: adapt_mask of every ticket of the pass (mvpath_multi.h:306-307), else nullptr
     unsigned long long *counters;   // [0] next-lane ticket, [1] closest rays, [2] shadow rays, [3] nodes, [4] tris, [5] path vertices
 };
 
@@ -60,6 +61,9 @@ uint32_t run_wavefront_pass(const DScene &s, const RenderParams &p, const WfPool
 void launch_reuse_pass(const DScene &s, const RenderParams &p, int sm_count, bool stats, cudaStream_t st);
 size_t reuse_staged_float4s(uint32_t n_reuse, uint32_t m_cap);    // size of `buf` below
 uint32_t run_reuse_staged(const DScene &s, const RenderParams &p, float4 *buf, uint32_t m_cap, int schedule /* 1 staged, 2 pipeline */, int sm_count, cudaStream_t st);
+// fill-in pass of the reuse branch (mvpath_multi.h:79-115) over the pass described by p (adapt_mask filled by the kernels above); scratch = at least
+// n_lanes / 1024 + 2 uint32; returns the number of launches and the number of fill-in paths traced
+uint32_t run_reuse_fill_in(const DScene &s, const RenderParams &p, uint32_t base_seed, uint32_t *scratch, uint32_t **compact, size_t *compact_cap, int sm_count, cudaStream_t st, unsigned long long *n_fill);
 void launch_reuse_tap(const DScene &s, uint32_t seed_value, uint32_t spp_per_pass, uint32_t lane_begin, uint32_t n, float *out /* n * n_reuse * 9 */, cudaStream_t st);
 
 // host-callable launchers (kernels.cu)

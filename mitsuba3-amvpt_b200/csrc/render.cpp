@@ -41,8 +41,7 @@ void render(Scene &s, const RenderOptions &opt) {
     if (s.integrator.is_mvpath && !s.multi_sensor) AM_THROW("This integrator can only be used with MultiSensor !");
     const bool reuse = s.reuse_samples() > 0;      // mvpath.cpp:17
     if (reuse) {
-        if (s.integrator.adaptive) AM_THROW("mvpath: the `adaptive` fill-in of the reuse branch (mvpath_multi.h:79-115) is not built");
-        if (s.integrator.debug) AM_THROW("mvpath: the `debug` output of the reuse branch is not built");
+        if (s.d.n_adapt && opt.shard.world > 1) AM_THROW("mvpath: the `adaptive` fill-in numbers its samples over the whole wavefront (dr::compress, mvpath_multi.h:81); it is built for one rank");
         if (s.rfilter_type != 0) AM_THROW("mvpath: sample reuse needs the box reconstruction filter in this build");
         if (opt.adaptive) AM_THROW("render: the adaptive allocator keeps per-pixel moments of the owning view; it cannot be combined with sample reuse");
         if (s.d.n_reuse != s.reuse_samples()) AM_THROW("render: integrator parameters changed after commit");
@@ -51,7 +50,7 @@ void render(Scene &s, const RenderOptions &opt) {
     if (opt.shard.world == 0 || opt.shard.rank >= opt.shard.world) AM_THROW("render: invalid shard %u/%u", opt.shard.rank, opt.shard.world);
     AM_CUDA(cudaSetDevice(s.device));
     cudaStream_t st = opt.stream;
-    s.stop = false;
+    s.stop = false; s.last_fill_paths = 0;
     // mvpath.cpp:33-41
     uint32_t spp = opt.spp ? opt.spp : s.sample_count;
     if (!spp) AM_THROW("render: sample count is zero");
@@ -105,7 +104,11 @@ void render(Scene &s, const RenderOptions &opt) {
         AM_CUDA(cudaMemcpyAsync(s.tiles_dev, tiles.data(), sizeof(TileDesc) * tiles.size(), cudaMemcpyHostToDevice, st));
         AM_CUDA(cudaMemsetAsync(s.counters + CTR_TICKET, 0, sizeof(unsigned long long), st));
         p.seed_value = s.sampler_seed + (spp_per_pass * pass + opt.seed);     // mvpath.cpp:226-231, sampler.cpp:129
-        p.n_tiles = (uint32_t) tiles.size(); p.n_lanes = lanes;
+        p.n_tiles = (uint32_t) tiles.size(); p.n_lanes = lanes; p.adapt_mask = nullptr;
+        if (reuse && s.d.n_adapt) {
+            if (s.adapt_cap < lanes) { s.adapt_mask = (uint8_t *) s.dalloc((size_t) lanes); s.adapt_scratch = (uint32_t *) s.dalloc(sizeof(uint32_t) * ((size_t) (lanes / 1024ull) + 4)); s.adapt_cap = lanes; }
+            p.adapt_mask = s.adapt_mask;
+        }
         if (mode == 3) {
             if (!s.wf.n_slots) {
                 // pool size: a multiple of the CTA size; 2^22 slots (~860 MB of state and queues; measured 193 / 209 / 217 Mpaths/s at 2^20 / 2^21 / 2^22 on the 1M-triangle scene)
@@ -145,6 +148,11 @@ void render(Scene &s, const RenderOptions &opt) {
                 rs.launches++;
             }
             AM_CUDA(cudaGetLastError());
+            if (s.d.n_adapt && !s.d.reuse_debug) {      // fill-in pass for the lanes whose sample no other camera could reuse (mvpath_multi.h:79-115)
+                unsigned long long n_fill = 0;
+                rs.launches += run_reuse_fill_in(s.d, p, s.sampler_seed, s.adapt_scratch, &s.adapt_compact, &s.adapt_compact_cap, s.sm_count, st, &n_fill);
+                AM_CUDA(cudaGetLastError()); s.last_fill_paths += n_fill;
+            }
         } else {
             launch_render_pass(s.d, p, mode, s.sm_count, opt.stats, st);
             AM_CUDA(cudaGetLastError());

@@ -12,7 +12,9 @@
 //
 // Schedule: a persistent kernel, one lane per thread, 32 tickets per warp fetch.  The per-camera records (92 B each) live
 // in local memory; the kernel is instantiated for group sizes up to 8 / 64 so that small groups keep a small frame.
-// Not built: the `adaptive` fill-in of mvpath_multi.h:79-115 (the host rejects adaptive > 0) and the `debug` output.
+// The `adaptive` fill-in of mvpath_multi.h:52-58, 79-115: every schedule records adapt_mask per ticket and scales the primary weight;
+// run_reuse_fill_in compacts the mask in lane order (block counts -> scan -> ranks), and a persistent path kernel traces n_adapt plain
+// paths per masked lane with the forked sampler's streams.  `debug` puts the mask instead of the image.
 #include "dpath.cuh"
 
 namespace amvpt {
@@ -213,7 +215,8 @@ AM_D void mis_weights(const DScene &s, DSample *samples, uint32_t n, const BsdfD
 
 // MVPT::sample_multi (mvpath_multi.h:133-358).  `ps` arrives from lane_setup (sampler state, primary ray) and leaves as the
 // state of the finished suffix path.
-template <bool STATS, int STAGED> AM_D void sample_multi(const DScene &s, PathState &ps, DSample *samples, uint32_t n, V2 p_app, StatCtx *st, TapCtx *tap, const Staged *stg, bool *mis_out = nullptr) {
+template <bool STATS, int STAGED> AM_D void sample_multi(const DScene &s, PathState &ps, DSample *samples, uint32_t n, V2 p_app, StatCtx *st, TapCtx *tap, const Staged *stg, bool *mis_out = nullptr, bool *adapt_out = nullptr) {
+    if (adapt_out) *adapt_out = false;
     if (s.max_depth == 0) return;
     DSample &p0 = samples[0];
     const Ray p_ray = ps.ray;
@@ -280,6 +283,7 @@ template <bool STATS, int STAGED> AM_D void sample_multi(const DScene &s, PathSt
             sk.indirect = sk.indirect && valid;
         }
         bsdf_sample.pdf = p_not_delta ? fdiv(pdf, n_indir) : bsdf_sample.pdf;
+        if (adapt_out) *adapt_out = p_hit && !flag_null && n_indir <= 1.f;       // mvpath_multi.h:306-307
     }
     // suffix (mvpath_multi.h:522-689): the loop of sample_single entered after the first bounce
     ps.ray = ray; ps.throughput = should_mis ? v3(1.f) : bsdf_weight; ps.result = v3(0.f); ps.prev_p = si.p; ps.eta = bsdf_sample.eta;
@@ -313,7 +317,7 @@ template <bool STATS, int STAGED> AM_D void sample_multi(const DScene &s, PathSt
 
 // MVPT::render_multisample (mvpath_multi.h:8-78) for one lane: camera group, sample_multi, tile offsets of the reused samples
 template <bool STATS, int STAGED = 0> AM_D void lane_multi(const DScene &s, uint32_t seed_value, uint32_t lane, uint32_t px, uint32_t py, DSample *samples, uint32_t n,
-                                           StatCtx *st, TapCtx *tap, const Staged *stg = nullptr, PathState *ps_out = nullptr, bool *mis_out = nullptr) {
+                                           StatCtx *st, TapCtx *tap, const Staged *stg = nullptr, PathState *ps_out = nullptr, bool *mis_out = nullptr, bool *adapt_out = nullptr) {
     PathState ps; LaneSetup ls; V2 aperture;
     lane_setup(s, seed_value, lane, px, py, ps, ls, &aperture);
     const uint32_t p_idx = ls.view, max_idx = n * (p_idx / n + 1u);
@@ -324,8 +328,16 @@ template <bool STATS, int STAGED = 0> AM_D void lane_multi(const DScene &s, uint
         const uint32_t i = p_idx + k; d.idx = i < max_idx ? i : i - n;
     }
     samples[0].px = ls.spx; samples[0].py = ls.spy;
-    sample_multi<STATS, STAGED>(s, ps, samples, n, aperture, st, tap, stg, mis_out);
+    bool adapt = false;
+    sample_multi<STATS, STAGED>(s, ps, samples, n, aperture, st, tap, stg, mis_out, &adapt);
+    if (adapt_out) *adapt_out = adapt;
     if (ps_out) *ps_out = ps;
+    if (s.reuse_debug) {          // mvpath_multi.h:54-56: put(pos, Float(adapt_mask), alpha, 1) and nothing else
+        samples[0].result = v3(adapt ? 1.f : 0.f); samples[0].weight = 1.f; samples[0].valid = true; samples[0].indirect = false;
+        for (uint32_t k = 1; k < n; ++k) { samples[k].valid = false; samples[k].indirect = false; }
+        if (ps_out) ps_out->active = false;
+        if (mis_out) *mis_out = true;         // finish stage: result = record 1 as it stands
+    } else if (s.n_adapt && adapt) samples[0].weight = samples[0].weight * s.adapt_w;
     const uint32_t sres_x = s.film_w / s.grid_x, sres_y = s.film_h / s.grid_y;
     for (uint32_t k = 1; k < n; ++k) {
         DSample &d = samples[k];
@@ -404,7 +416,9 @@ reuse_shade_kernel(const __grid_constant__ DScene s, const __grid_constant__ Ren
     const uint32_t n = s.n_reuse;
     Staged g; g.prim = prim; g.proj = proj; g.m = m; g.i = i; g.nk = n - 1u;
     StatCtx st; st.closest = st.shadow = st.nodes = st.tris = st.vertices = 0;
-    lane_multi<false, 1>(s, p.seed_value, lane, px, py, samples, n, &st, nullptr, &g);
+    bool adapt = false;
+    lane_multi<false, 1>(s, p.seed_value, lane, px, py, samples, n, &st, nullptr, &g, nullptr, nullptr, &adapt);
+    if (p.adapt_mask) p.adapt_mask[c0 + i] = adapt ? 1 : 0;
     splat_samples(s, p.film, samples, n);
 }
 
@@ -423,7 +437,9 @@ reuse_select_kernel(const __grid_constant__ DScene s, const __grid_constant__ Re
     Staged g; g.prim = prim; g.proj = proj; g.m = m; g.i = i; g.nk = n - 1u;
     StatCtx st; PathState ps; bool mis = false; ps.active = false; ps.depth = 0; ps.prev_delta = false;
     ps.ray.o = ps.ray.d = ps.throughput = ps.prev_p = v3(0.f); ps.eta = ps.prev_bsdf_pdf = 0.f; ps.rng.state = ps.rng.inc = 0;
-    lane_multi<false, 2>(s, p.seed_value, lane, px, py, samples, n, &st, nullptr, &g, &ps, &mis);
+    bool adapt = false;
+    lane_multi<false, 2>(s, p.seed_value, lane, px, py, samples, n, &st, nullptr, &g, &ps, &mis, &adapt);
+    if (p.adapt_mask) p.adapt_mask[c0 + i] = adapt ? 1 : 0;
     const bool act = ps.active && s.max_depth != 0;
     b.state[i] = make_float4(ps.ray.o.x, ps.ray.o.y, ps.ray.o.z, ps.prev_bsdf_pdf);
     b.state[(size_t) m + i] = make_float4(ps.ray.d.x, ps.ray.d.y, ps.ray.d.z, ps.eta);
@@ -510,7 +526,9 @@ render_reuse_kernel(const __grid_constant__ DScene s, const __grid_constant__ Re
         if (base >= p.n_lanes) break;
         uint32_t lane, px, py;
         if (!ticket_to_lane(p, s, base + lane_id, &lane, &px, &py)) continue;
-        lane_multi<STATS>(s, p.seed_value, lane, px, py, samples, n, &st, nullptr);
+        bool adapt = false;
+        lane_multi<STATS>(s, p.seed_value, lane, px, py, samples, n, &st, nullptr, nullptr, nullptr, nullptr, &adapt);
+        if (p.adapt_mask) p.adapt_mask[base + lane_id] = adapt ? 1 : 0;
         splat_samples(s, p.film, samples, n);
     }
     if (STATS) flush_stats(st, p.counters);
@@ -521,11 +539,12 @@ template <int NMAX> __global__ void reuse_tap_kernel(const __grid_constant__ DSc
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; if (i >= count) return;
     const uint32_t n = s.n_reuse, lane = lane_begin + i, idx = lane / spp_per_pass, py = idx / s.film_w, px = idx - s.film_w * py;
     StatCtx st; st.closest = st.shadow = st.nodes = st.tris = st.vertices = 0;
-    lane_multi<false>(s, seed_value, lane, px, py, samples, n, &st, nullptr);
+    bool adapt = false;
+    lane_multi<false>(s, seed_value, lane, px, py, samples, n, &st, nullptr, nullptr, nullptr, nullptr, &adapt);
     for (uint32_t k = 0; k < n; ++k) {
         float *o = out + 9 * ((size_t) i * n + k); const DSample &d = samples[k];
         o[0] = d.px; o[1] = d.py; o[2] = d.weight; o[3] = d.result.x; o[4] = d.result.y; o[5] = d.result.z;
-        o[6] = d.valid ? 1.f : 0.f; o[7] = d.indirect ? 1.f : 0.f; o[8] = (float) d.idx;
+        o[6] = (d.valid ? 1.f : 0.f) + (k == 0 && adapt ? 2.f : 0.f); o[7] = d.indirect ? 1.f : 0.f; o[8] = (float) d.idx;
     }
 }
 
@@ -573,6 +592,89 @@ uint32_t run_reuse_staged(const DScene &s, const RenderParams &p, float4 *buf, u
         launches += 3;
     }
     return launches;
+}
+// ------------------------------------------------------------------------------------------------ fill-in pass (mvpath_multi.h:79-115)
+// idx = dr::compress(adapt_mask) keeps the lane order; dr::repeat(idx, n_adapt) repeats every index n_adapt times in place.
+__global__ void __launch_bounds__(1024) adapt_count_kernel(const uint8_t *mask, unsigned long long n, uint32_t *counts) {
+    const unsigned long long t = (unsigned long long) blockIdx.x * 1024ull + threadIdx.x;
+    const int c = __syncthreads_count(t < n && mask[t] != 0);
+    if (threadIdx.x == 0) counts[blockIdx.x] = (uint32_t) c;
+}
+__global__ void __launch_bounds__(1024) adapt_scan_kernel(uint32_t *counts, uint32_t n_blocks) {      // exclusive scan in place, counts[n_blocks] = total
+    __shared__ uint32_t part[1024];
+    const uint32_t t = threadIdx.x, per = (n_blocks + 1023u) / 1024u, b0 = t * per; uint32_t sum = 0;
+    for (uint32_t k = 0; k < per && b0 + k < n_blocks; ++k) sum += counts[b0 + k];
+    part[t] = sum; __syncthreads();
+    for (uint32_t off = 1; off < 1024u; off <<= 1) { const uint32_t x = t >= off ? part[t - off] : 0u; __syncthreads(); part[t] += x; __syncthreads(); }
+    uint32_t run = part[t] - sum;
+    for (uint32_t k = 0; k < per && b0 + k < n_blocks; ++k) { const uint32_t c = counts[b0 + k]; counts[b0 + k] = run; run += c; }
+    if (t == 1023u) counts[n_blocks] = part[1023];
+}
+__global__ void __launch_bounds__(1024) adapt_write_kernel(const uint8_t *mask, unsigned long long n, const uint32_t *offsets, uint32_t *compact) {
+    __shared__ uint32_t warp_base[32];
+    const unsigned long long t = (unsigned long long) blockIdx.x * 1024ull + threadIdx.x;
+    const bool m = t < n && mask[t] != 0; const unsigned lane_id = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const unsigned b = __ballot_sync(0xffffffffu, m);
+    if (lane_id == 0) warp_base[warp] = (uint32_t) __popc(b);
+    __syncthreads();
+    if (warp == 0) { uint32_t v = warp_base[lane_id], inc = v; for (int o = 1; o < 32; o <<= 1) { const uint32_t x = __shfl_up_sync(0xffffffffu, inc, o); if ((int) lane_id >= o) inc += x; } warp_base[lane_id] = inc - v; }
+    __syncthreads();
+    if (m) compact[offsets[blockIdx.x] + warp_base[warp] + (uint32_t) __popc(b & ((1u << lane_id) - 1u))] = (uint32_t) t;      // tickets of one pass fit 32 bits (mvpath.cpp:133-147)
+}
+// One plain path per entry j of repeat(compress(mask), n_adapt): the primary sample's own camera ray (same jitter / aperture / time:
+// regenerated from the primary's stream), the sampler forked and seeded (wavefront2, wavefront2), put with weight adapt_w.
+__global__ void __launch_bounds__(128, AM_REUSE_SUFFIX_MIN_CTAS)
+reuse_fill_kernel(const __grid_constant__ DScene s, const __grid_constant__ RenderParams p, const uint32_t *compact, unsigned long long wavefront2, uint32_t seed2, unsigned long long *ticket_ctr) {
+    const unsigned lane_id = threadIdx.x & 31u;
+    PathState ps; LaneSetup ls; ps.active = false; bool has_result = false, exhausted = false; StatCtx st;
+    for (;;) {
+        const bool idle = !ps.active;
+        const unsigned idle_mask = __ballot_sync(0xffffffffu, idle);
+        if (__popc(idle_mask) >= (int) p.regen_min || idle_mask == 0xffffffffu) {
+            if (idle) {
+                if (has_result && ls.in_film) {
+                    const V3 L = ps.valid_ray ? ps.result : v3(0.f); const float w = s.adapt_w;
+                    atomicAdd(p.film + ls.pixel, make_float4(w * L.x, w * L.y, w * L.z, w));
+                }
+                has_result = false;
+                const unsigned fm = __ballot_sync(idle_mask, !exhausted);
+                if (!exhausted) {
+                    unsigned long long base = 0; const unsigned leader = __ffs(fm) - 1;
+                    if (lane_id == leader) base = atomicAdd(ticket_ctr, (unsigned long long) __popc(fm));
+                    base = __shfl_sync(fm, base, leader);
+                    const unsigned long long j = base + __popc(fm & ((1u << lane_id) - 1u));
+                    if (j < wavefront2) {
+                        uint32_t lane, px, py;
+                        if (ticket_to_lane(p, s, (unsigned long long) compact[j / s.n_adapt], &lane, &px, &py)) {
+                            lane_setup(s, p.seed_value, lane, px, py, ps, ls);
+                            ps.rng = sampler_seed(seed2, (uint32_t) j);
+                            has_result = true; if (s.max_depth == 0) ps.active = false;
+                        }
+                    } else exhausted = true;
+                }
+            }
+            if (__all_sync(0xffffffffu, !ps.active && !has_result && exhausted)) break;
+        }
+        if (ps.active) path_bounce<false, false>(s, ps, nullptr, &st);
+    }
+}
+uint32_t run_reuse_fill_in(const DScene &s, const RenderParams &p, uint32_t base_seed, uint32_t *scratch, uint32_t **compact, size_t *compact_cap, int sm_count, cudaStream_t st, unsigned long long *n_fill) {
+    const unsigned long long n = p.n_lanes; if (!n || !s.n_adapt || !p.adapt_mask) return 0;
+    const uint32_t n_blocks = (uint32_t) ((n + 1023ull) / 1024ull);
+    adapt_count_kernel<<<n_blocks, 1024, 0, st>>>(p.adapt_mask, n, scratch);
+    adapt_scan_kernel<<<1, 1024, 0, st>>>(scratch, n_blocks);
+    uint32_t total = 0; cudaMemcpyAsync(&total, scratch + n_blocks, sizeof(uint32_t), cudaMemcpyDeviceToHost, st); cudaStreamSynchronize(st);
+    if (!total) return 2;
+    if (*compact_cap < total) { if (*compact) cudaFree(*compact); *compact = nullptr; *compact_cap = 0; const size_t cap = (size_t) total + total / 4 + 1024;
+        if (cudaMalloc((void **) compact, cap * sizeof(uint32_t)) != cudaSuccess) return 0; *compact_cap = cap; }
+    adapt_write_kernel<<<n_blocks, 1024, 0, st>>>(p.adapt_mask, n, scratch, *compact);
+    const unsigned long long wavefront2 = (unsigned long long) total * s.n_adapt;
+    cudaMemsetAsync(p.counters + CTR_TICKET, 0, sizeof(unsigned long long), st);
+    int per_sm = 0; cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, reuse_fill_kernel, 128, 0); if (per_sm < 1) per_sm = 1;
+    unsigned grid = (unsigned) (sm_count * per_sm); const unsigned long long need = (wavefront2 + 127ull) / 128ull; if (need < grid) grid = (unsigned) need;
+    reuse_fill_kernel<<<grid, 128, 0, st>>>(s, p, *compact, wavefront2, base_seed + (uint32_t) wavefront2, p.counters + CTR_TICKET);
+    if (n_fill) *n_fill += wavefront2;
+    return 4;
 }
 void launch_reuse_tap(const DScene &s, uint32_t seed_value, uint32_t spp_per_pass, uint32_t lane_begin, uint32_t n, float *out, cudaStream_t st) {
     if (!n) return;

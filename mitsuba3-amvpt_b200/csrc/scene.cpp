@@ -137,7 +137,7 @@ void bsdf_prepare(DBsdf &b) {
 
 // ---------------------------------------------------------------- Scene
 Scene::~Scene() {
-    if (device >= 0) { cudaSetDevice(device); for (void *p : allocs) cudaFree(p); }
+    if (device >= 0) { cudaSetDevice(device); for (void *p : allocs) cudaFree(p); if (adapt_compact) cudaFree(adapt_compact); }
 }
 void *Scene::dalloc(size_t bytes) {
     void *p = nullptr; AM_CUDA(cudaMalloc(&p, bytes ? bytes : 16)); allocs.push_back(p); return p;
@@ -236,7 +236,7 @@ void Scene::set_reuse(bool sa_reuse, bool sa_mis, bool fast_mis, uint32_t reuse_
     integrator.sa_reuse = sa_reuse; integrator.sa_mis = sa_mis; integrator.fast_mis = fast_mis; integrator.reuse_count = reuse_count;
     integrator.adaptive = adaptive;
     if (reuse_samples() > 64) AM_THROW("mvpath: reuse_count %u exceeds the 64 cameras per group this build keeps per lane", reuse_samples());
-    if (committed) { d.n_reuse = reuse_samples(); d.sa_mis = sa_mis; d.fast_mis = fast_mis; }
+    if (committed) { d.n_reuse = reuse_samples(); d.sa_mis = sa_mis; d.fast_mis = fast_mis; d.n_adapt = d.n_reuse ? std::min(adaptive, d.n_reuse - 1u) : 0u; d.adapt_w = 1.f / (float) (d.n_adapt + 1u); d.reuse_debug = integrator.debug ? 1 : 0; }
 }
 // View tiles of the quilt owned by one rank: view v = ix + grid_x * iy (sub-sensor index), tile position follows
 // GridSensor::sample_ray's axis reversal (grid.cpp:246-255).
@@ -315,6 +315,8 @@ void Scene::commit(int dev) {
         aux.push_back(a);
     }
     d.sensor_aux = upload(aux); d.n_reuse = reuse_samples(); d.sa_mis = integrator.sa_mis; d.fast_mis = integrator.fast_mis;
+    d.n_adapt = d.n_reuse ? std::min(integrator.adaptive, d.n_reuse - 1u) : 0u; d.adapt_w = 1.f / (float) (d.n_adapt + 1u); d.reuse_debug = integrator.debug ? 1 : 0;
+    adapt_mask = nullptr; adapt_scratch = nullptr; adapt_cap = 0; if (adapt_compact) { cudaFree(adapt_compact); adapt_compact = nullptr; adapt_compact_cap = 0; }
     d.sensors = upload(sensors); d.area_cdf = upload(cdf_all); d.area_pmf = upload(pmf_all);
     d.n_tris = n_tris; d.n_nodes = n_nodes; d.n_emitters = (uint32_t) emitters.size(); d.n_sensors = (uint32_t) sensors.size();
     d.grid_x = grid_x; d.grid_y = grid_y; d.reverse_x = reverse_x; d.reverse_y = reverse_y; d.thinlens = thinlens; d.shutter_draw = shutter_draw ? 1 : 0;

@@ -9,6 +9,8 @@ S2: procedural height field z = 0.15 sin(7x) cos(5y) + 0.05 sin(31x + 17y) over 
     1 002 528 triangles), four meshes with roughconductor / roughdielectric / roughplastic / diffuse BSDFs, inside a
     12-triangle diffuse box with a 2-triangle area light of radiance 10.
 """
+import os
+
 import numpy as np
 
 CBOX_QUADS = {
@@ -75,6 +77,32 @@ def cornell_box(grid_x=4, grid_y=1, view_res=256, cam_dist=200.0, max_depth=6, r
     return dict(name=f"cbox_{grid_x}x{grid_y}_{view_res}", bsdfs=bsdfs, meshes=meshes, sensor=sensor, integrator=integrator)
 
 
+CBOX_XML = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden", "scenes", "scenes", "cbox", "cbox-rgb.xml")
+
+
+def cornell_box_ref(grid_x=4, grid_y=1, view_res=256, cam_dist=200.0, max_depth=6, rr_depth=5, spp_pass_lim=16, sample_count=64, sampler_seed=0):
+    """S1 of SURVEY.md sec.8d: the geometry and materials of the reference's own resources/data/scenes/cbox/cbox-rgb.xml (8 OBJ meshes, 38
+    triangles, 5 diffuse BSDFs, one area emitter; a byte-for-byte copy lives under tests/golden/scenes), read by the product's XML loader, with
+    the file's perspective camera replaced by a `grid` of such cameras on a line (the reference has no scene that uses its grid sensor)."""
+    import importlib
+    pkg = importlib.import_module("mitsuba3-amvpt_b200")
+    s = pkg.load_file(CBOX_XML, res=view_res, spp=sample_count, max_depth=max_depth)
+    c = s.counts()
+    bsdfs = [s.bsdf(i) for i in range(c["n_bsdfs"])]
+    for b in bsdfs:
+        b["alpha_u"], b["alpha_v"] = float(b["alpha_u"]), float(b["alpha_v"])
+    meshes = []
+    for i in range(c["n_meshes"]):
+        m = s.mesh(i); meshes.append(dict(name=f"cbox{i}", positions=m["positions"], faces=m["faces"], normals=m["normals"], bsdf=m["bsdf"],
+                                          radiance=m["radiance"], flip_normals=m["flip_normals"]))
+    sensor = dict(grid_x=grid_x, grid_y=grid_y, res_x=grid_x * view_res, res_y=grid_y * view_res,
+                  to_world=look_at((278, 273, -800), (278, 273, -799), (0, 1, 0)), fov=39.3077, fov_axis="smaller", near_clip=10.0,
+                  far_clip=2800.0, focus_distance=1000.0, thinlens=False, aperture_radius=0.0, reverse_x=False,
+                  reverse_y=True, cone_deg=None, cam_dir=(1.0, 0.0, 0.0), cam_dist=cam_dist, cam_center=True, cam_off=(0.0, 0.0, 0.0))
+    integrator = dict(max_depth=max_depth, rr_depth=rr_depth, hide_emitters=False, spp_pass_lim=spp_pass_lim, sampler_seed=sampler_seed, sample_count=sample_count)
+    return dict(name=f"cboxref_{grid_x}x{grid_y}_{view_res}", bsdfs=bsdfs, meshes=meshes, sensor=sensor, integrator=integrator)
+
+
 def height_field(n=708, grid_x=4, grid_y=4, view_res=1024, max_depth=8, rr_depth=5, spp_pass_lim=16, sample_count=64,
                  sampler_seed=0, smooth_normals=True):
     """S2 of SURVEY.md sec.8d.  Vertex data are float32 functions of integer grid indices (no RNG)."""
@@ -137,7 +165,10 @@ def build(desc, device=0, commit=True):
     if desc.get("rfilter"):
         s.set_rfilter(*desc["rfilter"])
     if desc.get("reuse"):
-        s.set_reuse(**desc["reuse"])
+        r = dict(desc["reuse"]); dbg = r.pop("debug", False)
+        s.set_reuse(**r)
+        if dbg:
+            s.set_reuse_debug(True)
     if commit:
         s.commit(device)
     return s

@@ -17,6 +17,7 @@
 #include <algorithm>
 #include <atomic>
 #include <chrono>
+#include <functional>
 #include <thread>
 #include <vector>
 
@@ -86,7 +87,7 @@ struct Scene {
     uint32_t max_depth = 0xffffffffu, rr_depth = 5; int hide_emitters = 0;
     uint32_t base_seed = 0;
     // cross-view sample reuse (mvpath.h:120-129): n_reuse = samples per primary sample after mvpath.cpp:192-218 (0 = off)
-    int sa_mis = 0, fast_mis = 0; uint32_t n_reuse = 0;
+    int sa_mis = 0, fast_mis = 0; uint32_t n_reuse = 0; uint32_t adaptive = 0; int debug = 0;     // adaptive: fill-in samples of the reuse branch (mvpath.h:125)
     // reconstruction filter of the film: 0 box, 1 gaussian (src/rfilters/gaussian.cpp), 2 tent (src/rfilters/tent.cpp)
     int filter_type = 0; float filter_radius = 0.5f, filter_coeff[10] = { 0 }, filter_inv_radius = 1.f;
     // flattened primitives
@@ -744,6 +745,7 @@ void orc_set_integrator(void *sp, int64_t max_depth, uint32_t rr_depth, int hide
     s.max_depth = max_depth < 0 ? 0xffffffffu : (uint32_t) max_depth;        // integrator.cpp:503-520
     s.rr_depth = rr_depth; s.hide_emitters = hide_emitters; s.base_seed = sampler_seed;
 }
+void orc_set_reuse_adaptive(void *sp, uint32_t adaptive, int debug) { Scene &s = *(Scene *) sp; s.adaptive = adaptive; s.debug = debug; }
 void orc_set_shutter_draw(void *sp, int draw) { ((Scene *) sp)->shutter_draw = draw; }
 // scene-level emitters (src/emitters/{point,constant,envmap}.cpp); the environment map is rebuilt here from the raw RGB pixels
 int orc_add_emitter_point(void *sp, const float *pos, const float *intensity) {
@@ -961,6 +963,40 @@ double orc_render_rows(void *sp, uint32_t seed, uint32_t spp, uint32_t spp_pass_
     size_t film_floats = 4 * (size_t) s.film_w * s.film_h;
     std::vector<std::vector<float>> tfilm; if (s.filter_type != 0 && nthreads > 1) tfilm.assign(nthreads, std::vector<float>(film_floats, 0.f));
     auto t0 = std::chrono::steady_clock::now();
+    const uint32_t n_adapt = s.n_reuse ? std::min(s.adaptive, s.n_reuse - 1u) : 0u;
+    if (n_adapt && !s.debug && row_stride == 1 && row_begin == 0 && row_end == s.film_h) {
+        // render_multisample with the fill-in pass (mvpath_multi.h:79-115), pass by pass: (1) every lane of the wavefront, recording
+        // adapt_mask; (2) idx = compress(mask) in lane order, each index repeated n_adapt times; (3) a forked sampler seeded
+        // (wavefront2, wavefront2) traces one plain path per entry through the primary sample's own camera ray and puts it with weight adapt_w
+        auto add = [](float *p, float v) { uint32_t o, n; std::memcpy(&o, p, 4);
+            do { float f; std::memcpy(&f, &o, 4); f += v; std::memcpy(&n, &f, 4); } while (!__atomic_compare_exchange_n((uint32_t *) p, &o, n, true, __ATOMIC_RELAXED, __ATOMIC_RELAXED)); };
+        auto put = [&](uint32_t ux, uint32_t uy, V3 v, float w) { float *px = film + 4 * ((size_t) uy * s.film_w + ux); add(px, v.x); add(px + 1, v.y); add(px + 2, v.z); add(px + 3, w); };
+        const float adapt_w = 1.f / (float) (n_adapt + 1u);
+        const size_t wavefront = (size_t) s.film_w * s.film_h * spp_per_pass;
+        std::vector<uint8_t> mask(wavefront);
+        auto parallel = [&](size_t count, const std::function<void(size_t, int)> &fn) {
+            std::atomic<size_t> next{ 0 }; const size_t chunk = 4096;
+            auto w = [&](int tid) { for (;;) { size_t b = next.fetch_add(chunk); if (b >= count) break; for (size_t i = b; i < std::min(count, b + chunk); ++i) fn(i, tid); } };
+            if (nthreads <= 1) w(0); else { std::vector<std::thread> th; for (int i = 0; i < nthreads; ++i) th.emplace_back(w, i); for (auto &t : th) t.join(); }
+        };
+        for (uint32_t pass = 0; pass < n_passes; ++pass) {
+            const uint32_t seed_value = s.base_seed + (spp_per_pass * pass + seed);
+            parallel(wavefront, [&](size_t lane, int tid) { bool m = false;
+                render_lane_multi(s, seed_value, (uint32_t) lane, spp_per_pass, s.n_reuse, brute != 0, nullptr, &tstats[tid], put, nullptr, &m); mask[lane] = m ? 1 : 0; });
+            std::vector<uint32_t> idx; for (size_t lane = 0; lane < wavefront; ++lane) if (mask[lane]) idx.push_back((uint32_t) lane);
+            const size_t wavefront2 = idx.size() * n_adapt; if (!wavefront2) continue;
+            const uint32_t seed2 = s.base_seed + (uint32_t) wavefront2;              // sampler2->seed(wavefront, wavefront), sampler.cpp:125-144
+            parallel(wavefront2, [&](size_t j, int tid) {
+                const uint32_t src = idx[j / n_adapt];
+                LaneOut o = render_lane(s, seed_value, src, spp_per_pass, brute != 0, nullptr, &tstats[tid], /* trace = */ false);   // sample_pos, aperture, ray of the primary sample
+                Pcg32 rng2 = sampler_seed(seed2, (uint32_t) j);
+                PathResult r = sample_single(s, rng2, o.ray, brute != 0, nullptr, &tstats[tid]);
+                if (o.in_film) put(o.pixel % s.film_w, o.pixel / s.film_w, V3(adapt_w) * r.L, adapt_w); });
+        }
+        double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+        if (stats) { stats[0] = stats[1] = 0; for (auto &t : tstats) { stats[0] += t.nodes; stats[1] += t.tris; } }
+        return sec;
+    }
     auto worker = [&](int tid) {
         for (;;) {
             uint64_t yy = (uint64_t) row_begin + (uint64_t) next_row.fetch_add(1) * row_stride; if (yy >= row_end) break;
@@ -1000,11 +1036,12 @@ void orc_trace_lanes_multi(void *sp, uint32_t seed_value, uint32_t spp_per_pass,
     Scene &s = *(Scene *) sp; uint32_t nr = s.n_reuse; if (!nr) return;
     for (uint32_t i = 0; i < n; ++i) {
         SampleData sd[MaxReuse];
-        render_lane_multi(s, seed_value, lane_begin + i, spp_per_pass, nr, brute != 0, nullptr, nullptr, [](uint32_t, uint32_t, V3, float) {}, sd);
+        bool adapt = false;
+        render_lane_multi(s, seed_value, lane_begin + i, spp_per_pass, nr, brute != 0, nullptr, nullptr, [](uint32_t, uint32_t, V3, float) {}, sd, &adapt);
         for (uint32_t k = 0; k < nr; ++k) {
             float *o = out + 9 * ((size_t) i * nr + k);
             o[0] = sd[k].pos.x; o[1] = sd[k].pos.y; o[2] = sd[k].weight; o[3] = sd[k].result.x; o[4] = sd[k].result.y; o[5] = sd[k].result.z;
-            o[6] = sd[k].valid ? 1.f : 0.f; o[7] = sd[k].indirect ? 1.f : 0.f; o[8] = (float) sd[k].idx;
+            o[6] = (sd[k].valid ? 1.f : 0.f) + (k == 0 && adapt ? 2.f : 0.f); o[7] = sd[k].indirect ? 1.f : 0.f; o[8] = (float) sd[k].idx;      // + 2: adapt_mask of the lane (record 0 only)
         }
     }
 }

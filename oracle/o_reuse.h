@@ -8,7 +8,8 @@
 // Semantics are those of the JIT variants, lane by lane: `dr::any_or<true>` / `dr::none_or<false>` never skip a statement,
 // a masked virtual call returns zeros for a masked-out lane, random numbers are drawn by every lane that reaches the draw.
 // PARITY UNPINNED: the reference holds no test for this branch; this restatement is the only checker.
-// Not restated: the `adaptive` fill-in (mvpath_multi.h:79-115) and the `debug` output (:56-58).
+// The `adaptive` fill-in (mvpath_multi.h:52-58, 79-115) is restated in render_lane_multi (mask, primary weight, `debug` output) and in
+// orc_render_rows (amvpt_oracle.cpp: dr::compress / dr::repeat order, the forked sampler seeded (wavefront, wavefront), the weighted put).
 
 struct SampleData {          // mvpath.h:150-167
     V3 result, bsdf_val, wi, wo_r; V2 pos{ 0.f, 0.f };
@@ -246,7 +247,8 @@ static void mis_weights(const Scene &s, SampleData *samples, uint32_t n, const B
 }
 
 // MVPT::sample_multi (mvpath_multi.h:133-358)
-static bool sample_multi(const Scene &s, Pcg32 &rng, SampleData *samples, uint32_t n, const Ray &p_ray, V2 p_app, bool brute, Tap *tap, TraverseStats *st) {
+static bool sample_multi(const Scene &s, Pcg32 &rng, SampleData *samples, uint32_t n, const Ray &p_ray, V2 p_app, bool brute, Tap *tap, TraverseStats *st, bool *adapt_mask = nullptr) {
+    if (adapt_mask) *adapt_mask = false;
     if (s.max_depth == 0) return false;
     SampleData &ps = samples[0];
     bool valid_ray = false;                                // no environment emitter on this path
@@ -308,6 +310,7 @@ static bool sample_multi(const Scene &s, Pcg32 &rng, SampleData *samples, uint32
             sk.indirect = sk.indirect && valid;
         }
         bsdf_sample.pdf = p_not_delta ? pdf / n_indir : bsdf_sample.pdf;
+        if (adapt_mask) *adapt_mask = p_hit && !flag_null && n_indir <= 1.f;      // mvpath_multi.h:306-307: only the primary camera collected the sample
     }
     V3 throughput = should_mis ? V3(1.f) : bsdf_weight;
     valid_ray = valid_ray || (p_hit && !flag_null);
@@ -331,7 +334,7 @@ static bool sample_multi(const Scene &s, Pcg32 &rng, SampleData *samples, uint32
 // MVPT::render_multisample (mvpath_multi.h:8-78) for one lane; the n splats go through `put(x, y, rgb, weight)`
 constexpr uint32_t MaxReuse = 64;
 template <typename Put> static void render_lane_multi(const Scene &s, uint32_t seed_value, uint32_t lane, uint32_t spp_per_pass, uint32_t n, bool brute, Tap *tap,
-                                                     TraverseStats *st, Put put, SampleData *out = nullptr) {
+                                                     TraverseStats *st, Put put, SampleData *out = nullptr, bool *adapt_out = nullptr) {
     Pcg32 rng = sampler_seed(seed_value, lane);
     uint32_t idx = lane / spp_per_pass, py = idx / s.film_w, px = idx - s.film_w * py;
     float sx = 1.f / (float) s.film_w, sy = 1.f / (float) s.film_h;
@@ -346,7 +349,17 @@ template <typename Put> static void render_lane_multi(const Scene &s, uint32_t s
     uint32_t max_idx = n * (p_idx / n + 1u);
     for (uint32_t k = 0; k < n; ++k) { uint32_t i = p_idx + k; samples[k].idx = i < max_idx ? i : i - n; }
     samples[0].pos = { spx, spy };
-    sample_multi(s, rng, samples, n, ray, aperture, brute, tap, st);
+    bool adapt_mask = false;
+    sample_multi(s, rng, samples, n, ray, aperture, brute, tap, st, &adapt_mask);
+    if (adapt_out) *adapt_out = adapt_mask;
+    // mvpath_multi.h:52-58: the fill-in samples are averaged with the primary one; `debug` shows the mask instead of the image
+    const uint32_t n_adapt = std::min(s.adaptive, n - 1u); const float adapt_w = 1.f / (float) (n_adapt + 1u);
+    if (s.debug) {
+        if (out) for (uint32_t i = 0; i < n; ++i) { out[i] = samples[i]; if (i) out[i].valid = false; else { out[0].result = V3(adapt_mask ? 1.f : 0.f); out[0].weight = 1.f; out[0].valid = true; } }
+        int32_t fx = (int32_t) std::floor(spx), fy = (int32_t) std::floor(spy); uint32_t ux = (uint32_t) fx, uy = (uint32_t) fy;
+        if (ux < s.film_w && uy < s.film_h) put(ux, uy, V3(adapt_mask ? 1.f : 0.f), 1.f);
+        return;
+    } else if (n_adapt && adapt_mask) samples[0].weight = samples[0].weight * adapt_w;
     uint32_t sres_x = s.film_w / s.grid_x, sres_y = s.film_h / s.grid_y;
     for (uint32_t i = 0; i < n; ++i) {
         SampleData &sa = samples[i];

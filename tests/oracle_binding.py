@@ -167,10 +167,11 @@ class OracleScene:
         self.spp_pass_lim = spp_pass_lim
         self.o.orc_set_integrator(self.h, C.c_int64(max_depth), C.c_uint32(rr_depth), C.c_int(int(hide_emitters)), C.c_uint32(sampler_seed))
 
-    def set_reuse(self, sa_reuse=True, sa_mis=False, fast_mis=False, reuse_count=0):
+    def set_reuse(self, sa_reuse=True, sa_mis=False, fast_mis=False, reuse_count=0, adaptive=0, debug=False):
         """MVPathIntegrator sa_reuse / sa_mis / fast_mis / reuse_count; returns the samples per primary sample (0 = off)."""
         self.o.orc_set_reuse.restype = C.c_uint32
         self.n_reuse = self.o.orc_set_reuse(self.h, C.c_int(int(sa_reuse)), C.c_int(int(sa_mis)), C.c_int(int(fast_mis)), C.c_uint32(reuse_count))
+        self.o.orc_set_reuse_adaptive(self.h, C.c_uint32(adaptive), C.c_int(int(debug)))
         return self.n_reuse
 
     def trace_lanes_multi(self, seed_value, spp_per_pass, lane_begin, n, brute=True):

@@ -502,6 +502,53 @@ def test_sample_reuse_lanes_and_film_match_oracle(name, ov, cfg, scenes, ob, gpu
         assert np.abs(other[..., :3] - film[..., :3]).max() <= 5 * FILM_RTOL * scale, env
 
 
+@pytest.mark.parametrize("adaptive", [1, 4])
+@pytest.mark.parametrize("ov", [None, "rough", "glass"])
+def test_sample_reuse_adaptive_fill_in(ov, adaptive, scenes, ob, gpu):
+    """The reference's `adaptive` feature (mvpath_multi.h:52-58, 79-115): lanes whose sample only the primary camera collected get their weight
+    scaled by 1 / (n_adapt + 1) and n_adapt extra plain paths (compress / repeat order, forked sampler seeded (wavefront, wavefront)).  Lane
+    records incl. the mask are bit-exact against the oracle, the film agrees within the summation-order tolerance, weights are conserved, and
+    `debug` shows the mask."""
+    desc = scenes.cornell_box(grid_x=4, grid_y=2, view_res=16, cam_dist=150.0, sample_count=16, bsdf_overrides=REUSE_OVERRIDES[ov])
+    desc["reuse"] = dict(sa_reuse=True, sa_mis=True, fast_mis=False, reuse_count=4, adaptive=adaptive)
+    s = scenes.build(desc, device=gpu); o = ob.OracleScene(desc)
+    W, H = o.film_size(); n = W * H * 4
+    a = s.trace_lanes_multi(7, 4, 0, n); b = o.trace_lanes_multi(7, 4, 0, n, brute=True)
+    assert np.array_equal(a[..., 6:], b[..., 6:]), "validity + adapt mask / indirect flags / camera indices"
+    mask = b[:, 0, 6] >= 2
+    assert 0.01 < mask.mean() < 0.99, f"adapt mask fraction {mask.mean()}: the test would be vacuous"
+    valid = (b[..., 6] % 2) > 0
+    for c in (slice(0, 2), slice(2, 3), slice(3, 6)):
+        assert np.array_equal(a[..., c][valid].view(np.uint32), b[..., c][valid].view(np.uint32))
+    n_adapt = min(adaptive, 3)
+    # without the fill-in the masked lanes' primary weight is (n_adapt + 1) times larger
+    d0 = dict(desc); d0["reuse"] = dict(desc["reuse"], adaptive=0); s0 = scenes.build(d0, device=gpu); a0 = s0.trace_lanes_multi(7, 4, 0, n)
+    assert np.allclose(a[mask, 0, 2] * (n_adapt + 1), a0[mask, 0, 2], rtol=1e-6) and np.array_equal(a[~mask, 0, 2], a0[~mask, 0, 2])
+    s.render(seed=3, spp=16, develop=False); film = s.film_raw(); fills = s.last_fill_paths()
+    ofilm, _, _ = o.render(seed=3, spp=16, brute=True, nthreads=4)
+    assert fills > 0 and fills % n_adapt == 0
+    scale = ofilm[..., :3].max()
+    assert np.allclose(film[..., 3], ofilm[..., 3], rtol=1e-5, atol=1e-5)
+    assert np.abs(film[..., :3] - ofilm[..., :3]).max() <= 5 * FILM_RTOL * scale
+    s0.render(seed=3, spp=16, develop=False); film0 = s0.film_raw()
+    assert abs(film[..., 3].sum() - film0[..., 3].sum()) < 1e-2 * film0[..., 3].sum()         # (w0 + n_adapt) / (n_adapt + 1) per masked lane: equal when the primary's MIS weight is 1
+    # every schedule records the same mask and runs the same fill-in
+    for env in (dict(AMVPT_REUSE_CHUNK="1000"), dict(AMVPT_REUSE_STAGED="1", AMVPT_REUSE_CHUNK="1500"), dict(AMVPT_REUSE_STAGED="0")):
+        os.environ.update(env)
+        try:
+            s.render(seed=3, spp=16, develop=False); other = s.film_raw(); assert s.last_fill_paths() == fills
+        finally:
+            for k in env:
+                del os.environ[k]
+        assert np.allclose(other[..., 3], film[..., 3], rtol=1e-5, atol=1e-5) and np.abs(other[..., :3] - film[..., :3]).max() <= 5 * FILM_RTOL * scale, env
+    # debug: the film holds the mask (weight 1 per primary sample), nothing else
+    s.set_reuse_debug(True); s.render(seed=3, spp=4, develop=False); dbg = s.film_raw()
+    o2 = ob.OracleScene(dict(desc, reuse=dict(desc["reuse"], debug=True))); odbg, _, _ = o2.render(seed=3, spp=4, brute=True, nthreads=4)
+    assert np.array_equal(dbg, odbg) and np.array_equal(dbg[..., 0], dbg[..., 1]) and (dbg[..., 3] >= 3).all() and 0 < dbg[..., 0].sum() < dbg[..., 3].sum()
+    with pytest.raises(Exception, match="one rank"):
+        s.set_reuse_debug(False); s.render(seed=3, spp=4, develop=False, rank=0, world=2)
+
+
 def test_sample_reuse_is_consistent_with_plain_path_tracing(scenes, gpu):
     """With MIS the reused estimator converges to the same image as the plain integrator and, at equal primary samples, has a
     lower error against a high-spp reference (the point of the method); sharding by view still sums to the single-GPU film."""
