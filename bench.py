@@ -232,9 +232,11 @@ def b200_arm(args, factory, kw, spp, threads, rank, world, local, extra_workload
             dist.barrier()
         torch.cuda.synchronize()
 
-    hook = None
-    if args.adaptive and world > 1:
-        hook = importlib.import_module("mitsuba3-amvpt_b200.multigpu").make_allreduce_hook(f"cuda:{local}")
+    # torch.distributed is the bootstrap (rendezvous, the timing max / sum over ranks); the two data exchanges of the path -- film gather
+    # and the adaptive statistics all-reduce -- go through the library's own NCCL communicator (amvpt_comm, csrc/comm.cpp)
+    comm = None
+    if world > 1:
+        comm = importlib.import_module("mitsuba3-amvpt_b200.multigpu").bootstrap_comm(pkg, rank, world, local)
 
     def measure(workload, factory, kw, spp, steps, warmup, adaptive, with_e2e=True):
         desc = getattr(scenes, factory)(**kw); desc.update(EXTRA.get(workload, {}))
@@ -243,14 +245,10 @@ def b200_arm(args, factory, kw, spp, threads, rank, world, local, extra_workload
         n_paths = W * H * spp
         film_ptr, _ = s.film_device_ptr()
 
-        def gather_film(ptr):
-            """NCCL film hand-off: ranks own disjoint pixels (box filter), so a sum-reduce to rank 0 equals the gather of tiles."""
-            if dist is not None:
-                dist.reduce(torch.as_tensor(_Ptr(ptr, W * H * 4), device=f"cuda:{local}"), dst=0, op=dist.ReduceOp.SUM)
-
         def step():
-            s.render(seed=0, spp=spp, develop=False, scheduler=args.scheduler, rank=rank, world=world, adaptive=adaptive, allreduce=hook)
-            gather_film(film_ptr)
+            s.render(seed=0, spp=spp, develop=False, scheduler=args.scheduler, rank=rank, world=world, adaptive=adaptive, comm=comm)
+            if comm is not None:
+                s.film_gather(comm, root=0)        # every rank sends the view tiles it rendered; rank 0 adds them into its film
             return s.last_stats
 
         for _ in range(warmup):
@@ -289,12 +287,10 @@ def b200_arm(args, factory, kw, spp, threads, rank, world, local, extra_workload
             # ---- end to end through the C ABI with host buffers (scene description -> BVH build -> upload + render + develop + D2H every step)
             def e2e_step():
                 sc = scenes.build(desc, device=local)
-                img = sc.render(seed=0, spp=spp, develop=(world == 1), scheduler=args.scheduler, rank=rank, world=world, adaptive=adaptive, allreduce=hook)
-                if world > 1:
-                    fp, _ = sc.film_device_ptr(); gather_film(fp)
-                    if rank == 0:
-                        img = sc.develop()
-                return img
+                sc.render(seed=0, spp=spp, develop=False, scheduler=args.scheduler, rank=rank, world=world, adaptive=adaptive, comm=comm)
+                if comm is not None:
+                    sc.film_gather(comm, root=0)
+                return sc.develop_pinned() if rank == 0 else None      # develop + D2H into the library's page-locked buffer (synchronises)
             e2e_steps = max(1, min(steps, 5))
             e2e_step(); barrier(); t0 = time.perf_counter()
             for _ in range(e2e_steps):
@@ -316,7 +312,7 @@ def b200_arm(args, factory, kw, spp, threads, rank, world, local, extra_workload
                "config": {"workload": r["workload"], **r["kw"], **({"reuse": EXTRA[r["workload"]]["reuse"], "reuse_samples": s.n_reuse} if r["workload"] in EXTRA else {}),
                           "spp": r["spp"], "adaptive": bool(args.adaptive), "scheduler": args.scheduler, "scheduler_used": sched, "quilt": [W, H], "paths_per_step": r["n_paths"],
                           "l2_policy": f"film {W * H * 16 / 1e6:.0f} MB > 126 MB L2 rewritten every pass" if W * H * 16 > 126e6 else "film smaller than L2 (small workload)",
-                          "parallelism": f"views sharded over {world} rank(s), NCCL film reduce to rank 0" if world > 1 else "single GPU"},
+                          "parallelism": f"views sharded over {world} rank(s); each rank sends its own view tiles to rank 0 (ncclSend/Recv behind the C ABI)" if world > 1 else "single GPU"},
                "clocks": r["clk"], "gpu_launches": r["launches"], "wall_s": r["wall"], "rank_ms_render_step": r["rank_ms"]}
         if "e2e" in r:
             out["e2e"] = r["e2e"]

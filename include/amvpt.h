@@ -23,6 +23,7 @@ extern "C" {
 #define AMVPT_ERR_IO (-3)        /* file not found / parse error */
 
 typedef struct amvpt_scene amvpt_scene;
+typedef struct amvpt_comm amvpt_comm;      /* one NCCL communicator of this process (one process per GPU) */
 
 /* BSDF plugin parameters (src/bsdfs/{diffuse,conductor,dielectric,roughconductor,roughdielectric,roughplastic}.cpp
  * constructors; `twosided` = wrapped in src/bsdfs/twosided.cpp).  type: 0 diffuse, 1 conductor, 2 dielectric,
@@ -62,7 +63,8 @@ typedef struct amvpt_render_desc {
     uint32_t rank, world;          /* this process renders the view tiles v with v mod world == rank */
     int32_t adaptive; float adaptive_threshold; uint32_t adaptive_min_spp;
     void *stream;                  /* cudaStream_t or NULL */
-    void (*allreduce)(float *dev, uint32_t n, void *user); void *allreduce_user;   /* stats all-reduce hook (NCCL) */
+    void (*allreduce)(float *dev, uint32_t n, void *user); void *allreduce_user;   /* stats all-reduce hook (any collective library); must complete before it returns */
+    struct amvpt_comm *comm;       /* or: an amvpt_comm -- the library all-reduces the statistics itself (ncclAllReduce on `stream`) */
 } amvpt_render_desc;
 
 typedef struct amvpt_render_stats {
@@ -149,11 +151,31 @@ int amvpt_shard_tiles(amvpt_scene *s, uint32_t rank, uint32_t world, uint32_t *o
  * GridSensor::sample_ray's axis reversal (src/sensors/grid.cpp:246-255): same 5-uint32 records, returns their number.  This is
  * the per-view split amvpt_film_write_pfm / _exr(view) cut by */
 int amvpt_view_tiles(amvpt_scene *s, uint32_t *out5, uint32_t cap);
+/* ---- multi-GPU hand-off (build-defined; the reference is single-device).  NCCL is bound at run time.
+ * amvpt_comm_unique_id: ncclGetUniqueId on one rank (128 bytes, hand them to the other ranks by any means: MPI, a file, torch.distributed);
+ * amvpt_comm_init: ncclCommInitRank on `device`; amvpt_film_gather: the root's film receives every other rank's view tiles (each rank
+ * sends only what it rendered, 1 / world of the quilt, plus the border pixels where a jittered sample can round up into the next pixel; with sample reuse or a wide reconstruction filter the whole quilt is sum-reduced);
+ * enqueued on `stream` (NULL = default stream), returns without synchronising */
+int amvpt_comm_unique_id(uint8_t *id128);
+int amvpt_comm_init(const uint8_t *id128, uint32_t rank, uint32_t world, int device, amvpt_comm **out);
+void amvpt_comm_destroy(amvpt_comm *c);
+int amvpt_film_gather(amvpt_scene *s, amvpt_comm *c, uint32_t root, void *stream);
+int amvpt_comm_allreduce_sum(amvpt_comm *c, float *dev, uint32_t n, void *stream);
+/* the rectangles amvpt_film_gather moves for `rank` of `world` (host logic, no device needed): the rank's view tiles and 1-pixel-wide runs of
+ * the foreign pixels just right of / below them (every pixel at most once), records of 5 uint32 {x0, y0, w, h, pixel offset in the staging
+ * buffer}; returns their number */
+int amvpt_gather_tiles(amvpt_scene *s, uint32_t rank, uint32_t world, uint32_t *out5, uint32_t cap);
+/* the adaptive allocator's decisions of the last amvpt_render(adaptive = 1): out[pass * n_views + view] = samples per pixel (lane
+ * indices k < that number of the pass's lane map were traced); pass out = NULL to query the sizes.  Identical on every rank */
+int amvpt_adaptive_alloc(amvpt_scene *s, uint32_t *out, uint32_t cap, uint32_t *n_passes, uint32_t *n_views);
 int amvpt_cancel(amvpt_scene *s);                                        /* Integrator::cancel (integrator.h:303-306) */
 int amvpt_film_clear(amvpt_scene *s);                                    /* Film::prepare / clear (hdrfilm.cpp:245-273) */
 int amvpt_film_raw(amvpt_scene *s, float *rgbw_host);                    /* film storage, H*W*4 floats to host */
 int amvpt_film_develop(amvpt_scene *s, float *rgb_host);                 /* HDRFilm::develop (hdrfilm.cpp:321-408), H*W*3 to host */
 int amvpt_film_develop_device(amvpt_scene *s, float *rgb_dev, void *stream);
+/* develop into a page-locked host buffer owned by the library (one per process, grown on demand, reused by every call and every scene):
+ * *rgb_host stays valid until the next call; the copy runs at PCIe rate instead of through a pageable bounce buffer */
+int amvpt_film_develop_pinned(amvpt_scene *s, float **rgb_host);
 int amvpt_film_device_ptr(amvpt_scene *s, void **rgbw_dev, void **moments_dev);   /* for the NCCL film gather */
 int amvpt_film_add_host(amvpt_scene *s, const float *rgbw_host);         /* ImageBlock::put_block (imageblock.cpp:135-172) */
 

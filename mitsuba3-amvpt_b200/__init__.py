@@ -61,7 +61,7 @@ ALLREDUCE_FN = C.CFUNCTYPE(None, C.c_void_p, C.c_uint32, C.c_void_p)
 class RenderDesc(C.Structure):
     _fields_ = [("seed", C.c_uint32), ("spp", C.c_uint32), ("scheduler", C.c_int32), ("collect_stats", C.c_int32),
                 ("rank", C.c_uint32), ("world", C.c_uint32), ("adaptive", C.c_int32), ("adaptive_threshold", C.c_float),
-                ("adaptive_min_spp", C.c_uint32), ("stream", C.c_void_p), ("allreduce", ALLREDUCE_FN), ("allreduce_user", C.c_void_p)]
+                ("adaptive_min_spp", C.c_uint32), ("stream", C.c_void_p), ("allreduce", ALLREDUCE_FN), ("allreduce_user", C.c_void_p), ("comm", C.c_void_p)]
 
 
 class RenderStats(C.Structure):
@@ -76,12 +76,14 @@ EXPORTS = ["amvpt_last_error", "amvpt_device_count", "amvpt_scene_create", "amvp
            "amvpt_scene_from_xml_string", "amvpt_scene_add_bsdf", "amvpt_scene_add_mesh", "amvpt_scene_set_sensor_grid",
            "amvpt_scene_set_sensor_batch", "amvpt_scene_add_emitter_point", "amvpt_scene_add_emitter_constant", "amvpt_scene_add_emitter_envmap", "amvpt_scene_get_emitter", "amvpt_scene_get_sensor_params", "amvpt_scene_get_envmap", "amvpt_scene_get_shutter_draw", "amvpt_scene_set_shutter", "amvpt_env_warp", "amvpt_image_read", "amvpt_spectrum_to_srgb", "amvpt_scene_set_integrator", "amvpt_scene_set_rfilter", "amvpt_scene_set_reuse", "amvpt_scene_set_reuse_debug", "amvpt_last_fill_paths", "amvpt_scene_commit", "amvpt_scene_info",
            "amvpt_scene_get_sensor", "amvpt_scene_get_bsdf_tables", "amvpt_scene_counts", "amvpt_scene_get_mesh",
-           "amvpt_scene_get_bsdf", "amvpt_scene_get_integrator", "amvpt_render", "amvpt_shard_tiles", "amvpt_view_tiles", "amvpt_cancel", "amvpt_film_clear",
+           "amvpt_scene_get_bsdf", "amvpt_scene_get_integrator", "amvpt_render", "amvpt_shard_tiles", "amvpt_view_tiles", "amvpt_adaptive_alloc", "amvpt_comm_unique_id", "amvpt_comm_init", "amvpt_comm_destroy", "amvpt_film_gather", "amvpt_comm_allreduce_sum", "amvpt_gather_tiles", "amvpt_film_develop_pinned", "amvpt_cancel", "amvpt_film_clear",
            "amvpt_film_raw", "amvpt_film_develop", "amvpt_film_develop_device", "amvpt_film_device_ptr", "amvpt_film_add_host",
            "amvpt_trace_lanes", "amvpt_trace_lanes_multi", "amvpt_intersect", "amvpt_bsdf_eval_pdf_sample", "amvpt_math1", "amvpt_sampler_stream",
            "amvpt_bvh_validate", "amvpt_bvh_q4_validate", "amvpt_membench", "amvpt_film_write_pfm", "amvpt_film_write_exr", "amvpt_f32_to_f16", "amvpt_film_to_srgb8", "amvpt_interlace", "amvpt_display_last_ms"]
 lib.amvpt_scene_destroy.restype = None
 lib.amvpt_scene_destroy.argtypes = [C.c_void_p]
+lib.amvpt_comm_destroy.restype = None
+lib.amvpt_comm_destroy.argtypes = [C.c_void_p]
 
 
 def _chk(rc):
@@ -309,7 +311,7 @@ class Scene:
 
     # ---- the hot path: Integrator.render(scene, sensor, seed, spp, develop, evaluate)
     def render(self, seed=0, spp=0, develop=True, scheduler="auto", stats=False, rank=0, world=1, adaptive=False,
-               adaptive_threshold=0.0, adaptive_min_spp=16, stream=None, allreduce=None, clear=True, time_stages=False):
+               adaptive_threshold=0.0, adaptive_min_spp=16, stream=None, allreduce=None, clear=True, time_stages=False, comm=None):
         """Mirrors MVPathIntegrator::render (src/integrators/mvpath.cpp:7-278): accumulates `spp` samples per pixel into the
         film and returns the developed (H, W, 3) image if `develop` (else None).  `clear=False` keeps accumulating."""
         if clear:
@@ -318,6 +320,8 @@ class Scene:
         d.seed = seed; d.spp = spp; d.scheduler = SCHEDULERS[scheduler] if isinstance(scheduler, str) else scheduler
         d.collect_stats = int(stats) | (2 if time_stages else 0); d.rank = rank; d.world = world; d.adaptive = int(adaptive)
         d.adaptive_threshold = adaptive_threshold; d.adaptive_min_spp = adaptive_min_spp; d.stream = stream
+        if comm is not None:
+            d.comm = comm._h
         if allreduce is not None:
             cb = ALLREDUCE_FN(lambda dev, n, user: allreduce(dev, n)); self._keep = [cb]; d.allreduce = cb
         st = RenderStats()
@@ -329,6 +333,12 @@ class Scene:
         """Rectangles (x0, y0, w, h, view) of the quilt that `rank` of `world` renders."""
         buf = np.zeros((4096, 5), np.uint32)
         n = _chk(lib.amvpt_shard_tiles(self._h, C.c_uint32(rank), C.c_uint32(world), _p(buf, u32p), C.c_uint32(len(buf))))
+        return buf[:n].copy()
+
+    def gather_tiles(self, rank, world):
+        """Rectangles (x0, y0, w, h, staging offset) amvpt_film_gather moves for `rank`: its view tiles grown by one pixel."""
+        buf = np.zeros((4096, 5), np.uint32)
+        n = _chk(lib.amvpt_gather_tiles(self._h, C.c_uint32(rank), C.c_uint32(world), _p(buf, u32p), C.c_uint32(len(buf))))
         return buf[:n].copy()
 
     def view_tiles(self):
@@ -351,6 +361,24 @@ class Scene:
     def film_device_ptr(self):
         a, b = C.c_void_p(), C.c_void_p()
         _chk(lib.amvpt_film_device_ptr(self._h, C.byref(a), C.byref(b))); return a.value, b.value
+
+    def adaptive_alloc(self):
+        """(passes, views) samples per pixel the adaptive allocator handed out in the last render."""
+        a, b = C.c_uint32(), C.c_uint32(); _chk(lib.amvpt_adaptive_alloc(self._h, None, C.c_uint32(0), C.byref(a), C.byref(b)))
+        out = np.zeros((a.value, b.value), np.uint32)
+        if out.size:
+            _chk(lib.amvpt_adaptive_alloc(self._h, _p(out, u32p), C.c_uint32(out.size), C.byref(a), C.byref(b)))
+        return out
+
+    def film_gather(self, comm, root=0, stream=None):
+        """Rank-owned view tiles -> the root's film over NCCL (amvpt_film_gather); asynchronous on `stream`."""
+        _chk(lib.amvpt_film_gather(self._h, comm._h, C.c_uint32(root), stream))
+
+    def develop_pinned(self):
+        """HDRFilm::develop into the library's page-locked host buffer (reused from call to call): (H, W, 3) view, valid until the next call."""
+        p = C.POINTER(C.c_float)(); i = self.info()
+        _chk(lib.amvpt_film_develop_pinned(self._h, C.byref(p)))
+        return np.ctypeslib.as_array(p, shape=(i["film_h"], i["film_w"], 3))
 
     def film_add(self, rgbw):
         _chk(lib.amvpt_film_add_host(self._h, _p(_f32(rgbw))))
@@ -458,6 +486,24 @@ def spectrum_to_srgb(wavelengths, values, within_emitter=False, unbounded_name=F
     dp = C.POINTER(C.c_double)
     _chk(lib.amvpt_spectrum_to_srgb(wl.ctypes.data_as(dp), v.ctypes.data_as(dp), C.c_uint32(len(v)), C.c_int(int(within_emitter)), C.c_int(int(unbounded_name)), out.ctypes.data_as(dp)))
     return out
+
+
+class Comm:
+    """One NCCL communicator behind the C ABI (amvpt_comm).  `unique_id()` on one rank, hand the 128 bytes to the others, then Comm(id, rank, world, device)."""
+
+    @staticmethod
+    def unique_id():
+        buf = (C.c_uint8 * 128)(); _chk(lib.amvpt_comm_unique_id(buf)); return bytes(buf)
+
+    def __init__(self, unique_id, rank, world, device):
+        self._h = C.c_void_p(); buf = (C.c_uint8 * 128)(*unique_id)
+        _chk(lib.amvpt_comm_init(buf, C.c_uint32(rank), C.c_uint32(world), C.c_int(device), C.byref(self._h)))
+        self.rank, self.world = rank, world
+
+    def __del__(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h and lib is not None:
+            lib.amvpt_comm_destroy(h)
 
 
 def device_count():

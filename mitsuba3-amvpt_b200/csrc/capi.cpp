@@ -52,6 +52,8 @@ static std::vector<std::pair<std::string, std::string>> parse_defines(const char
     return out;
 }
 
+extern "C" int amvpt_guard_call(const std::function<int()> &fn) { return guard(fn); }      // comm.cpp shares the exception -> error code mapping
+
 extern "C" {
 
 const char *amvpt_last_error(void) { return g_err.c_str(); }
@@ -175,6 +177,12 @@ int amvpt_scene_set_reuse(amvpt_scene *h, int sa_reuse, int sa_mis, int fast_mis
 int amvpt_scene_set_reuse_debug(amvpt_scene *h, int debug) {
     return guard([&] { NEED(h); h->s->integrator.debug = debug != 0; if (h->s->committed) h->s->d.reuse_debug = debug != 0; return AMVPT_OK; });
 }
+int amvpt_adaptive_alloc(amvpt_scene *h, uint32_t *out, uint32_t cap, uint32_t *n_passes, uint32_t *n_views) {
+    return guard([&] { NEED(h); Scene &s = *h->s; const uint32_t nv = s.grid_x * s.grid_y, np = nv ? (uint32_t) (s.alloc_log.size() / nv) : 0;
+        if (n_passes) *n_passes = np; if (n_views) *n_views = nv;
+        if (out) { if (cap < s.alloc_log.size()) AM_THROW("amvpt_adaptive_alloc: buffer too small (%zu entries)", s.alloc_log.size()); std::memcpy(out, s.alloc_log.data(), s.alloc_log.size() * 4); }
+        return AMVPT_OK; });
+}
 int amvpt_last_fill_paths(amvpt_scene *h, uint64_t *n) { return guard([&] { NEED(h); NEED(n); *n = h->s->last_fill_paths; return AMVPT_OK; }); }
 int amvpt_scene_set_rfilter(amvpt_scene *h, int type, float param, float param2) {
     return guard([&] { NEED(h); h->s->set_rfilter(type, param, param2); return AMVPT_OK; });
@@ -237,7 +245,7 @@ int amvpt_render(amvpt_scene *h, const amvpt_render_desc *d, amvpt_render_stats 
         RenderOptions o; o.seed = d->seed; o.spp = d->spp; o.scheduler = d->scheduler; o.stats = (d->collect_stats & 1) != 0; o.time_stages = (d->collect_stats & 2) != 0;
         o.shard.rank = d->rank; o.shard.world = d->world ? d->world : 1; o.stream = (cudaStream_t) d->stream;
         o.adaptive = d->adaptive != 0; o.adaptive_threshold = d->adaptive_threshold; o.adaptive_min_spp = d->adaptive_min_spp ? d->adaptive_min_spp : 16;
-        o.allreduce = d->allreduce; o.allreduce_user = d->allreduce_user;
+        o.allreduce = d->allreduce; o.allreduce_user = d->allreduce_user; o.comm = d->comm;
         render(s, o);
         if (out) { const RenderStats &r = s.last; out->seconds = r.seconds; out->paths = r.paths; out->closest_rays = r.closest_rays; out->shadow_rays = r.shadow_rays;
             out->bvh_nodes = r.nodes; out->tri_tests = r.tris; out->path_vertices = r.vertices; out->passes = r.passes; out->launches = r.launches; out->spp_done = r.spp_done; out->scheduler_used = r.scheduler_used;
@@ -271,6 +279,15 @@ int amvpt_film_develop(amvpt_scene *h, float *rgb) {
         if (!s.rgb) s.rgb = (float *) s.dalloc(npix * 3 * sizeof(float));
         launch_develop(s.film, s.rgb, npix, nullptr); AM_CUDA(cudaGetLastError());
         AM_CUDA(cudaMemcpy(rgb, s.rgb, npix * 3 * sizeof(float), cudaMemcpyDeviceToHost)); return AMVPT_OK; });
+}
+int amvpt_film_develop_pinned(amvpt_scene *h, float **rgb_host) {
+    return guard([&] { NEED(rgb_host); Scene &s = committed(h); const size_t npix = (size_t) s.film_w * s.film_h, bytes = npix * 3 * sizeof(float);
+        static float *pinned = nullptr; static size_t pinned_bytes = 0;        // process-wide: page-locking 200 MB costs tens of milliseconds, so it happens once
+        if (pinned_bytes < bytes) { if (pinned) cudaFreeHost(pinned); pinned = nullptr; pinned_bytes = 0; AM_CUDA(cudaHostAlloc((void **) &pinned, bytes, cudaHostAllocDefault)); pinned_bytes = bytes; }
+        if (!s.rgb) s.rgb = (float *) s.dalloc(bytes);
+        launch_develop(s.film, s.rgb, npix, nullptr); AM_CUDA(cudaGetLastError());
+        AM_CUDA(cudaMemcpyAsync(pinned, s.rgb, bytes, cudaMemcpyDeviceToHost, nullptr)); AM_CUDA(cudaStreamSynchronize(nullptr));
+        *rgb_host = pinned; return AMVPT_OK; });
 }
 int amvpt_film_device_ptr(amvpt_scene *h, void **rgbw, void **moments) {
     return guard([&] { Scene &s = committed(h); if (rgbw) *rgbw = s.film; if (moments) *moments = s.moments; return AMVPT_OK; });

@@ -103,6 +103,7 @@ struct Scene {
     float4 *split_buf = nullptr; uint32_t split_cap = 0;   // "split" scheduler: first-vertex records of one chunk
     uint8_t *adapt_mask = nullptr; uint32_t *adapt_scratch = nullptr, *adapt_compact = nullptr; unsigned long long adapt_cap = 0; size_t adapt_compact_cap = 0;   // reuse `adaptive` fill-in
     unsigned long long last_fill_paths = 0;
+    std::vector<uint32_t> alloc_log;      // adaptive allocator: samples per pixel given to view v in pass p of the last render, [pass][view]
     float4 *reuse_buf = nullptr; uint32_t reuse_cap = 0;   // staged sample-reuse schedule: per-chunk hit + projection records
     WfPool wf{}; uint32_t wf_type_mask = 0;     // wavefront scheduler pool (allocated on first use)
     uint32_t n_nodes = 0, n_tris = 0;
@@ -152,8 +153,12 @@ struct RenderOptions {
     bool adaptive = false; float adaptive_threshold = 0.f; uint32_t adaptive_min_spp = 16;
     // optional collective hook: sums `n` floats across ranks in place (NCCL all-reduce in the multi-GPU driver)
     void (*allreduce)(float *dev, uint32_t n, void *user) = nullptr; void *allreduce_user = nullptr;
+    void *comm = nullptr;            // amvpt_comm: the statistics all-reduce goes through NCCL on the render stream (takes precedence over the hook)
 };
 void render(Scene &s, const RenderOptions &opt);
+// comm.cpp: NCCL behind the C ABI
+void comm_allreduce_sum(void *comm, float *dev, uint32_t n, cudaStream_t st);
+void film_gather(Scene &s, void *comm, uint32_t root, cudaStream_t st);
 std::vector<TileDesc> rank_tiles(const Scene &s, const Shard &sh, bool per_view);
 
 // xml.cpp

@@ -262,7 +262,7 @@ void launch_develop(const float4 *film, float *rgb, size_t npix, cudaStream_t st
 }
 
 // Adaptive allocator statistics (build-defined; the reference has no variance estimator).
-// Per tile: [0] sum over pixels of the variance of the pixel mean (relative, luminance), [1] number of pixels with
+// Per view (tile.pad): [0] sum over pixels of the variance of the pixel mean (relative, luminance), [1] number of pixels with
 // weight > 1, [2] sum of weights (samples traced so far), [3] sum of luminance.
 __global__ void view_stats_kernel(const float4 *__restrict__ film, const float2 *__restrict__ moments, uint32_t film_w,
                                   const TileDesc *__restrict__ tiles, float *__restrict__ stats) {
@@ -285,15 +285,14 @@ __global__ void view_stats_kernel(const float4 *__restrict__ film, const float2 
         a2 += __shfl_down_sync(0xffffffffu, a2, o); a3 += __shfl_down_sync(0xffffffffu, a3, o);
     }
     if ((threadIdx.x & 31) == 0) {
-        float *o = stats + 4 * blockIdx.y;
+        float *o = stats + 4 * t.pad;          // pad = view index: bands of one view share a slot
         atomicAdd(o, a0); atomicAdd(o + 1, a1); atomicAdd(o + 2, a2); atomicAdd(o + 3, a3);
     }
 }
 void launch_view_stats(const float4 *film, const float2 *moments, uint32_t film_w, const TileDesc *tiles, uint32_t n_tiles,
                        float *stats, cudaStream_t st) {
     if (!n_tiles) return;
-    cudaMemsetAsync(stats, 0, sizeof(float) * 4 * n_tiles, st);
-    dim3 grid(64, n_tiles);
+    dim3 grid(64, n_tiles);      // the caller clears stats (4 floats per view)
     view_stats_kernel<<<grid, 256, 0, st>>>(film, moments, film_w, tiles, stats);
 }
 
@@ -400,6 +399,20 @@ __global__ void sampler_tap_kernel(uint32_t seed_value, uint32_t lane, uint32_t 
 }
 void launch_sampler_tap(uint32_t seed_value, uint32_t lane, uint32_t n, float *out, cudaStream_t st) {
     sampler_tap_kernel<<<1, 32, 0, st>>>(seed_value, lane, n, out);
+}
+// Film hand-off between ranks (comm.cpp): one thread per staged pixel finds its tile by bisection over the pixel offsets
+template <bool UNPACK> __global__ void __launch_bounds__(256) film_pack_kernel(float4 *__restrict__ film, uint32_t film_w, const TileDesc *__restrict__ tiles, uint32_t n_tiles, float4 *__restrict__ stage, size_t n_px) {
+    const size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; if (i >= n_px) return;
+    uint32_t lo = 0, hi = n_tiles - 1;
+    while (lo < hi) { const uint32_t mid = (lo + hi + 1) >> 1; if (tiles[mid].lane_begin <= i) lo = mid; else hi = mid - 1; }
+    const TileDesc t = tiles[lo]; const size_t r = i - t.lane_begin; const uint32_t ty = (uint32_t) (r / t.w), tx = (uint32_t) (r - (size_t) ty * t.w);
+    float4 *px = film + (size_t) (t.y0 + ty) * film_w + (t.x0 + tx);
+    if (UNPACK) { const float4 v = stage[i]; if (v.x != 0.f || v.y != 0.f || v.z != 0.f || v.w != 0.f) { float4 f = *px; f.x += v.x; f.y += v.y; f.z += v.z; f.w += v.w; *px = f; } }
+    else stage[i] = *px;
+}
+void launch_film_pack(float4 *film, uint32_t film_w, const TileDesc *tiles, uint32_t n_tiles, float4 *stage, size_t n_px, bool unpack_add, cudaStream_t st) {
+    if (!n_px || !n_tiles) return; const unsigned grid = (unsigned) ((n_px + 255) / 256);
+    if (unpack_add) film_pack_kernel<true><<<grid, 256, 0, st>>>(film, film_w, tiles, n_tiles, stage, n_px); else film_pack_kernel<false><<<grid, 256, 0, st>>>(film, film_w, tiles, n_tiles, stage, n_px);
 }
 __global__ void l2_flush_kernel(float *buf, size_t n) {
     size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x, stride = (size_t) gridDim.x * blockDim.x;

@@ -87,6 +87,8 @@ void launch_math_tap(int op, const float *in, uint32_t n, float *out, cudaStream
 void launch_env_warp_tap(const DScene &s, const float *u, uint32_t n, float *out /* n * 4: uv, pdf, eval(uv) */, cudaStream_t st);
 void launch_sampler_tap(uint32_t seed_value, uint32_t lane, uint32_t n, float *out, cudaStream_t st);
 void launch_l2_flush(float *buf, size_t n, cudaStream_t st);
+// film gather: tiles (lane_begin = pixel offset of the tile in `stage`) -> contiguous staging buffer, or staging buffer added into the film
+void launch_film_pack(float4 *film, uint32_t film_w, const TileDesc *tiles, uint32_t n_tiles, float4 *stage, size_t n_px, bool unpack_add, cudaStream_t st);
 double run_membench_read(size_t bytes, uint32_t iters, int sm_count, cudaStream_t st);   // GB/s of 16-byte loads over `bytes`, or < 0 on failure
 
 } // namespace amvpt

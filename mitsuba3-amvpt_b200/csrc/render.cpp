@@ -50,7 +50,7 @@ void render(Scene &s, const RenderOptions &opt) {
     if (opt.shard.world == 0 || opt.shard.rank >= opt.shard.world) AM_THROW("render: invalid shard %u/%u", opt.shard.rank, opt.shard.world);
     AM_CUDA(cudaSetDevice(s.device));
     cudaStream_t st = opt.stream;
-    s.stop = false; s.last_fill_paths = 0;
+    s.stop = false; s.last_fill_paths = 0; s.alloc_log.clear();
     // mvpath.cpp:33-41
     uint32_t spp = opt.spp ? opt.spp : s.sample_count;
     if (!spp) AM_THROW("render: sample count is zero");
@@ -67,6 +67,7 @@ void render(Scene &s, const RenderOptions &opt) {
         n_passes = spp / spp_per_pass;
     }
     bool adaptive = opt.adaptive;
+    if (adaptive && opt.shard.world > 1 && !opt.allreduce && !opt.comm) AM_THROW("render: the adaptive allocator on %u ranks needs the statistics summed over ranks: pass an amvpt_comm or an allreduce hook", opt.shard.world);
     if (adaptive && s.rfilter_type != 0) AM_THROW("render: the adaptive allocator keeps per-pixel moments and needs the box reconstruction filter");
     std::vector<TileDesc> base = rank_tiles(s, opt.shard, adaptive);
     if (base.size() > s.tiles_cap) {
@@ -74,7 +75,8 @@ void render(Scene &s, const RenderOptions &opt) {
     }
     uint32_t n_views = s.grid_x * s.grid_y;
     RenderStats rs;
-    cudaEvent_t e0, e1; AM_CUDA(cudaEventCreate(&e0)); AM_CUDA(cudaEventCreate(&e1));
+    struct Events { cudaEvent_t a = nullptr, b = nullptr; ~Events() { if (a) cudaEventDestroy(a); if (b) cudaEventDestroy(b); } } ev;      // released on every exit path
+    AM_CUDA(cudaEventCreate(&ev.a)); AM_CUDA(cudaEventCreate(&ev.b)); cudaEvent_t e0 = ev.a, e1 = ev.b;
     AM_CUDA(cudaMemsetAsync(s.counters, 0, sizeof(unsigned long long) * CTR_COUNT, st));
 
     RenderParams p{};
@@ -176,7 +178,7 @@ void render(Scene &s, const RenderOptions &opt) {
         unsigned long long view_px = (unsigned long long) s.res_x * s.res_y, budget = (unsigned long long) spp * view_px * n_views, used = 0;
         uint32_t warm = std::max(1u, (std::min(opt.adaptive_min_spp, spp) + spp_per_pass - 1) / spp_per_pass);
         std::vector<float> hstats(4 * (size_t) n_views), err(n_views, 1.f);
-        if (4 * n_views > 4 * s.tiles_cap) s.view_stats_dev = (float *) s.dalloc(sizeof(float) * 4 * n_views);
+        if (n_views > s.tiles_cap) s.view_stats_dev = (float *) s.dalloc(sizeof(float) * 4 * n_views);
         Shard all; std::vector<TileDesc> all_views = s.view_tiles(all);
         std::vector<uint32_t> alloc(n_views, spp_per_pass);
         // the reference's lane map allows spp / spp_per_pass passes of distinct seeds; adaptive passes keep going with
@@ -184,21 +186,16 @@ void render(Scene &s, const RenderOptions &opt) {
         uint32_t max_passes = 4 * n_passes + 16;
         for (uint32_t pass = 0; pass < max_passes && used < budget && !s.stop; ++pass) {
             if (pass >= warm) {
-                // statistics of the views this rank owns, summed over ranks
+                // statistics of the views this rank owns: ONE launch over the owned tile list (bands of a view accumulate into the view's
+                // slot on the device), summed over ranks in place (NCCL on the render stream, or the caller's hook), one read-back per pass
                 std::vector<TileDesc> mine = base; for (auto &t : mine) t.spp = 1;
                 AM_CUDA(cudaMemsetAsync(s.view_stats_dev, 0, sizeof(float) * 4 * n_views, st));
-                std::vector<TileDesc> per_view(n_views);
-                for (auto &t : all_views) { per_view[t.pad] = t; per_view[t.pad].w = 0; per_view[t.pad].h = 0; }
-                // bands of the same view accumulate into the view's slot (launch once per owned tile list)
-                for (auto &t : mine) {
-                    TileDesc one = t; AM_CUDA(cudaMemcpyAsync(s.tiles_dev, &one, sizeof(TileDesc), cudaMemcpyHostToDevice, st));
-                    launch_view_stats(s.film, s.moments, s.film_w, s.tiles_dev, 1, s.view_stats_dev + 4 * (size_t) n_views, st);
-                    AM_CUDA(cudaStreamSynchronize(st));
-                    float tmp[4]; AM_CUDA(cudaMemcpy(tmp, s.view_stats_dev + 4 * (size_t) n_views, sizeof(tmp), cudaMemcpyDeviceToHost));
-                    for (int k = 0; k < 4; ++k) hstats[4 * (size_t) t.pad + k] += tmp[k];
+                if (!mine.empty()) {
+                    AM_CUDA(cudaMemcpyAsync(s.tiles_dev, mine.data(), sizeof(TileDesc) * mine.size(), cudaMemcpyHostToDevice, st));
+                    launch_view_stats(s.film, s.moments, s.film_w, s.tiles_dev, (uint32_t) mine.size(), s.view_stats_dev, st);
                 }
-                AM_CUDA(cudaMemcpyAsync(s.view_stats_dev, hstats.data(), sizeof(float) * 4 * n_views, cudaMemcpyHostToDevice, st));
-                if (opt.allreduce) opt.allreduce(s.view_stats_dev, 4 * n_views, opt.allreduce_user);
+                if (opt.comm) comm_allreduce_sum(opt.comm, s.view_stats_dev, 4 * n_views, st);
+                else if (opt.allreduce) { AM_CUDA(cudaStreamSynchronize(st)); opt.allreduce(s.view_stats_dev, 4 * n_views, opt.allreduce_user); }      // the hook completes before it returns
                 AM_CUDA(cudaMemcpyAsync(hstats.data(), s.view_stats_dev, sizeof(float) * 4 * n_views, cudaMemcpyDeviceToHost, st));
                 AM_CUDA(cudaStreamSynchronize(st));
                 double total = 0.0; bool any = false;
@@ -207,7 +204,6 @@ void render(Scene &s, const RenderOptions &opt) {
                     if (opt.adaptive_threshold > 0.f && e <= opt.adaptive_threshold) e = 0.f;
                     err[v] = e; total += e; any |= e > 0.f;
                 }
-                std::fill(hstats.begin(), hstats.end(), 0.f);
                 if (!any) break;
                 unsigned long long remaining = budget - used;
                 double pass_budget = std::min<double>((double) remaining / (double) view_px, (double) spp_per_pass * n_views);
@@ -228,6 +224,7 @@ void render(Scene &s, const RenderOptions &opt) {
                 }
             }
             for (uint32_t v = 0; v < n_views; ++v) used += (unsigned long long) alloc[v] * view_px;
+            s.alloc_log.insert(s.alloc_log.end(), alloc.begin(), alloc.end());
             std::vector<TileDesc> tiles = base; for (auto &t : tiles) t.spp = alloc[t.pad];
             launch(tiles, pass); rs.passes++;
         }
@@ -236,7 +233,6 @@ void render(Scene &s, const RenderOptions &opt) {
     AM_CUDA(cudaEventRecord(e1, st));
     AM_CUDA(cudaEventSynchronize(e1));
     float ms = 0.f; AM_CUDA(cudaEventElapsedTime(&ms, e0, e1)); rs.seconds = ms * 1e-3;
-    cudaEventDestroy(e0); cudaEventDestroy(e1);
     unsigned long long c[CTR_COUNT]; AM_CUDA(cudaMemcpy(c, s.counters, sizeof(c), cudaMemcpyDeviceToHost));
     rs.closest_rays = c[CTR_CLOSEST]; rs.shadow_rays = c[CTR_SHADOW]; rs.nodes = c[CTR_NODES]; rs.tris = c[CTR_TRIS]; rs.vertices = c[CTR_VERTICES];
     s.last = rs;

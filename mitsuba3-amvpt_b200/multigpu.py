@@ -1,41 +1,26 @@
-"""Multi-GPU plumbing (torch.distributed over NCCL on the GPU box, gloo in the CPU tests).  The render path itself has
-no data-path collective: views are sharded, the scene is replicated, lane indices stay global.  The two
-collectives are (1) the final film hand-off to rank 0 and (2) the all-reduce of per-view statistics in adaptive mode."""
+"""Multi-GPU bootstrap.  The path's two exchanges -- the film gather and the adaptive statistics all-reduce -- live behind the C ABI
+(csrc/comm.cpp: amvpt_comm_*, amvpt_film_gather; NCCL bound at run time).  What remains here is the rendezvous: rank 0 creates the NCCL
+unique id and torch.distributed (NCCL on the GPU box, gloo in the CPU tests) hands its 128 bytes to the other ranks.  DevicePtr wraps a
+raw device pointer of the C ABI for tests that emulate the all-reduce on one GPU."""
 import torch
 import torch.distributed as dist
 
 
 class DevicePtr:
-    """Wraps a raw device pointer of the C ABI (amvpt_film_device_ptr) for torch.as_tensor without a copy."""
+    """Wraps a raw device pointer of the C ABI (amvpt_film_device_ptr, the allreduce hook's argument) for torch.as_tensor without a copy."""
 
     def __init__(self, ptr, n_floats):
         self.__cuda_array_interface__ = {"shape": (n_floats,), "typestr": "<f4", "data": (ptr, False), "version": 2}
 
 
-def film_tensor(scene, device):
-    info = scene.info(); ptr, _ = scene.film_device_ptr()
-    return torch.as_tensor(DevicePtr(ptr, info["film_w"] * info["film_h"] * 4), device=device)
+def exchange_unique_id(make_id, rank):
+    """Rank 0 calls make_id() -> 128 bytes; every rank returns them (broadcast over the initialised process group)."""
+    box = [make_id() if rank == 0 else None]
+    dist.broadcast_object_list(box, src=0)
+    return box[0]
 
 
-def reduce_film(film, dst=0):
-    """Ranks own disjoint pixels (box filter; a jittered sample that rounds into a neighbour's pixel is the only overlap),
-    so a sum-reduce to `dst` equals the gather of the owned tiles, including those strays."""
-    if dist.is_initialized() and dist.get_world_size() > 1:
-        dist.reduce(film, dst=dst, op=dist.ReduceOp.SUM)
-    return film
-
-
-def allreduce_stats(stats):
-    if dist.is_initialized() and dist.get_world_size() > 1:
-        dist.all_reduce(stats, op=dist.ReduceOp.SUM)
-    return stats
-
-
-def make_allreduce_hook(device):
-    """Callback for Scene.render(allreduce=...): sums `n` floats at a raw device pointer across ranks."""
-    def hook(dev_ptr, n):
-        t = torch.as_tensor(DevicePtr(dev_ptr, n), device=device)
-        torch.cuda.current_stream().synchronize()
-        allreduce_stats(t)
-        torch.cuda.current_stream().synchronize()
-    return hook
+def bootstrap_comm(pkg, rank, world, device):
+    """An amvpt Comm (ncclCommInitRank behind the C ABI) for this process; torch.distributed must be initialised."""
+    uid = exchange_unique_id(pkg.Comm.unique_id, rank)
+    return pkg.Comm(uid, rank, world, device)

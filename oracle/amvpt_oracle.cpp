@@ -1030,6 +1030,31 @@ double orc_render_rows(void *sp, uint32_t seed, uint32_t spp, uint32_t spp_pass_
     if (stats) { stats[0] = stats[1] = 0; for (auto &t : tstats) { stats[0] += t.nodes; stats[1] += t.tris; } }
     return sec;
 }
+// The film of an adaptive render whose allocation is given: pass p traces, for every pixel of view v, the lanes k < alloc[p][v] of the pass's
+// lane map (lane = pixel * spp_per_pass + k, seed_value = base_seed + spp_per_pass * p + seed) -- exactly the samples the product claims it traced.
+void orc_render_alloc(void *sp, uint32_t seed, uint32_t spp_per_pass, uint32_t n_passes, const uint32_t *alloc, int brute, int nthreads, float *film) {
+    Scene &s = *(Scene *) sp; const uint32_t n_views = s.grid_x * s.grid_y, rx = s.film_w / s.grid_x, ry = s.film_h / s.grid_y;
+    std::atomic<uint32_t> next_row{ 0 };
+    auto worker = [&](int) {
+        for (;;) {
+            const uint32_t y = next_row.fetch_add(1); if (y >= s.film_h) break;
+            for (uint32_t pass = 0; pass < n_passes; ++pass) {
+                const uint32_t seed_value = s.base_seed + (spp_per_pass * pass + seed);
+                for (uint32_t x = 0; x < s.film_w; ++x) {
+                    uint32_t ix = x / rx, iy = y / ry; if (s.reverse_x) ix = s.grid_x - 1 - ix; if (s.reverse_y) iy = s.grid_y - 1 - iy;
+                    const uint32_t view = ix + s.grid_x * iy, nk = alloc[(size_t) pass * n_views + view];
+                    for (uint32_t k = 0; k < nk; ++k) {
+                        LaneOut o = render_lane(s, seed_value, (y * s.film_w + x) * spp_per_pass + k, spp_per_pass, brute != 0, nullptr, nullptr);
+                        if (!o.in_film) continue;
+                        float *px = film + 4 * (size_t) o.pixel;       // strays into another row are rare; rows are owned by one thread at a time except for them
+                        px[0] += o.r.L.x; px[1] += o.r.L.y; px[2] += o.r.L.z; px[3] += 1.f;
+                    }
+                }
+            }
+        }
+    };
+    if (nthreads <= 1) worker(0); else { std::vector<std::thread> th; for (int i = 0; i < nthreads; ++i) th.emplace_back(worker, i); for (auto &t : th) t.join(); }
+}
 // Per-lane tap of the reuse branch: for lanes [lane_begin, lane_begin + n) the n_reuse SampleData records after
 // render_multisample's tile offset: out[lane][k] = { pos.x, pos.y, weight, result.rgb, valid, indirect, idx } (9 floats)
 void orc_trace_lanes_multi(void *sp, uint32_t seed_value, uint32_t spp_per_pass, uint32_t lane_begin, uint32_t n, int brute, float *out) {

@@ -228,6 +228,12 @@ class OracleScene:
                                         _p(r["bs_pdf"]), _p(r["bs_eta"]), _p(r["bs_type"], u32p), _p(r["weight"]))
         return r
 
+    def render_alloc(self, alloc, seed=0, spp_per_pass=16, brute=False, nthreads=1):
+        """Film of the samples an adaptive render claims: alloc[pass][view] samples per pixel (single thread by default: exact row ownership)."""
+        alloc = np.ascontiguousarray(alloc, np.uint32); w, h = self.film_size(); film = np.zeros((h, w, 4), np.float32)
+        self.o.orc_render_alloc(self.h, C.c_uint32(seed), C.c_uint32(spp_per_pass), C.c_uint32(alloc.shape[0]), _p(alloc, u32p), C.c_int(int(brute)), C.c_int(nthreads), _p(film))
+        return film
+
     def render(self, seed=0, spp=16, brute=False, nthreads=None, rows=None, row_stride=1):
         """Returns (RGBW film [H, W, 4], seconds in the pass loop, (nodes, tris))."""
         w, h = self.film_size(); film = np.zeros((h, w, 4), np.float32); stats = np.zeros(2, np.uint64)

@@ -120,22 +120,29 @@ pkg = importlib.import_module('mitsuba3-amvpt_b200'); scenes = importlib.import_
 mg = importlib.import_module('mitsuba3-amvpt_b200.multigpu')
 dist.init_process_group('gloo', rank=int(os.environ['RANK']), world_size=int(os.environ['WORLD_SIZE']))
 rank, world = dist.get_rank(), dist.get_world_size()
+# (1) the rendezvous of the NCCL unique id: rank 0 makes it, everybody ends up with the same 128 bytes
+uid = mg.exchange_unique_id(lambda: bytes(range(128)), rank)
+assert uid == bytes(range(128))
+# (2) the film hand-off with the library's own rectangles (amvpt_gather_tiles: owned view tiles grown by one pixel), moved here with
+# send / recv the way comm.cpp moves them with ncclSend / ncclRecv: pack -> send -> add into the root's film
 s = scenes.build(scenes.cornell_box(grid_x=4, grid_y=2, view_res=8), commit=False)
 H, W = 16, 32
-# every rank fills its own tiles with (rank + 1) and leaves the rest at zero, as the sharded render does
 film = torch.zeros(H, W, 4)
 for x0, y0, w, h, view in s.shard_tiles(rank, world):
     film[y0:y0 + h, x0:x0 + w] = float(view + 1)
-mg.reduce_film(film, dst=0)
-stats = torch.zeros(8 * 4); stats[4 * rank:4 * rank + 4] = rank + 1.0     # per-view statistics, summed so that every rank derives the same allocation
-mg.allreduce_stats(stats)
-assert torch.equal(stats[:8], torch.tensor([1., 1., 1., 1., 2., 2., 2., 2.]))
-if rank == 0:
-    want = torch.zeros(H, W)
-    for r in range(world):
-        for x0, y0, w, h, view in s.shard_tiles(r, world):
-            want[y0:y0 + h, x0:x0 + w] = float(view + 1)
-    assert torch.equal(film[..., 0], want) and (want > 0).all()
+    if x0 + w < W: film[y0, x0 + w, 3] += 0.25           # a jittered sample that rounded into the neighbouring view's pixel
+full = film.clone(); dist.all_reduce(full)                # what a whole-quilt sum would give
+def pack(f, tiles): return torch.cat([f[y0:y0 + h, x0:x0 + w].reshape(-1, 4) for x0, y0, w, h, off in tiles])
+if rank != 0:
+    t = s.gather_tiles(rank, world); buf = pack(film, t); assert int(t[-1][4] + t[-1][2] * t[-1][3]) == len(buf)
+    dist.send(buf.contiguous(), dst=0)
+else:
+    for r in range(1, world):
+        t = s.gather_tiles(r, world); n = int(t[-1][4] + t[-1][2] * t[-1][3]); buf = torch.zeros(n, 4); dist.recv(buf, src=r)
+        for x0, y0, w, h, off in t:
+            film[y0:y0 + h, x0:x0 + w] += buf[int(off):int(off) + int(w) * int(h)].reshape(int(h), int(w), 4)
+    assert torch.equal(film, full), 'tile gather must equal the whole-quilt sum, strays included'
+    sent = sum(int(t[2] * t[3]) for r in range(1, world) for t in s.gather_tiles(r, world)); assert sent < H * W
 dist.destroy_process_group()
 sys.stdout.write('ok %d\n' % rank); sys.stdout.flush()
 """

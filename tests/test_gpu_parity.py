@@ -445,6 +445,48 @@ def test_adaptive_allocation(scenes, gpu):
     assert s.film_raw()[..., 3].mean() <= 17
 
 
+def test_adaptive_film_is_the_claimed_samples_and_identical_on_any_world_size(scenes, ob, gpu):
+    """(1) The adaptive film equals the CPU oracle's film of exactly the samples the allocator says it handed out (weights exact, radiance within
+    the summation-order tolerance).  (2) 2 / 4 / 8 ranks -- run in lockstep on this one GPU, their statistics summed by a host-side hook at the
+    point where NCCL sums them on a multi-GPU box -- derive the same allocation pass by pass and their films add up to the one-rank film."""
+    import threading
+    import torch
+    mg = __import__("importlib").import_module("mitsuba3-amvpt_b200.multigpu")
+    desc = scenes.cornell_box(grid_x=4, grid_y=2, view_res=16, sample_count=64, cam_dist=900.0)
+    s = scenes.build(desc, device=gpu); o = ob.OracleScene(desc)
+    s.render(seed=1, spp=64, adaptive=True, adaptive_min_spp=16, develop=False); film = s.film_raw().copy(); alloc = s.adaptive_alloc()
+    assert alloc.shape[1] == 8 and alloc.shape[0] >= 4 and len({tuple(r) for r in alloc}) > 1, "allocation never differentiated the views"
+    assert alloc.sum() * 16 * 16 == film[..., 3].sum()
+    ofilm = o.render_alloc(alloc, seed=1, spp_per_pass=16, brute=True, nthreads=4)
+    assert np.array_equal(film[..., 3], ofilm[..., 3])
+    assert np.abs(film[..., :3] - ofilm[..., :3]).max() <= FILM_RTOL * ofilm[..., :3].max()
+    with pytest.raises(Exception, match="summed over ranks"):
+        s.render(seed=1, spp=64, adaptive=True, rank=0, world=2, develop=False)
+    for world in (2, 4, 8):
+        ranks = [scenes.build(desc, device=gpu) for _ in range(world)]
+        barrier = threading.Barrier(world); shared = [None] * world; errors = []
+
+        def run(r):
+            def hook(dev_ptr, n):               # what ncclAllReduce(sum) does between the ranks of a multi-GPU run
+                t = torch.as_tensor(mg.DevicePtr(dev_ptr, n), device=f"cuda:{gpu}"); torch.cuda.synchronize()
+                shared[r] = t.cpu().numpy().copy(); barrier.wait()
+                total = np.sum(np.stack(shared), axis=0, dtype=np.float32); barrier.wait()
+                t.copy_(torch.from_numpy(total)); torch.cuda.synchronize()
+            try:
+                ranks[r].render(seed=1, spp=64, adaptive=True, adaptive_min_spp=16, develop=False, rank=r, world=world, allreduce=hook)
+            except Exception as e:       # a failing rank must not leave the others waiting at the barrier
+                errors.append(e); barrier.abort()
+        th = [threading.Thread(target=run, args=(r,)) for r in range(world)]
+        [t.start() for t in th]; [t.join() for t in th]
+        assert not errors, errors
+        total = np.zeros_like(film)
+        for r in range(world):
+            assert np.array_equal(ranks[r].adaptive_alloc(), alloc), f"rank {r} of {world} derived another allocation"
+            total += ranks[r].film_raw()
+        assert np.array_equal(total[..., 3], film[..., 3])
+        assert np.abs(total[..., :3] - film[..., :3]).max() <= FILM_RTOL * film[..., :3].max()
+
+
 # ---------------------------------------------------------------------------------------------------------------------
 # Cross-view sample reuse + MIS (SURVEY.md sec.8f next-1; src/integrators/mvpath_multi.h).  Parity unpinned in the reference
 # (no tests); the checker is the CPU restatement oracle/o_reuse.h.
