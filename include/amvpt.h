@@ -51,6 +51,8 @@ typedef struct amvpt_integrator_desc {
     int64_t max_depth; uint32_t rr_depth; int32_t hide_emitters; uint32_t spp_pass_lim;
     uint32_t sampler_seed, sample_count;
 } amvpt_integrator_desc;
+/* Integrator `timeout` (seconds, <= 0 = none; src/render/integrator.cpp:22-28, should_stop() integrator.h:303-306): checked between passes */
+int amvpt_scene_set_timeout(struct amvpt_scene *s, float seconds);
 
 /* Integrator::render(scene, sensor, seed, spp, develop, evaluate) arguments (include/mitsuba/render/integrator.h:77-96)
  * plus the build-defined extensions (view sharding, scheduler choice, adaptive allocation). */
@@ -99,6 +101,12 @@ int amvpt_scene_set_sensor_grid(amvpt_scene *s, const amvpt_grid_sensor_desc *d)
 /* `batch` multi-sensor (src/sensors/batch.cpp:94-180): n explicit perspective sub-cameras, film = n*res_x by res_y */
 int amvpt_scene_set_sensor_batch(amvpt_scene *s, uint32_t n, uint32_t res_x, uint32_t res_y, const float *sample_to_camera,
                                  const float *to_world, float near_clip, float far_clip, int reverse_x);
+/* any MultiSensor as the table of its sub-cameras in sensor-index order (MultiSensor::sensors() / grid_dim() / reverse_axis(), src/sensors/grid.cpp:
+ * 435-457): grid_x * grid_y records of sample_to_camera (16 floats), to_world (16 floats) and { near_clip, far_clip, aperture_radius,
+ * focus_distance }; the film is grid_x * view_res_x by grid_y * view_res_y.  This is what a plugin shim inside the reference calls
+ * (integration/mvpath_b200.cpp) */
+int amvpt_scene_set_sensor_table(amvpt_scene *s, uint32_t grid_x, uint32_t grid_y, uint32_t view_res_x, uint32_t view_res_y, int reverse_x, int reverse_y,
+                                 int thinlens, const float *sample_to_camera, const float *to_world, const float *scalars4);
 int amvpt_scene_set_integrator(amvpt_scene *s, const amvpt_integrator_desc *d);
 /* cross-view sample reuse of the mvpath integrator (src/integrators/mvpath.h:120-129: sa_reuse, sa_mis, fast_mis, reuse_count,
  * adaptive; render_multisample / sample_multi, mvpath_multi.h:8-358).  Reuse is active when sa_reuse, more than one sub-sensor

@@ -74,7 +74,7 @@ class RenderStats(C.Structure):
 lib.amvpt_last_error.restype = C.c_char_p
 EXPORTS = ["amvpt_last_error", "amvpt_device_count", "amvpt_scene_create", "amvpt_scene_destroy", "amvpt_scene_from_xml",
            "amvpt_scene_from_xml_string", "amvpt_scene_add_bsdf", "amvpt_scene_add_mesh", "amvpt_scene_set_sensor_grid",
-           "amvpt_scene_set_sensor_batch", "amvpt_scene_add_emitter_point", "amvpt_scene_add_emitter_constant", "amvpt_scene_add_emitter_envmap", "amvpt_scene_get_emitter", "amvpt_scene_get_sensor_params", "amvpt_scene_get_envmap", "amvpt_scene_get_shutter_draw", "amvpt_scene_set_shutter", "amvpt_env_warp", "amvpt_image_read", "amvpt_spectrum_to_srgb", "amvpt_scene_set_integrator", "amvpt_scene_set_rfilter", "amvpt_scene_set_reuse", "amvpt_scene_set_reuse_debug", "amvpt_last_fill_paths", "amvpt_scene_commit", "amvpt_scene_info",
+           "amvpt_scene_set_sensor_batch", "amvpt_scene_set_sensor_table", "amvpt_scene_add_emitter_point", "amvpt_scene_add_emitter_constant", "amvpt_scene_add_emitter_envmap", "amvpt_scene_get_emitter", "amvpt_scene_get_sensor_params", "amvpt_scene_get_envmap", "amvpt_scene_get_shutter_draw", "amvpt_scene_set_shutter", "amvpt_env_warp", "amvpt_image_read", "amvpt_spectrum_to_srgb", "amvpt_scene_set_integrator", "amvpt_scene_set_rfilter", "amvpt_scene_set_reuse", "amvpt_scene_set_reuse_debug", "amvpt_scene_set_timeout", "amvpt_last_fill_paths", "amvpt_scene_commit", "amvpt_scene_info",
            "amvpt_scene_get_sensor", "amvpt_scene_get_bsdf_tables", "amvpt_scene_counts", "amvpt_scene_get_mesh",
            "amvpt_scene_get_bsdf", "amvpt_scene_get_integrator", "amvpt_render", "amvpt_shard_tiles", "amvpt_view_tiles", "amvpt_adaptive_alloc", "amvpt_comm_unique_id", "amvpt_comm_init", "amvpt_comm_destroy", "amvpt_film_gather", "amvpt_comm_allreduce_sum", "amvpt_gather_tiles", "amvpt_film_develop_pinned", "amvpt_cancel", "amvpt_film_clear",
            "amvpt_film_raw", "amvpt_film_develop", "amvpt_film_develop_device", "amvpt_film_device_ptr", "amvpt_film_add_host",
@@ -224,6 +224,10 @@ class Scene:
                                        C.c_uint32(adaptive), C.byref(n)))
         self.n_reuse = n.value
         return n.value
+
+    def set_timeout(self, seconds):
+        """Integrator `timeout`: the render stops after the pass during which this many seconds have elapsed (should_stop(), integrator.h:303-306)."""
+        _chk(lib.amvpt_scene_set_timeout(self._h, C.c_float(seconds)))
 
     def set_reuse_debug(self, debug=True):
         _chk(lib.amvpt_scene_set_reuse_debug(self._h, C.c_int(int(debug))))

@@ -160,6 +160,11 @@ int amvpt_scene_set_sensor_batch(amvpt_scene *h, uint32_t n, uint32_t res_x, uin
     return guard([&] { NEED(h); NEED(s2c); NEED(to_world);
         h->s->set_sensor_explicit(n, res_x, res_y, s2c, to_world, near_clip, far_clip, reverse_x != 0); return AMVPT_OK; });
 }
+int amvpt_scene_set_sensor_table(amvpt_scene *h, uint32_t grid_x, uint32_t grid_y, uint32_t view_res_x, uint32_t view_res_y, int reverse_x, int reverse_y, int thinlens,
+                                 const float *s2c, const float *to_world, const float *scalars4) {
+    return guard([&] { NEED(h); NEED(s2c); NEED(to_world); NEED(scalars4);
+        h->s->set_sensor_table(grid_x, grid_y, view_res_x, view_res_y, reverse_x != 0, reverse_y != 0, thinlens != 0, s2c, to_world, scalars4); return AMVPT_OK; });
+}
 int amvpt_scene_set_integrator(amvpt_scene *h, const amvpt_integrator_desc *d) {
     return guard([&] { NEED(h); NEED(d);
         IntegratorParams &ip = h->s->integrator;
@@ -174,6 +179,7 @@ int amvpt_scene_set_reuse(amvpt_scene *h, int sa_reuse, int sa_mis, int fast_mis
     return guard([&] { NEED(h); h->s->set_reuse(sa_reuse != 0, sa_mis != 0, fast_mis != 0, reuse_count, adaptive);
         if (n_samples) *n_samples = h->s->reuse_samples(); return AMVPT_OK; });
 }
+int amvpt_scene_set_timeout(amvpt_scene *h, float seconds) { return guard([&] { NEED(h); h->s->integrator.timeout = seconds; return AMVPT_OK; }); }
 int amvpt_scene_set_reuse_debug(amvpt_scene *h, int debug) {
     return guard([&] { NEED(h); h->s->integrator.debug = debug != 0; if (h->s->committed) h->s->d.reuse_debug = debug != 0; return AMVPT_OK; });
 }

@@ -126,6 +126,8 @@ struct Scene {
     void set_sensor_grid(const GridSensorParams &g);
     void set_sensor_explicit(uint32_t n, uint32_t res_x, uint32_t res_y, const float *s2c, const float *to_world,
                              float near_clip, float far_clip, bool reverse_x);
+    void set_sensor_table(uint32_t grid_x, uint32_t grid_y, uint32_t res_x, uint32_t res_y, bool reverse_x, bool reverse_y, bool thinlens,
+                          const float *s2c, const float *to_world, const float *scalars4);
     void prepare_host();
     void commit(int device);
     void film_clear(cudaStream_t st);

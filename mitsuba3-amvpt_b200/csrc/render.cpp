@@ -3,6 +3,7 @@
 // reference does not have: view sharding across ranks and the adaptive per-view allocator.
 #include "host.h"
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstdlib>
 
@@ -163,13 +164,21 @@ void render(Scene &s, const RenderOptions &opt) {
         rs.paths += lanes;
     };
 
+    // Integrator::should_stop() (include/mitsuba/render/integrator.h:303-306): cancel() or the `timeout` property (seconds of render time).  The
+    // reference tests it between work units; here between passes -- with a timeout set the host waits for each pass so that the clock means something
+    const auto t_start = std::chrono::steady_clock::now(); const float timeout = s.integrator.timeout;
+    auto should_stop = [&]() {
+        if (s.stop) return true;
+        if (timeout > 0.f) { cudaStreamSynchronize(st); if (std::chrono::duration<float>(std::chrono::steady_clock::now() - t_start).count() > timeout) return true; }
+        return false;
+    };
     AM_CUDA(cudaEventRecord(e0, st));
     if (!adaptive) {
-        for (uint32_t pass = 0; pass < n_passes && !s.stop; ++pass) {
+        for (uint32_t pass = 0; pass < n_passes && !should_stop(); ++pass) {
             std::vector<TileDesc> tiles = base; for (auto &t : tiles) t.spp = spp_per_pass;
             launch(tiles, pass); rs.passes++;
         }
-        rs.spp_done = spp;
+        rs.spp_done = rs.passes * spp_per_pass;
     } else {
         // Adaptive allocation (build-defined).  Budget: spp * (pixels of the whole quilt) samples.  Warm-up passes give
         // every view adaptive_min_spp; then each pass hands view v a sample count n_v <= spp_per_pass proportional to its
@@ -184,7 +193,7 @@ void render(Scene &s, const RenderOptions &opt) {
         // the reference's lane map allows spp / spp_per_pass passes of distinct seeds; adaptive passes keep going with
         // fresh seeds (pass index) until the budget is spent
         uint32_t max_passes = 4 * n_passes + 16;
-        for (uint32_t pass = 0; pass < max_passes && used < budget && !s.stop; ++pass) {
+        for (uint32_t pass = 0; pass < max_passes && used < budget && !should_stop(); ++pass) {
             if (pass >= warm) {
                 // statistics of the views this rank owns: ONE launch over the owned tile list (bands of a view accumulate into the view's
                 // slot on the device), summed over ranks in place (NCCL on the render stream, or the caller's hook), one read-back per pass

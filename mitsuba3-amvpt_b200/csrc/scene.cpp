@@ -211,6 +211,18 @@ void Scene::set_sensor_explicit(uint32_t n, uint32_t rx, uint32_t ry, const floa
     }
     committed = false;
 }
+// Any MultiSensor as a table of sub-cameras (MultiSensor::sensors(), grid_dim(), reverse_axis(); src/sensors/grid.cpp:435-457): what a plugin
+// shim inside the reference hands over.  scalars4[i] = near_clip, far_clip, aperture_radius, focus_distance of sub-camera i
+void Scene::set_sensor_table(uint32_t gx, uint32_t gy, uint32_t rx, uint32_t ry, bool rev_x, bool rev_y, bool thin, const float *s2c, const float *to_world, const float *scalars4) {
+    if (!gx || !gy || !rx || !ry) AM_THROW("sensor table: need at least one sub-sensor and a non-empty film");
+    grid_x = gx; grid_y = gy; reverse_x = rev_x; reverse_y = rev_y; thinlens = thin; multi_sensor = true;
+    res_x = rx; res_y = ry; film_w = rx * gx; film_h = ry * gy; sensors.clear();
+    for (uint32_t i = 0; i < gx * gy; ++i) {
+        DSensor c; memcpy(c.s2c, s2c + 16 * i, 64); memcpy(c.to_world, to_world + 16 * i, 48);
+        c.near_clip = scalars4[4 * i]; c.far_clip = scalars4[4 * i + 1]; c.aperture_radius = scalars4[4 * i + 2]; c.focus_distance = scalars4[4 * i + 3]; sensors.push_back(c);
+    }
+    committed = false;
+}
 // ReconstructionFilter plugins of the film (src/rfilters/{box,gaussian,tent,mitchell,catmullrom,lanczos}.cpp)
 void Scene::set_rfilter(int type, float param, float param2) {
     if (type < 0 || type > 5) AM_THROW("rfilter: unknown filter type %d (0 box, 1 gaussian, 2 tent, 3 mitchell, 4 catmullrom, 5 lanczos)", type);

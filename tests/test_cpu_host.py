@@ -204,3 +204,20 @@ def test_view_tiles_are_the_per_view_split_of_the_quilt(pkg, scenes):
         if n > 1:
             sharded = sorted(tuple(int(x) for x in r) for rank in range(n) for r in s.shard_tiles(rank, n))
             assert sharded == sorted(tuple(int(x) for x in r) for r in t)
+
+
+def test_integration_shim_compiles_against_the_reference_headers():
+    """integration/mvpath_b200.cpp -- the plugin a maintainer adds to the reference tree -- passes `g++ -fsyntax-only` against the reference's
+    own headers (scalar_rgb config generated by oracle/gen_ref_config.py) and include/amvpt.h.  Skipped where /root/reference is absent."""
+    ref = "/root/reference"
+    if not os.path.isdir(os.path.join(ref, "include", "mitsuba")):
+        pytest.skip("reference tree not mounted")
+    cfg = os.path.join(ROOT, "oracle", "_ref", "include", "mitsuba", "core", "config.h")
+    if not os.path.exists(cfg):
+        subprocess.run(["make", "-C", os.path.join(ROOT, "oracle"), "_ref/include/mitsuba/core/config.h"], check=True, capture_output=True)
+    inc = [os.path.join(ROOT, "oracle", "_ref", "include"), os.path.join(ROOT, "include"), f"{ref}/include", f"{ref}/ext/drjit/include",
+           f"{ref}/ext/drjit/ext/drjit-core/include", f"{ref}/ext/nanobind/include", f"{ref}/ext/tinyformat",
+           f"{ref}/ext/drjit/ext/drjit-core/ext/nanothread/include", f"{ref}/ext/fastfloat/include"]
+    cmd = ["g++", "-std=c++17", "-fsyntax-only", "-include", "cmath"] + [x for i in inc for x in ("-I", i)] + [os.path.join(ROOT, "integration", "mvpath_b200.cpp")]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-3000:]
