@@ -11,13 +11,14 @@ u = dict(zip(hdr, rows[1]))
 def bytes_of(k):
     v = num(k); unit = u.get(k, "")
     return v * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(unit, 1) if v is not None else None
-m = {"workload": workload, "units_per_launch": units, "kernel_name": d["Kernel Name"], "duration_ns_under_ncu": num("gpu__time_duration.sum"),
+m = {"workload": workload, "units_per_launch": units, "kernel_name": d["Kernel Name"], "duration_under_ncu": num("gpu__time_duration.sum"), "duration_unit": u.get("gpu__time_duration.sum", ""),
      "registers": num("launch__registers_per_thread"), "grid": num("launch__grid_size"),
      "inst_executed": num("smsp__inst_executed.sum"), "thread_inst_executed": num("smsp__thread_inst_executed.sum"),
      "lanes_per_inst": num("smsp__thread_inst_executed_per_inst_executed.ratio"),
      "issue_active_pct": num("smsp__issue_active.avg.pct_of_peak_sustained_active"),
      "dram_bytes": (bytes_of("dram__bytes_read.sum") or 0) + (bytes_of("dram__bytes_write.sum") or 0),
-     "lts_bytes": bytes_of("lts__t_bytes.sum"), "l2_hit_pct": num("lts__t_sector_hit_rate.pct"), "l1_hit_pct": num("l1tex__t_sector_hit_rate.pct"),
+     "lts_bytes": (num("lts__t_sectors.sum") or 0) * 32.0 or bytes_of("lts__t_bytes.sum"),
+     "l1_bytes": (num("l1tex__t_sectors_pipe_lsu_mem_global_op_ld.sum") or 0) * 32.0, "l2_hit_pct": num("lts__t_sector_hit_rate.pct"), "l1_hit_pct": num("l1tex__t_sector_hit_rate.pct"),
      "long_scoreboard": num("smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio"),
      "warps_active_pct": num("sm__warps_active.avg.pct_of_peak_sustained_active"), "source": source}
 if m["thread_inst_executed"] is None and m["lanes_per_inst"]:
