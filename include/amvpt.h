@@ -221,6 +221,14 @@ int amvpt_trace_lanes(amvpt_scene *s, uint32_t seed_value, uint32_t spp_per_pass
 /* any_hit: bit 0 = Scene::ray_test semantics (first accepted triangle), bit 1 = walk the compressed 4-wide tree of the wavefront trace stage */
 int amvpt_intersect(amvpt_scene *s, const float *o, const float *d, const float *maxt, uint32_t n, int any_hit,
                     uint32_t *prim, float *tuv, uint64_t *stats2);
+/* amvpt_intersect without any allocation (csrc/noalloc.cu).  No counterpart in the reference; added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  Same arguments, same results
+ * bit for bit.  Rays, results and counters are staged in ONE file-scope device array of AMVPT_STATIC_MAX_RAYS x 44 B + 64 B = 2.75 MiB that
+ * every GPU loading the library holds until exit; n > AMVPT_STATIC_MAX_RAYS returns AMVPT_ERR_INVALID.  All calls share that array: calls
+ * that overlap on the GPU (two host threads, two streams) race -- serialise them. */
+#define AMVPT_STATIC_MAX_RAYS 65536u
+int amvpt_intersect_static(amvpt_scene *s, const float *o, const float *d, const float *maxt, uint32_t n, int any_hit,
+                           uint32_t *prim, float *tuv, uint64_t *stats2);
 int amvpt_bsdf_eval_pdf_sample(amvpt_scene *s, int bsdf, const float *wi, const float *wo, const float *s1, const float *s2, uint32_t n,
                                float *f, float *pdf, float *bs_wo, float *bs_pdf, float *bs_eta, uint32_t *bs_type, float *weight);
 int amvpt_math1(int device, int op, const float *in, uint32_t n, float *out);

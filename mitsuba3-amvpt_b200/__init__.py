@@ -78,7 +78,7 @@ EXPORTS = ["amvpt_last_error", "amvpt_device_count", "amvpt_scene_create", "amvp
            "amvpt_scene_get_sensor", "amvpt_scene_get_bsdf_tables", "amvpt_scene_counts", "amvpt_scene_get_mesh",
            "amvpt_scene_get_bsdf", "amvpt_scene_get_integrator", "amvpt_render", "amvpt_shard_tiles", "amvpt_view_tiles", "amvpt_adaptive_alloc", "amvpt_comm_unique_id", "amvpt_comm_init", "amvpt_comm_destroy", "amvpt_film_gather", "amvpt_comm_allreduce_sum", "amvpt_gather_tiles", "amvpt_film_develop_pinned", "amvpt_cancel", "amvpt_film_clear",
            "amvpt_film_raw", "amvpt_film_develop", "amvpt_film_develop_device", "amvpt_film_device_ptr", "amvpt_film_add_host",
-           "amvpt_trace_lanes", "amvpt_trace_lanes_multi", "amvpt_intersect", "amvpt_bsdf_eval_pdf_sample", "amvpt_math1", "amvpt_sampler_stream",
+           "amvpt_trace_lanes", "amvpt_trace_lanes_multi", "amvpt_intersect", "amvpt_intersect_static", "amvpt_bsdf_eval_pdf_sample", "amvpt_math1", "amvpt_sampler_stream",
            "amvpt_bvh_validate", "amvpt_bvh_q4_validate", "amvpt_membench", "amvpt_film_write_pfm", "amvpt_film_write_exr", "amvpt_f32_to_f16", "amvpt_film_to_srgb8", "amvpt_interlace", "amvpt_display_last_ms"]
 lib.amvpt_scene_destroy.restype = None
 lib.amvpt_scene_destroy.argtypes = [C.c_void_p]
@@ -437,6 +437,15 @@ class Scene:
         o = _f32(o, (-1, 3)); d = _f32(d, (-1, 3)); maxt = _f32(maxt, (-1,)); n = len(o)
         prim = np.zeros(n, np.uint32); tuv = np.zeros((n, 3), np.float32); stats = np.zeros(2, np.uint64)
         _chk(lib.amvpt_intersect(self._h, _p(o), _p(d), _p(maxt), C.c_uint32(n), C.c_int(int(any_hit) | (2 if q4 else 0)), _p(prim, u32p), _p(tuv), _p(stats, u64p)))
+        return prim, tuv, stats
+
+    STATIC_MAX_RAYS = 65536      # AMVPT_STATIC_MAX_RAYS (include/amvpt.h)
+
+    def intersect_static(self, o, d, maxt, any_hit=False, q4=False):
+        """amvpt_intersect_static: the same tap with its scratch in a static device array (no allocation; at most STATIC_MAX_RAYS rays)."""
+        o = _f32(o, (-1, 3)); d = _f32(d, (-1, 3)); maxt = _f32(maxt, (-1,)); n = len(o)
+        prim = np.zeros(n, np.uint32); tuv = np.zeros((n, 3), np.float32); stats = np.zeros(2, np.uint64)
+        _chk(lib.amvpt_intersect_static(self._h, _p(o), _p(d), _p(maxt), C.c_uint32(n), C.c_int(int(any_hit) | (2 if q4 else 0)), _p(prim, u32p), _p(tuv), _p(stats, u64p)))
         return prim, tuv, stats
 
     def bsdf_eval_pdf_sample(self, bsdf, wi, wo, s1, s2):

@@ -9,7 +9,7 @@ NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 # canonical arithmetic: no FMA contraction on device (-fmad=false) or host (-ffp-contract=off); FMA only where written
 COMMON = os.environ.get("AMVPT_CFLAGS", "").split() + ["-std=c++17", "-O3", "-lineinfo", "-fmad=false", "-Xcompiler", "-fPIC,-mfma,-ffp-contract=off,-fno-fast-math,-pthread"]
-SOURCES = ["kernels.cu", "wavefront.cu", "reuse.cu", "display.cu", "scene.cpp", "emitters.cpp", "imageio.cpp", "bvh.cpp", "render.cpp", "comm.cpp", "xml.cpp", "meshio.cpp", "capi.cpp"]
+SOURCES = ["kernels.cu", "wavefront.cu", "reuse.cu", "display.cu", "noalloc.cu", "scene.cpp", "emitters.cpp", "imageio.cpp", "bvh.cpp", "render.cpp", "comm.cpp", "xml.cpp", "meshio.cpp", "capi.cpp"]
 
 
 def _stamp(paths):
