@@ -238,8 +238,13 @@ void build_bvh(const Scene &s, float scene_scale, BvhOut &out) {
     for (size_t i = 0; i < bl.nodes.size(); ++i) if (bl.nodes[i].left >= 0) inner_id[i] = n_inner++;
     auto put = [&](int32_t id, const Box &a, int32_t ca, const Box &b, int32_t cb) {
         float fa, fb; memcpy(&fa, &ca, 4); memcpy(&fb, &cb, 4);
+#if AM_FFMA2       // (lo.x, lo.y, hi.x, hi.y): the packed slab test multiplies register pairs by (id.x, id.y)
+        out.nodes[4 * (size_t) id + 0] = make_float4(a.lo[0], a.lo[1], a.hi[0], a.hi[1]);
+        out.nodes[4 * (size_t) id + 1] = make_float4(b.lo[0], b.lo[1], b.hi[0], b.hi[1]);
+#else
         out.nodes[4 * (size_t) id + 0] = make_float4(a.lo[0], a.hi[0], a.lo[1], a.hi[1]);
         out.nodes[4 * (size_t) id + 1] = make_float4(b.lo[0], b.hi[0], b.lo[1], b.hi[1]);
+#endif
         out.nodes[4 * (size_t) id + 2] = make_float4(a.lo[2], a.hi[2], b.lo[2], b.hi[2]);
         out.nodes[4 * (size_t) id + 3] = make_float4(fa, fb, 0.f, 0.f);
     };

@@ -551,7 +551,11 @@ int amvpt_bvh_validate(amvpt_scene *h, uint32_t *max_depth, uint32_t *n_leaves) 
             }
 #else
             const float4 *n = &s.bvh.nodes[4 * (size_t) ref];
+#if AM_FFMA2
+            B a = { { n[0].x, n[0].y, n[2].x }, { n[0].z, n[0].w, n[2].y } }, b = { { n[1].x, n[1].y, n[2].z }, { n[1].z, n[1].w, n[2].w } };
+#else
             B a = { { n[0].x, n[0].z, n[2].x }, { n[0].y, n[0].w, n[2].y } }, b = { { n[1].x, n[1].z, n[2].z }, { n[1].y, n[1].w, n[2].w } };
+#endif
             int32_t ca, cb; memcpy(&ca, &n[3].x, 4); memcpy(&cb, &n[3].y, 4);
             bool a_empty = ca == -1, b_empty = cb == -1;
             if (box) for (int k = 0; k < 3; ++k) {

@@ -148,14 +148,43 @@ AM_D int32_t node_step(const DScene &s, const SlabRay &r, float best, int32_t no
     return next;
 }
 #else
+#if AM_FFMA2
+// d = a * b + c on two packed binary32 lanes (sm_100 FFMA2; each lane is the IEEE fma)
+AM_D float2 fma2(float2 a, float2 b, float2 c) {
+    float2 d;
+    asm("{ .reg .b64 ra, rb, rc, rd; mov.b64 ra, {%2, %3}; mov.b64 rb, {%4, %5}; mov.b64 rc, {%6, %7}; fma.rn.f32x2 rd, ra, rb, rc; mov.b64 {%0, %1}, rd; }"
+        : "=f"(d.x), "=f"(d.y) : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y), "f"(c.x), "f"(c.y));
+    return d;
+}
+// slab test of one child box from (lo.x, lo.y, hi.x, hi.y) and (lo.z, hi.z): three FFMA2 instead of six FFMA, same values
+AM_D bool slab2(float4 xy, float loz, float hiz, const SlabRay &r, float tbest, float *tnear) {
+    const float2 idxy = make_float2(r.id.x, r.id.y), nxy = make_float2(-r.ood.x, -r.ood.y), idzz = make_float2(r.id.z, r.id.z), nzz = make_float2(-r.ood.z, -r.ood.z);
+    const float2 t0 = fma2(make_float2(xy.x, xy.y), idxy, nxy), t1 = fma2(make_float2(xy.z, xy.w), idxy, nxy), tz = fma2(make_float2(loz, hiz), idzz, nzz);
+    float tmin = fmaxf(fmax3(fminf(t0.x, t1.x), fminf(t0.y, t1.y), fminf(tz.x, tz.y)), 0.f);
+    float tmax = fminf(fmin3(fmaxf(t0.x, t1.x), fmaxf(t0.y, t1.y), fmaxf(tz.x, tz.y)), tbest);
+    *tnear = tmin;
+    return tmin <= tmax * (1.f + AM_SLAB_EPS);
+}
+#endif
 AM_D int32_t node_step(const DScene &s, const SlabRay &r, float best, int32_t node, int32_t *stack, int &sp) {
     const float4 *np = s.nodes + 4 * (size_t) node;
     float4 n0 = ldg4(np), n1 = ldg4(np + 1), n2 = ldg4(np + 2), n3 = ldg4(np + 3);
     float ta, tb;
+#if AM_FFMA2
+    bool ha = slab2(n0, n2.x, n2.y, r, best, &ta);
+    bool hb = slab2(n1, n2.z, n2.w, r, best, &tb);
+#else
     bool ha = slab(n0.x, n0.y, n0.z, n0.w, n2.x, n2.y, r, best, &ta);
     bool hb = slab(n1.x, n1.y, n1.z, n1.w, n2.z, n2.w, r, best, &tb);
+#endif
     int32_t ca = __float_as_int(n3.x), cb = __float_as_int(n3.y);
-    if (ha && hb) { bool swap = tb < ta; stack[sp++] = swap ? ca : cb; return swap ? cb : ca; }
+    if (ha && hb) {
+        bool swap = tb < ta; int32_t far = swap ? ca : cb;
+#if AM_PREFETCH_FAR       // the postponed child's record is pulled towards L1 while the near subtree is walked
+        if (far >= 0) asm volatile("prefetch.global.L1 [%0];" :: "l"(s.nodes + 4 * (size_t) far));
+#endif
+        stack[sp++] = far; return swap ? cb : ca;
+    }
     if (ha || hb) return ha ? ca : cb;
     return stack[--sp];
 }

@@ -6,6 +6,12 @@
 #ifndef AM_BVH_WIDTH
 #define AM_BVH_WIDTH 2     /* children per BVH node: 2 (default) or 4 (build with -DAM_BVH_WIDTH=4; measured slower on B200); host builder and kernels share the value */
 #endif
+#ifndef AM_FFMA2
+#define AM_FFMA2 0         /* 1: binary-tree nodes hold (lo.x, lo.y, hi.x, hi.y) and the slab test uses Blackwell's packed fma.rn.f32x2 (FFMA2) */
+#endif
+#ifndef AM_PREFETCH_FAR
+#define AM_PREFETCH_FAR 0  /* 1: prefetch.global.L1 of the postponed child's node record when both children are hit */
+#endif
 #define AM_STACK_SIZE (AM_BVH_WIDTH == 4 ? 96 : 64)   /* per-thread traversal stack entries; the builder checks the tree against it */
 #define AM_NODE_F4 (AM_BVH_WIDTH == 4 ? 8 : 4)         /* float4 per node */
 
