@@ -158,7 +158,9 @@ def roofline(pkg, s, args, spp, sched_arg, clk, device):
     cs = s.last_stats
     rays = cs["closest_rays"] + cs["shadow_rays"]
     bvh_bytes_per_path = (cs["bvh_nodes"] * float(NODE_BYTES) + cs["tri_tests"] * float(TRI_BYTES)) / cs["paths"]
-    s.render(seed=0, spp=spp, develop=False, scheduler=sched_arg, time_stages=True); ks = s.last_stats
+    # launch durations are per pass (16 spp), so a capped sample count gives the same per-launch figures; it bounds this single-GPU pass on the
+    # multi-GPU / 1024-spp configurations
+    s.render(seed=0, spp=min(spp, 64), develop=False, scheduler=sched_arg, time_stages=True); ks = s.last_stats
     hbm_peak, peak_src = peaks()
     sched = SCHED_NAMES[ks["scheduler_used"]]
     if sched == "wavefront":

@@ -41,6 +41,11 @@ void spectrum_to_srgb(std::vector<double> wavelengths, std::vector<double> value
         if (n > 0 && wavelengths[n] - wavelengths[n - 1] < 0) AM_THROW("Wavelengths must be specified in increasing order!");
     }
     const bool bounded = !(within_emitter || unbounded_name), d65 = !(within_emitter && !unbounded_name);      // xml.cpp:1249-1252
+    spectrum_list_to_srgb(wavelengths, values, bounded, d65, rgb);
+}
+// spectrum_list_to_srgb (src/core/spectrum.cpp:85-130); `values` already carry the unit conversion
+void spectrum_list_to_srgb(const std::vector<double> &wavelengths, const std::vector<double> &values, bool bounded, bool d65, double *rgb) {
+    if (wavelengths.size() != values.size() || wavelengths.size() < 2) AM_THROW("spectrum: need at least two wavelength:value pairs");
     double xyz[3] = { 0, 0, 0 }; const int steps = 1000;
     for (int i = 0; i < steps; ++i) {                                 // spectrum.cpp:92-114
         const double w = kCieMin + (i / (double) (steps - 1)) * (kCieMax - kCieMin);

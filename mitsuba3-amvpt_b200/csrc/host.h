@@ -60,6 +60,7 @@ struct EnvMap {
 // (spectrum_list_to_srgb, src/core/spectrum.cpp:85-130), a uniform value inside an emitter -> value * xyz_to_srgb(1, 1, 1)
 void spectrum_to_srgb(std::vector<double> wavelengths, std::vector<double> values, bool within_emitter, bool unbounded_name, double *rgb);
 void uniform_emitter_spectrum_to_srgb(double value, double *rgb);
+void spectrum_list_to_srgb(const std::vector<double> &wavelengths, const std::vector<double> &values, bool bounded, bool d65, double *rgb);
 // imageio.cpp: Bitmap(path) -> convert(RGB, Float32, linear), top row first
 void load_image_rgb(const std::string &path, uint32_t *w, uint32_t *h, std::vector<float> &rgb);
 
@@ -169,6 +170,7 @@ Scene *load_xml_string(const std::string &xml, const std::string &base_dir, cons
 // meshio.cpp
 void load_obj(const std::string &path, const M4d &to_world, bool face_normals, bool flip_tex, HMesh &out);
 void load_ply(const std::string &path, const M4d &to_world, bool face_normals, HMesh &out);
+void load_serialized(const std::string &path, int shape_index, const M4d &to_world, bool face_normals, HMesh &out);
 void make_cube(const M4d &to_world, HMesh &out);
 
 } // namespace amvpt

@@ -1,5 +1,5 @@
 // meshio.cpp -- mesh shape plugins of the AMVPT path: `obj` (src/shapes/obj.cpp:142-411), `ply` (src/shapes/ply.cpp:160-455),
-// `cube` (src/shapes/cube.cpp:101-165).  All three end in the same Mesh record: float32 positions already in world space
+// `serialized` (src/shapes/serialized.cpp:237-404), `cube` (src/shapes/cube.cpp:101-165).  All of them end in the same Mesh record: float32 positions already in world space
 // (Transform4f::transform_affine, include/mitsuba/core/transform.h:119-127), optional world-space vertex normals
 // (normalize(inverse_transpose * n), :164-173) and triangle indices.  What matters for parity is the *order* of vertices
 // and faces (global primitive indices feed the closest-hit tie rule and emitter sampling) and the float32 arithmetic of
@@ -13,6 +13,9 @@
 #include <map>
 #include <sstream>
 #include <array>
+#include <algorithm>
+#include <functional>
+#include <dlfcn.h>
 
 namespace amvpt {
 
@@ -278,6 +281,100 @@ void load_ply(const std::string &path, const M4d &to_world, bool face_normals, H
     if (fmt == 0) while (rd.pos < data.size() && isspace((unsigned char) data[rd.pos])) ++rd.pos;
     if (rd.pos != data.size()) fail("invalid file -- trailing content");
     if (!face_normals && !have_normals) recompute_vertex_normals(out);   // ply.cpp:444-449
+}
+
+// ------------------------------------------------------------------------------------------------ serialized
+// SerializedMesh (src/shapes/serialized.cpp:237-404): header (0x041C, version 3 | 4), for shape_index > 0 the offset dictionary at the end of
+// the file, then ONE zlib stream per sub-mesh: flags, [v4: name], vertex / face counts (u64), positions, [normals], [texcoords], [colours],
+// faces (u32 x 3), single or double precision.  zlib is bound at run time (libz.so.1, like NCCL in comm.cpp): the library itself keeps no
+// link-time dependency beyond the CUDA runtime.
+namespace {
+struct ZApi {
+    struct z_stream_s { const unsigned char *next_in; unsigned avail_in; unsigned long total_in; unsigned char *next_out; unsigned avail_out; unsigned long total_out;
+                        const char *msg; void *state; void *zalloc; void *zfree; void *opaque; int data_type; unsigned long adler; unsigned long reserved; };
+    int (*inflateInit2_)(z_stream_s *, int, const char *, int) = nullptr; int (*inflate)(z_stream_s *, int) = nullptr; int (*inflateEnd)(z_stream_s *) = nullptr;
+    const char *(*zlibVersion)() = nullptr;
+    static ZApi &get() {
+        static ZApi z; static bool tried = false;
+        if (!tried) { tried = true;
+            void *h = dlopen("libz.so.1", RTLD_NOW | RTLD_LOCAL); if (!h) h = dlopen("libz.so", RTLD_NOW | RTLD_LOCAL);
+            if (h) { z.inflateInit2_ = (decltype(z.inflateInit2_)) dlsym(h, "inflateInit2_"); z.inflate = (decltype(z.inflate)) dlsym(h, "inflate");
+                     z.inflateEnd = (decltype(z.inflateEnd)) dlsym(h, "inflateEnd"); z.zlibVersion = (decltype(z.zlibVersion)) dlsym(h, "zlibVersion"); } }
+        return z;
+    }
+};
+// Inflates one zlib stream starting at `src` until `want` more bytes are available or the stream ends.
+struct Inflater {
+    ZApi &z; ZApi::z_stream_s zs{}; std::vector<unsigned char> buf; size_t rd = 0; bool ended = false; const std::function<void(const std::string &)> &fail;
+    Inflater(const unsigned char *src, size_t n, const std::function<void(const std::string &)> &f) : z(ZApi::get()), fail(f) {
+        if (!z.inflateInit2_ || !z.inflate || !z.inflateEnd || !z.zlibVersion) fail("zlib (libz.so.1) could not be loaded");
+        zs.next_in = src; zs.avail_in = (unsigned) std::min<size_t>(n, 0xffffffffu);
+        if (z.inflateInit2_(&zs, 15, z.zlibVersion(), (int) sizeof(zs)) != 0) fail("could not initialize ZLIB");
+    }
+    ~Inflater() { if (z.inflateEnd) z.inflateEnd(&zs); }
+    void read(void *dst, size_t n) {
+        while (buf.size() - rd < n && !ended) {
+            const size_t old = buf.size(), chunk = std::max<size_t>(1u << 20, n); buf.resize(old + chunk);
+            zs.next_out = buf.data() + old; zs.avail_out = (unsigned) chunk;
+            const int rc = z.inflate(&zs, 0 /* Z_NO_FLUSH */);
+            buf.resize(old + chunk - zs.avail_out);
+            if (rc == 1 /* Z_STREAM_END */) ended = true;
+            else if (rc != 0 || (zs.avail_in == 0 && zs.avail_out != 0)) { if (rc != 0) fail("inflate(): " + std::string(zs.msg ? zs.msg : "stream error")); ended = true; }
+        }
+        if (buf.size() - rd < n) fail("read less data than expected");
+        if (dst) std::memcpy(dst, buf.data() + rd, n);
+        rd += n;
+    }
+    template <class T> T get() { T v; read(&v, sizeof(T)); return v; }
+};
+} // namespace
+
+void load_serialized(const std::string &path, int shape_index, const M4d &to_world, bool face_normals, HMesh &out) {
+    const std::function<void(const std::string &)> fail = [&](const std::string &d) { AM_THROW("io: Error while loading serialized file \"%s\": %s!", path.c_str(), d.c_str()); };
+    std::ifstream f(path, std::ios::binary); if (!f) fail("file not found");
+    if (shape_index < 0) fail("shape index must be nonnegative!");
+    std::ostringstream ss; ss << f.rdbuf(); const std::string data = ss.str(); const size_t size = data.size();
+    auto at = [&](size_t off, void *dst, size_t n) { if (off + n > size) fail("unexpected end of file"); std::memcpy(dst, data.data() + off, n); };
+    int16_t format = 0, version = 0; at(0, &format, 2); at(2, &version, 2);
+    if (format != 0x041C) fail("encountered an invalid file format");
+    if (version != 3 && version != 4) fail("encountered an incompatible file version");
+    size_t start = 4;
+    if (shape_index != 0) {
+        if (size < 8) fail("unexpected end of file");
+        uint32_t count = 0; at(size - 4, &count, 4);
+        if (shape_index >= (int) count) fail("Unable to unserialize mesh, shape index is out of range! (requested " + std::to_string(shape_index) + " out of 0.." + std::to_string((int) count - 1) + ")");
+        if (version == 4) { uint64_t off = 0; at(size - 8 * (size_t) (count - shape_index) - 4, &off, 8); start = (size_t) off + 4; }
+        else { uint32_t off = 0; at(size - 4 * (size_t) (count - shape_index + 1), &off, 4); start = (size_t) off + 4; }
+        if (start > size) fail("unexpected end of file");
+    }
+    Inflater in((const unsigned char *) data.data() + start, size - start, fail);
+    const uint32_t flags = in.get<uint32_t>();
+    if (version == 4) for (;;) { char ch = in.get<char>(); if (ch == 0) break; }
+    const uint64_t nv = in.get<uint64_t>(), nf = in.get<uint64_t>();
+    if (nv > 0xffffffffull || nf > 0xffffffffull) fail("mesh too large");
+    const bool dp = (flags & 0x2000u) != 0, has_normals = (flags & 0x0001u) != 0, has_uv = (flags & 0x0002u) != 0, has_colors = (flags & 0x0008u) != 0;
+    auto read_floats = [&](std::vector<float> *dst, size_t dim) {
+        const size_t n = (size_t) nv * dim;
+        if (dp) { std::vector<double> tmp(n); in.read(tmp.data(), n * 8); if (dst) { dst->resize(n); for (size_t i = 0; i < n; ++i) (*dst)[i] = (float) tmp[i]; } }
+        else if (dst) { dst->resize(n); in.read(dst->data(), n * 4); } else in.read(nullptr, n * 4);
+    };
+    out.pos.clear(); out.nrm.clear(); out.faces.clear();
+    read_floats(&out.pos, 3);
+    if (has_normals) read_floats(face_normals ? nullptr : &out.nrm, 3);
+    if (has_uv) read_floats(nullptr, 2);                 // texture coordinates: no textures on this path
+    if (has_colors) read_floats(nullptr, 3);
+    out.faces.resize((size_t) nf * 3); in.read(out.faces.data(), (size_t) nf * 12);
+    for (uint32_t idx : out.faces) if (idx >= nv) fail("face index out of range");
+    XfF xf = to_float(to_world);
+    for (size_t i = 0; i < (size_t) nv; ++i) {           // serialized.cpp:359-374
+        V3 p = xf_point(xf.mat, v3(out.pos[3 * i], out.pos[3 * i + 1], out.pos[3 * i + 2]));
+        out.pos[3 * i] = p.x; out.pos[3 * i + 1] = p.y; out.pos[3 * i + 2] = p.z;
+        if (has_normals && !face_normals) {
+            V3 n = normalize(xf_normal(xf.inv_t, v3(out.nrm[3 * i], out.nrm[3 * i + 1], out.nrm[3 * i + 2])));
+            out.nrm[3 * i] = n.x; out.nrm[3 * i + 1] = n.y; out.nrm[3 * i + 2] = n.z;
+        }
+    }
+    if (!face_normals && !has_normals) recompute_vertex_normals(out);      // :396-401
 }
 
 // ------------------------------------------------------------------------------------------------ cube

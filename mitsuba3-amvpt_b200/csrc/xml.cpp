@@ -343,14 +343,60 @@ void alphas(Obj &o, DBsdf &b) {      // roughconductor.cpp:189-199
         b.alpha_u = o.scalar_tex("alpha_u", 0.1f); b.alpha_v = o.scalar_tex("alpha_v", 0.1f);
     } else b.alpha_u = b.alpha_v = o.scalar_tex("alpha", 0.1f);
 }
-void no_material(Obj &o) {
-    std::string m = o.s("material", "none");
-    if (o.has("eta") || m == "none") { if (o.has("material") && m != "none") AM_THROW("%s: Should specify either (eta, k) or material, not both.", o.where.c_str()); return; }
-    AM_THROW("%s: conductor `material` presets read measured spectra (resources/data/ior), which this RGB path does not load; give <rgb name=\"eta\"> and <rgb name=\"k\">", o.where.c_str());
+// spectrum_from_file (src/core/spectrum.cpp:10-55): `.spd` text, "wavelength value" per line, '#' starts a comment that runs to the end of the line
+void read_spd(const std::string &path, std::vector<double> &wl, std::vector<double> &val) {
+    if (path.size() < 4 || path.compare(path.size() - 4, 4, ".spd") != 0) AM_THROW("io: \"%s\": You need to provide a valid extension like \".spd\" to read the information from an ASCII file.", path.c_str());
+    std::ifstream f(path, std::ios::binary); if (!f) AM_THROW("io: \"%s\": file does not exist!", path.c_str());
+    std::ostringstream ss; ss << f.rdbuf(); const std::string text = ss.str();
+    const char *cur = text.c_str(), *end = cur + text.size(); bool comment = false; size_t counter = 0;
+    while (cur < end) {
+        const char c = *cur;
+        if (c == '#') { comment = true; ++cur; }
+        else if (c == '\n') { comment = false; counter = 0; ++cur; }
+        else if (!comment && c != ' ' && c != '\r') {
+            char *tmp = nullptr; const double v = std::strtod(cur, &tmp);
+            if (tmp == cur) AM_THROW("io: \"%s\": could not parse a floating point value", path.c_str());
+            cur = tmp;
+            if (counter == 0) wl.push_back(v); else if (counter == 1) val.push_back(v);
+            else AM_THROW("io: \"%s\": While parsing the file, more than two elements were defined in a line", path.c_str());
+            ++counter;
+        } else ++cur;
+    }
+    if (wl.size() != val.size() || wl.size() < 2) AM_THROW("io: \"%s\": expected at least two \"wavelength value\" lines", path.c_str());
+}
+// ior_from_file in an RGB variant (include/mitsuba/render/ior.h:101-137): values * MI_CIE_Y_NORMALIZATION, spectrum_list_to_srgb(bounded = false,
+// d65 = false), handed to an unbounded `srgb` texture, i.e. used as the colour it is
+void ior_from_file(const std::string &path, float *rgb) {
+    std::vector<double> wl, val; read_spd(path, wl, val);
+    for (double &v : val) v *= 1.0 / 106.7502593994140625;
+    double c[3]; spectrum_list_to_srgb(wl, val, false, false, c);
+    for (int k = 0; k < 3; ++k) rgb[k] = (float) c[k];
 }
 
 struct Builder {
-    Scene &sc; std::map<Obj *, int> bsdf_index; std::set<Obj *> used_emitters;
+    Scene &sc; std::map<Obj *, int> bsdf_index; std::set<Obj *> used_emitters; Loader *loader = nullptr; std::string base_dir;
+
+    // conductor.cpp:228-241 / roughconductor.cpp: (eta, k) given explicitly, `material = none` (eta 0, k 1: a perfect mirror), or a preset read
+    // from data/ior/<material>.{eta,k}.spd (complex_ior_from_file, ior.h:138-143).  The reference finds the files through its resource
+    // directory; here: the scene's directory, the <path> entries, $AMVPT_DATA_DIR, and `data/ior` / `ior` under each ancestor of the scene's directory.
+    void conductor_ior(Obj &o, DBsdf &b) {
+        const std::string m = o.s("material", "none");
+        if (o.has("eta") || m == "none") {
+            if (o.has("material") && m != "none") AM_THROW("%s: Should specify either (eta, k) or material, not both.", o.where.c_str());
+            o.color("eta", 0.f, b.eta); o.color("k", 1.f, b.k); return;
+        }
+        std::vector<std::string> roots; if (const char *e = getenv("AMVPT_DATA_DIR")) roots.push_back(e);
+        for (std::string d = base_dir.empty() ? "." : base_dir; ; ) {
+            roots.push_back(d + "/data"); roots.push_back(d);
+            size_t sl = d.rfind('/'); if (sl == std::string::npos || sl == 0) break; d = d.substr(0, sl);
+        }
+        if (loader) for (auto &d : loader->search) { roots.push_back(d + "/data"); roots.push_back(d); }
+        auto find = [&](const std::string &leaf) -> std::string {
+            for (auto &r : roots) { std::string c = r + "/ior/" + leaf; std::ifstream f(c); if (f) return c; }
+            AM_THROW("io: %s: \"data/ior/%s\": file does not exist! (conductor material \"%s\"; set AMVPT_DATA_DIR to the reference's resources/data directory)", o.where.c_str(), leaf.c_str(), m.c_str());
+        };
+        ior_from_file(find(m + ".eta.spd"), b.eta); ior_from_file(find(m + ".k.spd"), b.k);
+    }
 
     int bsdf(const std::shared_ptr<Obj> &op) {
         auto it = bsdf_index.find(op.get()); if (it != bsdf_index.end()) return it->second;
@@ -370,7 +416,7 @@ struct Builder {
         if (t == "diffuse") { b.type = BSDF_DIFFUSE; o->color("reflectance", .5f, b.reflectance); }
         else if (t == "conductor" || t == "roughconductor") {
             b.type = t == "conductor" ? BSDF_CONDUCTOR : BSDF_ROUGHCONDUCTOR;
-            no_material(*o); o->color("eta", 0.f, b.eta); o->color("k", 1.f, b.k); o->color("specular_reflectance", 1.f, b.spec_refl);
+            conductor_ior(*o, b); o->color("specular_reflectance", 1.f, b.spec_refl);
             if (b.type == BSDF_ROUGHCONDUCTOR) { b.distr = distribution(*o); if (!o->b("sample_visible", true)) AM_THROW("%s: sample_visible=false is not supported on this path", o->where.c_str()); alphas(*o, b); }
         }
         else if (t == "dielectric" || t == "roughdielectric") {
@@ -404,8 +450,9 @@ struct Builder {
         bool face_normals = o.b("face_normals", false); m.flip_normals = o.b("flip_normals", false) ? 1 : 0;
         if (o.type == "obj") load_obj(ld.resolve(o.s("filename", ""), base), tw, face_normals, o.b("flip_tex_coords", true), m);
         else if (o.type == "ply") { o.b("flip_tex_coords", false); load_ply(ld.resolve(o.s("filename", ""), base), tw, face_normals, m); }
+        else if (o.type == "serialized") load_serialized(ld.resolve(o.s("filename", ""), base), (int) o.i("shape_index", 0), tw, face_normals, m);
         else if (o.type == "cube") { make_cube(tw, m); if (face_normals) m.nrm.clear(); }
-        else AM_THROW("%s: shape plugin \"%s\" is not part of the AMVPT path (supported meshes: obj, ply, cube)", o.where.c_str(), o.type.c_str());
+        else AM_THROW("%s: shape plugin \"%s\" is not part of the AMVPT path (supported meshes: obj, ply, serialized, cube)", o.where.c_str(), o.type.c_str());
         if (face_normals) m.nrm.clear();
         std::shared_ptr<Obj> bs, em;
         for (auto &k : o.children()) {
@@ -610,7 +657,7 @@ struct Builder {
 Scene *build_scene(Loader &ld, const std::shared_ptr<Obj> &root, const std::string &base) {
     if (root->cls != "scene") AM_THROW("%s: the root element must be <scene>", root->where.c_str());
     std::set<Obj *> seen; ld.resolve_refs(*root, seen);
-    std::unique_ptr<Scene> sc(new Scene()); Builder b{ *sc };
+    std::unique_ptr<Scene> sc(new Scene()); Builder b{ *sc }; b.loader = &ld; b.base_dir = base;
     std::shared_ptr<Obj> integ, sens;
     for (auto &k : root->children()) {
         if (k->cls == "integrator") { if (integ) AM_THROW("%s: Only one integrator can be specified per scene.", k->where.c_str()); integ = k; }

@@ -8,7 +8,8 @@
    byte for byte in the reference's directory layout so that the XML files load unmodified (they are data fixtures; the GPU box has no
    /root/reference).  Also the Cornell box scene of resources/data/scenes/cbox (BASELINE configs 1-3 use its geometry).
 3. tests/golden/spectrum_refs.json: wavelength spectra of those scenes converted to linear sRGB by an independent numpy restatement of
-   spectrum_list_to_srgb (src/core/spectrum.cpp:85-130) over the CIE tables parsed from the reference sources.
+   spectrum_list_to_srgb (src/core/spectrum.cpp:85-130) over the CIE tables parsed from the reference sources; also the measured
+   (eta, k) spectra of three conductor `material` presets (resources/data/ior/{Au,Cu,Al}.*.spd, copied to tests/golden/scenes/ior/).
 """
 import json, os, re, shutil
 os.environ["OPENCV_IO_ENABLE_OPENEXR"] = "1"
@@ -24,6 +25,7 @@ SCENES = {
     "infinite_mirrors": ("tests/scenes/infinite_mirrors/scene_path.xml", "tests/scenes/infinite_mirrors/refs/scene_ref_rgb"),
 }
 COPY = ["tests/scenes/bsdf_spheres/fragments/single_sphere.xml", "common/meshes/sphere.obj", "common/meshes/rectangle.obj", "common/textures/museum.exr",
+        "tests/serialized/rectangle_normals.serialized", "tests/serialized/rectangle_normals_uv.serialized", "tests/serialized/rectangle_uv.serialized",
         "scenes/cbox/cbox-rgb.xml", "scenes/cbox/fragments/base.xml", "scenes/cbox/fragments/bsdfs-rgb.xml", "scenes/cbox/fragments/shapes.xml"]
 
 
@@ -47,9 +49,9 @@ def main():
     d65_tbl = np.array(re.findall(r"([-0-9.eE+]+)f", blk), np.float32).astype(np.float64) / 98.99741751876255
     M = np.array([[3.240479, -1.537150, -0.498535], [-0.969256, 1.875991, 0.041556], [0.055648, -0.204043, 1.057311]], np.float32).astype(np.float64)
 
-    def to_srgb(wl, val, within_emitter, unbounded=False):
+    def to_srgb(wl, val, within_emitter, unbounded=False, flags=None):
         wl = np.asarray(wl, np.float64); val = np.asarray(val, np.float64) / 106.7502593994140625
-        bounded = not (within_emitter or unbounded); d65 = not (within_emitter and not unbounded)
+        bounded, d65 = flags if flags is not None else (not (within_emitter or unbounded), not (within_emitter and not unbounded))
         w = 360.0 + (np.arange(1000) / 999.0) * 470.0
         w = w[(w >= wl[0]) & (w <= wl[-1])]
         v = np.interp(w, wl, val)
@@ -66,7 +68,15 @@ def main():
     for c in cases:
         c["rgb"] = to_srgb(c["wavelengths"], c["values"], c["within_emitter"])
     uniform_emitter = (M @ np.ones(3)).tolist()
-    json.dump(dict(cases=cases, uniform_emitter_white=uniform_emitter), open(os.path.join(HERE, "spectrum_refs.json"), "w"), indent=1)
+    # conductor `material` presets (ior_from_file, include/mitsuba/render/ior.h:101-137: bounded = false, d65 = false) of three measured metals
+    ior = {}
+    for m in ("Au", "Cu", "Al"):
+        for part in ("eta", "k"):
+            fn = f"ior/{m}.{part}.spd"; dst = os.path.join(HERE, "scenes", fn); os.makedirs(os.path.dirname(dst), exist_ok=True)
+            shutil.copyfile(os.path.join(REF, fn), dst)
+            rows = [l.split() for l in open(dst) if l.strip() and not l.lstrip().startswith("#")]
+            ior[f"{m}.{part}"] = to_srgb([float(r[0]) for r in rows], [float(r[1]) for r in rows], False, flags=(False, False))
+    json.dump(dict(cases=cases, uniform_emitter_white=uniform_emitter, ior=ior), open(os.path.join(HERE, "spectrum_refs.json"), "w"), indent=1)
     print("wrote render_refs.npz,", len(COPY), "scene files, spectrum_refs.json")
 
 

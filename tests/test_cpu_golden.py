@@ -148,6 +148,89 @@ def test_golden_scenes_load_unmodified(pkg):
     assert s.counts()["n_meshes"] == 8 and s.info()["n_prims"] == 38 and s.counts()["n_emitters"] == 1
 
 
+def test_conductor_material_presets(pkg):
+    """`material` of conductor / roughconductor (conductor.cpp:228-241): complex_ior_from_file reads data/ior/<name>.{eta,k}.spd and, in an RGB
+    variant, converts each to an unbounded sRGB colour.  Fixtures: three of the reference's measured spectra + an independent numpy restatement."""
+    refs = json.load(open(os.path.join(ROOT, "tests", "golden", "spectrum_refs.json")))["ior"]
+    xml = """<scene version="3.0.0">
+      <sensor type="perspective"><film type="hdrfilm"><integer name="width" value="8"/><integer name="height" value="8"/></film></sensor>
+      <shape type="obj"><string name="filename" value="meshes/cbox_floor.obj"/><bsdf type="conductor"><string name="material" value="Au"/></bsdf></shape>
+      <shape type="obj"><string name="filename" value="meshes/cbox_back.obj"/>
+        <bsdf type="roughconductor"><string name="material" value="Cu"/><float name="alpha" value="0.2"/></bsdf></shape>
+      <shape type="obj"><string name="filename" value="meshes/cbox_ceiling.obj"/><bsdf type="twosided"><bsdf type="conductor"><string name="material" value="Al"/></bsdf></bsdf></shape>
+      <shape type="obj"><string name="filename" value="meshes/cbox_luminaire.obj"/><bsdf type="conductor"><string name="material" value="none"/></bsdf>
+        <emitter type="area"><rgb name="radiance" value="1"/></emitter></shape>
+    </scene>"""
+    base = os.path.join(SCENE_DIR, "scenes", "cbox")
+    s = pkg.load_string(xml, base_dir=base)
+    for i, m in enumerate(("Au", "Cu", "Al")):
+        b = s.bsdf(i)
+        assert np.allclose(b["eta"], refs[m + ".eta"], rtol=2e-6) and np.allclose(b["k"], refs[m + ".k"], rtol=2e-6), (m, b["eta"], b["k"])
+    assert np.allclose(s.bsdf(0)["eta"], [0.143, 0.375, 1.442], atol=1e-3) and np.allclose(s.bsdf(0)["k"], [3.983, 2.386, 1.603], atol=1e-3)   # gold as the documentation tabulates it
+    assert tuple(s.bsdf(3)["eta"]) == (0.0, 0.0, 0.0) and tuple(s.bsdf(3)["k"]) == (1.0, 1.0, 1.0)             # material = none: a perfect mirror
+    assert s.bsdf(1)["type"] == "roughconductor" and s.bsdf(2)["twosided"]
+    with pytest.raises(pkg.AmvptError, match="Should specify either"):
+        pkg.load_string(xml.replace('<string name="material" value="Au"/>', '<string name="material" value="Au"/><rgb name="eta" value="1"/>'), base_dir=base)
+    with pytest.raises(pkg.AmvptError, match="file does not exist"):
+        pkg.load_string(xml.replace('value="Au"', 'value="Unobtainium"'), base_dir=base)
+
+
+def _serialized_blob(meshes, version=4):
+    """Writes the container of src/shapes/serialized.cpp:85-178 (independent of the loader under test): per sub-mesh a 4-byte header and one
+    zlib stream; the offset dictionary + count at the end."""
+    import struct, zlib
+    out, offs = b"", []
+    for name, pos, nrm, faces, dp in meshes:
+        offs.append(len(out))
+        flags = (0x2000 if dp else 0x1000) | (0x0001 if nrm is not None else 0)
+        ft = "<f8" if dp else "<f4"
+        body = struct.pack("<I", flags) + (name.encode() + b"\0" if version == 4 else b"") + struct.pack("<QQ", len(pos), len(faces))
+        body += np.asarray(pos, ft).tobytes() + (np.asarray(nrm, ft).tobytes() if nrm is not None else b"") + np.asarray(faces, "<u4").tobytes()
+        out += struct.pack("<HH", 0x041C, version) + zlib.compress(body)
+    out += b"".join(struct.pack("<Q" if version == 4 else "<I", o) for o in offs) + struct.pack("<I", len(offs))
+    return out
+
+
+def test_serialized_meshes(pkg, tmp_path):
+    """`serialized` shape plugin: the reference's own fixtures with the known answers of src/render/tests/test_mesh.py:151-196 (test06), and
+    sub-mesh selection / double precision / format 3 on files written here."""
+    scene = """<scene version="3.0.0">
+      <sensor type="perspective"><film type="hdrfilm"><integer name="width" value="8"/><integer name="height" value="8"/></film></sensor>
+      <shape type="serialized"><string name="filename" value="$fn"/><boolean name="face_normals" value="$fnrm"/><integer name="shape_index" value="$idx"/>
+        <emitter type="area"><rgb name="radiance" value="1"/></emitter></shape></scene>"""
+    fixtures = os.path.join(SCENE_DIR, "tests", "serialized")
+    for features in ("normals", "uv", "normals_uv"):
+        for face_normals in (True, False):
+            s = pkg.load_string(scene, base_dir=fixtures, fn=f"rectangle_{features}.serialized", fnrm=str(face_normals).lower(), idx=0)
+            m = s.mesh(0); p = m["positions"]
+            assert np.allclose(p[0], [-2.85, 0.0, -7.6], atol=1e-3) and np.allclose(p[2], [2.85, 0.0, 0.599999], atol=1e-3) and np.allclose(p[3], [2.85, 0.0, -7.6], atol=1e-3)
+            assert (m["normals"] is not None) == (not face_normals)
+            if m["normals"] is not None:
+                assert np.allclose(m["normals"][[0, 2, 3]], [0.0, 1.0, 0.0])
+    rng = np.random.default_rng(5)
+    def mesh(nv, nf, normals): return (rng.uniform(-1, 1, (nv, 3)), (lambda n: n / np.linalg.norm(n, axis=1, keepdims=True))(rng.normal(size=(nv, 3))) if normals else None,
+                                       rng.integers(0, nv, (nf, 3)))
+    a, b, c = mesh(7, 5, True), mesh(300, 411, False), mesh(12, 9, True)
+    for version in (4, 3):
+        fn = tmp_path / f"multi_v{version}.serialized"
+        fn.write_bytes(_serialized_blob([("first", *a, False), ("second", *b, True), ("third", *c, True)], version))
+        for idx, (pos, nrm, faces), dp in ((0, a, False), (1, b, True), (2, c, True)):
+            m = pkg.load_string(scene, base_dir=str(tmp_path), fn=fn.name, fnrm="false", idx=idx).mesh(0)
+            assert np.array_equal(m["positions"], np.asarray(pos, np.float64 if dp else np.float32).astype(np.float32)), (version, idx)
+            assert np.array_equal(m["faces"], faces)
+            assert m["normals"] is not None                      # given, or recomputed (serialized.cpp:396-401)
+            if nrm is not None:
+                assert np.allclose(m["normals"], nrm, atol=1e-6)
+        with pytest.raises(pkg.AmvptError, match="shape index is out of range"):
+            pkg.load_string(scene, base_dir=str(tmp_path), fn=fn.name, fnrm="false", idx=3)
+    bad = tmp_path / "bad.serialized"; bad.write_bytes(b"\x1d\x04\x04\x00" + b"garbage")
+    with pytest.raises(pkg.AmvptError, match="invalid file format"):
+        pkg.load_string(scene, base_dir=str(tmp_path), fn=bad.name, fnrm="false", idx=0)
+    bad.write_bytes(_serialized_blob([("x", *a, False)])[:40])
+    with pytest.raises(pkg.AmvptError, match="serialized file"):
+        pkg.load_string(scene, base_dir=str(tmp_path), fn=bad.name, fnrm="false", idx=0)
+
+
 # ------------------------------------------------------------------ emitter leaves vs the reference's headers
 def test_oracle_emitter_leaves_match_reference_headers(ob):
     o = ob.orc(); P = lambda x, t=ob.f32p: x.ctypes.data_as(t)
