@@ -132,7 +132,7 @@ struct Scene {
     void prepare_host();
     void commit(int device);
     void film_clear(cudaStream_t st);
-    void *dalloc(size_t bytes);
+    void *dalloc(size_t bytes); void release_device_blocks(); std::vector<size_t> alloc_bytes;      // sizes of `allocs` (device block cache, scene.cpp)
     template <class T> T *upload(const std::vector<T> &v) {
         T *p = (T *) dalloc(std::max<size_t>(v.size(), 1) * sizeof(T));
         if (!v.empty()) AM_CUDA(cudaMemcpy(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));

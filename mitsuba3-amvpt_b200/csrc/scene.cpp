@@ -3,6 +3,9 @@
 #include <algorithm>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
+#include <map>
+#include <mutex>
 
 namespace amvpt {
 
@@ -136,11 +139,59 @@ void bsdf_prepare(DBsdf &b) {
 }
 
 // ---------------------------------------------------------------- Scene
+// Device block cache.  A frame loop that builds a scene per frame (bench.py's end-to-end step, the reference's viewer) allocates and frees the
+// same film-sized blocks every frame; cudaMalloc / cudaFree of a 268 MB block cost about a millisecond each and cudaFree synchronises the
+// device.  Blocks of >= 1 MB released by a scene are kept per (device, size) and handed to the next scene that asks for exactly that size;
+// at most AMVPT_BLOCK_CACHE_MB (default 8192) are kept per process, AMVPT_BLOCK_CACHE_MB=0 switches the cache off.  Contents are stale:
+// every consumer initialises what it reads (film_clear, uploads), exactly as with cudaMalloc, which does not zero either.
+namespace {
+struct BlockCache {
+    std::mutex m; std::multimap<std::pair<int, size_t>, void *> blocks; size_t held = 0, limit;
+    BlockCache() { const char *e = getenv("AMVPT_BLOCK_CACHE_MB"); limit = (size_t) (e ? atoll(e) : 8192) << 20; }
+    ~BlockCache() { /* process exit: the driver reclaims device memory; no CUDA calls during static destruction */ }
+    void *take(int dev, size_t bytes) {
+        std::lock_guard<std::mutex> l(m); auto it = blocks.find({ dev, bytes });
+        if (it == blocks.end()) return nullptr; void *p = it->second; blocks.erase(it); held -= bytes; return p;
+    }
+    bool give(int dev, size_t bytes, void *p) {
+        std::lock_guard<std::mutex> l(m); if (bytes < (1u << 20) || held + bytes > limit) return false;
+        blocks.insert({ { dev, bytes }, p }); held += bytes; return true;
+    }
+};
+BlockCache &block_cache() { static BlockCache *c = new BlockCache(); return *c; }
+} // namespace
+
+void Scene::release_device_blocks() {
+    if (device < 0) { allocs.clear(); alloc_bytes.clear(); return; }
+    cudaSetDevice(device);
+    bool synced = false;
+    for (size_t i = 0; i < allocs.size(); ++i) {
+        const size_t bytes = i < alloc_bytes.size() ? alloc_bytes[i] : 0;
+        if (bytes >= (1u << 20)) {
+            if (!synced) { cudaDeviceSynchronize(); synced = true; }       // no kernel of this scene may still touch a block that changes hands
+            if (block_cache().give(device, bytes, allocs[i])) continue;
+        }
+        cudaFree(allocs[i]);
+    }
+    allocs.clear(); alloc_bytes.clear();
+}
 Scene::~Scene() {
-    if (device >= 0) { cudaSetDevice(device); for (void *p : allocs) cudaFree(p); if (adapt_compact) cudaFree(adapt_compact); }
+    release_device_blocks();
+    if (device >= 0 && adapt_compact) cudaFree(adapt_compact);
 }
 void *Scene::dalloc(size_t bytes) {
-    void *p = nullptr; AM_CUDA(cudaMalloc(&p, bytes ? bytes : 16)); allocs.push_back(p); return p;
+    if (!bytes) bytes = 16;
+    void *p = device >= 0 ? block_cache().take(device, bytes) : nullptr;
+    if (!p) {
+        cudaError_t e = cudaMalloc(&p, bytes);
+        if (e != cudaSuccess && device >= 0) {          // out of memory with blocks parked in the cache: give them back and retry once
+            cudaGetLastError();
+            for (;;) { void *q = nullptr; { std::lock_guard<std::mutex> l(block_cache().m); auto &b = block_cache().blocks; if (b.empty()) break; q = b.begin()->second; block_cache().held -= b.begin()->first.second; b.erase(b.begin()); } cudaFree(q); }
+            e = cudaMalloc(&p, bytes);
+        }
+        AM_CUDA(e);
+    }
+    allocs.push_back(p); alloc_bytes.push_back(bytes); return p;
 }
 int Scene::add_bsdf(const DBsdf &b_, const std::string &id) {
     DBsdf b = b_; bsdf_prepare(b); bsdfs.push_back(b); bsdf_ids.push_back(id); committed = false;
@@ -281,8 +332,8 @@ void Scene::commit(int dev) {
     if ((unsigned long long) film_w * film_h * 4ull >= (1ull << 32)) AM_THROW("commit: film index exceeds 32 bits");
     if (device >= 0 && device != dev) AM_THROW("commit: scene already lives on device %d", device);
     AM_CUDA(cudaSetDevice(dev)); device = dev;
-    for (void *p : allocs) cudaFree(p);
-    allocs.clear(); wf = WfPool{}; reuse_buf = nullptr; reuse_cap = 0; split_buf = nullptr; split_cap = 0; srgb8 = nullptr;
+    release_device_blocks();
+    wf = WfPool{}; reuse_buf = nullptr; reuse_cap = 0; split_buf = nullptr; split_cap = 0; srgb8 = nullptr;
     cudaDeviceProp prop; AM_CUDA(cudaGetDeviceProperties(&prop, dev)); sm_count = prop.multiProcessorCount;
     prepare_host();
     n_nodes = (uint32_t) (bvh.nodes.size() / AM_NODE_F4); n_tris = (uint32_t) (bvh.tris.size() / 3);

@@ -19,3 +19,6 @@ timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --c
 REPS=1 timeout 600 ncu --metrics gpu__time_duration.sum,smsp__thread_inst_executed_per_inst_executed.ratio,dram__bytes_read.sum --clock-control none -c 700 --csv \
     --log-file $OUT/launches_hfield16_pass.csv python scripts/one_render.py hfield16 auto 16 > $OUT/ncu_launches_hf.log 2>&1; echo "ncu launch list hf rc=$?" | tee -a $OUT/rc.txt
 ls -la $OUT
+timeout 900 python -m pytest tests -m gpu -x -q > $OUT/pytest_gpu.log 2>&1; echo "pytest rc=$?" | tee -a $OUT/rc.txt; tail -n 3 $OUT/pytest_gpu.log
+( time timeout 900 python bench.py ) > $OUT/bench_default.json 2> $OUT/bench_default.err; echo "bench default rc=$?" | tee -a $OUT/rc.txt; tail -n 4 $OUT/bench_default.err
+( time timeout 600 python bench.py --impl reference ) > $OUT/bench_reference.json 2> $OUT/bench_reference.err; echo "bench reference rc=$?" | tee -a $OUT/rc.txt; tail -n 4 $OUT/bench_reference.err
