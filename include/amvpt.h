@@ -249,6 +249,9 @@ int amvpt_membench(int device, int kind, uint64_t bytes, uint32_t iters, double 
 int amvpt_bvh_validate(amvpt_scene *s, uint32_t *max_depth, uint32_t *n_leaves);
 /* the same for the compressed 4-wide tree of the wavefront trace stage: every triangle inside the decoded box of every slot above it;
  * *n_nodes = 0 when the scene has no such tree (a single leaf) */
+/* FNV-1a over the flattened tree as it is uploaded (nodes | leaf-ordered triangles | compressed nodes): the build is deterministic and does not
+ * depend on AMVPT_BVH_THREADS (tests/test_cpu_host.py) */
+int amvpt_bvh_checksum(amvpt_scene *s, uint64_t *checksum);
 int amvpt_bvh_q4_validate(amvpt_scene *s, uint32_t *n_nodes, uint32_t *max_depth, uint32_t *n_leaves);
 
 #ifdef __cplusplus

@@ -79,7 +79,7 @@ EXPORTS = ["amvpt_last_error", "amvpt_device_count", "amvpt_scene_create", "amvp
            "amvpt_scene_get_bsdf", "amvpt_scene_get_integrator", "amvpt_render", "amvpt_shard_tiles", "amvpt_view_tiles", "amvpt_adaptive_alloc", "amvpt_comm_unique_id", "amvpt_comm_init", "amvpt_comm_destroy", "amvpt_film_gather", "amvpt_comm_allreduce_sum", "amvpt_gather_tiles", "amvpt_film_develop_pinned", "amvpt_cancel", "amvpt_film_clear",
            "amvpt_film_raw", "amvpt_film_develop", "amvpt_film_develop_device", "amvpt_film_device_ptr", "amvpt_film_add_host",
            "amvpt_trace_lanes", "amvpt_trace_lanes_multi", "amvpt_intersect", "amvpt_intersect_static", "amvpt_bsdf_eval_pdf_sample", "amvpt_math1", "amvpt_sampler_stream",
-           "amvpt_bvh_validate", "amvpt_bvh_q4_validate", "amvpt_membench", "amvpt_film_write_pfm", "amvpt_film_write_exr", "amvpt_f32_to_f16", "amvpt_film_to_srgb8", "amvpt_interlace", "amvpt_display_last_ms"]
+           "amvpt_bvh_validate", "amvpt_bvh_checksum", "amvpt_bvh_q4_validate", "amvpt_membench", "amvpt_film_write_pfm", "amvpt_film_write_exr", "amvpt_f32_to_f16", "amvpt_film_to_srgb8", "amvpt_interlace", "amvpt_display_last_ms"]
 lib.amvpt_scene_destroy.restype = None
 lib.amvpt_scene_destroy.argtypes = [C.c_void_p]
 lib.amvpt_comm_destroy.restype = None
@@ -307,6 +307,9 @@ class Scene:
         d, n = C.c_uint32(), C.c_uint32()
         _chk(lib.amvpt_bvh_validate(self._h, C.byref(d), C.byref(n)))
         return d.value, n.value
+
+    def bvh_checksum(self):
+        x = C.c_uint64(); _chk(lib.amvpt_bvh_checksum(self._h, C.byref(x))); return x.value
 
     def bvh_q4_validate(self):
         n, d, l = C.c_uint32(), C.c_uint32(), C.c_uint32()

@@ -10,6 +10,11 @@
 #include <cmath>
 #include <cstdlib>
 #include <functional>
+#include <chrono>
+#include <cstdio>
+#include <atomic>
+#include <thread>
+#include <cstring>
 
 namespace amvpt {
 
@@ -33,7 +38,7 @@ static int kMaxLeaf = 4; static float kCostTri = 1.5f, kCostNode = 1.f;
 
 struct Builder {
     std::vector<Prim> &prims; std::vector<TNode> nodes;
-    explicit Builder(std::vector<Prim> &p) : prims(p) { nodes.reserve(2 * p.size() + 2); }
+    explicit Builder(std::vector<Prim> &p, size_t expect = ~(size_t) 0) : prims(p) { nodes.reserve(2 * std::min(expect, p.size()) + 2); }
     int32_t build(uint32_t begin, uint32_t end, int depth) {
         TNode n; Box cb;
         for (uint32_t i = begin; i < end; ++i) { n.b.grow(prims[i].b); cb.grow(prims[i].c); }
@@ -69,16 +74,67 @@ struct Builder {
             std::nth_element(prims.begin() + begin, prims.begin() + mid, prims.begin() + end,
                              [axis](const Prim &a, const Prim &b) { return a.c[axis] < b.c[axis] || (a.c[axis] == b.c[axis] && a.prim < b.prim); });
         }
+        if (stop_after_split) { did_split = true; split_mid = mid; return self; }      // build_parallel: one step only
         int32_t l = build(begin, mid, depth + 1), r = build(mid, end, depth + 1);
         nodes[self].left = l; nodes[self].right = r;
         return self;
     }
     int depth_of(int32_t n) const { return nodes[n].left < 0 ? 1 : 1 + std::max(depth_of(nodes[n].left), depth_of(nodes[n].right)); }
+
+    // The same tree, built on several host threads.  The top of the tree is built here down to ranges of <= grain primitives, whose
+    // subtrees are deferred; the deferred ranges are disjoint slices of `prims`, so each is built independently by the very same
+    // recursion (private node vector); finally everything is emitted in the pre-order the sequential recursion produces (node, whole
+    // left subtree, whole right subtree).  Node numbering, leaf order and boxes are therefore identical to build(0, n, 0) -- tested.
+    struct Deferred { uint32_t begin, end; int depth; std::vector<TNode> nodes; };
+    void build_parallel(uint32_t n, unsigned n_threads) {
+        const uint32_t grain = std::max<uint32_t>(n / (8 * n_threads), 4096);
+        std::vector<Deferred> tasks;
+        // top tree: children < 0 that are not leaves are encoded as -(2 + task index) while it is being built
+        std::vector<TNode> top; std::vector<int32_t> top_left, top_right;
+        std::function<int32_t(uint32_t, uint32_t, int)> top_build = [&](uint32_t begin, uint32_t end, int depth) -> int32_t {
+            if (end - begin <= grain) { tasks.push_back({ begin, end, depth, {} }); return -(2 + (int32_t) tasks.size() - 1); }
+            // one step of build(): reuse it on a scratch builder restricted to this node by temporarily limiting the recursion
+            Builder one(prims, 1); one.stop_after_split = true;
+            one.build(begin, end, depth);
+            TNode nd = one.nodes[0]; const uint32_t mid = one.split_mid;
+            int32_t self = (int32_t) top.size(); top.push_back(nd); top_left.push_back(-1); top_right.push_back(-1);
+            if (!one.did_split) return self;                 // became a leaf
+            int32_t l = top_build(begin, mid, depth + 1), r = top_build(mid, end, depth + 1);
+            top_left[self] = l; top_right[self] = r;
+            return self;
+        };
+        auto t0 = std::chrono::steady_clock::now();
+        int32_t root = top_build(0, n, 0);
+        auto t1 = std::chrono::steady_clock::now();
+        std::atomic<size_t> next{ 0 };
+        auto worker = [&]() { for (size_t i; (i = next.fetch_add(1)) < tasks.size();) { Builder b(prims, tasks[i].end - tasks[i].begin); b.build(tasks[i].begin, tasks[i].end, tasks[i].depth); tasks[i].nodes.swap(b.nodes); } };
+        std::vector<std::thread> pool; for (unsigned t = 1; t < n_threads; ++t) pool.emplace_back(worker);
+        worker(); for (auto &t : pool) t.join();
+        auto t2 = std::chrono::steady_clock::now();
+        nodes.clear();
+        std::function<int32_t(int32_t)> emit = [&](int32_t ref) -> int32_t {
+            const int32_t base = (int32_t) nodes.size();
+            if (ref <= -2) {                                   // a deferred subtree: append with its indices shifted
+                const std::vector<TNode> &sub = tasks[(size_t) (-(ref + 2))].nodes;
+                for (const TNode &t : sub) { TNode c = t; if (c.left >= 0) { c.left += base; c.right += base; } nodes.push_back(c); }
+                return base;
+            }
+            nodes.push_back(top[ref]);
+            if (top_left[ref] != -1) { const int32_t l = emit(top_left[ref]), r = emit(top_right[ref]); nodes[base].left = l; nodes[base].right = r; }
+            return base;
+        };
+        emit(root);
+        if (getenv("AMVPT_BVH_TIMING")) fprintf(stderr, "[bvh] parallel build: top %.1f ms (%zu subtrees), subtrees on %u threads %.1f ms, merge %.1f ms\n", std::chrono::duration<double, std::milli>(t1 - t0).count(), tasks.size(), n_threads,
+                                               std::chrono::duration<double, std::milli>(t2 - t1).count(), std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t2).count());
+    }
+    bool stop_after_split = false, did_split = false; uint32_t split_mid = 0;
 };
 } // namespace
 
 void build_bvh(const Scene &s, float scene_scale, BvhOut &out) {
     uint32_t np = s.nprims();
+    const bool timing = getenv("AMVPT_BVH_TIMING") != nullptr; auto t_last = std::chrono::steady_clock::now();
+    auto lap = [&](const char *what) { if (!timing) return; auto t = std::chrono::steady_clock::now(); fprintf(stderr, "[bvh] %-22s %.1f ms\n", what, std::chrono::duration<double, std::milli>(t - t_last).count()); t_last = t; };
     std::vector<Prim> prims(np);
     std::vector<uint32_t> prim_mesh(np);
     // Padding: Moeller-Trumbore decides with a positional error of a few 2^-24 * (|origin| + |vertex| + t); boxes get
@@ -99,11 +155,16 @@ void build_bvh(const Scene &s, float scene_scale, BvhOut &out) {
         }
     }
     kMaxLeaf = std::min(std::max(env_int("AMVPT_MAX_LEAF", 4), 1), 7); kCostTri = env_float("AMVPT_SAH_CT", 1.5f);
+    lap("primitive boxes");
     Builder bl(prims);
-    if (np) bl.build(0, np, 0);
+    // AMVPT_BVH_THREADS: host threads of the build (default: up to 16 of the machine's; 1 = the plain recursion); the tree does not depend on it
+    unsigned n_threads = (unsigned) std::max(1, env_int("AMVPT_BVH_THREADS", (int) std::min(16u, std::max(1u, std::thread::hardware_concurrency()))));
+    if (np >= 65536 && n_threads > 1) bl.build_parallel(np, n_threads);
+    else if (np) bl.build(0, np, 0);
     out.depth = np ? (uint32_t) bl.depth_of(0) : 1u;
     if (AM_BVH_WIDTH == 2 && out.depth > AM_STACK_SIZE - 2) AM_THROW("BVH depth %u exceeds the traversal stack", out.depth);
 
+    lap("tree");
     // triangles in leaf order
     out.tris.resize(3 * (size_t) np); out.prim_to_tri.resize(np);
     bool any_nrm = false; for (auto &m : s.meshes) any_nrm |= !m.nrm.empty();
@@ -119,6 +180,7 @@ void build_bvh(const Scene &s, float scene_scale, BvhOut &out) {
         }
     }
     auto leaf_code = [&](const TNode &n) -> int32_t { return (int32_t) ~((n.first << 3) | n.count); };
+    lap("leaf-order triangles");
     // ---- compressed 4-wide tree over the same leaves (DScene::nodes_q4, the wavefront trace stage): the binary tree is collapsed (a
     // node's two children, then repeatedly the inner child with the largest surface is replaced by its own two children until four
     // slots are used), and the child boxes are quantised to 8 bits per plane on a power-of-two grid anchored at the node's own box
@@ -228,6 +290,7 @@ void build_bvh(const Scene &s, float scene_scale, BvhOut &out) {
         float rf[4]; memcpy(rf, ref, 16); o[6] = make_float4(rf[0], rf[1], rf[2], rf[3]);
     }
 #else
+    lap("compressed wide tree");
     // flatten: inner nodes numbered in depth-first order, each holding its two children's boxes
     auto child_ref = [&](const std::vector<int32_t> &inner_id, int32_t c) -> int32_t {
         const TNode &n = bl.nodes[c];

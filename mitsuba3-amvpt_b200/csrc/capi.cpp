@@ -485,6 +485,14 @@ int amvpt_membench(int device, int kind, uint64_t bytes, uint32_t iters, double 
         if (v < 0.0) AM_THROW("CUDA error: membench failed (%s)", cudaGetErrorString(cudaGetLastError()));
         *gb_per_s = v; return AMVPT_OK; });
 }
+int amvpt_bvh_checksum(amvpt_scene *h, uint64_t *checksum) {
+    return guard([&] { NEED(h); NEED(checksum); Scene &s = *h->s; s.prepare_host();
+        uint64_t x = 1469598103934665603ull;
+        auto eat = [&](const void *p, size_t n) { const unsigned char *b = (const unsigned char *) p; for (size_t i = 0; i < n; ++i) { x ^= b[i]; x *= 1099511628211ull; } };
+        eat(s.bvh.nodes.data(), s.bvh.nodes.size() * sizeof(float4)); eat(s.bvh.tris.data(), s.bvh.tris.size() * sizeof(float4));
+        eat(s.bvh.nodes_q4.data(), s.bvh.nodes_q4.size() * sizeof(uint4)); eat(s.bvh.prim_to_tri.data(), s.bvh.prim_to_tri.size() * 4);
+        *checksum = x; return AMVPT_OK; });
+}
 int amvpt_bvh_q4_validate(amvpt_scene *h, uint32_t *n_nodes, uint32_t *max_depth, uint32_t *n_leaves) {
     return guard([&] { NEED(h); Scene &s = *h->s; s.prepare_host();
         const std::vector<uint4> &q = s.bvh.nodes_q4;

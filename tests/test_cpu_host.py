@@ -68,6 +68,18 @@ def test_bvh_structure(pkg, scenes):
     assert s.bvh_validate()[1] >= 3 and s.info()["n_prims"] == 11
 
 
+def test_bvh_build_does_not_depend_on_the_thread_count(pkg, scenes, monkeypatch):
+    """The host build runs on several threads above 65 536 primitives (top of the tree sequentially, disjoint subtrees in parallel, emitted in
+    the pre-order of the plain recursion): node numbering, leaf order and the compressed tree must be identical whatever the thread count."""
+    sums = []
+    for threads in ("1", "3", "8"):
+        monkeypatch.setenv("AMVPT_BVH_THREADS", threads)
+        s = scenes.build(scenes.height_field(n=200, grid_x=2, grid_y=2, view_res=8), commit=False)       # 80 000 triangles
+        assert s.info()["n_prims"] >= 65536
+        sums.append(s.bvh_checksum()); s.bvh_validate()
+    assert sums[0] == sums[1] == sums[2], sums
+
+
 def test_error_behaviour(pkg, scenes):
     s = pkg.Scene(); b = s.add_bsdf(type="diffuse")
     with pytest.raises(pkg.AmvptError, match="out of range"):
