@@ -240,25 +240,51 @@ template <bool ANY, bool Q4 = false> AM_D Hit intersect(const DScene &s, const R
     int32_t node = 0;
     stack[sp++] = AM_TRAVERSAL_DONE;
     for (;;) {
+#if AM_SPECULATIVE
+        // speculative descent (Aila & Laine): the first leaf a lane finds is postponed and the lane keeps walking until it holds a second
+        // leaf or its ray is done, so that the warp alternates half as often between the node loop and the leaf loop.  The postponed
+        // leaf's hit cannot prune the extra steps, so a few more nodes are visited; the reported hit is the same (closest hit and tie
+        // rule do not depend on the order in which leaves are tested; for ANY only occlusion is defined).
+        int32_t pend = AM_TRAVERSAL_DONE;
+        for (;;) {
+            while (node >= 0) {
+                if (n_nodes) (*n_nodes)++;
+                node = Q4 ? node_step_q4(s, sr, best, node, stack, sp) : node_step(s, sr, best, node, stack, sp);
+            }
+            if (node == AM_TRAVERSAL_DONE || pend != AM_TRAVERSAL_DONE) break;
+            pend = node; node = stack[--sp];
+        }
+        if (pend == AM_TRAVERSAL_DONE) break;                       // no leaf at all: the ray is done
+        for (int which = 0; which < 2; ++which) {
+            const int32_t leaf = which == 0 ? pend : node;
+            if (leaf == AM_TRAVERSAL_DONE) break;
+            uint32_t code = ~(uint32_t) leaf, first = code >> 3, count = code & 7u;
+#else
         while (node >= 0) {
             if (n_nodes) (*n_nodes)++;
             node = Q4 ? node_step_q4(s, sr, best, node, stack, sp) : node_step(s, sr, best, node, stack, sp);
         }
         if (node == AM_TRAVERSAL_DONE) break;
-        uint32_t code = ~(uint32_t) node, first = code >> 3, count = code & 7u;
-        for (uint32_t i = 0; i < count; ++i) {
-            const float4 *tp = s.tris + 3 * (size_t) (first + i);
-            float4 a = ldg4(tp), b = ldg4(tp + 1), c = ldg4(tp + 2);
-            if (n_tris) (*n_tris)++;
-            float t, u, v;
-            if (moeller_trumbore(ray, v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), v3(c.x, c.y, c.z), &t, &u, &v)) {
-                uint32_t prim = __float_as_uint(a.w);
-                if (ANY) { h.t = t; h.u = u; h.v = v; h.tri = first + i; return h; }
-                if (h.tri == AM_NO_HIT || t < h.t || (t == h.t && prim > best_prim)) {
-                    h.t = t; h.u = u; h.v = v; h.tri = first + i; best_prim = prim; best = t;
+        {
+            uint32_t code = ~(uint32_t) node, first = code >> 3, count = code & 7u;
+#endif
+            for (uint32_t i = 0; i < count; ++i) {
+                const float4 *tp = s.tris + 3 * (size_t) (first + i);
+                float4 a = ldg4(tp), b = ldg4(tp + 1), c = ldg4(tp + 2);
+                if (n_tris) (*n_tris)++;
+                float t, u, v;
+                if (moeller_trumbore(ray, v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), v3(c.x, c.y, c.z), &t, &u, &v)) {
+                    uint32_t prim = __float_as_uint(a.w);
+                    if (ANY) { h.t = t; h.u = u; h.v = v; h.tri = first + i; return h; }
+                    if (h.tri == AM_NO_HIT || t < h.t || (t == h.t && prim > best_prim)) {
+                        h.t = t; h.u = u; h.v = v; h.tri = first + i; best_prim = prim; best = t;
+                    }
                 }
             }
         }
+#if AM_SPECULATIVE
+        if (node == AM_TRAVERSAL_DONE) break;
+#endif
         node = stack[--sp];
     }
     return h;

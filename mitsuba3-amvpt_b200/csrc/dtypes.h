@@ -9,6 +9,9 @@
 #ifndef AM_FFMA2
 #define AM_FFMA2 0         /* 1: binary-tree nodes hold (lo.x, lo.y, hi.x, hi.y) and the slab test uses Blackwell's packed fma.rn.f32x2 (FFMA2) */
 #endif
+#ifndef AM_SPECULATIVE
+#define AM_SPECULATIVE 0   /* 1: intersect() postpones the first leaf a lane finds and keeps descending until it holds two (dscene.cuh) */
+#endif
 #ifndef AM_PREFETCH_FAR
 #define AM_PREFETCH_FAR 0  /* 1: prefetch.global.L1 of the postponed child's node record when both children are hit */
 #endif
