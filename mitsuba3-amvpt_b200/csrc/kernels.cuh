@@ -33,12 +33,27 @@ struct LaneTaps {
 enum Counter { CTR_TICKET = 0, CTR_CLOSEST = 1, CTR_SHADOW = 2, CTR_NODES = 3, CTR_TRIS = 4, CTR_VERTICES = 5, CTR_COUNT = 8 };
 
 // Path-slot pool of the wavefront scheduler (wavefront.cu): structure of arrays, n_slots entries each.
+// Path-state pool of the wavefront scheduler.  The 16-byte fields of one slot are grouped into three 64-byte records so that the shade stages,
+// which visit slots in queue order (scattered: one queue per BSDF plugin type), touch whole 32-byte sectors instead of half-used ones:
+//   record A: ro, rd, tp, pp   (the path's next ray and carry state: read and rewritten by every shade)
+//   record B: res, rng, hit, - (radiance so far + pixel, sampler, last closest hit)
+//   record C: so, sd, sT, sV   (pending next-event shadow ray and its parked contribution)
+// The trace and regen stages walk slots in order, so their accesses stay coalesced either way.  -DAM_WF_AOS=0 restores one array per field.
+#ifndef AM_WF_AOS
+#define AM_WF_AOS 1
+#endif
+template <class T, int OFF> struct PoolField {
+    T *base;
+#ifdef __CUDACC__
+    __device__ __forceinline__ T &operator[](size_t i) const { return AM_WF_AOS ? base[4 * i + OFF] : base[i]; }
+#endif
+};
 struct WfPool {
-    float4 *ro, *rd;        // next closest-hit ray: (o, maxt), (d, eta)
-    float4 *tp, *res, *pp;  // (throughput, prev_bsdf_pdf), (result, bits pixel), (prev_p, bits depth)
-    uint4 *rng;             // PCG32 state, inc
-    float4 *hit;            // (t, u, v, bits tri) of the last closest-hit ray
-    float4 *so, *sd, *sT, *sV;   // pending next-event shadow ray and the parked operands of result = fmadd(sT, sV, result)
+    PoolField<float4, 0> ro; PoolField<float4, 1> rd;        // next closest-hit ray: (o, maxt), (d, eta)
+    PoolField<float4, 2> tp; PoolField<float4, 0> res; PoolField<float4, 3> pp;  // (throughput, prev_bsdf_pdf), (result, bits pixel), (prev_p, bits depth)
+    PoolField<uint4, 1> rng;             // PCG32 state, inc
+    PoolField<float4, 2> hit;            // (t, u, v, bits tri) of the last closest-hit ray
+    PoolField<float4, 0> so; PoolField<float4, 1> sd; PoolField<float4, 2> sT; PoolField<float4, 3> sV;   // pending next-event shadow ray and the parked operands of result = fmadd(sT, sV, result)
     uint32_t *flags;        // WF_* bits
     float2 *spos;           // sample position on the film (read by the splat when the reconstruction filter is not the box)
     uint32_t *queue;        // [6][n_slots] slot indices per BSDF plugin type

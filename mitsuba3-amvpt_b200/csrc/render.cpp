@@ -118,9 +118,15 @@ void render(Scene &s, const RenderOptions &opt) {
                 uint32_t n = getenv("AMVPT_WF_POOL") ? (uint32_t) atoi(getenv("AMVPT_WF_POOL")) : (1u << 22);
                 n = std::max(128u, (n + 127u) / 128u * 128u);
                 WfPool &w = s.wf; w.n_slots = n;
-                float4 **f4s[] = { &w.ro, &w.rd, &w.tp, &w.res, &w.pp, &w.hit, &w.so, &w.sd, &w.sT, &w.sV };
-                for (float4 **a : f4s) *a = (float4 *) s.dalloc(sizeof(float4) * n);
-                w.rng = (uint4 *) s.dalloc(sizeof(uint4) * n); w.flags = (uint32_t *) s.dalloc(sizeof(uint32_t) * n); w.spos = (float2 *) s.dalloc(sizeof(float2) * n);
+                if (AM_WF_AOS) {       // three 64-byte records per slot (kernels.cuh)
+                    float4 *A = (float4 *) s.dalloc(sizeof(float4) * 4 * (size_t) n), *B = (float4 *) s.dalloc(sizeof(float4) * 4 * (size_t) n), *Cc = (float4 *) s.dalloc(sizeof(float4) * 4 * (size_t) n);
+                    w.ro.base = w.rd.base = w.tp.base = w.pp.base = A; w.res.base = w.hit.base = B; w.rng.base = (uint4 *) B; w.so.base = w.sd.base = w.sT.base = w.sV.base = Cc;
+                } else {
+                    float4 **f4s[] = { &w.ro.base, &w.rd.base, &w.tp.base, &w.res.base, &w.pp.base, &w.hit.base, &w.so.base, &w.sd.base, &w.sT.base, &w.sV.base };
+                    for (float4 **a : f4s) *a = (float4 *) s.dalloc(sizeof(float4) * n);
+                    w.rng.base = (uint4 *) s.dalloc(sizeof(uint4) * n);
+                }
+                w.flags = (uint32_t *) s.dalloc(sizeof(uint32_t) * n); w.spos = (float2 *) s.dalloc(sizeof(float2) * n);
                 w.queue = (uint32_t *) s.dalloc(sizeof(uint32_t) * 7 * (size_t) n); w.qcount = (uint32_t *) s.dalloc(sizeof(uint32_t) * 8);      // six BSDF-type queues + the escaped-ray queue
                 w.live = (uint32_t *) s.dalloc(sizeof(uint32_t) * 64);
                 w.sort_hist = w.sort_key = w.sort_rank = w.order = nullptr;

@@ -141,7 +141,7 @@ void bsdf_prepare(DBsdf &b) {
 // ---------------------------------------------------------------- Scene
 // Device block cache.  A frame loop that builds a scene per frame (bench.py's end-to-end step, the reference's viewer) allocates and frees the
 // same film-sized blocks every frame; cudaMalloc / cudaFree of a 268 MB block cost about a millisecond each and cudaFree synchronises the
-// device.  Blocks of >= 1 MB released by a scene are kept per (device, size) and handed to the next scene that asks for exactly that size;
+// device -- and a commit makes about twenty small allocations besides.  Blocks released by a scene are kept per (device, size) and handed to the next scene that asks for exactly that size;
 // at most AMVPT_BLOCK_CACHE_MB (default 8192) are kept per process, AMVPT_BLOCK_CACHE_MB=0 switches the cache off.  Contents are stale:
 // every consumer initialises what it reads (film_clear, uploads), exactly as with cudaMalloc, which does not zero either.
 namespace {
@@ -154,7 +154,7 @@ struct BlockCache {
         if (it == blocks.end()) return nullptr; void *p = it->second; blocks.erase(it); held -= bytes; return p;
     }
     bool give(int dev, size_t bytes, void *p) {
-        std::lock_guard<std::mutex> l(m); if (bytes < (1u << 20) || held + bytes > limit) return false;
+        std::lock_guard<std::mutex> l(m); if (held + bytes > limit || blocks.size() >= 65536) return false;
         blocks.insert({ { dev, bytes }, p }); held += bytes; return true;
     }
 };
@@ -167,7 +167,7 @@ void Scene::release_device_blocks() {
     bool synced = false;
     for (size_t i = 0; i < allocs.size(); ++i) {
         const size_t bytes = i < alloc_bytes.size() ? alloc_bytes[i] : 0;
-        if (bytes >= (1u << 20)) {
+        if (bytes && block_cache().limit) {
             if (!synced) { cudaDeviceSynchronize(); synced = true; }       // no kernel of this scene may still touch a block that changes hands
             if (block_cache().give(device, bytes, allocs[i])) continue;
         }
