@@ -6,6 +6,10 @@
 #include <cstdlib>
 #include <map>
 #include <mutex>
+#include <atomic>
+#include <thread>
+#include <tuple>
+#include <cstring>
 
 namespace amvpt {
 
@@ -127,15 +131,32 @@ void bsdf_prepare(DBsdf &b) {
     float d_mean = (b.reflectance[0] + b.reflectance[1] + b.reflectance[2]) / 3.f;
     float s_mean = (b.spec_refl[0] + b.spec_refl[1] + b.spec_refl[2]) / 3.f;
     b.spec_sampling_weight = s_mean / (d_mean + s_mean);
+    // The two tables cost 128 quadratures of 32 x 32 nodes (0.4 s on one core) and depend only on (distribution, alpha, eta): they are computed
+    // on several threads (each entry independently, the sum taken in index order afterwards: same bits) and kept per process, so that a frame
+    // loop that rebuilds its scene does not recompute them.
+    struct Key { int distr; uint32_t alpha, eta; bool operator<(const Key &o) const { return std::tie(distr, alpha, eta) < std::tie(o.distr, o.alpha, o.eta); } };
+    struct Val { float ext[AM_ROUGH_TRANSMITTANCE_RES]; float internal; };
+    static std::mutex cache_mutex; static std::map<Key, Val> cache;
+    Key key{ (int) b.distr, 0u, 0u }; memcpy(&key.alpha, &b.alpha_u, 4); memcpy(&key.eta, &b.ior_eta, 4);
+    { std::lock_guard<std::mutex> l(cache_mutex); auto it = cache.find(key);
+      if (it != cache.end()) { memcpy(b.ext_transmittance, it->second.ext, sizeof(it->second.ext)); b.internal_reflectance = it->second.internal; return; } }
     Microfacet d(b.distr, b.alpha_u, b.alpha_u);
-    float acc = 0.f;
-    for (int i = 0; i < AM_ROUGH_TRANSMITTANCE_RES; ++i) {
+    float term[AM_ROUGH_TRANSMITTANCE_RES];
+    auto entry = [&](int i) {
         float mu = max_(1e-6f, fmadd((float) i, 1.f / (float) (AM_ROUGH_TRANSMITTANCE_RES - 1), 0.f));
         V3 wi = v3(fsqrt(1.f - mu * mu), 0.f, mu);
         b.ext_transmittance[i] = mf_quadrature(d, wi, b.ior_eta, true);
-        acc += mf_quadrature(d, wi, 1.f / b.ior_eta, false) * wi.z;
-    }
+        term[i] = mf_quadrature(d, wi, 1.f / b.ior_eta, false) * wi.z;
+    };
+    const unsigned n_threads = std::min(8u, std::max(1u, std::thread::hardware_concurrency()));
+    std::atomic<int> next{ 0 };
+    auto worker = [&]() { for (int i; (i = next.fetch_add(1)) < AM_ROUGH_TRANSMITTANCE_RES;) entry(i); };
+    std::vector<std::thread> pool; for (unsigned t = 1; t < n_threads; ++t) pool.emplace_back(worker);
+    worker(); for (auto &t : pool) t.join();
+    float acc = 0.f;
+    for (int i = 0; i < AM_ROUGH_TRANSMITTANCE_RES; ++i) acc += term[i];
     b.internal_reflectance = acc / (float) AM_ROUGH_TRANSMITTANCE_RES * 2.f;
+    { Val v; memcpy(v.ext, b.ext_transmittance, sizeof(v.ext)); v.internal = b.internal_reflectance; std::lock_guard<std::mutex> l(cache_mutex); cache[key] = v; }
 }
 
 // ---------------------------------------------------------------- Scene
