@@ -28,6 +28,16 @@ struct Box {
 struct Prim { Box b; float c[3]; uint32_t prim; };
 struct TNode { Box b; int32_t left = -1, right = -1; uint32_t first = 0, count = 0; };
 
+// index-parallel loop over [0, n): the bodies below write disjoint elements, so the result does not depend on the thread count
+static unsigned g_threads = 1;
+template <class F> void parallel_for(size_t n, F body) {
+    const unsigned nt = (unsigned) std::min<size_t>(g_threads, n / 16384 + 1);
+    if (nt <= 1) { for (size_t i = 0; i < n; ++i) body(i); return; }
+    std::atomic<size_t> next{ 0 }; const size_t chunk = std::max<size_t>(4096, n / (8 * nt));
+    auto worker = [&]() { for (size_t b; (b = next.fetch_add(chunk)) < n;) for (size_t i = b, e = std::min(n, b + chunk); i < e; ++i) body(i); };
+    std::vector<std::thread> pool; for (unsigned t = 1; t < nt; ++t) pool.emplace_back(worker);
+    worker(); for (auto &t : pool) t.join();
+}
 const int kBins = 16, kSahDepth = 40;
 // Leaf policy: at most kMaxLeaf triangles (<= 7 by the leaf encoding); a range that already fits becomes a leaf unless
 // the best SAH split is cheaper (cost of one node step kCostNode vs. one triangle test kCostTri, measured on sm_100a:
@@ -141,9 +151,11 @@ void build_bvh(const Scene &s, float scene_scale, BvhOut &out) {
     // an absolute margin tied to the scene scale plus a relative one, far above that error and far below feature size.
     const float pad_abs = 2e-6f * scene_scale + 1e-30f;
     uint32_t g = 0;
+    g_threads = (unsigned) std::max(1, env_int("AMVPT_BVH_THREADS", (int) std::min(16u, std::max(1u, std::thread::hardware_concurrency()))));
     for (size_t mi = 0; mi < s.meshes.size(); ++mi) {
-        const HMesh &m = s.meshes[mi];
-        for (uint32_t f = 0; f < m.nfaces(); ++f, ++g) {
+        const HMesh &m = s.meshes[mi]; const uint32_t g0 = g; g += m.nfaces();
+        parallel_for(m.nfaces(), [&](size_t f) {
+            const uint32_t g = g0 + (uint32_t) f;
             Prim &p = prims[g]; p.prim = g; prim_mesh[g] = (uint32_t) mi;
             Box b; for (int k = 0; k < 3; ++k) b.grow(&m.pos[3 * m.faces[3 * f + k]]);
             for (int a = 0; a < 3; ++a) {
@@ -152,13 +164,13 @@ void build_bvh(const Scene &s, float scene_scale, BvhOut &out) {
                 b.lo[a] -= pad; b.hi[a] += pad;
             }
             p.b = b;
-        }
+        });
     }
     kMaxLeaf = std::min(std::max(env_int("AMVPT_MAX_LEAF", 4), 1), 7); kCostTri = env_float("AMVPT_SAH_CT", 1.5f);
     lap("primitive boxes");
     Builder bl(prims);
     // AMVPT_BVH_THREADS: host threads of the build (default: up to 16 of the machine's; 1 = the plain recursion); the tree does not depend on it
-    unsigned n_threads = (unsigned) std::max(1, env_int("AMVPT_BVH_THREADS", (int) std::min(16u, std::max(1u, std::thread::hardware_concurrency()))));
+    unsigned n_threads = g_threads;
     if (np >= 65536 && n_threads > 1) bl.build_parallel(np, n_threads);
     else if (np) bl.build(0, np, 0);
     out.depth = np ? (uint32_t) bl.depth_of(0) : 1u;
@@ -169,16 +181,16 @@ void build_bvh(const Scene &s, float scene_scale, BvhOut &out) {
     out.tris.resize(3 * (size_t) np); out.prim_to_tri.resize(np);
     bool any_nrm = false; for (auto &m : s.meshes) any_nrm |= !m.nrm.empty();
     out.tri_nrm.assign(any_nrm ? 3 * (size_t) np : 0, make_float4(0.f, 0.f, 0.f, 0.f));
-    for (uint32_t i = 0; i < np; ++i) {
+    parallel_for(np, [&](size_t i) {
         uint32_t prim = prims[i].prim, mi = prim_mesh[prim]; const HMesh &m = s.meshes[mi]; uint32_t f = prim - m.prim_offset;
-        out.prim_to_tri[prim] = i;
+        out.prim_to_tri[prim] = (uint32_t) i;
         for (int k = 0; k < 3; ++k) {
             const float *p = &m.pos[3 * m.faces[3 * f + k]];
             uint32_t w = k == 0 ? prim : (k == 1 ? mi : (uint32_t) s.bsdfs[m.bsdf].type); float wf; memcpy(&wf, &w, 4);   // third word: BSDF plugin type (wavefront sort key)
             out.tris[3 * (size_t) i + k] = make_float4(p[0], p[1], p[2], wf);
             if (!m.nrm.empty()) { const float *n = &m.nrm[3 * m.faces[3 * f + k]]; out.tri_nrm[3 * (size_t) i + k] = make_float4(n[0], n[1], n[2], 0.f); }
         }
-    }
+    });
     auto leaf_code = [&](const TNode &n) -> int32_t { return (int32_t) ~((n.first << 3) | n.count); };
     lap("leaf-order triangles");
     // ---- compressed 4-wide tree over the same leaves (DScene::nodes_q4, the wavefront trace stage): the binary tree is collapsed (a
@@ -206,7 +218,7 @@ void build_bvh(const Scene &s, float scene_scale, BvhOut &out) {
         build_wide(0, 0);
         if (3 * depth4 + 2 <= AM_STACK_SIZE) {
             out.depth_q4 = depth4; out.nodes_q4.assign(4 * wide.size(), make_uint4(0u, 0u, 0u, 0u));
-            for (size_t id = 0; id < wide.size(); ++id) {
+            parallel_for(wide.size(), [&](size_t id) {
                 const Wide &w = wide[id]; Box nb; for (int i = 0; i < w.n; ++i) nb.grow(bl.nodes[w.kid[i]].b);
                 uint32_t e[3], qlo[3][4], qhi[3][4]; int32_t ref[4] = { 0, 0, 0, 0 };
                 for (int a = 0; a < 3; ++a) {
@@ -239,7 +251,7 @@ void build_bvh(const Scene &s, float scene_scale, BvhOut &out) {
                 o[1] = make_uint4(pack(qlo[0]), pack(qlo[1]), pack(qlo[2]), pack(qhi[0]));
                 o[2] = make_uint4(pack(qhi[1]), pack(qhi[2]), (uint32_t) ref[0], (uint32_t) ref[1]);
                 o[3] = make_uint4((uint32_t) ref[2], (uint32_t) ref[3], 0u, 0u);
-            }
+            });
         }
     }
 #if AM_BVH_WIDTH == 4
