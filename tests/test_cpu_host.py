@@ -49,6 +49,11 @@ def test_roughplastic_tables_match_oracle(pkg, scenes, ob):
         ta, sa = s.bsdf_tables(i); tb, sb = o.bsdf_tables(i)
         assert np.array_equal(ta.view(np.uint32), tb.view(np.uint32)) and np.array_equal(sa.view(np.uint32), sb.view(np.uint32))
         assert 0 < ta.min() and ta.max() < 1 and np.all(np.diff(ta) > -1e-3)      # transmittance grows with cos(theta)
+    # the tables are computed on several threads and then kept per (distribution, alpha, eta): a second scene gets the cached copy -- same bits
+    s2 = scenes.build(desc, commit=False)
+    for i in range(2):
+        (ta, sa), (tb, sb) = s.bsdf_tables(i), s2.bsdf_tables(i)
+        assert np.array_equal(ta.view(np.uint32), tb.view(np.uint32)) and np.array_equal(sa.view(np.uint32), sb.view(np.uint32))
 
 
 def test_bvh_structure(pkg, scenes):
