@@ -20,7 +20,8 @@ m = {"workload": workload, "units_per_launch": units, "kernel_name": d["Kernel N
      "lts_bytes": (num("lts__t_sectors.sum") or 0) * 32.0 or bytes_of("lts__t_bytes.sum"),
      "l1_bytes": (num("l1tex__t_sectors_pipe_lsu_mem_global_op_ld.sum") or 0) * 32.0, "l2_hit_pct": num("lts__t_sector_hit_rate.pct"), "l1_hit_pct": num("l1tex__t_sector_hit_rate.pct"),
      "long_scoreboard": num("smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio"),
-     "warps_active_pct": num("sm__warps_active.avg.pct_of_peak_sustained_active"), "source": source}
+     "warps_active_pct": num("sm__warps_active.avg.pct_of_peak_sustained_active"), "source": source,
+     "captured": subprocess.run(["git", "-C", ROOT, "log", "-1", "--format=%cs, commit %h"], capture_output=True, text=True).stdout.strip()}
 if m["thread_inst_executed"] is None and m["lanes_per_inst"]:
     m["thread_inst_executed"] = m["inst_executed"] * m["lanes_per_inst"]
 path = os.path.join(ROOT, "profiles", "r02_ncu_metrics.json")
