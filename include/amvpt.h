@@ -218,7 +218,8 @@ int amvpt_display_last_ms(amvpt_scene *s, float *srgb8_ms, float *interlace_ms);
 int amvpt_trace_lanes(amvpt_scene *s, uint32_t seed_value, uint32_t spp_per_pass, uint32_t lane_begin, uint32_t n, int trace,
                       float *sample_pos, float *ray_o, float *ray_d, float *ray_maxt, uint32_t *view, float *radiance,
                       uint32_t *pixel, uint32_t max_hits, uint32_t *hit_prim, float *hit_t, uint64_t *stats2);
-/* any_hit: bit 0 = Scene::ray_test semantics (first accepted triangle), bit 1 = walk the compressed 4-wide tree of the wavefront trace stage */
+/* any_hit: bit 0 = Scene::ray_test semantics (first accepted triangle), bit 1 = walk the compressed 4-wide tree of the wavefront trace stage,
+ * bit 2 = no traversal counters (stats2 stays 0): scenes with at most 32 leaves then take the flat leaf list the render kernels use */
 int amvpt_intersect(amvpt_scene *s, const float *o, const float *d, const float *maxt, uint32_t n, int any_hit,
                     uint32_t *prim, float *tuv, uint64_t *stats2);
 /* amvpt_intersect without any allocation (csrc/noalloc.cu).  No counterpart in the reference; added

@@ -436,10 +436,10 @@ class Scene:
         o["stats"] = stats
         return o
 
-    def intersect(self, o, d, maxt, any_hit=False, q4=False):
+    def intersect(self, o, d, maxt, any_hit=False, q4=False, flat=False):
         o = _f32(o, (-1, 3)); d = _f32(d, (-1, 3)); maxt = _f32(maxt, (-1,)); n = len(o)
         prim = np.zeros(n, np.uint32); tuv = np.zeros((n, 3), np.float32); stats = np.zeros(2, np.uint64)
-        _chk(lib.amvpt_intersect(self._h, _p(o), _p(d), _p(maxt), C.c_uint32(n), C.c_int(int(any_hit) | (2 if q4 else 0)), _p(prim, u32p), _p(tuv), _p(stats, u64p)))
+        _chk(lib.amvpt_intersect(self._h, _p(o), _p(d), _p(maxt), C.c_uint32(n), C.c_int(int(any_hit) | (2 if q4 else 0) | (4 if flat else 0)), _p(prim, u32p), _p(tuv), _p(stats, u64p)))
         return prim, tuv, stats
 
     STATIC_MAX_RAYS = 65536      # AMVPT_STATIC_MAX_RAYS (include/amvpt.h)

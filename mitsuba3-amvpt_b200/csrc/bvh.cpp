@@ -174,6 +174,15 @@ void build_bvh(const Scene &s, float scene_scale, BvhOut &out) {
     if (np >= 65536 && n_threads > 1) bl.build_parallel(np, n_threads);
     else if (np) bl.build(0, np, 0);
     out.depth = np ? (uint32_t) bl.depth_of(0) : 1u;
+    {   // flat leaf list for small scenes (DScene::flat): leaves in tree (pre-)order
+        std::vector<float4> fl; bool ok = np > 0;
+        for (const TNode &n : bl.nodes) if (n.left < 0) {
+            if (fl.size() >= 64) { ok = false; break; }
+            int32_t code = (int32_t) ~((n.first << 3) | n.count); float cf; memcpy(&cf, &code, 4);
+            fl.push_back(make_float4(n.b.lo[0], n.b.lo[1], n.b.lo[2], cf)); fl.push_back(make_float4(n.b.hi[0], n.b.hi[1], n.b.hi[2], 0.f));
+        }
+        if (ok && env_int("AMVPT_FLAT", 1)) out.flat.swap(fl);
+    }
     if (AM_BVH_WIDTH == 2 && out.depth > AM_STACK_SIZE - 2) AM_THROW("BVH depth %u exceeds the traversal stack", out.depth);
 
     lap("tree");

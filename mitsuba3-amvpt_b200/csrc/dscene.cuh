@@ -236,6 +236,44 @@ template <bool ANY, bool Q4 = false> AM_D Hit intersect(const DScene &s, const R
     uint32_t best_prim = 0;
     float best = ray.maxt;
     SlabRay sr = slab_ray(ray.o, ray.d);
+#if AM_FLAT_LEAVES
+    if (!Q4 && s.n_flat && !n_nodes) {      // passes that count tree steps (stats, the roofline leg) walk the tree
+        // Small scene: every lane tests ALL leaf boxes in one loop of fixed length (no stack, no divergence: the binary tree's node loop runs
+        // at 11 of 32 lanes because rays need different numbers of steps), remembering which boxes it hit and which of them is nearest;
+        // then the lanes visit their leaves, nearest first, re-testing each further box against the hit distance found so far.
+        uint32_t mask = 0, k_near = 0; float t_near = AM_INF;
+        for (uint32_t k = 0; k < s.n_flat; ++k) {
+            const float4 lo = ldg4(s.flat + 2 * k), hi = ldg4(s.flat + 2 * k + 1); float tn;
+            if (slab(lo.x, hi.x, lo.y, hi.y, lo.z, hi.z, sr, best, &tn)) { mask |= 1u << k; if (tn < t_near) { t_near = tn; k_near = k; } }
+        }
+        bool first = true;
+        while (mask) {
+            uint32_t k;
+            if (first) { k = k_near; first = false; } else k = (uint32_t) __ffs((int) mask) - 1u;
+            mask &= ~(1u << k);
+            const float4 lo = ldg4(s.flat + 2 * k);
+            if (!ANY && h.tri != AM_NO_HIT) {        // a hit exists: is this box still in front of it?
+                const float4 hi = ldg4(s.flat + 2 * k + 1); float tn;
+                if (!slab(lo.x, hi.x, lo.y, hi.y, lo.z, hi.z, sr, best, &tn)) continue;
+            }
+            const uint32_t code = ~__float_as_uint(lo.w), first_tri = code >> 3, count = code & 7u;
+            for (uint32_t i = 0; i < count; ++i) {
+                const float4 *tp = s.tris + 3 * (size_t) (first_tri + i);
+                float4 a = ldg4(tp), b = ldg4(tp + 1), c = ldg4(tp + 2);
+                if (n_tris) (*n_tris)++;
+                float t, u, v;
+                if (moeller_trumbore(ray, v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), v3(c.x, c.y, c.z), &t, &u, &v)) {
+                    uint32_t prim = __float_as_uint(a.w);
+                    if (ANY) { h.t = t; h.u = u; h.v = v; h.tri = first_tri + i; return h; }
+                    if (h.tri == AM_NO_HIT || t < h.t || (t == h.t && prim > best_prim)) {
+                        h.t = t; h.u = u; h.v = v; h.tri = first_tri + i; best_prim = prim; best = t;
+                    }
+                }
+            }
+        }
+        return h;
+    }
+#endif
     int32_t stack[AM_STACK_SIZE]; int sp = 0;
     int32_t node = 0;
     stack[sp++] = AM_TRAVERSAL_DONE;

@@ -9,6 +9,9 @@
 #ifndef AM_FFMA2
 #define AM_FFMA2 0         /* 1: binary-tree nodes hold (lo.x, lo.y, hi.x, hi.y) and the slab test uses Blackwell's packed fma.rn.f32x2 (FFMA2) */
 #endif
+#ifndef AM_FLAT_LEAVES
+#define AM_FLAT_LEAVES 1   /* 1: intersect() uses DScene::flat when the scene has one */
+#endif
 #ifndef AM_SPECULATIVE
 #define AM_SPECULATIVE 0   /* 1: intersect() postpones the first leaf a lane finds and keeps descending until it holds two (dscene.cuh) */
 #endif
@@ -92,6 +95,9 @@ struct DScene {
     uint32_t env_level_off[12], env_level_width[12];
     float env_scale, env_patch_size[2], env_inv_patch_size[2]; uint32_t env_max_patch[2], pad3;
     float env_to_world[12], env_from_world[12];      // first three rows of to_world and of its inverse
+    // Small scenes (a tree with at most 32 leaves, e.g. the Cornell box: 19): the leaves' boxes as a flat list, (lo.xyz, leaf code), (hi.xyz, -)
+    // in tree order.  intersect() tests ALL of them in one loop without divergence, then visits the leaves whose box was hit (dscene.cuh).
+    const float4 *flat; uint32_t n_flat;
 };
 
 } // namespace amvpt

@@ -67,7 +67,8 @@ void load_image_rgb(const std::string &path, uint32_t *w, uint32_t *h, std::vect
 enum SchedulerMode { SCHED_WARP_BATCH = 0, SCHED_REGENERATE = 1, SCHED_STREAM = 2, SCHED_WAVEFRONT = 3, SCHED_AUTO = 4, SCHED_REUSE = 5 /* reported only */, SCHED_SPLIT = 6 };
 
 struct BvhOut { std::vector<float4> nodes, tris, tri_nrm; std::vector<uint32_t> prim_to_tri; uint32_t depth = 0;
-                std::vector<uint4> nodes_q4; uint32_t depth_q4 = 0; };     // nodes_q4: compressed 4-wide tree over the same leaves (empty = not built)
+                std::vector<uint4> nodes_q4; uint32_t depth_q4 = 0;
+                std::vector<float4> flat; };     // flat: the leaves' boxes of a tree with at most 32 leaves, two float4 each (DScene::flat), else empty     // nodes_q4: compressed 4-wide tree over the same leaves (empty = not built)
 struct RenderStats {
     double seconds = 0.0;            // device time of the pass loop (CUDA events)
     unsigned long long paths = 0, closest_rays = 0, shadow_rays = 0, nodes = 0, tris = 0, vertices = 0;

@@ -339,8 +339,9 @@ __global__ void intersect_kernel(const DScene s, const float *o, const float *d,
     if (i < n) {
         Ray r; r.o = v3(o[3 * i], o[3 * i + 1], o[3 * i + 2]); r.d = v3(d[3 * i], d[3 * i + 1], d[3 * i + 2]); r.maxt = maxt[i];
         const bool q4 = (any & 2) != 0 && s.nodes_q4 != nullptr;      // bit 1 of `any`: walk the compressed 4-wide tree
-        Hit h = (any & 1) ? (q4 ? intersect<true, true>(s, r, &st.nodes, &st.tris) : intersect<true>(s, r, &st.nodes, &st.tris))
-                          : (q4 ? intersect<false, true>(s, r, &st.nodes, &st.tris) : intersect<false>(s, r, &st.nodes, &st.tris));
+        uint32_t *cn = (any & 4) ? nullptr : &st.nodes, *ct = (any & 4) ? nullptr : &st.tris;      // bit 2 of `any`: no counters -> small scenes take the flat leaf list
+        Hit h = (any & 1) ? (q4 ? intersect<true, true>(s, r, cn, ct) : intersect<true>(s, r, cn, ct))
+                          : (q4 ? intersect<false, true>(s, r, cn, ct) : intersect<false>(s, r, cn, ct));
         prim[i] = h.tri == AM_NO_HIT ? AM_NO_HIT : __float_as_uint(s.tris[3 * (size_t) h.tri].w);
         if (tuv) { tuv[3 * i] = h.t; tuv[3 * i + 1] = h.u; tuv[3 * i + 2] = h.v; }
         if (any & 1) st.shadow++; else st.closest++;

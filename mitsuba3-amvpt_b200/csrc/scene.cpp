@@ -377,6 +377,7 @@ void Scene::commit(int dev) {
     d.tri_nrm = any_nrm ? upload(bvh.tri_nrm) : nullptr;
     { int v = 0; cudaDeviceGetAttribute(&v, cudaDevAttrMaxPersistingL2CacheSize, dev); l2_persist_max = (size_t) std::max(v, 0);
       cudaDeviceGetAttribute(&v, cudaDevAttrMaxAccessPolicyWindowSize, dev); l2_window_max = (size_t) std::max(v, 0); }
+    d.flat = bvh.flat.empty() ? nullptr : upload(bvh.flat); d.n_flat = (uint32_t) (bvh.flat.size() / 2);
     d.prim_to_tri = upload(bvh.prim_to_tri); d.meshes = upload(dm); d.bsdfs = upload(bsdfs); d.emitters = upload(emitters);
     // PerspectiveCamera::update_camera_transforms (perspective.cpp:173-199) members read by sample_surface: camera_to_sample
     // (inverse of sample_to_camera), Transform4f::inverse of to_world, normalization = 1 / area of the near-plane image rectangle

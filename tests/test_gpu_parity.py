@@ -133,6 +133,11 @@ def test_bvh_equals_brute_force_cbox(cbox):
     assert_bits(tuv[hit], rtuv[hit], "closest-hit t,u,v")
     occ, _, _ = s.intersect(ro, rd, mt, any_hit=True); rocc = o.ray_test(ro, rd, mt, brute=True)
     assert np.array_equal(occ != 0xffffffff, rocc != 0), "shadow-ray occlusion"
+    # the flat leaf list the render kernels use for small scenes (no counters requested): same hits
+    fprim, ftuv, fst = s.intersect(ro, rd, mt, flat=True)
+    assert_bits(fprim, rprim, "flat leaf list: closest-hit primitive"); assert_bits(ftuv[hit], rtuv[hit], "flat leaf list: t,u,v"); assert fst[0] == 0
+    focc, _, _ = s.intersect(ro, rd, mt, any_hit=True, flat=True)
+    assert np.array_equal(focc != 0xffffffff, rocc != 0), "flat leaf list: shadow-ray occlusion"
 
 
 def test_bvh_equals_brute_force_heightfield(hfield):
