@@ -228,12 +228,12 @@ AM_NOINLINE DirectionSample emitter_call(const DScene &s, const SI &si, V2 u, V3
 // OUTLINE = true calls the out-of-line copies above instead of inlining ray caster, emitter sampler and BSDF dispatch.
 // FIRST = true: the camera ray's hit and the first vertex's light sample (with its visibility) were computed by
 // primary_vertex_kernel and are read from prim[i], prim[m + i], prim[2 m + i] instead of being traced here.
-template <bool TAP, bool STATS, bool OUTLINE = false, bool FIRST = false, bool GEN = false> AM_D void path_bounce(const DScene &s, PathState &ps, TapCtx *tap, StatCtx *st,
+template <bool TAP, bool STATS, bool OUTLINE = false, bool FIRST = false, bool GEN = false, int ACCEL = 0> AM_D void path_bounce(const DScene &s, PathState &ps, TapCtx *tap, StatCtx *st,
                                                                                              const float4 *prim = nullptr, uint32_t pm = 0, uint32_t pi = 0) {
     uint32_t *cn = STATS ? &st->nodes : nullptr, *ct = STATS ? &st->tris : nullptr;
     Hit h;
     if (FIRST) { const float4 a = prim[pi]; h.t = a.x; h.u = a.y; h.v = a.z; h.tri = __float_as_uint(a.w); }
-    else h = OUTLINE ? trace_closest(s, ps.ray, STATS ? st : nullptr) : intersect<false>(s, ps.ray, cn, ct);
+    else h = OUTLINE ? trace_closest(s, ps.ray, STATS ? st : nullptr) : intersect<false, false, ACCEL>(s, ps.ray, cn, ct);
     if (STATS) { st->closest++; st->vertices++; }
     const DMesh *mesh;
     SI si = make_si(s, ps.ray, h, &mesh);
@@ -257,7 +257,7 @@ template <bool TAP, bool STATS, bool OUTLINE = false, bool FIRST = false, bool G
     DirectionSample ds; V3 em_weight = v3(0.f), wo = v3(0.f); ds.pdf = 0.f; ds.delta = false;
     if (active_em) {
         if (FIRST) { const float4 a = prim[(size_t) pm + pi], b = prim[2 * (size_t) pm + pi]; em_weight = v3(a.x, a.y, a.z); ds.pdf = a.w; ds.d = v3(b.x, b.y, b.z); }
-        else ds = OUTLINE ? emitter_call(s, si, es, &em_weight, STATS ? st : nullptr) : sample_emitter_direction<false, GEN>(s, si, es, &em_weight, cn, ct);
+        else ds = OUTLINE ? emitter_call(s, si, es, &em_weight, STATS ? st : nullptr) : sample_emitter_direction<false, GEN, ACCEL>(s, si, es, &em_weight, cn, ct);
         if (STATS) st->shadow++;
         active_em = ds.pdf != 0.f;
         wo = si.to_local(ds.d);

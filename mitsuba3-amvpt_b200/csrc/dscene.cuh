@@ -231,13 +231,15 @@ AM_D int32_t node_step_q4(const DScene &s, const SlabRay &r, float best, int32_t
 // "while-while" traversal: every lane first descends through inner nodes until it holds a leaf, the warp reconverges,
 // then the lanes intersect their leaves together -- the triangle test is the expensive, divergence-sensitive part.
 #define AM_TRAVERSAL_DONE ((int32_t) 0x80000000)      /* not a valid leaf code: first would be 2^28 - 1 */
-template <bool ANY, bool Q4 = false> AM_D Hit intersect(const DScene &s, const Ray &ray, uint32_t *n_nodes = nullptr, uint32_t *n_tris = nullptr) {
+// ACCEL = 1: the caller knows the scene has a flat leaf list and asks for no counters -- only that path is compiled in (the megakernel instantiation
+// for small scenes: no traversal stack, no tree code).
+template <bool ANY, bool Q4 = false, int ACCEL = 0> AM_D Hit intersect(const DScene &s, const Ray &ray, uint32_t *n_nodes = nullptr, uint32_t *n_tris = nullptr) {
     Hit h; h.t = AM_INF; h.u = 0.f; h.v = 0.f; h.tri = AM_NO_HIT;
     uint32_t best_prim = 0;
     float best = ray.maxt;
     SlabRay sr = slab_ray(ray.o, ray.d);
 #if AM_FLAT_LEAVES
-    if (!Q4 && s.n_flat && !n_nodes) {      // passes that count tree steps (stats, the roofline leg) walk the tree
+    if (ACCEL == 1 || (!Q4 && s.n_flat && !n_nodes)) {      // passes that count tree steps (stats, the roofline leg) walk the tree
         // Small scene: every lane tests ALL leaf boxes in one loop of fixed length (no stack, no divergence: the binary tree's node loop runs
         // at 11 of 32 lanes because rays need different numbers of steps), remembering which boxes it hit and which of them is nearest;
         // then the lanes visit their leaves, nearest first, re-testing each further box against the hit distance found so far.
@@ -273,6 +275,7 @@ template <bool ANY, bool Q4 = false> AM_D Hit intersect(const DScene &s, const R
         }
         return h;
     }
+    if (ACCEL == 1) return h;
 #endif
     int32_t stack[AM_STACK_SIZE]; int sp = 0;
     int32_t node = 0;
@@ -474,7 +477,7 @@ AM_D float env_pdf_direction(const DScene &s, V3 d) {
 // EnvironmentMapEmitter (envmap.cpp:419-462); then the visibility test.
 // DEFER = true leaves the visibility test to the caller: *shadow_out is the shadow ray to trace when the returned
 // ds.pdf != 0; an occluded sample then contributes nothing (the reference zeroes spec and ds.pdf, scene.cpp:333-342).
-template <bool DEFER, bool GEN = false> AM_D DirectionSample sample_emitter_direction(const DScene &s, const SI &ref, V2 sample, V3 *spec_out,
+template <bool DEFER, bool GEN = false, int ACCEL = 0> AM_D DirectionSample sample_emitter_direction(const DScene &s, const SI &ref, V2 sample, V3 *spec_out,
                                               uint32_t *n_nodes, uint32_t *n_tris, Ray *shadow_out = nullptr) {
     DirectionSample ds; ds.p = v3(0.f); ds.n = v3(0.f); ds.d = v3(0.f); ds.pdf = 0.f; ds.dist = 0.f; ds.delta = false;
     *spec_out = v3(0.f);
@@ -549,7 +552,7 @@ template <bool DEFER, bool GEN = false> AM_D DirectionSample sample_emitter_dire
     if (ds.pdf != 0.f) {
         Ray sr = spawn_ray_to(ref.p, ref.n, ds.p);
         if (DEFER) *shadow_out = sr;
-        else if (intersect<true>(s, sr, n_nodes, n_tris).tri != AM_NO_HIT) { spec = v3(0.f); ds.pdf = 0.f; }
+        else if (intersect<true, false, ACCEL>(s, sr, n_nodes, n_tris).tri != AM_NO_HIT) { spec = v3(0.f); ds.pdf = 0.f; }
     }
     *spec_out = spec;
     return ds;

@@ -9,6 +9,7 @@
 //   tap kernels          : parity taps (lanes, rays, BSDFs, leaf math) used by tests through the C ABI
 // Compiled with -fmad=false (see dmath.cuh).  Reference citations are relative to the upstream tree.
 #include "dpath.cuh"
+#include <cstdlib>
 
 namespace amvpt {
 
@@ -23,7 +24,11 @@ namespace amvpt {
 #define AM_RP_MIN_CTAS 5      // 96 registers -> 5 CTAs per SM: same-box A/B 1690 vs 1566 Mpaths/s on the Cornell quilt (profiles/r01_ab_min_ctas.txt)
 #endif
 // GEN = true: scenes with point / constant / environment-map emitters (dscene.cuh); the area-light-only instantiation keeps the short path.
-template <int MODE, bool STATS, bool GEN = false> __global__ void __launch_bounds__(128, AM_RP_MIN_CTAS)
+// ACCEL = 1: small scenes (DScene::flat), no counters: intersect() is compiled with the flat leaf list only -- no stack, no tree code.
+#ifndef AM_RP_FLAT_CTAS
+#define AM_RP_FLAT_CTAS 7     // 72 registers, 80 bytes of spills: same-box sweep on the Cornell quilt 5 / 6 / 7 / 8 CTAs per SM -> 1746 / 1858 / 1902 / 1855 Mpaths/s
+#endif
+template <int MODE, bool STATS, bool GEN = false, int ACCEL = 0> __global__ void __launch_bounds__(128, ACCEL == 1 ? AM_RP_FLAT_CTAS : AM_RP_MIN_CTAS)
 render_pass_kernel(const DScene s, const RenderParams p) {
     const unsigned lane_id = threadIdx.x & 31u;
     PathState ps; LaneSetup ls; ps.active = false;
@@ -58,7 +63,7 @@ render_pass_kernel(const DScene s, const RenderParams p) {
             }
             if (__all_sync(0xffffffffu, !ps.active && !has_result)) break;
         }
-        if (ps.active) path_bounce<false, STATS, false, false, GEN>(s, ps, nullptr, &st);
+        if (ps.active) path_bounce<false, STATS, false, false, GEN, ACCEL>(s, ps, nullptr, &st);
     }
     if (STATS) flush_stats(st, p.counters);
 }
@@ -228,6 +233,13 @@ void launch_render_pass(const DScene &s, const RenderParams &p, int mode, int sm
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, gfn, 128, 0); if (per_sm < 1) per_sm = 1;
         unsigned long long need = ((p.n_lanes + 31) / 32 + 3) / 4; unsigned g = (unsigned) (sm_count * per_sm); if (need < g) g = (unsigned) (need ? need : 1);
         if (stats) render_pass_kernel<1, true, true><<<g, 128, 0, stream>>>(s, p); else render_pass_kernel<1, false, true><<<g, 128, 0, stream>>>(s, p);
+        return;
+    }
+    if (AM_FLAT_LEAVES && mode == 1 && !stats && s.n_flat && !(getenv("AMVPT_FLAT_KERNEL") && atoi(getenv("AMVPT_FLAT_KERNEL")) == 0)) {
+        // small scene: the instantiation that holds the flat leaf list only
+        int per_sm = 0; cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, render_pass_kernel<1, false, false, 1>, 128, 0); if (per_sm < 1) per_sm = 1;
+        unsigned long long need = ((p.n_lanes + 31) / 32 + 3) / 4; unsigned g = (unsigned) (sm_count * per_sm); if (need < g) g = (unsigned) (need ? need : 1);
+        render_pass_kernel<1, false, false, 1><<<g, 128, 0, stream>>>(s, p);
         return;
     }
     // persistent grid: a whole number of CTAs per SM
