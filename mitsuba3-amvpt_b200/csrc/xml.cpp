@@ -120,6 +120,7 @@ struct Obj {
     }
 };
 
+void read_spd(const std::string &path, std::vector<double> &wl, std::vector<double> &val);     // defined below (spectrum_from_file)
 struct Loader {
     std::map<std::string, std::string> params; std::set<std::string> cli_params;
     std::vector<std::string> search;
@@ -272,9 +273,14 @@ struct Loader {
             // src/core/xml.cpp:777-833 + create_texture_from_spectrum (:1170-1268) in an RGB variant: a uniform value stays uniform
             // (inside an emitter it is the colour of a flat spectrum under the sRGB white point), wavelength:value pairs are integrated
             // against the CIE 1931 observer (reflectances also against D65) and become an sRGB colour
-            if (k.attr("filename")) err(k, "<spectrum filename=...> is not supported on this path (give wavelength:value pairs, a uniform value or <rgb>)");
-            auto tk = tokens(attr(k, "value")); v.kind = Value::Color;
             const bool within_emitter = o.cls == "emitter", unbounded = name == "eta" || name == "k" || name == "int_ior" || name == "ext_ior";
+            if (k.attr("filename")) {           // src/core/xml.cpp:805-815: spectrum_from_file, then the same conversion as wavelength:value pairs
+                std::vector<double> wl, val; read_spd(resolve(attr(k, "filename"), base), wl, val);
+                v.kind = Value::Color; spectrum_to_srgb(wl, val, within_emitter, unbounded, v.v);
+                if (name.empty()) err(k, "missing attribute \"name\" in <spectrum>");
+                put(k, name, std::move(v)); return;
+            }
+            auto tk = tokens(attr(k, "value")); v.kind = Value::Color;
             if (tk.empty()) err(k, "'spectrum' tag requires one of \"value\" or \"filename\" attributes");
             if (tk.size() == 1 && tk[0].find(':') == std::string::npos) {
                 const double c = to_f(k, tk[0]);

@@ -169,6 +169,11 @@ def test_conductor_material_presets(pkg):
     assert np.allclose(s.bsdf(0)["eta"], [0.143, 0.375, 1.442], atol=1e-3) and np.allclose(s.bsdf(0)["k"], [3.983, 2.386, 1.603], atol=1e-3)   # gold as the documentation tabulates it
     assert tuple(s.bsdf(3)["eta"]) == (0.0, 0.0, 0.0) and tuple(s.bsdf(3)["k"]) == (1.0, 1.0, 1.0)             # material = none: a perfect mirror
     assert s.bsdf(1)["type"] == "roughconductor" and s.bsdf(2)["twosided"]
+    # <spectrum filename="x.spd"> (src/core/xml.cpp:805-815): the file's pairs go through the same conversion as value="w:v ..." pairs
+    rows = [l.split() for l in open(os.path.join(SCENE_DIR, "ior", "Cu.k.spd")) if l.strip() and not l.lstrip().startswith("#")]
+    want = pkg.spectrum_to_srgb([float(r[0]) for r in rows], [float(r[1]) for r in rows], unbounded_name=True)
+    s4 = pkg.load_string(xml.replace('<string name="material" value="Au"/>', '<spectrum name="eta" value="0.2"/><spectrum name="k" filename="../../ior/Cu.k.spd"/>'), base_dir=base)
+    assert np.allclose(s4.bsdf(0)["k"], want, rtol=2e-6) and np.allclose(s4.bsdf(0)["eta"], 0.2)
     with pytest.raises(pkg.AmvptError, match="Should specify either"):
         pkg.load_string(xml.replace('<string name="material" value="Au"/>', '<string name="material" value="Au"/><rgb name="eta" value="1"/>'), base_dir=base)
     with pytest.raises(pkg.AmvptError, match="file does not exist"):
