@@ -22,6 +22,7 @@ struct HMesh {
     std::vector<float> pos, nrm;          // 3 floats per vertex; nrm empty = no vertex normals
     std::vector<uint32_t> faces;          // 3 indices per face
     int bsdf = 0, emitter = -1, flip_normals = 0;
+    bool had_uv = false;                  // the file carried texture coordinates (dropped: no textures on this path; see the anisotropy guard in xml.cpp)
     uint32_t prim_offset = 0;
     std::vector<float> pmf, cdf; float sum = 0.f, normalization = 0.f;
     uint32_t nfaces() const { return (uint32_t) (faces.size() / 3); }

@@ -135,7 +135,7 @@ void load_obj(const std::string &path, const M4d &to_world, bool face_normals, b
             }
         }
     }
-    (void) n_tex;
+    out.had_uv = n_tex != 0;
     size_t nv = keys.size(); out.pos.resize(3 * nv);
     bool want_normals = !face_normals;
     if (want_normals) out.nrm.assign(3 * nv, 0.f);
@@ -239,7 +239,9 @@ void load_ply(const std::string &path, const M4d &to_world, bool face_normals, H
                 if (e.props[k].list) fail("incompatible contents -- is this a triangle mesh?");
                 if (n == "x") ix[0] = (int) k; else if (n == "y") ix[1] = (int) k; else if (n == "z") ix[2] = (int) k;
                 else if (n == "nx") ix[3] = (int) k; else if (n == "ny") ix[4] = (int) k; else if (n == "nz") ix[5] = (int) k;
+                else if (n == "u" || n == "s" || n == "texture_u") ix[6] = (int) k; else if (n == "v" || n == "t" || n == "texture_v") ix[7] = (int) k;
             }
+            out.had_uv = ix[6] >= 0 && ix[7] >= 0;        // ply.cpp:224-243 (u, v or s, t); the values are dropped
             if (ix[0] < 0 || ix[1] < 0 || ix[2] < 0) fail("incompatible contents -- is this a triangle mesh?");
             have_normals = !face_normals && ix[3] >= 0 && ix[4] >= 0 && ix[5] >= 0;
             out.pos.resize(3 * e.count); if (have_normals) out.nrm.resize(3 * e.count);
@@ -362,6 +364,7 @@ void load_serialized(const std::string &path, int shape_index, const M4d &to_wor
     read_floats(&out.pos, 3);
     if (has_normals) read_floats(face_normals ? nullptr : &out.nrm, 3);
     if (has_uv) read_floats(nullptr, 2);                 // texture coordinates: no textures on this path
+    out.had_uv = has_uv;
     if (has_colors) read_floats(nullptr, 3);
     out.faces.resize((size_t) nf * 3); in.read(out.faces.data(), (size_t) nf * 12);
     for (uint32_t idx : out.faces) if (idx >= nv) fail("face index out of range");

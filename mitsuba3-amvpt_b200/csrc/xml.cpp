@@ -475,6 +475,11 @@ struct Builder {
         }
         if (bs) m.bsdf = bsdf(bs);
         else { DBsdf b{}; b.type = BSDF_DIFFUSE; float r = emits ? 0.f : .5f; b.reflectance[0] = b.reflectance[1] = b.reflectance[2] = r; m.bsdf = sc.add_bsdf(b); }   // shape.cpp:64-70
+        // Mesh::compute_surface_interaction (mesh.cpp:1484-1510) derives dp_du / dp_dv -- the orientation of the shading frame about the normal -- from
+        // the texture coordinates when the mesh has them; this path drops them and always uses coordinate_system(n).  For isotropic BSDFs the two
+        // are the same distribution (the golden Z-tests on the UV-mapped sphere pass); an anisotropic lobe would point elsewhere: refuse it.
+        if (bs && m.had_uv) { const DBsdf &b = sc.bsdfs[m.bsdf]; if ((b.type == BSDF_ROUGHCONDUCTOR || b.type == BSDF_ROUGHDIELECTRIC) && b.alpha_u != b.alpha_v)
+            AM_THROW("%s: anisotropic roughness (alpha_u != alpha_v) on a mesh with texture coordinates follows the UV parameterisation in the reference, which this path does not keep", o.where.c_str()); }
         o.check_unqueried();
         sc.add_mesh(std::move(m), emits ? radiance : nullptr);
     }

@@ -193,3 +193,18 @@ def test_ply_ascii_and_big_endian(pkg, scenes, tmp_path):
         assert m["normals"] is not None and np.allclose(np.linalg.norm(m["normals"], axis=1), 1, atol=1e-6)   # recomputed (ply.cpp:444-449)
     assert np.array_equal(out[0]["normals"], out[1]["normals"]) and np.array_equal(out[1]["normals"], out[2]["normals"])
     assert np.allclose(out[0]["normals"][0], [0, 0, 1])
+
+
+def test_anisotropic_bsdf_on_uv_mapped_mesh_is_refused(pkg, tmp_path):
+    """The reference orients the shading frame of a UV-mapped mesh along its texture coordinates (mesh.cpp:1484-1510); this path drops them, which
+    is the same distribution for isotropic lobes only: the loader refuses the anisotropic case instead of rendering it differently."""
+    (tmp_path / "uv.obj").write_text("v 0 0 0\nv 1 0 0\nv 0 1 0\nvt 0 0\nvt 1 0\nvt 0 1\nf 1/1 2/2 3/3\n")
+    (tmp_path / "plain.obj").write_text("v 0 0 0\nv 1 0 0\nv 0 1 0\nf 1 2 3\n")
+    xml = """<scene version="3.0.0"><sensor type="perspective"><film type="hdrfilm"><integer name="width" value="8"/><integer name="height" value="8"/></film></sensor>
+      <shape type="obj"><string name="filename" value="$mesh"/>
+        <bsdf type="roughconductor"><float name="alpha_u" value="$au"/><float name="alpha_v" value="0.3"/></bsdf>
+        <emitter type="area"><rgb name="radiance" value="1"/></emitter></shape></scene>"""
+    pkg.load_string(xml, base_dir=str(tmp_path), mesh="uv.obj", au="0.3")            # isotropic: fine
+    pkg.load_string(xml, base_dir=str(tmp_path), mesh="plain.obj", au="0.05")        # anisotropic without texture coordinates: fine
+    with pytest.raises(pkg.AmvptError, match="anisotropic roughness"):
+        pkg.load_string(xml, base_dir=str(tmp_path), mesh="uv.obj", au="0.05")
