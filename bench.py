@@ -177,7 +177,9 @@ def roofline(pkg, s, args, spp, sched_arg, clk, device):
         kernel = "render_pass_kernel"; b_path = 16.0 + bvh_bytes_per_path; bound = "issue"
         per_launch_s = ks["seconds"] / ks["launches"]; paths_per_launch = ks["paths"] / ks["launches"]; share = 1.0
         note = ("persistent megakernel, path state in registers: the only HBM bytes are the film splat (16 B/path); BVH bytes are served by L1 for the Cornell box. "
-                "Bound by SM issue slots x lane utilisation (ncu), so `achieved`/`peak` are warp instructions per second; the hbm / l2 objects give the byte lines of SURVEY sec.8d")
+                "Bound by SM issue slots x lane utilisation (ncu), so `achieved`/`peak` are warp instructions per second; the hbm / l2 objects give the byte lines of SURVEY sec.8d. "
+                "Scenes whose tree has at most 32 leaves (the Cornell box) are traced through the flat leaf list (32 B per leaf box, all leaves tested per ray); "
+                "bytes_per_path / nodes_per_ray come from the counter pass, which walks the tree")
     alg_bytes = paths_per_launch * b_path
     byte_rate = alg_bytes / per_launch_s / 1e9
     # L2 denominator: live micro-benchmark (32 MB buffer, 16-byte loads)
